@@ -1,0 +1,243 @@
+"""ctypes binding of the CPU oracle (oracle/libpmc_oracle.so).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, by bench.py's cpu_baseline /
+``--impl reference`` leg and by ``__graft_entry__.smoke()`` as the checker.
+The product package never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int)
+c_lp = C.POINTER(C.c_longlong)
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "libpmc_oracle.so")
+        if not os.path.exists(path):
+            build()
+        _LIB = C.CDLL(path)
+        L = _LIB
+        L.pmco_create.restype = C.c_void_p
+        L.pmco_last_error.restype = C.c_char_p
+        L.pmco_get_next_id.restype = C.c_longlong
+        L.pmco_get_rel_humid.restype = C.c_double
+        L.pmco_kernel_brown.restype = C.c_double
+        L.pmco_kernel_brown.argtypes = [C.c_double] * 6
+        L.pmco_philox_uniform.restype = C.c_double
+        L.pmco_poisson_pmf.restype = C.c_double
+        L.pmco_poisson_pmf.argtypes = [C.c_double, C.c_int]
+        L.pmco_binomial_pmf.restype = C.c_double
+        L.pmco_binomial_pmf.argtypes = [C.c_int, C.c_double, C.c_int]
+        L.pmco_mt_u32.restype = C.c_uint
+    return _LIB
+
+
+def _p(a, ct):
+    return None if a is None else a.ctypes.data_as(C.POINTER(ct))
+
+
+def _f64(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _i64(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.int64)
+
+
+KERNEL_ADDITIVE, KERNEL_CONSTANT, KERNEL_BROWN, KERNEL_ZERO = 2, 3, 4, 5
+WEIGHT_NONE, WEIGHT_POWER = 1, 2
+
+
+class AeroData:
+    """aero_data_t (aero_data.F90:55-93): species table read by the path."""
+
+    def __init__(self, density, kappa=None, molec_weight=None, num_ions=None, i_water=0, names=None):
+        self.density = _f64(density)
+        n = len(self.density)
+        self.n_spec = n
+        self.kappa = _f64(kappa if kappa is not None else np.zeros(n))
+        self.molec_weight = _f64(molec_weight if molec_weight is not None else np.full(n, 18e-3))
+        self.num_ions = _i32(num_ions if num_ions is not None else np.zeros(n))
+        self.i_water = int(i_water)
+        self.names = names
+
+
+class Oracle:
+    """A domain of independent grid cells, each an aero_state_t + env_state_t."""
+
+    def __init__(self, n_cells, data, n_group=1, n_class=1, n_part_ideal=1000.0, rng="philox", seed=1,
+                 n_cells_global=None, global_cell=None):
+        L = lib()
+        self.L = L
+        self.n_cells = n_cells
+        self.data = data
+        self.n_group, self.n_class = n_group, n_class
+        gc = _i64(global_cell) if global_cell is not None else None
+        self.h = C.c_void_p(L.pmco_create(
+            C.c_int(n_cells), C.c_int(data.n_spec), _p(data.density, C.c_double), _p(data.kappa, C.c_double),
+            _p(data.molec_weight, C.c_double), _p(data.num_ions, C.c_int), C.c_int(data.i_water),
+            C.c_int(n_group), C.c_int(n_class), C.c_double(n_part_ideal), C.c_int(0 if rng == "philox" else 1),
+            C.c_uint(seed), C.c_longlong(n_cells_global if n_cells_global is not None else n_cells),
+            _p(gc, C.c_longlong)))
+
+    def __del__(self):
+        try:
+            self.L.pmco_destroy(self.h)
+        except Exception:
+            pass
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise RuntimeError("oracle error %d: %s" % (rc, self.L.pmco_last_error(self.h).decode()))
+
+    def set_cell(self, cell, vol, wgroup=None, wclass=None, ids=None, n_primary=None, hyst=None, lct=None, gct=None):
+        vol = _f64(vol)  # [S][n]
+        assert vol.ndim == 2 and vol.shape[0] == self.data.n_spec
+        n = vol.shape[1]
+        a = [_i32(wgroup), _i32(wclass), _i64(ids), _i32(n_primary), _i32(hyst), _f64(lct), _f64(gct)]
+        self._chk(self.L.pmco_set_cell(self.h, C.c_int(cell), C.c_int(n), _p(vol, C.c_double), _p(a[0], C.c_int),
+                                       _p(a[1], C.c_int), _p(a[2], C.c_longlong), _p(a[3], C.c_int),
+                                       _p(a[4], C.c_int), _p(a[5], C.c_double), _p(a[6], C.c_double)))
+
+    def count(self, cell):
+        return int(self.L.pmco_cell_count(self.h, C.c_int(cell)))
+
+    def get_cell(self, cell):
+        n = self.count(cell)
+        S = self.data.n_spec
+        out = dict(vol=np.zeros((S, n)), wgroup=np.zeros(n, np.int32), wclass=np.zeros(n, np.int32),
+                   id=np.zeros(n, np.int64), n_primary=np.zeros(n, np.int32), hyst=np.zeros(n, np.int32),
+                   lct=np.zeros(n), gct=np.zeros(n))
+        self.L.pmco_get_cell(self.h, C.c_int(cell), _p(out["vol"], C.c_double), _p(out["wgroup"], C.c_int),
+                             _p(out["wclass"], C.c_int), _p(out["id"], C.c_longlong), _p(out["n_primary"], C.c_int),
+                             _p(out["hyst"], C.c_int), _p(out["lct"], C.c_double), _p(out["gct"], C.c_double))
+        return out
+
+    def set_weights(self, cell, wtype, magnitude, exponent):
+        t, m, e = _i32(wtype).ravel(), _f64(magnitude).ravel(), _f64(exponent).ravel()
+        self.L.pmco_set_weights(self.h, C.c_int(cell), _p(t, C.c_int), _p(m, C.c_double), _p(e, C.c_double))
+
+    def get_weights(self, cell):
+        k = self.n_group * self.n_class
+        t, m, e = np.zeros(k, np.int32), np.zeros(k), np.zeros(k)
+        self.L.pmco_get_weights(self.h, C.c_int(cell), _p(t, C.c_int), _p(m, C.c_double), _p(e, C.c_double))
+        return t, m, e
+
+    def set_env(self, cell, T=288.0, p=1e5, RH=0.5, rrho=1.0, cell_volume=1.0, elapsed=0.0):
+        self.L.pmco_set_env(self.h, C.c_int(cell), C.c_double(T), C.c_double(p), C.c_double(RH), C.c_double(rrho),
+                            C.c_double(cell_volume), C.c_double(elapsed))
+
+    def set_next_id(self, cell, v):
+        self.L.pmco_set_next_id(self.h, C.c_int(cell), C.c_longlong(v))
+
+    def sort(self, cell, force_resort=True, physical=True):
+        self._chk(self.L.pmco_sort(self.h, C.c_int(cell), C.c_int(int(force_resort)), C.c_int(int(physical))))
+
+    def grid(self, cell, cap=512):
+        nb, gmin, gmax = C.c_int(0), C.c_double(0), C.c_double(0)
+        edges = np.zeros(cap)
+        self.L.pmco_get_grid(self.h, C.c_int(cell), C.byref(nb), C.byref(gmin), C.byref(gmax), _p(edges, C.c_double),
+                             C.c_int(cap))
+        return nb.value, gmin.value, gmax.value, edges[: nb.value + 1].copy()
+
+    def bins(self, cell):
+        out = np.zeros(self.count(cell), np.int32)
+        rc = self.L.pmco_get_bins(self.h, C.c_int(cell), _p(out, C.c_int))
+        assert rc == 0
+        return out
+
+    def bin_counts(self, cell):
+        nb = self.grid(cell)[0]
+        out = np.zeros((self.n_class, nb), np.int32)
+        self.L.pmco_get_bin_counts(self.h, C.c_int(cell), _p(out, C.c_int))
+        return out
+
+    def kernel_bounds(self, cell, kernel_type):
+        nb = self.grid(cell)[0]
+        kmin, kmax = np.zeros((nb, nb)), np.zeros((nb, nb))  # [b2][b1]
+        self._chk(self.L.pmco_kernel_bounds(self.h, C.c_int(cell), C.c_int(kernel_type), _p(kmin, C.c_double),
+                                            _p(kmax, C.c_double)))
+        return kmin, kmax
+
+    def mc_coag(self, cell, kernel_type, del_t, step=0):
+        st = np.zeros(3, np.int32)
+        self._chk(self.L.pmco_mc_coag(self.h, C.c_int(cell), C.c_int(kernel_type), C.c_double(del_t), C.c_uint(step),
+                                      _p(st, C.c_int)))
+        return int(st[0]), int(st[1]), int(st[2])
+
+    def mc_coag_all(self, kernel_type, del_t, step=0, n_threads=1):
+        tot = np.zeros(2, np.int64)
+        rc = self.L.pmco_mc_coag_all(self.h, C.c_int(kernel_type), C.c_double(del_t), C.c_uint(step),
+                                     C.c_int(n_threads), _p(tot, C.c_longlong))
+        assert rc == 0, rc
+        return int(tot[0]), int(tot[1])
+
+    def rebalance(self, cell, allow_doubling=True, allow_halving=True, step=0):
+        self._chk(self.L.pmco_rebalance(self.h, C.c_int(cell), C.c_int(int(allow_doubling)),
+                                        C.c_int(int(allow_halving)), C.c_uint(step)))
+
+    def scale_weight(self, cell, g, c, ratio, allow_doubling=True, allow_halving=True, step=0):
+        self._chk(self.L.pmco_scale_weight(self.h, C.c_int(cell), C.c_int(g), C.c_int(c), C.c_double(ratio),
+                                           C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step)))
+
+
+def kernel_brown(v1, d1, v2, d2, T, p):
+    return lib().pmco_kernel_brown(v1, d1, v2, d2, T, p)
+
+
+def bin_grid_make(n_bin, gmin, gmax):
+    e, c = np.zeros(n_bin + 1), np.zeros(n_bin)
+    lib().pmco_bin_grid_make(C.c_int(n_bin), C.c_double(gmin), C.c_double(gmax), _p(e, C.c_double), _p(c, C.c_double))
+    return e, c
+
+
+def bin_grid_find(n_bin, gmin, gmax, r):
+    r = _f64(r)
+    out = np.zeros(len(r), np.int32)
+    lib().pmco_bin_grid_find(C.c_int(n_bin), C.c_double(gmin), C.c_double(gmax), C.c_int(len(r)), _p(r, C.c_double),
+                             _p(out, C.c_int))
+    return out
+
+
+def philox_uniform(seed, cell, step, phase, a, b, j):
+    return lib().pmco_philox_uniform(C.c_uint(seed), C.c_uint(cell), C.c_uint(step), C.c_uint(phase), C.c_uint(a),
+                                     C.c_uint(b), C.c_uint(j))
+
+
+def philox_raw(ctr, key):
+    c = np.asarray(ctr, np.uint32)
+    k = np.asarray(key, np.uint32)
+    o = np.zeros(4, np.uint32)
+    lib().pmco_philox_raw(_p(c, C.c_uint), _p(k, C.c_uint), _p(o, C.c_uint))
+    return o
+
+
+def sample_poisson(mean, n_samp, seed=1, rng="mt", hist_len=200):
+    h = np.zeros(hist_len, np.int64)
+    lib().pmco_sample_poisson(C.c_double(mean), C.c_int(n_samp), C.c_uint(seed), C.c_int(0 if rng == "philox" else 1),
+                              _p(h, C.c_longlong), C.c_int(hist_len))
+    return h
+
+
+def sample_binomial(n, p, n_samp, seed=1, rng="mt", hist_len=200):
+    h = np.zeros(hist_len, np.int64)
+    lib().pmco_sample_binomial(C.c_int(n), C.c_double(p), C.c_int(n_samp), C.c_uint(seed),
+                               C.c_int(0 if rng == "philox" else 1), _p(h, C.c_longlong), C.c_int(hist_len))
+    return h
