@@ -1,0 +1,138 @@
+/* pmcgpu.h -- C ABI of the B200-native PartMC per-grid-cell aerosol step.
+ *
+ * This is the drop-in boundary: a Fortran host (WRF-PartMC's interface/ layer)
+ * binds these symbols through ISO_C_BINDING (wrf-partmc_b200/fortran/pmc_gpu.F90,
+ * INTEGRATION.md) in place of its serial per-cell loops.  Conventions follow the
+ * reference's own C boundary (partmc/src/condense.F90:183-195 <->
+ * condense_solver.c:84): scalars by value, arrays as plain pointers, int return
+ * code, 0 = success; a non-zero code is what the Fortran side hands to
+ * die_msg(code, ...) (util.F90:134).
+ *
+ * All particles of one WRF patch live in device memory behind the opaque
+ * handle.  Cell order everywhere is WRF memory order: i fastest, then k, then j
+ * (aero_states(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je),
+ * interface/wrf_pmc_driver.F90:46-87), cell = i + nx*(k + nz*j), zero based.
+ * Weight arrays are (group, class) with group fastest, like
+ * aero_weight_array_t%weight(n_group, n_class) (aero_weight_array.F90:35-39).
+ * Bins, classes and groups are 1-based in every array that crosses this
+ * boundary.  There is no CPU fallback: every entry point fails with
+ * PMCGPU_ERR_CUDA when no CUDA device is usable.
+ */
+#ifndef PMCGPU_H
+#define PMCGPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pmcgpu_ctx pmcgpu_ctx;
+
+enum {
+  PMCGPU_OK = 0,
+  PMCGPU_ERR_CUDA = 1,            /* CUDA runtime error (see pmcgpu_last_error) */
+  PMCGPU_ERR_ARG = 2,             /* bad argument */
+  PMCGPU_ERR_CAPACITY = 3,        /* a cell outgrew cell_capacity */
+  PMCGPU_ERR_BIN_RANGE = 134572570, /* coagulated particle outside bin grid (aero_sorted.F90:434 die_msg code) */
+  PMCGPU_ERR_NBINS = 5,           /* adaptive grid needs more than max_bins bins */
+  PMCGPU_ERR_ACCEL = 6,           /* try_per_particle_coag would be taken (coagulation.F90:150), not built yet */
+  PMCGPU_ERR_CONDENSE = 7,        /* condensation integrator failed (condense.F90:331-363 codes) */
+  PMCGPU_ERR_PROB = 414897881,    /* transport probabilities invalid (wrf_pmc_trans.F90:702-771 assert codes) */
+  PMCGPU_ERR_NCCL = 9
+};
+
+/* coag_kernel.F90:24-40 type codes */
+enum { PMCGPU_KERNEL_ADDITIVE = 2, PMCGPU_KERNEL_CONSTANT = 3, PMCGPU_KERNEL_BROWN = 4, PMCGPU_KERNEL_ZERO = 5 };
+/* aero_weight.F90:25-30 */
+enum { PMCGPU_WEIGHT_NONE = 1, PMCGPU_WEIGHT_POWER = 2, PMCGPU_WEIGHT_MFA = 3 };
+
+typedef struct {
+  /* aero_data_t (aero_data.F90:55-93) */
+  int n_spec;
+  const double* density;       /* [n_spec] kg/m^3 */
+  const double* kappa;         /* [n_spec] */
+  const double* molec_weight;  /* [n_spec] kg/mol */
+  const int* num_ions;         /* [n_spec] */
+  int i_water;                 /* 1-based, 0 = none */
+  /* aero_weight_array_t dims; WRF uses n_group = 1 (wrf_pmc_init.F90:251-254) */
+  int n_group, n_class;
+  /* patch geometry (cells owned by this process) and the global domain */
+  int nx, nz, ny;              /* local cells: i, k, j extents */
+  int global_nx, global_ny;    /* global horizontal extents */
+  int i_offset, j_offset;      /* global index of local (0,0) */
+  int periodic_x, periodic_y;
+  double n_part_ideal;         /* grid%num_particles, split evenly over (group, class) (aero_state.F90:241) */
+  int cell_capacity;           /* particle slots per cell (>= 2 * n_part_ideal + slack) */
+  int max_bins;                /* capacity of the per-cell adaptive bin grid (<= 255) */
+  unsigned int seed;           /* random_seed (wrf_pmc_init.F90:131) */
+  int device;                  /* CUDA device ordinal */
+} pmcgpu_config;
+
+/* ---- lifetime -------------------------------------------------------- */
+int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out);
+int pmcgpu_destroy(pmcgpu_ctx* ctx);
+const char* pmcgpu_last_error(pmcgpu_ctx* ctx);
+/* number of kernels this library has launched so far (bench.py's gpu_launches) */
+long long pmcgpu_launch_count(pmcgpu_ctx* ctx);
+/* the CUDA stream every kernel of this context is launched on (for event timing) */
+void* pmcgpu_stream(pmcgpu_ctx* ctx);
+int pmcgpu_synchronize(pmcgpu_ctx* ctx);
+
+/* ---- aero_state upload / download (host SoA views) --------------------
+ * cell_count[n_cells]; the per-particle arrays are the concatenation of all
+ * cells in cell order, N = sum(cell_count).  vol is species-major: vol[s*N + p].
+ * Any of wgroup..gct may be NULL on upload (defaults: group 1, class 1, id 0,
+ * n_primary 1, hyst 0, times 0). */
+int pmcgpu_set_particles(pmcgpu_ctx* ctx, const int* cell_count, const double* vol, const int* wgroup,
+                         const int* wclass, const int64_t* id, const int* n_primary, const int* hyst,
+                         const double* least_create_time, const double* greatest_create_time);
+int pmcgpu_get_counts(pmcgpu_ctx* ctx, int* cell_count);
+int pmcgpu_get_particles(pmcgpu_ctx* ctx, long long n_total, double* vol, int* wgroup, int* wclass, int64_t* id,
+                         int* n_primary, int* hyst, double* least_create_time, double* greatest_create_time);
+/* per-cell id counters (aero_particle.F90:64 next_id, one per cell on the device) */
+int pmcgpu_set_next_id(pmcgpu_ctx* ctx, const int64_t* next_id);
+int pmcgpu_get_next_id(pmcgpu_ctx* ctx, int64_t* next_id);
+/* aero_weight_array per cell: [n_cells][n_class][n_group] */
+int pmcgpu_set_weights(pmcgpu_ctx* ctx, const int* type, const double* magnitude, const double* exponent);
+int pmcgpu_get_weights(pmcgpu_ctx* ctx, int* type, double* magnitude, double* exponent);
+/* env_state per cell (env_state.F90:29-76; wrf_to_partmc, wrf_pmc_driver.F90:576-644). NULL = keep. */
+int pmcgpu_set_env(pmcgpu_ctx* ctx, const double* temp, const double* pressure, const double* rel_humid,
+                   const double* inverse_density, const double* cell_volume);
+int pmcgpu_get_rel_humid(pmcgpu_ctx* ctx, double* rel_humid);
+
+/* ---- the path ---------------------------------------------------------- */
+/* aero_state_sort (aero_state.F90:3218) for every cell: adaptive bin grid
+ * (aero_sorted.F90:214-373), bin of every particle (bin_grid.F90:143), and the
+ * (class, bin)-ordered particle layout that replaces integer_rmap2. */
+int pmcgpu_aero_state_sort(pmcgpu_ctx* ctx);
+/* est_k_minmax_binned_unweighted (coag_kernel.F90:253) for cells whose bounds are stale. */
+int pmcgpu_kernel_bounds(pmcgpu_ctx* ctx, int coag_kernel_type);
+/* mc_coag (coagulation.F90:43) for every cell.  tot_n_samp / tot_n_coag are
+ * per-cell outputs [n_cells], may be NULL.  step addresses the random draws. */
+int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned int step, int* tot_n_samp,
+                   int* tot_n_coag);
+/* aero_state_rebalance (aero_state.F90:1765) for every cell. */
+int pmcgpu_aero_state_rebalance(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned int step);
+/* scenario_update_aero_state, WRF branch (scenario.F90:331-334): awa *= old_rrho / rrho */
+int pmcgpu_update_density(pmcgpu_ctx* ctx, const double* new_inverse_density);
+/* partmc_to_wrf (wrf_pmc_driver.F90:1704-1719): out[cell*n_class + c] = max(count*magnitude*alt, 1e-16) */
+int pmcgpu_num_conc_by_class(pmcgpu_ctx* ctx, float* out);
+
+/* ---- inspection (parity tests) ----------------------------------------- */
+int pmcgpu_get_grid(pmcgpu_ctx* ctx, int* n_bin, double* grid_min, double* grid_max); /* [n_cells] each */
+int pmcgpu_get_bins(pmcgpu_ctx* ctx, long long n_total, int* bin_of_particle);        /* packed like particles */
+int pmcgpu_get_bin_counts(pmcgpu_ctx* ctx, int* counts); /* [n_cells][n_class][max_bins] */
+int pmcgpu_get_kernel_max(pmcgpu_ctx* ctx, int cell, double* kmax); /* [n_bin][n_bin], (b1,b2) at [(b2-1)*n_bin+b1-1] */
+int pmcgpu_get_cell_status(pmcgpu_ctx* ctx, int* status); /* [n_cells] first error per cell */
+/* stand-alone evaluations of device functions, for known-answer tests */
+int pmcgpu_eval_kernel_brown(pmcgpu_ctx* ctx, int n, const double* v1, const double* d1, const double* v2,
+                             const double* d2, const double* temp, const double* pressure, double* out);
+int pmcgpu_eval_philox(pmcgpu_ctx* ctx, int n, const unsigned int* cell, const unsigned int* step,
+                       const unsigned int* phase, const unsigned int* a, const unsigned int* b,
+                       const unsigned int* j, double* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PMCGPU_H */

@@ -1,0 +1,231 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU
+oracle on the same seeded inputs.  Bar: bit-exact for bins, orders, ids, counts
+and volumes (sums of IEEE doubles); 1e-10 relative for kernel / majorant values."""
+import numpy as np
+import pytest
+
+import common
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import wrf_partmc_b200 as W
+    from oracle import oracle as O
+    return W, O
+
+
+def test_philox_device_equals_oracle(mods):
+    W, O = mods
+    g = W.PartMCGPU(W.AeroData([1000.0]), seed=12345)
+    rng = np.random.default_rng(0)
+    n = 4096
+    a = [rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32) for _ in range(5)]
+    a[1] = (a[1] >> 5).astype(np.uint32)  # step < 2^27
+    a[2] = (a[2] % 9).astype(np.uint32)
+    j = rng.integers(0, 64, n).astype(np.uint32)
+    dev = g.eval_philox(a[0], a[1], a[2], a[3], a[4], j)
+    ref = np.array([O.philox_uniform(12345, int(a[0][i]), int(a[1][i]), int(a[2][i]), int(a[3][i]), int(a[4][i]),
+                                     int(j[i])) for i in range(n)])
+    assert np.array_equal(dev, ref)
+    assert dev.min() >= 0.0 and dev.max() < 1.0
+
+
+def test_kernel_brown_device_vs_oracle(mods):
+    """coag_kernel_brown.F90:111-197, 1e-10 relative (north star)."""
+    W, O = mods
+    g = W.PartMCGPU(W.AeroData([1000.0]))
+    rng = np.random.default_rng(1)
+    n = 20000
+    r1, r2 = 10 ** rng.uniform(-9, -5, n), 10 ** rng.uniform(-9, -5, n)
+    v1, v2 = 4 * np.pi * r1 ** 3 / 3, 4 * np.pi * r2 ** 3 / 3
+    d1, d2 = rng.uniform(1000, 2600, n), rng.uniform(1000, 2600, n)
+    T, P = rng.uniform(230, 315, n), rng.uniform(3e4, 1.05e5, n)
+    dev = g.eval_kernel_brown(v1, d1, v2, d2, T, P)
+    ref = np.array([O.kernel_brown(v1[i], d1[i], v2[i], d2[i], T[i], P[i]) for i in range(n)])
+    rel = np.abs(dev - ref) / np.abs(ref)
+    assert rel.max() < 1e-10, rel.max()
+
+
+@pytest.mark.parametrize("n_spec,n_class,n_per,n_cells", [(1, 1, 1000, 6), (3, 2, 700, 9), (20, 3, 400, 5),
+                                                            (1, 1, 40000, 1)])
+def test_sort_bit_exact(mods, n_spec, n_class, n_per, n_cells):
+    """aero_state_sort: grid (n_bin, min, max), bin of every particle, per-(class, bin)
+    counts and the permuted particle order all equal the oracle's, bit for bit.
+    Includes a ragged population and an empty cell."""
+    W, O = mods
+    case = common.make_cells(n_cells, n_per, n_spec=n_spec, n_class=n_class, seed=20 + n_spec)
+    g = common.gpu_from_case(W, case)
+    o = common.oracle_from_case(O, case)
+    g.aero_state_sort()
+    nb, gmin, gmax = g.grid()
+    bins = g.bins()
+    bc = g.bin_counts()
+    off = np.concatenate([[0], np.cumsum(g.counts())])
+    for c in range(n_cells):
+        o.sort(c, force_resort=True, physical=True)
+        onb, omin, omax, _ = o.grid(c)
+        assert nb[c] == onb
+        if onb == 0:
+            assert case["counts"][c] == 0
+            continue
+        assert gmin[c] == omin and gmax[c] == omax
+        assert np.array_equal(bins[off[c]:off[c + 1]], o.bins(c))
+        assert np.array_equal(bc[c, :, :onb], o.bin_counts(c))
+        assert bc[c, :, onb:].sum() == 0
+    common.assert_same_population(g, o, case)
+    # idempotence: sorting a sorted state changes nothing
+    before = g.get_particles()
+    g.aero_state_sort()
+    after = g.get_particles()
+    for k in before:
+        assert np.array_equal(before[k], after[k])
+
+
+def test_sort_keeps_grid_until_safety_factor(mods):
+    """aero_sorted.F90:338-347: the grid is remade only when a particle comes within x3 of an edge."""
+    W, O = mods
+    case = common.make_cells(2, 300, seed=4, ragged=False)
+    g = common.gpu_from_case(W, case)
+    o = common.oracle_from_case(O, case)
+    g.aero_state_sort()
+    for c in range(2):
+        o.sort(c)
+    nb0, gmin0, gmax0 = g.grid()
+    # grow every particle of cell 0 by x2.5 in radius: still inside the x3 margin of a x10 over-extension
+    P = g.get_particles()
+    vol = P["vol"].copy()
+    n0 = P["count"][0]
+    vol[:, :n0] *= 2.5 ** 3
+    g.set_particles(P["count"], vol, P["wgroup"], P["wclass"], P["id"], P["n_primary"], P["hyst"], P["lct"], P["gct"])
+    q = o.get_cell(0)
+    o.set_cell(0, q["vol"] * 2.5 ** 3, q["wgroup"], q["wclass"], q["id"], q["n_primary"], q["hyst"], q["lct"], q["gct"])
+    g.aero_state_sort()
+    o.sort(0)
+    nb1, gmin1, gmax1 = g.grid()
+    assert (nb1[0], gmin1[0], gmax1[0]) == (nb0[0], gmin0[0], gmax0[0]) == o.grid(0)[:3]
+    # x2 more crosses the margin -> new grid, identical to the oracle's
+    P = g.get_particles()
+    vol = P["vol"].copy()
+    vol[:, :n0] *= 2.0 ** 3
+    g.set_particles(P["count"], vol, P["wgroup"], P["wclass"], P["id"], P["n_primary"], P["hyst"], P["lct"], P["gct"])
+    q = o.get_cell(0)
+    o.set_cell(0, q["vol"] * 2.0 ** 3, q["wgroup"], q["wclass"], q["id"], q["n_primary"], q["hyst"], q["lct"], q["gct"])
+    g.aero_state_sort()
+    o.sort(0)
+    nb2, gmin2, gmax2 = g.grid()
+    assert (nb2[0], gmin2[0], gmax2[0]) == o.grid(0)[:3]
+    assert gmax2[0] != gmax0[0]
+    common.assert_same_population(g, o, case)
+
+
+@pytest.mark.parametrize("kernel", ["brown", "additive"])
+@pytest.mark.parametrize("n_spec", [1, 20])
+def test_kernel_bounds_table(mods, kernel, n_spec):
+    """est_k_minmax_binned_unweighted (coag_kernel.F90:253-341): 1e-10 relative."""
+    W, O = mods
+    kt = W.KERNEL_BROWN if kernel == "brown" else W.KERNEL_ADDITIVE
+    case = common.make_cells(3, 300, n_spec=n_spec, seed=8, ragged=False)
+    g = common.gpu_from_case(W, case)
+    o = common.oracle_from_case(O, case)
+    g.aero_state_sort()
+    g.kernel_bounds(kt)
+    for c in range(3):
+        o.sort(c)
+        _, kmax = o.kernel_bounds(c, kt)
+        dev = g.kernel_max(c)
+        assert dev.shape == kmax.shape
+        rel = np.abs(dev - kmax) / np.abs(kmax)
+        assert rel.max() < 1e-10, rel.max()
+
+
+@pytest.mark.parametrize("n_spec,n_class,n_per,n_cells,dt", [(1, 1, 1000, 8, 3600.0), (3, 2, 600, 12, 3600.0),
+                                                              (20, 3, 300, 6, 7200.0), (1, 1, 20000, 1, 600.0)])
+def test_mc_coag_bit_exact(mods, n_spec, n_class, n_per, n_cells, dt):
+    """mc_coag (Brownian): same sample counts, same events, same surviving particles in the
+    same order with identical volumes and ids as the sequential CPU oracle, over several steps."""
+    W, O = mods
+    case = common.make_cells(n_cells, n_per, n_spec=n_spec, n_class=n_class, seed=31 + n_class, num_conc=3e11)
+    g = common.gpu_from_case(W, case)
+    o = common.oracle_from_case(O, case)
+    total_events = 0
+    for step in range(3):
+        ns, nc = g.mc_coag(W.KERNEL_BROWN, dt, step=step)
+        for c in range(n_cells):
+            o.sort(c, force_resort=True, physical=True)
+            s, k, acc = o.mc_coag(c, O.KERNEL_BROWN, dt, step=step)
+            assert acc == 0
+            assert (s, k) == (ns[c], nc[c]), "cell %d step %d: oracle (%d,%d) device (%d,%d)" % (c, step, s, k, ns[c], nc[c])
+        total_events += int(nc.sum())
+        common.assert_same_population(g, o, case)
+        assert np.array_equal(g.get_next_id(), [o.L.pmco_get_next_id(o.h, c) for c in range(n_cells)])
+    assert total_events > 20, "the case must actually coagulate (%d events)" % total_events
+
+
+def test_mc_coag_additive_with_rebalance_bit_exact(mods):
+    """Additive kernel + aero_state_rebalance (doubling) every step, like test/additive."""
+    W, O = mods
+    rng = np.random.default_rng(1)
+    n, N0, rmean = 4000, 1e9, 1e-5
+    mean_vol = 4 * np.pi * rmean ** 3 / 3
+    vol = -mean_vol * np.log(rng.random(n))
+    case = common.make_cells(1, n, seed=9, ragged=False)
+    case["vol"] = vol[None, :]
+    case["wmag"][:] = N0 / n
+    g = common.gpu_from_case(W, case, cell_capacity=3 * n)
+    o = common.oracle_from_case(O, case)
+    doubled = 0
+    for step in range(120):
+        ns, nc = g.mc_coag(W.KERNEL_ADDITIVE, 5.0, step=step)
+        g.aero_state_rebalance(True, True, step=step)
+        o.sort(0, force_resort=True, physical=True)
+        s, k, _ = o.mc_coag(0, O.KERNEL_ADDITIVE, 5.0, step=step)
+        n_before = o.count(0)
+        o.rebalance(0, True, True, step=step)
+        doubled += o.count(0) > n_before
+        assert (s, k) == (ns[0], nc[0])
+    assert doubled >= 1
+    common.assert_same_population(g, o, case)
+
+
+def test_rebalance_halving_bit_exact(mods):
+    """aero_state_halve (aero_state.F90:1726): backwards swap-with-last removal, magnitude x2."""
+    W, O = mods
+    case = common.make_cells(5, 900, n_spec=3, n_class=2, seed=13, n_part_ideal=300.0)
+    g = common.gpu_from_case(W, case)
+    o = common.oracle_from_case(O, case)
+    g.aero_state_rebalance(True, True, step=4)
+    for c in range(5):
+        o.rebalance(c, True, True, step=4)
+    assert g.counts().sum() < case["counts"].sum()
+    common.assert_same_population(g, o, case)
+
+
+def test_golovin_on_device(mods):
+    """K1: additive kernel on the GPU against the Golovin solution (test/additive tolerances
+    0.05 / 0.2 are for 1e5 particles; with 1e4 particles and 4 seeds we check the seed-averaged
+    distribution against a proportionally wider bound, and total number against the analytic decay)."""
+    W, O = mods
+    from oracle import golovin
+    n, N0, rmean = 10000, 1e9, 1e-5
+    mean_vol = 4 * np.pi * rmean ** 3 / 3
+    errs = []
+    for seed in range(4):
+        rng = np.random.default_rng(100 + seed)
+        vol = -mean_vol * np.log(rng.random(n))
+        case = common.make_cells(1, n, seed=seed + 1, ragged=False)
+        case["vol"] = vol[None, :]
+        case["wmag"][:] = N0 / n
+        g = common.gpu_from_case(W, case, cell_capacity=3 * n)
+        for step in range(600):
+            g.mc_coag(W.KERNEL_ADDITIVE, 1.0, step=step)
+            g.aero_state_rebalance(True, True, step=step)
+        P = g.get_particles()
+        _, m, _ = g.get_weights()
+        errs.append(golovin.compare(P["vol"][0], m[0, 0, 0], 600.0, N0, rmean))
+        n_expect = N0 * np.exp(-N0 * mean_vol * 1000.0 * 600.0)
+        assert abs(P["count"][0] * m[0, 0, 0] - n_expect) / n_expect < 0.1
+        np.testing.assert_allclose((P["vol"][0] * m[0, 0, 0]).sum(), vol.sum() * N0 / n, rtol=0.08)
+    errs = np.array(errs)
+    assert errs[:, 0].mean() < 0.15 and errs[:, 1].mean() < 0.45, errs

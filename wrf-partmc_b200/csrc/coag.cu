@@ -1,0 +1,536 @@
+// coag.cu -- mc_coag (partmc/src/coagulation.F90:43-96) for every grid cell.
+//
+// One warp owns one cell and reproduces the reference's *sequential* semantics
+// exactly (bin pairs visited in the order of coagulation.F90:74-94; every
+// sample sees the population left by the previous accepted event), so the
+// result is bit-identical to the CPU oracle given the same addressed draws:
+//   * the 32 lanes scan 32 candidate (b1, b2) pairs at once -- destination
+//     class (coag_kernel.F90:382), weight factor majorant (:422), k_max and
+//     the Poisson sample count (coagulation.F90:648) -- and the warp then
+//     handles the first pair that has samples; pairs behind an accepted event
+//     are rescanned with the new counts;
+//   * inside a pair the lanes evaluate 32 candidate samples speculatively
+//     (find_rand_pair :766, num_conc_weighted_kernel, accept test :753); the
+//     first accepted one is applied (coagulate :928, coagulate_weighting :810)
+//     and evaluation resumes right behind it.
+// Every draw is a pure function Philox(seed; cell, step, phase, pair, sample, j),
+// which is what makes the speculation exact.
+//
+// The size_class multimap of integer_rmap2.F90 is kept per cell as index lists
+// in a 3*cap arena (lists start as the contiguous runs the sort produced and
+// are relocated with doubled capacity when they outgrow their run), with the
+// same swap-with-last bookkeeping as integer_rmap2_remove (:190-243).
+#include "pmcgpu_internal.cuh"
+
+#define COAG_WARPS 4
+static const double BETA_1 = 1000.0;
+static const double BETA_0 = 0.25 / (60.0 * 2e8);
+#define COAG_ACCEL_N_EVENT 1.0
+#define MAX_ALLOWABLE_GROWTH_FACTOR 1.5
+
+struct CellCtx {
+  const DevView* v;
+  int cell, lane;
+  size_t base;   // cell * cap
+  size_t NS;     // n_cells * cap
+  int nb;
+  double gmin, gmax, lnmin, lnmax;
+  int* L;        // cell arena
+  int* lptr; int* llen; int* lcap;  // per (class, bin): key = (c-1)*nbcap + (b-1)
+  int n_part;
+  int arena_top;
+  int err;
+};
+
+__device__ __forceinline__ int lkey(const CellCtx& cx, int c, int b) { return (c - 1) * cx.v->nbcap + (b - 1); }
+
+// aero_particle_volume / aero_particle_mass (aero_particle.F90:316, :252): in-order sums
+__device__ __forceinline__ void part_vol_mass(const CellCtx& cx, int p, double& vol, double& mass) {
+  const DevView& v = *cx.v;
+  double vt = 0.0, mt = 0.0;
+  for (int s = 0; s < v.S; s++) {
+    const double x = v.vol[(size_t)s * cx.NS + cx.base + p];
+    vt += x;
+    mt += x * v.density[s];
+  }
+  vol = vt;
+  mass = mt;
+}
+
+// coag_kernel.F90:346-377
+__device__ __forceinline__ double coag_num_conc_factor(const CellCtx& cx, double i_r, double j_r, int ic, int jc,
+                                                       int ijc) {
+  const double ij_r = vol2rad(rad2vol(i_r) + rad2vol(j_r));
+  const double i_nc = awa_nc_at_radius(*cx.v, cx.cell, ic, i_r);
+  const double j_nc = awa_nc_at_radius(*cx.v, cx.cell, jc, j_r);
+  const double ij_nc = awa_nc_at_radius(*cx.v, cx.cell, ijc, ij_r);
+  const double nc_min = fmin(fmin(i_nc, j_nc), ij_nc);
+  return i_nc * j_nc / nc_min;
+}
+
+// move the record of slot `src` into slot `dst` (aero_particle_array.F90:178-200), all lanes
+__device__ __forceinline__ void move_record(CellCtx& cx, int dst, int src) {
+  const DevView& v = *cx.v;
+  for (int s = cx.lane; s < v.S; s += 32) v.vol[(size_t)s * cx.NS + cx.base + dst] = v.vol[(size_t)s * cx.NS + cx.base + src];
+  if (cx.lane == 0) v.id[cx.base + dst] = v.id[cx.base + src];
+  if (cx.lane == 1) v.wgc[cx.base + dst] = v.wgc[cx.base + src];
+  if (cx.lane == 2) v.nprim[cx.base + dst] = v.nprim[cx.base + src];
+  if (cx.lane == 3) v.hyst[cx.base + dst] = v.hyst[cx.base + src];
+  if (cx.lane == 4) v.lct[cx.base + dst] = v.lct[cx.base + src];
+  if (cx.lane == 5) v.gct[cx.base + dst] = v.gct[cx.base + src];
+}
+
+// aero_sorted_remove_particle (aero_sorted.F90:455-470): apa swap-with-last +
+// integer_rmap2_remove on size_class.  p is a 0-based slot.
+__device__ void cell_remove_particle(CellCtx& cx, int p) {
+  const DevView& v = *cx.v;
+  const int last = cx.n_part - 1;
+  if (cx.lane == 0) {
+    const int b_old = v.pbin[cx.base + p];
+    const int c_old = v.wgc[cx.base + p] / v.G + 1;
+    const int pos_old = v.fidx[cx.base + p];
+    if (last != p) {
+      const int b_fix = v.pbin[cx.base + last];
+      const int c_fix = v.wgc[cx.base + last] / v.G + 1;
+      const int pos_fix = v.fidx[cx.base + last];
+      cx.L[cx.lptr[lkey(cx, c_fix, b_fix)] + pos_fix] = p;
+      v.pbin[cx.base + p] = b_fix;
+      v.fidx[cx.base + p] = pos_fix;
+    }
+    const int k_old = lkey(cx, c_old, b_old);
+    const int lp = cx.lptr[k_old];
+    const int pos_last = cx.llen[k_old] - 1;
+    const int dom_fix = cx.L[lp + pos_last];
+    if (pos_old < pos_last) cx.L[lp + pos_old] = cx.L[lp + pos_last];
+    cx.llen[k_old] = pos_last;
+    if (pos_last != pos_old) v.fidx[cx.base + dom_fix] = pos_old;
+  }
+  __syncwarp();
+  if (last != p) move_record(cx, p, last);
+  cx.n_part = last;
+  __syncwarp();
+}
+
+// integer_varray_append on list (c, b) with pow2-style growth inside the arena
+__device__ void cell_list_append(CellCtx& cx, int c, int b, int slot) {
+  const DevView& v = *cx.v;
+  const int k = lkey(cx, c, b);
+  int len = cx.llen[k], capk = cx.lcap[k], lp = cx.lptr[k];
+  if (len == capk) {
+    const int ncap = max(4, 2 * capk);
+    if (cx.arena_top + ncap > 3 * v.cap) {
+      cx.err = PMCGPU_ERR_CAPACITY;
+      return;
+    }
+    const int np = cx.arena_top;
+    for (int q = cx.lane; q < len; q += 32) cx.L[np + q] = cx.L[lp + q];
+    __syncwarp();
+    cx.arena_top += ncap;
+    lp = np;
+    if (cx.lane == 0) {
+      cx.lptr[k] = np;
+      cx.lcap[k] = ncap;
+    }
+  }
+  if (cx.lane == 0) {
+    cx.L[lp + len] = slot;
+    v.fidx[cx.base + slot] = len;
+    cx.llen[k] = len + 1;
+  }
+  __syncwarp();
+}
+
+__device__ __forceinline__ double unweighted_kernel(int ktype, const BrownEnv& be, double v1, double m1, double v2,
+                                                    double m2) {
+  if (ktype == PMCGPU_KERNEL_BROWN) {
+    return brown_pair(brown_part(be, v1, m1 / v1), brown_part(be, v2, m2 / v2));
+  } else if (ktype == PMCGPU_KERNEL_ADDITIVE) {
+    return BETA_1 * (v1 + v2);
+  } else if (ktype == PMCGPU_KERNEL_CONSTANT) {
+    return BETA_0;
+  }
+  return 0.0;
+}
+
+// coagulate (coagulation.F90:928-985) + coagulate_weighting (:810-922) for the
+// particles in slots p1, p2 (0-based); warp-cooperative, uniform arguments.
+__device__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1, int c2, int cc, const RKey& key) {
+  const DevView& v = *cx.v;
+  double v1, m1, v2, m2;
+  part_vol_mass(cx, p1, v1, m1);
+  part_vol_mass(cx, p2, v2, m2);
+  const double r1 = vol2rad(v1), r2 = vol2rad(v2);
+  const double rc = vol2rad(rad2vol(r1) + rad2vol(r2));
+  const double nc1 = awa_nc_at_radius(v, cx.cell, c1, r1);
+  const double nc2 = awa_nc_at_radius(v, cx.cell, c2, r2);
+  const double ncc = awa_nc_at_radius(v, cx.cell, cc, rc);
+  // aero_weight_array_rand_group (aero_weight_array.F90:374) -> sample_cts_pdf (rand.F90:550), draws 6..
+  int new_group = 1;
+  if (v.G > 1) {
+    const size_t wb = ((size_t)cx.cell * v.C + (cc - 1)) * v.G;
+    double pdf_max = 0.0;
+    for (int g = 0; g < v.G; g++) pdf_max = fmax(pdf_max, 1.0 / weight_nc(v.wtype[wb + g], v.wmag[wb + g], v.wexp[wb + g], rc));
+    RStream sg{key, 6};
+    for (;;) {
+      const int k = pmc_rand_int(sg.next(), v.G);
+      const double pk = 1.0 / weight_nc(v.wtype[wb + k - 1], v.wmag[wb + k - 1], v.wexp[wb + k - 1], rc);
+      if (sg.next() < pk / pdf_max) {
+        new_group = k;
+        break;
+      }
+    }
+  }
+  const double nc_min = fmin(fmin(nc1, nc2), ncc);
+  const bool remove_1 = rng_uniform(key, 3) < nc_min / nc1;
+  const bool remove_2 = rng_uniform(key, 4) < nc_min / nc2;
+  const bool create_new = rng_uniform(key, 5) < nc_min / ncc;
+  bool id_1_lost, id_2_lost;
+  if (create_new) {
+    id_1_lost = false;
+    id_2_lost = false;
+    if (remove_1 && remove_2) {
+      if (v1 > v2) id_2_lost = true; else id_1_lost = true;
+    }
+  } else {
+    id_1_lost = remove_1;
+    id_2_lost = remove_2;
+  }
+  // aero_particle_coagulate (aero_particle.F90:900-980) into registers
+  double volc[(PMC_MAX_SPEC + 31) / 32];
+  long long idc = 0;
+  int hystc = 0, nprimc = 0;
+  double lctc = 0.0, gctc = 0.0;
+  if (create_new) {
+#pragma unroll
+    for (int q = 0; q < (PMC_MAX_SPEC + 31) / 32; q++) {
+      const int s = q * 32 + cx.lane;
+      volc[q] = (s < v.S) ? v.vol[(size_t)s * cx.NS + cx.base + p1] + v.vol[(size_t)s * cx.NS + cx.base + p2] : 0.0;
+    }
+    const long long id1 = v.id[cx.base + p1], id2 = v.id[cx.base + p2];
+    hystc = (v.hyst[cx.base + p1] == 1 && v.hyst[cx.base + p2] == 1) ? 1 : 0;
+    nprimc = v.nprim[cx.base + p1] + v.nprim[cx.base + p2];
+    gctc = fmax(v.gct[cx.base + p1], v.gct[cx.base + p2]);
+    lctc = fmin(v.lct[cx.base + p1], v.lct[cx.base + p2]);
+    if (remove_1 && !id_1_lost) {
+      idc = id1;
+    } else if (remove_2 && !id_2_lost) {
+      idc = id2;
+    } else {
+      // aero_particle_new_id (aero_particle.F90:141-149) with one counter per cell
+      const long long nx = v.next_id[cx.cell];
+      idc = (nx - 1) * v.n_cells_global + v.gcell[cx.cell] + 1;
+      __syncwarp();
+      if (cx.lane == 0) v.next_id[cx.cell] = nx + 1;
+    }
+  }
+  __syncwarp();
+  // remove old particles (coagulation.F90:948-970)
+  if (p2 > p1) {
+    if (remove_2) cell_remove_particle(cx, p2);
+    if (remove_1) cell_remove_particle(cx, p1);
+  } else {
+    if (remove_1) cell_remove_particle(cx, p1);
+    if (remove_2) cell_remove_particle(cx, p2);
+  }
+  // add new particle, allow_resort = .false. (aero_sorted.F90:397-449)
+  if (create_new) {
+    double vt = 0.0;
+    for (int s = 0; s < v.S; s++) vt += __shfl_sync(0xffffffffu, volc[s >> 5], s & 31);
+    const int b_new = log_grid_find(cx.lnmin, cx.lnmax, cx.nb, log(vol2rad(vt)));
+    if (b_new < 1 || b_new > cx.nb) {
+      cx.err = PMCGPU_ERR_BIN_RANGE;
+      return;
+    }
+    if (cx.n_part >= v.cap) {
+      cx.err = PMCGPU_ERR_CAPACITY;
+      return;
+    }
+    const int slot = cx.n_part;
+#pragma unroll
+    for (int q = 0; q < (PMC_MAX_SPEC + 31) / 32; q++) {
+      const int s = q * 32 + cx.lane;
+      if (s < v.S) v.vol[(size_t)s * cx.NS + cx.base + slot] = volc[q];
+    }
+    if (cx.lane == 0) {
+      v.id[cx.base + slot] = idc;
+      v.wgc[cx.base + slot] = (cc - 1) * v.G + (new_group - 1);
+      v.nprim[cx.base + slot] = nprimc;
+      v.hyst[cx.base + slot] = hystc;
+      v.lct[cx.base + slot] = lctc;
+      v.gct[cx.base + slot] = gctc;
+      v.pbin[cx.base + slot] = b_new;
+    }
+    cx.n_part = slot + 1;
+    __syncwarp();
+    cell_list_append(cx, cc, b_new, slot);
+  }
+}
+
+__global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * COAG_WARPS + warp;
+  if (cell >= v.n_cells) return;
+  extern __shared__ double s_dyn[];
+  double* hm = s_dyn + (size_t)warp * v.C;                                  // harmonic magnitude per class
+  int* flat = (int*)(s_dyn + (size_t)COAG_WARPS * v.C) + (size_t)warp * v.C;  // class has only flat weights
+
+  CellCtx cx;
+  cx.v = &v;
+  cx.cell = cell;
+  cx.lane = lane;
+  cx.base = (size_t)cell * v.cap;
+  cx.NS = (size_t)v.n_cells * v.cap;
+  cx.nb = v.grid_nb[cell];
+  cx.gmin = v.grid_min[cell];
+  cx.gmax = v.grid_max[cell];
+  cx.lnmin = cx.nb > 0 ? log(cx.gmin) : 0.0;
+  cx.lnmax = cx.nb > 0 ? log(cx.gmax) : 0.0;
+  cx.L = v.L + (size_t)cell * 3 * v.cap;
+  cx.lptr = v.lptr + (size_t)cell * v.C * v.nbcap;
+  cx.llen = v.llen + (size_t)cell * v.C * v.nbcap;
+  cx.lcap = v.lcap + (size_t)cell * v.C * v.nbcap;
+  cx.n_part = v.count[cell];
+  cx.arena_top = v.cap;
+  cx.err = 0;
+  int tot_n_samp = 0, tot_n_coag = 0;
+  const int nb = cx.nb;
+  if (v.status[cell] != 0 || nb < 1 || cx.n_part == 0) {
+    if (lane == 0) {
+      v.coag_samp[cell] = 0;
+      v.coag_ncoag[cell] = 0;
+    }
+    return;
+  }
+  // ---- list set-up: exclusive scan of bin_count in (class, bin) order
+  {
+    const int* bc = v.bin_count + (size_t)cell * v.C * v.nbcap;
+    int carry = 0;
+    const int nk = v.C * v.nbcap;
+    for (int k0 = 0; k0 < nk; k0 += 32) {
+      const int k = k0 + lane;
+      const int x = (k < nk) ? bc[k] : 0;
+      int incl = x;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      if (k < nk) {
+        cx.lptr[k] = carry + incl - x;
+        cx.llen[k] = x;
+        cx.lcap[k] = x;
+      }
+      carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    __syncwarp();
+    for (int p = lane; p < cx.n_part; p += 32) {
+      cx.L[p] = p;
+      const int k = (v.wgc[cx.base + p] / v.G) * v.nbcap + (v.pbin[cx.base + p] - 1);
+      v.fidx[cx.base + p] = p - cx.lptr[k];
+    }
+    // per-class weight summary; monotone_decreasing over the whole array (aero_weight_array.F90:304)
+    for (int c = lane; c < v.C; c += 32) {
+      flat[c] = class_is_flat(v, cell, c + 1) ? 1 : 0;
+      hm[c] = awa_nc_at_radius(v, cell, c + 1, 1.0);
+    }
+    __syncwarp();
+  }
+  bool mono_dec = true, all_flat = true;
+  for (int q = 0; q < v.C * v.G; q++) {
+    const size_t wi = (size_t)cell * v.C * v.G + q;
+    if (v.wtype[wi] == PMCGPU_WEIGHT_POWER && v.wexp[wi] > 0.0) mono_dec = false;
+    if (v.wtype[wi] != PMCGPU_WEIGHT_NONE) all_flat = false;
+  }
+  const BrownEnv be = brown_env(v.temp[cell], v.pres[cell]);
+  const double* ktab = v.kmax + (size_t)cell * v.nbcap * v.nbcap;
+
+  for (int c1 = 1; c1 <= v.C && !cx.err; c1++) {
+    for (int c2 = 1; c2 <= c1 && !cx.err; c2++) {
+      for (int b1 = 1; b1 <= nb && !cx.err; b1++) {
+        if (cx.llen[lkey(cx, c1, b1)] == 0) continue;
+        int b2 = (c1 == c2) ? b1 : 1;
+        while (b2 <= nb && !cx.err) {
+          // ---- lane-parallel scan of 32 candidate partner bins
+          const int my_b2 = b2 + lane;
+          int n_samp = 0, cc = c2, accel = 0;
+          double k_max = 0.0;
+          const int n1 = cx.llen[lkey(cx, c1, b1)];
+          int n2 = 0;
+          if (my_b2 <= nb) n2 = cx.llen[lkey(cx, c2, my_b2)];
+          if (n2 > 0) {
+            double f_max;
+            const bool pair_flat = all_flat || (flat[c1 - 1] && flat[c2 - 1]);
+            if (pair_flat) {
+              // flat weights: every radius gives the same factor (coag_kernel.F90:382-465)
+              cc = (hm[c1 - 1] < hm[c2 - 1]) ? c1 : c2;
+              const double ncm = fmin(fmin(hm[c1 - 1], hm[c2 - 1]), hm[cc - 1]);
+              f_max = fmax(0.0, hm[c1 - 1] * hm[c2 - 1] / ncm);
+            } else {
+              // coag_dest_class: sic, both radii from bin b1 (coag_kernel.F90:402-403)
+              const double i_r = grid_center(cx.gmin, cx.gmax, nb, b1);
+              const double ij_r = vol2rad(rad2vol(i_r) + rad2vol(i_r));
+              cc = (awa_nc_at_radius(v, cell, c1, ij_r) < awa_nc_at_radius(v, cell, c2, ij_r)) ? c1 : c2;
+              const double i_lo = grid_edge(cx.gmin, cx.gmax, nb, b1), i_hi = grid_edge(cx.gmin, cx.gmax, nb, b1 + 1);
+              const double j_lo = grid_edge(cx.gmin, cx.gmax, nb, my_b2), j_hi = grid_edge(cx.gmin, cx.gmax, nb, my_b2 + 1);
+              f_max = 0.0;
+              for (int is = 1; is <= 5; is++)
+                for (int js = 1; js <= 5; js++) {
+                  const double ir = interp_linear_disc(i_lo, i_hi, 5, is);
+                  const double jr = interp_linear_disc(j_lo, j_hi, 5, js);
+                  f_max = fmax(f_max, coag_num_conc_factor(cx, ir, jr, c1, c2, cc));
+                }
+            }
+            k_max = ktab[(size_t)(my_b2 - 1) * nb + (b1 - 1)] * f_max;
+            // determine_target_and_source + compute_n_source (coagulation.F90:247-329)
+            if (mono_dec) {
+              double nc1_min, nc1_max, nc2_min, nc2_max;
+              if (pair_flat) {
+                nc1_min = nc1_max = hm[c1 - 1];
+                nc2_min = nc2_max = hm[c2 - 1];
+              } else {
+                const double a1 = awa_nc_at_radius(v, cell, c1, grid_edge(cx.gmin, cx.gmax, nb, b1));
+                const double a2 = awa_nc_at_radius(v, cell, c1, grid_edge(cx.gmin, cx.gmax, nb, b1 + 1));
+                const double e1 = awa_nc_at_radius(v, cell, c2, grid_edge(cx.gmin, cx.gmax, nb, my_b2));
+                const double e2 = awa_nc_at_radius(v, cell, c2, grid_edge(cx.gmin, cx.gmax, nb, my_b2 + 1));
+                nc1_min = fmin(a1, a2); nc1_max = fmax(a1, a2);
+                nc2_min = fmin(e1, e2); nc2_max = fmax(e1, e2);
+              }
+              int bt = 0, bs = 0, ns = 0;
+              bool ok = false;
+              if ((nc1_max < nc2_min) && (cc == c1)) { bt = b1; bs = my_b2; ns = n2; ok = true; }
+              if ((nc2_max < nc1_min) && (cc == c2)) { bt = my_b2; bs = b1; ns = n1; ok = true; }
+              if (ok) {
+                const double n_source_per_target = k_max * del_t * (double)ns;
+                if (!(n_source_per_target < COAG_ACCEL_N_EVENT)) {
+                  const double min_target_vol = rad2vol(grid_edge(cx.gmin, cx.gmax, nb, bt));
+                  const double max_source_vol = rad2vol(grid_edge(cx.gmin, cx.gmax, nb, bs + 1));
+                  const double growth = (min_target_vol + max_source_vol * n_source_per_target) / min_target_vol;
+                  if (!(growth > MAX_ALLOWABLE_GROWTH_FACTOR)) accel = 1;
+                }
+              }
+            }
+            if (!accel) {
+              // compute_n_samp (coagulation.F90:648-685)
+              const bool same = (b1 == my_b2) && (c1 == c2);
+              const double n_possible = same ? (double)n1 * ((double)n2 - 1.0) / 2.0 : (double)n1 * (double)n2;
+              const double n_samp_mean = (k_max * del_t) * n_possible;
+              const unsigned pid = ((unsigned)((c1 - 1) * v.C + (c2 - 1)) * 256u + (unsigned)b1) * 256u + (unsigned)my_b2;
+              RStream s0{RKey{v.seed, (unsigned)v.gcell[cell], step, PH_COAG, pid, 0u}, 0u};
+              n_samp = rand_poisson(n_samp_mean, s0);
+            }
+          }
+          unsigned has = __ballot_sync(0xffffffffu, (n_samp > 0) || accel);
+          bool rescan = false;
+          int next_b2 = b2 + 32;
+          while (has && !rescan && !cx.err) {
+            const int f = __ffs(has) - 1;
+            has &= has - 1;
+            const int pb2 = b2 + f;
+            const int p_nsamp = __shfl_sync(0xffffffffu, n_samp, f);
+            const int p_cc = __shfl_sync(0xffffffffu, cc, f);
+            const double p_kmax = __shfl_sync(0xffffffffu, k_max, f);
+            const int p_accel = __shfl_sync(0xffffffffu, accel, f);
+            if (p_accel) {
+              cx.err = PMCGPU_ERR_ACCEL;
+              break;
+            }
+            // ---- per_set_coag (coagulation.F90:587-643)
+            tot_n_samp += p_nsamp;
+            const bool same = (b1 == pb2) && (c1 == c2);
+            const double accept_factor = 1.0 / p_kmax;
+            const unsigned pid = ((unsigned)((c1 - 1) * v.C + (c2 - 1)) * 256u + (unsigned)b1) * 256u + (unsigned)pb2;
+            const int k1 = lkey(cx, c1, b1), k2 = lkey(cx, c2, pb2);
+            int d = 1;
+            while (d <= p_nsamp && !cx.err) {
+              const int m1 = cx.llen[k1], m2 = cx.llen[k2];
+              if (((m1 < 2) && same) || (m1 < 1) || (m2 < 1)) break;
+              const int my_d = d + lane;
+              bool accept = false;
+              int p1 = 0, p2 = 0;
+              if (my_d <= p_nsamp) {
+                const RKey key{v.seed, (unsigned)v.gcell[cell], step, PH_COAG, pid, (unsigned)my_d};
+                // find_rand_pair (coagulation.F90:766-803): draws 0, 1
+                const int i1 = pmc_rand_int(rng_uniform(key, 0), m1);
+                int i2;
+                if (same) {
+                  i2 = pmc_rand_int(rng_uniform(key, 1), m2 - 1);
+                  if (i2 == i1) i2 = m2;
+                } else {
+                  i2 = pmc_rand_int(rng_uniform(key, 1), m2);
+                }
+                p1 = cx.L[cx.lptr[k1] + i1 - 1];
+                p2 = cx.L[cx.lptr[k2] + i2 - 1];
+                // num_conc_weighted_kernel (coag_kernel.F90:175-209)
+                double v1, ms1, v2, ms2;
+                part_vol_mass(cx, p1, v1, ms1);
+                part_vol_mass(cx, p2, v2, ms2);
+                const double uk = unweighted_kernel(ktype, be, v1, ms1, v2, ms2);
+                const double k = uk * coag_num_conc_factor(cx, vol2rad(v1), vol2rad(v2), c1, c2, p_cc);
+                accept = rng_uniform(key, 2) < k * accept_factor;  // maybe_coag_pair :753
+              }
+              const unsigned acc = __ballot_sync(0xffffffffu, accept);
+              if (acc == 0) {
+                d += 32;
+                continue;
+              }
+              const int fa = __ffs(acc) - 1;
+              const int e1 = __shfl_sync(0xffffffffu, p1, fa);
+              const int e2 = __shfl_sync(0xffffffffu, p2, fa);
+              const RKey ekey{v.seed, (unsigned)v.gcell[cell], step, PH_COAG, pid, (unsigned)(d + fa)};
+              cell_coagulate(cx, e1, e2, c1, c2, p_cc, ekey);
+              tot_n_coag += 1;
+              rescan = true;  // counts changed: pairs behind this one must be rescanned
+              d = d + fa + 1;
+            }
+            if (rescan) next_b2 = pb2 + 1;
+          }
+          b2 = next_b2;
+        }
+      }
+    }
+  }
+  __syncwarp();
+  // publish the per-(class, bin) counts and the population size
+  {
+    int* bc = v.bin_count + (size_t)cell * v.C * v.nbcap;
+    for (int k = lane; k < v.C * v.nbcap; k += 32) bc[k] = cx.llen[k];
+  }
+  if (lane == 0) {
+    v.count[cell] = cx.n_part;
+    v.coag_samp[cell] = tot_n_samp;
+    v.coag_ncoag[cell] = tot_n_coag;
+    if (cx.err && v.status[cell] == 0) v.status[cell] = cx.err;
+  }
+}
+
+int pmc_kernel_bounds_async(pmcgpu_ctx* ctx, int ktype);
+
+int pmc_mc_coag_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step) {
+  DevView& v = ctx->v;
+  // coagulation.F90:64-70: bounds are (re)computed only when the grid was remade
+  int rc = pmc_kernel_bounds_async(ctx, ktype);
+  if (rc) return rc;
+  const size_t smem = (size_t)COAG_WARPS * v.C * (sizeof(double) + sizeof(int));
+  const int blocks = (v.n_cells + COAG_WARPS - 1) / COAG_WARPS;
+  k_mc_coag<<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+  LAUNCH_CHECK(ctx);
+  return PMCGPU_OK;
+}
+
+int pmc_sort_async(pmcgpu_ctx* ctx);
+
+extern "C" int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned int step,
+                              int* tot_n_samp, int* tot_n_coag) {
+  if (!ctx) return PMCGPU_ERR_ARG;
+  // mc_coag starts with aero_state_sort (coagulation.F90:63)
+  int rc = pmc_sort_async(ctx);
+  if (rc) return rc;
+  rc = pmc_mc_coag_async(ctx, coag_kernel_type, del_t, step);
+  if (rc) return rc;
+  if (tot_n_samp)
+    CUDA_OK(ctx, cudaMemcpyAsync(tot_n_samp, ctx->v.coag_samp, ctx->v.n_cells * sizeof(int), cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+  if (tot_n_coag)
+    CUDA_OK(ctx, cudaMemcpyAsync(tot_n_coag, ctx->v.coag_ncoag, ctx->v.n_cells * sizeof(int), cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+  return pmc_first_status(ctx);
+}

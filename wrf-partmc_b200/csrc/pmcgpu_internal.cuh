@@ -1,0 +1,313 @@
+// pmcgpu_internal.cuh -- shared declarations of the B200 aerosol-step library.
+// Product code: never includes anything under oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/pmcgpu.h"
+
+#define PMC_MAX_SPEC 64
+#define PMC_WARPS_PER_CTA 8
+
+// draw-address phases; must agree with the documented stream layout
+enum : uint32_t {
+  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8
+};
+
+struct PmcConst {  // partmc/src/constants.F90:30-65
+  static constexpr double pi = 3.14159265358979323846;
+  static constexpr double boltzmann = 1.3806505e-23;
+  static constexpr double avagadro = 6.02214179e23;
+  static constexpr double univ_gas_const = 8.314472;
+  static constexpr double accom_coeff = 1.0;
+  static constexpr double water_eq_vap_press = 611.0;
+  static constexpr double water_freeze_temp = 273.15;
+  static constexpr double water_surf_eng = 0.073;
+  static constexpr double water_latent_heat = 2.272e6;
+  static constexpr double air_spec_heat = 1005.0;
+  static constexpr double water_molec_weight = 18e-3;
+  static constexpr double water_density = 1e3;
+  static constexpr double air_molec_weight = 2.89644e-2;
+  static constexpr double air_std_press = 101325.0;
+};
+
+// Device view of one patch: structure-of-arrays particle slabs, one fixed-size
+// slab of `cap` slots per grid cell, so no phase needs a global compaction.
+struct DevView {
+  int n_cells, cap, S, G, C, nbcap;
+  int i_water;  // 1-based, 0 none
+  unsigned seed;
+  long long n_cells_global;
+  // particle slabs: live buffer (cur) and scratch buffer (alt) of a ping-pong pair
+  double* vol;        // [S][n_cells*cap]
+  long long* id;      // [n_cells*cap]
+  int* wgc;           // packed (class-1)*G + (group-1)
+  int* nprim;
+  int* hyst;
+  double* lct;
+  double* gct;
+  double* vol_alt; long long* id_alt; int* wgc_alt; int* nprim_alt; int* hyst_alt; double* lct_alt; double* gct_alt;
+  int* count;         // [n_cells]
+  long long* next_id; // [n_cells]
+  long long* gcell;   // [n_cells] global cell index
+  int* status;        // [n_cells] first error
+  // sorted state
+  int* pbin;          // [n_cells*cap] bin (1-based) of each particle, sorted layout
+  int* pbin_alt;
+  double* lnr;        // [n_cells*cap] scratch: ln(radius)
+  int* bin_count;     // [n_cells][C][nbcap]   entries per (class, bin)
+  int* grid_nb;       // [n_cells]
+  double* grid_min;   // [n_cells]
+  double* grid_max;
+  int* bounds_valid;  // [n_cells] coag_kernel_bounds_valid
+  double* kmax;       // [n_cells][nbcap*nbcap] (b1,b2) at [(b2-1)*nb + b1-1], nb = grid_nb
+  // weights / env
+  int* wtype;         // [n_cells][C][G]
+  double* wmag;
+  double* wexp;
+  double* temp; double* pres; double* rh; double* rrho; double* cellvol;
+  // species table
+  const double* density; const double* kappa; const double* molw; const int* nions;
+  double dens_min, dens_max;
+  double ideal;       // n_part_ideal per (group, class)
+  // coagulation work space
+  int* L;             // [n_cells][3*cap] list arena
+  int* fidx;          // [n_cells*cap] position of particle in its (bin, class) list
+  int* lptr;          // [n_cells][C*nbcap]
+  int* llen;
+  int* lcap;
+  int* coag_samp;     // [n_cells]
+  int* coag_ncoag;
+};
+
+struct pmcgpu_ctx {
+  pmcgpu_config cfg;
+  DevView v;
+  cudaStream_t stream;
+  std::string err;
+  long long launches;
+  std::vector<void*> allocs;
+  std::vector<double> h_density;
+  int cur;  // unused: pointers are swapped in v
+};
+
+#define CUDA_OK(ctx, call)                                                              \
+  do {                                                                                  \
+    cudaError_t e_ = (call);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                  \
+      return PMCGPU_ERR_CUDA;                                                           \
+    }                                                                                   \
+  } while (0)
+
+#define LAUNCH_CHECK(ctx)                                                               \
+  do {                                                                                  \
+    (ctx)->launches++;                                                                  \
+    cudaError_t e_ = cudaGetLastError();                                                \
+    if (e_ != cudaSuccess) {                                                            \
+      (ctx)->err = std::string("kernel launch: ") + cudaGetErrorString(e_);             \
+      return PMCGPU_ERR_CUDA;                                                           \
+    }                                                                                   \
+  } while (0)
+
+int pmc_first_status(pmcgpu_ctx* ctx);  // reduce per-cell status to one code (syncs)
+
+// ---------------------------------------------------------------------------
+// device math
+// ---------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+// Philox4x32-10 (Salmon et al. SC'11).  Address = (cell, step, phase, a, b, j):
+// counter = (j>>1, b, a, cell), key = (seed, step*16 + phase); one block yields
+// two 53-bit uniforms (j even / odd).
+__device__ __forceinline__ void philox_block(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                             uint32_t k1, uint32_t o[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0;
+    const uint32_t n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  o[0] = c0; o[1] = c1; o[2] = c2; o[3] = c3;
+}
+struct RKey {
+  uint32_t seed, cell, step, phase, a, b;
+};
+__device__ __forceinline__ double rng_uniform(const RKey& k, uint32_t j) {
+  uint32_t o[4];
+  philox_block(j >> 1, k.b, k.a, k.cell, k.seed, k.step * 16u + k.phase, o);
+  const uint32_t hi = (j & 1u) ? o[2] : o[0];
+  const uint32_t lo = (j & 1u) ? o[3] : o[1];
+  const unsigned long long m = ((unsigned long long)(hi >> 5) << 26) | (unsigned long long)(lo >> 6);
+  return (double)m * (1.0 / 9007199254740992.0);
+}
+// rand.F90:172-205 (in-tree branch): mod(int(u*n), n) + 1
+__device__ __forceinline__ int pmc_rand_int(double u, int n) {
+  const int v = (int)(u * (double)n);
+  return (v % n) + 1;
+}
+// rand.F90:214-226
+__device__ __forceinline__ int prob_round(double val, double u) {
+  return (u < ceil(val) - val) ? (int)floor(val) : (int)ceil(val);
+}
+struct RStream {
+  RKey k;
+  uint32_t j;
+  __device__ __forceinline__ double next() { return rng_uniform(k, j++); }
+};
+// rand.F90:410-474 Box-Muller branch
+__device__ inline double rand_normal(double mean, double stddev, RStream& s) {
+  const double u1 = s.next();
+  const double u2 = s.next();
+  const double r = sqrt(-2.0 * log(u1));
+  const double theta = 2.0 * PmcConst::pi * u2;
+  return stddev * (r * cos(theta)) + mean;
+}
+// rand.F90:252-304 in-tree branch
+__device__ inline int rand_poisson(double mean, RStream& s) {
+  if (mean <= 10.0) {
+    const double L = exp(-mean);
+    int k = 0;
+    double p = 1.0;
+    do {
+      k++;
+      p = p * s.next();
+    } while (!(p < L));
+    return k - 1;
+  }
+  const int k = (int)llround(rand_normal(mean, sqrt(mean), s));
+  return max(k, 0);
+}
+// rand.F90:319-404 in-tree branch
+__device__ inline int rand_binomial(int n, double p, RStream& s) {
+  const double np = (double)n * p;
+  const double nomp = (double)n * (1.0 - p);
+  if (np >= 10.0 && nomp >= 10.0) {
+    const int k = (int)llround(rand_normal(np, sqrt(np * (1.0 - p)), s));
+    return min(max(k, 0), n);
+  } else if (p < 1e-15) {
+    return 0;
+  } else if (np < 1e-200) {
+    return 0;
+  } else if (nomp < 1e-200) {
+    return n;
+  }
+  const double q = (p <= 0.5) ? p : 1.0 - p;
+  int k = 0, sum = 0;
+  for (;;) {
+    const double G_real = log(s.next()) / log(1.0 - q);
+    if (G_real > (double)(n - sum)) break;
+    const int Gi = (int)ceil(G_real);
+    sum += Gi;
+    if (sum > n) break;
+    k++;
+  }
+  return (p <= 0.5) ? k : n - k;
+}
+
+// util.F90:240 / :265 (spherical particles, fractal.F90:113)
+__device__ __forceinline__ double vol2rad(double v) { return pow(3.0 * v / 4.0 / PmcConst::pi, 1.0 / 3.0); }
+__device__ __forceinline__ double rad2vol(double r) { return 4.0 * PmcConst::pi * (r * r * r) / 3.0; }
+// util.F90:663
+__device__ __forceinline__ double interp_linear_disc(double x_1, double x_n, int n, int i) {
+  if (x_1 == x_n) return x_1;
+  const double alpha = (double)(i - 1) / (double)(n - 1);
+  return (1.0 - alpha) * x_1 + alpha * x_n;
+}
+// util.F90:532 on logs (util.F90:566): bin of ln(r) on a log grid with n_bin bins
+__device__ __forceinline__ int log_grid_find(double ln_min, double ln_max, int n_bin, double ln_r) {
+  const int n = n_bin + 1;
+  if (ln_r == ln_max) return n - 1;
+  const double f = floor((ln_r - ln_min) / (ln_max - ln_min) * (double)(n - 1));
+  long long v = (f > 2.0e9) ? 2000000000LL : (f < -2.0e9 ? -2000000000LL : (long long)f);
+  v = v + 1;
+  v = v < (long long)n ? v : (long long)n;
+  v = v > 0 ? v : 0;
+  return (int)v;
+}
+// bin_grid.F90:83-134 edges = exp(linspace(ln min, ln max, n_bin+1)) with exact ends
+__device__ __forceinline__ double grid_edge(double gmin, double gmax, int n_bin, int i /*1..n_bin+1*/) {
+  if (i == 1) return gmin;
+  if (i == n_bin + 1) return gmax;
+  const double a = (double)(i - 1) / (double)n_bin;
+  return exp((1.0 - a) * log(gmin) + a * log(gmax));
+}
+// bin_grid.F90:113-118 centers = logspace(c1, c2, n_bin)
+__device__ __forceinline__ double grid_center(double gmin, double gmax, int n_bin, int i /*1..n_bin*/) {
+  const double c1 = exp(interp_linear_disc(log(gmin), log(gmax), 2 * n_bin + 1, 2));
+  const double c2 = exp(interp_linear_disc(log(gmin), log(gmax), 2 * n_bin + 1, 2 * n_bin));
+  if (i == 1) return c1;
+  if (i == n_bin) return c2;
+  const double a = (double)(i - 1) / (double)(n_bin - 1);
+  return exp((1.0 - a) * log(c1) + a * log(c2));
+}
+
+// aero_weight.F90:127-146
+__device__ __forceinline__ double weight_nc(int type, double mag, double ex, double radius) {
+  if (type == PMCGPU_WEIGHT_NONE) return mag;
+  return mag * pow(radius, ex);
+}
+// aero_weight_array.F90:232-251: harmonic combination over groups of class c (1-based)
+__device__ __forceinline__ double awa_nc_at_radius(const DevView& v, int cell, int c, double radius) {
+  const size_t base = ((size_t)cell * v.C + (c - 1)) * v.G;
+  double s = 0.0;
+  for (int g = 0; g < v.G; g++) s += 1.0 / weight_nc(v.wtype[base + g], v.wmag[base + g], v.wexp[base + g], radius);
+  return 1.0 / s;
+}
+__device__ __forceinline__ bool class_is_flat(const DevView& v, int cell, int c) {
+  const size_t base = ((size_t)cell * v.C + (c - 1)) * v.G;
+  for (int g = 0; g < v.G; g++)
+    if (v.wtype[base + g] != PMCGPU_WEIGHT_NONE) return false;
+  return true;
+}
+
+// coag_kernel_brown.F90:111-197, split into the single-particle part and the
+// pair combination (identical operation order, so identical values).
+struct BrownEnv {
+  double viscosd, gasfreepath, kT;
+};
+__device__ __forceinline__ BrownEnv brown_env(double temp, double pressure) {
+  BrownEnv e;
+  const double rhoair = (pressure * PmcConst::air_molec_weight) / (PmcConst::univ_gas_const * temp);
+  e.viscosd = 1.8325e-05 * (416.16 / (temp + 120.0)) * pow(temp / 296.16, 1.5);
+  const double viscosk = e.viscosd / rhoair;
+  const double gasspeed =
+      sqrt((8.0 * PmcConst::boltzmann * temp * PmcConst::avagadro) / (PmcConst::pi * PmcConst::air_molec_weight));
+  e.gasfreepath = 2.0 * viscosk / gasspeed;
+  e.kT = temp;
+  return e;
+}
+struct BrownPart {
+  double rad, diffus, speedsq, deltasq;
+};
+__device__ __forceinline__ BrownPart brown_part(const BrownEnv& e, double vol, double den) {
+  BrownPart b;
+  const double temp = e.kT;
+  b.rad = vol2rad(vol);
+  const double Rme = b.rad;
+  const double knud = e.gasfreepath / Rme;
+  const double cunning = 1.0 + knud * (1.249 + 0.42 * exp(-0.87 / knud));
+  b.diffus = (PmcConst::boltzmann * temp * cunning) / (6.0 * PmcConst::pi * Rme * e.viscosd);
+  b.speedsq = 8.0 * PmcConst::boltzmann * temp / (PmcConst::pi * den * vol);
+  const double freepath = 8.0 * b.diffus / (PmcConst::pi * sqrt(b.speedsq));
+  const double t = 2.0 * Rme + freepath;
+  const double tmp1 = t * t * t;
+  const double tmp2 = pow(4.0 * Rme * Rme + freepath * freepath, 1.5);
+  const double dd = (tmp1 - tmp2) / (6.0 * Rme * freepath) - 2.0 * Rme;
+  b.deltasq = dd * dd;
+  return b;
+}
+__device__ __forceinline__ double brown_pair(const BrownPart& a, const BrownPart& b) {
+  const double rad_sum = a.rad + b.rad;
+  const double diffus_sum = a.diffus + b.diffus;
+  const double tmp1 = rad_sum / (rad_sum + sqrt(a.deltasq + b.deltasq));
+  const double tmp2 = 4.0 * diffus_sum / (rad_sum * sqrt(a.speedsq + b.speedsq));
+  return 4.0 * PmcConst::pi * rad_sum * diffus_sum / (tmp1 + tmp2);
+}
+
+#endif  // __CUDACC__

@@ -1,0 +1,150 @@
+// rebalance.cu -- aero_state_rebalance (partmc/src/aero_state.F90:1765-1825),
+// aero_state_double (:1695-1718) and aero_state_halve (:1726-1758) for every
+// cell of the patch; one warp per cell.
+//
+// Doubling appends one copy (new id) of every (group, class) particle in
+// particle-index order and halves the weight magnitude.  Halving walks the
+// particle array backwards, removing with probability 1/2 by swap-with-last and
+// doubles the magnitude; the draw of particle i is addressed
+// (PH_HALVE, pass*4096 + (group,class), i), so all draws are evaluated in
+// parallel, the swap-with-last permutation is then replayed serially on
+// indices only, and the records move in parallel.
+#include "pmcgpu_internal.cuh"
+
+#define REB_WARPS 4
+
+__device__ __forceinline__ int warp_sum(int x) {
+  for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+  return x;
+}
+
+__global__ void __launch_bounds__(REB_WARPS * 32) k_rebalance(DevView v, int allow_doubling, int allow_halving,
+                                                               unsigned step) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * REB_WARPS + warp;
+  if (cell >= v.n_cells) return;
+  if (v.status[cell] != 0) return;
+  const size_t base = (size_t)cell * v.cap;
+  const size_t NS = (size_t)v.n_cells * v.cap;
+  int n_part = v.count[cell];
+  int err = 0;
+  int* map = v.L + (size_t)cell * 3 * v.cap;  // scratch: current slot -> original slot
+  const double ideal = v.ideal;
+
+  if (allow_doubling) {
+    for (int g = 1; g <= v.G && !err; g++)
+      for (int c = 1; c <= v.C && !err; c++) {
+        const int gc = (c - 1) * v.G + (g - 1);
+        for (;;) {
+          int m = 0;
+          for (int p = lane; p < n_part; p += 32) m += (v.wgc[base + p] == gc);
+          m = warp_sum(m);
+          if (!(((double)m < ideal / 2.0) && (m > 0))) break;
+          if (n_part + m > v.cap) {
+            err = PMCGPU_ERR_CAPACITY;
+            break;
+          }
+          // aero_state_double: copies appended in particle order, ids in the same order
+          const long long nx = v.next_id[cell];
+          int run = 0;
+          for (int p0 = 0; p0 < n_part; p0 += 32) {
+            const int p = p0 + lane;
+            const bool match = (p < n_part) && (v.wgc[base + p] == gc);
+            const unsigned bm = __ballot_sync(0xffffffffu, match);
+            if (match) {
+              const int r = run + __popc(bm & ((1u << lane) - 1u));
+              const int dst = n_part + r;
+              for (int s = 0; s < v.S; s++) v.vol[(size_t)s * NS + base + dst] = v.vol[(size_t)s * NS + base + p];
+              v.id[base + dst] = (nx + r - 1) * v.n_cells_global + v.gcell[cell] + 1;
+              v.wgc[base + dst] = gc;
+              v.nprim[base + dst] = v.nprim[base + p];
+              v.hyst[base + dst] = v.hyst[base + p];
+              v.lct[base + dst] = v.lct[base + p];
+              v.gct[base + dst] = v.gct[base + p];
+            }
+            run += __popc(bm);
+          }
+          __syncwarp();
+          n_part += m;
+          if (lane == 0) {
+            v.next_id[cell] = nx + m;
+            v.wmag[(size_t)cell * v.C * v.G + gc] *= 0.5;
+          }
+          __syncwarp();
+        }
+      }
+  }
+  if (allow_halving && !err) {
+    for (int g = 1; g <= v.G; g++)
+      for (int c = 1; c <= v.C; c++) {
+        const int gc = (c - 1) * v.G + (g - 1);
+        unsigned pass = 0;
+        for (;;) {
+          int m = 0;
+          for (int p = lane; p < n_part; p += 32) m += (v.wgc[base + p] == gc);
+          m = warp_sum(m);
+          if (!((double)m > ideal * 2.0)) break;
+          // removal decisions, all draws in parallel; map[p] = -1 marks a removal
+          for (int p = lane; p < n_part; p += 32) {
+            int keep = p;
+            if (v.wgc[base + p] == gc) {
+              const RKey key{v.seed, (unsigned)v.gcell[cell], step, PH_HALVE, pass * 4096u + (unsigned)gc, (unsigned)(p + 1)};
+              if (rng_uniform(key, 0) < 0.5) keep = -1;
+            }
+            map[p] = keep;
+          }
+          __syncwarp();
+          // replay the backward swap-with-last loop on indices only
+          int n_cur = n_part;
+          if (lane == 0) {
+            for (int i = n_part - 1; i >= 0; i--) {
+              if (map[i] < 0) {
+                if (i != n_cur - 1) map[i] = map[n_cur - 1];
+                n_cur--;
+              }
+            }
+          }
+          n_cur = __shfl_sync(0xffffffffu, n_cur, 0);
+          __syncwarp();
+          // sources are original slots >= n_cur, destinations < n_cur: disjoint
+          for (int p = lane; p < n_cur; p += 32) {
+            const int src = map[p];
+            if (src != p) {
+              for (int s = 0; s < v.S; s++) v.vol[(size_t)s * NS + base + p] = v.vol[(size_t)s * NS + base + src];
+              v.id[base + p] = v.id[base + src];
+              v.wgc[base + p] = v.wgc[base + src];
+              v.nprim[base + p] = v.nprim[base + src];
+              v.hyst[base + p] = v.hyst[base + src];
+              v.lct[base + p] = v.lct[base + src];
+              v.gct[base + p] = v.gct[base + src];
+            }
+          }
+          __syncwarp();
+          n_part = n_cur;
+          if (lane == 0) v.wmag[(size_t)cell * v.C * v.G + gc] *= 2.0;
+          __syncwarp();
+          pass++;
+        }
+      }
+  }
+  if (lane == 0) {
+    v.count[cell] = n_part;
+    if (err && v.status[cell] == 0) v.status[cell] = err;
+  }
+}
+
+int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step) {
+  DevView& v = ctx->v;
+  const int blocks = (v.n_cells + REB_WARPS - 1) / REB_WARPS;
+  k_rebalance<<<blocks, REB_WARPS * 32, 0, ctx->stream>>>(v, allow_doubling, allow_halving, step);
+  LAUNCH_CHECK(ctx);
+  return PMCGPU_OK;
+}
+
+extern "C" int pmcgpu_aero_state_rebalance(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving,
+                                           unsigned int step) {
+  if (!ctx) return PMCGPU_ERR_ARG;
+  int rc = pmc_rebalance_async(ctx, allow_doubling, allow_halving, step);
+  if (rc) return rc;
+  return pmc_first_status(ctx);
+}

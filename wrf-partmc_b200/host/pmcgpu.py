@@ -1,0 +1,279 @@
+"""Host-side mirror of the reference's entry points over the C ABI
+(include/pmcgpu.h).  Method names follow the Fortran they stand for:
+
+    aero_state_sort      partmc/src/aero_state.F90:3218
+    mc_coag              partmc/src/coagulation.F90:43
+    aero_state_rebalance partmc/src/aero_state.F90:1765
+    condense_particles   partmc/src/condense.F90:147
+    trans_aero           interface/wrf_pmc_trans_aero.F90:40
+    partmc_to_wrf        interface/wrf_pmc_driver.F90:1663
+
+Only ctypes and numpy are used; no oracle code is imported here and nothing
+runs on the CPU: a missing library or device raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+KERNEL_ADDITIVE, KERNEL_CONSTANT, KERNEL_BROWN, KERNEL_ZERO = 2, 3, 4, 5
+WEIGHT_NONE, WEIGHT_POWER = 1, 2
+
+_PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_LIB = None
+
+
+class PmcGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("pmcgpu error %d: %s" % (code, msg))
+        self.code = code
+
+
+def library_path():
+    return os.path.join(_PKG, "libpmcgpu.so")
+
+
+def load_library():
+    """Load libpmcgpu.so.  Fails loudly when it has not been built."""
+    global _LIB
+    if _LIB is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise RuntimeError("%s is missing: build it with __graft_entry__.build() "
+                               "(there is no CPU fallback for the aerosol step)" % path)
+        _LIB = C.CDLL(path)
+        _LIB.pmcgpu_last_error.restype = C.c_char_p
+        _LIB.pmcgpu_last_error.argtypes = [C.c_void_p]
+        _LIB.pmcgpu_launch_count.restype = C.c_longlong
+        _LIB.pmcgpu_launch_count.argtypes = [C.c_void_p]
+        _LIB.pmcgpu_stream.restype = C.c_void_p
+        _LIB.pmcgpu_stream.argtypes = [C.c_void_p]
+    return _LIB
+
+
+class _Config(C.Structure):
+    _fields_ = [("n_spec", C.c_int), ("density", C.POINTER(C.c_double)), ("kappa", C.POINTER(C.c_double)),
+                ("molec_weight", C.POINTER(C.c_double)), ("num_ions", C.POINTER(C.c_int)), ("i_water", C.c_int),
+                ("n_group", C.c_int), ("n_class", C.c_int), ("nx", C.c_int), ("nz", C.c_int), ("ny", C.c_int),
+                ("global_nx", C.c_int), ("global_ny", C.c_int), ("i_offset", C.c_int), ("j_offset", C.c_int),
+                ("periodic_x", C.c_int), ("periodic_y", C.c_int), ("n_part_ideal", C.c_double),
+                ("cell_capacity", C.c_int), ("max_bins", C.c_int), ("seed", C.c_uint), ("device", C.c_int)]
+
+
+def _f64(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _i64(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.int64)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class AeroData:
+    """aero_data_t (aero_data.F90:55-93): the species table the path reads."""
+
+    def __init__(self, density, kappa=None, molec_weight=None, num_ions=None, i_water=0):
+        self.density = _f64(density)
+        n = len(self.density)
+        self.n_spec = n
+        self.kappa = _f64(kappa if kappa is not None else np.zeros(n))
+        self.molec_weight = _f64(molec_weight if molec_weight is not None else np.full(n, 18e-3))
+        self.num_ions = _i32(num_ions if num_ions is not None else np.zeros(n))
+        self.i_water = int(i_water)
+
+
+class PartMCGPU:
+    """All aero_state_t / env_state_t of one WRF patch, resident on one B200."""
+
+    def __init__(self, aero_data, nx=1, nz=1, ny=1, n_group=1, n_class=1, n_part_ideal=1000.0, cell_capacity=None,
+                 max_bins=64, seed=1, device=0, global_nx=None, global_ny=None, i_offset=0, j_offset=0,
+                 periodic_x=True, periodic_y=True):
+        self.L = load_library()
+        self.data = aero_data
+        self.nx, self.nz, self.ny = nx, nz, ny
+        self.n_cells = nx * nz * ny
+        self.n_group, self.n_class = n_group, n_class
+        self.max_bins = max_bins
+        if cell_capacity is None:
+            cell_capacity = int(3 * n_part_ideal) + 64
+        self.cell_capacity = cell_capacity
+        cfg = _Config()
+        cfg.n_spec = aero_data.n_spec
+        cfg.density = aero_data.density.ctypes.data_as(C.POINTER(C.c_double))
+        cfg.kappa = aero_data.kappa.ctypes.data_as(C.POINTER(C.c_double))
+        cfg.molec_weight = aero_data.molec_weight.ctypes.data_as(C.POINTER(C.c_double))
+        cfg.num_ions = aero_data.num_ions.ctypes.data_as(C.POINTER(C.c_int))
+        cfg.i_water = aero_data.i_water
+        cfg.n_group, cfg.n_class = n_group, n_class
+        cfg.nx, cfg.nz, cfg.ny = nx, nz, ny
+        cfg.global_nx = global_nx if global_nx is not None else nx
+        cfg.global_ny = global_ny if global_ny is not None else ny
+        cfg.i_offset, cfg.j_offset = i_offset, j_offset
+        cfg.periodic_x, cfg.periodic_y = int(periodic_x), int(periodic_y)
+        cfg.n_part_ideal = float(n_part_ideal)
+        cfg.cell_capacity = cell_capacity
+        cfg.max_bins = max_bins
+        cfg.seed = seed
+        cfg.device = device
+        self.h = C.c_void_p()
+        rc = self.L.pmcgpu_create(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            msg = self.L.pmcgpu_last_error(self.h).decode() if self.h else "pmcgpu_create failed (no CUDA device?)"
+            raise PmcGpuError(rc, msg)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.pmcgpu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise PmcGpuError(rc, self.L.pmcgpu_last_error(self.h).decode())
+
+    # ---- state transfer
+    def set_particles(self, cell_count, vol, wgroup=None, wclass=None, ids=None, n_primary=None, hyst=None, lct=None,
+                      gct=None):
+        cc = _i32(cell_count)
+        assert len(cc) == self.n_cells
+        vol = _f64(vol)
+        a = [_i32(wgroup), _i32(wclass), _i64(ids), _i32(n_primary), _i32(hyst), _f64(lct), _f64(gct)]
+        self._chk(self.L.pmcgpu_set_particles(self.h, _p(cc), _p(vol), *[_p(x) for x in a]))
+
+    def counts(self):
+        out = np.zeros(self.n_cells, np.int32)
+        self._chk(self.L.pmcgpu_get_counts(self.h, _p(out)))
+        return out
+
+    def get_particles(self):
+        cnt = self.counts()
+        N = int(cnt.sum())
+        S = self.data.n_spec
+        out = dict(count=cnt, vol=np.zeros((S, N)), wgroup=np.zeros(N, np.int32), wclass=np.zeros(N, np.int32),
+                   id=np.zeros(N, np.int64), n_primary=np.zeros(N, np.int32), hyst=np.zeros(N, np.int32),
+                   lct=np.zeros(N), gct=np.zeros(N))
+        self._chk(self.L.pmcgpu_get_particles(self.h, C.c_longlong(N), _p(out["vol"]), _p(out["wgroup"]),
+                                              _p(out["wclass"]), _p(out["id"]), _p(out["n_primary"]),
+                                              _p(out["hyst"]), _p(out["lct"]), _p(out["gct"])))
+        return out
+
+    def set_next_id(self, next_id):
+        a = _i64(next_id)
+        self._chk(self.L.pmcgpu_set_next_id(self.h, _p(a)))
+
+    def get_next_id(self):
+        out = np.zeros(self.n_cells, np.int64)
+        self._chk(self.L.pmcgpu_get_next_id(self.h, _p(out)))
+        return out
+
+    def set_weights(self, wtype, magnitude, exponent):
+        n = self.n_cells * self.n_class * self.n_group
+        t, m, e = _i32(wtype), _f64(magnitude), _f64(exponent)
+        assert t.size == n and m.size == n and e.size == n
+        self._chk(self.L.pmcgpu_set_weights(self.h, _p(t), _p(m), _p(e)))
+
+    def get_weights(self):
+        shp = (self.n_cells, self.n_class, self.n_group)
+        t, m, e = np.zeros(shp, np.int32), np.zeros(shp), np.zeros(shp)
+        self._chk(self.L.pmcgpu_get_weights(self.h, _p(t), _p(m), _p(e)))
+        return t, m, e
+
+    def set_env(self, temp=None, pressure=None, rel_humid=None, inverse_density=None, cell_volume=None):
+        a = [_f64(x) for x in (temp, pressure, rel_humid, inverse_density, cell_volume)]
+        for x in a:
+            assert x is None or x.size == self.n_cells
+        self._chk(self.L.pmcgpu_set_env(self.h, *[_p(x) for x in a]))
+
+    def rel_humid(self):
+        out = np.zeros(self.n_cells)
+        self._chk(self.L.pmcgpu_get_rel_humid(self.h, _p(out)))
+        return out
+
+    # ---- the path
+    def aero_state_sort(self):
+        self._chk(self.L.pmcgpu_aero_state_sort(self.h))
+
+    def kernel_bounds(self, kernel_type):
+        self._chk(self.L.pmcgpu_kernel_bounds(self.h, C.c_int(kernel_type)))
+
+    def mc_coag(self, kernel_type, del_t, step=0):
+        ns, nc = np.zeros(self.n_cells, np.int32), np.zeros(self.n_cells, np.int32)
+        self._chk(self.L.pmcgpu_mc_coag(self.h, C.c_int(kernel_type), C.c_double(del_t), C.c_uint(step), _p(ns),
+                                        _p(nc)))
+        return ns, nc
+
+    def aero_state_rebalance(self, allow_doubling=True, allow_halving=True, step=0):
+        self._chk(self.L.pmcgpu_aero_state_rebalance(self.h, C.c_int(int(allow_doubling)),
+                                                     C.c_int(int(allow_halving)), C.c_uint(step)))
+
+    def update_density(self, new_inverse_density):
+        a = _f64(new_inverse_density)
+        self._chk(self.L.pmcgpu_update_density(self.h, _p(a)))
+
+    def partmc_to_wrf(self):
+        out = np.zeros((self.n_cells, self.n_class), np.float32)
+        self._chk(self.L.pmcgpu_num_conc_by_class(self.h, _p(out)))
+        return out
+
+    # ---- inspection
+    def grid(self):
+        nb, gmin, gmax = np.zeros(self.n_cells, np.int32), np.zeros(self.n_cells), np.zeros(self.n_cells)
+        self._chk(self.L.pmcgpu_get_grid(self.h, _p(nb), _p(gmin), _p(gmax)))
+        return nb, gmin, gmax
+
+    def bins(self):
+        N = int(self.counts().sum())
+        out = np.zeros(N, np.int32)
+        self._chk(self.L.pmcgpu_get_bins(self.h, C.c_longlong(N), _p(out)))
+        return out
+
+    def bin_counts(self):
+        out = np.zeros((self.n_cells, self.n_class, self.max_bins), np.int32)
+        self._chk(self.L.pmcgpu_get_bin_counts(self.h, _p(out)))
+        return out
+
+    def kernel_max(self, cell):
+        nb = int(self.grid()[0][cell])
+        out = np.zeros((nb, nb))
+        self._chk(self.L.pmcgpu_get_kernel_max(self.h, C.c_int(cell), _p(out)))
+        return out
+
+    def cell_status(self):
+        out = np.zeros(self.n_cells, np.int32)
+        self._chk(self.L.pmcgpu_get_cell_status(self.h, _p(out)))
+        return out
+
+    def launch_count(self):
+        return int(self.L.pmcgpu_launch_count(self.h))
+
+    def stream(self):
+        return self.L.pmcgpu_stream(self.h)
+
+    def synchronize(self):
+        self._chk(self.L.pmcgpu_synchronize(self.h))
+
+    def eval_kernel_brown(self, v1, d1, v2, d2, temp, pressure):
+        a = [_f64(x) for x in (v1, d1, v2, d2, temp, pressure)]
+        n = a[0].size
+        out = np.zeros(n)
+        self._chk(self.L.pmcgpu_eval_kernel_brown(self.h, C.c_int(n), *[_p(x) for x in a], _p(out)))
+        return out
+
+    def eval_philox(self, cell, step, phase, a, b, j):
+        arrs = [np.ascontiguousarray(x, dtype=np.uint32) for x in (cell, step, phase, a, b, j)]
+        n = arrs[0].size
+        out = np.zeros(n)
+        self._chk(self.L.pmcgpu_eval_philox(self.h, C.c_int(n), *[_p(x) for x in arrs], _p(out)))
+        return out
