@@ -147,8 +147,9 @@ class Oracle:
     def set_next_id(self, cell, v):
         self.L.pmco_set_next_id(self.h, C.c_int(cell), C.c_longlong(v))
 
-    def sort(self, cell, force_resort=True, physical=True):
-        self._chk(self.L.pmco_sort(self.h, C.c_int(cell), C.c_int(int(force_resort)), C.c_int(int(physical))))
+    def sort(self, cell, force_resort=True, physical=True, edge_recheck=False):
+        self._chk(self.L.pmco_sort(self.h, C.c_int(cell), C.c_int(int(force_resort)), C.c_int(int(physical)),
+                                   C.c_int(int(edge_recheck))))
 
     def grid(self, cell, cap=512):
         nb, gmin, gmax = C.c_int(0), C.c_double(0), C.c_double(0)

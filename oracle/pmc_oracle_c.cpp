@@ -149,12 +149,17 @@ double pmco_get_rel_humid(void* h, int cell) { return ((OracleDomain*)h)->env[ce
 // aero_state_sort (aero_state.F90:3218).  force_resort=1 models an entry state
 // with valid_sort = .false. (what every device step starts from); physical=1
 // additionally permutes apa into the device's (class, bin, index) order.
-int pmco_sort(void* h, int cell, int force_resort, int physical) {
+// edge_recheck=1 repeats aero_state_sort on the now valid state, which is what the
+// aero_state_sort call at the top of mc_coag (coagulation.F90:63) does after a
+// preceding full sort: the safety-factor test on occupied-bin edges
+// (aero_sorted.F90:258-276), possibly a new grid and a re-append in apa order.
+int pmco_sort(void* h, int cell, int force_resort, int physical, int edge_recheck) {
   OracleDomain* d = (OracleDomain*)h;
   ORACLE_TRY
   AeroState& st = d->cells[cell];
   if (force_resort) st.valid_sort = false;
   aero_state_sort(st);
+  if (edge_recheck) aero_state_sort(st);
   if (physical) aero_state_physical_sort(st);
   aero_sorted_check(st.sorted, st.apa, st.awa.n_group, st.awa.n_class);
   ORACLE_CATCH(d)

@@ -516,13 +516,15 @@ int pmc_mc_coag_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step) {
   return PMCGPU_OK;
 }
 
-int pmc_sort_async(pmcgpu_ctx* ctx);
+int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck);
 
 extern "C" int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned int step,
                               int* tot_n_samp, int* tot_n_coag) {
   if (!ctx) return PMCGPU_ERR_ARG;
-  // mc_coag starts with aero_state_sort (coagulation.F90:63)
-  int rc = pmc_sort_async(ctx);
+  // mc_coag starts with aero_state_sort (coagulation.F90:63).  The device state is
+  // unsorted between steps, so this is a full sort (valid_sort = .false.) followed by
+  // the bin-edge safety test the reference applies to an already sorted state.
+  int rc = pmc_sort_async(ctx, 1);
   if (rc) return rc;
   rc = pmc_mc_coag_async(ctx, coag_kernel_type, del_t, step);
   if (rc) return rc;

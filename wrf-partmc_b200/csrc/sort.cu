@@ -20,7 +20,7 @@ static const double BINS_PER_DECADE = 10.0;   // aero_sorted.F90:69
 static const double BIN_OVER_FACTOR = 10.0;   // :71
 static const double BIN_SAFETY_FACTOR = 3.0;  // :73
 
-__global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v) {
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge_recheck) {
   const int cell = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = v.count[cell];
@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v) {
   extern __shared__ int s_hist[];  // [SORT_WARPS][nk] then [nk] totals
   __shared__ double s_min[SORT_WARPS], s_max[SORT_WARPS];
   __shared__ double s_lnmin, s_lnmax;
-  __shared__ int s_nb, s_fail;
+  __shared__ int s_nb, s_fail, s_redo;
 
   // ---- phase 1: radius of every particle, r_min / r_max (aero_sorted.F90:277-290)
   double rmin = 1e300, rmax = 0.0;
@@ -97,44 +97,92 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v) {
     s_lnmax = (nb > 0) ? log(gmax) : 0.0;
   }
   __syncthreads();
-  const int nb = s_nb;
   // zero the published counts, (class, bin) -> bin_count[cell][c][b]
   int* bc = v.bin_count + (size_t)cell * v.C * v.nbcap;
   for (int q = tid; q < v.C * v.nbcap; q += SORT_THREADS) bc[q] = 0;
-  if (nb == 0 || s_fail) return;
-  const int nk = v.C * nb;
-  for (int q = tid; q < (SORT_WARPS + 1) * nk; q += SORT_THREADS) s_hist[q] = 0;
-  __syncthreads();
-  const double lnmin = s_lnmin, lnmax = s_lnmax;
-
+  if (s_nb == 0 || s_fail) return;
   // ---- phase 2: bin of every particle (bin_grid.F90:143) + per-warp histograms.
   // Warp w owns the contiguous index range [w*seg, (w+1)*seg) so that ranks
   // inside a key follow the original particle order (stable).
+  // With edge_recheck (the aero_state_sort call at the top of mc_coag, which sees
+  // valid_sort = .true.) the safety-factor test is repeated on the edges of the
+  // lowest / highest occupied bins (aero_sorted.F90:258-276); if that asks for a
+  // new grid the bins are recomputed once.
   const int seg = (n + SORT_WARPS - 1) / SORT_WARPS;
   const int lo = warp * seg, hi = min(n, lo + seg);
+  int nb = s_nb;
+  int nk = v.C * nb;
   int* myhist = s_hist + warp * nk;
-  for (int p0 = lo; p0 < hi; p0 += 32) {
-    const int p = p0 + lane;
-    int key = -1;
-    if (p < hi) {
-      int b = log_grid_find(lnmin, lnmax, nb, v.lnr[base + p]);
-      b = min(max(b, 1), nb);  // unreachable clamp: the grid was just checked against r_min / r_max
-      v.pbin[base + p] = b;
-      key = (v.wgc[base + p] / v.G) * nb + (b - 1);
-    }
-    const unsigned m = __match_any_sync(0xffffffffu, key);
-    if (key >= 0 && (m & ((1u << lane) - 1u)) == 0) myhist[key] += __popc(m);
-    __syncwarp();
-  }
-  __syncthreads();
-  // ---- exclusive scan: key-major, warp-minor
   int* tot = s_hist + SORT_WARPS * nk;
-  for (int k = tid; k < nk; k += SORT_THREADS) {
-    int t = 0;
-    for (int w = 0; w < SORT_WARPS; w++) t += s_hist[w * nk + k];
-    tot[k] = t;
-    bc[(k / nb) * v.nbcap + (k % nb)] = t;
+  for (int attempt = 0; attempt < 2; attempt++) {
+    nb = s_nb;
+    nk = v.C * nb;
+    myhist = s_hist + warp * nk;
+    tot = s_hist + SORT_WARPS * nk;
+    const double lnmin = s_lnmin, lnmax = s_lnmax;
+    for (int q = tid; q < (SORT_WARPS + 1) * nk; q += SORT_THREADS) s_hist[q] = 0;
+    __syncthreads();
+    for (int p0 = lo; p0 < hi; p0 += 32) {
+      const int p = p0 + lane;
+      int key = -1;
+      if (p < hi) {
+        int b = log_grid_find(lnmin, lnmax, nb, v.lnr[base + p]);
+        b = min(max(b, 1), nb);  // unreachable clamp: the grid was just checked against r_min / r_max
+        v.pbin[base + p] = b;
+        key = (v.wgc[base + p] / v.G) * nb + (b - 1);
+      }
+      const unsigned m = __match_any_sync(0xffffffffu, key);
+      if (key >= 0 && (m & ((1u << lane) - 1u)) == 0) myhist[key] += __popc(m);
+      __syncwarp();
+    }
+    __syncthreads();
+    for (int k = tid; k < nk; k += SORT_THREADS) {
+      int t = 0;
+      for (int w = 0; w < SORT_WARPS; w++) t += s_hist[w * nk + k];
+      tot[k] = t;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      s_redo = 0;
+      if (attempt == 0 && edge_recheck) {
+        int i_min = 0, i_max = 0;
+        for (int b = 1; b <= nb; b++) {
+          int t = 0;
+          for (int c = 0; c < v.C; c++) t += tot[c * nb + (b - 1)];
+          if (t > 0) {
+            if (i_min == 0) i_min = b;
+            i_max = b;
+          }
+        }
+        const double gmin = v.grid_min[cell], gmax = v.grid_max[cell];
+        const double r_min = grid_edge(gmin, gmax, nb, i_min);
+        const double r_max = grid_edge(gmin, gmax, nb, i_max + 1);
+        if ((r_min / gmin < BIN_SAFETY_FACTOR) || (gmax / r_max < BIN_SAFETY_FACTOR)) {
+          const double ngmin = r_min / BIN_OVER_FACTOR;
+          const double ngmax = r_max * BIN_OVER_FACTOR;
+          int nnb = (int)ceil((log10(ngmax) - log10(ngmin)) * BINS_PER_DECADE);
+          v.bounds_valid[cell] = 0;
+          if (nnb > v.nbcap) {
+            s_fail = 1;
+            if (v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_NBINS;
+            nnb = 0;
+          }
+          v.grid_nb[cell] = nnb;
+          v.grid_min[cell] = ngmin;
+          v.grid_max[cell] = ngmax;
+          s_nb = nnb;
+          s_lnmin = (nnb > 0) ? log(ngmin) : 0.0;
+          s_lnmax = (nnb > 0) ? log(ngmax) : 0.0;
+          s_redo = 1;
+        }
+      }
+    }
+    __syncthreads();
+    if (s_fail) return;
+    if (!s_redo) break;
   }
+  // ---- exclusive scan: key-major, warp-minor
+  for (int k = tid; k < nk; k += SORT_THREADS) bc[(k / nb) * v.nbcap + (k % nb)] = tot[k];
   __syncthreads();
   if (warp == 0) {
     int carry = 0;
@@ -202,7 +250,7 @@ static void swap_slabs(DevView& v) {
   std::swap(v.pbin, v.pbin_alt);
 }
 
-int pmc_sort_async(pmcgpu_ctx* ctx) {
+int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck) {
   DevView& v = ctx->v;
   const size_t smem = (size_t)(SORT_WARPS + 1) * v.C * v.nbcap * sizeof(int);
   if (smem > 200 * 1024) {
@@ -214,7 +262,7 @@ int pmc_sort_async(pmcgpu_ctx* ctx) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_sort_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  k_sort_cells<<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v);
+  k_sort_cells<<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, edge_recheck);
   LAUNCH_CHECK(ctx);
   // cells with an empty grid keep their (empty) slab: nothing to copy
   swap_slabs(v);
@@ -223,7 +271,7 @@ int pmc_sort_async(pmcgpu_ctx* ctx) {
 
 extern "C" int pmcgpu_aero_state_sort(pmcgpu_ctx* ctx) {
   if (!ctx) return PMCGPU_ERR_ARG;
-  int rc = pmc_sort_async(ctx);
+  int rc = pmc_sort_async(ctx, 0);
   if (rc) return rc;
   return pmc_first_status(ctx);
 }
