@@ -39,7 +39,8 @@ enum {
   PMCGPU_ERR_ACCEL = 6,           /* try_per_particle_coag would be taken (coagulation.F90:150), not built yet */
   PMCGPU_ERR_CONDENSE = 7,        /* condensation integrator failed (condense.F90:331-363 codes) */
   PMCGPU_ERR_PROB = 414897881,    /* transport probabilities invalid (wrf_pmc_trans.F90:702-771 assert codes) */
-  PMCGPU_ERR_NCCL = 9
+  PMCGPU_ERR_NCCL = 9,
+  PMCGPU_ERR_REWEIGHT = 10        /* aero_state_reweight with size-dependent weights (aero_state.F90:597), not built yet */
 };
 
 /* coag_kernel.F90:24-40 type codes */
@@ -112,6 +113,19 @@ int pmcgpu_kernel_bounds(pmcgpu_ctx* ctx, int coag_kernel_type);
  * per-cell outputs [n_cells], may be NULL.  step addresses the random draws. */
 int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned int step, int* tot_n_samp,
                    int* tot_n_coag);
+/* condense_particles (condense.F90:147) for every cell: env_state_initial is the cell's current
+ * env_state (pmcgpu_set_env), env_state_final = (temp_final, pressure_final) [n_cells]; on return the
+ * device env is the final one with rel_humid from the integrator (condense.F90:263).  reltol <= 0
+ * selects the reference's 1e-8.  Optional outputs [n_cells]: rel_humid_out; stats_out [n_cells][3] =
+ * internal steps, rejected steps, rate evaluations per particle; water_rel_error_out (condense.F90:315). */
+int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_final, const double* pressure_final,
+                              double del_t, double reltol, double* rel_humid_out, int* stats_out,
+                              double* water_rel_error_out);
+/* condense_equilib_particles (condense.F90:744) with each cell's current env_state. */
+int pmcgpu_condense_equilib_particles(pmcgpu_ctx* ctx);
+/* evaluation of condense_rates (condense.F90:371) on the device, for known-answer tests:
+ * in [n][9] = T,Tdot,H,p,pdot,V_comp,D,D_dry,kappa ; out [n][6] = Ddot,Hdot_i,dDdot_dD,dDdot_dH,dHdoti_dD,dHdoti_dH */
+int pmcgpu_eval_condense_rates(pmcgpu_ctx* ctx, int n, const double* in, double* out);
 /* aero_state_rebalance (aero_state.F90:1765) for every cell. */
 int pmcgpu_aero_state_rebalance(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned int step);
 /* scenario_update_aero_state, WRF branch (scenario.F90:331-334): awa *= old_rrho / rrho */

@@ -42,6 +42,8 @@ def lib():
         L.pmco_binomial_pmf.restype = C.c_double
         L.pmco_binomial_pmf.argtypes = [C.c_int, C.c_double, C.c_int]
         L.pmco_mt_u32.restype = C.c_uint
+        L.pmco_sat_vapor_pressure.restype = C.c_double
+        L.pmco_sat_vapor_pressure.argtypes = [C.c_double]
     return _LIB
 
 
@@ -194,9 +196,45 @@ class Oracle:
         self._chk(self.L.pmco_rebalance(self.h, C.c_int(cell), C.c_int(int(allow_doubling)),
                                         C.c_int(int(allow_halving)), C.c_uint(step)))
 
+    def env_rel_humid(self, cell):
+        return float(self.L.pmco_get_rel_humid(self.h, C.c_int(cell)))
+
+    def condense_equilib(self, cell, step=0):
+        self._chk(self.L.pmco_condense_equilib(self.h, C.c_int(cell), C.c_uint(step)))
+
+    def condense_particles(self, cell, T1, p1, del_t, step=0, reltol=0.0, method=0):
+        st = np.zeros(3, np.int32)
+        wre = C.c_double(0)
+        self._chk(self.L.pmco_condense_particles(self.h, C.c_int(cell), C.c_double(T1), C.c_double(p1),
+                                                 C.c_double(del_t), C.c_uint(step), C.c_double(reltol),
+                                                 C.c_int(method), _p(st, C.c_int), C.byref(wre)))
+        return st, wre.value
+
     def scale_weight(self, cell, g, c, ratio, allow_doubling=True, allow_halving=True, step=0):
         self._chk(self.L.pmco_scale_weight(self.h, C.c_int(cell), C.c_int(g), C.c_int(c), C.c_double(ratio),
                                            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step)))
+
+
+def condense_rates(inputs):
+    """inputs [n][9] = T, Tdot, H, p, pdot, V_comp, D, D_dry, kappa -> outputs [n][9] (condense.F90:74-84 order)"""
+    a = _f64(inputs).reshape(-1, 9)
+    out = np.zeros_like(a)
+    lib().pmco_condense_rates(C.c_int(a.shape[0]), _p(a, C.c_double), _p(out, C.c_double))
+    return out
+
+
+def condense_integrate(D, H, D_dry, kappa, num_conc, T0, p0, Tdot, pdot, del_t, reltol=1e-8, abstol_scale=1e-8,
+                       abstol_H=1e-10, h_init=0.0, method=4):
+    D = _f64(D).copy()
+    Hc = C.c_double(H)
+    st = np.zeros(3, np.int32)
+    a = [_f64(D_dry), _f64(kappa), _f64(num_conc)]
+    rc = lib().pmco_condense_integrate(C.c_int(len(D)), _p(D, C.c_double), C.byref(Hc), _p(a[0], C.c_double),
+                                       _p(a[1], C.c_double), _p(a[2], C.c_double), C.c_double(T0), C.c_double(p0),
+                                       C.c_double(Tdot), C.c_double(pdot), C.c_double(del_t), C.c_double(reltol),
+                                       C.c_double(abstol_scale), C.c_double(abstol_H), C.c_double(h_init),
+                                       C.c_int(method), _p(st, C.c_int))
+    return rc, D, Hc.value, st
 
 
 def kernel_brown(v1, d1, v2, d2, T, p):

@@ -3,34 +3,12 @@
 // include/pmcgpu.h so that the parity tests drive both with the same arrays.
 #include "pmc_oracle.hpp"
 #include "pmc_oracle_ext.hpp"
+#include "pmc_oracle_domain.hpp"
 #include <cstring>
 #include <memory>
 #include <thread>
 
 using namespace pmco;
-
-struct OracleDomain {
-  AeroData data;
-  std::vector<AeroState> cells;
-  std::vector<EnvState> env;
-  std::unique_ptr<Rng> rng;
-  std::vector<int64_t> global_cell;  // global cell index of each local cell (rng address + id rank)
-  std::string last_error;
-  TransDomain trans;  // transport geometry + met + probabilities (pmc_oracle_ext.hpp)
-};
-
-#define ORACLE_TRY try {
-#define ORACLE_CATCH(D)                       \
-  }                                           \
-  catch (const PmcError& e) {                 \
-    (D)->last_error = e.what();               \
-    return e.code ? e.code : -1;              \
-  }                                           \
-  catch (const std::exception& e) {           \
-    (D)->last_error = e.what();               \
-    return -1;                                \
-  }                                           \
-  return 0;
 
 extern "C" {
 

@@ -1,0 +1,375 @@
+// pmc_oracle_cond.cpp -- oracle restatement of water condensation
+// (partmc/src/condense.F90).  TEST INFRASTRUCTURE ONLY (see pmc_oracle.hpp).
+#include "pmc_oracle_ext.hpp"
+#include <algorithm>
+#include <cstdio>
+
+namespace pmco {
+
+double sat_vapor_pressure(double temp) {
+  return Const::water_eq_vap_press * std::pow(10.0, 7.45 * (temp - Const::water_freeze_temp) / (temp - 38.0));
+}
+
+// condense.F90:371-502, statement for statement
+void condense_rates(const CondenseRatesInputs& in, CondenseRatesOutputs& out) {
+  const double rho_w = Const::water_density;
+  const double M_w = Const::water_molec_weight;
+  const double P_0 =
+      Const::water_eq_vap_press * std::pow(10.0, 7.45 * (in.T - Const::water_freeze_temp) / (in.T - 38.0));
+  const double dP0_dT_div_P0 =
+      7.45 * std::log(10.0) * (Const::water_freeze_temp - 38.0) / ((in.T - 38.0) * (in.T - 38.0));
+  const double rho_air = Const::air_molec_weight * in.p / (Const::univ_gas_const * in.T);
+  const double k_a = 1e-3 * (4.39 + 0.071 * in.T);
+  const double D_v = 0.211e-4 / (in.p / Const::air_std_press) * std::pow(in.T / 273.0, 1.94);
+  const double U = Const::water_latent_heat * rho_w / (4.0 * in.T);
+  const double V = 4.0 * M_w * P_0 / (rho_w * Const::univ_gas_const * in.T);
+  const double W = Const::water_latent_heat * M_w / (Const::univ_gas_const * in.T);
+  const double X = 4.0 * M_w * Const::water_surf_eng / (Const::univ_gas_const * in.T * rho_w);
+  const double Y = 2.0 * k_a / (Const::accom_coeff * rho_air * Const::air_spec_heat) *
+                   std::sqrt(2.0 * Const::pi * Const::air_molec_weight / (Const::univ_gas_const * in.T));
+  const double Z =
+      2.0 * D_v / Const::accom_coeff * std::sqrt(2.0 * Const::pi * M_w / (Const::univ_gas_const * in.T));
+
+  out.Hdot_env = -dP0_dT_div_P0 * in.Tdot * in.H + in.H * in.pdot / in.p;
+  out.dHdotenv_dD = 0.0;
+  out.dHdotenv_dH = -dP0_dT_div_P0 * in.Tdot + in.pdot / in.p;
+
+  if (in.D <= in.D_dry) {
+    const double k_ap = k_a / (1.0 + Y / in.D_dry);
+    const double D_vp = D_v / (1.0 + Z / in.D_dry);
+    const double delta_star = U * V * D_vp * in.H / k_ap;
+    out.Ddot = k_ap * delta_star / (U * in.D_dry);
+    out.Hdot_i = -2.0 * Const::pi / (V * in.V_comp) * (in.D_dry * in.D_dry) * out.Ddot;
+    const double dh_ddelta = k_ap;
+    const double dh_dH = -U * V * D_vp;
+    const double ddeltastar_dH = -dh_dH / dh_ddelta;
+    out.dDdot_dD = 0.0;
+    out.dDdot_dH = k_ap / (U * in.D_dry) * ddeltastar_dH;
+    out.dHdoti_dD = -2.0 * Const::pi / (V * in.V_comp) * (in.D_dry * in.D_dry) * out.dDdot_dD;
+    out.dHdoti_dH = -2.0 * Const::pi / (V * in.V_comp) * (in.D_dry * in.D_dry) * out.dDdot_dH;
+    return;
+  }
+  const double D3 = in.D * in.D * in.D, Dd3 = in.D_dry * in.D_dry * in.D_dry;
+  const double k_ap = k_a / (1.0 + Y / in.D);
+  const double dkap_dD = k_a * Y / ((in.D + Y) * (in.D + Y));
+  const double D_vp = D_v / (1.0 + Z / in.D);
+  const double dDvp_dD = D_v * Z / ((in.D + Z) * (in.D + Z));
+  const double a_w = (D3 - Dd3) / (D3 + (in.kappa - 1.0) * Dd3);
+  const double den = D3 + (in.kappa - 1.0) * Dd3;
+  const double daw_dD = 3.0 * (in.D * in.D) * in.kappa * Dd3 / (den * den);
+  double delta_star = 0.0, h = 0.0, dh_ddelta = 1.0;
+  for (int newton_step = 1; newton_step <= 5; newton_step++) {
+    delta_star = delta_star - h / dh_ddelta;
+    const double ex = std::exp(W * delta_star / (1.0 + delta_star) + (X / in.D) / (1.0 + delta_star));
+    h = k_ap * delta_star - U * V * D_vp * (in.H - a_w / (1.0 + delta_star) * ex);
+    dh_ddelta = k_ap - U * V * D_vp * a_w / ((1.0 + delta_star) * (1.0 + delta_star)) *
+                           (1.0 - W / (1.0 + delta_star) + (X / in.D) / (1.0 + delta_star)) * ex;
+  }
+  out.Ddot = k_ap * delta_star / (U * in.D);
+  out.Hdot_i = -2.0 * Const::pi / (V * in.V_comp) * (in.D * in.D) * out.Ddot;
+  const double ex = std::exp((W * delta_star) / (1.0 + delta_star) + (X / in.D) / (1.0 + delta_star));
+  const double dh_dD = dkap_dD * delta_star - U * V * dDvp_dD * in.H +
+                       U * V * (a_w * dDvp_dD + D_vp * daw_dD - D_vp * a_w * (X / (in.D * in.D)) / (1.0 + delta_star)) *
+                           (1.0 / (1.0 + delta_star)) * ex;
+  const double dh_dH = -U * V * D_vp;
+  const double ddeltastar_dD = -dh_dD / dh_ddelta;
+  const double ddeltastar_dH = -dh_dH / dh_ddelta;
+  out.dDdot_dD = dkap_dD * delta_star / (U * in.D) + k_ap * ddeltastar_dD / (U * in.D) -
+                 k_ap * delta_star / (U * (in.D * in.D));
+  out.dDdot_dH = k_ap / (U * in.D) * ddeltastar_dH;
+  out.dHdoti_dD = -2.0 * Const::pi / (V * in.V_comp) * (2.0 * in.D * out.Ddot + (in.D * in.D) * out.dDdot_dD);
+  out.dHdoti_dH = -2.0 * Const::pi / (V * in.V_comp) * (in.D * in.D) * out.dDdot_dH;
+}
+
+// condense.F90:701-739
+void condense_equilib_particle(const EnvState& env, const AeroData& d, Particle& p) {
+  const double X = 4.0 * Const::water_molec_weight * Const::water_surf_eng /
+                   (Const::univ_gas_const * env.temp * Const::water_density);
+  const double kappa = particle_solute_kappa(p, d);
+  const double D_dry = 2.0 * sphere_vol2rad(particle_solute_volume(p, d));
+  double D = D_dry, g = 0.0, dg_dD = 1.0;
+  const double Dd3 = D_dry * D_dry * D_dry;
+  for (int newton_step = 1; newton_step <= 20; newton_step++) {
+    D = D - g / dg_dD;
+    const double D3 = D * D * D;
+    const double a_w = (D3 - Dd3) / (D3 + (kappa - 1.0) * Dd3);
+    const double den = D3 + (kappa - 1.0) * Dd3;
+    const double daw_dD = 3.0 * (D * D) * kappa * Dd3 / (den * den);
+    g = env.rel_humid - a_w * std::exp(X / D);
+    dg_dD = -daw_dD * std::exp(X / D) + a_w * std::exp(X / D) * (X / (D * D));
+  }
+  p.vol[d.i_water - 1] = sphere_rad2vol(D / 2.0) - sphere_rad2vol(D_dry / 2.0);
+}
+void condense_equilib_particles(const EnvState& env, const AeroData& d, AeroState& st, const RunCtx& rc) {
+  st.valid_sort = false;
+  std::vector<double> rw((size_t)st.n_part());
+  for (int i = 0; i < st.n_part(); i++) rw[i] = awa_single_num_conc(st.awa, st.apa[i]);
+  for (int i = st.n_part(); i >= 1; i--) condense_equilib_particle(env, d, st.apa[i - 1]);
+  aero_state_reweight(st, rw, rc, 1000u);
+}
+
+// ------------------------------------------------------------------ integrator
+namespace {
+struct CondSys {
+  int n;
+  const double *D_dry, *kappa, *num_conc;
+  double T0, p0, Tdot, pdot;
+  // f and the arrow-head Jacobian at (t, D, H): condense_vf_f / condense_jac (condense.F90:509-616)
+  void eval(double t, const double* D, double H, double* fD, double& fH, double* a, double* b, double* c, double& dd,
+            int& n_rates) const {
+    CondenseRatesInputs in;
+    CondenseRatesOutputs out{};
+    in.T = T0 + t * Tdot;
+    in.p = p0 + t * pdot;
+    in.Tdot = Tdot;
+    in.pdot = pdot;
+    in.H = H;
+    double Hdot = 0.0, dHdot_dH = 0.0;
+    for (int i = 0; i < n; i++) {
+      in.D = D[i];
+      in.D_dry = D_dry[i];
+      in.V_comp = (in.T * p0) / (T0 * in.p) / num_conc[i];
+      in.kappa = kappa[i];
+      condense_rates(in, out);
+      fD[i] = out.Ddot;
+      Hdot += out.Hdot_i;
+      if (a) {
+        a[i] = out.dDdot_dD;
+        b[i] = out.dDdot_dH;
+        c[i] = out.dHdoti_dD + out.dHdotenv_dD;
+        dHdot_dH += out.dHdoti_dH;
+      }
+    }
+    if (n == 0) {  // Hdot_env does not depend on the particle
+      in.D = 1e-7;
+      in.D_dry = 1e-7;
+      in.V_comp = 1.0;
+      in.kappa = 0.0;
+      condense_rates(in, out);
+    }
+    n_rates += n;
+    fH = Hdot + out.Hdot_env;
+    if (a) dd = dHdot_dH + out.dHdotenv_dH;
+  }
+};
+}  // namespace
+
+// Rosenbrock tableaux in the (A, C, M, E, alpha, gamma_i) form:
+//   (1/(h gamma) - J) K_i = f(t + alpha_i h, y + sum_j A_ij K_j) + sum_j (C_ij / h) K_j + gamma_i h df/dt
+//   y_new = y + sum_i M_i K_i,  err = sum_i E_i K_i
+struct RosTableau {
+  int S;
+  double gamma;
+  double A[6][6], C[6][6], M[6], E[6], alpha[6], gam[6];
+  bool newf[6];
+  double elo;  // order used by the step-size controller
+};
+static RosTableau tableau_rodas3() {
+  // RODAS3 (Sandu, Verwer, Blom, Spee, Carmichael, Potra 1997): 4 stages, order 3(2),
+  // stiffly accurate, L-stable.
+  RosTableau t{};
+  t.S = 4;
+  t.gamma = 0.5;
+  t.A[2][0] = 2.0;
+  t.A[3][0] = 2.0; t.A[3][2] = 1.0;
+  t.C[1][0] = 4.0;
+  t.C[2][0] = 1.0; t.C[2][1] = -1.0;
+  t.C[3][0] = 1.0; t.C[3][1] = -1.0; t.C[3][2] = -8.0 / 3.0;
+  t.M[0] = 2.0; t.M[1] = 0.0; t.M[2] = 1.0; t.M[3] = 1.0;
+  t.E[3] = 1.0;
+  t.alpha[0] = 0.0; t.alpha[1] = 0.0; t.alpha[2] = 1.0; t.alpha[3] = 1.0;
+  t.gam[0] = 0.5; t.gam[1] = 1.5; t.gam[2] = 0.0; t.gam[3] = 0.0;
+  t.newf[0] = true; t.newf[1] = false; t.newf[2] = true; t.newf[3] = true;
+  t.elo = 3.0;
+  return t;
+}
+static RosTableau tableau_rodas4() {
+  // RODAS4 (Hairer & Wanner, Solving ODEs II, sect. IV.7): 6 stages, order 4(3),
+  // stiffly accurate, L-stable.
+  RosTableau t{};
+  t.S = 6;
+  t.gamma = 0.25;
+  t.alpha[0] = 0.0; t.alpha[1] = 0.386; t.alpha[2] = 0.210; t.alpha[3] = 0.630; t.alpha[4] = 1.0; t.alpha[5] = 1.0;
+  t.gam[0] = 0.25; t.gam[1] = -0.1043; t.gam[2] = 0.1035; t.gam[3] = -0.3620000000000023e-01; t.gam[4] = 0.0; t.gam[5] = 0.0;
+  t.A[1][0] = 0.1544000000000000e+01;
+  t.A[2][0] = 0.9466785280815826; t.A[2][1] = 0.2557011698983284;
+  t.A[3][0] = 0.3314825187068521e+01; t.A[3][1] = 0.2896124015972201e+01; t.A[3][2] = 0.9986419139977817;
+  t.A[4][0] = 0.1221224509226641e+01; t.A[4][1] = 0.6019134481288629e+01; t.A[4][2] = 0.1253708332932087e+02;
+  t.A[4][3] = -0.6878860361058950;
+  t.A[5][0] = t.A[4][0]; t.A[5][1] = t.A[4][1]; t.A[5][2] = t.A[4][2]; t.A[5][3] = t.A[4][3]; t.A[5][4] = 1.0;
+  t.C[1][0] = -0.5668800000000000e+01;
+  t.C[2][0] = -0.2430093356833875e+01; t.C[2][1] = -0.2063599157091915;
+  t.C[3][0] = -0.1073529058151375; t.C[3][1] = -0.9594562251023355e+01; t.C[3][2] = -0.2047028614809616e+02;
+  t.C[4][0] = 0.7496443313967647e+01; t.C[4][1] = -0.1024680431464352e+02; t.C[4][2] = -0.3399990352819905e+02;
+  t.C[4][3] = 0.1170890893206160e+02;
+  t.C[5][0] = 0.8083246795921522e+01; t.C[5][1] = -0.7981132988064893e+01; t.C[5][2] = -0.3152159432874371e+02;
+  t.C[5][3] = 0.1631930543123136e+02; t.C[5][4] = -0.6058818238834054e+01;
+  t.M[0] = t.A[4][0]; t.M[1] = t.A[4][1]; t.M[2] = t.A[4][2]; t.M[3] = t.A[4][3]; t.M[4] = 1.0; t.M[5] = 1.0;
+  t.E[5] = 1.0;
+  for (int i = 0; i < 6; i++) t.newf[i] = true;
+  t.elo = 4.0;
+  return t;
+}
+
+int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const double* kappa,
+                       const double* num_conc, double T0, double p0, double Tdot, double pdot, double del_t,
+                       const CondenseOpts& opt, CondenseStats& stats) {
+  const RosTableau tb = (opt.method == 4) ? tableau_rodas4() : tableau_rodas3();
+  const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.9, FAC_REJ = 0.1;
+  const double DT_FD = 1e-2;  // forward difference in t for df/dt (T and p are linear in t)
+  CondSys sys{n, D_dry, kappa, num_conc, T0, p0, Tdot, pdot};
+  const int S = tb.S;
+  std::vector<double> atol((size_t)n), f0((size_t)n), ft((size_t)n), a((size_t)n), b((size_t)n), c((size_t)n),
+      y((size_t)n), fs((size_t)n), dfdt((size_t)n), r((size_t)n);
+  std::vector<std::vector<double>> K((size_t)S, std::vector<double>((size_t)n));
+  double KH[6];
+  for (int i = 0; i < n; i++) atol[i] = std::max(1e-30, opt.abstol_scale * (D[i] - D_dry[i]));
+  double H = *Hio;
+  double t = 0.0;
+  double h = (opt.h_init > 0.0) ? std::min(opt.h_init, del_t) : del_t;
+  double h_natural = h;  // last step size chosen by the controller (not by hitting the end of the interval)
+  stats.n_steps = stats.n_reject = stats.n_rates = 0;
+  bool reject_last = false, reject_more = false;
+  while (t < del_t) {
+    if (stats.n_steps + stats.n_reject >= opt.max_steps) return 6;  // PMC_CONDENSE_SOLVER_SET_MAX_STEPS-like
+    bool truncated = false;
+    if (t + h > del_t * (1.0 - 1e-14)) {
+      h_natural = h;
+      h = del_t - t;
+      truncated = true;
+    }
+    double f0H, ftH, dd, dummy;
+    sys.eval(t, D, H, f0.data(), f0H, a.data(), b.data(), c.data(), dd, stats.n_rates);
+    sys.eval(t + DT_FD, D, H, ft.data(), ftH, nullptr, nullptr, nullptr, dummy, stats.n_rates);
+    for (int i = 0; i < n; i++) dfdt[i] = (ft[i] - f0[i]) / DT_FD;
+    const double dfdtH = (ftH - f0H) / DT_FD;
+    for (;;) {
+      const double eps = 1.0 / (tb.gamma * h);
+      double sden = 0.0;
+      for (int i = 0; i < n; i++) sden += c[i] * b[i] / (eps - a[i]);
+      const double lhs_H = eps - dd - sden;
+      double fsH = f0H;
+      for (int i = 0; i < n; i++) fs[i] = f0[i];
+      for (int st = 0; st < S; st++) {
+        if (st > 0 && tb.newf[st]) {
+          double Hs = H;
+          for (int i = 0; i < n; i++) y[i] = D[i];
+          for (int j = 0; j < st; j++) {
+            if (tb.A[st][j] == 0.0) continue;
+            for (int i = 0; i < n; i++) y[i] += tb.A[st][j] * K[j][i];
+            Hs += tb.A[st][j] * KH[j];
+          }
+          sys.eval(t + tb.alpha[st] * h, y.data(), Hs, fs.data(), fsH, nullptr, nullptr, nullptr, dummy,
+                   stats.n_rates);
+        }
+        double rH = fsH + h * tb.gam[st] * dfdtH;
+        for (int i = 0; i < n; i++) r[i] = fs[i] + h * tb.gam[st] * dfdt[i];
+        for (int j = 0; j < st; j++) {
+          if (tb.C[st][j] == 0.0) continue;
+          const double cj = tb.C[st][j] / h;
+          for (int i = 0; i < n; i++) r[i] += cj * K[j][i];
+          rH += cj * KH[j];
+        }
+        double ssum = 0.0;
+        for (int i = 0; i < n; i++) ssum += c[i] * r[i] / (eps - a[i]);
+        KH[st] = (rH + ssum) / lhs_H;
+        for (int i = 0; i < n; i++) K[st][i] = (r[i] + b[i] * KH[st]) / (eps - a[i]);
+      }
+      // weighted RMS error norm with CVODE-style weights (condense.F90:239-255 tolerances)
+      double esum = 0.0;
+      for (int i = 0; i < n; i++) {
+        double ynew = D[i], e = 0.0;
+        for (int j = 0; j < S; j++) {
+          ynew += tb.M[j] * K[j][i];
+          e += tb.E[j] * K[j][i];
+        }
+        y[i] = ynew;
+        const double w = opt.reltol * std::max(std::fabs(D[i]), std::fabs(ynew)) + atol[i];
+        esum += (e / w) * (e / w);
+      }
+      double Hnew = H, eH = 0.0;
+      for (int j = 0; j < S; j++) {
+        Hnew += tb.M[j] * KH[j];
+        eH += tb.E[j] * KH[j];
+      }
+      {
+        const double w = opt.reltol * std::max(std::fabs(H), std::fabs(Hnew)) + opt.abstol_H;
+        esum += (eH / w) * (eH / w);
+      }
+      double err = std::sqrt(esum / (double)(n + 1));
+      if (!std::isfinite(err)) err = 1e10;
+      err = std::max(err, 1e-10);
+      const double fac = std::min(FAC_MAX, std::max(FAC_MIN, FAC_SAFE / std::pow(err, 1.0 / tb.elo)));
+      double hnew = h * fac;
+      if (err <= 1.0) {
+        for (int i = 0; i < n; i++) D[i] = y[i];
+        H = Hnew;
+        t += h;
+        stats.n_steps++;
+        if (reject_last) hnew = std::min(hnew, h);  // no growth right after a rejection
+        reject_last = false;
+        reject_more = false;
+        h = truncated ? std::max(h_natural, hnew) : hnew;
+        h_natural = h;
+        stats.h_last = h_natural;
+        break;
+      }
+      stats.n_reject++;
+      if (stats.n_steps + stats.n_reject >= opt.max_steps) return 6;
+      if (reject_more) hnew = h * FAC_REJ;
+      reject_more = reject_last;
+      reject_last = true;
+      h = hnew;
+      truncated = false;
+      if (!(h > 1e-13 * del_t)) return 7;  // PMC_CONDENSE_SOLVER_FAIL-like
+    }
+  }
+  *Hio = H;
+  return 0;
+}
+
+void condense_particles(AeroState& st, const AeroData& d, const EnvState& env_initial, EnvState& env_final,
+                        double del_t, const RunCtx& rc, const CondenseOpts& opt, CondenseStats& stats) {
+  const int n = st.n_part();
+  const int iw = d.i_water - 1;
+  double water_vol_conc_initial = 0.0;
+  for (int i = 0; i < n; i++) water_vol_conc_initial += st.apa[i].vol[iw] * awa_num_conc(st.awa, st.apa[i]);
+  const double Tdot = (env_final.temp - env_initial.temp) / del_t;
+  const double pdot = (env_final.pressure - env_initial.pressure) / del_t;
+  std::vector<double> kappa((size_t)n), D_dry((size_t)n), nc((size_t)n), D((size_t)n);
+  for (int i = n - 1; i >= 0; i--) {
+    kappa[i] = particle_solute_kappa(st.apa[i], d);
+    D_dry[i] = 2.0 * sphere_vol2rad(particle_solute_volume(st.apa[i], d));
+    nc[i] = awa_num_conc(st.awa, st.apa[i]);
+    D[i] = 2.0 * particle_radius(st.apa[i]);
+  }
+  double H = env_initial.rel_humid;
+  const int rcode = condense_integrate(n, D.data(), &H, D_dry.data(), kappa.data(), nc.data(), env_initial.temp,
+                                       env_initial.pressure, Tdot, pdot, del_t, opt, stats);
+  if (rcode != 0) die_msg(rcode == 6 ? 592214019 : 592432510, "condense_solver failed");  // condense.F90:331-363
+  env_final.rel_humid = H;
+  double water_vol_conc_final = 0.0;
+  std::vector<double> rw((size_t)n);
+  for (int i = 0; i < n; i++) rw[i] = awa_single_num_conc(st.awa, st.apa[i]);
+  for (int i = 0; i < n; i++) {
+    const double num_conc = awa_num_conc(st.awa, st.apa[i]);
+    st.apa[i].vol[iw] = sphere_rad2vol(D[i] / 2.0) - particle_solute_volume(st.apa[i], d);
+    st.apa[i].vol[iw] = std::max(0.0, st.apa[i].vol[iw]);
+    water_vol_conc_final += st.apa[i].vol[iw] * num_conc;
+  }
+  // sizes changed: the reference leaves valid_sort alone here (the lists are
+  // stale until the next sort); the device always re-sorts, so mark it invalid
+  st.valid_sort = false;
+  aero_state_reweight(st, rw, rc, 0u);
+  const double V_comp_ratio = env_final.temp * env_initial.pressure / (env_initial.temp * env_final.pressure);
+  const double rho_w = d.density[iw];
+  const double M_w = d.molec_weight[iw];
+  const double vapor_i = M_w / (Const::univ_gas_const * env_initial.temp) * sat_vapor_pressure(env_initial.temp) *
+                         env_initial.rel_humid / rho_w;
+  const double vapor_f = M_w / (Const::univ_gas_const * env_final.temp) * sat_vapor_pressure(env_final.temp) *
+                         env_final.rel_humid * V_comp_ratio / rho_w;
+  stats.water_rel_error =
+      ((vapor_f - vapor_i) + (water_vol_conc_final - water_vol_conc_initial)) / (vapor_f + water_vol_conc_final);
+}
+
+}  // namespace pmco

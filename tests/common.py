@@ -131,3 +131,46 @@ def assert_same_population(g, o, case, exact_fp=True, rtol=0.0):
             np.testing.assert_allclose(P["vol"][:, a:b], q["vol"], rtol=rtol, atol=0)
         ot, om, oe = o.get_weights(c)
         np.testing.assert_allclose(m[c].ravel(), om, rtol=1e-13)
+
+
+# ---------------------------------------------------------------- condensation scenario
+def condense_case(n_per_mode=500, n_cells=1, seed=1):
+    """The partmc/test/condense scenario as a deterministic population: both log-normal modes of
+    aero_init_dist.dat represented by n_per_mode particles at the quantiles (i + 1/2) / n of their
+    diameter distribution, one weight class per mode with flat weight N_mode / n_per_mode, composition
+    OC : SO4 : NH4 = 1.375 : 1 : 0.375 by mass (aero_init_comp.dat), 20-species table (aero_data.dat)."""
+    from scipy.stats import norm
+    sp = SPEC20
+    modes = [(3.2e9, 2e-8, 0.161), (2.9e9, 1.16e-7, 0.217)]
+    mass_frac = {"OC": 1.375, "SO4": 1.0, "NH4": 0.375}
+    vf = np.zeros(20)
+    for k, val in mass_frac.items():
+        i = sp["names"].index(k)
+        vf[i] = val / sp["density"][i]
+    vf /= vf.sum()
+    vols, cls = [], []
+    for m, (N, dg, ls) in enumerate(modes):
+        q = (np.arange(n_per_mode) + 0.5) / n_per_mode
+        diam = dg * 10 ** (ls * norm.ppf(q))
+        v = np.pi / 6 * diam ** 3
+        vols.append(vf[:, None] * v[None, :])
+        cls += [m + 1] * n_per_mode
+    vol1 = np.concatenate(vols, axis=1)
+    cls1 = np.array(cls, np.int32)
+    n1 = 2 * n_per_mode
+    rng = np.random.default_rng(seed)
+    vol = np.concatenate([vol1 * (1.0 + 0.05 * c) for c in range(n_cells)], axis=1)
+    N = n1 * n_cells
+    shp = (n_cells, 2, 1)
+    wmag = np.zeros(shp)
+    wmag[:, 0, 0] = modes[0][0] / n_per_mode
+    wmag[:, 1, 0] = modes[1][0] / n_per_mode
+    case = dict(n_cells=n_cells, nx=n_cells, nz=1, ny=1, n_spec=20, n_class=2, n_group=1,
+                sp=dict(density=sp["density"], num_ions=sp["num_ions"], molec_weight=sp["molec_weight"],
+                        kappa=sp["kappa"], i_water=20),
+                counts=np.full(n_cells, n1, np.int32), vol=vol, wclass=np.tile(cls1, n_cells),
+                wgroup=np.ones(N, np.int32), id=np.arange(1, N + 1, dtype=np.int64), n_primary=np.ones(N, np.int32),
+                hyst=np.zeros(N, np.int32), lct=np.zeros(N), gct=np.zeros(N), wtype=np.ones(shp, np.int32), wmag=wmag,
+                wexp=np.zeros(shp), T=np.full(n_cells, 290.0), P=np.full(n_cells, 1e5), seed=seed,
+                n_part_ideal=float(n1))
+    return case

@@ -1,0 +1,120 @@
+"""GPU parity tests for condensation: the device integrator against the CPU oracle
+(1e-10 relative, north star) and against the reference's golden RH table."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import common
+from test_oracle_condense import _rates_inputs
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import wrf_partmc_b200 as W
+    from oracle import oracle as O
+    return W, O
+
+
+def test_condense_rates_device_vs_oracle(mods):
+    """condense.F90:371-502 including the dry branch: 1e-10 relative."""
+    W, O = mods
+    g = W.PartMCGPU(W.AeroData([1000.0]))
+    a = _rates_inputs(5000, seed=3)
+    dev = g.eval_condense_rates(a)
+    ref = O.condense_rates(a)[:, [0, 1, 3, 4, 5, 6]]
+    scale = np.abs(ref).max(axis=0)
+    rel = np.abs(dev - ref) / np.maximum(np.abs(ref), 1e-6 * scale)
+    assert rel.max() < 1e-10, rel.max(axis=0)
+
+
+def test_condense_equilib_device_vs_oracle(mods):
+    W, O = mods
+    case = common.condense_case(200, n_cells=3)
+    g = common.gpu_from_case(W, case)
+    o = common.oracle_from_case(O, case)
+    rh = np.array([0.95, 0.8, 0.6])
+    g.set_env(rel_humid=rh)
+    g.condense_equilib_particles()
+    for c in range(3):
+        o.set_env(c, T=case["T"][c], p=case["P"][c], RH=rh[c])
+        o.condense_equilib(c)
+    common.assert_same_population(g, o, case, exact_fp=False, rtol=1e-10)
+
+
+@pytest.mark.parametrize("n_per_mode,n_cells", [(100, 4), (400, 3), (900, 2)])
+def test_condense_particles_device_vs_oracle(mods, n_per_mode, n_cells):
+    """condense_particles over several steps through activation: per-particle water volume, RH and
+    the number of internal steps agree with the oracle (1e-10 relative on RH and on wet diameters).
+    Covers the 1-, 4- and 8-particles-per-thread instantiations."""
+    W, O = mods
+    case = common.condense_case(n_per_mode, n_cells=n_cells)
+    g = common.gpu_from_case(W, case, cell_capacity=2 * n_per_mode + 64)
+    o = common.oracle_from_case(O, case)
+    rh0 = np.linspace(0.95, 0.90, n_cells)
+    g.set_env(rel_humid=rh0)
+    g.condense_equilib_particles()
+    for c in range(n_cells):
+        o.set_env(c, T=290.0, p=1e5, RH=rh0[c])
+        o.condense_equilib(c)
+    for k in range(30):
+        t1 = (k + 1) * 10.0
+        T1 = np.full(n_cells, 290.0 - 10.0 * t1 / 1200.0)
+        p1 = np.full(n_cells, 1e5 - 2e4 * t1 / 1200.0)
+        rh, st, wre = g.condense_particles(T1, p1, 10.0)
+        for c in range(n_cells):
+            ost, owre = o.condense_particles(c, T1[c], p1[c], 10.0, step=k)
+            assert abs(rh[c] / o.env_rel_humid(c) - 1) < 1e-10, (k, c, rh[c], o.env_rel_humid(c))
+            assert (st[c, 0], st[c, 1]) == (ost[0], ost[1]), (k, c, st[c], ost)
+            assert abs(wre[c]) < 1e-6
+    assert rh.max() > 1.0  # the case went through activation
+    P = g.get_particles()
+    off = np.concatenate([[0], np.cumsum(P["count"])])
+    for c in range(n_cells):
+        q = o.get_cell(c)
+        Dd = (P["vol"][:, off[c]:off[c + 1]].sum(axis=0)) ** (1 / 3)
+        Do = (q["vol"].sum(axis=0)) ** (1 / 3)
+        assert np.abs(Dd / Do - 1).max() < 1e-10
+        assert np.array_equal(P["vol"][:19, off[c]:off[c + 1]], q["vol"][:19])  # solutes untouched
+
+
+def test_condense_golden_on_device(mods):
+    """K3 scenario on the GPU against ref_condense_0001_env.txt (RH 1e-4) and water mass (0.05)."""
+    W, O = mods
+    gold = json.load(open(os.path.join(HERE, "golden", "condense_env_golden.json")))
+    case = common.condense_case(500)
+    g = common.gpu_from_case(W, case)
+    g.set_env(rel_humid=np.array([0.95]))
+    g.condense_equilib_particles()
+    _, m, _ = g.get_weights()
+
+    def water_mass():
+        P = g.get_particles()
+        nc = np.where(P["wclass"] == 1, m[0, 0, 0], m[0, 1, 0])
+        return float((P["vol"][19] * nc).sum() * 1000.0)
+    rh, water = [0.95], [water_mass()]
+    for k in range(60):
+        t1 = (k + 1) * 10.0
+        r, st, wre = g.condense_particles([290.0 - 10.0 * t1 / 1200.0], [1e5 - 2e4 * t1 / 1200.0], 10.0)
+        rh.append(r[0])
+        water.append(water_mass())
+        assert abs(wre[0]) < 1e-6
+    gr = np.array(gold["rel_humid"])
+    assert np.linalg.norm(np.array(rh) - gr) / np.linalg.norm(gr) < 1e-4
+    gw = np.array(gold["water_mass_conc"])
+    assert np.linalg.norm(np.array(water) - gw) / np.linalg.norm(gw) < 0.05
+
+
+def test_condense_reports_unbuilt_reweight(mods):
+    """Size-dependent weights need aero_state_reweight after the solve; until that is built the
+    device must refuse rather than skip it."""
+    W, O = mods
+    case = common.make_cells(2, 100, n_spec=3, n_group=2, weight="nummass", seed=2, ragged=False)
+    g = common.gpu_from_case(W, case)
+    with pytest.raises(W.PmcGpuError) as ei:
+        g.condense_particles(case["T"] - 0.1, case["P"] - 100.0, 10.0)
+    assert ei.value.code == 10

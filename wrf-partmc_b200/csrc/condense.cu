@@ -1,0 +1,584 @@
+// condense.cu -- condense_particles (partmc/src/condense.F90:147-325) for every
+// grid cell of the patch.
+//
+// The reference integrates, per cell, the state (D_1..D_n, H) with SUNDIALS
+// CVODE (BDF + Newton + SPGMR, condense_solver.c:84-181) using the rate
+// function condense_rates (:371-502) and, as preconditioner, the exact solve of
+// the arrow-head system (I - gamma J) by the Schur complement on H
+// (condense_jac_solve_f, :625-695).  SUNDIALS is not part of the reference tree;
+// here every particle carries its own implicit stage equations and the cell
+// couples them only through H:
+//   * time stepper: 4-stage / 4th-order Rosenbrock method (Kaps-Rentrop, Shampine
+//     parameters) with embedded 3rd-order error estimate, the reference's
+//     tolerances (reltol 1e-8, abstol_i = max(1e-30, 1e-8 (D_i - D_dry_i)),
+//     abstol_H = 1e-10) in a CVODE-style weighted RMS norm;
+//   * Jacobian: the analytic partials of condense_rates, evaluated once per step;
+//   * linear algebra: each stage solves (1/(gamma h) - J) x = r exactly --
+//     per particle x_i = (r_i + b_i x_H) / (eps - a_i), with x_H from two
+//     cell-wide sums -- so the only cross-particle work is a block reduction;
+//   * T and p are linear in time over the step (condense_vf_f, :525-528); df/dt
+//     comes from one extra rate evaluation.
+// One CTA per cell, particle state in registers (PPT particles per thread),
+// FP64-pipe bound: ~6 rate evaluations x (5 Newton steps with one exp each) per
+// particle per internal step.  Fused multiply-add is allowed in this file.
+#include "pmcgpu_internal.cuh"
+
+#define COND_THREADS 256
+
+struct CondEnv {  // cell-level terms of condense_rates that depend on (T, p) only
+  double T, p, Tdot, pdot;
+  double k_a, D_v, U, V, W, X, Y, Z, UV;
+  double dP0_dT_div_P0;
+  double vc;  // V_comp * num_conc = (T * p0) / (T0 * p)
+};
+__device__ __forceinline__ CondEnv cond_env(double T0, double p0, double Tdot, double pdot, double t) {
+  CondEnv e;
+  e.T = T0 + t * Tdot;
+  e.p = p0 + t * pdot;
+  e.Tdot = Tdot;
+  e.pdot = pdot;
+  const double rho_w = PmcConst::water_density, M_w = PmcConst::water_molec_weight;
+  const double P_0 =
+      PmcConst::water_eq_vap_press * pow(10.0, 7.45 * (e.T - PmcConst::water_freeze_temp) / (e.T - 38.0));
+  e.dP0_dT_div_P0 = 7.45 * log(10.0) * (PmcConst::water_freeze_temp - 38.0) / ((e.T - 38.0) * (e.T - 38.0));
+  const double rho_air = PmcConst::air_molec_weight * e.p / (PmcConst::univ_gas_const * e.T);
+  e.k_a = 1e-3 * (4.39 + 0.071 * e.T);
+  e.D_v = 0.211e-4 / (e.p / PmcConst::air_std_press) * pow(e.T / 273.0, 1.94);
+  e.U = PmcConst::water_latent_heat * rho_w / (4.0 * e.T);
+  e.V = 4.0 * M_w * P_0 / (rho_w * PmcConst::univ_gas_const * e.T);
+  e.W = PmcConst::water_latent_heat * M_w / (PmcConst::univ_gas_const * e.T);
+  e.X = 4.0 * M_w * PmcConst::water_surf_eng / (PmcConst::univ_gas_const * e.T * rho_w);
+  e.Y = 2.0 * e.k_a / (PmcConst::accom_coeff * rho_air * PmcConst::air_spec_heat) *
+        sqrt(2.0 * PmcConst::pi * PmcConst::air_molec_weight / (PmcConst::univ_gas_const * e.T));
+  e.Z = 2.0 * e.D_v / PmcConst::accom_coeff * sqrt(2.0 * PmcConst::pi * M_w / (PmcConst::univ_gas_const * e.T));
+  e.UV = e.U * e.V;
+  e.vc = (e.T * p0) / (T0 * e.p);
+  return e;
+}
+
+// condense_rates (condense.F90:371-502) for one particle.  WITH_JAC also returns
+// a = dDdot/dD, b = dDdot/dH, c = dHdot_i/dD, dH = dHdot_i/dH.
+template <bool WITH_JAC>
+__device__ __forceinline__ void cond_rates(const CondEnv& e, double H, double D, double D_dry, double kappa,
+                                           double num_conc, double& Ddot, double& Hdot_i, double& a, double& b,
+                                           double& c, double& dH) {
+  const double hfac = -2.0 * PmcConst::pi / (e.V * (e.vc / num_conc));
+  if (D <= D_dry) {
+    const double k_ap = e.k_a / (1.0 + e.Y / D_dry);
+    const double D_vp = e.D_v / (1.0 + e.Z / D_dry);
+    const double delta_star = e.UV * D_vp * H / k_ap;
+    Ddot = k_ap * delta_star / (e.U * D_dry);
+    Hdot_i = hfac * (D_dry * D_dry) * Ddot;
+    if (WITH_JAC) {
+      const double ddeltastar_dH = e.UV * D_vp / k_ap;
+      a = 0.0;
+      b = k_ap / (e.U * D_dry) * ddeltastar_dH;
+      c = 0.0;
+      dH = hfac * (D_dry * D_dry) * b;
+    }
+    return;
+  }
+  const double D2 = D * D, D3 = D2 * D, Dd3 = D_dry * D_dry * D_dry;
+  const double k_ap = e.k_a / (1.0 + e.Y / D);
+  const double D_vp = e.D_v / (1.0 + e.Z / D);
+  const double den = D3 + (kappa - 1.0) * Dd3;
+  const double a_w = (D3 - Dd3) / den;
+  const double XD = e.X / D;
+  const double UVD = e.UV * D_vp;
+  double delta_star = 0.0, h = 0.0, dh_ddelta = 1.0, ex = 0.0, q = 1.0;
+#pragma unroll
+  for (int newton_step = 1; newton_step <= 5; newton_step++) {
+    delta_star = delta_star - h / dh_ddelta;
+    q = 1.0 / (1.0 + delta_star);
+    ex = exp((e.W * delta_star + XD) * q);
+    h = k_ap * delta_star - UVD * (H - a_w * q * ex);
+    dh_ddelta = k_ap - UVD * a_w * (q * q) * (1.0 - e.W * q + XD * q) * ex;
+  }
+  Ddot = k_ap * delta_star / (e.U * D);
+  Hdot_i = hfac * D2 * Ddot;
+  if (WITH_JAC) {
+    const double dkap_dD = e.k_a * e.Y / ((D + e.Y) * (D + e.Y));
+    const double dDvp_dD = e.D_v * e.Z / ((D + e.Z) * (D + e.Z));
+    const double daw_dD = 3.0 * D2 * kappa * Dd3 / (den * den);
+    const double dh_dD = dkap_dD * delta_star - e.UV * dDvp_dD * H +
+                         e.UV * (a_w * dDvp_dD + D_vp * daw_dD - D_vp * a_w * (e.X / D2) * q) * q * ex;
+    const double dh_dH = -UVD;
+    const double ddeltastar_dD = -dh_dD / dh_ddelta;
+    const double ddeltastar_dH = -dh_dH / dh_ddelta;
+    a = dkap_dD * delta_star / (e.U * D) + k_ap * ddeltastar_dD / (e.U * D) - k_ap * delta_star / (e.U * D2);
+    b = k_ap / (e.U * D) * ddeltastar_dH;
+    c = hfac * (2.0 * D * Ddot + D2 * a);
+    dH = hfac * D2 * b;
+  }
+}
+
+// deterministic block sum of up to 3 values; result valid in every thread
+template <int NV>
+__device__ __forceinline__ void block_sum(double* x, double* s_red /*[NV][COND_THREADS/32]*/) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double t = x[k];
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+    if (lane == 0) s_red[k * (COND_THREADS / 32) + warp] = t;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < COND_THREADS / 32; w++) t += s_red[k * (COND_THREADS / 32) + w];
+    x[k] = t;
+  }
+  __syncthreads();
+}
+
+struct CondParams {
+  double del_t, reltol, abstol_scale, abstol_H;
+  int max_steps;
+};
+
+// RODAS4 (Hairer & Wanner, Solving ODEs II, sect. IV.7): 6 stages, order 4(3), stiffly
+// accurate and L-stable, in the (A, C, M, E, alpha, gamma_i) form
+//   (1/(h gamma) - J) K_i = f(t + alpha_i h, y + sum_j A_ij K_j) + sum_j (C_ij / h) K_j + gamma_i h df/dt
+#define ROS_S 6
+__constant__ double c_rosA[ROS_S][ROS_S] = {
+    {0, 0, 0, 0, 0, 0},
+    {0.1544000000000000e+01, 0, 0, 0, 0, 0},
+    {0.9466785280815826, 0.2557011698983284, 0, 0, 0, 0},
+    {0.3314825187068521e+01, 0.2896124015972201e+01, 0.9986419139977817, 0, 0, 0},
+    {0.1221224509226641e+01, 0.6019134481288629e+01, 0.1253708332932087e+02, -0.6878860361058950, 0, 0},
+    {0.1221224509226641e+01, 0.6019134481288629e+01, 0.1253708332932087e+02, -0.6878860361058950, 1.0, 0}};
+__constant__ double c_rosC[ROS_S][ROS_S] = {
+    {0, 0, 0, 0, 0, 0},
+    {-0.5668800000000000e+01, 0, 0, 0, 0, 0},
+    {-0.2430093356833875e+01, -0.2063599157091915, 0, 0, 0, 0},
+    {-0.1073529058151375, -0.9594562251023355e+01, -0.2047028614809616e+02, 0, 0, 0},
+    {0.7496443313967647e+01, -0.1024680431464352e+02, -0.3399990352819905e+02, 0.1170890893206160e+02, 0, 0},
+    {0.8083246795921522e+01, -0.7981132988064893e+01, -0.3152159432874371e+02, 0.1631930543123136e+02,
+     -0.6058818238834054e+01, 0}};
+__constant__ double c_rosM[ROS_S] = {0.1221224509226641e+01, 0.6019134481288629e+01, 0.1253708332932087e+02,
+                                     -0.6878860361058950, 1.0, 1.0};
+__constant__ double c_rosAlpha[ROS_S] = {0.0, 0.386, 0.210, 0.630, 1.0, 1.0};
+__constant__ double c_rosGam[ROS_S] = {0.25, -0.1043, 0.1035, -0.3620000000000023e-01, 0.0, 0.0};
+#define ROS_GAMMA 0.25
+#define ROS_ELO 4.0
+
+template <int PPT>
+__global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const double* __restrict__ T1,
+                                                           const double* __restrict__ p1, CondParams prm,
+                                                           double* __restrict__ h_state, int* __restrict__ stats,
+                                                           double* __restrict__ wre_out, int n_limit_lo,
+                                                           int n_limit_hi) {
+  const int cell = blockIdx.x;
+  const int n = v.count[cell];
+  if (n <= n_limit_lo || n > n_limit_hi) return;  // another instantiation owns this cell
+  if (v.status[cell] != 0) return;
+  const int tid = threadIdx.x;
+  const size_t base = (size_t)cell * v.cap;
+  const size_t NS = (size_t)v.n_cells * v.cap;
+  __shared__ double s_red[3 * (COND_THREADS / 32)];
+  extern __shared__ double s_K[];  // [ROS_S + 2][PPT][COND_THREADS]: stage vectors, abstol, solute volume
+#define SK(st, k) s_K[((st) * PPT + (k)) * COND_THREADS + tid]
+#define S_ATOL(k) SK(ROS_S, k)
+#define S_SOLV(k) SK(ROS_S + 1, k)
+  // aero_state_reweight (aero_state.F90:597-653) after the solve is the identity for flat
+  // weights (ratio 1, prob_round(1) = 1); size-dependent weights need the duplicate / remove
+  // pass, which is not built yet: say so instead of skipping it silently.
+  for (int q = 0; q < v.C * v.G; q++)
+    if (v.wtype[(size_t)cell * v.C * v.G + q] != PMCGPU_WEIGHT_NONE) {
+      if (tid == 0 && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_REWEIGHT;
+      return;
+    }
+  const int iw = v.i_water - 1;
+  const double T0 = v.temp[cell], p0 = v.pres[cell];
+  const double Tdot = (T1[cell] - T0) / prm.del_t, pdot = (p1[cell] - p0) / prm.del_t;
+  double H = v.rh[cell];
+
+  // ---- set-up (condense.F90:196-237): kappa, D_dry, num_conc, D, abstol per particle
+  double D[PPT], Ddry[PPT], kap[PPT], nc[PPT];
+  double wsum = 0.0;
+#pragma unroll
+  for (int k = 0; k < PPT; k++) {
+    const int p = tid + k * COND_THREADS;
+    D[k] = 1.0; Ddry[k] = 1.0; kap[k] = 0.0; nc[k] = 1.0;
+    S_ATOL(k) = 1.0;
+    S_SOLV(k) = 0.0;
+    if (p < n) {
+      // aero_particle_solute_kappa (aero_particle.F90:724-755), solute volume, total volume
+      double vt = 0.0, vs = 0.0, ks = 0.0;
+      const double M_w = v.molw[iw], rho_w = v.density[iw];
+      for (int s = 0; s < v.S; s++) {
+        const double x = v.vol[(size_t)s * NS + base + p];
+        vt += x;
+        if (s != iw) {
+          vs += x;
+          double kp;
+          if (v.nions[s] > 0)
+            kp = M_w * v.density[s] / (v.molw[s] * rho_w) * (double)v.nions[s];
+          else
+            kp = v.kappa[s];
+          ks += x * kp;
+        }
+      }
+      const int gc = v.wgc[base + p];
+      const double r = vol2rad(vt);
+      S_SOLV(k) = vs;
+      kap[k] = ks / vs;
+      Ddry[k] = 2.0 * vol2rad(vs);
+      nc[k] = awa_nc_at_radius(v, cell, gc / v.G + 1, r);
+      D[k] = 2.0 * r;
+      S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (D[k] - Ddry[k]));
+      wsum += v.vol[(size_t)iw * NS + base + p] * nc[k];
+    }
+  }
+  {
+    double x[1] = {wsum};
+    block_sum<1>(x, s_red);
+    wsum = x[0];  // water_vol_conc_initial
+  }
+
+  const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.9, FAC_REJ = 0.1;
+  const double DT_FD = 1e-2;
+  const double del_t = prm.del_t;
+  double t = 0.0;
+  double h = h_state[cell];
+  h = (h > 0.0) ? fmin(h, del_t) : del_t;
+  double h_natural = h;
+  int n_steps = 0, n_reject = 0, fail = 0;
+  bool reject_last = false, reject_more = false;
+
+  while (t < del_t && !fail) {
+    if (n_steps + n_reject >= prm.max_steps) { fail = 6; break; }
+    bool truncated = false;
+    if (t + h > del_t * (1.0 - 1e-14)) { h_natural = h; h = del_t - t; truncated = true; }
+    // f, Jacobian at (t, y) and f at (t + DT_FD, y)
+    double f0[PPT], dfdt[PPT], ja[PPT], jb[PPT], jc[PPT];
+    double f0H, dfdtH, dd;
+    {
+      const CondEnv e0 = cond_env(T0, p0, Tdot, pdot, t);
+      const CondEnv e1 = cond_env(T0, p0, Tdot, pdot, t + DT_FD);
+      double acc[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+      for (int k = 0; k < PPT; k++) {
+        const int p = tid + k * COND_THREADS;
+        f0[k] = 0.0; dfdt[k] = 0.0; ja[k] = 0.0; jb[k] = 0.0; jc[k] = 0.0;
+        if (p < n) {
+          double hd, dh, f1, hd1, u1, u2, u3, u4;
+          cond_rates<true>(e0, H, D[k], Ddry[k], kap[k], nc[k], f0[k], hd, ja[k], jb[k], jc[k], dh);
+          cond_rates<false>(e1, H, D[k], Ddry[k], kap[k], nc[k], f1, hd1, u1, u2, u3, u4);
+          dfdt[k] = (f1 - f0[k]) / DT_FD;
+          acc[0] += hd;
+          acc[1] += dh;
+          acc[2] += hd1;
+        }
+      }
+      block_sum<3>(acc, s_red);
+      const double env0 = -e0.dP0_dT_div_P0 * Tdot * H + H * pdot / e0.p;
+      const double env1 = -e1.dP0_dT_div_P0 * Tdot * H + H * pdot / e1.p;
+      f0H = acc[0] + env0;
+      dd = acc[1] + (-e0.dP0_dT_div_P0 * Tdot + pdot / e0.p);
+      dfdtH = ((acc[2] + env1) - f0H) / DT_FD;
+    }
+    for (;;) {
+      const double eps = 1.0 / (ROS_GAMMA * h);
+      double inv[PPT];
+      double KH[ROS_S];
+      double sden[1] = {0.0};
+#pragma unroll
+      for (int k = 0; k < PPT; k++) {
+        inv[k] = 1.0 / (eps - ja[k]);
+        if (tid + k * COND_THREADS < n) sden[0] += jc[k] * jb[k] * inv[k];
+      }
+      block_sum<1>(sden, s_red);
+      const double lhs_H = eps - dd - sden[0];
+#pragma unroll
+      for (int st = 0; st < ROS_S; st++) {
+        // stage function value (stage 1 reuses f at (t, y))
+        double fs[PPT];
+        double acc[2] = {0.0, 0.0};
+        double Hs = H;
+        if (st > 0) {
+#pragma unroll
+          for (int j = 0; j < st; j++) Hs += c_rosA[st][j] * KH[j];
+        }
+        const CondEnv es = cond_env(T0, p0, Tdot, pdot, t + c_rosAlpha[st] * h);
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+          const int p = tid + k * COND_THREADS;
+          fs[k] = f0[k];
+          if (p < n) {
+            double hd = 0.0;
+            if (st > 0) {
+              double y = D[k];
+#pragma unroll
+              for (int j = 0; j < st; j++) y += c_rosA[st][j] * SK(j, k);
+              double u1, u2, u3, u4;
+              cond_rates<false>(es, Hs, y, Ddry[k], kap[k], nc[k], fs[k], hd, u1, u2, u3, u4);
+            }
+            double r = fs[k] + h * c_rosGam[st] * dfdt[k];
+#pragma unroll
+            for (int j = 0; j < st; j++) r += (c_rosC[st][j] / h) * SK(j, k);
+            fs[k] = r;
+            acc[0] += hd;
+            acc[1] += jc[k] * r * inv[k];
+          }
+        }
+        block_sum<2>(acc, s_red);
+        double fsH;
+        if (st == 0)
+          fsH = f0H;
+        else
+          fsH = acc[0] + (-es.dP0_dT_div_P0 * Tdot * Hs + Hs * pdot / es.p);
+        double rH = fsH + h * c_rosGam[st] * dfdtH;
+#pragma unroll
+        for (int j = 0; j < st; j++) rH += (c_rosC[st][j] / h) * KH[j];
+        KH[st] = (rH + acc[1]) / lhs_H;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) SK(st, k) = (fs[k] + jb[k] * KH[st]) * inv[k];
+      }
+      // new state and weighted RMS error norm (E = last stage for RODAS4)
+      double esum[1] = {0.0};
+      double Dn[PPT];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) {
+        const int p = tid + k * COND_THREADS;
+        double yn = D[k];
+#pragma unroll
+        for (int j = 0; j < ROS_S; j++) yn += c_rosM[j] * SK(j, k);
+        Dn[k] = yn;
+        if (p < n) {
+          const double er = SK(ROS_S - 1, k);
+          const double w = prm.reltol * fmax(fabs(D[k]), fabs(yn)) + S_ATOL(k);
+          esum[0] += (er / w) * (er / w);
+        }
+      }
+      block_sum<1>(esum, s_red);
+      double Hn = H;
+#pragma unroll
+      for (int j = 0; j < ROS_S; j++) Hn += c_rosM[j] * KH[j];
+      {
+        const double er = KH[ROS_S - 1];
+        const double w = prm.reltol * fmax(fabs(H), fabs(Hn)) + prm.abstol_H;
+        esum[0] += (er / w) * (er / w);
+      }
+      double err = sqrt(esum[0] / (double)(n + 1));
+      if (!isfinite(err)) err = 1e10;
+      err = fmax(err, 1e-10);
+      const double fac = fmin(FAC_MAX, fmax(FAC_MIN, FAC_SAFE / pow(err, 1.0 / ROS_ELO)));
+      double hnew = h * fac;
+      if (err <= 1.0) {
+#pragma unroll
+        for (int k = 0; k < PPT; k++) D[k] = Dn[k];
+        H = Hn;
+        t += h;
+        n_steps++;
+        if (reject_last) hnew = fmin(hnew, h);
+        reject_last = false;
+        reject_more = false;
+        h = truncated ? fmax(h_natural, hnew) : hnew;
+        h_natural = h;
+        break;
+      }
+      n_reject++;
+      if (n_steps + n_reject >= prm.max_steps) { fail = 6; break; }
+      if (reject_more) hnew = h * FAC_REJ;
+      reject_more = reject_last;
+      reject_last = true;
+      h = hnew;
+      truncated = false;
+      if (!(h > 1e-13 * del_t)) { fail = 7; break; }
+    }
+  }
+  // ---- write back (condense.F90:266-293): water volume, clamp at zero, water balance
+  double wfin = 0.0;
+#pragma unroll
+  for (int k = 0; k < PPT; k++) {
+    const int p = tid + k * COND_THREADS;
+    if (p < n && !fail) {
+      double wv = rad2vol(D[k] / 2.0) - S_SOLV(k);
+      wv = fmax(0.0, wv);
+      v.vol[(size_t)iw * NS + base + p] = wv;
+      wfin += wv * nc[k];
+    }
+  }
+  {
+    double x[1] = {wfin};
+    block_sum<1>(x, s_red);
+    wfin = x[0];
+  }
+  if (tid == 0) {
+    if (fail) {
+      if (v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_CONDENSE;
+    } else {
+      const double Tf = T1[cell], pf = p1[cell];
+      const double V_comp_ratio = Tf * p0 / (T0 * pf);
+      const double rho_w = v.density[iw], M_w = v.molw[iw];
+      const double P0i = PmcConst::water_eq_vap_press * pow(10.0, 7.45 * (T0 - PmcConst::water_freeze_temp) / (T0 - 38.0));
+      const double P0f = PmcConst::water_eq_vap_press * pow(10.0, 7.45 * (Tf - PmcConst::water_freeze_temp) / (Tf - 38.0));
+      const double vap_i = M_w / (PmcConst::univ_gas_const * T0) * P0i * v.rh[cell] / rho_w;
+      const double vap_f = M_w / (PmcConst::univ_gas_const * Tf) * P0f * H * V_comp_ratio / rho_w;
+      wre_out[cell] = ((vap_f - vap_i) + (wfin - wsum)) / (vap_f + wfin);
+      v.rh[cell] = H;
+      v.temp[cell] = Tf;
+      v.pres[cell] = pf;
+      h_state[cell] = h_natural;
+    }
+    stats[3 * cell + 0] = n_steps;
+    stats[3 * cell + 1] = n_reject;
+    stats[3 * cell + 2] = n_steps * 7 + n_reject * 5;  // rate evaluations per particle
+  }
+#undef SK
+#undef S_ATOL
+#undef S_SOLV
+}
+
+int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, CondParams prm, double* h_state,
+                           int* stats, double* wre, int n_lo);
+
+// device pointers T1/p1 (final env per cell)
+static size_t cond_smem(int ppt) { return (size_t)(ROS_S + 2) * ppt * COND_THREADS * sizeof(double); }
+
+int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, double del_t, double reltol) {
+  static bool configured = false;
+  if (!configured) {
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(4)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(8)));
+    configured = true;
+  }
+  DevView& v = ctx->v;
+  DevView* cw = &v;
+  CUDA_OK(ctx, cudaMemsetAsync(v.cond_stats, 0, 3 * v.n_cells * sizeof(int), ctx->stream));
+  CUDA_OK(ctx, cudaMemsetAsync(v.cond_wre, 0, v.n_cells * sizeof(double), ctx->stream));
+  if (v.i_water < 1) {
+    ctx->err = "condense_particles needs a water species (aero_data%i_water)";
+    return PMCGPU_ERR_ARG;
+  }
+  CondParams prm;
+  prm.del_t = del_t;
+  prm.reltol = reltol > 0.0 ? reltol : 1e-8;
+  prm.abstol_scale = 1e-8;
+  prm.abstol_H = 1e-10;
+  prm.max_steps = 100000;
+  // the population size of a cell picks the instantiation: 1..256 -> PPT 1, ..512 -> 2, ..1024 -> 4, ..2048 -> 8
+  const int cap = v.cap;
+  k_condense<1><<<v.n_cells, COND_THREADS, cond_smem(1), ctx->stream>>>(v, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, -1, 256);
+  LAUNCH_CHECK(ctx);
+  if (cap > 256) {
+    k_condense<2><<<v.n_cells, COND_THREADS, cond_smem(2), ctx->stream>>>(v, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 256, 512);
+    LAUNCH_CHECK(ctx);
+  }
+  if (cap > 512) {
+    k_condense<4><<<v.n_cells, COND_THREADS, cond_smem(4), ctx->stream>>>(v, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 512, 1024);
+    LAUNCH_CHECK(ctx);
+  }
+  if (cap > 1024) {
+    k_condense<8><<<v.n_cells, COND_THREADS, cond_smem(8), ctx->stream>>>(v, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 1024, 2048);
+    LAUNCH_CHECK(ctx);
+  }
+  if (cap > 2048) {
+    int rc = pmc_condense_big_async(ctx, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 2048);
+    if (rc) return rc;
+  }
+  return PMCGPU_OK;
+}
+
+extern "C" int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_final, const double* pressure_final,
+                                         double del_t, double reltol, double* rel_humid_out, int* stats_out,
+                                         double* water_rel_error_out) {
+  if (!ctx || !temp_final || !pressure_final || !(del_t > 0.0)) return PMCGPU_ERR_ARG;
+  DevView& v = ctx->v;
+  DevView* cw = &v;
+  int rc;
+  CUDA_OK(ctx, cudaMemcpyAsync(cw->cond_T1, temp_final, v.n_cells * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(ctx, cudaMemcpyAsync(cw->cond_p1, pressure_final, v.n_cells * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  rc = pmc_condense_async(ctx, cw->cond_T1, cw->cond_p1, del_t, reltol);
+  if (rc) return rc;
+  if (rel_humid_out)
+    CUDA_OK(ctx, cudaMemcpyAsync(rel_humid_out, v.rh, v.n_cells * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  if (stats_out)
+    CUDA_OK(ctx, cudaMemcpyAsync(stats_out, cw->cond_stats, 3 * v.n_cells * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  if (water_rel_error_out)
+    CUDA_OK(ctx, cudaMemcpyAsync(water_rel_error_out, cw->cond_wre, v.n_cells * sizeof(double), cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+  return pmc_first_status(ctx);
+}
+
+int pmc_condense_device(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, double del_t, double reltol) {
+  return pmc_condense_async(ctx, dT1, dp1, del_t, reltol);
+}
+
+// cells larger than the register-resident kernels handle (single-box runs): see condense_big.cu
+
+// ---- condense_equilib_particles (condense.F90:701-770), one thread per particle
+__global__ void k_condense_equilib(DevView v) {
+  const int cell = blockIdx.x;
+  const int n = v.count[cell];
+  const size_t base = (size_t)cell * v.cap;
+  const size_t NS = (size_t)v.n_cells * v.cap;
+  const int iw = v.i_water - 1;
+  const double X = 4.0 * PmcConst::water_molec_weight * PmcConst::water_surf_eng /
+                   (PmcConst::univ_gas_const * v.temp[cell] * PmcConst::water_density);
+  const double RH = v.rh[cell];
+  for (int p = threadIdx.x; p < n; p += blockDim.x) {
+    double vs = 0.0, ks = 0.0;
+    const double M_w = v.molw[iw], rho_w = v.density[iw];
+    for (int s = 0; s < v.S; s++) {
+      if (s == iw) continue;
+      const double x = v.vol[(size_t)s * NS + base + p];
+      vs += x;
+      const double kp = (v.nions[s] > 0) ? M_w * v.density[s] / (v.molw[s] * rho_w) * (double)v.nions[s] : v.kappa[s];
+      ks += x * kp;
+    }
+    const double kappa = ks / vs;
+    const double D_dry = 2.0 * vol2rad(vs);
+    const double Dd3 = D_dry * D_dry * D_dry;
+    double D = D_dry, g = 0.0, dg_dD = 1.0;
+    for (int newton_step = 1; newton_step <= 20; newton_step++) {
+      D = D - g / dg_dD;
+      const double D3 = D * D * D;
+      const double den = D3 + (kappa - 1.0) * Dd3;
+      const double a_w = (D3 - Dd3) / den;
+      const double daw_dD = 3.0 * (D * D) * kappa * Dd3 / (den * den);
+      const double ex = exp(X / D);
+      g = RH - a_w * ex;
+      dg_dD = -daw_dD * ex + a_w * ex * (X / (D * D));
+    }
+    v.vol[(size_t)iw * NS + base + p] = rad2vol(D / 2.0) - rad2vol(D_dry / 2.0);
+  }
+}
+extern "C" int pmcgpu_condense_equilib_particles(pmcgpu_ctx* ctx) {
+  if (!ctx) return PMCGPU_ERR_ARG;
+  if (ctx->v.i_water < 1) return PMCGPU_ERR_ARG;
+  k_condense_equilib<<<ctx->v.n_cells, 128, 0, ctx->stream>>>(ctx->v);
+  LAUNCH_CHECK(ctx);
+  CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}
+
+__global__ void k_eval_cond_rates(int n, const double* __restrict__ in, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double* q = in + 9 * i;
+  // T = T0 at t = 0; V_comp is passed directly: choose num_conc so that vc / num_conc = V_comp
+  CondEnv e = cond_env(q[0], q[3], q[1], q[4], 0.0);
+  const double num_conc = e.vc / q[5];
+  double Ddot, Hd, a, b, c, dH;
+  cond_rates<true>(e, q[2], q[6], q[7], q[8], num_conc, Ddot, Hd, a, b, c, dH);
+  double* o = out + 6 * i;
+  o[0] = Ddot; o[1] = Hd; o[2] = a; o[3] = b; o[4] = c; o[5] = dH;
+}
+extern "C" int pmcgpu_eval_condense_rates(pmcgpu_ctx* ctx, int n, const double* in, double* out) {
+  if (!ctx || n < 0 || !in || !out) return PMCGPU_ERR_ARG;
+  double *di = nullptr, *dout = nullptr;
+  CUDA_OK(ctx, cudaMalloc((void**)&di, (size_t)n * 9 * sizeof(double)));
+  CUDA_OK(ctx, cudaMalloc((void**)&dout, (size_t)n * 6 * sizeof(double)));
+  CUDA_OK(ctx, cudaMemcpyAsync(di, in, (size_t)n * 9 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  k_eval_cond_rates<<<(n + 127) / 128, 128, 0, ctx->stream>>>(n, di, dout);
+  LAUNCH_CHECK(ctx);
+  CUDA_OK(ctx, cudaMemcpyAsync(out, dout, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  cudaFree(di);
+  cudaFree(dout);
+  return PMCGPU_OK;
+}

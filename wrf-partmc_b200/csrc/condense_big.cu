@@ -1,0 +1,23 @@
+// condense_big.cu -- condensation for cells too large for the register-resident
+// kernels of condense.cu (single-box runs with 1e4..1e5 particles).
+#include "pmcgpu_internal.cuh"
+
+struct CondParams {
+  double del_t, reltol, abstol_scale, abstol_H;
+  int max_steps;
+};
+
+__global__ void k_flag_big_cells(DevView v, int n_lo) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= v.n_cells) return;
+  if (v.count[c] > n_lo && v.status[c] == 0) v.status[c] = PMCGPU_ERR_CAPACITY;
+}
+
+int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, CondParams prm, double* h_state,
+                           int* stats, double* wre, int n_lo) {
+  // not built yet: report cells above n_lo particles instead of skipping them
+  (void)dT1; (void)dp1; (void)prm; (void)h_state; (void)stats; (void)wre;
+  k_flag_big_cells<<<(ctx->v.n_cells + 127) / 128, 128, 0, ctx->stream>>>(ctx->v, n_lo);
+  LAUNCH_CHECK(ctx);
+  return PMCGPU_OK;
+}

@@ -89,6 +89,8 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   A(v.lptr, (size_t)v.n_cells * v.C * v.nbcap) A(v.llen, (size_t)v.n_cells * v.C * v.nbcap)
   A(v.lcap, (size_t)v.n_cells * v.C * v.nbcap)
   A(v.coag_samp, v.n_cells) A(v.coag_ncoag, v.n_cells)
+  A(v.cond_T1, v.n_cells) A(v.cond_p1, v.n_cells) A(v.cond_h, v.n_cells) A(v.cond_stats, (size_t)3 * v.n_cells)
+  A(v.cond_wre, v.n_cells)
   double *d_density, *d_kappa, *d_molw;
   int* d_nions;
   A(d_density, v.S) A(d_kappa, v.S) A(d_molw, v.S) A(d_nions, v.S)

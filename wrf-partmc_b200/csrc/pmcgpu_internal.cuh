@@ -79,6 +79,12 @@ struct DevView {
   int* lcap;
   int* coag_samp;     // [n_cells]
   int* coag_ncoag;
+  // condensation work space
+  double* cond_T1;    // [n_cells] final temperature / pressure of the step
+  double* cond_p1;
+  double* cond_h;     // [n_cells] step size carried from one call to the next
+  int* cond_stats;    // [n_cells][3] steps, rejected steps, rate evaluations per particle
+  double* cond_wre;   // [n_cells] water balance (condense.F90:301-319)
 };
 
 struct pmcgpu_ctx {

@@ -214,6 +214,24 @@ class PartMCGPU:
                                         _p(nc)))
         return ns, nc
 
+    def condense_particles(self, temp_final, pressure_final, del_t, reltol=0.0):
+        """condense_particles (condense.F90:147) for every cell; returns (rel_humid, stats[n][3], water_rel_error)."""
+        T1, p1 = _f64(temp_final), _f64(pressure_final)
+        assert T1.size == self.n_cells and p1.size == self.n_cells
+        rh, st, wre = np.zeros(self.n_cells), np.zeros((self.n_cells, 3), np.int32), np.zeros(self.n_cells)
+        self._chk(self.L.pmcgpu_condense_particles(self.h, _p(T1), _p(p1), C.c_double(del_t), C.c_double(reltol),
+                                                   _p(rh), _p(st), _p(wre)))
+        return rh, st, wre
+
+    def condense_equilib_particles(self):
+        self._chk(self.L.pmcgpu_condense_equilib_particles(self.h))
+
+    def eval_condense_rates(self, inputs):
+        a = _f64(inputs).reshape(-1, 9)
+        out = np.zeros((a.shape[0], 6))
+        self._chk(self.L.pmcgpu_eval_condense_rates(self.h, C.c_int(a.shape[0]), _p(a), _p(out)))
+        return out
+
     def aero_state_rebalance(self, allow_doubling=True, allow_halving=True, step=0):
         self._chk(self.L.pmcgpu_aero_state_rebalance(self.h, C.c_int(int(allow_doubling)),
                                                      C.c_int(int(allow_halving)), C.c_uint(step)))
