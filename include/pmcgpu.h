@@ -133,12 +133,54 @@ int pmcgpu_update_density(pmcgpu_ctx* ctx, const double* new_inverse_density);
 /* partmc_to_wrf (wrf_pmc_driver.F90:1704-1719): out[cell*n_class + c] = max(count*magnitude*alt, 1e-16) */
 int pmcgpu_num_conc_by_class(pmcgpu_ctx* ctx, float* out);
 
+/* partmc_timestep (interface/wrf_pmc_driver.F90:46-290) for every cell of the patch, as one
+ * asynchronous chain on the context's stream: wrf_to_partmc (new env_state from the host arrays below,
+ * the previous one becomes old_env_states), mc_coag when mod(elapsed_time, chem_dt) == 0 and
+ * do_coagulation (:189-197), scenario_update_aero_state's WRF branch (awa *= old_rrho / rrho),
+ * water uptake by condense_particles(old_env, env, chem_dt) in the slot of mosaic_timestep (:235) when
+ * do_condensation, aero_state_rebalance (:248) and partmc_to_wrf (:1704-1719).
+ * Arrays are [n_cells] in cell order, in host memory (what the Fortran side passes) or in device memory
+ * (unified addressing tells them apart); NULL keeps the device value / skips the output. */
+typedef struct {
+  const double* temp;             /* env_state%temp            (wrf_to_partmc, :576-644) */
+  const double* pressure;         /* env_state%pressure */
+  const double* rel_humid;        /* env_state%rel_humid; NULL keeps the integrator's value */
+  const double* inverse_density;  /* grid%alt */
+  const double* cell_volume;
+  double elapsed_time;            /* seconds since simulation start (:126) */
+  double dt;                      /* grid%dt */
+  double chem_dt;                 /* grid%partmc_chem_dt */
+  int do_coagulation;             /* grid%do_coagulation */
+  int coag_kernel_type;           /* WRF: PMCGPU_KERNEL_BROWN (:192) */
+  int do_condensation;
+  int allow_doubling, allow_halving;
+  unsigned int step;              /* addresses the random draws of this call */
+  float* num_conc_out;            /* [n_cells][n_class] partmc_to_wrf, optional */
+  double* rel_humid_out;          /* [n_cells], optional */
+  int no_wait;                    /* 1: return after enqueueing; call pmcgpu_check_status later */
+} pmcgpu_timestep_args;
+int pmcgpu_partmc_timestep(pmcgpu_ctx* ctx, const pmcgpu_timestep_args* args);
+/* waits for the stream and returns the first non-zero per-cell status (0 = ok) */
+int pmcgpu_check_status(pmcgpu_ctx* ctx);
+
+/* ---- measurement ---------------------------------------------------------
+ * per-kernel CUDA-event timing on the context's stream; pmcgpu_profile_read writes one
+ * "kernel_name total_ms launches" line per kernel into buf. */
+int pmcgpu_profile_enable(pmcgpu_ctx* ctx, int on);
+int pmcgpu_profile_read(pmcgpu_ctx* ctx, char* buf, int buf_len, int reset);
+/* FP64 FMA throughput of the device (TFLOP/s), the roofline denominator of the FP64-bound kernels */
+int pmcgpu_measure_fp64_peak(pmcgpu_ctx* ctx, double* tflops);
+
 /* ---- inspection (parity tests) ----------------------------------------- */
 int pmcgpu_get_grid(pmcgpu_ctx* ctx, int* n_bin, double* grid_min, double* grid_max); /* [n_cells] each */
 int pmcgpu_get_bins(pmcgpu_ctx* ctx, long long n_total, int* bin_of_particle);        /* packed like particles */
 int pmcgpu_get_bin_counts(pmcgpu_ctx* ctx, int* counts); /* [n_cells][n_class][max_bins] */
 int pmcgpu_get_kernel_max(pmcgpu_ctx* ctx, int cell, double* kmax); /* [n_bin][n_bin], (b1,b2) at [(b2-1)*n_bin+b1-1] */
 int pmcgpu_get_cell_status(pmcgpu_ctx* ctx, int* status); /* [n_cells] first error per cell */
+/* counters of the last condensation ([n_cells][3]: steps, rejected steps, rate evaluations per particle;
+ * condense.F90:135-138 condense_count_vf / _solve) and of the last mc_coag (tot_n_samp, tot_n_coag) */
+int pmcgpu_get_condense_stats(pmcgpu_ctx* ctx, int* stats);
+int pmcgpu_get_coag_stats(pmcgpu_ctx* ctx, int* tot_n_samp, int* tot_n_coag);
 /* stand-alone evaluations of device functions, for known-answer tests */
 int pmcgpu_eval_kernel_brown(pmcgpu_ctx* ctx, int n, const double* v1, const double* d1, const double* v2,
                              const double* d2, const double* temp, const double* pressure, double* out);

@@ -210,6 +210,19 @@ class Oracle:
                                                  C.c_int(method), _p(st, C.c_int), C.byref(wre)))
         return st, wre.value
 
+    def partmc_timestep(self, cell_lo, cell_hi, temp=None, pressure=None, rel_humid=None, inverse_density=None,
+                        elapsed_time=0.0, chem_dt=60.0, do_coagulation=True, coag_kernel_type=KERNEL_BROWN,
+                        do_condensation=False, allow_doubling=True, allow_halving=True, step=0, n_threads=1):
+        """partmc_timestep (wrf_pmc_driver.F90:46-290) for cells [cell_lo, cell_hi); met arrays are full length"""
+        a = [_f64(x) for x in (temp, pressure, rel_humid, inverse_density)]
+        tot = np.zeros(4, np.int64)
+        self._chk(self.L.pmco_partmc_timestep(
+            self.h, C.c_int(cell_lo), C.c_int(cell_hi), *[_p(x, C.c_double) for x in a], C.c_double(elapsed_time),
+            C.c_double(chem_dt), C.c_int(int(do_coagulation)), C.c_int(coag_kernel_type),
+            C.c_int(int(do_condensation)), C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)),
+            C.c_uint(step), C.c_int(n_threads), _p(tot, C.c_longlong)))
+        return dict(n_samp=int(tot[0]), n_coag=int(tot[1]), cond_steps=int(tot[2]), cond_rates=int(tot[3]))
+
     def scale_weight(self, cell, g, c, ratio, allow_doubling=True, allow_halving=True, step=0):
         self._chk(self.L.pmco_scale_weight(self.h, C.c_int(cell), C.c_int(g), C.c_int(c), C.c_double(ratio),
                                            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step)))

@@ -77,4 +77,86 @@ int pmco_condense_particles(void* h, int cell, double T1, double p1, double del_
 }
 double pmco_sat_vapor_pressure(double T) { return sat_vapor_pressure(T); }
 
+// partmc_timestep (interface/wrf_pmc_driver.F90:46-290) for the cells [cell_lo, cell_hi): per cell
+// wrf_to_partmc (new T, p[, RH, rrho]; the previous env_state becomes old_env_states, :120), mc_coag when
+// mod(elapsed_time, chem_dt) == 0 and do_coag (:189-197), scenario_update_aero_state's WRF branch
+// (scenario.F90:331-334), condense_particles(old_env, env, chem_dt) in the slot of mosaic_timestep (:235),
+// aero_state_rebalance (:248).  n_threads host threads work on contiguous cell ranges (cells are
+// independent; one MPI rank per core in WRF).  The arrays are indexed by cell number (full length).
+// tot[0..3] = samples, coagulation events, condensation steps, condensation rate evaluations.
+int pmco_partmc_timestep(void* h, int cell_lo, int cell_hi, const double* T, const double* p, const double* RH,
+                         const double* rrho, double elapsed_time, double chem_dt, int do_coag, int kernel_type,
+                         int do_cond, int allow_doubling, int allow_halving, unsigned step, int n_threads,
+                         long long* tot) {
+  OracleDomain* d = (OracleDomain*)h;
+  const int nc = cell_hi - cell_lo;
+  if (n_threads < 1) n_threads = 1;
+  if (d->cond_h.size() != d->cells.size()) d->cond_h.assign(d->cells.size(), 0.0);
+  std::vector<long long> acc((size_t)n_threads * 4, 0);
+  std::vector<int> err((size_t)n_threads, 0);
+  const bool chem = std::fmod(elapsed_time, chem_dt) == 0.0;
+  auto work = [&](int t) {
+    const int lo = cell_lo + (int)((long long)nc * t / n_threads);
+    const int hi = cell_lo + (int)((long long)nc * (t + 1) / n_threads);
+    for (int c = lo; c < hi; c++) {
+      try {
+        RunCtx rc{d->rng.get(), (uint32_t)d->global_cell[c], step};
+        const EnvState old_env = d->env[c];
+        EnvState& env = d->env[c];
+        if (T) env.temp = T[c];
+        if (p) env.pressure = p[c];
+        if (RH) env.rel_humid = RH[c];
+        if (rrho) env.inverse_density = rrho[c];
+        env.elapsed_time = elapsed_time;
+        AeroState& st = d->cells[c];
+        if (chem && do_coag) {
+          CoagStats cs;
+          st.valid_sort = false;  // the device state is unsorted between steps
+          mc_coag(kernel_type, env, d->data, st, chem_dt, rc, cs);
+          acc[4 * t + 0] += cs.tot_n_samp;
+          acc[4 * t + 1] += cs.tot_n_coag;
+        }
+        if (rrho) {
+          const double f = old_env.inverse_density * (1.0 / env.inverse_density);
+          for (auto& w : st.awa.w) w.magnitude *= f;
+        }
+        if (chem && do_cond) {
+          EnvState e0 = old_env;
+          e0.rel_humid = env.rel_humid;
+          EnvState e1 = env;
+          CondenseOpts opt;
+          opt.h_init = d->cond_h[c];
+          CondenseStats cst;
+          condense_particles(st, d->data, e0, e1, chem_dt, rc, opt, cst);
+          d->cond_h[c] = cst.h_last;
+          env.rel_humid = e1.rel_humid;
+          acc[4 * t + 2] += cst.n_steps;
+          acc[4 * t + 3] += (long long)cst.n_rates;
+        }
+        aero_state_rebalance(st, allow_doubling != 0, allow_halving != 0, rc);
+      } catch (const PmcError& e) {
+        err[t] = e.code ? e.code : -1;
+      } catch (const std::exception&) {
+        err[t] = -1;
+      }
+    }
+  };
+  if (n_threads == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < n_threads; t++) th.emplace_back(work, t);
+    for (auto& x : th) x.join();
+  }
+  int e = 0;
+  long long s[4] = {0, 0, 0, 0};
+  for (int t = 0; t < n_threads; t++) {
+    for (int k = 0; k < 4; k++) s[k] += acc[4 * t + k];
+    if (err[t]) e = err[t];
+  }
+  if (tot)
+    for (int k = 0; k < 4; k++) tot[k] = s[k];
+  return e;
+}
+
 }  // extern "C"

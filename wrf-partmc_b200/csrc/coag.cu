@@ -511,8 +511,11 @@ int pmc_mc_coag_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step) {
   if (rc) return rc;
   const size_t smem = (size_t)COAG_WARPS * v.C * (sizeof(double) + sizeof(int));
   const int blocks = (v.n_cells + COAG_WARPS - 1) / COAG_WARPS;
-  k_mc_coag<<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
-  LAUNCH_CHECK(ctx);
+  {
+    ProfScope ps_(ctx, "k_mc_coag");
+    k_mc_coag<<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+    LAUNCH_CHECK(ctx);
+  }
   return PMCGPU_OK;
 }
 

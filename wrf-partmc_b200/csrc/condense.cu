@@ -165,8 +165,10 @@ __constant__ double c_rosGam[ROS_S] = {0.25, -0.1043, 0.1035, -0.362000000000002
 #define ROS_ELO 4.0
 
 template <int PPT>
-__global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const double* __restrict__ T1,
-                                                           const double* __restrict__ p1, CondParams prm,
+__global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const double* T0a /* may alias v.temp */,
+                                                           const double* p0a,
+                                                           const double* T1 /* may alias v.temp */,
+                                                           const double* p1, CondParams prm,
                                                            double* __restrict__ h_state, int* __restrict__ stats,
                                                            double* __restrict__ wre_out, int n_limit_lo,
                                                            int n_limit_hi) {
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       return;
     }
   const int iw = v.i_water - 1;
-  const double T0 = v.temp[cell], p0 = v.pres[cell];
+  const double T0 = T0a[cell], p0 = p0a[cell];  // env_state_initial
   const double Tdot = (T1[cell] - T0) / prm.del_t, pdot = (p1[cell] - p0) / prm.del_t;
   double H = v.rh[cell];
 
@@ -433,13 +435,14 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
 #undef S_SOLV
 }
 
-int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, CondParams prm, double* h_state,
-                           int* stats, double* wre, int n_lo);
+int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
+                           CondParams prm, double* h_state, int* stats, double* wre, int n_lo);
 
 // device pointers T1/p1 (final env per cell)
 static size_t cond_smem(int ppt) { return (size_t)(ROS_S + 2) * ppt * COND_THREADS * sizeof(double); }
 
-int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, double del_t, double reltol) {
+int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
+                       double del_t, double reltol) {
   static bool configured = false;
   if (!configured) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(4)));
@@ -460,24 +463,25 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, do
   prm.abstol_scale = 1e-8;
   prm.abstol_H = 1e-10;
   prm.max_steps = 100000;
+  ProfScope ps_(ctx, "k_condense");
   // the population size of a cell picks the instantiation: 1..256 -> PPT 1, ..512 -> 2, ..1024 -> 4, ..2048 -> 8
   const int cap = v.cap;
-  k_condense<1><<<v.n_cells, COND_THREADS, cond_smem(1), ctx->stream>>>(v, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, -1, 256);
+  k_condense<1><<<v.n_cells, COND_THREADS, cond_smem(1), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, -1, 256);
   LAUNCH_CHECK(ctx);
   if (cap > 256) {
-    k_condense<2><<<v.n_cells, COND_THREADS, cond_smem(2), ctx->stream>>>(v, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 256, 512);
+    k_condense<2><<<v.n_cells, COND_THREADS, cond_smem(2), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 256, 512);
     LAUNCH_CHECK(ctx);
   }
   if (cap > 512) {
-    k_condense<4><<<v.n_cells, COND_THREADS, cond_smem(4), ctx->stream>>>(v, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 512, 1024);
+    k_condense<4><<<v.n_cells, COND_THREADS, cond_smem(4), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 512, 1024);
     LAUNCH_CHECK(ctx);
   }
   if (cap > 1024) {
-    k_condense<8><<<v.n_cells, COND_THREADS, cond_smem(8), ctx->stream>>>(v, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 1024, 2048);
+    k_condense<8><<<v.n_cells, COND_THREADS, cond_smem(8), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 1024, 2048);
     LAUNCH_CHECK(ctx);
   }
   if (cap > 2048) {
-    int rc = pmc_condense_big_async(ctx, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 2048);
+    int rc = pmc_condense_big_async(ctx, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 2048);
     if (rc) return rc;
   }
   return PMCGPU_OK;
@@ -492,7 +496,7 @@ extern "C" int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_fin
   int rc;
   CUDA_OK(ctx, cudaMemcpyAsync(cw->cond_T1, temp_final, v.n_cells * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   CUDA_OK(ctx, cudaMemcpyAsync(cw->cond_p1, pressure_final, v.n_cells * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-  rc = pmc_condense_async(ctx, cw->cond_T1, cw->cond_p1, del_t, reltol);
+  rc = pmc_condense_async(ctx, v.temp, v.pres, cw->cond_T1, cw->cond_p1, del_t, reltol);
   if (rc) return rc;
   if (rel_humid_out)
     CUDA_OK(ctx, cudaMemcpyAsync(rel_humid_out, v.rh, v.n_cells * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -504,9 +508,6 @@ extern "C" int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_fin
   return pmc_first_status(ctx);
 }
 
-int pmc_condense_device(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, double del_t, double reltol) {
-  return pmc_condense_async(ctx, dT1, dp1, del_t, reltol);
-}
 
 // cells larger than the register-resident kernels handle (single-box runs): see condense_big.cu
 

@@ -13,10 +13,10 @@ __global__ void k_flag_big_cells(DevView v, int n_lo) {
   if (v.count[c] > n_lo && v.status[c] == 0) v.status[c] = PMCGPU_ERR_CAPACITY;
 }
 
-int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT1, const double* dp1, CondParams prm, double* h_state,
-                           int* stats, double* wre, int n_lo) {
+int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
+                           CondParams prm, double* h_state, int* stats, double* wre, int n_lo) {
   // not built yet: report cells above n_lo particles instead of skipping them
-  (void)dT1; (void)dp1; (void)prm; (void)h_state; (void)stats; (void)wre;
+  (void)dT0; (void)dp0; (void)dT1; (void)dp1; (void)prm; (void)h_state; (void)stats; (void)wre;
   k_flag_big_cells<<<(ctx->v.n_cells + 127) / 128, 128, 0, ctx->stream>>>(ctx->v, n_lo);
   LAUNCH_CHECK(ctx);
   return PMCGPU_OK;

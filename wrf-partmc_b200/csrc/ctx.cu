@@ -61,6 +61,12 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   }
   DevView& v = ctx->v;
   memset(&v, 0, sizeof(v));
+  ctx->d_flag = nullptr;
+  ctx->h_flag = nullptr;
+  if (cudaMallocHost((void**)&ctx->h_flag, sizeof(int)) != cudaSuccess) {
+    delete ctx;
+    return PMCGPU_ERR_CUDA;
+  }
   v.n_cells = cfg->nx * cfg->ny * cfg->nz;
   v.cap = cfg->cell_capacity;
   v.S = cfg->n_spec;
@@ -90,7 +96,8 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   A(v.lcap, (size_t)v.n_cells * v.C * v.nbcap)
   A(v.coag_samp, v.n_cells) A(v.coag_ncoag, v.n_cells)
   A(v.cond_T1, v.n_cells) A(v.cond_p1, v.n_cells) A(v.cond_h, v.n_cells) A(v.cond_stats, (size_t)3 * v.n_cells)
-  A(v.cond_wre, v.n_cells)
+  A(v.cond_wre, v.n_cells) A(v.cond_T0, v.n_cells) A(v.cond_p0, v.n_cells) A(v.stage, (size_t)5 * v.n_cells)
+  A(v.numconc, (size_t)v.n_cells * v.C) A(ctx->d_flag, 1)
   double *d_density, *d_kappa, *d_molw;
   int* d_nions;
   A(d_density, v.S) A(d_kappa, v.S) A(d_molw, v.S) A(d_nions, v.S)
@@ -128,6 +135,7 @@ extern "C" int pmcgpu_destroy(pmcgpu_ctx* ctx) {
   if (!ctx) return PMCGPU_ERR_ARG;
   cudaStreamSynchronize(ctx->stream);
   for (void* p : ctx->allocs) cudaFree(p);
+  if (ctx->h_flag) cudaFreeHost(ctx->h_flag);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
   return PMCGPU_OK;
@@ -369,6 +377,19 @@ extern "C" int pmcgpu_get_kernel_max(pmcgpu_ctx* ctx, int cell, double* kmax) {
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
   return PMCGPU_OK;
 }
+extern "C" int pmcgpu_get_condense_stats(pmcgpu_ctx* ctx, int* stats) {
+  if (!ctx || !stats) return PMCGPU_ERR_ARG;
+  D2H_OPT(stats, ctx->v.cond_stats, (size_t)3 * ctx->v.n_cells, int)
+  CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}
+extern "C" int pmcgpu_get_coag_stats(pmcgpu_ctx* ctx, int* tot_n_samp, int* tot_n_coag) {
+  if (!ctx) return PMCGPU_ERR_ARG;
+  D2H_OPT(tot_n_samp, ctx->v.coag_samp, ctx->v.n_cells, int)
+  D2H_OPT(tot_n_coag, ctx->v.coag_ncoag, ctx->v.n_cells, int)
+  CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}
 extern "C" int pmcgpu_get_cell_status(pmcgpu_ctx* ctx, int* status) {
   if (!ctx || !status) return PMCGPU_ERR_ARG;
   D2H_OPT(status, ctx->v.status, ctx->v.n_cells, int)
@@ -381,19 +402,17 @@ __global__ void k_first_status(const int* __restrict__ status, int n, int* out) 
     if (status[i] != 0) atomicCAS(out, 0, status[i]);
 }
 int pmc_first_status(pmcgpu_ctx* ctx) {
-  int* d = nullptr;
-  int h = 0;
-  if (cudaMalloc((void**)&d, sizeof(int)) != cudaSuccess) return PMCGPU_ERR_CUDA;
+  int* d = ctx->d_flag;
   cudaMemsetAsync(d, 0, sizeof(int), ctx->stream);
   k_first_status<<<std::min((ctx->v.n_cells + 255) / 256, 1024), 256, 0, ctx->stream>>>(ctx->v.status, ctx->v.n_cells, d);
   ctx->launches++;
-  cudaMemcpyAsync(&h, d, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+  cudaMemcpyAsync(ctx->h_flag, d, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
   cudaError_t e = cudaStreamSynchronize(ctx->stream);
-  cudaFree(d);
   if (e != cudaSuccess) {
     ctx->err = cudaGetErrorString(e);
     return PMCGPU_ERR_CUDA;
   }
+  const int h = *ctx->h_flag;
   if (h != 0) ctx->err = "device reported cell status " + std::to_string(h);
   return h;
 }
@@ -405,6 +424,11 @@ __global__ void k_update_density(DevView v, const double* __restrict__ new_rrho)
   const double f = v.rrho[c] * (1.0 / new_rrho[c]);
   for (int q = 0; q < v.C * v.G; q++) v.wmag[(size_t)c * v.C * v.G + q] *= f;
   v.rrho[c] = new_rrho[c];
+}
+int pmc_update_density_async(pmcgpu_ctx* ctx, const double* d_new_rrho) {
+  k_update_density<<<(ctx->v.n_cells + 255) / 256, 256, 0, ctx->stream>>>(ctx->v, d_new_rrho);
+  LAUNCH_CHECK(ctx);
+  return PMCGPU_OK;
 }
 extern "C" int pmcgpu_update_density(pmcgpu_ctx* ctx, const double* new_inverse_density) {
   if (!ctx || !new_inverse_density) return PMCGPU_ERR_ARG;
@@ -433,6 +457,12 @@ __global__ void k_num_conc_by_class(DevView v, float* __restrict__ out) {
     const double nc = (double)s_cnt[c] * v.wmag[((size_t)cell * v.C + c) * v.G + 0];
     out[(size_t)cell * v.C + c] = fmaxf((float)nc * (float)v.rrho[cell], 1e-16f);
   }
+}
+int pmc_num_conc_async(pmcgpu_ctx* ctx, float* d_out) {
+  ProfScope ps_(ctx, "k_num_conc_by_class");
+  k_num_conc_by_class<<<ctx->v.n_cells, 128, ctx->v.C * sizeof(int), ctx->stream>>>(ctx->v, d_out);
+  LAUNCH_CHECK(ctx);
+  return PMCGPU_OK;
 }
 extern "C" int pmcgpu_num_conc_by_class(pmcgpu_ctx* ctx, float* out) {
   if (!ctx || !out) return PMCGPU_ERR_ARG;
@@ -495,5 +525,42 @@ extern "C" int pmcgpu_eval_philox(pmcgpu_ctx* ctx, int n, const unsigned int* ce
   LAUNCH_CHECK(ctx);
   CUDA_OK(ctx, cudaMemcpyAsync(out, o.p, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}
+
+// ---- per-kernel timing with CUDA events on the launching stream (bench.py's roofline)
+extern "C" int pmcgpu_profile_enable(pmcgpu_ctx* ctx, int on) {
+  if (!ctx) return PMCGPU_ERR_ARG;
+  ctx->prof_on = on != 0;
+  return PMCGPU_OK;
+}
+static int prof_drain(pmcgpu_ctx* ctx) {
+  CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  for (ProfEntry& e : ctx->prof_pending) {
+    float ms = 0.f;
+    CUDA_OK(ctx, cudaEventElapsedTime(&ms, e.a, e.b));
+    auto& acc = ctx->prof_acc[e.name];
+    acc.first += ms;
+    acc.second += 1;
+    ctx->ev_pool.push_back(e.a);
+    ctx->ev_pool.push_back(e.b);
+  }
+  ctx->prof_pending.clear();
+  return PMCGPU_OK;
+}
+// writes "name ms launches\n" lines into buf; reset != 0 clears the accumulators afterwards
+extern "C" int pmcgpu_profile_read(pmcgpu_ctx* ctx, char* buf, int buf_len, int reset) {
+  if (!ctx || !buf || buf_len < 1) return PMCGPU_ERR_ARG;
+  int rc = prof_drain(ctx);
+  if (rc) return rc;
+  std::string out;
+  for (auto& kv : ctx->prof_acc) {
+    char line[256];
+    snprintf(line, sizeof line, "%s %.6f %lld\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    out += line;
+  }
+  if ((int)out.size() + 1 > buf_len) return PMCGPU_ERR_ARG;
+  memcpy(buf, out.c_str(), out.size() + 1);
+  if (reset) ctx->prof_acc.clear();
   return PMCGPU_OK;
 }

@@ -96,8 +96,11 @@ int pmc_kernel_bounds_async(pmcgpu_ctx* ctx, int ktype) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_kernel_bounds, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  k_kernel_bounds<<<v.n_cells, KMAX_THREADS, smem, ctx->stream>>>(v, ktype);
-  LAUNCH_CHECK(ctx);
+  {
+    ProfScope ps_(ctx, "k_kernel_bounds");
+    k_kernel_bounds<<<v.n_cells, KMAX_THREADS, smem, ctx->stream>>>(v, ktype);
+    LAUNCH_CHECK(ctx);
+  }
   return PMCGPU_OK;
 }
 

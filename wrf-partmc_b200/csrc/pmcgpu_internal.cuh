@@ -3,7 +3,9 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <map>
 #include <string>
+#include <utility>
 #include <vector>
 #include "../../include/pmcgpu.h"
 
@@ -85,9 +87,21 @@ struct DevView {
   double* cond_h;     // [n_cells] step size carried from one call to the next
   int* cond_stats;    // [n_cells][3] steps, rejected steps, rate evaluations per particle
   double* cond_wre;   // [n_cells] water balance (condense.F90:301-319)
+  double* cond_T0;    // [n_cells] env_state_initial of the step (old_env_states, wrf_pmc_driver.F90:120)
+  double* cond_p0;
+  double* stage;      // [5][n_cells] H2D staging of wrf_to_partmc outputs
+  float* numconc;     // [n_cells][C] partmc_to_wrf output
 };
 
+struct ProfEntry {
+  const char* name;
+  cudaEvent_t a, b;
+};
 struct pmcgpu_ctx {
+  bool prof_on = false;                 // per-kernel CUDA-event timing (pmcgpu_profile_enable)
+  std::vector<ProfEntry> prof_pending;  // recorded, not yet read
+  std::vector<cudaEvent_t> ev_pool;
+  std::map<std::string, std::pair<double, long long>> prof_acc;  // name -> (ms, launches)
   pmcgpu_config cfg;
   DevView v;
   cudaStream_t stream;
@@ -96,6 +110,8 @@ struct pmcgpu_ctx {
   std::vector<void*> allocs;
   std::vector<double> h_density;
   int cur;  // unused: pointers are swapped in v
+  int* d_flag;  // first non-zero cell status of the last check
+  int* h_flag;  // pinned mirror
 };
 
 #define CUDA_OK(ctx, call)                                                              \
@@ -117,7 +133,31 @@ struct pmcgpu_ctx {
     }                                                                                   \
   } while (0)
 
-int pmc_first_status(pmcgpu_ctx* ctx);  // reduce per-cell status to one code (syncs)
+int pmc_first_status(pmcgpu_ctx* ctx);
+// brackets the launches of one scope with a pair of events on the context's stream
+struct ProfScope {
+  pmcgpu_ctx* c;
+  int idx;
+  ProfScope(pmcgpu_ctx* ctx, const char* name) : c(ctx), idx(-1) {
+    if (!c->prof_on) return;
+    ProfEntry e;
+    e.name = name;
+    for (cudaEvent_t* ev : {&e.a, &e.b}) {
+      if (!c->ev_pool.empty()) {
+        *ev = c->ev_pool.back();
+        c->ev_pool.pop_back();
+      } else {
+        cudaEventCreate(ev);
+      }
+    }
+    cudaEventRecord(e.a, c->stream);
+    idx = (int)c->prof_pending.size();
+    c->prof_pending.push_back(e);
+  }
+  ~ProfScope() {
+    if (idx >= 0) cudaEventRecord(c->prof_pending[idx].b, c->stream);
+  }
+};  // reduce per-cell status to one code (syncs)
 
 // ---------------------------------------------------------------------------
 // device math

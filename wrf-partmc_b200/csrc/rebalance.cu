@@ -136,8 +136,11 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_rebalance(DevView v, int all
 int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step) {
   DevView& v = ctx->v;
   const int blocks = (v.n_cells + REB_WARPS - 1) / REB_WARPS;
-  k_rebalance<<<blocks, REB_WARPS * 32, 0, ctx->stream>>>(v, allow_doubling, allow_halving, step);
-  LAUNCH_CHECK(ctx);
+  {
+    ProfScope ps_(ctx, "k_rebalance");
+    k_rebalance<<<blocks, REB_WARPS * 32, 0, ctx->stream>>>(v, allow_doubling, allow_halving, step);
+    LAUNCH_CHECK(ctx);
+  }
   return PMCGPU_OK;
 }
 

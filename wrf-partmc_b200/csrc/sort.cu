@@ -262,8 +262,11 @@ int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_sort_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  k_sort_cells<<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, edge_recheck);
-  LAUNCH_CHECK(ctx);
+  {
+    ProfScope ps_(ctx, "k_sort_cells");
+    k_sort_cells<<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, edge_recheck);
+    LAUNCH_CHECK(ctx);
+  }
   // cells with an empty grid keep their (empty) slab: nothing to copy
   swap_slabs(v);
   return PMCGPU_OK;

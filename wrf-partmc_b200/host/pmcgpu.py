@@ -60,8 +60,28 @@ class _Config(C.Structure):
                 ("cell_capacity", C.c_int), ("max_bins", C.c_int), ("seed", C.c_uint), ("device", C.c_int)]
 
 
+class _TimestepArgs(C.Structure):
+    _fields_ = [("temp", C.c_void_p), ("pressure", C.c_void_p), ("rel_humid", C.c_void_p),
+                ("inverse_density", C.c_void_p), ("cell_volume", C.c_void_p), ("elapsed_time", C.c_double),
+                ("dt", C.c_double), ("chem_dt", C.c_double), ("do_coagulation", C.c_int),
+                ("coag_kernel_type", C.c_int), ("do_condensation", C.c_int), ("allow_doubling", C.c_int),
+                ("allow_halving", C.c_int), ("step", C.c_uint), ("num_conc_out", C.c_void_p),
+                ("rel_humid_out", C.c_void_p), ("no_wait", C.c_int)]
+
+
 def _f64(a):
     return None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _addr(a):
+    """address of a numpy array, a torch tensor (host or device) or a raw integer pointer; None -> NULL"""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    if hasattr(a, "data_ptr"):
+        return a.data_ptr()
+    return a.ctypes.data
 
 
 def _i32(a):
@@ -235,6 +255,58 @@ class PartMCGPU:
     def aero_state_rebalance(self, allow_doubling=True, allow_halving=True, step=0):
         self._chk(self.L.pmcgpu_aero_state_rebalance(self.h, C.c_int(int(allow_doubling)),
                                                      C.c_int(int(allow_halving)), C.c_uint(step)))
+
+    def partmc_timestep(self, temp=None, pressure=None, rel_humid=None, inverse_density=None, cell_volume=None,
+                        elapsed_time=0.0, dt=1.0, chem_dt=60.0, do_coagulation=True, coag_kernel_type=KERNEL_BROWN,
+                        do_condensation=False, allow_doubling=True, allow_halving=True, step=0, num_conc_out=None,
+                        rel_humid_out=None, no_wait=False):
+        """partmc_timestep (interface/wrf_pmc_driver.F90:46) for every cell of the patch.  The met arrays are
+        float64 [n_cells] buffers (numpy, pinned torch tensors, or device tensors); they are handed to the
+        library as plain pointers and must stay alive until the call has completed."""
+        a = _TimestepArgs()
+        a.temp, a.pressure, a.rel_humid = _addr(temp), _addr(pressure), _addr(rel_humid)
+        a.inverse_density, a.cell_volume = _addr(inverse_density), _addr(cell_volume)
+        a.elapsed_time, a.dt, a.chem_dt = float(elapsed_time), float(dt), float(chem_dt)
+        a.do_coagulation, a.coag_kernel_type = int(do_coagulation), int(coag_kernel_type)
+        a.do_condensation = int(do_condensation)
+        a.allow_doubling, a.allow_halving = int(allow_doubling), int(allow_halving)
+        a.step = int(step)
+        a.num_conc_out, a.rel_humid_out = _addr(num_conc_out), _addr(rel_humid_out)
+        a.no_wait = int(no_wait)
+        self._chk(self.L.pmcgpu_partmc_timestep(self.h, C.byref(a)))
+
+    def check_status(self):
+        self._chk(self.L.pmcgpu_check_status(self.h))
+
+    def profile_enable(self, on=True):
+        self._chk(self.L.pmcgpu_profile_enable(self.h, C.c_int(int(on))))
+
+    def profile_read(self, reset=True):
+        """{kernel name: (total ms, launches)} since the last reset"""
+        buf = C.create_string_buffer(1 << 16)
+        self._chk(self.L.pmcgpu_profile_read(self.h, buf, C.c_int(len(buf)), C.c_int(int(reset))))
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, ms, n = line.split()
+            out[name] = (float(ms), int(n))
+        return out
+
+    def measure_fp64_peak(self):
+        v = C.c_double(0)
+        self._chk(self.L.pmcgpu_measure_fp64_peak(self.h, C.byref(v)))
+        return v.value
+
+    def condense_stats(self):
+        """[n_cells][3] internal steps, rejected steps, rate evaluations per particle of the last condensation"""
+        out = np.zeros((self.n_cells, 3), np.int32)
+        self._chk(self.L.pmcgpu_get_condense_stats(self.h, _p(out)))
+        return out
+
+    def coag_stats(self):
+        """(tot_n_samp[n_cells], tot_n_coag[n_cells]) of the last mc_coag"""
+        a, b = np.zeros(self.n_cells, np.int32), np.zeros(self.n_cells, np.int32)
+        self._chk(self.L.pmcgpu_get_coag_stats(self.h, _p(a), _p(b)))
+        return a, b
 
     def update_density(self, new_inverse_density):
         a = _f64(new_inverse_density)
