@@ -223,6 +223,48 @@ class Oracle:
             C.c_uint(step), C.c_int(n_threads), _p(tot, C.c_longlong)))
         return dict(n_samp=int(tot[0]), n_coag=int(tot[1]), cond_steps=int(tot[2]), cond_rates=int(tot[3]))
 
+    # ---- transport (pmc_oracle_trans.cpp)
+    def trans_setup(self, gnx, nz, gny, px=1, py=1, dx=100.0, dy=100.0, vertmix=1):
+        self.trans_dims = (gnx, nz, gny)
+        self._chk(self.L.pmco_trans_setup(self.h, C.c_int(gnx), C.c_int(nz), C.c_int(gny), C.c_int(px), C.c_int(py),
+                                          C.c_float(dx), C.c_float(dy), C.c_int(vertmix)))
+
+    def trans_set_met(self, f):
+        """f: the dict of synthetic.transport_fields (global float32 arrays)"""
+        a = [np.ascontiguousarray(f[k], dtype=np.float32) for k in
+             ("u_flux", "v_flux", "w_flux", "xkhh", "alt", "z", "z_at_w", "exch_h")]
+        self._chk(self.L.pmco_trans_set_met(self.h, *[_p(x, C.c_float) for x in a]))
+
+    def trans_probs(self, dt):
+        """compute_advect_probs_wrf / compute_diffusion_probs / compute_vertical_probs / normalize_probs"""
+        self._chk(self.L.pmco_trans_probs(self.h, C.c_float(dt)))
+
+    def trans_get_probs(self, cell, cl):
+        nz = self.trans_dims[1]
+        adv, diff, vert = np.zeros(6), np.zeros(4), np.zeros(nz)
+        self.L.pmco_trans_get_probs(self.h, C.c_int(cell), C.c_int(cl), _p(adv, C.c_double), _p(diff, C.c_double),
+                                    _p(vert, C.c_double))
+        return adv, diff, vert
+
+    def trans_aero(self, step=0, allow_doubling=True, allow_halving=True, n_threads=1):
+        """trans_aero (wrf_pmc_trans_aero.F90:40); returns the number of particles added to other cells"""
+        m = C.c_longlong(0)
+        self._chk(self.L.pmco_trans_aero(self.h, C.c_uint(step), C.c_int(int(allow_doubling)),
+                                         C.c_int(int(allow_halving)), C.c_int(n_threads), C.byref(m)))
+        return m.value
+
+    def wrf_pmc_trans_driver(self, f, step=0, allow_doubling=True, allow_halving=True, n_threads=1):
+        """wrf_pmc_trans_driver (wrf_pmc_trans.F90:37): probabilities, then trans_aero"""
+        self.trans_set_met(f)
+        self.trans_probs(float(f["dt"]))
+        return self.trans_aero(step, allow_doubling, allow_halving, n_threads)
+
+    def num_conc_by_class(self):
+        """partmc_to_wrf (wrf_pmc_driver.F90:1704-1719): max(count * magnitude * alt, 1e-16) as float32"""
+        out = np.zeros((self.n_cells, self.n_class), np.float32)
+        self.L.pmco_num_conc_by_class(self.h, _p(out, C.c_float))
+        return out
+
     def scale_weight(self, cell, g, c, ratio, allow_doubling=True, allow_halving=True, step=0):
         self._chk(self.L.pmco_scale_weight(self.h, C.c_int(cell), C.c_int(g), C.c_int(c), C.c_double(ratio),
                                            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step)))

@@ -116,7 +116,7 @@ struct CondSys {
   double T0, p0, Tdot, pdot;
   // f and the arrow-head Jacobian at (t, D, H): condense_vf_f / condense_jac (condense.F90:509-616)
   void eval(double t, const double* D, double H, double* fD, double& fH, double* a, double* b, double* c, double& dd,
-            int& n_rates) const {
+            int& n_rates, bool jac) const {
     CondenseRatesInputs in;
     CondenseRatesOutputs out{};
     in.T = T0 + t * Tdot;
@@ -133,7 +133,7 @@ struct CondSys {
       condense_rates(in, out);
       fD[i] = out.Ddot;
       Hdot += out.Hdot_i;
-      if (a) {
+      if (jac) {
         a[i] = out.dDdot_dD;
         b[i] = out.dDdot_dH;
         c[i] = out.dHdoti_dD + out.dHdotenv_dD;
@@ -149,7 +149,7 @@ struct CondSys {
     }
     n_rates += n;
     fH = Hdot + out.Hdot_env;
-    if (a) dd = dHdot_dH + out.dHdotenv_dH;
+    if (jac) dd = dHdot_dH + out.dHdotenv_dH;  // (an empty cell has no arrays but still has dH'/dH)
   }
 };
 }  // namespace
@@ -239,8 +239,8 @@ int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const
       truncated = true;
     }
     double f0H, ftH, dd, dummy;
-    sys.eval(t, D, H, f0.data(), f0H, a.data(), b.data(), c.data(), dd, stats.n_rates);
-    sys.eval(t + DT_FD, D, H, ft.data(), ftH, nullptr, nullptr, nullptr, dummy, stats.n_rates);
+    sys.eval(t, D, H, f0.data(), f0H, a.data(), b.data(), c.data(), dd, stats.n_rates, true);
+    sys.eval(t + DT_FD, D, H, ft.data(), ftH, nullptr, nullptr, nullptr, dummy, stats.n_rates, false);
     for (int i = 0; i < n; i++) dfdt[i] = (ft[i] - f0[i]) / DT_FD;
     const double dfdtH = (ftH - f0H) / DT_FD;
     for (;;) {
@@ -260,7 +260,7 @@ int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const
             Hs += tb.A[st][j] * KH[j];
           }
           sys.eval(t + tb.alpha[st] * h, y.data(), Hs, fs.data(), fsH, nullptr, nullptr, nullptr, dummy,
-                   stats.n_rates);
+                   stats.n_rates, false);
         }
         double rH = fsH + h * tb.gam[st] * dfdtH;
         for (int i = 0; i < n; i++) r[i] = fs[i] + h * tb.gam[st] * dfdt[i];

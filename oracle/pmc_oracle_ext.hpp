@@ -47,6 +47,32 @@ int condense_integrate(int n, double* D, double* H, const double* D_dry, const d
                        double T0, double p0, double Tdot, double pdot, double del_t, const CondenseOpts& opt,
                        CondenseStats& stats);
 
-struct TransDomain {};  // filled in by the transport restatement
+// ---------------------------------------------------------------- transport (pmc_oracle_trans.cpp)
+// Global doubly periodic domain of gnx x nz x gny cells, emulated px x py patch decomposition.
+// Indices are 1-based like the Fortran; fields are WRF `real` (float), class index slowest.
+struct TransDomain {
+  int gnx = 0, nz = 0, gny = 0, px = 1, py = 1, n_class = 1;
+  float dx = 100.f, dy = 100.f, dt = 1.f;
+  int vertmix = 1;
+  std::vector<float> u_flux, v_flux, w_flux, xkhh, alt, z, z_at_w, exch_h;
+  // probabilities per (cell, class): adv -x +x -y +y -z +z; diff -x +x -y +y; vert[nz] (row of B* A)
+  std::vector<double> adv, diff, vert;
+  void setup(int gnx_, int nz_, int gny_, int px_, int py_, int n_class_);
+  size_t cell(int i, int k, int j) const { return (size_t)(i - 1) + (size_t)gnx * ((size_t)(k - 1) + (size_t)nz * (j - 1)); }
+  size_t cell_wrap(int i, int k, int j) const {
+    const int iw = ((i - 1) % gnx + gnx) % gnx + 1, jw = ((j - 1) % gny + gny) % gny + 1;
+    return cell(iw, k, jw);
+  }
+  size_t uidx(int i, int k, int j, int c) const {
+    return (size_t)(i - 1) + (size_t)(gnx + 1) * ((size_t)(k - 1) + (size_t)nz * ((size_t)(j - 1) + (size_t)gny * (c - 1)));
+  }
+  size_t vidx(int i, int k, int j, int c) const {
+    return (size_t)(i - 1) + (size_t)gnx * ((size_t)(k - 1) + (size_t)nz * ((size_t)(j - 1) + (size_t)(gny + 1) * (c - 1)));
+  }
+  size_t widx(int i, int k, int j, int c) const {
+    return (size_t)(i - 1) + (size_t)gnx * ((size_t)(k - 1) + (size_t)(nz + 1) * ((size_t)(j - 1) + (size_t)gny * (c - 1)));
+  }
+  size_t widx1(int i, int k, int j) const { return (size_t)(i - 1) + (size_t)gnx * ((size_t)(k - 1) + (size_t)(nz + 1) * (j - 1)); }
+};
 
 }  // namespace pmco

@@ -111,7 +111,13 @@ int pmco_partmc_timestep(void* h, int cell_lo, int cell_hi, const double* T, con
         AeroState& st = d->cells[c];
         if (chem && do_coag) {
           CoagStats cs;
-          st.valid_sort = false;  // the device state is unsorted between steps
+          // the device keeps no sorting between steps: full sort (valid_sort = .false.), the bin-edge
+          // safety test a valid sorting gets (aero_sorted.F90:258-276), and the particle array in the
+          // device's (class, bin, index) order -- exactly what pmco_sort(force, physical, edge_recheck) does
+          st.valid_sort = false;
+          aero_state_sort(st);
+          aero_state_sort(st);
+          aero_state_physical_sort(st);
           mc_coag(kernel_type, env, d->data, st, chem_dt, rc, cs);
           acc[4 * t + 0] += cs.tot_n_samp;
           acc[4 * t + 1] += cs.tot_n_coag;

@@ -93,12 +93,84 @@ def make_patch(nx, nz, ny, n_per_cell, n_spec=20, seed=1, num_conc_scale=10.0, r
                 cell_volume=np.full(n_cells, 100.0 ** 3), seed=seed, n_part_ideal=float(2 * per_mode))
 
 
-def met_sequence(case, n_steps, dT=-0.1, dp=-100.0):
-    """Per-step (T, p, inverse density) fields: a slow uniform cooling / lifting (the condense test drives
-    290 -> 280 K and 1e5 -> 8e4 Pa over 1200 s, partmc/test/condense/temp.dat, pressure.dat)."""
+def met_sequence(case, n_steps, dT=-0.4, dp=-400.0, period=8):
+    """Per-step (T, p, inverse density) fields: every cell is lifted and lowered adiabatically like a
+    parcel in a boundary-layer eddy, T = T0 + dT (1 - cos(2 pi k / period)) / 2 and the same for p (the
+    condense test drives 290 -> 280 K and 1e5 -> 8e4 Pa over 1200 s, i.e. -0.5 K and -1000 Pa per 60 s:
+    partmc/test/condense/temp.dat, pressure.dat).  With RH0 = 0.95 the cells stay sub-saturated
+    (RH 0.95 .. 0.98), so the cost of a step does not drift over the run."""
     out = []
     for k in range(1, n_steps + 1):
-        T = case["T"] + dT * k
-        P = case["P"] + dp * k
+        f = 0.5 * (1.0 - np.cos(2.0 * np.pi * k / period))
+        T = case["T"] + dT * f
+        P = case["P"] + dp * f
         out.append((T, P, 287.04 * T / P))
+    return out
+
+
+def transport_fields(case, num_conc, courant_x=0.3, courant_y=0.2, courant_z=0.05, xkhh=10.0, dx=100.0, dy=100.0,
+                     dt=6.0, seed=3):
+    """WRF-side inputs of wrf_pmc_trans_driver for the doubly periodic patch of `case`, as global arrays in WRF
+    memory order (i fastest, then k, then j; class slowest), all float32 like WRF's `real`:
+      u_flux [(nx+1), nz, ny, C], v_flux [nx, nz, (ny+1), C], w_flux [nx, (nz+1), ny, C]  per-class advective
+          fluxes of the number mixing ratio (WRFV3/dyn_em/module_advect_em.F:7806-7876), here first-order upwind
+          fluxes of `num_conc` ([n_cells][C], what partmc_to_wrf hands to WRF) for a wind field with the given
+          Courant numbers (a horizontally sheared flow that reverses with height, weak cellular vertical motion);
+      xkhh [nx, nz, ny] horizontal eddy diffusivity, alt [nx, nz, ny] inverse density, z [nx, nz, ny] and
+      z_at_w [nx, (nz+1), ny] heights, exch_h [nx, (nz+1), ny] vertical exchange coefficient."""
+    nx, nz, ny, C = case["nx"], case["nz"], case["ny"], case["n_class"]
+    rng = np.random.default_rng(seed)
+    q = np.asarray(num_conc, np.float32).reshape(ny, nz, nx, C)  # [j][k][i][c]
+    kk = np.arange(nz)[None, :, None]
+    jj = np.arange(ny)[:, None, None]
+    ii = np.arange(nx + 1)[None, None, :]
+    # Courant numbers on the faces
+    cx = courant_x * np.cos(np.pi * kk / max(nz - 1, 1)) * (1.0 + 0.2 * np.sin(2 * np.pi * jj / ny)) + 0.0 * ii
+    cy = courant_y * np.sin(2 * np.pi * np.arange(nx)[None, None, :] / nx) * np.ones((ny + 1, nz, 1))
+    cz = courant_z * np.sin(2 * np.pi * np.arange(nx)[None, None, :] / nx) * \
+        np.sin(np.pi * np.arange(nz + 1)[None, :, None] / nz) * np.ones((ny, 1, 1))
+    cz[:, 0, :] = 0.0
+    cz[:, nz, :] = 0.0
+    u_flux = np.zeros((C, ny, nz, nx + 1), np.float32)
+    v_flux = np.zeros((C, ny + 1, nz, nx), np.float32)
+    w_flux = np.zeros((C, ny, nz + 1, nx), np.float32)
+    for c in range(C):
+        qc = q[:, :, :, c]
+        left = np.concatenate([qc[:, :, -1:], qc], axis=2)   # cell i-1 of face i (periodic)
+        right = np.concatenate([qc, qc[:, :, :1]], axis=2)   # cell i of face i
+        u_flux[c] = np.where(cx > 0, cx * left, cx * right)
+        south = np.concatenate([qc[-1:], qc], axis=0)
+        north = np.concatenate([qc, qc[:1]], axis=0)
+        v_flux[c] = np.where(cy > 0, cy * south, cy * north)
+        below = np.concatenate([qc[:, :1], qc], axis=1)
+        above = np.concatenate([qc, qc[:, -1:]], axis=1)
+        w_flux[c] = np.where(cz > 0, cz * below, cz * above)
+    alt = np.asarray(case["rrho"], np.float32).reshape(ny, nz, nx)
+    kh = (xkhh * (1.0 + 0.3 * rng.random((ny, nz, nx)))).astype(np.float32)
+    z_w1 = (np.arange(nz + 1) * 100.0).astype(np.float32)
+    z_at_w = np.broadcast_to(z_w1[None, :, None], (ny, nz + 1, nx)).astype(np.float32).copy()
+    z = (0.5 * (z_at_w[:, 1:, :] + z_at_w[:, :-1, :])).astype(np.float32)
+    prof = 1.0 + 49.0 * np.sin(np.pi * np.arange(nz + 1) / nz) ** 2
+    exch_h = np.broadcast_to(prof[None, :, None], (ny, nz + 1, nx)).astype(np.float32).copy()
+    return dict(u_flux=u_flux, v_flux=v_flux, w_flux=w_flux, xkhh=kh, alt=alt, z=z, z_at_w=z_at_w, exch_h=exch_h,
+                dx=np.float32(dx), dy=np.float32(dy), dt=np.float32(dt))
+
+
+def patch_fields(f, i0, nxl, j0, nyl):
+    """The slabs of the global transport fields a rank owning cells [i0, i0+nxl) x [j0, j0+nyl) hands to the
+    library: staggered flux arrays of the patch, xkhh / alt with a one-cell periodic halo in x and y."""
+    ny, nz, nx = f["alt"].shape
+    ii = np.arange(i0, i0 + nxl)
+    jj = np.arange(j0, j0 + nyl)
+    iih = np.arange(i0 - 1, i0 + nxl + 1) % nx
+    jjh = np.arange(j0 - 1, j0 + nyl + 1) % ny
+    out = dict(dx=f["dx"], dy=f["dy"], dt=f["dt"])
+    out["u_flux"] = np.ascontiguousarray(f["u_flux"][:, jj][:, :, :, np.arange(i0, i0 + nxl + 1)])
+    out["v_flux"] = np.ascontiguousarray(f["v_flux"][:, np.arange(j0, j0 + nyl + 1)][:, :, :, ii])
+    out["w_flux"] = np.ascontiguousarray(f["w_flux"][:, jj][:, :, :, ii])
+    out["xkhh"] = np.ascontiguousarray(f["xkhh"][jjh][:, :, iih])
+    out["alt"] = np.ascontiguousarray(f["alt"][jjh][:, :, iih])
+    out["z"] = np.ascontiguousarray(f["z"][jj][:, :, ii])
+    out["z_at_w"] = np.ascontiguousarray(f["z_at_w"][jj][:, :, ii])
+    out["exch_h"] = np.ascontiguousarray(f["exch_h"][jj][:, :, ii])
     return out
