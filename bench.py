@@ -31,6 +31,7 @@ sys.path.insert(0, ROOT)
 METRIC = "particle-timesteps/sec (coag+cond+transport)"
 UNIT = "particle-timesteps/s"
 CHEM_DT = 60.0
+TRANS_DT = 6.0  # Courant numbers 0.3 / 0.2 / 0.05 at dx = dy = dz = 100 m
 
 
 def parse():
@@ -77,48 +78,62 @@ def oracle_sample(case, n_sample_cells):
     return o
 
 
-def time_oracle(case, met, n_cells_sample, steps, warmup, n_threads, transport):
-    """Returns (particle-timesteps/s, seconds per step, description)."""
-    o = oracle_sample(case, n_cells_sample)
-    n_part = int(case["counts"][:n_cells_sample].sum())
+def time_oracle(a, nx_s, ny_s, steps, warmup, n_threads, transport):
+    """The CPU restatement on its own small doubly periodic domain of nx_s x nz x ny_s cells with the
+    per-cell workload of the benchmark, decomposed into n_threads patches along x (one thread per patch,
+    like one MPI rank per core).  Returns (particle-timesteps/s, seconds per step, description)."""
+    from wrf_partmc_b200.host import synthetic
+    case = synthetic.make_patch(nx_s, a.nz, ny_s, a.n_per_cell, a.n_spec, seed=1)
+    n_cells = case["n_cells"]
+    o = oracle_sample(case, n_cells)
+    met = synthetic.met_sequence(case, warmup + steps)
+    if transport:
+        px = n_threads
+        while nx_s % px:
+            px -= 1
+        o.trans_setup(nx_s, a.nz, ny_s, px=px, py=1)
+        f = synthetic.transport_fields(case, o.num_conc_by_class(), dt=TRANS_DT)
+    n_part = int(case["counts"].sum())
     t_total = 0.0
     for k in range(warmup + steps):
-        T, P, rrho = met[k % len(met)]
+        T, P, rrho = met[k]
         t0 = time.perf_counter()
-        o.partmc_timestep(0, n_cells_sample, temp=T[:n_cells_sample], pressure=P[:n_cells_sample],
-                          inverse_density=rrho[:n_cells_sample], elapsed_time=k * CHEM_DT, chem_dt=CHEM_DT,
-                          do_coagulation=True, do_condensation=True, step=k + 1, n_threads=n_threads)
-        if transport and hasattr(o, "trans_step"):
-            o.trans_step(k + 1, n_threads=n_threads)
+        o.partmc_timestep(0, n_cells, temp=T, pressure=P, inverse_density=rrho, elapsed_time=k * CHEM_DT,
+                          chem_dt=CHEM_DT, do_coagulation=True, do_condensation=True, step=2 * k,
+                          n_threads=n_threads)
+        if transport:
+            o.wrf_pmc_trans_driver(f, step=2 * k + 1, n_threads=n_threads)
         t1 = time.perf_counter()
         if k >= warmup:
             t_total += t1 - t0
-    return n_part * steps / t_total, t_total / steps, "%d cells (%d particles) of the workload" % (n_cells_sample, n_part)
+    desc = "periodic sample domain %dx%dx%d cells (%d particles) with the per-cell workload of the benchmark" % (
+        nx_s, a.nz, ny_s, n_part)
+    return n_part * steps / t_total, t_total / steps, desc
+
+
+def sized_oracle_run(a, steps, warmup, seconds, transport):
+    """probe one small domain, then size ny_s so that the whole run takes about `seconds`"""
+    ncores = os.cpu_count() or 1
+    nx_s = max(2, min(ncores, 16))
+    v0, s0, _ = time_oracle(a, nx_s, 2, 1, 1, ncores, transport)
+    want = seconds / max(steps + warmup, 1)
+    ny_s = int(max(2, min(64, round(2 * want / max(s0, 1e-6)))))
+    return time_oracle(a, nx_s, ny_s, steps, warmup, ncores, transport) + (ncores,)
 
 
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from wrf_partmc_b200.host import synthetic
-    ncores = os.cpu_count() or 1
-    # a thin slab of the patch is enough: cells are independent
-    nx, nz, ny = min(a.nx, 16), a.nz, 1
-    case = synthetic.make_patch(nx, nz, ny, a.n_per_cell, a.n_spec, seed=1)
-    met = synthetic.met_sequence(case, a.steps + a.warmup)
-    # size the sample so that each step is about cpu_seconds / steps of wall time
-    probe = min(case["n_cells"], 2 * ncores)
-    v0, s0, _ = time_oracle(case, met, probe, 1, 1, ncores, False)
-    want = a.cpu_seconds / max(a.steps + a.warmup, 1)
-    n_sample = int(min(case["n_cells"], max(ncores, probe * want / max(s0, 1e-6))))
-    v, sps, desc = time_oracle(case, met, n_sample, a.steps, a.warmup, ncores, False)
+    transport = not a.no_transport
+    v, sps, desc, ncores = sized_oracle_run(a, a.steps, a.warmup, a.cpu_seconds, transport)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a, a.gpus), "sample": desc},
+            "config": {"workload": workload_name(a, a.gpus), "sample": desc, "transport": transport},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": ncores, "kind": "port",
                              "sample": desc + "; CPU restatement of the reference (oracle/), Philox draws, "
-                                              "one contiguous cell range per thread"},
+                                              "one patch per thread"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -226,9 +241,20 @@ def run_b200(a):
     g.set_env(temp=case["T"], pressure=case["P"], rel_humid=case["RH"], inverse_density=case["rrho"],
               cell_volume=case["cell_volume"])
     g.condense_equilib_particles()
-    has_transport = hasattr(g, "wrf_pmc_trans_driver") and not a.no_transport
+    has_transport = not a.no_transport
     if has_transport:
-        g.trans_setup_synthetic(case)
+        # WRF's side of the loop: per-class advective fluxes of the number mixing ratio partmc_to_wrf reports
+        f_glob = synthetic.transport_fields(case, g.partmc_to_wrf(), dt=TRANS_DT)
+        f_patch = synthetic.patch_fields(f_glob, 0, a.nx, 0, a.ny)
+        if world > 1:
+            px, py = (world, 1) if world < 4 else (world // 2, 2)
+            if rank == 0:
+                uid = torch.frombuffer(bytearray(W.comm_unique_id()), dtype=torch.uint8).clone()
+            else:
+                uid = torch.zeros(128, dtype=torch.uint8)
+            uid = uid.to(torch.device("cuda", local))
+            dist.broadcast(uid, 0)
+            g.comm_init(bytes(uid.cpu().numpy().tobytes()), world, rank, px, py)
 
     n_seq = a.warmup + a.steps
     met = synthetic.met_sequence(case, 2 * n_seq)
@@ -238,6 +264,12 @@ def run_b200(a):
     numconc_dev = torch.zeros(n_cells * case["n_class"], dtype=torch.float32, device=dev)
     numconc_pin = torch.zeros(n_cells * case["n_class"], dtype=torch.float32).pin_memory()
     stream = torch.cuda.ExternalStream(g.stream(), device=dev)
+    FK = ("u_flux", "v_flux", "w_flux", "xkhh", "alt", "z", "z_at_w", "exch_h")
+    if has_transport:
+        f_dev = {k: torch.from_numpy(f_patch[k]).to(dev) for k in FK}
+        f_pin = {k: torch.from_numpy(f_patch[k]).pin_memory() for k in FK}
+        for d_ in (f_dev, f_pin):
+            d_.update(dx=f_patch["dx"], dy=f_patch["dy"], dt=f_patch["dt"])
 
     def barrier():
         g.synchronize()
@@ -245,16 +277,16 @@ def run_b200(a):
         if world > 1:
             dist.barrier()
 
-    def one_step(k, m, out):
+    def one_step(k, m, out, fields):
         g.partmc_timestep(temp=m[0], pressure=m[1], inverse_density=m[2], elapsed_time=k * CHEM_DT, dt=CHEM_DT,
                           chem_dt=CHEM_DT, do_coagulation=True, coag_kernel_type=W.KERNEL_BROWN,
-                          do_condensation=True, step=k + 1, num_conc_out=out, no_wait=True)
+                          do_condensation=True, step=2 * k, num_conc_out=out, no_wait=True)
         if has_transport:
-            g.wrf_pmc_trans_driver(dt=CHEM_DT, step=k + 1, no_wait=True)
+            g.wrf_pmc_trans_driver(fields, step=2 * k + 1, no_wait=True)
 
     # ---- warm-up, then the timed region (device-resident inputs)
     for k in range(a.warmup):
-        one_step(k, met_dev[k], numconc_dev)
+        one_step(k, met_dev[k], numconc_dev, f_dev if has_transport else None)
     g.check_status()
     n_start = int(g.counts().sum())
     g.profile_read(reset=True)
@@ -265,7 +297,7 @@ def run_b200(a):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for k in range(a.warmup, n_seq):
-        one_step(k, met_dev[k], numconc_dev)
+        one_step(k, met_dev[k], numconc_dev, f_dev if has_transport else None)
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
@@ -284,12 +316,14 @@ def run_b200(a):
     t0 = time.perf_counter()
     for k in range(a.steps):
         kk = n_seq + k
-        one_step(kk, met_pin[k % len(met_pin)], numconc_pin)
+        one_step(kk, met_pin[k % len(met_pin)], numconc_pin, f_pin if has_transport else None)
     g.check_status()
     barrier()
     e2e_s = time.perf_counter() - t0
     n_end2 = int(g.counts().sum())
     h2d = 3 * n_cells * 8
+    if has_transport:
+        h2d += sum(f_patch[k].nbytes for k in FK)
     d2h = n_cells * case["n_class"] * 4 + 4
 
     # ---- max over ranks, sum of particles
@@ -362,15 +396,10 @@ def run_b200(a):
                 "gpu_launches": int(launches), "roofline": roofline, "roofline_hbm": roofline_hbm, "kernels": kern,
                 "fp64_peak_tflops": fp64_peak, "clocks": clk}
         if world == 1 and not a.no_cpu_baseline:
-            ncores = os.cpu_count() or 1
-            probe = min(n_cells, 2 * ncores)
-            met_cpu = synthetic.met_sequence(case, 4)
-            v0, s0, _ = time_oracle(case, met_cpu, probe, 1, 1, ncores, False)
-            n_sample = int(min(n_cells, max(ncores, probe * (a.cpu_seconds / 3.0) / max(s0, 1e-6))))
-            v, sps, desc = time_oracle(case, met_cpu, n_sample, 2, 1, ncores, False)
+            v, sps, desc, ncores = sized_oracle_run(a, 2, 1, a.cpu_seconds, has_transport)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": ncores, "kind": "port",
                                     "sample": desc + ", 2 timed steps after 1 warm-up; CPU restatement of the "
-                                                     "reference (oracle/), one contiguous cell range per thread"}
+                                                     "reference (oracle/), one patch per thread"}
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

@@ -163,6 +163,43 @@ int pmcgpu_partmc_timestep(pmcgpu_ctx* ctx, const pmcgpu_timestep_args* args);
 /* waits for the stream and returns the first non-zero per-cell status (0 = ok) */
 int pmcgpu_check_status(pmcgpu_ctx* ctx);
 
+/* wrf_pmc_trans_driver (interface/wrf_pmc_trans.F90:37-200) for the patch: the move probabilities
+ * (compute_advect_probs_wrf :205, compute_diffusion_probs :358, compute_vertical_probs :414, normalize_probs
+ * :692) from WRF's per-class advective fluxes and mixing coefficients, then trans_aero
+ * (interface/wrf_pmc_trans_aero.F90:40-971: preweighting, multinomial sampling of the moves, ghost exchange,
+ * add + rebalance + sort).  Doubly periodic domains (config_flags%periodic_x .and. periodic_y).
+ * Field slabs are WRF `real` arrays of the patch in WRF memory order (i fastest, then k, then j; the class
+ * index slowest), in host or device memory; NULL keeps the previous call's values:
+ *   u_flux [(nx+1) nz ny n_class]   grid%u_flux(i, k, j, 1 + class), staggered in x (faces i .. i+1)
+ *   v_flux [nx nz (ny+1) n_class]   grid%v_flux, staggered in y
+ *   w_flux [nx (nz+1) ny n_class]   grid%w_flux, staggered in z
+ *   xkhh, alt [(nx+2) nz (ny+2)]    grid%xkhh, grid%alt with WRF's one-cell halo in x and y
+ *   z [nx nz ny], z_at_w [nx (nz+1) ny], exch_h [nx (nz+1) ny]   grid%z, grid%z_at_w, grid%exch_h
+ * cell volumes and inverse densities are the env_state values (pmcgpu_set_env / pmcgpu_partmc_timestep). */
+typedef struct {
+  const float* u_flux; const float* v_flux; const float* w_flux;
+  const float* xkhh; const float* alt;
+  const float* z; const float* z_at_w; const float* exch_h;
+  float dx, dy, dt;               /* grid%dx, grid%dy, grid%dt */
+  int vertmix_onoff;              /* config_flags%vertmix_onoff */
+  int allow_doubling, allow_halving;
+  unsigned int step;              /* addresses the random draws of this call (use a value no other call of
+                                     the same WRF step uses) */
+  int no_wait;
+} pmcgpu_trans_args;
+int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_args* args);
+/* patch decomposition of the periodic domain: px x py patches, rank = rx + px * ry, one process and one
+ * GPU per patch (WRF's 2-D decomposition; MPI_Cart_shift of wrf_pmc_trans_aero.F90:153-159).  unique_id is
+ * the 128-byte NCCL id made by pmcgpu_comm_unique_id on one rank and distributed by the host (MPI_Bcast in
+ * WRF).  Without this call the context is a single periodic patch. */
+int pmcgpu_comm_unique_id(char* out, int len);
+int pmcgpu_comm_init(pmcgpu_ctx* ctx, const char* unique_id, int n_ranks, int rank, int px, int py);
+int pmcgpu_comm_destroy(pmcgpu_ctx* ctx);
+/* inspection: probabilities of the last call ([n_cells][n_class][6 | 4 | nz]; advection -x +x -y +y -z +z,
+ * diffusion -x +x -y +y, vertical row of B* A) and the number of arrivals per cell */
+int pmcgpu_get_trans_probs(pmcgpu_ctx* ctx, double* adv, double* diff, double* vert);
+int pmcgpu_get_trans_moved(pmcgpu_ctx* ctx, int* n_moved);
+
 /* ---- measurement ---------------------------------------------------------
  * per-kernel CUDA-event timing on the context's stream; pmcgpu_profile_read writes one
  * "kernel_name total_ms launches" line per kernel into buf. */

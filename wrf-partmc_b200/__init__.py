@@ -7,5 +7,5 @@ reference's entry points used by the tests and the benchmark.  There is no CPU
 fallback: importing works anywhere, but every call needs the built library and
 a CUDA device.
 """
-from .host.pmcgpu import (AeroData, PartMCGPU, PmcGpuError, library_path, load_library,  # noqa: F401
+from .host.pmcgpu import (AeroData, PartMCGPU, PmcGpuError, comm_unique_id, library_path, load_library,  # noqa: F401
                           KERNEL_ADDITIVE, KERNEL_BROWN, KERNEL_CONSTANT, KERNEL_ZERO, WEIGHT_NONE, WEIGHT_POWER)

@@ -63,6 +63,9 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   memset(&v, 0, sizeof(v));
   ctx->d_flag = nullptr;
   ctx->h_flag = nullptr;
+  ctx->rank = 0;
+  ctx->n_ranks = 1;
+  for (int s = 0; s < 4; s++) ctx->nb[s] = 0;
   if (cudaMallocHost((void**)&ctx->h_flag, sizeof(int)) != cudaSuccess) {
     delete ctx;
     return PMCGPU_ERR_CUDA;
@@ -136,6 +139,8 @@ extern "C" int pmcgpu_destroy(pmcgpu_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   for (void* p : ctx->allocs) cudaFree(p);
   if (ctx->h_flag) cudaFreeHost(ctx->h_flag);
+  if (ctx->h_tot) cudaFreeHost(ctx->h_tot);
+  pmcgpu_comm_destroy(ctx);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
   return PMCGPU_OK;

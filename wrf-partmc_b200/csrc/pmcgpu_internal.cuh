@@ -93,6 +93,41 @@ struct DevView {
   float* numconc;     // [n_cells][C] partmc_to_wrf output
 };
 
+// Transport work space of one patch (trans.cu).  "ext" arrays carry a one-cell ghost ring in x and y:
+// e = (i + 1) + (nx + 2) * (k + nz * (j + 1)).  Sides: 0 y-, 1 y+, 2 x-, 3 x+.
+struct TransView {
+  int nx, nz, ny, C;
+  float dx, dy, dt;
+  int vertmix;
+  // WRF fields of the patch (float, WRF memory order, class slowest)
+  float *u_flux, *v_flux, *w_flux;  // [(nx+1) nz ny C], [nx nz (ny+1) C], [nx (nz+1) ny C]
+  float *xkhh, *alt;                // ext arrays
+  float *zc, *z_at_w, *exch_h;      // [nx nz ny], [nx (nz+1) ny] x 2
+  int* ccount;                      // [n_cells][C] particles of (group 1, class)
+  double* num_old;                  // [n_cells][C] count * magnitude
+  double* scale_ratio;              // [n_cells][C] weight_ratio of the preweighting, 0 = none
+  double *padv, *pdiff, *pvert;     // [n_cells][C][6 | 4 | nz]
+  double* cellvol_ext;              // [n_ext]
+  double* wmag_ext;                 // [n_ext][C] magnitudes after the preweighting
+  int* out_dir;                     // [n_cells][C][4 + nz][2] offset, count of the out list per direction
+  int* out_slot;                    // [n_cells][cap] original slot of every transported particle
+  long long* out_newid;             // [n_cells][cap] new id when a copy stays behind, else 0
+  int* n_surv;                      // [n_cells]
+  int* n_moved;                     // [n_cells] arrivals of the last call
+  double* sbuf[4];                  // edge exchange buffers
+  double* rbuf[4];
+  int* scnt[4];
+  int* soff[4];                     // [L nz + 1] offsets of the ghost cells in the send slab
+  int* roff[4];
+};
+struct TrSlab {  // SoA particle records crossing one side
+  int cap;
+  double* vol;  // [S][cap]
+  long long* id;
+  int* wgc; int* nprim; int* hyst;
+  double* lct; double* gct;
+};
+
 struct ProfEntry {
   const char* name;
   cudaEvent_t a, b;
@@ -112,7 +147,19 @@ struct pmcgpu_ctx {
   int cur;  // unused: pointers are swapped in v
   int* d_flag;  // first non-zero cell status of the last check
   int* h_flag;  // pinned mirror
+  // transport
+  TransView t;
+  bool trans_ready = false;
+  TrSlab sslab[4], rslab[4];
+  int* h_tot = nullptr;  // pinned: particles sent / received per side
+  // patch neighbours (rank of the patch on side s; this rank itself on a periodic single patch)
+  int rank = 0, n_ranks = 1, px = 1, py = 1;
+  int nb[4] = {0, 0, 0, 0};
+  void* nccl_comm = nullptr;
 };
+int pmc_exchange_slabs(pmcgpu_ctx* ctx, const int* n_send, const int* n_recv);
+int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], const size_t send_bytes[4],
+                       const int* n_recv, size_t elem);
 
 #define CUDA_OK(ctx, call)                                                              \
   do {                                                                                  \

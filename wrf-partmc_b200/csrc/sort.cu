@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
   int* bc = v.bin_count + (size_t)cell * v.C * v.nbcap;
   for (int q = tid; q < v.C * v.nbcap; q += SORT_THREADS) bc[q] = 0;
   if (s_nb == 0 || s_fail) return;
+  if (edge_recheck == 2) return;  // grid decision only (end of trans_aero): the records stay where they are
   // ---- phase 2: bin of every particle (bin_grid.F90:143) + per-warp histograms.
   // Warp w owns the contiguous index range [w*seg, (w+1)*seg) so that ranks
   // inside a key follow the original particle order (stable).
@@ -239,6 +240,18 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
   }
 }
 
+static void swap_slabs(DevView& v);
+void pmc_swap_slabs(pmcgpu_ctx* ctx) { swap_slabs(ctx->v); }
+// aero_state_sort at the end of trans_aero (wrf_pmc_trans_aero.F90:803): the bin-grid decision of
+// aero_sorted_remake_if_needed only; the next mc_coag permutes the records anyway
+int pmc_sort_grid_only_async(pmcgpu_ctx* ctx) {
+  DevView& v = ctx->v;
+  const size_t smem = (size_t)(SORT_WARPS + 1) * v.C * v.nbcap * sizeof(int);
+  ProfScope ps_(ctx, "k_sort_cells_grid");
+  k_sort_cells<<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, 2);
+  LAUNCH_CHECK(ctx);
+  return PMCGPU_OK;
+}
 static void swap_slabs(DevView& v) {
   std::swap(v.vol, v.vol_alt);
   std::swap(v.id, v.id_alt);

@@ -29,6 +29,15 @@ class PmcGpuError(RuntimeError):
         self.code = code
 
 
+def comm_unique_id():
+    """128-byte NCCL unique id (made on one rank, broadcast by the host: MPI_Bcast in WRF)"""
+    buf = C.create_string_buffer(128)
+    rc = load_library().pmcgpu_comm_unique_id(buf, C.c_int(128))
+    if rc != 0:
+        raise PmcGpuError(rc, "pmcgpu_comm_unique_id failed")
+    return buf.raw
+
+
 def library_path():
     return os.path.join(_PKG, "libpmcgpu.so")
 
@@ -67,6 +76,13 @@ class _TimestepArgs(C.Structure):
                 ("coag_kernel_type", C.c_int), ("do_condensation", C.c_int), ("allow_doubling", C.c_int),
                 ("allow_halving", C.c_int), ("step", C.c_uint), ("num_conc_out", C.c_void_p),
                 ("rel_humid_out", C.c_void_p), ("no_wait", C.c_int)]
+
+
+class _TransArgs(C.Structure):
+    _fields_ = [("u_flux", C.c_void_p), ("v_flux", C.c_void_p), ("w_flux", C.c_void_p), ("xkhh", C.c_void_p),
+                ("alt", C.c_void_p), ("z", C.c_void_p), ("z_at_w", C.c_void_p), ("exch_h", C.c_void_p),
+                ("dx", C.c_float), ("dy", C.c_float), ("dt", C.c_float), ("vertmix_onoff", C.c_int),
+                ("allow_doubling", C.c_int), ("allow_halving", C.c_int), ("step", C.c_uint), ("no_wait", C.c_int)]
 
 
 def _f64(a):
@@ -274,6 +290,46 @@ class PartMCGPU:
         a.num_conc_out, a.rel_humid_out = _addr(num_conc_out), _addr(rel_humid_out)
         a.no_wait = int(no_wait)
         self._chk(self.L.pmcgpu_partmc_timestep(self.h, C.byref(a)))
+
+    def wrf_pmc_trans_driver(self, fields, step=0, vertmix_onoff=1, allow_doubling=True, allow_halving=True,
+                             no_wait=False):
+        """wrf_pmc_trans_driver (interface/wrf_pmc_trans.F90:37): move probabilities, then trans_aero
+        (interface/wrf_pmc_trans_aero.F90:40).  `fields` maps u_flux, v_flux, w_flux, xkhh, alt, z, z_at_w,
+        exch_h to float32 slabs of this patch (numpy, pinned or device tensors; a missing key keeps the values
+        of the previous call) and dx, dy, dt to scalars (synthetic.patch_fields builds such a dict)."""
+        a = _TransArgs()
+        keep = []
+        for k in ("u_flux", "v_flux", "w_flux", "xkhh", "alt", "z", "z_at_w", "exch_h"):
+            x = fields.get(k)
+            if x is not None and isinstance(x, np.ndarray):
+                x = np.ascontiguousarray(x, dtype=np.float32)
+                keep.append(x)
+            setattr(a, k, _addr(x))
+        a.dx, a.dy, a.dt = float(fields["dx"]), float(fields["dy"]), float(fields["dt"])
+        a.vertmix_onoff = int(vertmix_onoff)
+        a.allow_doubling, a.allow_halving = int(allow_doubling), int(allow_halving)
+        a.step = int(step)
+        a.no_wait = int(no_wait)
+        self._chk(self.L.pmcgpu_wrf_pmc_trans_driver(self.h, C.byref(a)))
+        if no_wait and keep:
+            self.synchronize()  # host copies made here must outlive the asynchronous upload
+
+    def trans_probs(self):
+        """(adv[n_cells][C][6], diff[n_cells][C][4], vert[n_cells][C][nz]) of the last transport call"""
+        n, Cc = self.n_cells, self.n_class
+        adv, diff, vert = np.zeros((n, Cc, 6)), np.zeros((n, Cc, 4)), np.zeros((n, Cc, self.nz))
+        self._chk(self.L.pmcgpu_get_trans_probs(self.h, _p(adv), _p(diff), _p(vert)))
+        return adv, diff, vert
+
+    def trans_moved(self):
+        out = np.zeros(self.n_cells, np.int32)
+        self._chk(self.L.pmcgpu_get_trans_moved(self.h, _p(out)))
+        return out
+
+    def comm_init(self, unique_id, n_ranks, rank, px, py):
+        """patch decomposition px x py of the periodic domain, one rank per patch (pmcgpu_comm_init)"""
+        self._chk(self.L.pmcgpu_comm_init(self.h, unique_id, C.c_int(n_ranks), C.c_int(rank), C.c_int(px),
+                                          C.c_int(py)))
 
     def check_status(self):
         self._chk(self.L.pmcgpu_check_status(self.h))
