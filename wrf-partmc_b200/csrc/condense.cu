@@ -164,15 +164,113 @@ __constant__ double c_rosGam[ROS_S] = {0.25, -0.1043, 0.1035, -0.362000000000002
 #define ROS_GAMMA 0.25
 #define ROS_ELO 4.0
 
+// condense_rates (condense.F90:371-502) for PPT particles of one thread at once.  The PPT
+// evaluations are independent dependency chains that the unrolled inner loops interleave, which is
+// what keeps the FP64 pipe busy with 8 warps per SM.  Per particle one division yields the four
+// reciprocals 1/D, 1/(D+Y), 1/(D+Z), 1/den; the Newton iteration on delta* keeps the reference's
+// five fixed steps with one exp and two divisions each.  Per-particle constants (D_dry, kappa,
+// num_conc) are read from shared memory (stride COND_THREADS).
+// WITH_JAC also returns a = dDdot/dD, b = dDdot/dH, c = dHdot_i/dD, dH = dHdot_i/dH.
+template <int PPT, bool WITH_JAC>
+__device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const double (&D)[PPT],
+                                               const double* __restrict__ sDdry, const double* __restrict__ sKap,
+                                               const double* __restrict__ sNc, double (&Ddot)[PPT],
+                                               double (&Hd)[PPT], double (&a)[PPT], double (&b)[PPT],
+                                               double (&c)[PPT], double (&dH)[PPT]) {
+  const double g = -2.0 * PmcConst::pi / (e.V * e.vc);  // Hdot_i = g * num_conc * D^2 * Ddot
+  const double invU = 1.0 / e.U;
+  double k_ap[PPT], UVD[PPT], a_w[PPT], XD[PPT], invD[PPT];
+  double inv_dY[PPT], inv_dZ[PPT], inv_den[PPT];
+  double delta[PPT], hh[PPT], dh[PPT], q[PPT], ex[PPT];
+#pragma unroll
+  for (int k = 0; k < PPT; k++) {
+    const double d = D[k], dd = sDdry[k * COND_THREADS], kp = sKap[k * COND_THREADS];
+    const double D3 = d * d * d, Dd3 = dd * dd * dd;
+    const double dY = d + e.Y, dZ = d + e.Z, den = D3 + (kp - 1.0) * Dd3;
+    const double pYZ = dY * dZ, pDn = d * den;
+    const double r = 1.0 / (pYZ * pDn);
+    invD[k] = r * pYZ * den;
+    inv_dY[k] = r * dZ * pDn;
+    inv_dZ[k] = r * dY * pDn;
+    inv_den[k] = r * pYZ * d;
+    k_ap[k] = e.k_a * d * inv_dY[k];
+    UVD[k] = e.UV * (e.D_v * d * inv_dZ[k]);
+    a_w[k] = (D3 - Dd3) * inv_den[k];
+    XD[k] = e.X * invD[k];
+    delta[k] = 0.0;
+    hh[k] = 0.0;
+    dh[k] = 1.0;
+    q[k] = 1.0;
+    ex[k] = 0.0;
+  }
+#pragma unroll 1
+  for (int newton_step = 1; newton_step <= 5; newton_step++) {
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+      delta[k] = delta[k] - hh[k] / dh[k];
+      q[k] = 1.0 / (1.0 + delta[k]);
+      ex[k] = exp((e.W * delta[k] + XD[k]) * q[k]);
+      hh[k] = k_ap[k] * delta[k] - UVD[k] * (H - a_w[k] * q[k] * ex[k]);
+      dh[k] = k_ap[k] - UVD[k] * a_w[k] * (q[k] * q[k]) * (1.0 - e.W * q[k] + XD[k] * q[k]) * ex[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < PPT; k++) {
+    const double d = D[k];
+    const double hf = g * sNc[k * COND_THREADS];
+    const double kU = k_ap[k] * invD[k] * invU;  // k_ap / (U D)
+    Ddot[k] = kU * delta[k];
+    Hd[k] = hf * (d * d) * Ddot[k];
+    if (WITH_JAC) {
+      const double dd = sDdry[k * COND_THREADS], kp = sKap[k * COND_THREADS];
+      const double Dd3 = dd * dd * dd;
+      const double D_vp = e.D_v * d * inv_dZ[k];
+      const double dkap_dD = e.k_a * e.Y * (inv_dY[k] * inv_dY[k]);
+      const double dDvp_dD = e.D_v * e.Z * (inv_dZ[k] * inv_dZ[k]);
+      const double daw_dD = 3.0 * (d * d) * kp * Dd3 * (inv_den[k] * inv_den[k]);
+      const double dh_dD = dkap_dD * delta[k] - e.UV * dDvp_dD * H +
+                           e.UV * (a_w[k] * dDvp_dD + D_vp * daw_dD - D_vp * a_w[k] * (XD[k] * invD[k]) * q[k]) * q[k] * ex[k];
+      const double inv_dh = 1.0 / dh[k];
+      const double ddeltastar_dD = -dh_dD * inv_dh;
+      const double ddeltastar_dH = UVD[k] * inv_dh;
+      a[k] = dkap_dD * delta[k] * invD[k] * invU + kU * ddeltastar_dD - kU * delta[k] * invD[k];
+      b[k] = kU * ddeltastar_dH;
+      c[k] = hf * (2.0 * d * Ddot[k] + (d * d) * a[k]);
+      dH[k] = hf * (d * d) * b[k];
+    }
+  }
+  // dry particles (D <= D_dry, condense.F90:418-436): rare, handled one by one
+#pragma unroll
+  for (int k = 0; k < PPT; k++) {
+    const double dd = sDdry[k * COND_THREADS];
+    if (D[k] <= dd) {
+      const double hf = g * sNc[k * COND_THREADS];
+      const double kd = e.k_a / (1.0 + e.Y / dd);
+      const double Dvd = e.D_v / (1.0 + e.Z / dd);
+      const double delta_star = e.UV * Dvd * H / kd;
+      Ddot[k] = kd * delta_star / (e.U * dd);
+      Hd[k] = hf * (dd * dd) * Ddot[k];
+      if (WITH_JAC) {
+        a[k] = 0.0;
+        b[k] = kd / (e.U * dd) * (e.UV * Dvd / kd);
+        c[k] = 0.0;
+        dH[k] = hf * (dd * dd) * b[k];
+      }
+    }
+  }
+}
+
+#define COND_NARR (ROS_S + 5)  // shared arrays per particle: 6 stage vectors, abstol, solute volume, D_dry, kappa, num_conc
 template <int PPT>
 __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const double* T0a /* may alias v.temp */,
                                                            const double* p0a,
                                                            const double* T1 /* may alias v.temp */,
                                                            const double* p1, CondParams prm,
                                                            double* __restrict__ h_state, int* __restrict__ stats,
-                                                           double* __restrict__ wre_out, int n_limit_lo,
+                                                           double* __restrict__ wre_out,
+                                                           const int* __restrict__ cell_list, int n_limit_lo,
                                                            int n_limit_hi) {
-  const int cell = blockIdx.x;
+  const int cell = cell_list ? cell_list[blockIdx.x] : blockIdx.x;
   const int n = v.count[cell];
   if (n <= n_limit_lo || n > n_limit_hi) return;  // another instantiation owns this cell
   if (v.status[cell] != 0) return;
@@ -180,10 +278,13 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
   __shared__ double s_red[3 * (COND_THREADS / 32)];
-  extern __shared__ double s_K[];  // [ROS_S + 2][PPT][COND_THREADS]: stage vectors, abstol, solute volume
+  extern __shared__ double s_K[];  // [COND_NARR][PPT][COND_THREADS]
 #define SK(st, k) s_K[((st) * PPT + (k)) * COND_THREADS + tid]
 #define S_ATOL(k) SK(ROS_S, k)
 #define S_SOLV(k) SK(ROS_S + 1, k)
+  const double* sDdry = &SK(ROS_S + 2, 0);
+  const double* sKap = &SK(ROS_S + 3, 0);
+  const double* sNc = &SK(ROS_S + 4, 0);
   // aero_state_reweight (aero_state.F90:597-653) after the solve is the identity for flat
   // weights (ratio 1, prob_round(1) = 1); size-dependent weights need the duplicate / remove
   // pass, which is not built yet: say so instead of skipping it silently.
@@ -197,15 +298,19 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
   const double Tdot = (T1[cell] - T0) / prm.del_t, pdot = (p1[cell] - p0) / prm.del_t;
   double H = v.rh[cell];
 
-  // ---- set-up (condense.F90:196-237): kappa, D_dry, num_conc, D, abstol per particle
-  double D[PPT], Ddry[PPT], kap[PPT], nc[PPT];
+  // ---- set-up (condense.F90:196-237): kappa, D_dry, num_conc, D, abstol per particle.
+  // Slots past the population hold a harmless wet dummy particle that never enters a sum.
+  double D[PPT];
   double wsum = 0.0;
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
     const int p = tid + k * COND_THREADS;
-    D[k] = 1.0; Ddry[k] = 1.0; kap[k] = 0.0; nc[k] = 1.0;
+    D[k] = 2.0;
     S_ATOL(k) = 1.0;
     S_SOLV(k) = 0.0;
+    SK(ROS_S + 2, k) = 1.0;
+    SK(ROS_S + 3, k) = 0.5;
+    SK(ROS_S + 4, k) = 1.0;
     if (p < n) {
       // aero_particle_solute_kappa (aero_particle.F90:724-755), solute volume, total volume
       double vt = 0.0, vs = 0.0, ks = 0.0;
@@ -225,13 +330,15 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       }
       const int gc = v.wgc[base + p];
       const double r = vol2rad(vt);
+      const double ddry = 2.0 * vol2rad(vs);
+      const double ncp = awa_nc_at_radius(v, cell, gc / v.G + 1, r);
       S_SOLV(k) = vs;
-      kap[k] = ks / vs;
-      Ddry[k] = 2.0 * vol2rad(vs);
-      nc[k] = awa_nc_at_radius(v, cell, gc / v.G + 1, r);
+      SK(ROS_S + 2, k) = ddry;
+      SK(ROS_S + 3, k) = ks / vs;
+      SK(ROS_S + 4, k) = ncp;
       D[k] = 2.0 * r;
-      S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (D[k] - Ddry[k]));
-      wsum += v.vol[(size_t)iw * NS + base + p] * nc[k];
+      S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (D[k] - ddry));
+      wsum += v.vol[(size_t)iw * NS + base + p] * ncp;
     }
   }
   {
@@ -249,6 +356,7 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
   double h_natural = h;
   int n_steps = 0, n_reject = 0, fail = 0;
   bool reject_last = false, reject_more = false;
+  double u1[PPT], u2[PPT], u3[PPT], u4[PPT];  // unused outputs of the no-Jacobian evaluations
 
   while (t < del_t && !fail) {
     if (n_steps + n_reject >= prm.max_steps) { fail = 6; break; }
@@ -260,19 +368,19 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
     {
       const CondEnv e0 = cond_env(T0, p0, Tdot, pdot, t);
       const CondEnv e1 = cond_env(T0, p0, Tdot, pdot, t + DT_FD);
+      double hd[PPT], dh[PPT], f1[PPT], hd1[PPT];
+      cond_rates_vec<PPT, true>(e0, H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh);
+      cond_rates_vec<PPT, false>(e1, H, D, sDdry, sKap, sNc, f1, hd1, u1, u2, u3, u4);
       double acc[3] = {0.0, 0.0, 0.0};
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
-        const int p = tid + k * COND_THREADS;
-        f0[k] = 0.0; dfdt[k] = 0.0; ja[k] = 0.0; jb[k] = 0.0; jc[k] = 0.0;
-        if (p < n) {
-          double hd, dh, f1, hd1, u1, u2, u3, u4;
-          cond_rates<true>(e0, H, D[k], Ddry[k], kap[k], nc[k], f0[k], hd, ja[k], jb[k], jc[k], dh);
-          cond_rates<false>(e1, H, D[k], Ddry[k], kap[k], nc[k], f1, hd1, u1, u2, u3, u4);
-          dfdt[k] = (f1 - f0[k]) / DT_FD;
-          acc[0] += hd;
-          acc[1] += dh;
-          acc[2] += hd1;
+        const bool live = tid + k * COND_THREADS < n;
+        dfdt[k] = (f1[k] - f0[k]) / DT_FD;
+        if (!live) { f0[k] = 0.0; dfdt[k] = 0.0; ja[k] = 0.0; jb[k] = 0.0; jc[k] = 0.0; }
+        if (live) {
+          acc[0] += hd[k];
+          acc[1] += dh[k];
+          acc[2] += hd1[k];
         }
       }
       block_sum<3>(acc, s_red);
@@ -284,6 +392,7 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
     }
     for (;;) {
       const double eps = 1.0 / (ROS_GAMMA * h);
+      const double inv_h = 1.0 / h;
       double inv[PPT];
       double KH[ROS_S];
       double sden[1] = {0.0};
@@ -294,36 +403,43 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       }
       block_sum<1>(sden, s_red);
       const double lhs_H = eps - dd - sden[0];
-#pragma unroll
+#pragma unroll 1
       for (int st = 0; st < ROS_S; st++) {
         // stage function value (stage 1 reuses f at (t, y))
-        double fs[PPT];
+        double fs[PPT], hd[PPT];
         double acc[2] = {0.0, 0.0};
         double Hs = H;
+        for (int j = 0; j < st; j++) Hs += c_rosA[st][j] * KH[j];
+        CondEnv es = cond_env(T0, p0, Tdot, pdot, t + c_rosAlpha[st] * h);
         if (st > 0) {
+          double y[PPT];
 #pragma unroll
-          for (int j = 0; j < st; j++) Hs += c_rosA[st][j] * KH[j];
+          for (int k = 0; k < PPT; k++) y[k] = D[k];
+          for (int j = 0; j < st; j++) {
+            const double aj = c_rosA[st][j];
+#pragma unroll
+            for (int k = 0; k < PPT; k++) y[k] += aj * SK(j, k);
+          }
+          cond_rates_vec<PPT, false>(es, Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4);
+        } else {
+#pragma unroll
+          for (int k = 0; k < PPT; k++) { fs[k] = f0[k]; hd[k] = 0.0; }
         }
-        const CondEnv es = cond_env(T0, p0, Tdot, pdot, t + c_rosAlpha[st] * h);
+        const double hg = h * c_rosGam[st];
+#pragma unroll
+        for (int k = 0; k < PPT; k++) fs[k] = fs[k] + hg * dfdt[k];
+        for (int j = 0; j < st; j++) {
+          const double cj = c_rosC[st][j] * inv_h;
+#pragma unroll
+          for (int k = 0; k < PPT; k++) fs[k] += cj * SK(j, k);
+        }
 #pragma unroll
         for (int k = 0; k < PPT; k++) {
-          const int p = tid + k * COND_THREADS;
-          fs[k] = f0[k];
-          if (p < n) {
-            double hd = 0.0;
-            if (st > 0) {
-              double y = D[k];
-#pragma unroll
-              for (int j = 0; j < st; j++) y += c_rosA[st][j] * SK(j, k);
-              double u1, u2, u3, u4;
-              cond_rates<false>(es, Hs, y, Ddry[k], kap[k], nc[k], fs[k], hd, u1, u2, u3, u4);
-            }
-            double r = fs[k] + h * c_rosGam[st] * dfdt[k];
-#pragma unroll
-            for (int j = 0; j < st; j++) r += (c_rosC[st][j] / h) * SK(j, k);
-            fs[k] = r;
-            acc[0] += hd;
-            acc[1] += jc[k] * r * inv[k];
+          if (tid + k * COND_THREADS < n) {
+            acc[0] += hd[k];
+            acc[1] += jc[k] * fs[k] * inv[k];
+          } else {
+            fs[k] = 0.0;
           }
         }
         block_sum<2>(acc, s_red);
@@ -332,9 +448,8 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
           fsH = f0H;
         else
           fsH = acc[0] + (-es.dP0_dT_div_P0 * Tdot * Hs + Hs * pdot / es.p);
-        double rH = fsH + h * c_rosGam[st] * dfdtH;
-#pragma unroll
-        for (int j = 0; j < st; j++) rH += (c_rosC[st][j] / h) * KH[j];
+        double rH = fsH + hg * dfdtH;
+        for (int j = 0; j < st; j++) rH += (c_rosC[st][j] * inv_h) * KH[j];
         KH[st] = (rH + acc[1]) / lhs_H;
 #pragma unroll
         for (int k = 0; k < PPT; k++) SK(st, k) = (fs[k] + jb[k] * KH[st]) * inv[k];
@@ -371,7 +486,8 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       double hnew = h * fac;
       if (err <= 1.0) {
 #pragma unroll
-        for (int k = 0; k < PPT; k++) D[k] = Dn[k];
+        for (int k = 0; k < PPT; k++)
+          if (tid + k * COND_THREADS < n) D[k] = Dn[k];
         H = Hn;
         t += h;
         n_steps++;
@@ -401,7 +517,7 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       double wv = rad2vol(D[k] / 2.0) - S_SOLV(k);
       wv = fmax(0.0, wv);
       v.vol[(size_t)iw * NS + base + p] = wv;
-      wfin += wv * nc[k];
+      wfin += wv * sNc[k * COND_THREADS];
     }
   }
   {
@@ -435,16 +551,18 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
 #undef S_SOLV
 }
 
+
 int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
                            CondParams prm, double* h_state, int* stats, double* wre, int n_lo);
 
 // device pointers T1/p1 (final env per cell)
-static size_t cond_smem(int ppt) { return (size_t)(ROS_S + 2) * ppt * COND_THREADS * sizeof(double); }
+static size_t cond_smem(int ppt) { return (size_t)COND_NARR * ppt * COND_THREADS * sizeof(double); }
 
 int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
                        double del_t, double reltol) {
   static bool configured = false;
   if (!configured) {
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(2)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(4)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(8)));
     configured = true;
@@ -466,18 +584,18 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
   ProfScope ps_(ctx, "k_condense");
   // the population size of a cell picks the instantiation: 1..256 -> PPT 1, ..512 -> 2, ..1024 -> 4, ..2048 -> 8
   const int cap = v.cap;
-  k_condense<1><<<v.n_cells, COND_THREADS, cond_smem(1), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, -1, 256);
+  k_condense<1><<<v.n_cells, COND_THREADS, cond_smem(1), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, nullptr, -1, 256);
   LAUNCH_CHECK(ctx);
   if (cap > 256) {
-    k_condense<2><<<v.n_cells, COND_THREADS, cond_smem(2), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 256, 512);
+    k_condense<2><<<v.n_cells, COND_THREADS, cond_smem(2), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, nullptr, 256, 512);
     LAUNCH_CHECK(ctx);
   }
   if (cap > 512) {
-    k_condense<4><<<v.n_cells, COND_THREADS, cond_smem(4), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 512, 1024);
+    k_condense<4><<<v.n_cells, COND_THREADS, cond_smem(4), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, nullptr, 512, 1024);
     LAUNCH_CHECK(ctx);
   }
   if (cap > 1024) {
-    k_condense<8><<<v.n_cells, COND_THREADS, cond_smem(8), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 1024, 2048);
+    k_condense<8><<<v.n_cells, COND_THREADS, cond_smem(8), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, nullptr, 1024, 2048);
     LAUNCH_CHECK(ctx);
   }
   if (cap > 2048) {
