@@ -164,12 +164,50 @@ __constant__ double c_rosGam[ROS_S] = {0.25, -0.1043, 0.1035, -0.362000000000002
 #define ROS_GAMMA 0.25
 #define ROS_ELO 4.0
 
+// ---- branch-free FP64 primitives for the rate evaluation.  The library versions of 1/x and exp
+// carry special-case branches and immediate-operand constants that showed up as 16 % UMOV and 10 %
+// BRA/BSSY/BSYNC of all executed instructions (profiles/r01_s9_condense_ncu.md); the arguments here
+// are always finite, normal and of moderate size, so the fast paths alone are enough.
+__constant__ double c_expc[14] = {1.0, 1.0, 1.0 / 2, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040,
+                                  1.0 / 40320, 1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600,
+                                  1.0 / 6227020800.0};
+// 1/x for normal x: MUFU.RCP64H seed (about 20 bits), one cubic and one quadratic correction (< 1 ulp)
+__device__ __forceinline__ double fast_rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  e = fma(e, e, e);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+}
+// exp(x) for |x| < 700: x = n ln2 + r, |r| <= ln2 / 2, degree-13 Taylor polynomial (remainder 4e-18),
+// 2^n by an add into the exponent field
+__device__ __forceinline__ double fast_exp(double x) {
+  const double SHIFT = 6755399441055744.0;  // 1.5 * 2^52
+  const double kd = fma(x, 1.4426950408889634, SHIFT);
+  const int n = __double2loint(kd);
+  const double nf = kd - SHIFT;
+  double r = fma(nf, -6.93147180369123816490e-01, x);
+  r = fma(nf, -1.90821492927058770002e-10, r);
+  double p = c_expc[13];
+#pragma unroll
+  for (int i = 12; i >= 0; i--) p = fma(p, r, c_expc[i]);
+  return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
+
 // condense_rates (condense.F90:371-502) for PPT particles of one thread at once.  The PPT
 // evaluations are independent dependency chains that the unrolled inner loops interleave, which is
-// what keeps the FP64 pipe busy with 8 warps per SM.  Per particle one division yields the four
-// reciprocals 1/D, 1/(D+Y), 1/(D+Z), 1/den; the Newton iteration on delta* keeps the reference's
-// five fixed steps with one exp and two divisions each.  Per-particle constants (D_dry, kappa,
-// num_conc) are read from shared memory (stride COND_THREADS).
+// what keeps the FP64 pipe busy with few warps per SM.  Per particle one reciprocal yields
+// 1/D, 1/(D+Y), 1/(D+Z), 1/den.
+// The reference finds delta* by five fixed Newton steps from zero on
+//   h(delta) = k_a' delta - U V D_v' (H - a_w exp((W delta + X/D)/(1+delta)) / (1+delta));
+// its iterates reach rounding level after the third update (profiles/r01_newton_convergence.md).  Here
+// the same root is found in the variable u = delta / (1 + delta), which removes the division from the
+// iteration: (1 - u) h = k_a' u - (1 - u) (B - g), g = A (1 - u) exp(X/D + (W - X/D) u), A = U V D_v' a_w,
+// B = U V D_v' H.  The iteration stops when every lane's update is below 1e-7 |u| (the next error is
+// then below 1e-16 |u|), after at most five evaluations like the reference.
+// Per-particle constants (D_dry, kappa, num_conc) are read from shared memory (stride COND_THREADS).
 // WITH_JAC also returns a = dDdot/dD, b = dDdot/dH, c = dHdot_i/dD, dH = dHdot_i/dH.
 template <int PPT, bool WITH_JAC>
 __device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const double (&D)[PPT],
@@ -181,14 +219,14 @@ __device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const
   const double invU = 1.0 / e.U;
   double k_ap[PPT], UVD[PPT], a_w[PPT], XD[PPT], invD[PPT];
   double inv_dY[PPT], inv_dZ[PPT], inv_den[PPT];
-  double delta[PPT], hh[PPT], dh[PPT], q[PPT], ex[PPT];
+  double u[PPT], A[PPT], kB[PPT], cW[PPT];
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
     const double d = D[k], dd = sDdry[k * COND_THREADS], kp = sKap[k * COND_THREADS];
     const double D3 = d * d * d, Dd3 = dd * dd * dd;
-    const double dY = d + e.Y, dZ = d + e.Z, den = D3 + (kp - 1.0) * Dd3;
+    const double dY = d + e.Y, dZ = d + e.Z, den = fma(kp - 1.0, Dd3, D3);
     const double pYZ = dY * dZ, pDn = d * den;
-    const double r = 1.0 / (pYZ * pDn);
+    const double r = fast_rcp(pYZ * pDn);
     invD[k] = r * pYZ * den;
     inv_dY[k] = r * dZ * pDn;
     inv_dZ[k] = r * dY * pDn;
@@ -197,43 +235,52 @@ __device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const
     UVD[k] = e.UV * (e.D_v * d * inv_dZ[k]);
     a_w[k] = (D3 - Dd3) * inv_den[k];
     XD[k] = e.X * invD[k];
-    delta[k] = 0.0;
-    hh[k] = 0.0;
-    dh[k] = 1.0;
-    q[k] = 1.0;
-    ex[k] = 0.0;
+    A[k] = UVD[k] * a_w[k];
+    kB[k] = fma(UVD[k], H, k_ap[k]);
+    cW[k] = e.W - XD[k];
+    u[k] = 0.0;
   }
 #pragma unroll 1
   for (int newton_step = 1; newton_step <= 5; newton_step++) {
+    bool small = true;
 #pragma unroll
     for (int k = 0; k < PPT; k++) {
-      delta[k] = delta[k] - hh[k] / dh[k];
-      q[k] = 1.0 / (1.0 + delta[k]);
-      ex[k] = exp((e.W * delta[k] + XD[k]) * q[k]);
-      hh[k] = k_ap[k] * delta[k] - UVD[k] * (H - a_w[k] * q[k] * ex[k]);
-      dh[k] = k_ap[k] - UVD[k] * a_w[k] * (q[k] * q[k]) * (1.0 - e.W * q[k] + XD[k] * q[k]) * ex[k];
+      const double s = 1.0 - u[k];
+      const double ex = fast_exp(fma(cW[k], u[k], XD[k]));
+      const double gg = A[k] * s * ex;
+      const double Bg = fma(UVD[k], H, -gg);             // B - g
+      const double hh = fma(k_ap[k], u[k], -s * Bg);     // (1 - u) h
+      const double dh = fma(gg, fma(s, cW[k], -2.0), kB[k]);
+      const double du = hh * fast_rcp(dh);
+      small = small && (fabs(du) <= 1e-7 * fabs(u[k]));
+      u[k] -= du;
     }
+    if (__all_sync(0xffffffffu, small)) break;
   }
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
     const double d = D[k];
     const double hf = g * sNc[k * COND_THREADS];
     const double kU = k_ap[k] * invD[k] * invU;  // k_ap / (U D)
-    Ddot[k] = kU * delta[k];
+    const double q = 1.0 - u[k];                 // 1 / (1 + delta*)
+    const double delta = u[k] * fast_rcp(q);
+    Ddot[k] = kU * delta;
     Hd[k] = hf * (d * d) * Ddot[k];
     if (WITH_JAC) {
       const double dd = sDdry[k * COND_THREADS], kp = sKap[k * COND_THREADS];
       const double Dd3 = dd * dd * dd;
+      const double ex = fast_exp(fma(cW[k], u[k], XD[k]));  // exp((W delta + X/D) / (1 + delta))
+      const double dhd = k_ap[k] - A[k] * (q * q) * (1.0 - e.W * q + XD[k] * q) * ex;  // dh/ddelta (:462)
       const double D_vp = e.D_v * d * inv_dZ[k];
       const double dkap_dD = e.k_a * e.Y * (inv_dY[k] * inv_dY[k]);
       const double dDvp_dD = e.D_v * e.Z * (inv_dZ[k] * inv_dZ[k]);
       const double daw_dD = 3.0 * (d * d) * kp * Dd3 * (inv_den[k] * inv_den[k]);
-      const double dh_dD = dkap_dD * delta[k] - e.UV * dDvp_dD * H +
-                           e.UV * (a_w[k] * dDvp_dD + D_vp * daw_dD - D_vp * a_w[k] * (XD[k] * invD[k]) * q[k]) * q[k] * ex[k];
-      const double inv_dh = 1.0 / dh[k];
+      const double dh_dD = dkap_dD * delta - e.UV * dDvp_dD * H +
+                           e.UV * (a_w[k] * dDvp_dD + D_vp * daw_dD - D_vp * a_w[k] * (XD[k] * invD[k]) * q) * q * ex;
+      const double inv_dh = fast_rcp(dhd);
       const double ddeltastar_dD = -dh_dD * inv_dh;
       const double ddeltastar_dH = UVD[k] * inv_dh;
-      a[k] = dkap_dD * delta[k] * invD[k] * invU + kU * ddeltastar_dD - kU * delta[k] * invD[k];
+      a[k] = dkap_dD * delta * invD[k] * invU + kU * ddeltastar_dD - kU * delta * invD[k];
       b[k] = kU * ddeltastar_dH;
       c[k] = hf * (2.0 * d * Ddot[k] + (d * d) * a[k]);
       dH[k] = hf * (d * d) * b[k];

@@ -1,0 +1,290 @@
+! pmc_gpu.F90 -- ISO_C_BINDING layer between WRF-PartMC's interface/ code and
+! libpmcgpu.so (include/pmcgpu.h).
+!
+! This is the only host code a WRF-PartMC build adds: it keeps the argument lists of
+!   partmc_timestep       (interface/wrf_pmc_driver.F90:46-87)
+!   wrf_pmc_trans_driver  (interface/wrf_pmc_trans.F90:37-76)
+! and forwards them to the device library, which owns all particles of the patch.
+! Conventions follow the reference's own C boundary (partmc/src/condense.F90:183-195):
+! scalars by value, arrays through c_loc of a contiguous target, int return code with
+! 0 = success, a non-zero code is handed to die_msg (util.F90:134).
+!
+! NOTE: no Fortran compiler exists in the build image of this repository (gfortran,
+! flang, nvfortran, ifx all absent), so this file is written against the Fortran 2003
+! standard and the header but has NOT been compiled; tests drive the same C symbols
+! through wrf-partmc_b200/host/pmcgpu.py.  INTEGRATION.md lists the build line.
+module pmc_gpu
+
+  use, intrinsic :: iso_c_binding
+  implicit none
+  private
+
+  public :: pmcgpu_config_t, pmcgpu_timestep_args_t, pmcgpu_trans_args_t
+  public :: pmc_gpu_init, pmc_gpu_finalize, pmc_gpu_upload_aero_states, &
+       pmc_gpu_download_aero_states, pmc_gpu_partmc_timestep, &
+       pmc_gpu_wrf_pmc_trans_driver, pmc_gpu_check
+  public :: pmc_gpu_handle
+
+  integer, parameter :: dp = c_double
+
+  !> coag_kernel.F90:24-40
+  integer(c_int), parameter, public :: PMCGPU_KERNEL_ADDITIVE = 2, &
+       PMCGPU_KERNEL_CONSTANT = 3, PMCGPU_KERNEL_BROWN = 4, PMCGPU_KERNEL_ZERO = 5
+
+  !> pmcgpu_config (include/pmcgpu.h); member order must match the C struct.
+  type, bind(c) :: pmcgpu_config_t
+     integer(c_int) :: n_spec
+     type(c_ptr) :: density, kappa, molec_weight, num_ions
+     integer(c_int) :: i_water
+     integer(c_int) :: n_group, n_class
+     integer(c_int) :: nx, nz, ny
+     integer(c_int) :: global_nx, global_ny
+     integer(c_int) :: i_offset, j_offset
+     integer(c_int) :: periodic_x, periodic_y
+     real(c_double) :: n_part_ideal
+     integer(c_int) :: cell_capacity
+     integer(c_int) :: max_bins
+     integer(c_int) :: seed          ! unsigned int on the C side (same size)
+     integer(c_int) :: device
+  end type pmcgpu_config_t
+
+  !> pmcgpu_timestep_args (include/pmcgpu.h)
+  type, bind(c) :: pmcgpu_timestep_args_t
+     type(c_ptr) :: temp, pressure, rel_humid, inverse_density, cell_volume
+     real(c_double) :: elapsed_time, dt, chem_dt
+     integer(c_int) :: do_coagulation, coag_kernel_type, do_condensation
+     integer(c_int) :: allow_doubling, allow_halving
+     integer(c_int) :: step
+     type(c_ptr) :: num_conc_out, rel_humid_out
+     integer(c_int) :: no_wait
+  end type pmcgpu_timestep_args_t
+
+  !> pmcgpu_trans_args (include/pmcgpu.h)
+  type, bind(c) :: pmcgpu_trans_args_t
+     type(c_ptr) :: u_flux, v_flux, w_flux, xkhh, alt, z, z_at_w, exch_h
+     real(c_float) :: dx, dy, dt
+     integer(c_int) :: vertmix_onoff, allow_doubling, allow_halving
+     integer(c_int) :: step
+     integer(c_int) :: no_wait
+  end type pmcgpu_trans_args_t
+
+  !> Opaque device context of this MPI rank (one GPU per rank).
+  type(c_ptr), save :: pmc_gpu_handle = c_null_ptr
+  !> Counter that addresses the random draws: two values per WRF step.
+  integer(c_int), save :: pmc_gpu_step = 0
+
+  interface
+     integer(c_int) function pmcgpu_create(cfg, ctx) bind(c, name='pmcgpu_create')
+       import :: c_int, c_ptr, pmcgpu_config_t
+       type(pmcgpu_config_t), intent(in) :: cfg
+       type(c_ptr), intent(out) :: ctx
+     end function pmcgpu_create
+     integer(c_int) function pmcgpu_destroy(ctx) bind(c, name='pmcgpu_destroy')
+       import :: c_int, c_ptr
+       type(c_ptr), value :: ctx
+     end function pmcgpu_destroy
+     type(c_ptr) function pmcgpu_last_error(ctx) bind(c, name='pmcgpu_last_error')
+       import :: c_ptr
+       type(c_ptr), value :: ctx
+     end function pmcgpu_last_error
+     integer(c_int) function pmcgpu_set_particles(ctx, cell_count, vol, wgroup, wclass, id, &
+          n_primary, hyst, lct, gct) bind(c, name='pmcgpu_set_particles')
+       import :: c_int, c_ptr
+       type(c_ptr), value :: ctx, cell_count, vol, wgroup, wclass, id, n_primary, hyst, lct, gct
+     end function pmcgpu_set_particles
+     integer(c_int) function pmcgpu_get_counts(ctx, cell_count) bind(c, name='pmcgpu_get_counts')
+       import :: c_int, c_ptr
+       type(c_ptr), value :: ctx, cell_count
+     end function pmcgpu_get_counts
+     integer(c_int) function pmcgpu_get_particles(ctx, n_total, vol, wgroup, wclass, id, &
+          n_primary, hyst, lct, gct) bind(c, name='pmcgpu_get_particles')
+       import :: c_int, c_ptr, c_long_long
+       type(c_ptr), value :: ctx
+       integer(c_long_long), value :: n_total
+       type(c_ptr), value :: vol, wgroup, wclass, id, n_primary, hyst, lct, gct
+     end function pmcgpu_get_particles
+     integer(c_int) function pmcgpu_set_weights(ctx, wtype, magnitude, exponent) &
+          bind(c, name='pmcgpu_set_weights')
+       import :: c_int, c_ptr
+       type(c_ptr), value :: ctx, wtype, magnitude, exponent
+     end function pmcgpu_set_weights
+     integer(c_int) function pmcgpu_get_weights(ctx, wtype, magnitude, exponent) &
+          bind(c, name='pmcgpu_get_weights')
+       import :: c_int, c_ptr
+       type(c_ptr), value :: ctx, wtype, magnitude, exponent
+     end function pmcgpu_get_weights
+     integer(c_int) function pmcgpu_set_env(ctx, temp, pressure, rel_humid, inverse_density, &
+          cell_volume) bind(c, name='pmcgpu_set_env')
+       import :: c_int, c_ptr
+       type(c_ptr), value :: ctx, temp, pressure, rel_humid, inverse_density, cell_volume
+     end function pmcgpu_set_env
+     integer(c_int) function pmcgpu_partmc_timestep(ctx, args) &
+          bind(c, name='pmcgpu_partmc_timestep')
+       import :: c_int, c_ptr, pmcgpu_timestep_args_t
+       type(c_ptr), value :: ctx
+       type(pmcgpu_timestep_args_t), intent(in) :: args
+     end function pmcgpu_partmc_timestep
+     integer(c_int) function pmcgpu_wrf_pmc_trans_driver(ctx, args) &
+          bind(c, name='pmcgpu_wrf_pmc_trans_driver')
+       import :: c_int, c_ptr, pmcgpu_trans_args_t
+       type(c_ptr), value :: ctx
+       type(pmcgpu_trans_args_t), intent(in) :: args
+     end function pmcgpu_wrf_pmc_trans_driver
+     integer(c_int) function pmcgpu_check_status(ctx) bind(c, name='pmcgpu_check_status')
+       import :: c_int, c_ptr
+       type(c_ptr), value :: ctx
+     end function pmcgpu_check_status
+     integer(c_int) function pmcgpu_comm_unique_id(out, len) bind(c, name='pmcgpu_comm_unique_id')
+       import :: c_int, c_char
+       character(kind=c_char), intent(out) :: out(*)
+       integer(c_int), value :: len
+     end function pmcgpu_comm_unique_id
+     integer(c_int) function pmcgpu_comm_init(ctx, unique_id, n_ranks, rank, px, py) &
+          bind(c, name='pmcgpu_comm_init')
+       import :: c_int, c_ptr, c_char
+       type(c_ptr), value :: ctx
+       character(kind=c_char), intent(in) :: unique_id(*)
+       integer(c_int), value :: n_ranks, rank, px, py
+     end function pmcgpu_comm_init
+  end interface
+
+contains
+
+  !> Map a library status to the reference's fatal-error path (util.F90:134 die_msg).
+  subroutine pmc_gpu_check(code, where)
+    use pmc_util, only: die_msg
+    integer(c_int), intent(in) :: code
+    character(len=*), intent(in) :: where
+    if (code /= 0) then
+       call die_msg(int(code), 'pmcgpu: ' // trim(where) // ' failed')
+    end if
+  end subroutine pmc_gpu_check
+
+  !> Create the device context of this rank's patch (called once from
+  !! partmc_init, interface/wrf_pmc_init.F90, after aero_data is read).
+  subroutine pmc_gpu_init(aero_data, n_class, n_part_ideal, pmc_is, pmc_ie, pmc_js, pmc_je, &
+       pmc_ks, pmc_ke, global_nx, global_ny, periodic_x, periodic_y, seed, local_rank)
+    use pmc_aero_data
+    type(aero_data_t), intent(in), target :: aero_data
+    integer, intent(in) :: n_class
+    real(kind=dp), intent(in) :: n_part_ideal
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    integer, intent(in) :: global_nx, global_ny
+    logical, intent(in) :: periodic_x, periodic_y
+    integer, intent(in) :: seed, local_rank
+
+    type(pmcgpu_config_t) :: cfg
+    real(c_double), allocatable, target :: density(:), kappa(:), molec_weight(:)
+    integer(c_int), allocatable, target :: num_ions(:)
+
+    density = aero_data%density
+    kappa = aero_data%kappa
+    molec_weight = aero_data%molec_weight
+    num_ions = aero_data%num_ions
+    cfg%n_spec = size(density)
+    cfg%density = c_loc(density)
+    cfg%kappa = c_loc(kappa)
+    cfg%molec_weight = c_loc(molec_weight)
+    cfg%num_ions = c_loc(num_ions)
+    cfg%i_water = aero_data%i_water
+    cfg%n_group = 1                      ! wrf_pmc_init.F90:251-254
+    cfg%n_class = n_class
+    cfg%nx = pmc_ie - pmc_is + 1
+    cfg%nz = pmc_ke - pmc_ks + 1
+    cfg%ny = pmc_je - pmc_js + 1
+    cfg%global_nx = global_nx
+    cfg%global_ny = global_ny
+    cfg%i_offset = pmc_is - 1
+    cfg%j_offset = pmc_js - 1
+    cfg%periodic_x = merge(1, 0, periodic_x)
+    cfg%periodic_y = merge(1, 0, periodic_y)
+    cfg%n_part_ideal = n_part_ideal
+    cfg%cell_capacity = int(2.5d0 * n_part_ideal) + 64
+    cfg%max_bins = 64
+    cfg%seed = seed
+    cfg%device = local_rank
+    call pmc_gpu_check(pmcgpu_create(cfg, pmc_gpu_handle), 'pmcgpu_create')
+  end subroutine pmc_gpu_init
+
+  subroutine pmc_gpu_finalize()
+    if (c_associated(pmc_gpu_handle)) then
+       call pmc_gpu_check(pmcgpu_destroy(pmc_gpu_handle), 'pmcgpu_destroy')
+       pmc_gpu_handle = c_null_ptr
+    end if
+  end subroutine pmc_gpu_finalize
+
+  !> aero_states(i,k,j) -> device SoA (after partmc_init and after a restart read).
+  subroutine pmc_gpu_upload_aero_states(aero_states, env_states, pmc_is, pmc_ie, pmc_js, &
+       pmc_je, pmc_ks, pmc_ke)
+    use pmc_aero_state
+    use pmc_env_state
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    type(aero_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), &
+         intent(in) :: aero_states
+    type(env_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), &
+         intent(in) :: env_states
+
+    integer :: i, j, k, c, p, n_cells, n_spec, n_class, n_tot, q, i_class
+    integer(c_int), allocatable, target :: counts(:), wgroup(:), wclass(:), nprim(:), hyst(:), wtype(:)
+    integer(c_int64_t), allocatable, target :: ids(:)
+    real(c_double), allocatable, target :: vol(:,:), lct(:), gct(:), wmag(:), wexp(:)
+    real(c_double), allocatable, target :: temp(:), pres(:), rh(:), alt(:), cvol(:)
+
+    n_cells = size(aero_states)
+    n_spec = 0
+    allocate(counts(n_cells))
+    c = 0
+    do j = pmc_js, pmc_je
+    do k = pmc_ks, pmc_ke
+    do i = pmc_is, pmc_ie
+       c = c + 1
+       counts(c) = aero_state_n_part(aero_states(i,k,j))
+       if (counts(c) > 0 .and. n_spec == 0) &
+            n_spec = size(aero_states(i,k,j)%apa%particle(1)%vol)
+    end do
+    end do
+    end do
+    n_tot = sum(counts)
+    n_class = size(aero_states(pmc_is,pmc_ks,pmc_js)%awa%weight, 2)
+    allocate(vol(n_tot, n_spec), wgroup(n_tot), wclass(n_tot), ids(n_tot), nprim(n_tot), &
+         hyst(n_tot), lct(n_tot), gct(n_tot))
+    allocate(wtype(n_cells * n_class), wmag(n_cells * n_class), wexp(n_cells * n_class))
+    allocate(temp(n_cells), pres(n_cells), rh(n_cells), alt(n_cells), cvol(n_cells))
+    c = 0
+    q = 0
+    do j = pmc_js, pmc_je
+    do k = pmc_ks, pmc_ke
+    do i = pmc_is, pmc_ie
+       c = c + 1
+       do p = 1, counts(c)
+          q = q + 1
+          vol(q, :) = aero_states(i,k,j)%apa%particle(p)%vol     ! species-major: vol(q, s)
+          wgroup(q) = aero_states(i,k,j)%apa%particle(p)%weight_group
+          wclass(q) = aero_states(i,k,j)%apa%particle(p)%weight_class
+          ids(q) = aero_states(i,k,j)%apa%particle(p)%id
+          nprim(q) = aero_states(i,k,j)%apa%particle(p)%n_primary_parts
+          hyst(q) = aero_states(i,k,j)%apa%particle(p)%water_hyst_leg
+          lct(q) = aero_states(i,k,j)%apa%particle(p)%least_create_time
+          gct(q) = aero_states(i,k,j)%apa%particle(p)%greatest_create_time
+       end do
+       do i_class = 1, n_class
+          wtype((c - 1) * n_class + i_class) = aero_states(i,k,j)%awa%weight(1, i_class)%type
+          wmag((c - 1) * n_class + i_class) = aero_states(i,k,j)%awa%weight(1, i_class)%magnitude
+          wexp((c - 1) * n_class + i_class) = aero_states(i,k,j)%awa%weight(1, i_class)%exponent
+       end do
+       temp(c) = env_states(i,k,j)%temp
+       pres(c) = env_states(i,k,j)%pressure
+       rh(c) = env_states(i,k,j)%rel_humid
+       alt(c) = env_states(i,k,j)%inverse_density
+       cvol(c) = env_states(i,k,j)%cell_volume
+    end do
+    end do
+    end do
+    call pmc_gpu_check(pmcgpu_set_particles(pmc_gpu_handle, c_loc(counts), c_loc(vol), &
+         c_loc(wgroup), c_loc(wclass), c_loc(ids), c_loc(nprim), c_loc(hyst), c_loc(lct), &
+         c_loc(gct)), 'pmcgpu_set_particles')
+    call pmc_gpu_check(pmcgpu_set_weights(pmc_gpu_handle, c_loc(wtype), c_loc(wmag), &
+         c_loc(wexp)), 'pmcgpu_set_weights')
+    call pmc_gpu_check(pmcgpu_set_env(pmc_gpu_handle, c_loc(temp), c_loc(pres), c_loc(rh), &
+         c_loc(alt), c_loc(cvol)), 'pmcgpu_set_env')
+  end subroutine pmc_gpu_upload_aero_states
