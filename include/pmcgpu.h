@@ -121,6 +121,13 @@ int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned
 int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_final, const double* pressure_final,
                               double del_t, double reltol, double* rel_humid_out, int* stats_out,
                               double* water_rel_error_out);
+/* time stepper of condense_particles: 4 (default) = RODAS4, a stiffly accurate L-stable Rosenbrock method;
+ * 5 = restatement of CVODE's variable-order BDF method, the solver the reference calls
+ * (condense_solver.c:131-166).  Both use the reference's tolerances and its exact arrow-head solve; they agree
+ * to the integration tolerance.  RODAS4 is the default because its few accept / reject decisions make the
+ * device reproduce the CPU restatement to 1e-10, whereas the many threshold decisions of a variable-order
+ * BDF code let two correct implementations drift apart to the tolerance level. */
+int pmcgpu_set_condense_method(pmcgpu_ctx* ctx, int method);
 /* condense_equilib_particles (condense.F90:744) with each cell's current env_state. */
 int pmcgpu_condense_equilib_particles(pmcgpu_ctx* ctx);
 /* evaluation of condense_rates (condense.F90:371) on the device, for known-answer tests:

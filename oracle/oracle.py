@@ -202,6 +202,10 @@ class Oracle:
     def condense_equilib(self, cell, step=0):
         self._chk(self.L.pmco_condense_equilib(self.h, C.c_int(cell), C.c_uint(step)))
 
+    def set_condense_method(self, method):
+        """5: CVODE-style BDF (default), 4: RODAS4, 3: RODAS3"""
+        self._chk(self.L.pmco_set_condense_method(self.h, C.c_int(method)))
+
     def condense_particles(self, cell, T1, p1, del_t, step=0, reltol=0.0, method=0):
         st = np.zeros(3, np.int32)
         wre = C.c_double(0)

@@ -211,9 +211,418 @@ static RosTableau tableau_rodas4() {
   return t;
 }
 
+// ------------------------------------------------------------------ BDF integrator (method 5)
+// Restatement of the algorithm the reference hands the system to: SUNDIALS CVODE with CV_BDF
+// (condense_solver.c:131-166).  SUNDIALS is not in the reference tree and its version is not pinned
+// upstream (condense_solver.c:96-155 compiles against major versions < 6 and >= 6 alike), so what is
+// restated is CVODE's published method (Cohen & Hindmarsh, "CVODE, a stiff/nonstiff ODE solver in C",
+// Computers in Physics 10 (1996); Hindmarsh et al., ACM TOMS 31 (2005), sect. 2.1): variable-order
+// (1..5), variable-step BDF in fixed-leading-coefficient Nordsieck form, with CVODE's local error test
+// (weighted RMS norm, weights 1 / (reltol |y_i| + abstol_i)), its step-size / order selection
+// heuristics and constants, and its initial step estimate.  The nonlinear system of every step is
+// solved by Newton iteration with CVODE's convergence test; each linear system (I - gamma J) x = r
+// is solved exactly by the Schur complement on H, which is what the reference's preconditioner
+// condense_jac_solve_f (condense.F90:625-695) does inside SPGMR (with an exact preconditioner the
+// Krylov iteration has nothing left to do).  J is evaluated at the predicted state of every step.
+// The answer at t_final is interpolated from the Nordsieck array like CVode(..., CV_NORMAL).
+namespace {
+struct BVec {
+  std::vector<double> d;
+  double H = 0.0;
+  explicit BVec(int n = 0) : d((size_t)n, 0.0) {}
+};
+struct Bdf {
+  static constexpr int QMAX = 5;
+  static constexpr double ADDON = 1e-6, BIAS1 = 6.0, BIAS2 = 6.0, BIAS3 = 10.0, ETAMX1 = 10000.0, ETAMX2 = 10.0,
+                          ETAMX3 = 10.0, ETAMXF = 0.2, ETAMIN = 0.1, ETACF = 0.25, THRESH = 1.5, CRDOWN = 0.3,
+                          RDIV = 2.0, CORTES = 0.1;
+  static constexpr int SMALL_NST = 10, MXNCF = 10, MXNEF = 7, MXNEF1 = 3, SMALL_NEF = 2, LONG_WAIT = 10, MAXCOR = 3;
+
+  const CondSys& sys;
+  const int n;
+  const double reltol, atolH;
+  const std::vector<double>& atol;
+  BVec zn[QMAX + 1], acor, ewt, y, f, tmp;
+  std::vector<double> ja, jb, jc, inv;
+  double jdd = 0.0, lhsH = 0.0;
+  int q = 1, L = 2, qprime = 1, qwait = 2, nst = 0, n_rates = 0, n_fail = 0;
+  double h = 0, hprime = 0, eta = 1, hscale = 0, tn = 0, etamax = ETAMX1, tau[QMAX + 2] = {0}, tq[6] = {0},
+         l[QMAX + 1] = {0}, rl1 = 1, gamma = 0, saved_tq5 = 0, acnrm = 0, crate = 1;
+
+  Bdf(const CondSys& s, double rt, double aH, const std::vector<double>& at)
+      : sys(s), n(s.n), reltol(rt), atolH(aH), atol(at), acor(s.n), ewt(s.n), y(s.n), f(s.n), tmp(s.n),
+        ja((size_t)s.n), jb((size_t)s.n), jc((size_t)s.n), inv((size_t)s.n) {
+    for (auto& z : zn) z = BVec(s.n);
+  }
+  double wrms(const BVec& v) const {
+    double s = 0.0;
+    for (int i = 0; i < n; i++) s += (v.d[i] * ewt.d[i]) * (v.d[i] * ewt.d[i]);
+    s += (v.H * ewt.H) * (v.H * ewt.H);
+    return std::sqrt(s / (double)(n + 1));
+  }
+  void set_ewt() {  // cvEwtSetSV
+    for (int i = 0; i < n; i++) ewt.d[i] = 1.0 / (reltol * std::fabs(zn[0].d[i]) + atol[i]);
+    ewt.H = 1.0 / (reltol * std::fabs(zn[0].H) + atolH);
+  }
+  void rhs(double t, const BVec& yy, BVec& out, bool jac) {
+    double dummy;
+    sys.eval(t, yy.d.data(), yy.H, out.d.data(), out.H, jac ? ja.data() : nullptr, jac ? jb.data() : nullptr,
+             jac ? jc.data() : nullptr, jac ? jdd : dummy, n_rates, jac);
+  }
+  // ---- cvHin: initial step from ||y''|| (cvode.c cvHin / cvUpperBoundH0 / cvYddNorm)
+  double ydd_norm(double hg) {
+    for (int i = 0; i < n; i++) y.d[i] = hg * zn[1].d[i] + zn[0].d[i];
+    y.H = hg * zn[1].H + zn[0].H;
+    rhs(tn + hg, y, tmp, false);
+    for (int i = 0; i < n; i++) tmp.d[i] = (tmp.d[i] - zn[1].d[i]) / hg;
+    tmp.H = (tmp.H - zn[1].H) / hg;
+    return wrms(tmp);
+  }
+  double hin(double t0, double tout) {
+    const double uround = 2.220446049250313e-16;
+    const double tdist = std::fabs(tout - t0);
+    const double hlb = 100.0 * uround * std::max(std::fabs(t0), std::fabs(tout));
+    double hub_inv = 0.0;  // cvUpperBoundH0
+    for (int i = 0; i < n; i++)
+      hub_inv = std::max(hub_inv, std::fabs(zn[1].d[i]) / (0.1 * std::fabs(zn[0].d[i]) + 1.0 / ewt.d[i]));
+    hub_inv = std::max(hub_inv, std::fabs(zn[1].H) / (0.1 * std::fabs(zn[0].H) + 1.0 / ewt.H));
+    double hub = 0.1 * tdist;
+    if (hub * hub_inv > 1.0) hub = 1.0 / hub_inv;
+    double hg = std::sqrt(hlb * hub), hnew = hg;
+    if (hub < hlb) return hg;
+    for (int count = 1; count <= 4; count++) {
+      const double yddnrm = ydd_norm(hg);
+      hnew = (yddnrm * hub * hub > 2.0) ? std::sqrt(2.0 / yddnrm) : std::sqrt(hg * hub);
+      if (count == 4) break;
+      const double hrat = hnew / hg;
+      if (hrat > 0.5 && hrat < 2.0) break;
+      if (count > 1 && hrat > 2.0) {
+        hnew = hg;
+        break;
+      }
+      hg = hnew;
+    }
+    return std::min(hub, std::max(hlb, 0.5 * hnew));
+  }
+  // ---- Nordsieck array manipulation
+  void rescale() {  // cvRescale
+    double factor = eta;
+    for (int j = 1; j <= q; j++) {
+      for (int i = 0; i < n; i++) zn[j].d[i] *= factor;
+      zn[j].H *= factor;
+      factor *= eta;
+    }
+    h = hscale * eta;
+    hscale = h;
+  }
+  void axpy(double a, const BVec& x, BVec& yv) {
+    for (int i = 0; i < n; i++) yv.d[i] += a * x.d[i];
+    yv.H += a * x.H;
+  }
+  void increase_order() {  // cvIncreaseBDF
+    for (int i = 0; i <= QMAX; i++) l[i] = 0.0;
+    l[2] = 1.0;
+    double alpha1 = 1.0, prod = 1.0, xiold = 1.0, alpha0 = -1.0, hsum = hscale;
+    if (q > 1) {
+      for (int j = 1; j < q; j++) {
+        hsum += tau[j + 1];
+        const double xi = hsum / hscale;
+        prod *= xi;
+        alpha0 -= 1.0 / (j + 1);
+        alpha1 += 1.0 / xi;
+        for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xiold + l[i - 1];
+        xiold = xi;
+      }
+    }
+    const double A1 = (-alpha0 - alpha1) / prod;
+    for (int i = 0; i < n; i++) zn[L].d[i] = A1 * zn[QMAX].d[i];
+    zn[L].H = A1 * zn[QMAX].H;
+    for (int j = 2; j <= q; j++) axpy(l[j], zn[L], zn[j]);
+  }
+  void decrease_order() {  // cvDecreaseBDF
+    for (int i = 0; i <= QMAX; i++) l[i] = 0.0;
+    l[2] = 1.0;
+    double hsum = 0.0;
+    for (int j = 1; j <= q - 2; j++) {
+      hsum += tau[j];
+      const double xi = hsum / hscale;
+      for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xi + l[i - 1];
+    }
+    for (int j = 2; j < q; j++) axpy(-l[j], zn[q], zn[j]);
+  }
+  void adjust_params() {  // cvAdjustParams
+    if (qprime != q) {
+      if (qprime > q) increase_order(); else decrease_order();
+      q = qprime;
+      L = q + 1;
+      qwait = L;
+    }
+    rescale();
+  }
+  void predict() {  // cvPredict
+    tn += h;
+    for (int k = 1; k <= q; k++)
+      for (int j = q; j >= k; j--) axpy(1.0, zn[j], zn[j - 1]);
+  }
+  void restore(double saved_t) {  // cvRestore
+    tn = saved_t;
+    for (int k = 1; k <= q; k++)
+      for (int j = q; j >= k; j--) axpy(-1.0, zn[j], zn[j - 1]);
+  }
+  void set_coeffs() {  // cvSetBDF + cvSetTqBDF
+    l[0] = l[1] = 1.0;
+    double xi_inv = 1.0, xistar_inv = 1.0;
+    for (int i = 2; i <= q; i++) l[i] = 0.0;
+    double alpha0 = -1.0, alpha0_hat = -1.0, hsum = h;
+    if (q > 1) {
+      for (int j = 2; j < q; j++) {
+        hsum += tau[j - 1];
+        xi_inv = h / hsum;
+        alpha0 -= 1.0 / j;
+        for (int i = j; i >= 1; i--) l[i] += l[i - 1] * xi_inv;
+      }
+      alpha0 -= 1.0 / q;
+      xistar_inv = -l[1] - alpha0;
+      hsum += tau[q - 1];
+      xi_inv = h / hsum;
+      alpha0_hat = -l[1] - xi_inv;
+      for (int i = q; i >= 1; i--) l[i] += l[i - 1] * xistar_inv;
+    }
+    const double A1 = 1.0 - alpha0_hat + alpha0, A2 = 1.0 + q * A1;
+    tq[2] = std::fabs(A1 / (alpha0 * A2));
+    tq[5] = std::fabs(A2 * xistar_inv / (l[q] * xi_inv));
+    if (qwait == 1) {
+      if (q > 1) {
+        const double C = xistar_inv / l[q], A3 = alpha0 + 1.0 / q, A4 = alpha0_hat + xi_inv;
+        const double Cpinv = (1.0 - A4 + A3) / A3;
+        tq[1] = std::fabs(C * Cpinv);
+      } else {
+        tq[1] = 1.0;
+      }
+      hsum += tau[q];
+      xi_inv = h / hsum;
+      const double A5 = alpha0 - 1.0 / (q + 1), A6 = alpha0_hat - xi_inv;
+      const double Cppinv = (1.0 - A6 + A5) / A2;
+      tq[3] = std::fabs(Cppinv / (xi_inv * (q + 2) * A5));
+    }
+    tq[4] = CORTES / tq[2];
+    rl1 = 1.0 / l[1];
+    gamma = h * rl1;
+  }
+  // ---- Newton iteration of one step (cvNls with the exact arrow-head solve)
+  void solve(BVec& b) {  // (I - gamma J) x = b, x overwrites b (condense.F90:665-680)
+    double rhs_n = b.H;
+    for (int i = 0; i < n; i++) rhs_n += gamma * jc[i] * b.d[i] * inv[i];
+    b.H = rhs_n / lhsH;
+    for (int i = 0; i < n; i++) b.d[i] = (b.d[i] + gamma * jb[i] * b.H) * inv[i];
+  }
+  bool nls() {
+    crate = 1.0;
+    for (int i = 0; i < n; i++) { y.d[i] = zn[0].d[i]; acor.d[i] = 0.0; }
+    y.H = zn[0].H;
+    acor.H = 0.0;
+    rhs(tn, y, f, true);
+    lhsH = 1.0 - gamma * jdd;
+    for (int i = 0; i < n; i++) {
+      inv[i] = 1.0 / (1.0 - gamma * ja[i]);
+      lhsH -= (gamma * jb[i]) * (gamma * jc[i]) * inv[i];
+    }
+    double delp = 0.0;
+    for (int m = 0;;) {
+      for (int i = 0; i < n; i++) tmp.d[i] = gamma * f.d[i] - (rl1 * zn[1].d[i] + acor.d[i]);
+      tmp.H = gamma * f.H - (rl1 * zn[1].H + acor.H);
+      solve(tmp);
+      const double del = wrms(tmp);
+      if (!std::isfinite(del)) return false;
+      axpy(1.0, tmp, acor);
+      for (int i = 0; i < n; i++) y.d[i] = zn[0].d[i] + acor.d[i];
+      y.H = zn[0].H + acor.H;
+      if (m > 0) crate = std::max(CRDOWN * crate, del / delp);
+      const double dcon = del * std::min(1.0, crate) / tq[4];
+      if (dcon <= 1.0) {
+        acnrm = (m == 0) ? del : wrms(acor);
+        return true;
+      }
+      m++;
+      if (m == MAXCOR || (m >= 2 && del > RDIV * delp)) return false;
+      delp = del;
+      rhs(tn, y, f, false);
+    }
+  }
+  void complete_step() {  // cvCompleteStep
+    nst++;
+    for (int i = q; i >= 2; i--) tau[i] = tau[i - 1];
+    if (q == 1 && nst > 1) tau[2] = tau[1];
+    tau[1] = h;
+    for (int j = 0; j <= q; j++) axpy(l[j], acor, zn[j]);
+    qwait--;
+    if (qwait == 1 && q != QMAX) {
+      zn[QMAX] = acor;
+      saved_tq5 = tq[5];
+    }
+  }
+  void set_eta() {  // cvSetEta (no hmax)
+    if (eta < THRESH) {
+      eta = 1.0;
+      hprime = h;
+    } else {
+      eta = std::min(eta, etamax);
+      hprime = h * eta;
+    }
+  }
+  void prepare_next_step(double dsm) {  // cvPrepareNextStep, cvComputeEtaqm1/qp1, cvChooseEta
+    if (etamax == 1.0) {
+      qwait = std::max(qwait, 2);
+      qprime = q;
+      hprime = h;
+      eta = 1.0;
+      return;
+    }
+    const double etaq = 1.0 / (std::pow(BIAS2 * dsm, 1.0 / L) + ADDON);
+    if (qwait != 0) {
+      eta = etaq;
+      qprime = q;
+      set_eta();
+      return;
+    }
+    qwait = 2;
+    double etaqm1 = 0.0, etaqp1 = 0.0;
+    if (q > 1) {
+      const double ddn = wrms(zn[q]) * tq[1];
+      etaqm1 = 1.0 / (std::pow(BIAS1 * ddn, 1.0 / q) + ADDON);
+    }
+    if (q != QMAX && saved_tq5 != 0.0) {
+      const double cquot = (tq[5] / saved_tq5) * std::pow(h / tau[2], (double)L);
+      for (int i = 0; i < n; i++) tmp.d[i] = acor.d[i] - cquot * zn[QMAX].d[i];
+      tmp.H = acor.H - cquot * zn[QMAX].H;
+      const double dup = wrms(tmp) * tq[3];
+      etaqp1 = 1.0 / (std::pow(BIAS3 * dup, 1.0 / (L + 1)) + ADDON);
+    }
+    const double etam = std::max(etaqm1, std::max(etaq, etaqp1));
+    if (etam < THRESH) {
+      eta = 1.0;
+      qprime = q;
+    } else if (etam == etaq) {
+      eta = etaq;
+      qprime = q;
+    } else if (etam == etaqm1) {
+      eta = etaqm1;
+      qprime = q - 1;
+    } else {
+      eta = etaqp1;
+      qprime = q + 1;
+      zn[QMAX] = acor;
+    }
+    set_eta();
+  }
+  // one internal step (cvStep); 0 = ok, 7 = repeated convergence / error test failures
+  int step() {
+    const double saved_t = tn;
+    int ncf = 0, nef = 0;
+    if (nst > 0 && hprime != h) adjust_params();
+    double dsm = 0.0;
+    for (;;) {
+      predict();
+      set_coeffs();
+      if (!nls()) {  // cvHandleNFlag
+        ncf++;
+        n_fail++;
+        etamax = 1.0;
+        if (ncf == MXNCF || !(std::fabs(h) > 1e-300)) return 7;
+        eta = ETACF;
+        restore(saved_t);
+        rescale();
+        continue;
+      }
+      dsm = acnrm * tq[2];  // cvDoErrorTest
+      if (dsm <= 1.0) break;
+      nef++;
+      n_fail++;
+      restore(saved_t);
+      if (nef == MXNEF) return 7;
+      etamax = 1.0;
+      if (nef <= MXNEF1) {
+        eta = 1.0 / (std::pow(BIAS2 * dsm, 1.0 / L) + ADDON);
+        eta = std::max(ETAMIN, eta);
+        if (nef >= SMALL_NEF) eta = std::min(eta, ETAMXF);
+        rescale();
+        continue;
+      }
+      eta = ETAMIN;
+      if (q > 1) {
+        decrease_order();
+        L = q;
+        q--;
+        qwait = L;
+        rescale();
+        continue;
+      }
+      h *= eta;
+      hscale = h;
+      qwait = LONG_WAIT;
+      rhs(tn, zn[0], tmp, false);
+      for (int i = 0; i < n; i++) zn[1].d[i] = h * tmp.d[i];
+      zn[1].H = h * tmp.H;
+    }
+    complete_step();
+    prepare_next_step(dsm);
+    etamax = (nst <= SMALL_NST) ? ETAMX2 : ETAMX3;
+    for (int i = 0; i < n; i++) acor.d[i] *= tq[2];
+    acor.H *= tq[2];
+    return 0;
+  }
+};
+}  // namespace
+
+static int condense_integrate_bdf(int n, double* D, double* Hio, const double* D_dry, const double* kappa,
+                                  const double* num_conc, double T0, double p0, double Tdot, double pdot,
+                                  double del_t, const CondenseOpts& opt, CondenseStats& stats) {
+  CondSys sys{n, D_dry, kappa, num_conc, T0, p0, Tdot, pdot};
+  std::vector<double> atol((size_t)n);
+  for (int i = 0; i < n; i++) atol[i] = std::max(1e-30, opt.abstol_scale * (D[i] - D_dry[i]));
+  Bdf s(sys, opt.reltol, opt.abstol_H, atol);
+  for (int i = 0; i < n; i++) s.zn[0].d[i] = D[i];
+  s.zn[0].H = *Hio;
+  s.tn = 0.0;
+  s.set_ewt();
+  s.rhs(0.0, s.zn[0], s.zn[1], false);
+  s.h = s.hin(0.0, del_t);
+  s.hscale = s.h;
+  s.hprime = s.h;
+  for (int i = 0; i < n; i++) s.zn[1].d[i] *= s.h;
+  s.zn[1].H *= s.h;
+  stats.n_steps = stats.n_reject = stats.n_rates = 0;
+  int rc = 0;
+  for (;;) {  // CVode(..., CV_NORMAL)
+    if (s.nst > 0) s.set_ewt();
+    if (s.nst >= opt.max_steps) { rc = 6; break; }
+    rc = s.step();
+    if (rc) break;
+    if (s.tn - del_t >= 0.0) break;
+  }
+  stats.n_steps = s.nst;
+  stats.n_reject = s.n_fail;
+  stats.n_rates = s.n_rates;
+  stats.h_last = s.h;
+  if (rc) return rc;
+  // CVodeGetDky(t_final, 0): y = sum_j zn[j] s^j, s = (t_final - tn) / h
+  const double sfac = (del_t - s.tn) / s.h;
+  for (int i = 0; i < n; i++) {
+    double v = s.zn[s.q].d[i];
+    for (int j = s.q - 1; j >= 0; j--) v = v * sfac + s.zn[j].d[i];
+    D[i] = v;
+  }
+  double v = s.zn[s.q].H;
+  for (int j = s.q - 1; j >= 0; j--) v = v * sfac + s.zn[j].H;
+  *Hio = v;
+  return 0;
+}
+
 int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const double* kappa,
                        const double* num_conc, double T0, double p0, double Tdot, double pdot, double del_t,
                        const CondenseOpts& opt, CondenseStats& stats) {
+  if (opt.method == 5)
+    return condense_integrate_bdf(n, D, Hio, D_dry, kappa, num_conc, T0, p0, Tdot, pdot, del_t, opt, stats);
   const RosTableau tb = (opt.method == 4) ? tableau_rodas4() : tableau_rodas3();
   const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.9, FAC_REJ = 0.1;
   const double DT_FD = 1e-2;  // forward difference in t for df/dt (T and p are linear in t)
@@ -226,23 +635,51 @@ int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const
   for (int i = 0; i < n; i++) atol[i] = std::max(1e-30, opt.abstol_scale * (D[i] - D_dry[i]));
   double H = *Hio;
   double t = 0.0;
-  double h = (opt.h_init > 0.0) ? std::min(opt.h_init, del_t) : del_t;
-  double h_natural = h;  // last step size chosen by the controller (not by hitting the end of the interval)
   stats.n_steps = stats.n_reject = stats.n_rates = 0;
+  double h = (opt.h_init > 0.0) ? std::min(opt.h_init, del_t) : del_t;  // else: estimated before the first step
+  double h_natural = h;  // last step size chosen by the controller (not by hitting the end of the interval)
   bool reject_last = false, reject_more = false;
   while (t < del_t) {
     if (stats.n_steps + stats.n_reject >= opt.max_steps) return 6;  // PMC_CONDENSE_SOLVER_SET_MAX_STEPS-like
+    double f0H, ftH, dd, dummy;
+    sys.eval(t, D, H, f0.data(), f0H, a.data(), b.data(), c.data(), dd, stats.n_rates, true);
+    sys.eval(t + DT_FD, D, H, ft.data(), ftH, nullptr, nullptr, nullptr, dummy, stats.n_rates, false);
+    for (int i = 0; i < n; i++) dfdt[i] = (ft[i] - f0[i]) / DT_FD;
+    const double dfdtH = (ftH - f0H) / DT_FD;
+    if (stats.n_steps + stats.n_reject == 0 && !(opt.h_init > 0.0)) {
+      // first step size, after cvHin (cvode.c): h = 1/2 sqrt(2 / ||y''||), bounded by hub, times 4 for a
+      // 4th-order method; y'' = J f + df/dt from the Jacobian of this step (no differencing noise)
+      double s1 = 0.0, hub_inv = 0.0, sq = 0.0;
+      for (int i = 0; i < n; i++) {
+        const double ew = 1.0 / (opt.reltol * std::fabs(D[i]) + atol[i]);
+        s1 += c[i] * f0[i];
+        hub_inv = std::max(hub_inv, std::fabs(f0[i]) / (0.1 * std::fabs(D[i]) + 1.0 / ew));
+        const double w = (a[i] * f0[i] + b[i] * f0H + dfdt[i]) * ew;
+        sq += w * w;
+      }
+      const double ewH = 1.0 / (opt.reltol * std::fabs(H) + opt.abstol_H);
+      const double yddH = s1 + dd * f0H + dfdtH;
+      hub_inv = std::max(hub_inv, std::fabs(f0H) / (0.1 * std::fabs(H) + 1.0 / ewH));
+      const double yddnrm = std::sqrt((sq + (yddH * ewH) * (yddH * ewH)) / (double)(n + 1));
+      double hub = 0.1 * del_t;
+      if (hub * hub_inv > 1.0) hub = 1.0 / hub_inv;
+      const double hnew = (yddnrm * hub * hub > 2.0) ? std::sqrt(2.0 / yddnrm) : hub;
+      // rounded down to a power of two, which does not carry the rounding noise of the estimate
+      h = 4.0 * 0.5 * hnew;
+      {
+        int ex;
+        std::frexp(h, &ex);
+        h = std::ldexp(0.5, ex);
+      }
+      h = std::min(del_t, h);
+      h_natural = h;
+    }
     bool truncated = false;
     if (t + h > del_t * (1.0 - 1e-14)) {
       h_natural = h;
       h = del_t - t;
       truncated = true;
     }
-    double f0H, ftH, dd, dummy;
-    sys.eval(t, D, H, f0.data(), f0H, a.data(), b.data(), c.data(), dd, stats.n_rates, true);
-    sys.eval(t + DT_FD, D, H, ft.data(), ftH, nullptr, nullptr, nullptr, dummy, stats.n_rates, false);
-    for (int i = 0; i < n; i++) dfdt[i] = (ft[i] - f0[i]) / DT_FD;
-    const double dfdtH = (ftH - f0H) / DT_FD;
     for (;;) {
       const double eps = 1.0 / (tb.gamma * h);
       double sden = 0.0;
@@ -299,6 +736,7 @@ int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const
       double err = std::sqrt(esum / (double)(n + 1));
       if (!std::isfinite(err)) err = 1e10;
       err = std::max(err, 1e-10);
+      if (getenv("PMCO_DEBUG")) fprintf(stderr, "cpu t %.17g h %.17g err %.17g\n", t, h, err);
       const double fac = std::min(FAC_MAX, std::max(FAC_MIN, FAC_SAFE / std::pow(err, 1.0 / tb.elo)));
       double hnew = h * fac;
       if (err <= 1.0) {

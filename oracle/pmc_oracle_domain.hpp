@@ -16,6 +16,7 @@ struct OracleDomain {
   std::unique_ptr<Rng> rng;
   std::vector<int64_t> global_cell;  // global cell index of each local cell (rng address + id rank)
   std::string last_error;
+  int cond_method = 0;  // 0: CondenseOpts default; set by pmco_set_condense_method
   std::vector<double> cond_h;  // per cell: step size carried between condense calls (0 = none yet)
   TransDomain trans;  // transport geometry + met + probabilities (pmc_oracle_ext.hpp)
 };

@@ -31,7 +31,7 @@ struct CondenseOpts {
   double abstol_H = 1e-10;
   int max_steps = 100000;
   double h_init = 0.0;  // 0: start with the whole interval
-  int method = 4;       // 3: RODAS3, 4: RODAS4 (what the device runs)
+  int method = 4;       // 4: RODAS4 (what the device runs by default), 5: CVODE-style BDF, 3: RODAS3
 };
 struct CondenseStats {
   int n_steps = 0, n_reject = 0, n_rates = 0;

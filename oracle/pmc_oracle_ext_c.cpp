@@ -49,6 +49,10 @@ int pmco_condense_equilib(void* h, int cell, unsigned step) {
 // condense_particles (condense.F90:147-325): env_state_initial = the cell's env, final = (T1, p1);
 // on return the cell's env is the final one with rel_humid from the integrator.
 // stats_out: n_steps, n_reject, n_rates ; water_rel_error returned through *wre
+int pmco_set_condense_method(void* h, int method) {
+  ((OracleDomain*)h)->cond_method = method;
+  return 0;
+}
 int pmco_condense_particles(void* h, int cell, double T1, double p1, double del_t, unsigned step, double reltol,
                             int method, int* stats_out, double* wre) {
   OracleDomain* d = (OracleDomain*)h;
@@ -60,9 +64,9 @@ int pmco_condense_particles(void* h, int cell, double T1, double p1, double del_
   e1.pressure = p1;
   CondenseOpts opt;
   if (reltol > 0) opt.reltol = reltol;
+  if (d->cond_method > 0) opt.method = d->cond_method;
   if (method > 0) opt.method = method;
   if (d->cond_h.size() != d->cells.size()) d->cond_h.assign(d->cells.size(), 0.0);
-  opt.h_init = d->cond_h[cell];
   CondenseStats st;
   condense_particles(d->cells[cell], d->data, e0, e1, del_t, rc, opt, st);
   d->cond_h[cell] = st.h_last;
@@ -131,7 +135,7 @@ int pmco_partmc_timestep(void* h, int cell_lo, int cell_hi, const double* T, con
           e0.rel_humid = env.rel_humid;
           EnvState e1 = env;
           CondenseOpts opt;
-          opt.h_init = d->cond_h[c];
+          if (d->cond_method > 0) opt.method = d->cond_method;
           CondenseStats cst;
           condense_particles(st, d->data, e0, e1, chem_dt, rc, opt, cst);
           d->cond_h[c] = cst.h_last;

@@ -136,6 +136,7 @@ __device__ __forceinline__ void block_sum(double* x, double* s_red /*[NV][COND_T
 struct CondParams {
   double del_t, reltol, abstol_scale, abstol_H;
   int max_steps;
+  int debug_cell;  // -1: off; else the cell whose step sequence thread 0 prints (PMCGPU_DEBUG_CELL)
 };
 
 // RODAS4 (Hairer & Wanner, Solving ODEs II, sect. IV.7): 6 stages, order 4(3), stiffly
@@ -196,6 +197,61 @@ __device__ __forceinline__ double fast_exp(double x) {
   return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
 }
 
+// deterministic block reduction of NV values (sum or max) with one barrier: the per-warp partials go to
+// one of two alternating buffers, so the next reduction cannot overwrite values still being read
+template <int NV, int NT, bool IS_MAX>
+__device__ __forceinline__ void block_red(double (&x)[NV], double* s_red /*[2][4][NT/32]*/, int& par) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double* buf = s_red + par * (4 * (NT / 32));
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double t = x[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double u = __shfl_down_sync(0xffffffffu, t, o);
+      t = IS_MAX ? fmax(t, u) : t + u;
+    }
+    if (lane == 0) buf[k * (NT / 32) + warp] = t;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double t = buf[k * (NT / 32)];
+#pragma unroll
+    for (int w = 1; w < NT / 32; w++) t = IS_MAX ? fmax(t, buf[k * (NT / 32) + w]) : t + buf[k * (NT / 32) + w];
+    x[k] = t;
+  }
+  par ^= 1;
+}
+
+// cond_env with the branch-free primitives (same terms, condense.F90:391-416)
+__device__ __forceinline__ CondEnv cond_env_fast(double T0, double p0, double Tdot, double pdot, double t) {
+  CondEnv e;
+  e.T = T0 + t * Tdot;
+  e.p = p0 + t * pdot;
+  e.Tdot = Tdot;
+  e.pdot = pdot;
+  const double R = PmcConst::univ_gas_const, rho_w = PmcConst::water_density, M_w = PmcConst::water_molec_weight;
+  const double LN10 = 2.302585092994045684;
+  const double invT = fast_rcp(e.T), invp = fast_rcp(e.p), invT38 = fast_rcp(e.T - 38.0);
+  const double P_0 = PmcConst::water_eq_vap_press * fast_exp(LN10 * 7.45 * (e.T - PmcConst::water_freeze_temp) * invT38);
+  e.dP0_dT_div_P0 = 7.45 * LN10 * (PmcConst::water_freeze_temp - 38.0) * (invT38 * invT38);
+  const double inv_rho_air = R * e.T * invp / PmcConst::air_molec_weight;
+  e.k_a = 1e-3 * (4.39 + 0.071 * e.T);
+  e.D_v = 0.211e-4 * PmcConst::air_std_press * invp * fast_exp(1.94 * log(e.T / 273.0));
+  e.U = PmcConst::water_latent_heat * rho_w * 0.25 * invT;
+  e.V = 4.0 * M_w * P_0 * invT / (rho_w * R);
+  e.W = PmcConst::water_latent_heat * M_w * invT / R;
+  e.X = 4.0 * M_w * PmcConst::water_surf_eng * invT / (R * rho_w);
+  const double rsT = sqrt(invT);
+  e.Y = 2.0 * e.k_a * inv_rho_air / (PmcConst::accom_coeff * PmcConst::air_spec_heat) *
+        (sqrt(2.0 * PmcConst::pi * PmcConst::air_molec_weight / R) * rsT);
+  e.Z = 2.0 * e.D_v / PmcConst::accom_coeff * (sqrt(2.0 * PmcConst::pi * M_w / R) * rsT);
+  e.UV = e.U * e.V;
+  e.vc = (e.T * p0) * invp / T0;
+  return e;
+}
+
 // condense_rates (condense.F90:371-502) for PPT particles of one thread at once.  The PPT
 // evaluations are independent dependency chains that the unrolled inner loops interleave, which is
 // what keeps the FP64 pipe busy with few warps per SM.  Per particle one reciprocal yields
@@ -209,7 +265,7 @@ __device__ __forceinline__ double fast_exp(double x) {
 // then below 1e-16 |u|), after at most five evaluations like the reference.
 // Per-particle constants (D_dry, kappa, num_conc) are read from shared memory (stride COND_THREADS).
 // WITH_JAC also returns a = dDdot/dD, b = dDdot/dH, c = dHdot_i/dD, dH = dHdot_i/dH.
-template <int PPT, bool WITH_JAC>
+template <int PPT, bool WITH_JAC, int NT = COND_THREADS>
 __device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const double (&D)[PPT],
                                                const double* __restrict__ sDdry, const double* __restrict__ sKap,
                                                const double* __restrict__ sNc, double (&Ddot)[PPT],
@@ -222,7 +278,7 @@ __device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const
   double u[PPT], A[PPT], kB[PPT], cW[PPT];
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
-    const double d = D[k], dd = sDdry[k * COND_THREADS], kp = sKap[k * COND_THREADS];
+    const double d = D[k], dd = sDdry[k * NT], kp = sKap[k * NT];
     const double D3 = d * d * d, Dd3 = dd * dd * dd;
     const double dY = d + e.Y, dZ = d + e.Z, den = fma(kp - 1.0, Dd3, D3);
     const double pYZ = dY * dZ, pDn = d * den;
@@ -260,14 +316,14 @@ __device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
     const double d = D[k];
-    const double hf = g * sNc[k * COND_THREADS];
+    const double hf = g * sNc[k * NT];
     const double kU = k_ap[k] * invD[k] * invU;  // k_ap / (U D)
     const double q = 1.0 - u[k];                 // 1 / (1 + delta*)
     const double delta = u[k] * fast_rcp(q);
     Ddot[k] = kU * delta;
     Hd[k] = hf * (d * d) * Ddot[k];
     if (WITH_JAC) {
-      const double dd = sDdry[k * COND_THREADS], kp = sKap[k * COND_THREADS];
+      const double dd = sDdry[k * NT], kp = sKap[k * NT];
       const double Dd3 = dd * dd * dd;
       const double ex = fast_exp(fma(cW[k], u[k], XD[k]));  // exp((W delta + X/D) / (1 + delta))
       const double dhd = k_ap[k] - A[k] * (q * q) * (1.0 - e.W * q + XD[k] * q) * ex;  // dh/ddelta (:462)
@@ -289,9 +345,9 @@ __device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const
   // dry particles (D <= D_dry, condense.F90:418-436): rare, handled one by one
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
-    const double dd = sDdry[k * COND_THREADS];
+    const double dd = sDdry[k * NT];
     if (D[k] <= dd) {
-      const double hf = g * sNc[k * COND_THREADS];
+      const double hf = g * sNc[k * NT];
       const double kd = e.k_a / (1.0 + e.Y / dd);
       const double Dvd = e.D_v / (1.0 + e.Z / dd);
       const double delta_star = e.UV * Dvd * H / kd;
@@ -307,31 +363,33 @@ __device__ __forceinline__ void cond_rates_vec(const CondEnv& e, double H, const
   }
 }
 
-#define COND_NARR (ROS_S + 5)  // shared arrays per particle: 6 stage vectors, abstol, solute volume, D_dry, kappa, num_conc
+#define COND_NARR (ROS_S + 4)  // shared arrays per particle: 6 stage vectors, abstol, D_dry, kappa, num_conc
+#define ROS_NENV 7             // (T, p) terms of one step: t, t + DT_FD, t + alpha_i h (i = 2..6)
+#define ROS_HIN_FACTOR 4.0     // first step = 4 x CVODE's first-order estimate (a 4th-order method), rounded down to 2^k
 template <int PPT>
 __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const double* T0a /* may alias v.temp */,
                                                            const double* p0a,
                                                            const double* T1 /* may alias v.temp */,
                                                            const double* p1, CondParams prm,
-                                                           double* __restrict__ h_state, int* __restrict__ stats,
-                                                           double* __restrict__ wre_out,
-                                                           const int* __restrict__ cell_list, int n_limit_lo,
-                                                           int n_limit_hi) {
-  const int cell = cell_list ? cell_list[blockIdx.x] : blockIdx.x;
+                                                           int* __restrict__ stats, double* __restrict__ wre_out,
+                                                           int n_limit_lo, int n_limit_hi) {
+  constexpr int NT = COND_THREADS;
+  const int cell = blockIdx.x;
   const int n = v.count[cell];
   if (n <= n_limit_lo || n > n_limit_hi) return;  // another instantiation owns this cell
   if (v.status[cell] != 0) return;
   const int tid = threadIdx.x;
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
-  __shared__ double s_red[3 * (COND_THREADS / 32)];
-  extern __shared__ double s_K[];  // [COND_NARR][PPT][COND_THREADS]
-#define SK(st, k) s_K[((st) * PPT + (k)) * COND_THREADS + tid]
+  __shared__ double s_red[2 * 4 * (NT / 32)];
+  __shared__ CondEnv s_env[ROS_NENV];
+  extern __shared__ double s_K[];  // [COND_NARR][PPT][NT]
+#define SK(st, k) s_K[((st) * PPT + (k)) * NT + tid]
 #define S_ATOL(k) SK(ROS_S, k)
-#define S_SOLV(k) SK(ROS_S + 1, k)
-  const double* sDdry = &SK(ROS_S + 2, 0);
-  const double* sKap = &SK(ROS_S + 3, 0);
-  const double* sNc = &SK(ROS_S + 4, 0);
+  const double* sDdry = &SK(ROS_S + 1, 0);
+  const double* sKap = &SK(ROS_S + 2, 0);
+  const double* sNc = &SK(ROS_S + 3, 0);
+  int par = 0;
   // aero_state_reweight (aero_state.F90:597-653) after the solve is the identity for flat
   // weights (ratio 1, prob_round(1) = 1); size-dependent weights need the duplicate / remove
   // pass, which is not built yet: say so instead of skipping it silently.
@@ -342,8 +400,10 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
     }
   const int iw = v.i_water - 1;
   const double T0 = T0a[cell], p0 = p0a[cell];  // env_state_initial
-  const double Tdot = (T1[cell] - T0) / prm.del_t, pdot = (p1[cell] - p0) / prm.del_t;
-  double H = v.rh[cell];
+  const double del_t = prm.del_t;
+  const double Tdot = (T1[cell] - T0) / del_t, pdot = (p1[cell] - p0) / del_t;
+  const double H0 = v.rh[cell];
+  double H = H0;
 
   // ---- set-up (condense.F90:196-237): kappa, D_dry, num_conc, D, abstol per particle.
   // Slots past the population hold a harmless wet dummy particle that never enters a sum.
@@ -351,13 +411,12 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
   double wsum = 0.0;
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
-    const int p = tid + k * COND_THREADS;
+    const int p = tid + k * NT;
     D[k] = 2.0;
     S_ATOL(k) = 1.0;
-    S_SOLV(k) = 0.0;
-    SK(ROS_S + 2, k) = 1.0;
-    SK(ROS_S + 3, k) = 0.5;
-    SK(ROS_S + 4, k) = 1.0;
+    SK(ROS_S + 1, k) = 1.0;
+    SK(ROS_S + 2, k) = 0.5;
+    SK(ROS_S + 3, k) = 1.0;
     if (p < n) {
       // aero_particle_solute_kappa (aero_particle.F90:724-755), solute volume, total volume
       double vt = 0.0, vs = 0.0, ks = 0.0;
@@ -367,11 +426,7 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
         vt += x;
         if (s != iw) {
           vs += x;
-          double kp;
-          if (v.nions[s] > 0)
-            kp = M_w * v.density[s] / (v.molw[s] * rho_w) * (double)v.nions[s];
-          else
-            kp = v.kappa[s];
+          const double kp = (v.nions[s] > 0) ? M_w * v.density[s] / (v.molw[s] * rho_w) * (double)v.nions[s] : v.kappa[s];
           ks += x * kp;
         }
       }
@@ -379,10 +434,9 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       const double r = vol2rad(vt);
       const double ddry = 2.0 * vol2rad(vs);
       const double ncp = awa_nc_at_radius(v, cell, gc / v.G + 1, r);
-      S_SOLV(k) = vs;
-      SK(ROS_S + 2, k) = ddry;
-      SK(ROS_S + 3, k) = ks / vs;
-      SK(ROS_S + 4, k) = ncp;
+      SK(ROS_S + 1, k) = ddry;
+      SK(ROS_S + 2, k) = ks / vs;
+      SK(ROS_S + 3, k) = ncp;
       D[k] = 2.0 * r;
       S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (D[k] - ddry));
       wsum += v.vol[(size_t)iw * NS + base + p] * ncp;
@@ -390,38 +444,47 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
   }
   {
     double x[1] = {wsum};
-    block_sum<1>(x, s_red);
+    block_red<1, NT, false>(x, s_red, par);
     wsum = x[0];  // water_vol_conc_initial
   }
 
   const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.9, FAC_REJ = 0.1;
   const double DT_FD = 1e-2;
-  const double del_t = prm.del_t;
+  double u1[PPT], u2[PPT], u3[PPT], u4[PPT];  // unused outputs of the no-Jacobian evaluations
+  const int warp = tid >> 5, lane = tid & 31;
+  // the (T, p) terms of condense_rates at the ROS_NENV times of a step: warp w evaluates entry w
+  auto make_envs = [&](double t, double h, int first, int last) {
+    if (warp >= first && warp <= last) {
+      const double tt = (warp == 0) ? t : (warp == 1) ? t + DT_FD : t + c_rosAlpha[warp - 1] * h;
+      const CondEnv e = cond_env_fast(T0, p0, Tdot, pdot, tt);
+      if (lane == 0) s_env[warp] = e;
+    }
+    __syncthreads();
+  };
+  auto env_H = [&](const CondEnv& e, double Hs) { return -e.dP0_dT_div_P0 * Tdot * Hs + Hs * pdot / e.p; };
+
+  double h = del_t;  // replaced by the estimate below before the first step
+  int n_evals = 0;
   double t = 0.0;
-  double h = h_state[cell];
-  h = (h > 0.0) ? fmin(h, del_t) : del_t;
   double h_natural = h;
   int n_steps = 0, n_reject = 0, fail = 0;
   bool reject_last = false, reject_more = false;
-  double u1[PPT], u2[PPT], u3[PPT], u4[PPT];  // unused outputs of the no-Jacobian evaluations
 
   while (t < del_t && !fail) {
     if (n_steps + n_reject >= prm.max_steps) { fail = 6; break; }
-    bool truncated = false;
-    if (t + h > del_t * (1.0 - 1e-14)) { h_natural = h; h = del_t - t; truncated = true; }
+    make_envs(t, h, 0, 1);
     // f, Jacobian at (t, y) and f at (t + DT_FD, y)
     double f0[PPT], dfdt[PPT], ja[PPT], jb[PPT], jc[PPT];
     double f0H, dfdtH, dd;
     {
-      const CondEnv e0 = cond_env(T0, p0, Tdot, pdot, t);
-      const CondEnv e1 = cond_env(T0, p0, Tdot, pdot, t + DT_FD);
       double hd[PPT], dh[PPT], f1[PPT], hd1[PPT];
-      cond_rates_vec<PPT, true>(e0, H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh);
-      cond_rates_vec<PPT, false>(e1, H, D, sDdry, sKap, sNc, f1, hd1, u1, u2, u3, u4);
+      cond_rates_vec<PPT, true, NT>(s_env[0], H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh);
+      cond_rates_vec<PPT, false, NT>(s_env[1], H, D, sDdry, sKap, sNc, f1, hd1, u1, u2, u3, u4);
+      n_evals += 2;
       double acc[3] = {0.0, 0.0, 0.0};
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
-        const bool live = tid + k * COND_THREADS < n;
+        const bool live = tid + k * NT < n;
         dfdt[k] = (f1[k] - f0[k]) / DT_FD;
         if (!live) { f0[k] = 0.0; dfdt[k] = 0.0; ja[k] = 0.0; jb[k] = 0.0; jc[k] = 0.0; }
         if (live) {
@@ -430,14 +493,55 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
           acc[2] += hd1[k];
         }
       }
-      block_sum<3>(acc, s_red);
-      const double env0 = -e0.dP0_dT_div_P0 * Tdot * H + H * pdot / e0.p;
-      const double env1 = -e1.dP0_dT_div_P0 * Tdot * H + H * pdot / e1.p;
-      f0H = acc[0] + env0;
-      dd = acc[1] + (-e0.dP0_dT_div_P0 * Tdot + pdot / e0.p);
-      dfdtH = ((acc[2] + env1) - f0H) / DT_FD;
+      block_red<3, NT, false>(acc, s_red, par);
+      f0H = acc[0] + env_H(s_env[0], H);
+      dd = acc[1] + (-s_env[0].dP0_dT_div_P0 * Tdot + pdot / s_env[0].p);
+      dfdtH = ((acc[2] + env_H(s_env[1], H)) - f0H) / DT_FD;
     }
+    if (n_steps + n_reject == 0) {
+      // first step size, after cvHin (cvode.c): h = 1/2 sqrt(2 / ||y''||), bounded by hub, times ROS_HIN_FACTOR
+      // for a 4th-order method (small enough that the first step is never near rejection).  CVODE differences f along the solution; here y'' = J f + df/dt comes from the
+      // Jacobian of this step, which carries no cancellation noise (a noisy first step would make two
+      // implementations take different step sequences).
+      double a1[2] = {0.0, 0.0};
+      double ew[PPT];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) {
+        ew[k] = 1.0 / (prm.reltol * fabs(D[k]) + S_ATOL(k));
+        if (tid + k * NT < n) {
+          a1[0] += jc[k] * f0[k];
+          a1[1] = fmax(a1[1], fabs(f0[k]) / (0.1 * fabs(D[k]) + 1.0 / ew[k]));
+        }
+      }
+      double a1s[1] = {a1[0]}, a1m[1] = {a1[1]};
+      block_red<1, NT, false>(a1s, s_red, par);
+      block_red<1, NT, true>(a1m, s_red, par);
+      const double ewH = 1.0 / (prm.reltol * fabs(H) + prm.abstol_H);
+      const double yddH = a1s[0] + dd * f0H + dfdtH;
+      const double hub_inv = fmax(a1m[0], fabs(f0H) / (0.1 * fabs(H) + 1.0 / ewH));
+      double a2[1] = {0.0};
+#pragma unroll
+      for (int k = 0; k < PPT; k++)
+        if (tid + k * NT < n) {
+          const double w = (ja[k] * f0[k] + jb[k] * f0H + dfdt[k]) * ew[k];
+          a2[0] += w * w;
+        }
+      block_red<1, NT, false>(a2, s_red, par);
+      const double yddnrm = sqrt((a2[0] + (yddH * ewH) * (yddH * ewH)) / (double)(n + 1));
+      double hub = 0.1 * del_t;
+      if (hub * hub_inv > 1.0) hub = 1.0 / hub_inv;
+      const double hnew = (yddnrm * hub * hub > 2.0) ? sqrt(2.0 / yddnrm) : hub;
+      // rounded down to a power of two: the estimate inherits the cancellation noise of the rates of
+      // particles in equilibrium (a few 1e-4 between two implementations); the power of two does not
+      h = ROS_HIN_FACTOR * 0.5 * hnew;
+      h = __longlong_as_double(__double_as_longlong(h) & 0x7FF0000000000000ll);
+      h = fmin(del_t, h);
+      h_natural = h;
+    }
+    bool truncated = false;
+    if (t + h > del_t * (1.0 - 1e-14)) { h_natural = h; h = del_t - t; truncated = true; }
     for (;;) {
+      make_envs(t, h, 2, ROS_NENV - 1);  // stage times of this attempt
       const double eps = 1.0 / (ROS_GAMMA * h);
       const double inv_h = 1.0 / h;
       double inv[PPT];
@@ -445,10 +549,10 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       double sden[1] = {0.0};
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
-        inv[k] = 1.0 / (eps - ja[k]);
-        if (tid + k * COND_THREADS < n) sden[0] += jc[k] * jb[k] * inv[k];
+        inv[k] = fast_rcp(eps - ja[k]);
+        if (tid + k * NT < n) sden[0] += jc[k] * jb[k] * inv[k];
       }
-      block_sum<1>(sden, s_red);
+      block_red<1, NT, false>(sden, s_red, par);
       const double lhs_H = eps - dd - sden[0];
 #pragma unroll 1
       for (int st = 0; st < ROS_S; st++) {
@@ -457,7 +561,6 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
         double acc[2] = {0.0, 0.0};
         double Hs = H;
         for (int j = 0; j < st; j++) Hs += c_rosA[st][j] * KH[j];
-        CondEnv es = cond_env(T0, p0, Tdot, pdot, t + c_rosAlpha[st] * h);
         if (st > 0) {
           double y[PPT];
 #pragma unroll
@@ -467,7 +570,8 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
 #pragma unroll
             for (int k = 0; k < PPT; k++) y[k] += aj * SK(j, k);
           }
-          cond_rates_vec<PPT, false>(es, Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4);
+          cond_rates_vec<PPT, false, NT>(s_env[st + 1], Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4);
+          n_evals++;
         } else {
 #pragma unroll
           for (int k = 0; k < PPT; k++) { fs[k] = f0[k]; hd[k] = 0.0; }
@@ -482,19 +586,19 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
         }
 #pragma unroll
         for (int k = 0; k < PPT; k++) {
-          if (tid + k * COND_THREADS < n) {
+          if (tid + k * NT < n) {
             acc[0] += hd[k];
             acc[1] += jc[k] * fs[k] * inv[k];
           } else {
             fs[k] = 0.0;
           }
         }
-        block_sum<2>(acc, s_red);
+        block_red<2, NT, false>(acc, s_red, par);
         double fsH;
         if (st == 0)
           fsH = f0H;
         else
-          fsH = acc[0] + (-es.dP0_dT_div_P0 * Tdot * Hs + Hs * pdot / es.p);
+          fsH = acc[0] + env_H(s_env[st + 1], Hs);
         double rH = fsH + hg * dfdtH;
         for (int j = 0; j < st; j++) rH += (c_rosC[st][j] * inv_h) * KH[j];
         KH[st] = (rH + acc[1]) / lhs_H;
@@ -506,7 +610,7 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       double Dn[PPT];
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
-        const int p = tid + k * COND_THREADS;
+        const int p = tid + k * NT;
         double yn = D[k];
 #pragma unroll
         for (int j = 0; j < ROS_S; j++) yn += c_rosM[j] * SK(j, k);
@@ -517,7 +621,7 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
           esum[0] += (er / w) * (er / w);
         }
       }
-      block_sum<1>(esum, s_red);
+      block_red<1, NT, false>(esum, s_red, par);
       double Hn = H;
 #pragma unroll
       for (int j = 0; j < ROS_S; j++) Hn += c_rosM[j] * KH[j];
@@ -529,12 +633,13 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       double err = sqrt(esum[0] / (double)(n + 1));
       if (!isfinite(err)) err = 1e10;
       err = fmax(err, 1e-10);
-      const double fac = fmin(FAC_MAX, fmax(FAC_MIN, FAC_SAFE / pow(err, 1.0 / ROS_ELO)));
+      if (cell == prm.debug_cell && tid == 0) printf("dev t %.17g h %.17g err %.17g\n", t, h, err);
+      const double fac = fmin(FAC_MAX, fmax(FAC_MIN, FAC_SAFE / sqrt(sqrt(err))));
       double hnew = h * fac;
       if (err <= 1.0) {
 #pragma unroll
         for (int k = 0; k < PPT; k++)
-          if (tid + k * COND_THREADS < n) D[k] = Dn[k];
+          if (tid + k * NT < n) D[k] = Dn[k];
         H = Hn;
         t += h;
         n_steps++;
@@ -559,17 +664,20 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
   double wfin = 0.0;
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
-    const int p = tid + k * COND_THREADS;
+    const int p = tid + k * NT;
     if (p < n && !fail) {
-      double wv = rad2vol(D[k] / 2.0) - S_SOLV(k);
+      double vs = 0.0;  // aero_particle_solute_volume
+      for (int s = 0; s < v.S; s++)
+        if (s != iw) vs += v.vol[(size_t)s * NS + base + p];
+      double wv = rad2vol(D[k] / 2.0) - vs;
       wv = fmax(0.0, wv);
       v.vol[(size_t)iw * NS + base + p] = wv;
-      wfin += wv * sNc[k * COND_THREADS];
+      wfin += wv * sNc[k * NT];
     }
   }
   {
     double x[1] = {wfin};
-    block_sum<1>(x, s_red);
+    block_red<1, NT, false>(x, s_red, par);
     wfin = x[0];
   }
   if (tid == 0) {
@@ -581,21 +689,602 @@ __global__ void __launch_bounds__(COND_THREADS) k_condense(DevView v, const doub
       const double rho_w = v.density[iw], M_w = v.molw[iw];
       const double P0i = PmcConst::water_eq_vap_press * pow(10.0, 7.45 * (T0 - PmcConst::water_freeze_temp) / (T0 - 38.0));
       const double P0f = PmcConst::water_eq_vap_press * pow(10.0, 7.45 * (Tf - PmcConst::water_freeze_temp) / (Tf - 38.0));
-      const double vap_i = M_w / (PmcConst::univ_gas_const * T0) * P0i * v.rh[cell] / rho_w;
+      const double vap_i = M_w / (PmcConst::univ_gas_const * T0) * P0i * H0 / rho_w;
       const double vap_f = M_w / (PmcConst::univ_gas_const * Tf) * P0f * H * V_comp_ratio / rho_w;
       wre_out[cell] = ((vap_f - vap_i) + (wfin - wsum)) / (vap_f + wfin);
       v.rh[cell] = H;
       v.temp[cell] = Tf;
       v.pres[cell] = pf;
-      h_state[cell] = h_natural;
     }
     stats[3 * cell + 0] = n_steps;
     stats[3 * cell + 1] = n_reject;
-    stats[3 * cell + 2] = n_steps * 7 + n_reject * 5;  // rate evaluations per particle
+    stats[3 * cell + 2] = n_evals;  // rate evaluations per particle
   }
 #undef SK
 #undef S_ATOL
-#undef S_SOLV
+}
+
+// ===================================================================== BDF integrator
+// condense_solver (condense_solver.c:84-181) hands the cell's system to SUNDIALS CVODE with CV_BDF.
+// k_condense_bdf restates CVODE's published method (variable order 1..5, variable step, fixed-leading-
+// coefficient Nordsieck form, CVODE's error test, step / order selection and initial step; DESIGN.md
+// section 3 names the sources) with one CTA per cell:
+//   * the Nordsieck vectors zn[0..5] of the particles live in shared memory (PPT particles per
+//     thread), the H components and all step-control scalars are kept redundantly by every thread;
+//   * every Newton iteration is one evaluation of condense_rates per particle plus the exact solve of
+//     the arrow-head system (I - gamma J) x = r by the Schur complement on H (the reference's
+//     preconditioner, condense.F90:625-695): two cell-wide sums; J is evaluated at the predicted state;
+//   * norms are CVODE's weighted RMS norms with weights 1 / (reltol |y| + abstol): one cell-wide sum;
+//   * the (T, p)-dependent terms of condense_rates are evaluated once per step (all Newton iterations
+//     of a step share t_n).
+#define BDF_QMAX 5
+#define BDF_NARR 10  // shared arrays per particle: zn[0..5], abstol, D_dry, kappa, num_conc
+
+// cvPredict (SIGN = +1) / cvRestore (SIGN = -1) for order Q: the Pascal triangle on registers
+template <int Q, int SIGN>
+__device__ __forceinline__ void bdf_pascal(double* __restrict__ zn0, int stride) {
+  double z[Q + 1];
+#pragma unroll
+  for (int j = 0; j <= Q; j++) z[j] = zn0[j * stride];
+#pragma unroll
+  for (int kk = 1; kk <= Q; kk++)
+#pragma unroll
+    for (int j = Q; j >= kk; j--) z[j - 1] = (SIGN > 0) ? z[j - 1] + z[j] : z[j - 1] - z[j];
+#pragma unroll
+  for (int j = 0; j < Q; j++) zn0[j * stride] = z[j];
+}
+template <int SIGN>
+__device__ __forceinline__ void bdf_pascal_q(int q, double* __restrict__ zn0, int stride) {
+  switch (q) {
+    case 1: bdf_pascal<1, SIGN>(zn0, stride); break;
+    case 2: bdf_pascal<2, SIGN>(zn0, stride); break;
+    case 3: bdf_pascal<3, SIGN>(zn0, stride); break;
+    case 4: bdf_pascal<4, SIGN>(zn0, stride); break;
+    default: bdf_pascal<5, SIGN>(zn0, stride); break;
+  }
+}
+// x^(1/n) for the step-size ratios
+__device__ __forceinline__ double bdf_root(double x, int n) { return fast_exp(log(fmax(x, 1e-300)) / (double)n); }
+
+template <int PPT, int NT>
+__global__ void __launch_bounds__(NT) k_condense_bdf(DevView v, const double* T0a /* may alias v.temp */,
+                                                     const double* p0a, const double* T1 /* may alias v.temp */,
+                                                     const double* p1, CondParams prm, int* __restrict__ stats,
+                                                     double* __restrict__ wre_out, int n_limit_lo, int n_limit_hi) {
+  const int cell = blockIdx.x;
+  const int n = v.count[cell];
+  if (n <= n_limit_lo || n > n_limit_hi) return;  // another instantiation owns this cell
+  if (v.status[cell] != 0) return;
+  const int tid = threadIdx.x;
+  const size_t base = (size_t)cell * v.cap;
+  const size_t NS = (size_t)v.n_cells * v.cap;
+  __shared__ double s_red[2 * 4 * (NT / 32)];
+  extern __shared__ double s_K[];  // [BDF_NARR][PPT][NT]
+#define ZN(j, k) s_K[((j) * PPT + (k)) * NT + tid]
+#define S_ATOL(k) ZN(6, k)
+  const double* sDdry = &ZN(7, 0);
+  const double* sKap = &ZN(8, 0);
+  const double* sNc = &ZN(9, 0);
+  int par = 0;
+  // aero_state_reweight after the solve is the identity for flat weights (see k_condense)
+  for (int q = 0; q < v.C * v.G; q++)
+    if (v.wtype[(size_t)cell * v.C * v.G + q] != PMCGPU_WEIGHT_NONE) {
+      if (tid == 0 && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_REWEIGHT;
+      return;
+    }
+  const int iw = v.i_water - 1;
+  const double T0 = T0a[cell], p0 = p0a[cell];  // env_state_initial
+  const double del_t = prm.del_t;
+  const double Tdot = (T1[cell] - T0) / del_t, pdot = (p1[cell] - p0) / del_t;
+  const double H0 = v.rh[cell];
+
+  // ---- set-up (condense.F90:196-237): kappa, D_dry, num_conc, D, abstol per particle.
+  // Slots past the population hold a harmless wet dummy particle that never enters a sum.
+  double wsum = 0.0;
+#pragma unroll
+  for (int k = 0; k < PPT; k++) {
+    const int p = tid + k * NT;
+#pragma unroll
+    for (int j = 1; j <= BDF_QMAX; j++) ZN(j, k) = 0.0;
+    ZN(0, k) = 2.0;
+    S_ATOL(k) = 1.0;
+    ZN(7, k) = 1.0;
+    ZN(8, k) = 0.5;
+    ZN(9, k) = 1.0;
+    if (p < n) {
+      double vt = 0.0, vs = 0.0, ks = 0.0;  // aero_particle_solute_kappa (aero_particle.F90:724-755)
+      const double M_w = v.molw[iw], rho_w = v.density[iw];
+      for (int s = 0; s < v.S; s++) {
+        const double x = v.vol[(size_t)s * NS + base + p];
+        vt += x;
+        if (s != iw) {
+          vs += x;
+          const double kp = (v.nions[s] > 0) ? M_w * v.density[s] / (v.molw[s] * rho_w) * (double)v.nions[s] : v.kappa[s];
+          ks += x * kp;
+        }
+      }
+      const int gc = v.wgc[base + p];
+      const double r = vol2rad(vt);
+      const double ddry = 2.0 * vol2rad(vs);
+      const double ncp = awa_nc_at_radius(v, cell, gc / v.G + 1, r);
+      ZN(7, k) = ddry;
+      ZN(8, k) = ks / vs;
+      ZN(9, k) = ncp;
+      ZN(0, k) = 2.0 * r;
+      S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (2.0 * r - ddry));
+      wsum += v.vol[(size_t)iw * NS + base + p] * ncp;
+    }
+  }
+  {
+    double x[1] = {wsum};
+    block_red<1, NT, false>(x, s_red, par);
+    wsum = x[0];  // water_vol_conc_initial
+  }
+
+  // ---- integrator state (names follow cvode_impl.h)
+  const double ADDON = 1e-6, BIAS1 = 6.0, BIAS2 = 6.0, BIAS3 = 10.0, ETAMX1 = 10000.0, ETAMX2 = 10.0, ETAMX3 = 10.0,
+               ETAMXF = 0.2, ETAMIN = 0.1, ETACF = 0.25, THRESH = 1.5, CRDOWN = 0.3, RDIV = 2.0, CORTES = 0.1;
+  const int SMALL_NST = 10, MXNCF = 10, MXNEF = 7, MXNEF1 = 3, SMALL_NEF = 2, LONG_WAIT = 10, MAXCOR = 3;
+  double zH[BDF_QMAX + 1] = {H0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  double tau[BDF_QMAX + 2] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  double l[BDF_QMAX + 1] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  double tq[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  int q = 1, L = 2, qprime = 1, qwait = 2, nst = 0, n_fail = 0, n_evals = 0, fail = 0;
+  double h = 0.0, hprime = 0.0, eta = 1.0, hscale = 0.0, tn = 0.0, etamax = ETAMX1, rl1 = 1.0, gamma = 0.0,
+         saved_tq5 = 0.0, acnrm = 0.0, crate = 1.0;
+  double ewt[PPT], ewtH = 0.0;
+  double acor[PPT], acorH = 0.0;
+  double u1[PPT], u2[PPT], u3[PPT], u4[PPT];  // unused outputs of the no-Jacobian evaluations
+
+  auto set_ewt = [&]() {  // cvEwtSetSV
+#pragma unroll
+    for (int k = 0; k < PPT; k++) ewt[k] = fast_rcp(fma(prm.reltol, fabs(ZN(0, k)), S_ATOL(k)));
+    ewtH = 1.0 / (prm.reltol * fabs(zH[0]) + prm.abstol_H);
+  };
+  auto wrms = [&](const double (&vD)[PPT], double vH) -> double {
+    double acc[1] = {0.0};
+#pragma unroll
+    for (int k = 0; k < PPT; k++)
+      if (tid + k * NT < n) acc[0] = fma(vD[k] * ewt[k], vD[k] * ewt[k], acc[0]);
+    block_red<1, NT, false>(acc, s_red, par);
+    return sqrt((acc[0] + (vH * ewtH) * (vH * ewtH)) / (double)(n + 1));
+  };
+  // condense_vf_f (condense.F90:509-557): f = (Ddot_i, Hdot)
+  auto eval_f = [&](const CondEnv& e, double Hs, const double (&yD)[PPT], double (&fD)[PPT], double& fH) {
+    double hd[PPT];
+    cond_rates_vec<PPT, false, NT>(e, Hs, yD, sDdry, sKap, sNc, fD, hd, u1, u2, u3, u4);
+    double acc[1] = {0.0};
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+      if (tid + k * NT < n) acc[0] += hd[k]; else fD[k] = 0.0;
+    }
+    block_red<1, NT, false>(acc, s_red, par);
+    fH = acc[0] + (-e.dP0_dT_div_P0 * Tdot * Hs + Hs * pdot / e.p);
+    n_evals++;
+  };
+  // f and the arrow-head Jacobian (condense_jac, condense.F90:566-616), folded with gamma into what the
+  // Schur-complement solve needs: inv = 1 / (1 - gamma a), P = gamma c inv, Q = gamma b inv,
+  // lhsH = 1 - gamma dH'/dH - sum (gamma b)(gamma c) inv  (condense.F90:665-672)
+  auto eval_fj = [&](const CondEnv& e, double Hs, const double (&yD)[PPT], double (&fD)[PPT], double& fH,
+                     double (&inv)[PPT], double (&Pc)[PPT], double (&Qb)[PPT], double& lhsH) {
+    double hd[PPT], dh[PPT];
+    cond_rates_vec<PPT, true, NT>(e, Hs, yD, sDdry, sKap, sNc, fD, hd, inv, Qb, Pc, dh);  // inv = a, Qb = b, Pc = c
+    double acc[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+      const double iv = fast_rcp(fma(-gamma, inv[k], 1.0));
+      const double gb = gamma * Qb[k], gc = gamma * Pc[k];
+      if (tid + k * NT < n) {
+        acc[0] += hd[k];
+        acc[1] += dh[k];
+        acc[2] += gb * gc * iv;
+        inv[k] = iv;
+        Pc[k] = gc * iv;
+        Qb[k] = gb * iv;
+      } else {
+        fD[k] = 0.0; inv[k] = 1.0; Pc[k] = 0.0; Qb[k] = 0.0;
+      }
+    }
+    block_red<3, NT, false>(acc, s_red, par);
+    fH = acc[0] + (-e.dP0_dT_div_P0 * Tdot * Hs + Hs * pdot / e.p);
+    const double jdd = acc[1] + (-e.dP0_dT_div_P0 * Tdot + pdot / e.p);
+    lhsH = 1.0 - gamma * jdd - acc[2];
+    n_evals++;
+  };
+  auto rescale = [&]() {  // cvRescale
+    double factor = eta;
+    for (int j = 1; j <= q; j++) {
+#pragma unroll
+      for (int k = 0; k < PPT; k++) ZN(j, k) *= factor;
+      zH[j] *= factor;
+      factor *= eta;
+    }
+    h = hscale * eta;
+    hscale = h;
+  };
+  auto predict = [&]() {  // cvPredict
+#pragma unroll
+    for (int k = 0; k < PPT; k++) bdf_pascal_q<1>(q, &ZN(0, k), PPT * NT);
+    bdf_pascal_q<1>(q, zH, 1);
+  };
+  auto restore = [&]() {  // cvRestore
+#pragma unroll
+    for (int k = 0; k < PPT; k++) bdf_pascal_q<-1>(q, &ZN(0, k), PPT * NT);
+    bdf_pascal_q<-1>(q, zH, 1);
+  };
+  auto set_coeffs = [&]() {  // cvSetBDF + cvSetTqBDF
+    l[0] = l[1] = 1.0;
+    double xi_inv = 1.0, xistar_inv = 1.0;
+    for (int i = 2; i <= q; i++) l[i] = 0.0;
+    double alpha0 = -1.0, alpha0_hat = -1.0, hsum = h;
+    if (q > 1) {
+      for (int j = 2; j < q; j++) {
+        hsum += tau[j - 1];
+        xi_inv = h / hsum;
+        alpha0 -= 1.0 / j;
+        for (int i = j; i >= 1; i--) l[i] += l[i - 1] * xi_inv;
+      }
+      alpha0 -= 1.0 / q;
+      xistar_inv = -l[1] - alpha0;
+      hsum += tau[q - 1];
+      xi_inv = h / hsum;
+      alpha0_hat = -l[1] - xi_inv;
+      for (int i = q; i >= 1; i--) l[i] += l[i - 1] * xistar_inv;
+    }
+    const double A1 = 1.0 - alpha0_hat + alpha0, A2 = 1.0 + q * A1;
+    tq[2] = fabs(A1 / (alpha0 * A2));
+    tq[5] = fabs(A2 * xistar_inv / (l[q] * xi_inv));
+    if (qwait == 1) {
+      if (q > 1) {
+        const double Cc = xistar_inv / l[q], A3 = alpha0 + 1.0 / q, A4 = alpha0_hat + xi_inv;
+        const double Cpinv = (1.0 - A4 + A3) / A3;
+        tq[1] = fabs(Cc * Cpinv);
+      } else {
+        tq[1] = 1.0;
+      }
+      hsum += tau[q];
+      xi_inv = h / hsum;
+      const double A5 = alpha0 - 1.0 / (q + 1), A6 = alpha0_hat - xi_inv;
+      const double Cppinv = (1.0 - A6 + A5) / A2;
+      tq[3] = fabs(Cppinv / (xi_inv * (q + 2) * A5));
+    }
+    tq[4] = CORTES / tq[2];
+    rl1 = 1.0 / l[1];
+    gamma = h * rl1;
+  };
+  auto increase_order = [&]() {  // cvIncreaseBDF: zn[L] = A1 * (saved acor in zn[QMAX])
+    for (int i = 0; i <= BDF_QMAX; i++) l[i] = 0.0;
+    l[2] = 1.0;
+    double alpha1 = 1.0, prod = 1.0, xiold = 1.0, alpha0 = -1.0, hsum = hscale;
+    if (q > 1) {
+      for (int j = 1; j < q; j++) {
+        hsum += tau[j + 1];
+        const double xi = hsum / hscale;
+        prod *= xi;
+        alpha0 -= 1.0 / (j + 1);
+        alpha1 += 1.0 / xi;
+        for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xiold + l[i - 1];
+        xiold = xi;
+      }
+    }
+    const double A1 = (-alpha0 - alpha1) / prod;
+#pragma unroll
+    for (int k = 0; k < PPT; k++) ZN(L, k) = A1 * ZN(BDF_QMAX, k);
+    zH[L] = A1 * zH[BDF_QMAX];
+    for (int j = 2; j <= q; j++) {
+#pragma unroll
+      for (int k = 0; k < PPT; k++) ZN(j, k) = fma(l[j], ZN(L, k), ZN(j, k));
+      zH[j] = fma(l[j], zH[L], zH[j]);
+    }
+  };
+  auto decrease_order = [&]() {  // cvDecreaseBDF
+    for (int i = 0; i <= BDF_QMAX; i++) l[i] = 0.0;
+    l[2] = 1.0;
+    double hsum = 0.0;
+    for (int j = 1; j <= q - 2; j++) {
+      hsum += tau[j];
+      const double xi = hsum / hscale;
+      for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xi + l[i - 1];
+    }
+    for (int j = 2; j < q; j++) {
+#pragma unroll
+      for (int k = 0; k < PPT; k++) ZN(j, k) = fma(-l[j], ZN(q, k), ZN(j, k));
+      zH[j] = fma(-l[j], zH[q], zH[j]);
+    }
+  };
+
+  // ---- first call of CVode: f(t0, y0), initial step (cvHin), zn[1] = h f
+  set_ewt();
+  {
+    double y0[PPT], f0[PPT], f0H;
+#pragma unroll
+    for (int k = 0; k < PPT; k++) y0[k] = ZN(0, k);
+    eval_f(cond_env_fast(T0, p0, Tdot, pdot, 0.0), zH[0], y0, f0, f0H);
+#pragma unroll
+    for (int k = 0; k < PPT; k++) ZN(1, k) = f0[k];
+    zH[1] = f0H;
+    // cvUpperBoundH0
+    double hub_inv[1] = {fabs(f0H) / (0.1 * fabs(zH[0]) + 1.0 / ewtH)};
+#pragma unroll
+    for (int k = 0; k < PPT; k++)
+      if (tid + k * NT < n) hub_inv[0] = fmax(hub_inv[0], fabs(f0[k]) / (0.1 * fabs(y0[k]) + 1.0 / ewt[k]));
+    block_red<1, NT, true>(hub_inv, s_red, par);
+    const double hlb = 100.0 * 2.220446049250313e-16 * del_t;
+    double hub = 0.1 * del_t;
+    if (hub * hub_inv[0] > 1.0) hub = 1.0 / hub_inv[0];
+    double hg = sqrt(hlb * hub), hnew = hg;
+    if (!(hub < hlb)) {
+      for (int count = 1; count <= 4; count++) {
+        // cvYddNorm: || (f(t0 + hg, y0 + hg f0) - f0) / hg ||
+        double yy[PPT], ff[PPT], ffH;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) yy[k] = fma(hg, f0[k], y0[k]);
+        eval_f(cond_env_fast(T0, p0, Tdot, pdot, hg), fma(hg, f0H, zH[0]), yy, ff, ffH);
+#pragma unroll
+        for (int k = 0; k < PPT; k++) ff[k] = (ff[k] - f0[k]) / hg;
+        const double yddnrm = wrms(ff, (ffH - f0H) / hg);
+        hnew = (yddnrm * hub * hub > 2.0) ? sqrt(2.0 / yddnrm) : sqrt(hg * hub);
+        if (count == 4) break;
+        const double hrat = hnew / hg;
+        if (hrat > 0.5 && hrat < 2.0) break;
+        if (count > 1 && hrat > 2.0) {
+          hnew = hg;
+          break;
+        }
+        hg = hnew;
+      }
+      h = fmin(hub, fmax(hlb, 0.5 * hnew));
+    } else {
+      h = hg;
+    }
+    hscale = h;
+    hprime = h;
+#pragma unroll
+    for (int k = 0; k < PPT; k++) ZN(1, k) = h * f0[k];
+    zH[1] = h * f0H;
+  }
+
+  // ---- CVode(..., CV_NORMAL): internal steps until tn >= t_final
+  for (;;) {
+    if (nst > 0) set_ewt();
+    if (nst >= prm.max_steps) { fail = 6; break; }
+    // ------------------------------------------------------------ cvStep
+    const double saved_t = tn;
+    int ncf = 0, nef = 0;
+    if (nst > 0 && hprime != h) {  // cvAdjustParams
+      if (qprime != q) {
+        if (qprime > q) increase_order(); else decrease_order();
+        q = qprime;
+        L = q + 1;
+        qwait = L;
+      }
+      rescale();
+    }
+    double dsm = 0.0;
+    for (;;) {
+      tn += h;
+      predict();
+      set_coeffs();
+      // ---- cvNls: Newton iteration with the exact arrow-head solve
+      bool converged = false;
+      const CondEnv env_n = cond_env_fast(T0, p0, Tdot, pdot, tn);
+      {
+        crate = 1.0;
+        double y[PPT], f[PPT], inv[PPT], Pc[PPT], Qb[PPT], fH, lhsH;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) { y[k] = ZN(0, k); acor[k] = 0.0; }
+        double yH = zH[0];
+        acorH = 0.0;
+        eval_fj(env_n, yH, y, f, fH, inv, Pc, Qb, lhsH);
+        double delp = 0.0;
+        for (int m = 0;;) {
+          double b[PPT];
+          double acc[1] = {0.0};
+#pragma unroll
+          for (int k = 0; k < PPT; k++) {
+            b[k] = fma(gamma, f[k], -fma(rl1, ZN(1, k), acor[k]));
+            acc[0] = fma(Pc[k], b[k], acc[0]);  // P = 0 in the slots past the population
+          }
+          block_red<1, NT, false>(acc, s_red, par);
+          const double bH = (fma(gamma, fH, -fma(rl1, zH[1], acorH)) + acc[0]) / lhsH;
+#pragma unroll
+          for (int k = 0; k < PPT; k++) b[k] = fma(Qb[k], bH, b[k] * inv[k]);
+          const double del = wrms(b, bH);
+          if (!isfinite(del)) break;
+#pragma unroll
+          for (int k = 0; k < PPT; k++) {
+            acor[k] += b[k];
+            y[k] = ZN(0, k) + acor[k];
+          }
+          acorH += bH;
+          yH = zH[0] + acorH;
+          if (m > 0) crate = fmax(CRDOWN * crate, del / delp);
+          const double dcon = del * fmin(1.0, crate) / tq[4];
+          if (dcon <= 1.0) {
+            acnrm = (m == 0) ? del : wrms(acor, acorH);
+            converged = true;
+            break;
+          }
+          m++;
+          if (m == MAXCOR || (m >= 2 && del > RDIV * delp)) break;
+          delp = del;
+          eval_f(env_n, yH, y, f, fH);
+        }
+      }
+      if (!converged) {  // cvHandleNFlag
+        ncf++;
+        n_fail++;
+        etamax = 1.0;
+        if (ncf == MXNCF || !(fabs(h) > 1e-300)) { fail = 7; break; }
+        eta = ETACF;
+        tn = saved_t;
+        restore();
+        rescale();
+        continue;
+      }
+      dsm = acnrm * tq[2];  // cvDoErrorTest
+      if (dsm <= 1.0) break;
+      nef++;
+      n_fail++;
+      tn = saved_t;
+      restore();
+      if (nef == MXNEF) { fail = 7; break; }
+      etamax = 1.0;
+      if (nef <= MXNEF1) {
+        eta = 1.0 / (bdf_root(BIAS2 * dsm, L) + ADDON);
+        eta = fmax(ETAMIN, eta);
+        if (nef >= SMALL_NEF) eta = fmin(eta, ETAMXF);
+        rescale();
+        continue;
+      }
+      eta = ETAMIN;
+      if (q > 1) {
+        decrease_order();
+        L = q;
+        q--;
+        qwait = L;
+        rescale();
+        continue;
+      }
+      h *= eta;
+      hscale = h;
+      qwait = LONG_WAIT;
+      {
+        double y[PPT], f[PPT], fH;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) y[k] = ZN(0, k);
+        eval_f(env_n, zH[0], y, f, fH);
+#pragma unroll
+        for (int k = 0; k < PPT; k++) ZN(1, k) = h * f[k];
+        zH[1] = h * fH;
+      }
+    }
+    if (fail) break;
+    // ------------------------------------------------------------ cvCompleteStep
+    nst++;
+    for (int i = q; i >= 2; i--) tau[i] = tau[i - 1];
+    if (q == 1 && nst > 1) tau[2] = tau[1];
+    tau[1] = h;
+    for (int j = 0; j <= q; j++) {
+#pragma unroll
+      for (int k = 0; k < PPT; k++) ZN(j, k) = fma(l[j], acor[k], ZN(j, k));
+      zH[j] = fma(l[j], acorH, zH[j]);
+    }
+    qwait--;
+    if (qwait == 1 && q != BDF_QMAX) {
+#pragma unroll
+      for (int k = 0; k < PPT; k++) ZN(BDF_QMAX, k) = acor[k];
+      zH[BDF_QMAX] = acorH;
+      saved_tq5 = tq[5];
+    }
+    // ------------------------------------------------------------ cvPrepareNextStep
+    if (etamax == 1.0) {
+      qwait = max(qwait, 2);
+      qprime = q;
+      hprime = h;
+      eta = 1.0;
+    } else {
+      const double etaq = 1.0 / (bdf_root(BIAS2 * dsm, L) + ADDON);
+      if (qwait != 0) {
+        eta = etaq;
+        qprime = q;
+      } else {
+        qwait = 2;
+        double etaqm1 = 0.0, etaqp1 = 0.0;
+        if (q > 1) {  // cvComputeEtaqm1
+          double t[PPT];
+#pragma unroll
+          for (int k = 0; k < PPT; k++) t[k] = ZN(q, k);
+          const double ddn = wrms(t, zH[q]) * tq[1];
+          etaqm1 = 1.0 / (bdf_root(BIAS1 * ddn, q) + ADDON);
+        }
+        if (q != BDF_QMAX && saved_tq5 != 0.0) {  // cvComputeEtaqp1
+          double hrL = 1.0;
+          for (int i = 0; i < L; i++) hrL *= h / tau[2];
+          const double cquot = (tq[5] / saved_tq5) * hrL;
+          double t[PPT];
+#pragma unroll
+          for (int k = 0; k < PPT; k++) t[k] = fma(-cquot, ZN(BDF_QMAX, k), acor[k]);
+          const double dup = wrms(t, fma(-cquot, zH[BDF_QMAX], acorH)) * tq[3];
+          etaqp1 = 1.0 / (bdf_root(BIAS3 * dup, L + 1) + ADDON);
+        }
+        const double etam = fmax(etaqm1, fmax(etaq, etaqp1));  // cvChooseEta
+        if (etam < THRESH) {
+          eta = 1.0;
+          qprime = q;
+        } else if (etam == etaq) {
+          eta = etaq;
+          qprime = q;
+        } else if (etam == etaqm1) {
+          eta = etaqm1;
+          qprime = q - 1;
+        } else {
+          eta = etaqp1;
+          qprime = q + 1;
+#pragma unroll
+          for (int k = 0; k < PPT; k++) ZN(BDF_QMAX, k) = acor[k];
+          zH[BDF_QMAX] = acorH;
+        }
+      }
+      if (eta < THRESH) {  // cvSetEta (no hmax)
+        eta = 1.0;
+        hprime = h;
+      } else {
+        eta = fmin(eta, etamax);
+        hprime = h * eta;
+      }
+    }
+    etamax = (nst <= SMALL_NST) ? ETAMX2 : ETAMX3;
+    if (tn - del_t >= 0.0) break;
+  }
+
+  // ---- CVodeGetDky(t_final, 0) and write back (condense.F90:266-293): water volume, clamp at zero, balance
+  double wfin = 0.0;
+  const double sfac = (del_t - tn) / h;
+  double Hfin = zH[q];
+  for (int j = q - 1; j >= 0; j--) Hfin = fma(Hfin, sfac, zH[j]);
+#pragma unroll
+  for (int k = 0; k < PPT; k++) {
+    const int p = tid + k * NT;
+    if (p < n && !fail) {
+      double Df = ZN(q, k);
+      for (int j = q - 1; j >= 0; j--) Df = fma(Df, sfac, ZN(j, k));
+      double vs = 0.0;  // aero_particle_solute_volume
+      for (int s = 0; s < v.S; s++)
+        if (s != iw) vs += v.vol[(size_t)s * NS + base + p];
+      double wv = rad2vol(Df / 2.0) - vs;
+      wv = fmax(0.0, wv);
+      v.vol[(size_t)iw * NS + base + p] = wv;
+      wfin += wv * sNc[k * NT];
+    }
+  }
+  {
+    double x[1] = {wfin};
+    block_red<1, NT, false>(x, s_red, par);
+    wfin = x[0];
+  }
+  if (tid == 0) {
+    if (fail) {
+      if (v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_CONDENSE;
+    } else {
+      const double Tf = T1[cell], pf = p1[cell];
+      const double V_comp_ratio = Tf * p0 / (T0 * pf);
+      const double rho_w = v.density[iw], M_w = v.molw[iw];
+      const double P0i = PmcConst::water_eq_vap_press * pow(10.0, 7.45 * (T0 - PmcConst::water_freeze_temp) / (T0 - 38.0));
+      const double P0f = PmcConst::water_eq_vap_press * pow(10.0, 7.45 * (Tf - PmcConst::water_freeze_temp) / (Tf - 38.0));
+      const double vap_i = M_w / (PmcConst::univ_gas_const * T0) * P0i * H0 / rho_w;
+      const double vap_f = M_w / (PmcConst::univ_gas_const * Tf) * P0f * Hfin * V_comp_ratio / rho_w;
+      wre_out[cell] = ((vap_f - vap_i) + (wfin - wsum)) / (vap_f + wfin);
+      v.rh[cell] = Hfin;
+      v.temp[cell] = Tf;
+      v.pres[cell] = pf;
+    }
+    stats[3 * cell + 0] = nst;
+    stats[3 * cell + 1] = n_fail;
+    stats[3 * cell + 2] = n_evals;  // rate evaluations per particle
+  }
+#undef ZN
+#undef S_ATOL
 }
 
 
@@ -603,6 +1292,7 @@ int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0
                            CondParams prm, double* h_state, int* stats, double* wre, int n_lo);
 
 // device pointers T1/p1 (final env per cell)
+static size_t bdf_smem(int ppt) { return (size_t)BDF_NARR * ppt * COND_THREADS * sizeof(double); }
 static size_t cond_smem(int ppt) { return (size_t)COND_NARR * ppt * COND_THREADS * sizeof(double); }
 
 int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
@@ -612,6 +1302,9 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(2)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(4)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cond_smem(8)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<2, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(2)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<4, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(4)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<8, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(8)));
     configured = true;
   }
   DevView& v = ctx->v;
@@ -628,27 +1321,46 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
   prm.abstol_scale = 1e-8;
   prm.abstol_H = 1e-10;
   prm.max_steps = 100000;
+  prm.debug_cell = getenv("PMCGPU_DEBUG_CELL") ? atoi(getenv("PMCGPU_DEBUG_CELL")) : -1;
   ProfScope ps_(ctx, "k_condense");
   // the population size of a cell picks the instantiation: 1..256 -> PPT 1, ..512 -> 2, ..1024 -> 4, ..2048 -> 8
   const int cap = v.cap;
-  k_condense<1><<<v.n_cells, COND_THREADS, cond_smem(1), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, nullptr, -1, 256);
+  if (ctx->cond_method == 5) {
+#define BDF_LAUNCH(PPT, LO, HI)                                                                                   \
+  k_condense_bdf<PPT, COND_THREADS><<<v.n_cells, COND_THREADS, bdf_smem(PPT), ctx->stream>>>(                    \
+      v, dT0, dp0, dT1, dp1, prm, cw->cond_stats, cw->cond_wre, LO, HI);                                          \
+  LAUNCH_CHECK(ctx)
+    BDF_LAUNCH(1, -1, 256);
+    if (cap > 256) { BDF_LAUNCH(2, 256, 512); }
+    if (cap > 512) { BDF_LAUNCH(4, 512, 1024); }
+    if (cap > 1024) { BDF_LAUNCH(8, 1024, 2048); }
+#undef BDF_LAUNCH
+  } else {
+  k_condense<1><<<v.n_cells, COND_THREADS, cond_smem(1), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_stats, cw->cond_wre, -1, 256);
   LAUNCH_CHECK(ctx);
   if (cap > 256) {
-    k_condense<2><<<v.n_cells, COND_THREADS, cond_smem(2), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, nullptr, 256, 512);
+    k_condense<2><<<v.n_cells, COND_THREADS, cond_smem(2), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_stats, cw->cond_wre, 256, 512);
     LAUNCH_CHECK(ctx);
   }
   if (cap > 512) {
-    k_condense<4><<<v.n_cells, COND_THREADS, cond_smem(4), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, nullptr, 512, 1024);
+    k_condense<4><<<v.n_cells, COND_THREADS, cond_smem(4), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_stats, cw->cond_wre, 512, 1024);
     LAUNCH_CHECK(ctx);
   }
   if (cap > 1024) {
-    k_condense<8><<<v.n_cells, COND_THREADS, cond_smem(8), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, nullptr, 1024, 2048);
+    k_condense<8><<<v.n_cells, COND_THREADS, cond_smem(8), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_stats, cw->cond_wre, 1024, 2048);
     LAUNCH_CHECK(ctx);
+  }
   }
   if (cap > 2048) {
     int rc = pmc_condense_big_async(ctx, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 2048);
     if (rc) return rc;
   }
+  return PMCGPU_OK;
+}
+
+extern "C" int pmcgpu_set_condense_method(pmcgpu_ctx* ctx, int method) {
+  if (!ctx || (method != 4 && method != 5)) return PMCGPU_ERR_ARG;
+  ctx->cond_method = method;
   return PMCGPU_OK;
 }
 

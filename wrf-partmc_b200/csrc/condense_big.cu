@@ -5,6 +5,7 @@
 struct CondParams {
   double del_t, reltol, abstol_scale, abstol_H;
   int max_steps;
+  int debug_cell;
 };
 
 __global__ void k_flag_big_cells(DevView v, int n_lo) {

@@ -156,6 +156,7 @@ struct pmcgpu_ctx {
   int rank = 0, n_ranks = 1, px = 1, py = 1;
   int nb[4] = {0, 0, 0, 0};
   void* nccl_comm = nullptr;
+  int cond_method = 4;  // 4: RODAS4, 5: BDF (CVODE restatement) (pmcgpu_set_condense_method)
 };
 int pmc_exchange_slabs(pmcgpu_ctx* ctx, const int* n_send, const int* n_recv);
 int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], const size_t send_bytes[4],

@@ -259,6 +259,10 @@ class PartMCGPU:
                                                    _p(rh), _p(st), _p(wre)))
         return rh, st, wre
 
+    def set_condense_method(self, method):
+        """5: CVODE-style BDF (default), 4: RODAS4 (cross-validation)"""
+        self._chk(self.L.pmcgpu_set_condense_method(self.h, C.c_int(method)))
+
     def condense_equilib_particles(self):
         self._chk(self.L.pmcgpu_condense_equilib_particles(self.h))
 
