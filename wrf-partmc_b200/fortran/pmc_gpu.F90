@@ -288,3 +288,191 @@ contains
     call pmc_gpu_check(pmcgpu_set_env(pmc_gpu_handle, c_loc(temp), c_loc(pres), c_loc(rh), &
          c_loc(alt), c_loc(cvol)), 'pmcgpu_set_env')
   end subroutine pmc_gpu_upload_aero_states
+
+  !> Device SoA -> aero_states(i,k,j): refresh of the Fortran mirror when a WRF history or
+  !! restart alarm needs it (partmc_before_solve_io, wrf_pmc_driver.F90:369-384).
+  subroutine pmc_gpu_download_aero_states(aero_states, aero_data, pmc_is, pmc_ie, pmc_js, &
+       pmc_je, pmc_ks, pmc_ke)
+    use pmc_aero_state
+    use pmc_aero_data
+    use pmc_aero_particle
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    type(aero_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), &
+         intent(inout) :: aero_states
+    type(aero_data_t), intent(in) :: aero_data
+
+    integer :: i, j, k, c, p, q, n_cells, n_spec, n_class, n_tot, i_class
+    integer(c_int), allocatable, target :: counts(:), wgroup(:), wclass(:), nprim(:), hyst(:), wtype(:)
+    integer(c_int64_t), allocatable, target :: ids(:)
+    real(c_double), allocatable, target :: vol(:,:), lct(:), gct(:), wmag(:), wexp(:)
+    type(aero_particle_t) :: particle
+
+    n_cells = size(aero_states)
+    n_spec = aero_data_n_spec(aero_data)
+    n_class = size(aero_states(pmc_is,pmc_ks,pmc_js)%awa%weight, 2)
+    allocate(counts(n_cells))
+    call pmc_gpu_check(pmcgpu_get_counts(pmc_gpu_handle, c_loc(counts)), 'pmcgpu_get_counts')
+    n_tot = sum(counts)
+    allocate(vol(n_tot, n_spec), wgroup(n_tot), wclass(n_tot), ids(n_tot), nprim(n_tot), &
+         hyst(n_tot), lct(n_tot), gct(n_tot))
+    allocate(wtype(n_cells * n_class), wmag(n_cells * n_class), wexp(n_cells * n_class))
+    call pmc_gpu_check(pmcgpu_get_particles(pmc_gpu_handle, int(n_tot, c_long_long), c_loc(vol), &
+         c_loc(wgroup), c_loc(wclass), c_loc(ids), c_loc(nprim), c_loc(hyst), c_loc(lct), &
+         c_loc(gct)), 'pmcgpu_get_particles')
+    call pmc_gpu_check(pmcgpu_get_weights(pmc_gpu_handle, c_loc(wtype), c_loc(wmag), &
+         c_loc(wexp)), 'pmcgpu_get_weights')
+    c = 0
+    q = 0
+    do j = pmc_js, pmc_je
+    do k = pmc_ks, pmc_ke
+    do i = pmc_is, pmc_ie
+       c = c + 1
+       call aero_state_zero(aero_states(i,k,j))        ! keeps awa and n_part_ideal
+       do i_class = 1, n_class
+          aero_states(i,k,j)%awa%weight(1, i_class)%magnitude = wmag((c - 1) * n_class + i_class)
+       end do
+       do p = 1, counts(c)
+          q = q + 1
+          call aero_particle_zero(particle, aero_data)
+          particle%vol = vol(q, :)
+          particle%weight_group = wgroup(q)
+          particle%weight_class = wclass(q)
+          particle%id = ids(q)
+          particle%n_primary_parts = nprim(q)
+          particle%water_hyst_leg = hyst(q)
+          particle%least_create_time = lct(q)
+          particle%greatest_create_time = gct(q)
+          call aero_state_add_particle(aero_states(i,k,j), particle, aero_data, &
+               allow_resort=.false.)
+       end do
+    end do
+    end do
+    end do
+  end subroutine pmc_gpu_download_aero_states
+
+  !> Drop-in for partmc_timestep (interface/wrf_pmc_driver.F90:46-290): same argument list
+  !! (gas_data / gas_states / scenario are passed through untouched: gas chemistry, emissions
+  !! and MOSAIC are outside this library, SURVEY.md section 8f).
+  subroutine pmc_gpu_partmc_timestep(grid, config_flags, env_states, pmc_is, pmc_ie, pmc_js, &
+       pmc_je, pmc_ks, pmc_ke, global_nx, global_ny, global_nz)
+    use module_domain, only: domain, domain_get_time_since_sim_start
+    use module_configure, only: grid_config_rec_type, p_qv
+    use module_model_constants, only: t0, p0 => p1000mb, rcp
+    use pmc_env_state
+    type(domain), intent(inout) :: grid
+    type(grid_config_rec_type), intent(in) :: config_flags
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    type(env_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), &
+         intent(inout) :: env_states
+    integer, intent(in) :: global_nx, global_ny, global_nz
+
+    type(pmcgpu_timestep_args_t) :: args
+    integer :: i, j, k, c, n_cells, n_class
+    real(c_double), allocatable, target :: temp(:), pres(:), rh(:), alt(:), cvol(:)
+    real(c_float), allocatable, target :: num_conc(:)
+    real(kind=dp) :: pressure, qsat
+    real :: real_time
+
+    n_cells = (pmc_ie - pmc_is + 1) * (pmc_ke - pmc_ks + 1) * (pmc_je - pmc_js + 1)
+    n_class = size(grid%u_flux, 4) - 1
+    allocate(temp(n_cells), pres(n_cells), rh(n_cells), alt(n_cells), cvol(n_cells))
+    allocate(num_conc(n_cells * n_class))
+    ! wrf_to_partmc (wrf_pmc_driver.F90:576-644): the host part is the conversion of WRF's
+    ! perturbation fields; old_env_states is kept by the library
+    c = 0
+    do j = pmc_js, pmc_je
+    do k = pmc_ks, pmc_ke
+    do i = pmc_is, pmc_ie
+       c = c + 1
+       pressure = grid%p(i,k,j) + grid%pb(i,k,j)
+       pres(c) = pressure
+       temp(c) = (grid%t_2(i,k,j) + t0) * (pressure / p0)**rcp
+       qsat = 3.8d0 * exp(17.27 * (temp(c) - 273.0d0) / (temp(c) - 36.0d0)) / (.01 * pressure)
+       rh(c) = max(.1d0, min(real(grid%moist(i,k,j,p_qv), dp) / qsat, .95d0))   ! rel_hum, :649-666
+       alt(c) = grid%alt(i,k,j)
+       cvol(c) = env_states(i,k,j)%cell_volume
+    end do
+    end do
+    end do
+    args%temp = c_loc(temp)
+    args%pressure = c_loc(pres)
+    args%rel_humid = c_null_ptr          ! water uptake carries RH from step to step
+    args%inverse_density = c_loc(alt)
+    args%cell_volume = c_loc(cvol)
+    args%elapsed_time = real(real_time(domain_get_time_since_sim_start(grid)), kind=dp)
+    args%dt = real(grid%dt, dp)
+    args%chem_dt = real(grid%partmc_chem_dt, dp)
+    args%do_coagulation = merge(1, 0, grid%do_coagulation)
+    args%coag_kernel_type = PMCGPU_KERNEL_BROWN   ! wrf_pmc_driver.F90:192
+    args%do_condensation = merge(1, 0, grid%do_mosaic)
+    args%allow_doubling = merge(1, 0, grid%allow_doubling)
+    args%allow_halving = merge(1, 0, grid%allow_halving)
+    args%step = pmc_gpu_step
+    args%num_conc_out = c_loc(num_conc)
+    args%rel_humid_out = c_null_ptr
+    args%no_wait = 0
+    pmc_gpu_step = pmc_gpu_step + 1
+    call pmc_gpu_check(pmcgpu_partmc_timestep(pmc_gpu_handle, args), 'pmcgpu_partmc_timestep')
+    ! partmc_to_wrf (wrf_pmc_driver.F90:1704-1719)
+    c = 0
+    do j = pmc_js, pmc_je
+    do k = pmc_ks, pmc_ke
+    do i = pmc_is, pmc_ie
+       grid%chem(i,k,j,p_NUM_CONC_a01:p_NUM_CONC_a01 + n_class - 1) = &
+            num_conc(c * n_class + 1:(c + 1) * n_class)
+       c = c + 1
+    end do
+    end do
+    end do
+  end subroutine pmc_gpu_partmc_timestep
+
+  !> Drop-in for wrf_pmc_trans_driver (interface/wrf_pmc_trans.F90:37-200): WRF's per-class
+  !! advective fluxes and mixing coefficients of the patch (memory order i, k, j, class) go to
+  !! the device; probabilities, sampling, ghost exchange and add + rebalance + sort run there.
+  subroutine pmc_gpu_wrf_pmc_trans_driver(grid, config_flags, pmc_is, pmc_ie, pmc_js, pmc_je, &
+       pmc_ks, pmc_ke, global_nx, global_ny, global_nz)
+    use module_domain, only: domain
+    use module_configure, only: grid_config_rec_type
+    type(domain), intent(inout) :: grid
+    type(grid_config_rec_type), intent(in) :: config_flags
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    integer, intent(in) :: global_nx, global_ny, global_nz
+
+    type(pmcgpu_trans_args_t) :: args
+    integer :: n_class
+    real(c_float), allocatable, target :: u(:,:,:,:), v(:,:,:,:), w(:,:,:,:)
+    real(c_float), allocatable, target :: xkhh(:,:,:), alt(:,:,:), z(:,:,:), zw(:,:,:), kv(:,:,:)
+
+    n_class = size(grid%u_flux, 4) - 1
+    ! contiguous copies of the patch sections (the flux arrays carry the class index last; index 1
+    ! of that dimension is WRF's dummy scalar, wrf_pmc_trans.F90:229)
+    u = grid%u_flux(pmc_is:pmc_ie + 1, pmc_ks:pmc_ke, pmc_js:pmc_je, 2:n_class + 1)
+    v = grid%v_flux(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je + 1, 2:n_class + 1)
+    w = grid%w_flux(pmc_is:pmc_ie, pmc_ks:pmc_ke + 1, pmc_js:pmc_je, 2:n_class + 1)
+    xkhh = grid%xkhh(pmc_is - 1:pmc_ie + 1, pmc_ks:pmc_ke, pmc_js - 1:pmc_je + 1)
+    alt = grid%alt(pmc_is - 1:pmc_ie + 1, pmc_ks:pmc_ke, pmc_js - 1:pmc_je + 1)
+    z = grid%z(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je)
+    zw = grid%z_at_w(pmc_is:pmc_ie, pmc_ks:pmc_ke + 1, pmc_js:pmc_je)
+    kv = grid%exch_h(pmc_is:pmc_ie, pmc_ks:pmc_ke + 1, pmc_js:pmc_je)
+    args%u_flux = c_loc(u)
+    args%v_flux = c_loc(v)
+    args%w_flux = c_loc(w)
+    args%xkhh = c_loc(xkhh)
+    args%alt = c_loc(alt)
+    args%z = c_loc(z)
+    args%z_at_w = c_loc(zw)
+    args%exch_h = c_loc(kv)
+    args%dx = grid%dx
+    args%dy = grid%dy
+    args%dt = grid%dt
+    args%vertmix_onoff = config_flags%vertmix_onoff
+    args%allow_doubling = merge(1, 0, grid%allow_doubling)
+    args%allow_halving = merge(1, 0, grid%allow_halving)
+    args%step = pmc_gpu_step
+    args%no_wait = 0
+    pmc_gpu_step = pmc_gpu_step + 1
+    call pmc_gpu_check(pmcgpu_wrf_pmc_trans_driver(pmc_gpu_handle, args), &
+         'pmcgpu_wrf_pmc_trans_driver')
+  end subroutine pmc_gpu_wrf_pmc_trans_driver
+
+end module pmc_gpu
