@@ -231,10 +231,12 @@ def run_b200(a):
     sp = case["sp"]
     data = W.AeroData(sp["density"], sp["kappa"], sp["molec_weight"], sp["num_ions"], sp["i_water"])
     cap = int(2.5 * a.n_per_cell) + 64
-    # ranks tile the global domain along x (weak scaling: one K4 patch per GPU)
+    # weak scaling: one K4 patch per GPU, patches arranged px x py like WRF's processor grid
+    from wrf_partmc_b200.host import decomp
+    px, py = decomp.patch_grid(world)
+    ext = decomp.patch_extents(rank, px, py, a.nx, a.ny)
     g = W.PartMCGPU(data, nx=a.nx, nz=a.nz, ny=a.ny, n_group=1, n_class=case["n_class"],
-                    n_part_ideal=case["n_part_ideal"], cell_capacity=cap, max_bins=64, seed=7, device=local,
-                    global_nx=a.nx * world, global_ny=a.ny, i_offset=a.nx * rank, j_offset=0)
+                    n_part_ideal=case["n_part_ideal"], cell_capacity=cap, max_bins=64, seed=7, device=local, **ext)
     g.set_particles(case["counts"], case["vol"], case["wgroup"], case["wclass"], case["id"], case["n_primary"],
                     case["hyst"], case["lct"], case["gct"])
     g.set_weights(case["wtype"], case["wmag"], case["wexp"])
@@ -247,14 +249,8 @@ def run_b200(a):
         f_glob = synthetic.transport_fields(case, g.partmc_to_wrf(), dt=TRANS_DT)
         f_patch = synthetic.patch_fields(f_glob, 0, a.nx, 0, a.ny)
         if world > 1:
-            px, py = (world, 1) if world < 4 else (world // 2, 2)
-            if rank == 0:
-                uid = torch.frombuffer(bytearray(W.comm_unique_id()), dtype=torch.uint8).clone()
-            else:
-                uid = torch.zeros(128, dtype=torch.uint8)
-            uid = uid.to(torch.device("cuda", local))
-            dist.broadcast(uid, 0)
-            g.comm_init(bytes(uid.cpu().numpy().tobytes()), world, rank, px, py)
+            uid = decomp.broadcast_unique_id(W.comm_unique_id, rank, device=torch.device("cuda", local))
+            g.comm_init(uid, world, rank, px, py)
 
     n_seq = a.warmup + a.steps
     met = synthetic.met_sequence(case, 2 * n_seq)
@@ -327,14 +323,10 @@ def run_b200(a):
     d2h = n_cells * case["n_class"] * 4 + 4
 
     # ---- max over ranks, sum of particles
-    t = torch.tensor([ms * 1e-3, e2e_s], dtype=torch.float64, device=dev)
-    npart = torch.tensor([n_avg, 0.5 * (n_end + n_end2)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(npart, op=dist.ReduceOp.SUM)
-    t_dev, t_e2e = float(t[0]), float(t[1])
-    value = float(npart[0]) * a.steps / t_dev
-    e2e = float(npart[1]) * a.steps / t_e2e
+    t, npart = decomp.reduce_job([ms * 1e-3, e2e_s], [n_avg, 0.5 * (n_end + n_end2)], device=dev)
+    t_dev, t_e2e = t
+    value = npart[0] * a.steps / t_dev
+    e2e = npart[1] * a.steps / t_e2e
 
     if rank == 0:
         peaks = {}

@@ -1,0 +1,102 @@
+"""Worker of the multi-rank tests (spawned once per rank by test_multirank.py).
+
+cpu mode : world_size ranks on the gloo backend exercise the host-side decomposition logic
+           (wrf-partmc_b200/host/decomp.py): patch grid, neighbour table, NCCL-id broadcast, job reduction.
+gpu mode : one rank per GPU; every rank owns one x-patch of a doubly periodic domain, the particle halos
+           travel through libpmcgpu.so's ncclSend / ncclRecv; every rank dumps its cells for the parent,
+           which compares them bit for bit with the oracle's emulation of the same decomposition.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+
+
+def patch_case(case, i0, nxl, j0, nyl):
+    """the cells [i0, i0+nxl) x all k x [j0, j0+nyl) of a global case, in the patch's own cell order"""
+    gnx, nz = case["nx"], case["nz"]
+    cells = np.array([(i0 + il) + gnx * (k + nz * (j0 + jl)) for jl in range(nyl) for k in range(nz)
+                      for il in range(nxl)])
+    off = np.concatenate([[0], np.cumsum(case["counts"])])
+    idx = np.concatenate([np.arange(off[c], off[c + 1]) for c in cells])
+    out = dict(case)
+    out.update(n_cells=len(cells), nx=nxl, ny=nyl, counts=case["counts"][cells], vol=case["vol"][:, idx])
+    for k in ("wclass", "wgroup", "id", "n_primary", "hyst", "lct", "gct"):
+        out[k] = case[k][idx]
+    for k in ("wtype", "wmag", "wexp", "T", "P", "RH", "rrho", "cell_volume"):
+        if k in case:
+            out[k] = case[k][cells]
+    out["cells"] = cells
+    return out
+
+
+def global_case(cfg):
+    from wrf_partmc_b200.host import synthetic
+    return synthetic.make_patch(cfg["gnx"], cfg["nz"], cfg["gny"], cfg["n_per_cell"], cfg["n_spec"], seed=cfg["seed"])
+
+
+def run_cpu(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from wrf_partmc_b200.host import decomp
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    px, py = decomp.patch_grid(world)
+    uid = decomp.broadcast_unique_id(lambda: bytes(range(128)), rank)
+    nb = decomp.neighbours(rank, px, py)
+    ext = decomp.patch_extents(rank, px, py, 5, 3)
+    t, n = decomp.reduce_job([1.0 + rank, 2.0 - rank], [100.0 * (rank + 1), 7.0])
+    np.savez(os.path.join(out_dir, "cpu_%d.npz" % rank), uid=np.frombuffer(uid, np.uint8), nb=nb, px=px, py=py,
+             ext=np.array([ext["global_nx"], ext["global_ny"], ext["i_offset"], ext["j_offset"]]), t=t, n=n)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def run_gpu(rank, world, port, out_dir, cfg):
+    import torch.distributed as dist
+    import wrf_partmc_b200 as W
+    from wrf_partmc_b200.host import decomp, synthetic
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    px, py = cfg["px"], cfg["py"]
+    nxl, nyl = cfg["gnx"] // px, cfg["gny"] // py
+    rx, ry = decomp.patch_of_rank(rank, px, py)
+    case = global_case(cfg)
+    pc = patch_case(case, rx * nxl, nxl, ry * nyl, nyl)
+    sp = case["sp"]
+    data = W.AeroData(sp["density"], sp["kappa"], sp["molec_weight"], sp["num_ions"], sp["i_water"])
+    g = W.PartMCGPU(data, nx=nxl, nz=cfg["nz"], ny=nyl, n_group=1, n_class=case["n_class"],
+                    n_part_ideal=case["n_part_ideal"], cell_capacity=3 * cfg["n_per_cell"] + 64, seed=case["seed"],
+                    device=rank, global_nx=cfg["gnx"], global_ny=cfg["gny"], i_offset=rx * nxl, j_offset=ry * nyl)
+    g.set_particles(pc["counts"], pc["vol"], pc["wgroup"], pc["wclass"], pc["id"], pc["n_primary"], pc["hyst"],
+                    pc["lct"], pc["gct"])
+    g.set_weights(pc["wtype"], pc["wmag"], pc["wexp"])
+    g.set_env(temp=pc["T"], pressure=pc["P"], rel_humid=pc["RH"], inverse_density=pc["rrho"],
+              cell_volume=pc["cell_volume"])
+    N = int(case["counts"].sum())
+    g.set_next_id(np.full(pc["n_cells"], N // case["n_cells"] + 2, np.int64))
+    uid = decomp.broadcast_unique_id(W.comm_unique_id, rank)
+    g.comm_init(uid, world, rank, px, py)
+    nc = np.load(os.path.join(out_dir, "num_conc.npy"))
+    f = synthetic.transport_fields(case, nc)
+    fp = synthetic.patch_fields(f, rx * nxl, nxl, ry * nyl, nyl)
+    moved = 0
+    for step in range(1, cfg["n_steps"] + 1):
+        g.wrf_pmc_trans_driver(fp, step=step)
+        moved += int(g.trans_moved().sum())
+    P = g.get_particles()
+    _, m, _ = g.get_weights()
+    nb, gmin, gmax = g.grid()
+    np.savez(os.path.join(out_dir, "gpu_%d.npz" % rank), cells=pc["cells"], count=P["count"], vol=P["vol"], id=P["id"],
+             wclass=P["wclass"], n_primary=P["n_primary"], wmag=m, nb=nb, gmin=gmin, gmax=gmax, moved=moved,
+             next_id=g.get_next_id())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def main(rank, mode, world, port, out_dir, cfg):
+    if mode == "cpu":
+        run_cpu(rank, world, port, out_dir)
+    else:
+        run_gpu(rank, world, port, out_dir, cfg)

@@ -1,0 +1,115 @@
+"""The N > 1 path.
+
+CPU (gloo, world_size 2 and 4): the host-side decomposition logic every rank runs before it calls the
+library: patch grid, neighbour table (MPI_Cart_shift order of interface/wrf_pmc_trans_aero.F90:153-159),
+broadcast of the NCCL id, max-over-ranks / sum-over-ranks reduction of the benchmark.
+GPU (needs >= 2 devices, skipped otherwise; run with `gpurun --gpus 2`): two ranks, one x-patch each, particle
+halos through ncclSend / ncclRecv inside libpmcgpu.so; the union of the ranks' cells must equal, bit for bit,
+the oracle's emulation of the same 2 x 1 decomposition (arrival order, ids, weights, bin grids)."""
+import os
+import socket
+import tempfile
+
+import numpy as np
+import pytest
+
+import multirank_worker as MW
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _spawn(mode, world, out_dir, cfg=None):
+    import torch.multiprocessing as mp
+    mp.spawn(MW.main, args=(mode, world, _free_port(), out_dir, cfg), nprocs=world, join=True)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_decomposition_host_logic_gloo(world):
+    from wrf_partmc_b200.host import decomp
+    with tempfile.TemporaryDirectory() as d:
+        _spawn("cpu", world, d)
+        r = [np.load(os.path.join(d, "cpu_%d.npz" % k)) for k in range(world)]
+    px, py = int(r[0]["px"]), int(r[0]["py"])
+    assert px * py == world and px >= py
+    for k in range(world):
+        assert np.array_equal(r[k]["uid"], np.arange(128, dtype=np.uint8))  # everybody holds rank 0's id
+        nb = r[k]["nb"]
+        # the neighbour relation is symmetric: my y- neighbour has me as y+, my x- neighbour has me as x+
+        assert r[nb[0]]["nb"][1] == k and r[nb[1]]["nb"][0] == k
+        assert r[nb[2]]["nb"][3] == k and r[nb[3]]["nb"][2] == k
+        rx, ry = decomp.patch_of_rank(k, px, py)
+        assert list(r[k]["ext"]) == [5 * px, 3 * py, 5 * rx, 3 * ry]
+        # max over ranks of the times, sum over ranks of the particles
+        assert list(r[k]["t"]) == [float(world), 2.0]
+        assert list(r[k]["n"]) == [100.0 * world * (world + 1) / 2, 7.0 * world]
+    # patches tile the global domain exactly once
+    seen = set()
+    for k in range(world):
+        gnx, gny, i0, j0 = r[k]["ext"]
+        for i in range(i0, i0 + 5):
+            for j in range(j0, j0 + 3):
+                assert (i, j) not in seen
+                seen.add((i, j))
+    assert len(seen) == 5 * px * 3 * py
+
+
+def test_patch_slicing_matches_global_cell_order():
+    """the patch a rank uploads is the global case restricted to its cells, in WRF memory order"""
+    cfg = dict(gnx=4, nz=3, gny=2, n_per_cell=20, n_spec=4, seed=3)
+    case = MW.global_case(cfg)
+    seen = []
+    for rx in range(2):
+        pc = MW.patch_case(case, rx * 2, 2, 0, 2)
+        assert pc["n_cells"] == 12 and pc["vol"].shape[1] == pc["counts"].sum()
+        seen += list(pc["cells"])
+        off = np.concatenate([[0], np.cumsum(case["counts"])])
+        c0 = pc["cells"][0]
+        assert np.array_equal(pc["id"][:pc["counts"][0]], case["id"][off[c0]:off[c0 + 1]])
+    assert sorted(seen) == list(range(case["n_cells"]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_spec", [4, 20])
+def test_two_rank_transport_bit_exact(n_spec):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    import common
+    from oracle import oracle as O
+    from wrf_partmc_b200.host import synthetic
+    cfg = dict(gnx=8, nz=4, gny=3, px=2, py=1, n_per_cell=200, n_spec=n_spec, seed=5, n_steps=3)
+    case = MW.global_case(cfg)
+    o = common.oracle_from_case(O, case)
+    for c in range(case["n_cells"]):
+        o.set_env(c, T=case["T"][c], p=case["P"][c], RH=case["RH"][c], rrho=case["rrho"][c],
+                  cell_volume=case["cell_volume"][c])
+    o.trans_setup(cfg["gnx"], cfg["nz"], cfg["gny"], px=2, py=1)
+    nc = o.num_conc_by_class()
+    f = synthetic.transport_fields(case, nc)
+    with tempfile.TemporaryDirectory() as d:
+        np.save(os.path.join(d, "num_conc.npy"), nc)
+        _spawn("gpu", 2, d, cfg)
+        r = [dict(np.load(os.path.join(d, "gpu_%d.npz" % k))) for k in range(2)]
+    moved = sum(o.wrf_pmc_trans_driver(f, step=s) for s in range(1, cfg["n_steps"] + 1))
+    assert moved == sum(int(x["moved"]) for x in r) and moved > 0
+    n_checked = 0
+    for x in r:
+        off = np.concatenate([[0], np.cumsum(x["count"])])
+        for lc, c in enumerate(x["cells"]):
+            q = o.get_cell(int(c))
+            a, b = off[lc], off[lc + 1]
+            assert b - a == q["vol"].shape[1], (c, b - a, q["vol"].shape[1])
+            assert np.array_equal(x["id"][a:b], q["id"]) and np.array_equal(x["wclass"][a:b], q["wclass"])
+            assert np.array_equal(x["vol"][:, a:b], q["vol"])
+            np.testing.assert_allclose(x["wmag"][lc].ravel(), o.get_weights(int(c))[1], rtol=1e-14)
+            onb, omin, omax, _ = o.grid(int(c))
+            assert x["nb"][lc] == onb
+            assert x["next_id"][lc] == o.L.pmco_get_next_id(o.h, int(c))
+            n_checked += 1
+    assert n_checked == case["n_cells"]
