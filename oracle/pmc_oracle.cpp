@@ -1025,7 +1025,10 @@ static void per_set_coag(int type, double k_max, const EnvState& env, const Aero
 // coagulation.F90:333-517 (components are cold data and not carried)
 static void sample_source_particle(AeroState& st, const AeroData& d, const EnvState& env, int type, int bs, int cs,
                                    const Particle& coag_particle, double n_samp_mean, double accept_factor,
-                                   Stream& s, int& n_samp, int& n_coag, int& n_remove, Particle& source) {
+                                   Stream& s, Stream& ss, int& n_samp, int& n_coag, int& n_remove, Particle& source) {
+  // Draw addresses: `s` is the sequential stream of the target (Poisson counts, binomial, prob_round,
+  // rand_group, dup); the three draws of sample i_samp sit at positions 3 (i_samp - 1) + {0, 1, 2} of the
+  // sample stream `ss`, so that a parallel implementation can evaluate candidate samples ahead of time.
   if (st.sorted.size_class.inv(bs, cs).n_entry() == 0) {
     n_samp = 0; n_remove = 0; n_coag = 0;
     return;
@@ -1055,7 +1058,9 @@ static void sample_source_particle(AeroState& st, const AeroData& d, const EnvSt
       for (int k = 0; k < S; k++) {
         const double vol_mean = source.vol[k] / (double)n_avg;
         if (vol_mean > 0.0) {
-          const double cv = std::sqrt(vol_sq[k] / (double)n_avg - vol_mean * vol_mean) / vol_mean;
+          // the variance is clamped at zero: rounding can make it slightly negative when every accepted
+          // sample is the same particle, and the reference's sqrt would then hand a NaN to maxval
+          const double cv = std::sqrt(std::max(0.0, vol_sq[k] / (double)n_avg - vol_mean * vol_mean)) / vol_mean;
           vol_cv_max = any ? std::max(vol_cv_max, cv) : cv;
           any = true;
         }
@@ -1064,13 +1069,14 @@ static void sample_source_particle(AeroState& st, const AeroData& d, const EnvSt
       if (mean_95_conf_cv < COAG_ACCEL_MAX_CV) break;
     }
     n_samp = n_samp + 1;
+    ss.j = 3u * (uint32_t)(i_samp - 1);
     const int ne = st.sorted.size_class.inv(bs, cs).n_entry();
-    const int i_unif_entry = pmc_rand_int(s.next(), ne);
+    const int i_unif_entry = pmc_rand_int(ss.next(), ne);
     const int i_part = st.sorted.size_class.inv(bs, cs).at(i_unif_entry);
     const double k = num_conc_weighted_kernel(type, st.apa[i_part - 1], coag_particle, cs, ct, ct, d, st.awa, env);
     const double prob_coag = k * accept_factor;
     prob_coag_tot = prob_coag_tot + prob_coag;
-    if (s.next() < prob_coag) {
+    if (ss.next() < prob_coag) {
       n_avg = n_avg + 1;
       Particle tmp;
       particle_coagulate(source, st.apa[i_part - 1], tmp);
@@ -1079,7 +1085,7 @@ static void sample_source_particle(AeroState& st, const AeroData& d, const EnvSt
       if (i_samp <= n_samp_remove) {
         const double num_conc_i = awa_num_conc(st.awa, st.apa[i_part - 1]);
         const double prob_remove_i = num_conc_target / num_conc_i;
-        if (s.next() < prob_remove_i / prob_remove_source_max) {
+        if (ss.next() < prob_remove_i / prob_remove_source_max) {
           n_remove = n_remove + 1;
           aero_state_remove_particle(st, i_part);
         }
@@ -1140,9 +1146,10 @@ static bool try_per_particle_coag(int type, double k_max, const EnvState& env, c
     const int target_part = st.sorted.size_class.inv(bt, ct).at(e);
     const Particle target_particle = st.apa[target_part - 1];
     Stream s(rc.rng, rc.key(PH_COAG_ACCEL, pid, (uint32_t)e));
+    Stream ss(rc.rng, rc.key(PH_COAG_ACCEL, pid | 0x80000000u, (uint32_t)e));
     int n_samp, n_coag, n_remove;
     Particle source;
-    sample_source_particle(st, d, env, type, bs, cs, target_particle, n_source_per_target, accept_factor, s, n_samp,
+    sample_source_particle(st, d, env, type, bs, cs, target_particle, n_source_per_target, accept_factor, s, ss, n_samp,
                            n_coag, n_remove, source);
     if (n_coag > 0) coag_target_with_source(st, bt, ct, e, source, cc, s);
     out.tot_n_samp += n_samp;

@@ -236,19 +236,29 @@ def test_golovin_on_device(mods):
     assert errs[:, 0].mean() < 0.15 and errs[:, 1].mean() < 0.45, errs
 
 
-def test_accelerated_path_is_reported(mods):
-    """When determine_target_and_source / compute_n_source (coagulation.F90:247-329) select the
-    accelerated per-particle path, the oracle takes it (n_accel_pairs > 0) and the device, which
-    does not build that path yet, must say so (PMCGPU_ERR_ACCEL) instead of doing something else."""
+@pytest.mark.parametrize("weight,n_spec,n_class,n_group,n_per,n_cells,dt", [
+    ("flat", 3, 2, 1, 600, 12, 7200.0), ("flat", 20, 3, 1, 400, 6, 10000.0), ("nummass", 3, 1, 2, 1500, 4, 3600.0),
+    ("nummass", 1, 2, 2, 800, 6, 7200.0)])
+def test_accelerated_per_particle_coag_bit_exact(mods, weight, n_spec, n_class, n_group, n_per, n_cells, dt):
+    """try_per_particle_coag (coagulation.F90:150-241): when determine_target_and_source / compute_n_source
+    (:247-329) select the accelerated path, the device takes it like the oracle: same sample counts, same
+    events, same particles (ids, groups, volumes bit for bit) in the same order, over several steps."""
     W, O = mods
-    case = common.make_cells(12, 600, n_spec=3, n_class=2, seed=33, num_conc=3e11)
+    case = common.make_cells(n_cells, n_per, n_spec=n_spec, n_class=n_class, n_group=n_group, weight=weight,
+                             seed=33, num_conc=3e11)
     g = common.gpu_from_case(W, case)
     o = common.oracle_from_case(O, case)
     acc = 0
-    for c in range(12):
-        o.sort(c, force_resort=True, physical=True, edge_recheck=True)
-        acc += o.mc_coag(c, O.KERNEL_BROWN, 36000.0, step=0)[2]
-    assert acc > 0
-    with pytest.raises(W.PmcGpuError) as ei:
-        g.mc_coag(W.KERNEL_BROWN, 36000.0, step=0)
-    assert ei.value.code == 6
+    events = 0
+    for step in range(3):
+        ns, nc = g.mc_coag(W.KERNEL_BROWN, dt, step=step)
+        for c in range(n_cells):
+            o.sort(c, force_resort=True, physical=True, edge_recheck=True)
+            s, k, a = o.mc_coag(c, O.KERNEL_BROWN, dt, step=step)
+            acc += a
+            assert (s, k) == (ns[c], nc[c]), "cell %d step %d: oracle (%d,%d) device (%d,%d)" % (c, step, s, k, ns[c], nc[c])
+        events += int(nc.sum())
+        common.assert_same_population(g, o, case)
+        assert np.array_equal(g.get_next_id(), [o.L.pmco_get_next_id(o.h, c) for c in range(n_cells)])
+    assert acc > 0, "the case must select the accelerated path"
+    assert events > 20

@@ -27,6 +27,7 @@ static const double BETA_1 = 1000.0;
 static const double BETA_0 = 0.25 / (60.0 * 2e8);
 #define COAG_ACCEL_N_EVENT 1.0
 #define MAX_ALLOWABLE_GROWTH_FACTOR 1.5
+#define COAG_ACCEL_MAX_CV 0.1
 
 struct CellCtx {
   const DevView* v;
@@ -266,6 +267,297 @@ __device__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1, int c2, int 
   }
 }
 
+// stats.F90:510-546
+__device__ __forceinline__ double student_t_95_coeff(int n_sample) {
+  const double limit = 1.959963984540054;
+  const int n_dof = n_sample - 1;
+  if (n_dof <= 15) {
+    switch (n_dof) {
+      case 1: return 12.7062047364;
+      case 2: return 4.30265272991;
+      case 3: return 3.18244630528;
+      case 4: return 2.7764451052;
+      case 5: return 2.57058183661;
+      case 6: return 2.44691184879;
+      case 7: return 2.36462425101;
+      case 8: return 2.30600413503;
+      case 9: return 2.26215716274;
+      case 10: return 2.22813885196;
+      case 11: return 2.20098516008;
+      case 12: return 2.17881282966;
+      case 13: return 2.16036865646;
+      case 14: return 2.14478668792;
+      default: return 2.13144954556;
+    }
+  }
+  if (n_dof <= 20) return (2.11990529922 - limit) * 16.0 / (double)n_dof + limit;
+  return (2.07961384473 - limit) * 21.0 / (double)n_dof + limit;
+}
+
+// determine_target_and_source (coagulation.F90:247-307) for bins (b1, b2) of classes (c1, c2); the
+// monotone_decreasing test over the whole weight array is done by the caller.
+__device__ __forceinline__ bool accel_target_source(const CellCtx& cx, bool pair_flat, const double* hm, int b1,
+                                                    int b2, int c1, int c2, int cc, int& bt, int& bs, int& ct,
+                                                    int& cs) {
+  const DevView& v = *cx.v;
+  double nc1_min, nc1_max, nc2_min, nc2_max;
+  if (pair_flat) {
+    nc1_min = nc1_max = hm[c1 - 1];
+    nc2_min = nc2_max = hm[c2 - 1];
+  } else {
+    const double a1 = awa_nc_at_radius(v, cx.cell, c1, grid_edge(cx.gmin, cx.gmax, cx.nb, b1));
+    const double a2 = awa_nc_at_radius(v, cx.cell, c1, grid_edge(cx.gmin, cx.gmax, cx.nb, b1 + 1));
+    const double e1 = awa_nc_at_radius(v, cx.cell, c2, grid_edge(cx.gmin, cx.gmax, cx.nb, b2));
+    const double e2 = awa_nc_at_radius(v, cx.cell, c2, grid_edge(cx.gmin, cx.gmax, cx.nb, b2 + 1));
+    nc1_min = fmin(a1, a2); nc1_max = fmax(a1, a2);
+    nc2_min = fmin(e1, e2); nc2_max = fmax(e1, e2);
+  }
+  bool ok = false;
+  if ((nc1_max < nc2_min) && (cc == c1)) { bt = b1; bs = b2; ct = c1; cs = c2; ok = true; }
+  if ((nc2_max < nc1_min) && (cc == c2)) { bt = b2; bs = b1; ct = c2; cs = c1; ok = true; }
+  return ok;
+}
+
+// aero_weight_array_rand_group (aero_weight_array.F90:374) -> sample_cts_pdf (rand.F90:550) on the
+// sequential stream s: two draws per rejection round, also when there is a single group
+__device__ __forceinline__ int rand_group_seq(const CellCtx& cx, int c, double radius, RStream& s) {
+  const DevView& v = *cx.v;
+  if (v.G == 1) {
+    s.j += 2;
+    return 1;
+  }
+  const size_t wb = ((size_t)cx.cell * v.C + (c - 1)) * v.G;
+  double pdf_max = 0.0;
+  for (int g = 0; g < v.G; g++) pdf_max = fmax(pdf_max, 1.0 / weight_nc(v.wtype[wb + g], v.wmag[wb + g], v.wexp[wb + g], radius));
+  for (;;) {
+    const int k = pmc_rand_int(s.next(), v.G);
+    const double pk = 1.0 / weight_nc(v.wtype[wb + k - 1], v.wmag[wb + k - 1], v.wexp[wb + k - 1], radius);
+    if (s.next() < pk / pdf_max) return k;
+  }
+}
+
+// integer_rmap2_change (integer_rmap2.F90:139-185) on size_class for slot p of class c: only the bin
+// changes on the accelerated path (ct == cc); an unchanged bin returns early like the reference (:160)
+__device__ void cell_change_bin(CellCtx& cx, int p, int c, int new_bin) {
+  const DevView& v = *cx.v;
+  const int b_old = v.pbin[cx.base + p];
+  if (b_old == new_bin) return;
+  __syncwarp();
+  if (cx.lane == 0) {
+    const int k_old = lkey(cx, c, b_old);
+    const int lp = cx.lptr[k_old];
+    const int pos_old = v.fidx[cx.base + p];
+    const int pos_last = cx.llen[k_old] - 1;
+    if (pos_old < pos_last) {
+      const int moved = cx.L[lp + pos_last];
+      cx.L[lp + pos_old] = moved;
+      v.fidx[cx.base + moved] = pos_old;
+    }
+    cx.llen[k_old] = pos_last;
+    v.pbin[cx.base + p] = new_bin;
+  }
+  __syncwarp();
+  cell_list_append(cx, c, new_bin, p);
+}
+
+// aero_state_dup_particle (aero_state.F90:488-539) for the sorted state of mc_coag: slot p of class c
+__device__ void cell_dup_particle(CellCtx& cx, int p, int c, double n_part_mean, bool random_weight_group,
+                                  RStream& s) {
+  const DevView& v = *cx.v;
+  const int n_copies = prob_round(n_part_mean, s.next());
+  if (n_copies == 0) {
+    cell_remove_particle(cx, p);
+    return;
+  }
+  for (int i_dup = 1; i_dup <= n_copies - 1 && !cx.err; i_dup++) {
+    int new_group = 0;
+    if (random_weight_group) {
+      double vt, mt;
+      part_vol_mass(cx, p, vt, mt);
+      new_group = rand_group_seq(cx, c, vol2rad(vt), s);
+    }
+    if (cx.n_part >= v.cap) {
+      cx.err = PMCGPU_ERR_CAPACITY;
+      return;
+    }
+    const int slot = cx.n_part;
+    const int b = v.pbin[cx.base + p];
+    __syncwarp();
+    move_record(cx, slot, p);
+    __syncwarp();
+    if (cx.lane == 0) {
+      // aero_particle_new_id (aero_particle.F90:141-149) with one counter per cell
+      const long long nx = v.next_id[cx.cell];
+      v.id[cx.base + slot] = (nx - 1) * v.n_cells_global + v.gcell[cx.cell] + 1;
+      v.next_id[cx.cell] = nx + 1;
+      if (new_group) v.wgc[cx.base + slot] = (c - 1) * v.G + (new_group - 1);
+      v.pbin[cx.base + slot] = b;
+    }
+    cx.n_part = slot + 1;
+    __syncwarp();
+    cell_list_append(cx, c, b, slot);
+  }
+}
+
+// try_per_particle_coag (coagulation.F90:150-241) for a bin pair the scan found eligible: every target
+// particle (backwards through its bin) coagulates with the average of a sample of source particles
+// (sample_source_particle :333-517, coag_target_with_source :522-582).  Warp-cooperative: the 32 lanes
+// evaluate the kernel of 32 candidate samples ahead (their draws are addressed by sample number), the
+// warp then consumes them in order with the running sums held one species per lane; a removal of a
+// source particle invalidates the candidates behind it, which are re-evaluated.
+__device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const BrownEnv& be, double k_max, double del_t, unsigned step,
+                                unsigned pid, int bt, int bs, int ct, int cs, int cc, int& tot_n_samp,
+                                int& tot_n_coag) {
+  const DevView& v = *cx.v;
+  constexpr int NQ = (PMC_MAX_SPEC + 31) / 32;
+  const int kt = lkey(cx, ct, bt), ks = lkey(cx, cs, bs);
+  const double n_samp_mean = k_max * del_t * (double)cx.llen[ks];  // compute_n_source :310-329
+  const double accept_factor = 1.0 / k_max;
+  for (int e = cx.llen[kt]; e >= 1 && !cx.err; e--) {
+    __syncwarp();
+    const int target0 = cx.L[cx.lptr[kt] + e - 1];
+    double v_t, m_t;
+    part_vol_mass(cx, target0, v_t, m_t);
+    const double r_t = vol2rad(v_t);
+    RStream s{RKey{v.seed, (unsigned)v.gcell[cx.cell], step, PH_COAG_ACCEL, pid, (unsigned)e}, 0u};
+    const RKey skey{v.seed, (unsigned)v.gcell[cx.cell], step, PH_COAG_ACCEL, pid | 0x80000000u, (unsigned)e};
+    int n_samp = 0, n_coag = 0, n_avg = 0;
+    if (cx.llen[ks] == 0) continue;
+    const double num_conc_target = awa_nc_at_radius(v, cx.cell, ct, r_t);
+    const double num_conc_source_min = awa_nc_at_radius(v, cx.cell, cs, grid_edge(cx.gmin, cx.gmax, cx.nb, bs));
+    const double prob_remove_source_max = num_conc_target / num_conc_source_min;
+    if (!(prob_remove_source_max <= 1.0)) {
+      cx.err = PMCGPU_ERR_ACCEL;  // assert 653606684
+      return;
+    }
+    const int n_samp_remove = rand_poisson(prob_remove_source_max * n_samp_mean, s);
+    const int n_samp_extra = rand_poisson((1.0 - prob_remove_source_max) * n_samp_mean, s);
+    const int n_samp_total = n_samp_remove + n_samp_extra;
+    double prob_coag_tot = 0.0;
+    double src_vol[NQ], vol_sq[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; q++) { src_vol[q] = 0.0; vol_sq[q] = 0.0; }
+    int src_nprim = 0;
+    double src_lct = 0.0, src_gct = 0.0;  // aero_particle_zero
+    int i_samp = 1;
+    bool done = false;
+    while (i_samp <= n_samp_total && !done) {
+      __syncwarp();
+      const int ne = cx.llen[ks];
+      if (ne == 0) break;
+      // ---- candidates i_samp + lane
+      const int my_i = i_samp + cx.lane;
+      int i_part = 0;
+      double prob_coag = 0.0, u_acc = 1.0, u_rem = 1.0, nc_i = 1.0;
+      if (my_i <= n_samp_total) {
+        const unsigned j0 = 3u * (unsigned)(my_i - 1);
+        i_part = cx.L[cx.lptr[ks] + pmc_rand_int(rng_uniform(skey, j0), ne) - 1];
+        double v_i, m_i;
+        part_vol_mass(cx, i_part, v_i, m_i);
+        const double r_i = vol2rad(v_i);
+        const double uk = unweighted_kernel(ktype, be, v_i, m_i, v_t, m_t);
+        prob_coag = (uk * coag_num_conc_factor(cx, r_i, r_t, cs, ct, ct)) * accept_factor;
+        u_acc = rng_uniform(skey, j0 + 1);
+        u_rem = rng_uniform(skey, j0 + 2);
+        nc_i = awa_nc_at_radius(v, cx.cell, cs, r_i);
+      }
+      // ---- in-order consumption
+      int l = 0;
+      for (; l < 32 && i_samp + l <= n_samp_total; l++) {
+        if ((n_samp > n_samp_remove) && (n_avg >= 2)) {
+          double cv_max = 0.0;
+#pragma unroll
+          for (int q = 0; q < NQ; q++) {
+            const double vol_mean = src_vol[q] / (double)n_avg;
+            if (vol_mean > 0.0)
+              cv_max = fmax(cv_max, sqrt(fmax(0.0, vol_sq[q] / (double)n_avg - vol_mean * vol_mean)) / vol_mean);
+          }
+          for (int o = 16; o > 0; o >>= 1) cv_max = fmax(cv_max, __shfl_xor_sync(0xffffffffu, cv_max, o));
+          const double mean_95_conf_cv = cv_max / sqrt((double)n_avg) * student_t_95_coeff(n_avg);
+          if (mean_95_conf_cv < COAG_ACCEL_MAX_CV) {
+            done = true;
+            break;
+          }
+        }
+        n_samp++;
+        const double pc = __shfl_sync(0xffffffffu, prob_coag, l);
+        prob_coag_tot = prob_coag_tot + pc;
+        if (__shfl_sync(0xffffffffu, u_acc, l) < pc) {
+          n_avg++;
+          const int ip = __shfl_sync(0xffffffffu, i_part, l);
+#pragma unroll
+          for (int q = 0; q < NQ; q++) {
+            const int sp = q * 32 + cx.lane;
+            const double x = (sp < v.S) ? v.vol[(size_t)sp * cx.NS + cx.base + ip] : 0.0;
+            src_vol[q] = src_vol[q] + x;
+            vol_sq[q] = vol_sq[q] + x * x;
+          }
+          src_nprim += v.nprim[cx.base + ip];
+          src_gct = fmax(src_gct, v.gct[cx.base + ip]);
+          src_lct = fmin(src_lct, v.lct[cx.base + ip]);
+          if (i_samp + l <= n_samp_remove) {
+            const double prob_remove_i = num_conc_target / __shfl_sync(0xffffffffu, nc_i, l);
+            if (__shfl_sync(0xffffffffu, u_rem, l) < prob_remove_i / prob_remove_source_max) {
+              cell_remove_particle(cx, ip);
+              l++;
+              break;  // the source bin changed: candidates behind this one are stale
+            }
+          }
+        }
+      }
+      i_samp += l;
+    }
+    if (n_avg > 0) {
+      const double prob_coag_mean = prob_coag_tot / (double)n_samp;  // note not n_avg
+      if (!(prob_coag_mean <= 1.0)) {
+        cx.err = PMCGPU_ERR_ACCEL;  // rand_binomial asserts p <= 1 (rand.F90:333)
+        return;
+      }
+      n_coag = rand_binomial(n_samp_total, prob_coag_mean, s);
+      const double f = (double)n_coag / (double)n_avg;
+#pragma unroll
+      for (int q = 0; q < NQ; q++) src_vol[q] = src_vol[q] * f;
+      src_nprim = prob_round((double)src_nprim * ((double)n_coag / n_avg), s.next());
+    }
+    if (n_coag > 0) {
+      // ---- coag_target_with_source (coagulation.F90:522-582)
+      __syncwarp();
+      const int tp = cx.L[cx.lptr[kt] + e - 1];  // re-read: removals may have moved the target
+      double v_old, m_old;
+      part_vol_mass(cx, tp, v_old, m_old);
+      const double old_num_conc_target = awa_nc_at_radius(v, cx.cell, ct, vol2rad(v_old));
+      __syncwarp();
+#pragma unroll
+      for (int q = 0; q < NQ; q++) {
+        const int sp = q * 32 + cx.lane;
+        if (sp < v.S) v.vol[(size_t)sp * cx.NS + cx.base + tp] = v.vol[(size_t)sp * cx.NS + cx.base + tp] + src_vol[q];
+      }
+      if (cx.lane == 0) {
+        v.hyst[cx.base + tp] = 0;  // the averaged source starts from aero_particle_zero: leg 0
+        v.nprim[cx.base + tp] = v.nprim[cx.base + tp] + src_nprim;
+        v.gct[cx.base + tp] = fmax(v.gct[cx.base + tp], src_gct);
+        v.lct[cx.base + tp] = fmin(v.lct[cx.base + tp], src_lct);
+      }
+      __syncwarp();
+      double v_new, m_new;
+      part_vol_mass(cx, tp, v_new, m_new);
+      const double r_new = vol2rad(v_new);
+      const int new_group = rand_group_seq(cx, cc, r_new, s);
+      if (cx.lane == 0) v.wgc[cx.base + tp] = (cc - 1) * v.G + (new_group - 1);
+      const int new_bin = log_grid_find(cx.lnmin, cx.lnmax, cx.nb, log(r_new));
+      if (new_bin < 1 || new_bin > cx.nb) {
+        cx.err = PMCGPU_ERR_BIN_RANGE;
+        return;
+      }
+      cell_change_bin(cx, tp, cc, new_bin);
+      const double new_num_conc_target = awa_nc_at_radius(v, cx.cell, cc, r_new);
+      cell_dup_particle(cx, tp, cc, old_num_conc_target / new_num_conc_target, true, s);
+    }
+    tot_n_samp += n_samp;
+    tot_n_coag += n_coag;
+  }
+}
+
 __global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * COAG_WARPS + warp;
@@ -382,24 +674,9 @@ __global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktyp
             k_max = ktab[(size_t)(my_b2 - 1) * nb + (b1 - 1)] * f_max;
             // determine_target_and_source + compute_n_source (coagulation.F90:247-329)
             if (mono_dec) {
-              double nc1_min, nc1_max, nc2_min, nc2_max;
-              if (pair_flat) {
-                nc1_min = nc1_max = hm[c1 - 1];
-                nc2_min = nc2_max = hm[c2 - 1];
-              } else {
-                const double a1 = awa_nc_at_radius(v, cell, c1, grid_edge(cx.gmin, cx.gmax, nb, b1));
-                const double a2 = awa_nc_at_radius(v, cell, c1, grid_edge(cx.gmin, cx.gmax, nb, b1 + 1));
-                const double e1 = awa_nc_at_radius(v, cell, c2, grid_edge(cx.gmin, cx.gmax, nb, my_b2));
-                const double e2 = awa_nc_at_radius(v, cell, c2, grid_edge(cx.gmin, cx.gmax, nb, my_b2 + 1));
-                nc1_min = fmin(a1, a2); nc1_max = fmax(a1, a2);
-                nc2_min = fmin(e1, e2); nc2_max = fmax(e1, e2);
-              }
-              int bt = 0, bs = 0, ns = 0;
-              bool ok = false;
-              if ((nc1_max < nc2_min) && (cc == c1)) { bt = b1; bs = my_b2; ns = n2; ok = true; }
-              if ((nc2_max < nc1_min) && (cc == c2)) { bt = my_b2; bs = b1; ns = n1; ok = true; }
-              if (ok) {
-                const double n_source_per_target = k_max * del_t * (double)ns;
+              int bt = 0, bs = 0, ct = 0, cs = 0;
+              if (accel_target_source(cx, pair_flat, hm, b1, my_b2, c1, c2, cc, bt, bs, ct, cs)) {
+                const double n_source_per_target = k_max * del_t * (double)((bs == b1 && cs == c1) ? n1 : n2);
                 if (!(n_source_per_target < COAG_ACCEL_N_EVENT)) {
                   const double min_target_vol = rad2vol(grid_edge(cx.gmin, cx.gmax, nb, bt));
                   const double max_source_vol = rad2vol(grid_edge(cx.gmin, cx.gmax, nb, bs + 1));
@@ -430,8 +707,14 @@ __global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktyp
             const double p_kmax = __shfl_sync(0xffffffffu, k_max, f);
             const int p_accel = __shfl_sync(0xffffffffu, accel, f);
             if (p_accel) {
-              cx.err = PMCGPU_ERR_ACCEL;
-              break;
+              const unsigned apid = ((unsigned)((c1 - 1) * v.C + (c2 - 1)) * 256u + (unsigned)b1) * 256u + (unsigned)pb2;
+              const bool pflat = all_flat || (flat[c1 - 1] && flat[c2 - 1]);
+              int bt = 0, bs = 0, ct = 0, cs = 0;
+              accel_target_source(cx, pflat, hm, b1, pb2, c1, c2, p_cc, bt, bs, ct, cs);
+              cell_accel_pair(cx, ktype, be, p_kmax, del_t, step, apid, bt, bs, ct, cs, p_cc, tot_n_samp, tot_n_coag);
+              rescan = true;  // counts changed: pairs behind this one must be rescanned
+              next_b2 = pb2 + 1;
+              continue;
             }
             // ---- per_set_coag (coagulation.F90:587-643)
             tot_n_samp += p_nsamp;
