@@ -113,6 +113,12 @@ int pmcgpu_kernel_bounds(pmcgpu_ctx* ctx, int coag_kernel_type);
  * per-cell outputs [n_cells], may be NULL.  step addresses the random draws. */
 int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned int step, int* tot_n_samp,
                    int* tot_n_coag);
+/* Step number that addresses the random draws of the stand-alone condensation calls below (the
+ * prob_round draws of aero_state_reweight, aero_state.F90:597-653, when weights depend on size);
+ * pmcgpu_partmc_timestep uses its own `step` argument instead.  The reference has one global
+ * stream (rand.F90), which a parallel device cannot reproduce: DESIGN.md section 2. */
+int pmcgpu_set_rng_step(pmcgpu_ctx* ctx, unsigned step);
+
 /* condense_particles (condense.F90:147) for every cell: env_state_initial is the cell's current
  * env_state (pmcgpu_set_env), env_state_final = (temp_final, pressure_final) [n_cells]; on return the
  * device env is the final one with rel_humid from the integrator (condense.F90:263).  reltol <= 0

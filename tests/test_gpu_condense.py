@@ -140,12 +140,76 @@ def test_condense_golden_on_device(mods):
     assert np.linalg.norm(np.array(water) - gw) / np.linalg.norm(gw) < 0.05
 
 
-def test_condense_reports_unbuilt_reweight(mods):
-    """Size-dependent weights need aero_state_reweight after the solve; until that is built the
-    device must refuse rather than skip it."""
+@pytest.mark.parametrize("n_per_mode,steps", [(1500, 12), (5000, 6), (50000, 2)])
+def test_condense_single_box_cells_device_vs_oracle(mods, n_per_mode, steps):
+    """Cells above 2048 particles (single-box runs; K3 = 1e5 particles in one cell) take the grid-wide
+    variant of the integrator (one cell spread over all SMs, cell sums through a grid barrier): RH and
+    wet diameters against the oracle to 1e-10, same accept / reject sequence, water balance < 1e-6."""
     W, O = mods
-    case = common.make_cells(2, 100, n_spec=3, n_group=2, weight="nummass", seed=2, ragged=False)
-    g = common.gpu_from_case(W, case)
-    with pytest.raises(W.PmcGpuError) as ei:
-        g.condense_particles(case["T"] - 0.1, case["P"] - 100.0, 10.0)
-    assert ei.value.code == 10
+    case = common.condense_case(n_per_mode, n_cells=2)
+    case["counts"][1] = 700  # a small cell beside it: both kernel families in one call
+    keep = np.concatenate([np.arange(2 * n_per_mode), 2 * n_per_mode + np.arange(700)])
+    for k in ("wclass", "wgroup", "id", "n_primary", "hyst", "lct", "gct"):
+        case[k] = case[k][keep]
+    case["vol"] = case["vol"][:, keep]
+    g = common.gpu_from_case(W, case, cell_capacity=2 * n_per_mode + 64)
+    o = common.oracle_from_case(O, case)
+    rh0 = np.array([0.95, 0.93])
+    g.set_env(rel_humid=rh0)
+    g.condense_equilib_particles()
+    for c in range(2):
+        o.set_env(c, T=290.0, p=1e5, RH=rh0[c])
+        o.condense_equilib(c)
+    for k in range(steps):
+        t1 = (k + 1) * 10.0
+        T1 = np.full(2, 290.0 - 10.0 * t1 / 1200.0)
+        p1 = np.full(2, 1e5 - 2e4 * t1 / 1200.0)
+        rh, st, wre = g.condense_particles(T1, p1, 10.0)
+        for c in range(2):
+            ost, owre = o.condense_particles(c, T1[c], p1[c], 10.0, step=k, method=4)
+            assert abs(rh[c] / o.env_rel_humid(c) - 1) < 1e-10, (k, c, rh[c], o.env_rel_humid(c))
+            assert (st[c, 0], st[c, 1]) == (ost[0], ost[1]), (k, c, st[c], ost)
+            assert abs(wre[c]) < 1e-6
+    P = g.get_particles()
+    off = np.concatenate([[0], np.cumsum(P["count"])])
+    for c in range(2):
+        q = o.get_cell(c)
+        Dd = (P["vol"][:, off[c]:off[c + 1]].sum(axis=0)) ** (1 / 3)
+        Do = (q["vol"].sum(axis=0)) ** (1 / 3)
+        assert np.abs(Dd / Do - 1).max() < 1e-10
+
+
+@pytest.mark.parametrize("n_per,n_cells", [(400, 3), (3000, 1)])
+def test_condense_reweight_size_dependent_weights(mods, n_per, n_cells):
+    """aero_state_reweight (aero_state.F90:597-653) after condense_equilib_particles and
+    condense_particles with nummass-like weights (group 2: power -3): magnitudes rescaled, particles
+    duplicated / removed by prob_round(old_nc / new_nc) backwards through the array.  The draws are
+    addressed, so the device takes the same decisions as the oracle: same survivors, copies and ids in the
+    same order (volumes agree to the integrator's 1e-10; a ratio within 1e-10 of a draw could flip a
+    decision, which this seed does not hit)."""
+    W, O = mods
+    case = common.make_cells(n_cells, n_per, n_spec=3, n_group=2, weight="nummass", seed=2, ragged=False,
+                             temp=285.0, num_conc=3e9, r_g=4e-8)
+    case["T"][:] = 290.0
+    case["P"][:] = 1e5
+    g = common.gpu_from_case(W, case, cell_capacity=3 * n_per)
+    o = common.oracle_from_case(O, case)
+    rh0 = np.full(n_cells, 0.95)
+    g.set_env(rel_humid=rh0)
+    g.condense_equilib_particles(step=77)
+    for c in range(n_cells):
+        o.set_env(c, T=290.0, p=1e5, RH=rh0[c])
+        o.condense_equilib(c, step=77)
+    n_after_equilib = g.counts().copy()
+    assert not np.array_equal(n_after_equilib, case["counts"]), "equilibration must change some particle counts"
+    common.assert_same_population(g, o, case, exact_fp=False, rtol=1e-9)
+    for k in range(6):
+        t1 = (k + 1) * 10.0
+        T1 = np.full(n_cells, 290.0 - 10.0 * t1 / 1200.0)
+        p1 = np.full(n_cells, 1e5 - 2e4 * t1 / 1200.0)
+        rh, st, wre = g.condense_particles(T1, p1, 10.0, step=k)
+        for c in range(n_cells):
+            o.condense_particles(c, T1[c], p1[c], 10.0, step=k, method=4)
+            assert abs(rh[c] / o.env_rel_humid(c) - 1) < 1e-10
+        common.assert_same_population(g, o, case, exact_fp=False, rtol=1e-9)
+    assert not np.array_equal(g.counts(), n_after_equilib), "condensation must change some particle counts"

@@ -375,17 +375,78 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
 #define COND_NARR (ROS_S + 4)  // shared arrays per particle: 6 stage vectors, abstol, D_dry, kappa, num_conc
 #define ROS_NENV 7             // (T, p) terms of one step: t, t + DT_FD, t + alpha_i h (i = 2..6)
 #define ROS_HIN_FACTOR 4.0     // first step = 4 x CVODE's first-order estimate (a 4th-order method), rounded down to 2^k
-template <int PPT, int NT>
+// ---- cells larger than one CTA holds (single-box runs, 1e4..1e5 particles): the same integrator with the
+// particles of ONE cell spread over all CTAs of a co-resident (cooperatively launched) grid.  Every cell-wide
+// sum becomes: block reduction -> one partial per CTA in global memory -> grid barrier -> every CTA adds the
+// partials in the same fixed order (so all CTAs hold bit-identical sums and take the same branches).
+#define COND_GRID_MAXB 1024
+struct GridRed {
+  double* buf;     // [2][4][COND_GRID_MAXB] partials, two alternating sets
+  unsigned* bar;   // arrival counter (zeroed before the launch)
+  unsigned gen;    // barriers passed so far
+  int par;
+};
+__device__ __forceinline__ void grid_barrier(GridRed& g) {
+  g.gen++;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(g.bar, 1u);
+    const unsigned target = g.gen * gridDim.x;
+    unsigned seen;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(g.bar) : "memory");
+    } while (seen < target);
+  }
+  __syncthreads();
+}
+template <int NV, int NT, bool IS_MAX, bool GRID>
+__device__ __forceinline__ void cell_red(double (&x)[NV], double* s_red, int& par, GridRed& g, double* s_g /*[4]*/) {
+  block_red<NV, NT, IS_MAX>(x, s_red, par);
+  if (GRID) {
+    double* gb = g.buf + (size_t)g.par * 4 * COND_GRID_MAXB;
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int k = 0; k < NV; k++) __stcg(&gb[k * COND_GRID_MAXB + blockIdx.x], x[k]);
+    }
+    grid_barrier(g);
+    if (threadIdx.x < 32) {
+#pragma unroll
+      for (int k = 0; k < NV; k++) {
+        double t = IS_MAX ? -1e300 : 0.0;
+        for (int bq = threadIdx.x; bq < (int)gridDim.x; bq += 32) {
+          const double u = __ldcg(&gb[k * COND_GRID_MAXB + bq]);
+          t = IS_MAX ? fmax(t, u) : t + u;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const double u = __shfl_xor_sync(0xffffffffu, t, o);
+          t = IS_MAX ? fmax(t, u) : t + u;
+        }
+        if (threadIdx.x == 0) s_g[k] = t;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < NV; k++) x[k] = s_g[k];
+    g.par ^= 1;
+  }
+}
+
+template <int PPT, int NT, bool GRID = false>
 __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /* may alias v.temp */,
                                                            const double* p0a,
                                                            const double* T1 /* may alias v.temp */,
                                                            const double* p1, CondParams prm,
                                                            int* __restrict__ stats, double* __restrict__ wre_out,
-                                                           int n_limit_lo, int n_limit_hi) {
-  const int cell = blockIdx.x;
+                                                           int n_limit_lo, int n_limit_hi, GridRed gr) {
+  // GRID: all CTAs walk the cells together and share each big cell; otherwise one CTA per cell
+  const int poff = GRID ? blockIdx.x * PPT : 0;
+  const bool writer = !GRID || blockIdx.x == 0;
+  __shared__ double s_g[4];
+  for (int cell = GRID ? 0 : blockIdx.x; cell < (GRID ? v.n_cells : (int)blockIdx.x + 1); cell++) {
   const int n = v.count[cell];
-  if (n <= n_limit_lo || n > n_limit_hi) return;  // another instantiation owns this cell
-  if (v.status[cell] != 0) return;
+  if (n <= n_limit_lo || n > n_limit_hi) continue;  // another instantiation owns this cell
+  if (v.status[cell] != 0) continue;
   const int tid = threadIdx.x;
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
@@ -401,14 +462,13 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   __shared__ double s_etab[32];
   if (tid < 32) s_etab[tid] = c_exp2tab[tid];
   __syncthreads();
-  // aero_state_reweight (aero_state.F90:597-653) after the solve is the identity for flat
-  // weights (ratio 1, prob_round(1) = 1); size-dependent weights need the duplicate / remove
-  // pass, which is not built yet: say so instead of skipping it silently.
+  // aero_state_reweight (aero_state.F90:597-653) after the solve is the identity for flat weights
+  // (ratio 1, prob_round(1) = 1).  For size-dependent weights this kernel leaves each particle's
+  // number concentration before the solve (aero_state_num_conc_for_reweight :564-587) in v.lnr and
+  // its new radius in v.gct_alt; k_reweight (rebalance.cu) then duplicates / removes particles.
+  bool nonflat = false;
   for (int q = 0; q < v.C * v.G; q++)
-    if (v.wtype[(size_t)cell * v.C * v.G + q] != PMCGPU_WEIGHT_NONE) {
-      if (tid == 0 && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_REWEIGHT;
-      return;
-    }
+    if (v.wtype[(size_t)cell * v.C * v.G + q] != PMCGPU_WEIGHT_NONE) nonflat = true;
   const int iw = v.i_water - 1;
   const double T0 = T0a[cell], p0 = p0a[cell];  // env_state_initial
   const double del_t = prm.del_t;
@@ -422,7 +482,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   double wsum = 0.0;
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
-    const int p = tid + k * NT;
+    const int p = tid + (poff + k) * NT;
     D[k] = 2.0;
     S_ATOL(k) = 1.0;
     SK(ROS_S + 1, k) = 1.0;
@@ -451,11 +511,15 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       D[k] = 2.0 * r;
       S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (D[k] - ddry));
       wsum += v.vol[(size_t)iw * NS + base + p] * ncp;
+      if (nonflat) {
+        const size_t wi = (size_t)cell * v.C * v.G + gc;
+        v.lnr[base + p] = weight_nc(v.wtype[wi], v.wmag[wi], v.wexp[wi], r);
+      }
     }
   }
   {
     double x[1] = {wsum};
-    block_red<1, NT, false>(x, s_red, par);
+    cell_red<1, NT, false, GRID>(x, s_red, par, gr, s_g);
     wsum = x[0];  // water_vol_conc_initial
   }
 
@@ -495,7 +559,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       double acc[3] = {0.0, 0.0, 0.0};
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
-        const bool live = tid + k * NT < n;
+        const bool live = tid + (poff + k) * NT < n;
         dfdt[k] = (f1[k] - f0[k]) * (1.0 / DT_FD);
         if (!live) { f0[k] = 0.0; dfdt[k] = 0.0; ja[k] = 0.0; jb[k] = 0.0; jc[k] = 0.0; }
         if (live) {
@@ -504,7 +568,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
           acc[2] += hd1[k];
         }
       }
-      block_red<3, NT, false>(acc, s_red, par);
+      cell_red<3, NT, false, GRID>(acc, s_red, par, gr, s_g);
       f0H = acc[0] + env_H(s_env[0], H);
       dd = acc[1] + (-s_env[0].dP0_dT_div_P0 * Tdot + pdot / s_env[0].p);
       dfdtH = ((acc[2] + env_H(s_env[1], H)) - f0H) / DT_FD;
@@ -519,25 +583,25 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
         ew[k] = 1.0 / (prm.reltol * fabs(D[k]) + S_ATOL(k));
-        if (tid + k * NT < n) {
+        if (tid + (poff + k) * NT < n) {
           a1[0] += jc[k] * f0[k];
           a1[1] = fmax(a1[1], fabs(f0[k]) / (0.1 * fabs(D[k]) + 1.0 / ew[k]));
         }
       }
       double a1s[1] = {a1[0]}, a1m[1] = {a1[1]};
-      block_red<1, NT, false>(a1s, s_red, par);
-      block_red<1, NT, true>(a1m, s_red, par);
+      cell_red<1, NT, false, GRID>(a1s, s_red, par, gr, s_g);
+      cell_red<1, NT, true, GRID>(a1m, s_red, par, gr, s_g);
       const double ewH = 1.0 / (prm.reltol * fabs(H) + prm.abstol_H);
       const double yddH = a1s[0] + dd * f0H + dfdtH;
       const double hub_inv = fmax(a1m[0], fabs(f0H) / (0.1 * fabs(H) + 1.0 / ewH));
       double a2[1] = {0.0};
 #pragma unroll
       for (int k = 0; k < PPT; k++)
-        if (tid + k * NT < n) {
+        if (tid + (poff + k) * NT < n) {
           const double w = (ja[k] * f0[k] + jb[k] * f0H + dfdt[k]) * ew[k];
           a2[0] += w * w;
         }
-      block_red<1, NT, false>(a2, s_red, par);
+      cell_red<1, NT, false, GRID>(a2, s_red, par, gr, s_g);
       const double yddnrm = sqrt((a2[0] + (yddH * ewH) * (yddH * ewH)) / (double)(n + 1));
       double hub = 0.1 * del_t;
       if (hub * hub_inv > 1.0) hub = 1.0 / hub_inv;
@@ -561,9 +625,9 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
         inv[k] = fast_rcp(eps - ja[k]);
-        if (tid + k * NT < n) sden[0] += jc[k] * jb[k] * inv[k];
+        if (tid + (poff + k) * NT < n) sden[0] += jc[k] * jb[k] * inv[k];
       }
-      block_red<1, NT, false>(sden, s_red, par);
+      cell_red<1, NT, false, GRID>(sden, s_red, par, gr, s_g);
       const double lhs_H = eps - dd - sden[0];
 #pragma unroll 1
       for (int st = 0; st < ROS_S; st++) {
@@ -597,14 +661,14 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
         }
 #pragma unroll
         for (int k = 0; k < PPT; k++) {
-          if (tid + k * NT < n) {
+          if (tid + (poff + k) * NT < n) {
             acc[0] += hd[k];
             acc[1] += jc[k] * fs[k] * inv[k];
           } else {
             fs[k] = 0.0;
           }
         }
-        block_red<2, NT, false>(acc, s_red, par);
+        cell_red<2, NT, false, GRID>(acc, s_red, par, gr, s_g);
         double fsH;
         if (st == 0)
           fsH = f0H;
@@ -621,7 +685,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       double Dn[PPT];
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
-        const int p = tid + k * NT;
+        const int p = tid + (poff + k) * NT;
         double yn = D[k];
 #pragma unroll
         for (int j = 0; j < ROS_S; j++) yn += c_rosM[j] * SK(j, k);
@@ -632,7 +696,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
           esum[0] = fma(ew, ew, esum[0]);
         }
       }
-      block_red<1, NT, false>(esum, s_red, par);
+      cell_red<1, NT, false, GRID>(esum, s_red, par, gr, s_g);
       double Hn = H;
 #pragma unroll
       for (int j = 0; j < ROS_S; j++) Hn += c_rosM[j] * KH[j];
@@ -644,13 +708,13 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       double err = sqrt(esum[0] / (double)(n + 1));
       if (!isfinite(err)) err = 1e10;
       err = fmax(err, 1e-10);
-      if (cell == prm.debug_cell && tid == 0) printf("dev t %.17g h %.17g err %.17g\n", t, h, err);
+      if (cell == prm.debug_cell && tid == 0 && writer) printf("dev t %.17g h %.17g err %.17g\n", t, h, err);
       const double fac = fmin(FAC_MAX, fmax(FAC_MIN, FAC_SAFE / sqrt(sqrt(err))));
       double hnew = h * fac;
       if (err <= 1.0) {
 #pragma unroll
         for (int k = 0; k < PPT; k++)
-          if (tid + k * NT < n) D[k] = Dn[k];
+          if (tid + (poff + k) * NT < n) D[k] = Dn[k];
         H = Hn;
         t += h;
         n_steps++;
@@ -675,7 +739,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   double wfin = 0.0;
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
-    const int p = tid + k * NT;
+    const int p = tid + (poff + k) * NT;
     if (p < n && !fail) {
       double vs = 0.0;  // aero_particle_solute_volume
       for (int s = 0; s < v.S; s++)
@@ -684,14 +748,15 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       wv = fmax(0.0, wv);
       v.vol[(size_t)iw * NS + base + p] = wv;
       wfin += wv * sNc[k * NT];
+      if (nonflat) v.gct_alt[base + p] = vol2rad(vs + wv);
     }
   }
   {
     double x[1] = {wfin};
-    block_red<1, NT, false>(x, s_red, par);
+    cell_red<1, NT, false, GRID>(x, s_red, par, gr, s_g);
     wfin = x[0];
   }
-  if (tid == 0) {
+  if (tid == 0 && writer) {
     if (fail) {
       if (v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_CONDENSE;
     } else {
@@ -710,6 +775,8 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     stats[3 * cell + 0] = n_steps;
     stats[3 * cell + 1] = n_reject;
     stats[3 * cell + 2] = n_evals;  // rate evaluations per particle
+  }
+    if (GRID) __syncthreads();
   }
 #undef SK
 #undef S_ATOL
@@ -781,11 +848,9 @@ __global__ void __launch_bounds__(NT) k_condense_bdf(DevView v, const double* T0
   if (tid < 32) s_etab[tid] = c_exp2tab[tid];
   __syncthreads();
   // aero_state_reweight after the solve is the identity for flat weights (see k_condense)
+  bool nonflat = false;
   for (int q = 0; q < v.C * v.G; q++)
-    if (v.wtype[(size_t)cell * v.C * v.G + q] != PMCGPU_WEIGHT_NONE) {
-      if (tid == 0 && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_REWEIGHT;
-      return;
-    }
+    if (v.wtype[(size_t)cell * v.C * v.G + q] != PMCGPU_WEIGHT_NONE) nonflat = true;
   const int iw = v.i_water - 1;
   const double T0 = T0a[cell], p0 = p0a[cell];  // env_state_initial
   const double del_t = prm.del_t;
@@ -827,6 +892,10 @@ __global__ void __launch_bounds__(NT) k_condense_bdf(DevView v, const double* T0
       ZN(0, k) = 2.0 * r;
       S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (2.0 * r - ddry));
       wsum += v.vol[(size_t)iw * NS + base + p] * ncp;
+      if (nonflat) {
+        const size_t wi = (size_t)cell * v.C * v.G + gc;
+        v.lnr[base + p] = weight_nc(v.wtype[wi], v.wmag[wi], v.wexp[wi], r);
+      }
     }
   }
   {
@@ -1270,6 +1339,7 @@ __global__ void __launch_bounds__(NT) k_condense_bdf(DevView v, const double* T0
       wv = fmax(0.0, wv);
       v.vol[(size_t)iw * NS + base + p] = wv;
       wfin += wv * sNc[k * NT];
+      if (nonflat) v.gct_alt[base + p] = vol2rad(vs + wv);
     }
   }
   {
@@ -1302,15 +1372,14 @@ __global__ void __launch_bounds__(NT) k_condense_bdf(DevView v, const double* T0
 }
 
 
-int pmc_condense_big_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
-                           CondParams prm, double* h_state, int* stats, double* wre, int n_lo);
-
 // device pointers T1/p1 (final env per cell)
 static size_t bdf_smem(int ppt) { return (size_t)BDF_NARR * ppt * COND_THREADS * sizeof(double); }
 static size_t ros_smem(int ppt, int nt) { return (size_t)COND_NARR * ppt * nt * sizeof(double); }
 
+int pmc_reweight_async(pmcgpu_ctx* ctx, unsigned step, unsigned pass);
+
 int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
-                       double del_t, double reltol) {
+                       double del_t, double reltol, unsigned step) {
   static bool configured = false;
   if (!configured) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(2, 256)));
@@ -1336,6 +1405,7 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
   prm.abstol_H = 1e-10;
   prm.max_steps = 100000;
   prm.debug_cell = getenv("PMCGPU_DEBUG_CELL") ? atoi(getenv("PMCGPU_DEBUG_CELL")) : -1;
+  {
   ProfScope ps_(ctx, "k_condense");
   // the population size of a cell picks the instantiation: 1..256 -> PPT 1, ..512 -> 2, ..1024 -> 4, ..2048 -> 8
   const int cap = v.cap;
@@ -1352,7 +1422,7 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
   } else {
 #define ROS_LAUNCH(PPT, NT, LO, HI)                                                                               \
   k_condense<PPT, NT><<<v.n_cells, NT, ros_smem(PPT, NT), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm,             \
-                                                                           cw->cond_stats, cw->cond_wre, LO, HI); \
+                                                                           cw->cond_stats, cw->cond_wre, LO, HI, GridRed{}); \
   LAUNCH_CHECK(ctx)
     // 256 threads x 4 particles per thread measured faster than 512 x 2 at ~1000 particles per cell
     // (300 vs 318 ms per K4 step): instruction-level parallelism beats the extra warps here
@@ -1363,7 +1433,47 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
 #undef ROS_LAUNCH
   }
   if (cap > 2048) {
-    int rc = pmc_condense_big_async(ctx, dT0, dp0, dT1, dp1, prm, cw->cond_h, cw->cond_stats, cw->cond_wre, 2048);
+    // single-box sized cells: the RODAS4 integrator with one cell spread over a co-resident grid
+    // (both methods: the BDF restatement has no grid-wide variant)
+    static int n_sm = 0;
+    static int max_blk4 = 0, max_blk8 = 0;
+    if (!n_sm) {
+      int dev = 0;
+      CUDA_OK(ctx, cudaGetDevice(&dev));
+      CUDA_OK(ctx, cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+      CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 256)));
+      CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<8, 256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(8, 256)));
+      CUDA_OK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_blk4, k_condense<4, 256, true>, 256, ros_smem(4, 256)));
+      CUDA_OK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_blk8, k_condense<8, 256, true>, 256, ros_smem(8, 256)));
+    }
+    if (!ctx->cond_grid_buf) {
+      CUDA_OK(ctx, cudaMalloc((void**)&ctx->cond_grid_buf, 2 * 4 * COND_GRID_MAXB * sizeof(double) + 256));
+      ctx->allocs.push_back(ctx->cond_grid_buf);
+    }
+    GridRed gr;
+    gr.buf = ctx->cond_grid_buf;
+    gr.bar = (unsigned*)(ctx->cond_grid_buf + 2 * 4 * COND_GRID_MAXB);
+    gr.gen = 0;
+    gr.par = 0;
+    CUDA_OK(ctx, cudaMemsetAsync(gr.bar, 0, sizeof(unsigned), ctx->stream));
+    const int ppt = (cap <= n_sm * max_blk4 * 4 * 256) ? 4 : 8;
+    int nblk = n_sm * (ppt == 4 ? max_blk4 : max_blk8);
+    if (nblk > COND_GRID_MAXB) nblk = COND_GRID_MAXB;
+    if (nblk < 1 || (long long)cap > (long long)nblk * ppt * 256) {
+      ctx->err = "condense_particles: cell_capacity exceeds what one co-resident grid integrates";
+      return PMCGPU_ERR_CAPACITY;
+    }
+    int lo = 2048, hi = cap;
+    void* args[] = {&v, &dT0, &dp0, &dT1, &dp1, &prm, &cw->cond_stats, &cw->cond_wre, &lo, &hi, &gr};
+    if (ppt == 4)
+      CUDA_OK(ctx, cudaLaunchCooperativeKernel((void*)k_condense<4, 256, true>, dim3(nblk), dim3(256), args, ros_smem(4, 256), ctx->stream));
+    else
+      CUDA_OK(ctx, cudaLaunchCooperativeKernel((void*)k_condense<8, 256, true>, dim3(nblk), dim3(256), args, ros_smem(8, 256), ctx->stream));
+    ctx->launches++;
+  }
+  }
+  if (ctx->any_nonflat) {  // aero_state_reweight (condense.F90:297), pass 0
+    int rc = pmc_reweight_async(ctx, step, 0u);
     if (rc) return rc;
   }
   return PMCGPU_OK;
@@ -1384,7 +1494,7 @@ extern "C" int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_fin
   int rc;
   CUDA_OK(ctx, cudaMemcpyAsync(cw->cond_T1, temp_final, v.n_cells * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   CUDA_OK(ctx, cudaMemcpyAsync(cw->cond_p1, pressure_final, v.n_cells * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-  rc = pmc_condense_async(ctx, v.temp, v.pres, cw->cond_T1, cw->cond_p1, del_t, reltol);
+  rc = pmc_condense_async(ctx, v.temp, v.pres, cw->cond_T1, cw->cond_p1, del_t, reltol, ctx->rng_step);
   if (rc) return rc;
   if (rel_humid_out)
     CUDA_OK(ctx, cudaMemcpyAsync(rel_humid_out, v.rh, v.n_cells * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1397,7 +1507,6 @@ extern "C" int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_fin
 }
 
 
-// cells larger than the register-resident kernels handle (single-box runs): see condense_big.cu
 
 // ---- condense_equilib_particles (condense.F90:701-770), one thread per particle
 __global__ void k_condense_equilib(DevView v) {
@@ -1409,6 +1518,9 @@ __global__ void k_condense_equilib(DevView v) {
   const double X = 4.0 * PmcConst::water_molec_weight * PmcConst::water_surf_eng /
                    (PmcConst::univ_gas_const * v.temp[cell] * PmcConst::water_density);
   const double RH = v.rh[cell];
+  bool nonflat = false;
+  for (int q = 0; q < v.C * v.G; q++)
+    if (v.wtype[(size_t)cell * v.C * v.G + q] != PMCGPU_WEIGHT_NONE) nonflat = true;
   for (int p = threadIdx.x; p < n; p += blockDim.x) {
     double vs = 0.0, ks = 0.0;
     const double M_w = v.molw[iw], rho_w = v.density[iw];
@@ -1433,7 +1545,20 @@ __global__ void k_condense_equilib(DevView v) {
       g = RH - a_w * ex;
       dg_dD = -daw_dD * ex + a_w * ex * (X / (D * D));
     }
-    v.vol[(size_t)iw * NS + base + p] = rad2vol(D / 2.0) - rad2vol(D_dry / 2.0);
+    if (nonflat) {
+      // aero_state_num_conc_for_reweight before, new radius after (k_reweight reads both)
+      double vt = 0.0;
+      for (int s = 0; s < v.S; s++) vt += v.vol[(size_t)s * NS + base + p];
+      const size_t wi = (size_t)cell * v.C * v.G + v.wgc[base + p];
+      v.lnr[base + p] = weight_nc(v.wtype[wi], v.wmag[wi], v.wexp[wi], vol2rad(vt));
+    }
+    const double wv = rad2vol(D / 2.0) - rad2vol(D_dry / 2.0);
+    v.vol[(size_t)iw * NS + base + p] = wv;
+    if (nonflat) {
+      double vt = 0.0;
+      for (int s = 0; s < v.S; s++) vt += v.vol[(size_t)s * NS + base + p];
+      v.gct_alt[base + p] = vol2rad(vt);
+    }
   }
 }
 extern "C" int pmcgpu_condense_equilib_particles(pmcgpu_ctx* ctx) {
@@ -1441,6 +1566,10 @@ extern "C" int pmcgpu_condense_equilib_particles(pmcgpu_ctx* ctx) {
   if (ctx->v.i_water < 1) return PMCGPU_ERR_ARG;
   k_condense_equilib<<<ctx->v.n_cells, 128, 0, ctx->stream>>>(ctx->v);
   LAUNCH_CHECK(ctx);
+  if (ctx->any_nonflat) {  // aero_state_reweight (condense.F90:767), pass 1000
+    int rc = pmc_reweight_async(ctx, ctx->rng_step, 1000u);
+    if (rc) return rc;
+  }
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
   return PMCGPU_OK;
 }

@@ -335,6 +335,16 @@ extern "C" int pmcgpu_set_weights(pmcgpu_ctx* ctx, const int* type, const double
   const size_t n = (size_t)ctx->v.n_cells * ctx->v.C * ctx->v.G;
   H2D_OPT(ctx->v.wtype, type, n, int) H2D_OPT(ctx->v.wmag, magnitude, n, double) H2D_OPT(ctx->v.wexp, exponent, n, double)
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  if (type) {
+    ctx->any_nonflat = false;
+    for (size_t i = 0; i < n; i++)
+      if (type[i] != PMCGPU_WEIGHT_NONE) ctx->any_nonflat = true;
+  }
+  return PMCGPU_OK;
+}
+extern "C" int pmcgpu_set_rng_step(pmcgpu_ctx* ctx, unsigned step) {
+  if (!ctx) return PMCGPU_ERR_ARG;
+  ctx->rng_step = step;
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_weights(pmcgpu_ctx* ctx, int* type, double* magnitude, double* exponent) {

@@ -157,6 +157,9 @@ struct pmcgpu_ctx {
   int nb[4] = {0, 0, 0, 0};
   void* nccl_comm = nullptr;
   int cond_method = 4;  // 4: RODAS4, 5: BDF (CVODE restatement) (pmcgpu_set_condense_method)
+  double* cond_grid_buf = nullptr;  // partial sums + barrier counter of the grid-wide condensation kernel
+  unsigned rng_step = 0;     // step number addressing the draws of the stand-alone condensation calls (pmcgpu_set_rng_step)
+  bool any_nonflat = false;  // some weight is size dependent (set by pmcgpu_set_weights): aero_state_reweight is not the identity
 };
 int pmc_exchange_slabs(pmcgpu_ctx* ctx, const int* n_send, const int* n_recv);
 int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], const size_t send_bytes[4],

@@ -133,6 +133,118 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_rebalance(DevView v, int all
   }
 }
 
+// aero_state_reweight (aero_state.F90:597-653) after a pass that changed particle sizes
+// (condense_particles :297, condense_equilib_particles :767).  The pass left, per particle, the
+// number concentration before the change in v.lnr (aero_state_num_conc_for_reweight :564-587) and the
+// new radius in v.gct_alt.  Per (group, class) the magnitude is rescaled to keep the computational
+// count in expectation; then, backwards through the particle array, particle i keeps
+// prob_round(old_nc / new_nc) copies (aero_state_dup_particle :488-539): 0 copies = swap-with-last
+// removal, extra copies are appended with new ids.  The draw of particle i is addressed
+// (PH_REWEIGHT, pass, i), so a chunk of 32 particles is decided in parallel and only the (rare)
+// particles whose count is not 1 are replayed in order.  Flat weights: ratio 1 exactly, nothing to do.
+__global__ void __launch_bounds__(REB_WARPS * 32) k_reweight(DevView v, unsigned step, unsigned pass) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * REB_WARPS + warp;
+  if (cell >= v.n_cells) return;
+  if (v.status[cell] != 0) return;
+  const int ngc = v.C * v.G;
+  const size_t wb = (size_t)cell * ngc;
+  bool nonflat = false;
+  for (int q = 0; q < ngc; q++)
+    if (v.wtype[wb + q] != PMCGPU_WEIGHT_NONE) nonflat = true;
+  if (!nonflat) return;
+  const size_t base = (size_t)cell * v.cap;
+  const size_t NS = (size_t)v.n_cells * v.cap;
+  const int n0 = v.count[cell];
+  int n_part = n0;
+  int err = 0;
+  // ---- magnitudes: n_part_new / n_part_old per (group, class)
+  for (int gc = 0; gc < ngc; gc++) {
+    double sn = 0.0;
+    int cnt = 0;
+    const int wt = v.wtype[wb + gc];
+    const double wm = v.wmag[wb + gc], we = v.wexp[wb + gc];
+    for (int p = lane; p < n0; p += 32)
+      if (v.wgc[base + p] == gc) {
+        sn += v.lnr[base + p] / weight_nc(wt, wm, we, v.gct_alt[base + p]);
+        cnt++;
+      }
+    for (int o = 16; o > 0; o >>= 1) sn += __shfl_xor_sync(0xffffffffu, sn, o);
+    cnt = warp_sum(cnt);
+    __syncwarp();
+    if (lane == 0 && cnt > 0) v.wmag[wb + gc] = wm * (sn / (double)cnt);
+  }
+  __syncwarp();
+  // ---- particles, backwards
+  for (int hi = n0 - 1; hi >= 0 && !err; hi -= 32) {
+    const int i = hi - lane;
+    int n_copies = 1;
+    if (i >= 0) {
+      const int gc = v.wgc[base + i];
+      const double new_nc = weight_nc(v.wtype[wb + gc], v.wmag[wb + gc], v.wexp[wb + gc], v.gct_alt[base + i]);
+      const RKey key{v.seed, (unsigned)v.gcell[cell], step, PH_REWEIGHT, pass, (unsigned)(i + 1)};
+      n_copies = prob_round(v.lnr[base + i] / new_nc, rng_uniform(key, 0));
+    }
+    unsigned todo = __ballot_sync(0xffffffffu, n_copies != 1);
+    while (todo && !err) {
+      const int l = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int ii = hi - l;
+      const int nc = __shfl_sync(0xffffffffu, n_copies, l);
+      if (nc == 0) {
+        const int last = n_part - 1;
+        if (ii != last) {
+          for (int sp = lane; sp < v.S; sp += 32) v.vol[(size_t)sp * NS + base + ii] = v.vol[(size_t)sp * NS + base + last];
+          if (lane == 0) {
+            v.id[base + ii] = v.id[base + last];
+            v.wgc[base + ii] = v.wgc[base + last];
+            v.nprim[base + ii] = v.nprim[base + last];
+            v.hyst[base + ii] = v.hyst[base + last];
+            v.lct[base + ii] = v.lct[base + last];
+            v.gct[base + ii] = v.gct[base + last];
+          }
+        }
+        n_part = last;
+      } else {
+        if (n_part + nc - 1 > v.cap) {
+          err = PMCGPU_ERR_CAPACITY;
+          break;
+        }
+        const long long nx = v.next_id[cell];
+        for (int d = 0; d < nc - 1; d++) {
+          const int dst = n_part + d;
+          for (int sp = lane; sp < v.S; sp += 32) v.vol[(size_t)sp * NS + base + dst] = v.vol[(size_t)sp * NS + base + ii];
+          if (lane == 0) {
+            v.id[base + dst] = (nx + d - 1) * v.n_cells_global + v.gcell[cell] + 1;
+            v.wgc[base + dst] = v.wgc[base + ii];
+            v.nprim[base + dst] = v.nprim[base + ii];
+            v.hyst[base + dst] = v.hyst[base + ii];
+            v.lct[base + dst] = v.lct[base + ii];
+            v.gct[base + dst] = v.gct[base + ii];
+          }
+        }
+        __syncwarp();
+        if (lane == 0) v.next_id[cell] = nx + (nc - 1);
+        n_part += nc - 1;
+      }
+      __syncwarp();
+    }
+  }
+  if (lane == 0) {
+    v.count[cell] = n_part;
+    if (err && v.status[cell] == 0) v.status[cell] = err;
+  }
+}
+
+int pmc_reweight_async(pmcgpu_ctx* ctx, unsigned step, unsigned pass) {
+  DevView& v = ctx->v;
+  const int blocks = (v.n_cells + REB_WARPS - 1) / REB_WARPS;
+  ProfScope ps_(ctx, "k_reweight");
+  k_reweight<<<blocks, REB_WARPS * 32, 0, ctx->stream>>>(v, step, pass);
+  LAUNCH_CHECK(ctx);
+  return PMCGPU_OK;
+}
+
 int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step) {
   DevView& v = ctx->v;
   const int blocks = (v.n_cells + REB_WARPS - 1) / REB_WARPS;

@@ -17,7 +17,7 @@
 int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck);
 int pmc_mc_coag_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step);
 int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
-                       double del_t, double reltol);
+                       double del_t, double reltol, unsigned step);
 int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step);
 int pmc_update_density_async(pmcgpu_ctx* ctx, const double* d_new_rrho);
 int pmc_num_conc_async(pmcgpu_ctx* ctx, float* d_out);
@@ -56,7 +56,7 @@ extern "C" int pmcgpu_partmc_timestep(pmcgpu_ctx* ctx, const pmcgpu_timestep_arg
       ctx->err = "do_condensation needs a water species (aero_data%i_water)";
       return PMCGPU_ERR_ARG;
     }
-    if ((rc = pmc_condense_async(ctx, v.cond_T0, v.cond_p0, v.temp, v.pres, a->chem_dt, 0.0))) return rc;
+    if ((rc = pmc_condense_async(ctx, v.cond_T0, v.cond_p0, v.temp, v.pres, a->chem_dt, 0.0, a->step))) return rc;
   }
   // ---- aero_state_rebalance
   if ((rc = pmc_rebalance_async(ctx, a->allow_doubling, a->allow_halving, a->step))) return rc;

@@ -250,8 +250,10 @@ class PartMCGPU:
                                         _p(nc)))
         return ns, nc
 
-    def condense_particles(self, temp_final, pressure_final, del_t, reltol=0.0):
-        """condense_particles (condense.F90:147) for every cell; returns (rel_humid, stats[n][3], water_rel_error)."""
+    def condense_particles(self, temp_final, pressure_final, del_t, reltol=0.0, step=0):
+        """condense_particles (condense.F90:147) for every cell; returns (rel_humid, stats[n][3], water_rel_error).
+        `step` addresses the draws of aero_state_reweight (only drawn when weights depend on size)."""
+        self._chk(self.L.pmcgpu_set_rng_step(self.h, C.c_uint(step)))
         T1, p1 = _f64(temp_final), _f64(pressure_final)
         assert T1.size == self.n_cells and p1.size == self.n_cells
         rh, st, wre = np.zeros(self.n_cells), np.zeros((self.n_cells, 3), np.int32), np.zeros(self.n_cells)
@@ -263,7 +265,8 @@ class PartMCGPU:
         """5: CVODE-style BDF (default), 4: RODAS4 (cross-validation)"""
         self._chk(self.L.pmcgpu_set_condense_method(self.h, C.c_int(method)))
 
-    def condense_equilib_particles(self):
+    def condense_equilib_particles(self, step=0):
+        self._chk(self.L.pmcgpu_set_rng_step(self.h, C.c_uint(step)))
         self._chk(self.L.pmcgpu_condense_equilib_particles(self.h))
 
     def eval_condense_rates(self, inputs):
