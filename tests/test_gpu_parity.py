@@ -262,3 +262,21 @@ def test_accelerated_per_particle_coag_bit_exact(mods, weight, n_spec, n_class, 
         assert np.array_equal(g.get_next_id(), [o.L.pmco_get_next_id(o.h, c) for c in range(n_cells)])
     assert acc > 0, "the case must select the accelerated path"
     assert events > 20
+
+
+@pytest.mark.parametrize("weight,n_group", [("flat", 1), ("nummass", 2)])
+def test_mc_coag_k2_single_box_bit_exact(mods, weight, n_group):
+    """BASELINE config K2 at full size: one box, 1e5 particles, Brownian kernel, flat and nummass-like
+    weights (weighted sampling: coagulate_weighting's remove / create probabilities, coagulation.F90:810)."""
+    W, O = mods
+    case = common.make_cells(1, 100000, n_spec=1, n_group=n_group, weight=weight, seed=5, ragged=False,
+                             num_conc=1e11, r_g=2.5e-8)
+    g = common.gpu_from_case(W, case, cell_capacity=120000)
+    o = common.oracle_from_case(O, case)
+    for step in range(2):
+        ns, nc = g.mc_coag(W.KERNEL_BROWN, 600.0, step=step)
+        o.sort(0, force_resort=True, physical=True, edge_recheck=True)
+        s, k, _ = o.mc_coag(0, O.KERNEL_BROWN, 600.0, step=step)
+        assert (s, k) == (ns[0], nc[0])
+        assert k > 5000
+        common.assert_same_population(g, o, case)

@@ -274,12 +274,21 @@ __device__ __forceinline__ CondEnv cond_env_fast(double T0, double p0, double Td
 // then below 1e-16 |u|), after at most five evaluations like the reference.
 // Per-particle constants (D_dry, kappa, num_conc) are read from shared memory (stride COND_THREADS).
 // WITH_JAC also returns a = dDdot/dD, b = dDdot/dH, c = dHdot_i/dD, dH = dHdot_i/dH.
-template <int PPT, bool WITH_JAC, int NT = COND_THREADS>
+// Newton iteration on u = delta* / (1 + delta*) (condense.F90:449-466 does five fixed updates from 0).  The
+// iteration converges quadratically with a small constant (profiles/r01_newton_convergence.md: relative
+// error e -> about 0.02 e^2), so an update of relative size <= NEWTON_TOL leaves an error below 1e-13 and
+// the loop stops there.  The size is measured against max(|u|, NEWTON_FLOOR): particles in equilibrium have
+// delta* -> 0 and a purely relative test would never pass (their rounding noise is ~1e-16 absolute).
+// WARM: the iteration starts from the root of the previous evaluation of the same particle (kept in
+// shared memory; successive stage states are close), which saves one update on average.
+#define NEWTON_TOL 1e-6
+#define NEWTON_FLOOR 1e-6
+template <int PPT, bool WITH_JAC, int NT = COND_THREADS, bool WARM = false>
 __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, const CondEnv& e, double H,
                                                const double (&D)[PPT], const double* __restrict__ sDdry, const double* __restrict__ sKap,
                                                const double* __restrict__ sNc, double (&Ddot)[PPT],
                                                double (&Hd)[PPT], double (&a)[PPT], double (&b)[PPT],
-                                               double (&c)[PPT], double (&dH)[PPT]) {
+                                               double (&c)[PPT], double (&dH)[PPT], double* uw = nullptr) {
   const double g = -2.0 * PmcConst::pi / (e.V * e.vc);  // Hdot_i = g * num_conc * D^2 * Ddot
   const double invU = 1.0 / e.U;
   double k_ap[PPT], UVD[PPT], a_w[PPT], XD[PPT], invD[PPT];
@@ -304,6 +313,10 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
     kB[k] = fma(UVD[k], H, k_ap[k]);
     cW[k] = e.W - XD[k];
     u[k] = 0.0;
+    if (WARM) {
+      const double up = uw[k * NT];
+      if (fabs(up) < 0.5) u[k] = up;
+    }
   }
 #pragma unroll 1
   for (int newton_step = 1; newton_step <= 5; newton_step++) {
@@ -317,10 +330,14 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
       const double hh = fma(k_ap[k], u[k], -s * Bg);     // (1 - u) h
       const double dh = fma(gg, fma(s, cW[k], -2.0), kB[k]);
       const double du = hh * fast_rcp(dh);
-      small = small && (fabs(du) <= 1e-7 * fabs(u[k]));
+      small = small && (fabs(du) <= NEWTON_TOL * fmax(fabs(u[k]), NEWTON_FLOOR));
       u[k] -= du;
     }
     if (__all_sync(0xffffffffu, small)) break;
+  }
+  if (WARM) {
+#pragma unroll
+    for (int k = 0; k < PPT; k++) uw[k * NT] = u[k];
   }
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
@@ -372,7 +389,7 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
   }
 }
 
-#define COND_NARR (ROS_S + 4)  // shared arrays per particle: 6 stage vectors, abstol, D_dry, kappa, num_conc
+#define COND_NARR (ROS_S + 5)  // shared arrays per particle: 6 stage vectors, abstol, D_dry, kappa, num_conc, Newton warm start
 #define ROS_NENV 7             // (T, p) terms of one step: t, t + DT_FD, t + alpha_i h (i = 2..6)
 #define ROS_HIN_FACTOR 4.0     // first step = 4 x CVODE's first-order estimate (a 4th-order method), rounded down to 2^k
 // ---- cells larger than one CTA holds (single-box runs, 1e4..1e5 particles): the same integrator with the
@@ -458,6 +475,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   const double* sDdry = &SK(ROS_S + 1, 0);
   const double* sKap = &SK(ROS_S + 2, 0);
   const double* sNc = &SK(ROS_S + 3, 0);
+  double* sUw = &SK(ROS_S + 4, 0);
   int par = 0;
   __shared__ double s_etab[32];
   if (tid < 32) s_etab[tid] = c_exp2tab[tid];
@@ -488,6 +506,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     SK(ROS_S + 1, k) = 1.0;
     SK(ROS_S + 2, k) = 0.5;
     SK(ROS_S + 3, k) = 1.0;
+    SK(ROS_S + 4, k) = 0.0;
     if (p < n) {
       // aero_particle_solute_kappa (aero_particle.F90:724-755), solute volume, total volume
       double vt = 0.0, vs = 0.0, ks = 0.0;
@@ -553,8 +572,8 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     double f0H, dfdtH, dd;
     {
       double hd[PPT], dh[PPT], f1[PPT], hd1[PPT];
-      cond_rates_vec<PPT, true, NT>(s_etab, s_env[0], H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh);
-      cond_rates_vec<PPT, false, NT>(s_etab, s_env[1], H, D, sDdry, sKap, sNc, f1, hd1, u1, u2, u3, u4);
+      cond_rates_vec<PPT, true, NT, true>(s_etab, s_env[0], H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh, sUw);
+      cond_rates_vec<PPT, false, NT, true>(s_etab, s_env[1], H, D, sDdry, sKap, sNc, f1, hd1, u1, u2, u3, u4, sUw);
       n_evals += 2;
       double acc[3] = {0.0, 0.0, 0.0};
 #pragma unroll
@@ -645,7 +664,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
 #pragma unroll
             for (int k = 0; k < PPT; k++) y[k] += aj * SK(j, k);
           }
-          cond_rates_vec<PPT, false, NT>(s_etab, s_env[st + 1], Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4);
+          cond_rates_vec<PPT, false, NT, true>(s_etab, s_env[st + 1], Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4, sUw);
           n_evals++;
         } else {
 #pragma unroll
