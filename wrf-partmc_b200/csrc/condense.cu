@@ -274,21 +274,35 @@ __device__ __forceinline__ CondEnv cond_env_fast(double T0, double p0, double Td
 // then below 1e-16 |u|), after at most five evaluations like the reference.
 // Per-particle constants (D_dry, kappa, num_conc) are read from shared memory (stride COND_THREADS).
 // WITH_JAC also returns a = dDdot/dD, b = dDdot/dH, c = dHdot_i/dD, dH = dHdot_i/dH.
-// Newton iteration on u = delta* / (1 + delta*) (condense.F90:449-466 does five fixed updates from 0).  The
-// iteration converges quadratically with a small constant (profiles/r01_newton_convergence.md: relative
-// error e -> about 0.02 e^2), so an update of relative size <= NEWTON_TOL leaves an error below 1e-13 and
-// the loop stops there.  The size is measured against max(|u|, NEWTON_FLOOR): particles in equilibrium have
-// delta* -> 0 and a purely relative test would never pass (their rounding noise is ~1e-16 absolute).
-// WARM: the iteration starts from the root of the previous evaluation of the same particle (kept in
-// shared memory; successive stage states are close), which saves one update on average.
-#define NEWTON_TOL 1e-6
+// Newton iteration on u = delta* / (1 + delta*) (condense.F90:449-466 does five fixed updates from 0).  Newton's
+// error recursion is e' = K e^2 with K = h'' / (2 h'); here h'' ~ 280 A and h' >= 17 A (W = L_v M_w / (R T) ~ 19
+// enters as exp(W u)), so K < 10 in absolute terms (profiles/r01_newton_convergence.md shows the resulting
+// relative constants 1e-3 .. 2e-2).  An update of size du therefore leaves an error below K du^2, and the loop
+// stops when NEWTON_K du^2 <= NEWTON_TOL max(|u|, NEWTON_FLOOR) with a tenfold margin on K: the root is then
+// exact to 1e-14 relative (rounding level; activation amplifies differences by 1e4 or more).  The floor is there because particles in equilibrium have delta* -> 0, where a
+// purely relative test would never pass (their rounding noise is ~1e-16 absolute).
+#define NEWTON_K 100.0
+#define NEWTON_TOL 1e-14
 #define NEWTON_FLOOR 1e-6
-template <int PPT, bool WITH_JAC, int NT = COND_THREADS, bool WARM = false>
+// MODE (where the iteration starts; sw = shared arrays u0, du/dD, du/dH, du/dt, uN of PPT * NT doubles each):
+//   0  cold, from 0 (the BDF kernel)
+//   1  f at (t, y) with the Jacobian: starts from uN (root at the end of the previous step); leaves u0 and
+//      the sensitivities du/dD, du/dH of the root (from d delta* / dD, d delta* / dH, which the Jacobian needs anyway)
+//   2  f at (t + DT_FD, y): starts from u0; leaves du/dt = (u - u0) / DT_FD
+//   3  stage values: starts from the first-order prediction u0 + du/dD (y - D) + du/dH (Hs - H) + du/dt dts
+//      (the error of the start is second order in the stage increment, so one update usually suffices);
+//      write_uN: the last stage (state at t + h) leaves its root in uN
+//   5  plain warm start from / to sw[0] (8 particles per thread: no room for the sensitivities)
+#define COND_DT_FD 1e-2
+template <int PPT, bool WITH_JAC, int NT = COND_THREADS, int MODE = 0>
 __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, const CondEnv& e, double H,
                                                const double (&D)[PPT], const double* __restrict__ sDdry, const double* __restrict__ sKap,
                                                const double* __restrict__ sNc, double (&Ddot)[PPT],
                                                double (&Hd)[PPT], double (&a)[PPT], double (&b)[PPT],
-                                               double (&c)[PPT], double (&dH)[PPT], double* uw = nullptr) {
+                                               double (&c)[PPT], double (&dH)[PPT], double* sw = nullptr,
+                                               const double* D0 = nullptr, double H0 = 0.0, double dts = 0.0,
+                                               bool write_uN = false) {
+  constexpr int AS = PPT * NT;
   const double g = -2.0 * PmcConst::pi / (e.V * e.vc);  // Hdot_i = g * num_conc * D^2 * Ddot
   const double invU = 1.0 / e.U;
   double k_ap[PPT], UVD[PPT], a_w[PPT], XD[PPT], invD[PPT];
@@ -313,31 +327,110 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
     kB[k] = fma(UVD[k], H, k_ap[k]);
     cW[k] = e.W - XD[k];
     u[k] = 0.0;
-    if (WARM) {
-      const double up = uw[k * NT];
+    if (MODE == 1 || MODE == 2 || MODE == 5) {
+      const double up = sw[(MODE == 1 ? 4 : 0) * AS + k * NT];
+      if (fabs(up) < 0.5) u[k] = up;
+    }
+    if (MODE == 3) {
+      double up = fma(sw[1 * AS + k * NT], d - D0[k], sw[0 * AS + k * NT]);
+      up = fma(sw[2 * AS + k * NT], H - H0, up);
+      up = fma(sw[3 * AS + k * NT], dts, up);
       if (fabs(up) < 0.5) u[k] = up;
     }
   }
+  // The loop body is written operation by operation across the PPT particles of the thread (not particle
+  // by particle): the FP64 pipe needs several independent instructions between two dependent ones, and the
+  // instruction scheduler keeps this order, while it serialises PPT long per-particle chains.
 #pragma unroll 1
   for (int newton_step = 1; newton_step <= 5; newton_step++) {
     bool small = true;
+    double s_[PPT], ex[PPT], gg[PPT], dh[PPT], hh[PPT], rc[PPT];
+    {
+      const double SHIFT = 6755399441055744.0;  // fast_exp_t, see above
+      double x[PPT], kd[PPT], nf[PPT], r[PPT], pl[PPT], tb[PPT];
+      int ki[PPT];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) x[k] = fma(cW[k], u[k], XD[k]);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) kd[k] = fma(x[k], 46.16624130844683, SHIFT);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) {
+        ki[k] = __double2loint(kd[k]);
+        nf[k] = kd[k] - SHIFT;
+      }
+#pragma unroll
+      for (int k = 0; k < PPT; k++) r[k] = fma(nf[k], -0.02166084938653512, x[k]);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) tb[k] = etab[ki[k] & 31];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) r[k] = fma(nf[k], -5.9631716539705866e-12, r[k]);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) pl[k] = fma(r[k], 1.0 / 720, 1.0 / 120);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) s_[k] = 1.0 - u[k];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) pl[k] = fma(pl[k], r[k], 1.0 / 24);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) x[k] = r[k] * r[k];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) pl[k] = fma(pl[k], r[k], 1.0 / 6);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) gg[k] = A[k] * s_[k];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) pl[k] = fma(pl[k], r[k], 0.5);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) dh[k] = fma(s_[k], cW[k], -2.0);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) pl[k] = fma(x[k], pl[k], r[k]);  // exp(r) - 1
+#pragma unroll
+      for (int k = 0; k < PPT; k++) pl[k] = fma(tb[k], pl[k], tb[k]);
+#pragma unroll
+      for (int k = 0; k < PPT; k++)
+        ex[k] = __hiloint2double(__double2hiint(pl[k]) + ((ki[k] >> 5) << 20), __double2loint(pl[k]));
+    }
+#pragma unroll
+    for (int k = 0; k < PPT; k++) gg[k] = gg[k] * ex[k];                    // A (1 - u) exp(..)
+#pragma unroll
+    for (int k = 0; k < PPT; k++) dh[k] = fma(gg[k], dh[k], kB[k]);
+#pragma unroll
+    for (int k = 0; k < PPT; k++) hh[k] = fma(UVD[k], H, -gg[k]);           // B - g
+    // fast_rcp(dh), see above
+#pragma unroll
+    for (int k = 0; k < PPT; k++) asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rc[k]) : "d"(dh[k]));
+#pragma unroll
+    for (int k = 0; k < PPT; k++) hh[k] = fma(k_ap[k], u[k], -s_[k] * hh[k]);  // (1 - u) h
+    {
+      double e1[PPT];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) e1[k] = fma(-dh[k], rc[k], 1.0);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) e1[k] = fma(e1[k], e1[k], e1[k]);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) rc[k] = fma(rc[k], e1[k], rc[k]);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) e1[k] = fma(-dh[k], rc[k], 1.0);
+#pragma unroll
+      for (int k = 0; k < PPT; k++) rc[k] = fma(rc[k], e1[k], rc[k]);
+    }
 #pragma unroll
     for (int k = 0; k < PPT; k++) {
-      const double s = 1.0 - u[k];
-      const double ex = fast_exp_t(fma(cW[k], u[k], XD[k]), etab);
-      const double gg = A[k] * s * ex;
-      const double Bg = fma(UVD[k], H, -gg);             // B - g
-      const double hh = fma(k_ap[k], u[k], -s * Bg);     // (1 - u) h
-      const double dh = fma(gg, fma(s, cW[k], -2.0), kB[k]);
-      const double du = hh * fast_rcp(dh);
-      small = small && (fabs(du) <= NEWTON_TOL * fmax(fabs(u[k]), NEWTON_FLOOR));
+      const double du = hh[k] * rc[k];
+      small = small && (NEWTON_K * du * du <= NEWTON_TOL * fmax(fabs(u[k]), NEWTON_FLOOR));
       u[k] -= du;
     }
     if (__all_sync(0xffffffffu, small)) break;
   }
-  if (WARM) {
+  if (MODE == 1 || MODE == 5) {
 #pragma unroll
-    for (int k = 0; k < PPT; k++) uw[k * NT] = u[k];
+    for (int k = 0; k < PPT; k++) sw[k * NT] = u[k];
+  }
+  if (MODE == 2) {
+#pragma unroll
+    for (int k = 0; k < PPT; k++) sw[3 * AS + k * NT] = (u[k] - sw[k * NT]) * (1.0 / COND_DT_FD);
+  }
+  if (MODE == 3 && write_uN) {
+#pragma unroll
+    for (int k = 0; k < PPT; k++) sw[4 * AS + k * NT] = u[k];
   }
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
@@ -362,6 +455,10 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
       const double inv_dh = fast_rcp(dhd);
       const double ddeltastar_dD = -dh_dD * inv_dh;
       const double ddeltastar_dH = UVD[k] * inv_dh;
+      if (MODE == 1) {  // du = q^2 d delta
+        sw[1 * AS + k * NT] = (q * q) * ddeltastar_dD;
+        sw[2 * AS + k * NT] = (q * q) * ddeltastar_dH;
+      }
       a[k] = dkap_dD * delta * invD[k] * invU + kU * ddeltastar_dD - kU * delta * invD[k];
       b[k] = kU * ddeltastar_dH;
       c[k] = hf * (2.0 * d * Ddot[k] + (d * d) * a[k]);
@@ -389,7 +486,10 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
   }
 }
 
-#define COND_NARR (ROS_S + 5)  // shared arrays per particle: 6 stage vectors, abstol, D_dry, kappa, num_conc, Newton warm start
+// shared arrays per particle: 6 stage vectors, abstol, D_dry, kappa, num_conc, then the Newton start values
+// (u0, du/dD, du/dH, du/dt, uN with the predictor; one array without)
+#define COND_PRED(PPT) ((PPT) <= 4)
+#define COND_NARR(PPT) (ROS_S + 4 + (COND_PRED(PPT) ? 5 : 1))
 #define ROS_NENV 7             // (T, p) terms of one step: t, t + DT_FD, t + alpha_i h (i = 2..6)
 #define ROS_HIN_FACTOR 4.0     // first step = 4 x CVODE's first-order estimate (a 4th-order method), rounded down to 2^k
 // ---- cells larger than one CTA holds (single-box runs, 1e4..1e5 particles): the same integrator with the
@@ -469,7 +569,8 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   const size_t NS = (size_t)v.n_cells * v.cap;
   __shared__ double s_red[2 * 4 * (NT / 32)];
   __shared__ CondEnv s_env[ROS_NENV];
-  extern __shared__ double s_K[];  // [COND_NARR][PPT][NT]
+  extern __shared__ double s_K[];  // [COND_NARR(PPT)][PPT][NT]
+  constexpr bool PRED = COND_PRED(PPT);
 #define SK(st, k) s_K[((st) * PPT + (k)) * NT + tid]
 #define S_ATOL(k) SK(ROS_S, k)
   const double* sDdry = &SK(ROS_S + 1, 0);
@@ -507,6 +608,12 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     SK(ROS_S + 2, k) = 0.5;
     SK(ROS_S + 3, k) = 1.0;
     SK(ROS_S + 4, k) = 0.0;
+    if (PRED) {
+      SK(ROS_S + 5, k) = 0.0;
+      SK(ROS_S + 6, k) = 0.0;
+      SK(ROS_S + 7, k) = 0.0;
+      SK(ROS_S + 8, k) = 0.0;
+    }
     if (p < n) {
       // aero_particle_solute_kappa (aero_particle.F90:724-755), solute volume, total volume
       double vt = 0.0, vs = 0.0, ks = 0.0;
@@ -543,7 +650,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   }
 
   const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.9, FAC_REJ = 0.1;
-  const double DT_FD = 1e-2;
+  const double DT_FD = COND_DT_FD;
   double u1[PPT], u2[PPT], u3[PPT], u4[PPT];  // unused outputs of the no-Jacobian evaluations
   const int warp = tid >> 5, lane = tid & 31;
   // the (T, p) terms of condense_rates at the ROS_NENV times of a step: warp w evaluates entry w
@@ -572,8 +679,8 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     double f0H, dfdtH, dd;
     {
       double hd[PPT], dh[PPT], f1[PPT], hd1[PPT];
-      cond_rates_vec<PPT, true, NT, true>(s_etab, s_env[0], H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh, sUw);
-      cond_rates_vec<PPT, false, NT, true>(s_etab, s_env[1], H, D, sDdry, sKap, sNc, f1, hd1, u1, u2, u3, u4, sUw);
+      cond_rates_vec<PPT, true, NT, PRED ? 1 : 5>(s_etab, s_env[0], H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh, sUw);
+      cond_rates_vec<PPT, false, NT, PRED ? 2 : 5>(s_etab, s_env[1], H, D, sDdry, sKap, sNc, f1, hd1, u1, u2, u3, u4, sUw);
       n_evals += 2;
       double acc[3] = {0.0, 0.0, 0.0};
 #pragma unroll
@@ -664,7 +771,8 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
 #pragma unroll
             for (int k = 0; k < PPT; k++) y[k] += aj * SK(j, k);
           }
-          cond_rates_vec<PPT, false, NT, true>(s_etab, s_env[st + 1], Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4, sUw);
+          cond_rates_vec<PPT, false, NT, PRED ? 3 : 5>(s_etab, s_env[st + 1], Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4, sUw,
+                                                         D, H, c_rosAlpha[st] * h, st == ROS_S - 1);
           n_evals++;
         } else {
 #pragma unroll
@@ -1393,7 +1501,7 @@ __global__ void __launch_bounds__(NT) k_condense_bdf(DevView v, const double* T0
 
 // device pointers T1/p1 (final env per cell)
 static size_t bdf_smem(int ppt) { return (size_t)BDF_NARR * ppt * COND_THREADS * sizeof(double); }
-static size_t ros_smem(int ppt, int nt) { return (size_t)COND_NARR * ppt * nt * sizeof(double); }
+static size_t ros_smem(int ppt, int nt) { return (size_t)COND_NARR(ppt) * ppt * nt * sizeof(double); }
 
 int pmc_reweight_async(pmcgpu_ctx* ctx, unsigned step, unsigned pass);
 
