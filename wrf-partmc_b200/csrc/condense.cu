@@ -327,8 +327,12 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
     kB[k] = fma(UVD[k], H, k_ap[k]);
     cW[k] = e.W - XD[k];
     u[k] = 0.0;
-    if (MODE == 1 || MODE == 2 || MODE == 5) {
+    if (MODE == 1 || MODE == 5) {
       const double up = sw[(MODE == 1 ? 4 : 0) * AS + k * NT];
+      if (fabs(up) < 0.5) u[k] = up;
+    }
+    if (MODE == 2) {  // u0 + (du/dt of the previous step) DT_FD
+      const double up = fma(sw[3 * AS + k * NT], COND_DT_FD, sw[k * NT]);
       if (fabs(up) < 0.5) u[k] = up;
     }
     if (MODE == 3) {
@@ -560,6 +564,11 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   const int poff = GRID ? blockIdx.x * PPT : 0;
   const bool writer = !GRID || blockIdx.x == 0;
   __shared__ double s_g[4];
+  if (GRID) {  // nothing to do unless some cell is larger than the per-CTA kernels handle (uniform over the grid)
+    int any = 0;
+    for (int c = threadIdx.x; c < v.n_cells; c += NT) any |= (v.count[c] > n_limit_lo);
+    if (!__syncthreads_or(any)) return;
+  }
   for (int cell = GRID ? 0 : blockIdx.x; cell < (GRID ? v.n_cells : (int)blockIdx.x + 1); cell++) {
   const int n = v.count[cell];
   if (n <= n_limit_lo || n > n_limit_hi) continue;  // another instantiation owns this cell
