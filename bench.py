@@ -136,7 +136,7 @@ def run_reference(a):
                                               "one patch per thread"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -401,14 +401,32 @@ def run_b200(a):
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": ncores, "kind": "port",
                                     "sample": desc + ", 2 timed steps after 1 warm-up; CPU restatement of the "
                                                      "reference (oracle/), one patch per thread"}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """the ONE JSON line, on the process's real stdout"""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
     a = parse()
+    # libraries (NCCL's version banner, torch warnings) write to fd 1: send everything but the JSON line to stderr
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
     else:
