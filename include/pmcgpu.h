@@ -201,6 +201,28 @@ typedef struct {
   int no_wait;
 } pmcgpu_trans_args;
 int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_args* args);
+
+/* wrf_pmc_dep_dry_driver (interface/wrf_pmc_dep.F90:31-97, called from wrf_pmc_trans_driver when
+ * grid%do_deposition, wrf_pmc_trans.F90:183-197): dry deposition of particles in the lowest layer.
+ * Aerodynamic resistance from depvel_partmc (:188-213), per-particle deposition velocity and removal
+ * probability (dt / dz) v_d from Zhang et al. (2001) as coded in wrf_pmc_dep_aero.F90:204-470, land-use
+ * mapping of dep_aero_dry_driver (:31-150), backward removal loop of aero_particles_remove_by_dep (:280).
+ * All fields are 2-D, [ny][nx] with i fastest (host or device pointers); cells on the outermost ring of
+ * the GLOBAL domain are skipped like in the reference (:113-114). */
+typedef struct {
+  const float* rmol;     /* grid%rmol: inverse Monin-Obukhov length */
+  const float* znt;      /* grid%znt: roughness length (m) */
+  const float* ust;      /* grid%ust: friction velocity (m/s) */
+  const int* ivgtyp;     /* grid%ivgtyp: USGS land-use category */
+  const double* height;  /* env_states(i,1,j)%height = z_at_w(i,2,j) - z_at_w(i,1,j) (wrf_pmc_driver.F90:627) */
+  double dt;             /* grid%dt */
+  unsigned int step;     /* addresses the random draws */
+  int no_wait;           /* 1: return without waiting for the device */
+} pmcgpu_dep_args;
+int pmcgpu_wrf_pmc_dep_dry_driver(pmcgpu_ctx* ctx, const pmcgpu_dep_args* args);
+/* unit evaluation of the deposition formulas (parity tests): in[n][10] = diameter, density, temp,
+ * inverse_density, ustar, rmol, znt, ivgtyp, dt, dz; out[n][3] = aer_res, v_d, removal probability */
+int pmcgpu_eval_dep(pmcgpu_ctx* ctx, int n, const double* in, double* out);
 /* patch decomposition of the periodic domain: px x py patches, rank = rx + px * ry, one process and one
  * GPU per patch (WRF's 2-D decomposition; MPI_Cart_shift of wrf_pmc_trans_aero.F90:153-159).  unique_id is
  * the 128-byte NCCL id made by pmcgpu_comm_unique_id on one rank and distributed by the host (MPI_Bcast in

@@ -269,9 +269,30 @@ class Oracle:
         self.L.pmco_num_conc_by_class(self.h, _p(out, C.c_float))
         return out
 
+    def dep_dry_driver(self, nx, nz, ny, rmol, znt, ust, ivgtyp, height, dt, step=0, i_offset=0, j_offset=0,
+                       global_nx=None, global_ny=None):
+        """wrf_pmc_dep_dry_driver (wrf_pmc_dep.F90:31): dry deposition in the lowest layer; 2-D fields [ny][nx]"""
+        a = [np.ascontiguousarray(x, np.float32).ravel() for x in (rmol, znt, ust)]
+        iv = _i32(np.asarray(ivgtyp).ravel())
+        hg = _f64(np.asarray(height).ravel())
+        self._chk(self.L.pmco_dep_dry_driver(
+            self.h, C.c_int(nx), C.c_int(nz), C.c_int(ny), C.c_int(i_offset), C.c_int(j_offset),
+            C.c_int(global_nx if global_nx is not None else nx), C.c_int(global_ny if global_ny is not None else ny),
+            _p(a[0], C.c_float), _p(a[1], C.c_float), _p(a[2], C.c_float), _p(iv, C.c_int), _p(hg, C.c_double),
+            C.c_double(dt), C.c_uint(step)))
+
     def scale_weight(self, cell, g, c, ratio, allow_doubling=True, allow_halving=True, step=0):
         self._chk(self.L.pmco_scale_weight(self.h, C.c_int(cell), C.c_int(g), C.c_int(c), C.c_double(ratio),
                                            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step)))
+
+
+def dep_eval(inputs):
+    """inputs [n][10] = diameter, density, temp, rrho, ustar, rmol, znt, ivgtyp, dt, dz ->
+    outputs [n][3] = aer_res, vd, remove_prob (wrf_pmc_dep.F90:188, wrf_pmc_dep_aero.F90:204-275)"""
+    a = _f64(inputs).reshape(-1, 10)
+    out = np.zeros((a.shape[0], 3))
+    lib().pmco_dep_eval(C.c_int(a.shape[0]), _p(a, C.c_double), _p(out, C.c_double))
+    return out
 
 
 def condense_rates(inputs):

@@ -71,7 +71,8 @@ enum Phase : uint32_t {
   PH_DOUBLE = 5,
   PH_SCALE = 6,       // a = (group,class), b = 0 (count) / removal number
   PH_TRANS = 7,       // a = class*64 + direction slot, b = 0 (count) / transfer
-  PH_INIT = 8
+  PH_INIT = 8,
+  PH_DEP = 9          // a = 0, b = particle index (dry deposition)
 };
 struct RngKey {
   uint32_t cell, step, phase, a, b;

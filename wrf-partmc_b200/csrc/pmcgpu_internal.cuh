@@ -14,7 +14,7 @@
 
 // draw-address phases; must agree with the documented stream layout
 enum : uint32_t {
-  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8
+  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8, PH_DEP = 9
 };
 
 struct PmcConst {  // partmc/src/constants.F90:30-65
@@ -157,6 +157,7 @@ struct pmcgpu_ctx {
   int nb[4] = {0, 0, 0, 0};
   void* nccl_comm = nullptr;
   int cond_method = 4;  // 4: RODAS4, 5: BDF (CVODE restatement) (pmcgpu_set_condense_method)
+  char* dep_buf = nullptr;          // device copies of the 2-D surface fields of the deposition driver
   double* cond_grid_buf = nullptr;  // partial sums + barrier counter of the grid-wide condensation kernel
   unsigned rng_step = 0;     // step number addressing the draws of the stand-alone condensation calls (pmcgpu_set_rng_step)
   bool any_nonflat = false;  // some weight is size dependent (set by pmcgpu_set_weights): aero_state_reweight is not the identity

@@ -68,6 +68,14 @@ module pmc_gpu
      integer(c_int) :: no_wait
   end type pmcgpu_trans_args_t
 
+  !> pmcgpu_dep_args (include/pmcgpu.h)
+  type, bind(c) :: pmcgpu_dep_args_t
+     type(c_ptr) :: rmol, znt, ust, ivgtyp, height
+     real(c_double) :: dt
+     integer(c_int) :: step
+     integer(c_int) :: no_wait
+  end type pmcgpu_dep_args_t
+
   !> Opaque device context of this MPI rank (one GPU per rank).
   type(c_ptr), save :: pmc_gpu_handle = c_null_ptr
   !> Counter that addresses the random draws: two values per WRF step.
@@ -130,6 +138,12 @@ module pmc_gpu
        type(c_ptr), value :: ctx
        type(pmcgpu_trans_args_t), intent(in) :: args
      end function pmcgpu_wrf_pmc_trans_driver
+     integer(c_int) function pmcgpu_wrf_pmc_dep_dry_driver(ctx, args) &
+          bind(c, name='pmcgpu_wrf_pmc_dep_dry_driver')
+       import :: c_int, c_ptr, pmcgpu_dep_args_t
+       type(c_ptr), value :: ctx
+       type(pmcgpu_dep_args_t), intent(in) :: args
+     end function pmcgpu_wrf_pmc_dep_dry_driver
      integer(c_int) function pmcgpu_check_status(ctx) bind(c, name='pmcgpu_check_status')
        import :: c_int, c_ptr
        type(c_ptr), value :: ctx
@@ -473,6 +487,42 @@ contains
     pmc_gpu_step = pmc_gpu_step + 1
     call pmc_gpu_check(pmcgpu_wrf_pmc_trans_driver(pmc_gpu_handle, args), &
          'pmcgpu_wrf_pmc_trans_driver')
+    ! Do deposition on lowest layer (wrf_pmc_trans.F90:183-197)
+    if (pmc_ks == 1 .and. grid%do_deposition) then
+       call pmc_gpu_wrf_pmc_dep_dry_driver(grid, pmc_is, pmc_ie, pmc_js, pmc_je)
+    end if
   end subroutine pmc_gpu_wrf_pmc_trans_driver
+
+  !> Drop-in for wrf_pmc_dep_dry_driver (interface/wrf_pmc_dep.F90:31): only the 2-D surface fields
+  !> cross the boundary; the particles of the lowest layer are already on the device.
+  subroutine pmc_gpu_wrf_pmc_dep_dry_driver(grid, pmc_is, pmc_ie, pmc_js, pmc_je)
+    use module_domain, only: domain
+    type(domain), intent(inout) :: grid
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je
+
+    type(pmcgpu_dep_args_t) :: args
+    real(c_float), allocatable, target :: rmol(:,:), znt(:,:), ust(:,:)
+    integer(c_int), allocatable, target :: ivgtyp(:,:)
+    real(c_double), allocatable, target :: height(:,:)
+
+    rmol = grid%rmol(pmc_is:pmc_ie, pmc_js:pmc_je)
+    znt = grid%znt(pmc_is:pmc_ie, pmc_js:pmc_je)
+    ust = grid%ust(pmc_is:pmc_ie, pmc_js:pmc_je)
+    ivgtyp = grid%ivgtyp(pmc_is:pmc_ie, pmc_js:pmc_je)
+    ! env_states(i,1,j)%height (wrf_pmc_driver.F90:627)
+    height = real(grid%z_at_w(pmc_is:pmc_ie, 2, pmc_js:pmc_je) &
+         - grid%z_at_w(pmc_is:pmc_ie, 1, pmc_js:pmc_je), c_double)
+    args%rmol = c_loc(rmol)
+    args%znt = c_loc(znt)
+    args%ust = c_loc(ust)
+    args%ivgtyp = c_loc(ivgtyp)
+    args%height = c_loc(height)
+    args%dt = real(grid%dt, c_double)
+    args%step = pmc_gpu_step
+    args%no_wait = 0
+    pmc_gpu_step = pmc_gpu_step + 1
+    call pmc_gpu_check(pmcgpu_wrf_pmc_dep_dry_driver(pmc_gpu_handle, args), &
+         'pmcgpu_wrf_pmc_dep_dry_driver')
+  end subroutine pmc_gpu_wrf_pmc_dep_dry_driver
 
 end module pmc_gpu

@@ -78,6 +78,11 @@ class _TimestepArgs(C.Structure):
                 ("rel_humid_out", C.c_void_p), ("no_wait", C.c_int)]
 
 
+class _DepArgs(C.Structure):
+    _fields_ = [("rmol", C.c_void_p), ("znt", C.c_void_p), ("ust", C.c_void_p), ("ivgtyp", C.c_void_p),
+                ("height", C.c_void_p), ("dt", C.c_double), ("step", C.c_uint), ("no_wait", C.c_int)]
+
+
 class _TransArgs(C.Structure):
     _fields_ = [("u_flux", C.c_void_p), ("v_flux", C.c_void_p), ("w_flux", C.c_void_p), ("xkhh", C.c_void_p),
                 ("alt", C.c_void_p), ("z", C.c_void_p), ("z_at_w", C.c_void_p), ("exch_h", C.c_void_p),
@@ -320,6 +325,25 @@ class PartMCGPU:
         self._chk(self.L.pmcgpu_wrf_pmc_trans_driver(self.h, C.byref(a)))
         if no_wait and keep:
             self.synchronize()  # host copies made here must outlive the asynchronous upload
+
+    def wrf_pmc_dep_dry_driver(self, rmol, znt, ust, ivgtyp, height, dt, step=0):
+        """wrf_pmc_dep_dry_driver (interface/wrf_pmc_dep.F90:31): dry deposition in the lowest layer.
+        2-D fields [ny][nx]: rmol, znt, ust (WRF reals), ivgtyp (USGS land use), height of the lowest layer."""
+        a = _DepArgs()
+        keep = [np.ascontiguousarray(x, dtype=np.float32) for x in (rmol, znt, ust)]
+        keep.append(np.ascontiguousarray(ivgtyp, dtype=np.int32))
+        keep.append(np.ascontiguousarray(height, dtype=np.float64))
+        for x in keep:
+            assert x.size == self.nx * self.ny
+        a.rmol, a.znt, a.ust, a.ivgtyp, a.height = [_addr(x) for x in keep]
+        a.dt, a.step, a.no_wait = float(dt), int(step), 0
+        self._chk(self.L.pmcgpu_wrf_pmc_dep_dry_driver(self.h, C.byref(a)))
+
+    def eval_dep(self, inputs):
+        a = _f64(inputs).reshape(-1, 10)
+        out = np.zeros((a.shape[0], 3))
+        self._chk(self.L.pmcgpu_eval_dep(self.h, C.c_int(a.shape[0]), _p(a), _p(out)))
+        return out
 
     def trans_probs(self):
         """(adv[n_cells][C][6], diff[n_cells][C][4], vert[n_cells][C][nz]) of the last transport call"""
