@@ -664,10 +664,10 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   const int warp = tid >> 5, lane = tid & 31;
   // the (T, p) terms of condense_rates at the ROS_NENV times of a step: warp w evaluates entry w
   auto make_envs = [&](double t, double h, int first, int last) {
-    if (warp >= first && warp <= last) {
-      const double tt = (warp == 0) ? t : (warp == 1) ? t + DT_FD : t + c_rosAlpha[warp - 1] * h;
+    for (int w = first + warp; w <= last; w += NT / 32) {  // entry w by warp (w - first) mod (NT / 32)
+      const double tt = (w == 0) ? t : (w == 1) ? t + DT_FD : t + c_rosAlpha[w - 1] * h;
       const CondEnv e = cond_env_fast(T0, p0, Tdot, pdot, tt);
-      if (lane == 0) s_env[warp] = e;
+      if (lane == 0) s_env[w] = e;
     }
     __syncthreads();
   };
@@ -1518,7 +1518,8 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
                        double del_t, double reltol, unsigned step) {
   static bool configured = false;
   if (!configured) {
-    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(2, 256)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 128)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 64)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 256)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<8, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(8, 256)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<2, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(2)));
@@ -1543,7 +1544,8 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
   prm.debug_cell = getenv("PMCGPU_DEBUG_CELL") ? atoi(getenv("PMCGPU_DEBUG_CELL")) : -1;
   {
   ProfScope ps_(ctx, "k_condense");
-  // the population size of a cell picks the instantiation: 1..256 -> PPT 1, ..512 -> 2, ..1024 -> 4, ..2048 -> 8
+  // the population size of a cell picks the instantiation: 1..256 -> PPT 1, ..512 -> 4 x 128 threads (BDF: 2),
+  // ..1024 -> 4, ..2048 -> 8
   const int cap = v.cap;
   if (ctx->cond_method == 5) {
 #define BDF_LAUNCH(PPT, LO, HI)                                                                                   \
@@ -1562,8 +1564,10 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
   LAUNCH_CHECK(ctx)
     // 256 threads x 4 particles per thread measured faster than 512 x 2 at ~1000 particles per cell
     // (300 vs 318 ms per K4 step): instruction-level parallelism beats the extra warps here
-    ROS_LAUNCH(1, 256, -1, 256);
-    if (cap > 256) { ROS_LAUNCH(2, 256, 256, 512); }
+    ROS_LAUNCH(4, 64, -1, 256);  // small cells: four CTAs of 64 threads per SM
+    // 257..512 particles: 128 threads x 4 particles, so that two cells share an SM (244 registers x 128
+    // threads each) instead of one CTA of 256 threads x 2 particles leaving half the register file idle
+    if (cap > 256) { ROS_LAUNCH(4, 128, 256, 512); }
     if (cap > 512) { ROS_LAUNCH(4, 256, 512, 1024); }
     if (cap > 1024) { ROS_LAUNCH(8, 256, 1024, 2048); }
 #undef ROS_LAUNCH
