@@ -20,6 +20,7 @@
 // in a 3*cap arena (lists start as the contiguous runs the sort produced and
 // are relocated with doubled capacity when they outgrow their run), with the
 // same swap-with-last bookkeeping as integer_rmap2_remove (:190-243).
+#define PMC_RNG_NOINLINE
 #include "pmcgpu_internal.cuh"
 
 #define COAG_WARPS 4
@@ -49,6 +50,7 @@ __device__ __forceinline__ int lkey(const CellCtx& cx, int c, int b) { return (c
 __device__ __forceinline__ void part_vol_mass(const CellCtx& cx, int p, double& vol, double& mass) {
   const DevView& v = *cx.v;
   double vt = 0.0, mt = 0.0;
+#pragma unroll 5
   for (int s = 0; s < v.S; s++) {
     const double x = v.vol[(size_t)s * cx.NS + cx.base + p];
     vt += x;
@@ -59,7 +61,7 @@ __device__ __forceinline__ void part_vol_mass(const CellCtx& cx, int p, double& 
 }
 
 // coag_kernel.F90:346-377
-__device__ __forceinline__ double coag_num_conc_factor(const CellCtx& cx, double i_r, double j_r, int ic, int jc,
+__device__ __noinline__ double coag_num_conc_factor(const CellCtx& cx, double i_r, double j_r, int ic, int jc,
                                                        int ijc) {
   const double ij_r = vol2rad(rad2vol(i_r) + rad2vol(j_r));
   const double i_nc = awa_nc_at_radius(*cx.v, cx.cell, ic, i_r);
@@ -83,7 +85,7 @@ __device__ __forceinline__ void move_record(CellCtx& cx, int dst, int src) {
 
 // aero_sorted_remove_particle (aero_sorted.F90:455-470): apa swap-with-last +
 // integer_rmap2_remove on size_class.  p is a 0-based slot.
-__device__ void cell_remove_particle(CellCtx& cx, int p) {
+__device__ __noinline__ void cell_remove_particle(CellCtx& cx, int p) {
   const DevView& v = *cx.v;
   const int last = cx.n_part - 1;
   if (cx.lane == 0) {
@@ -113,7 +115,7 @@ __device__ void cell_remove_particle(CellCtx& cx, int p) {
 }
 
 // integer_varray_append on list (c, b) with pow2-style growth inside the arena
-__device__ void cell_list_append(CellCtx& cx, int c, int b, int slot) {
+__device__ __noinline__ void cell_list_append(CellCtx& cx, int c, int b, int slot) {
   const DevView& v = *cx.v;
   const int k = lkey(cx, c, b);
   int len = cx.llen[k], capk = cx.lcap[k], lp = cx.lptr[k];
@@ -155,7 +157,7 @@ __device__ __forceinline__ double unweighted_kernel(int ktype, const BrownEnv& b
 
 // coagulate (coagulation.F90:928-985) + coagulate_weighting (:810-922) for the
 // particles in slots p1, p2 (0-based); warp-cooperative, uniform arguments.
-__device__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1, int c2, int cc, const RKey& key) {
+__device__ __noinline__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1, int c2, int cc, const RKey& key) {
   const DevView& v = *cx.v;
   double v1, m1, v2, m2;
   part_vol_mass(cx, p1, v1, m1);
@@ -338,7 +340,7 @@ __device__ __forceinline__ int rand_group_seq(const CellCtx& cx, int c, double r
 
 // integer_rmap2_change (integer_rmap2.F90:139-185) on size_class for slot p of class c: only the bin
 // changes on the accelerated path (ct == cc); an unchanged bin returns early like the reference (:160)
-__device__ void cell_change_bin(CellCtx& cx, int p, int c, int new_bin) {
+__device__ __noinline__ void cell_change_bin(CellCtx& cx, int p, int c, int new_bin) {
   const DevView& v = *cx.v;
   const int b_old = v.pbin[cx.base + p];
   if (b_old == new_bin) return;
@@ -361,7 +363,7 @@ __device__ void cell_change_bin(CellCtx& cx, int p, int c, int new_bin) {
 }
 
 // aero_state_dup_particle (aero_state.F90:488-539) for the sorted state of mc_coag: slot p of class c
-__device__ void cell_dup_particle(CellCtx& cx, int p, int c, double n_part_mean, bool random_weight_group,
+__device__ __noinline__ void cell_dup_particle(CellCtx& cx, int p, int c, double n_part_mean, bool random_weight_group,
                                   RStream& s) {
   const DevView& v = *cx.v;
   const int n_copies = prob_round(n_part_mean, s.next());
@@ -558,7 +560,51 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
   }
 }
 
-__global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
+// the reference's bin-pair order (coagulation.F90:74-94) as a flat sequence: step k pairs forward from
+// (c1, c2, b1, b2), skipping rows whose first bin is empty; false past the end
+__device__ __forceinline__ bool pair_advance(const CellCtx& cx, int C, int nb, int& c1, int& c2, int& b1, int& b2,
+                                             int k) {
+  for (;;) {
+    if (cx.llen[lkey(cx, c1, b1)] > 0) {
+      const int rem = nb - b2 + 1;
+      if (k < rem) {
+        b2 += k;
+        return true;
+      }
+      k -= rem;
+    }
+    b1++;
+    if (b1 > nb) {
+      b1 = 1;
+      c2++;
+      if (c2 > c1) {
+        c1++;
+        c2 = 1;
+        if (c1 > C) return false;
+      }
+    }
+    b2 = (c1 == c2) ? b1 : 1;
+  }
+}
+// one pair forward, whatever the occupancy of the row (the pair behind the one just handled)
+__device__ __forceinline__ bool pair_advance_exact(int C, int nb, int& c1, int& c2, int& b1, int& b2) {
+  b2++;
+  if (b2 <= nb) return true;
+  b1++;
+  if (b1 > nb) {
+    b1 = 1;
+    c2++;
+    if (c2 > c1) {
+      c1++;
+      c2 = 1;
+      if (c1 > C) return false;
+    }
+  }
+  b2 = (c1 == c2) ? b1 : 1;
+  return true;
+}
+
+__global__ void __launch_bounds__(COAG_WARPS * 32, 8) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * COAG_WARPS + warp;
   if (cell >= v.n_cells) return;
@@ -635,20 +681,29 @@ __global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktyp
   const BrownEnv be = brown_env(v.temp[cell], v.pres[cell]);
   const double* ktab = v.kmax + (size_t)cell * v.nbcap * v.nbcap;
 
-  for (int c1 = 1; c1 <= v.C && !cx.err; c1++) {
-    for (int c2 = 1; c2 <= c1 && !cx.err; c2++) {
-      for (int b1 = 1; b1 <= nb && !cx.err; b1++) {
-        if (cx.llen[lkey(cx, c1, b1)] == 0) continue;
-        int b2 = (c1 == c2) ? b1 : 1;
-        while (b2 <= nb && !cx.err) {
-          // ---- lane-parallel scan of 32 candidate partner bins
-          const int my_b2 = b2 + lane;
+  // The bin pairs are visited in the reference's order (coagulation.F90:74-94: c1, c2 <= c1, b1, b2 from b1
+  // resp. 1) through one cursor over the flattened sequence: the 32 lanes scan the next 32 pairs -- across
+  // row and class boundaries, rows with an empty first bin skipped like the reference's `cycle` -- and the
+  // warp handles the first pair that has samples; after an event the scan resumes right behind that pair.
+  int cu_c1 = 1, cu_c2 = 1, cu_b1 = 1, cu_b2 = 1;
+  bool more = true;
+  while (more && !cx.err) {
+    {
+      {
+        {
+          // ---- lane-parallel scan of 32 candidate bin pairs
+          int c1 = cu_c1, c2 = cu_c2, b1 = cu_b1, my_b2 = cu_b2;
+          const bool valid = pair_advance(cx, v.C, nb, c1, c2, b1, my_b2, lane);
+          more = __shfl_sync(0xffffffffu, (int)valid, 0) != 0;
+          if (!more) break;
           int n_samp = 0, cc = c2, accel = 0;
           double k_max = 0.0;
-          const int n1 = cx.llen[lkey(cx, c1, b1)];
-          int n2 = 0;
-          if (my_b2 <= nb) n2 = cx.llen[lkey(cx, c2, my_b2)];
-          if (n2 > 0) {
+          int n1 = 0, n2 = 0;
+          if (valid) {
+            n1 = cx.llen[lkey(cx, c1, b1)];
+            n2 = cx.llen[lkey(cx, c2, my_b2)];
+          }
+          if (n1 > 0 && n2 > 0) {
             double f_max;
             const bool pair_flat = all_flat || (flat[c1 - 1] && flat[c2 - 1]);
             if (pair_flat) {
@@ -697,31 +752,33 @@ __global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktyp
           }
           unsigned has = __ballot_sync(0xffffffffu, (n_samp > 0) || accel);
           bool rescan = false;
-          int next_b2 = b2 + 32;
           while (has && !rescan && !cx.err) {
             const int f = __ffs(has) - 1;
             has &= has - 1;
-            const int pb2 = b2 + f;
+            const int pb2 = __shfl_sync(0xffffffffu, my_b2, f);
+            const int p_c1 = __shfl_sync(0xffffffffu, c1, f), p_c2 = __shfl_sync(0xffffffffu, c2, f);
+            const int p_b1 = __shfl_sync(0xffffffffu, b1, f);
             const int p_nsamp = __shfl_sync(0xffffffffu, n_samp, f);
             const int p_cc = __shfl_sync(0xffffffffu, cc, f);
             const double p_kmax = __shfl_sync(0xffffffffu, k_max, f);
             const int p_accel = __shfl_sync(0xffffffffu, accel, f);
             if (p_accel) {
-              const unsigned apid = ((unsigned)((c1 - 1) * v.C + (c2 - 1)) * 256u + (unsigned)b1) * 256u + (unsigned)pb2;
-              const bool pflat = all_flat || (flat[c1 - 1] && flat[c2 - 1]);
+              const unsigned apid = ((unsigned)((p_c1 - 1) * v.C + (p_c2 - 1)) * 256u + (unsigned)p_b1) * 256u + (unsigned)pb2;
+              const bool pflat = all_flat || (flat[p_c1 - 1] && flat[p_c2 - 1]);
               int bt = 0, bs = 0, ct = 0, cs = 0;
-              accel_target_source(cx, pflat, hm, b1, pb2, c1, c2, p_cc, bt, bs, ct, cs);
+              accel_target_source(cx, pflat, hm, p_b1, pb2, p_c1, p_c2, p_cc, bt, bs, ct, cs);
               cell_accel_pair(cx, ktype, be, p_kmax, del_t, step, apid, bt, bs, ct, cs, p_cc, tot_n_samp, tot_n_coag);
               rescan = true;  // counts changed: pairs behind this one must be rescanned
-              next_b2 = pb2 + 1;
+              cu_c1 = p_c1; cu_c2 = p_c2; cu_b1 = p_b1; cu_b2 = pb2;
+              more = pair_advance_exact(v.C, nb, cu_c1, cu_c2, cu_b1, cu_b2);
               continue;
             }
             // ---- per_set_coag (coagulation.F90:587-643)
             tot_n_samp += p_nsamp;
-            const bool same = (b1 == pb2) && (c1 == c2);
+            const bool same = (p_b1 == pb2) && (p_c1 == p_c2);
             const double accept_factor = 1.0 / p_kmax;
-            const unsigned pid = ((unsigned)((c1 - 1) * v.C + (c2 - 1)) * 256u + (unsigned)b1) * 256u + (unsigned)pb2;
-            const int k1 = lkey(cx, c1, b1), k2 = lkey(cx, c2, pb2);
+            const unsigned pid = ((unsigned)((p_c1 - 1) * v.C + (p_c2 - 1)) * 256u + (unsigned)p_b1) * 256u + (unsigned)pb2;
+            const int k1 = lkey(cx, p_c1, p_b1), k2 = lkey(cx, p_c2, pb2);
             int d = 1;
             while (d <= p_nsamp && !cx.err) {
               const int m1 = cx.llen[k1], m2 = cx.llen[k2];
@@ -747,7 +804,7 @@ __global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktyp
                 part_vol_mass(cx, p1, v1, ms1);
                 part_vol_mass(cx, p2, v2, ms2);
                 const double uk = unweighted_kernel(ktype, be, v1, ms1, v2, ms2);
-                const double k = uk * coag_num_conc_factor(cx, vol2rad(v1), vol2rad(v2), c1, c2, p_cc);
+                const double k = uk * coag_num_conc_factor(cx, vol2rad(v1), vol2rad(v2), p_c1, p_c2, p_cc);
                 accept = rng_uniform(key, 2) < k * accept_factor;  // maybe_coag_pair :753
               }
               const unsigned acc = __ballot_sync(0xffffffffu, accept);
@@ -759,14 +816,17 @@ __global__ void __launch_bounds__(COAG_WARPS * 32) k_mc_coag(DevView v, int ktyp
               const int e1 = __shfl_sync(0xffffffffu, p1, fa);
               const int e2 = __shfl_sync(0xffffffffu, p2, fa);
               const RKey ekey{v.seed, (unsigned)v.gcell[cell], step, PH_COAG, pid, (unsigned)(d + fa)};
-              cell_coagulate(cx, e1, e2, c1, c2, p_cc, ekey);
+              cell_coagulate(cx, e1, e2, p_c1, p_c2, p_cc, ekey);
               tot_n_coag += 1;
               rescan = true;  // counts changed: pairs behind this one must be rescanned
               d = d + fa + 1;
             }
-            if (rescan) next_b2 = pb2 + 1;
+            if (rescan) {  // resume right behind the pair that changed the counts
+              cu_c1 = p_c1; cu_c2 = p_c2; cu_b1 = p_b1; cu_b2 = pb2;
+              more = pair_advance_exact(v.C, nb, cu_c1, cu_c2, cu_b1, cu_b2);
+            }
           }
-          b2 = next_b2;
+          if (!rescan) more = pair_advance(cx, v.C, nb, cu_c1, cu_c2, cu_b1, cu_b2, 32);
         }
       }
     }

@@ -236,7 +236,14 @@ __device__ __forceinline__ void philox_block(uint32_t c0, uint32_t c1, uint32_t 
 struct RKey {
   uint32_t seed, cell, step, phase, a, b;
 };
+// PMC_RNG_NOINLINE (defined by a translation unit before this header): one out-of-line copy of the
+// generator instead of one per call site; kernels with many draw sites (mc_coag) otherwise outgrow the
+// instruction cache
+#ifdef PMC_RNG_NOINLINE
+static __device__ __noinline__ double rng_uniform(const RKey& k, uint32_t j) {
+#else
 __device__ __forceinline__ double rng_uniform(const RKey& k, uint32_t j) {
+#endif
   uint32_t o[4];
   philox_block(j >> 1, k.b, k.a, k.cell, k.seed, k.step * 16u + k.phase, o);
   const uint32_t hi = (j & 1u) ? o[2] : o[0];
@@ -267,7 +274,11 @@ __device__ inline double rand_normal(double mean, double stddev, RStream& s) {
   return stddev * (r * cos(theta)) + mean;
 }
 // rand.F90:252-304 in-tree branch
+#ifdef PMC_RNG_NOINLINE
+static __device__ __noinline__ int rand_poisson(double mean, RStream& s) {
+#else
 __device__ inline int rand_poisson(double mean, RStream& s) {
+#endif
   if (mean <= 10.0) {
     const double L = exp(-mean);
     int k = 0;
@@ -309,7 +320,11 @@ __device__ inline int rand_binomial(int n, double p, RStream& s) {
 }
 
 // util.F90:240 / :265 (spherical particles, fractal.F90:113)
+#ifdef PMC_RNG_NOINLINE
+static __device__ __noinline__ double vol2rad(double v) { return pow(3.0 * v / 4.0 / PmcConst::pi, 1.0 / 3.0); }
+#else
 __device__ __forceinline__ double vol2rad(double v) { return pow(3.0 * v / 4.0 / PmcConst::pi, 1.0 / 3.0); }
+#endif
 __device__ __forceinline__ double rad2vol(double r) { return 4.0 * PmcConst::pi * (r * r * r) / 3.0; }
 // util.F90:663
 __device__ __forceinline__ double interp_linear_disc(double x_1, double x_n, int n, int i) {
@@ -329,14 +344,22 @@ __device__ __forceinline__ int log_grid_find(double ln_min, double ln_max, int n
   return (int)v;
 }
 // bin_grid.F90:83-134 edges = exp(linspace(ln min, ln max, n_bin+1)) with exact ends
+#ifdef PMC_RNG_NOINLINE
+static __device__ __noinline__ double grid_edge(double gmin, double gmax, int n_bin, int i /*1..n_bin+1*/) {
+#else
 __device__ __forceinline__ double grid_edge(double gmin, double gmax, int n_bin, int i /*1..n_bin+1*/) {
+#endif
   if (i == 1) return gmin;
   if (i == n_bin + 1) return gmax;
   const double a = (double)(i - 1) / (double)n_bin;
   return exp((1.0 - a) * log(gmin) + a * log(gmax));
 }
 // bin_grid.F90:113-118 centers = logspace(c1, c2, n_bin)
+#ifdef PMC_RNG_NOINLINE
+static __device__ __noinline__ double grid_center(double gmin, double gmax, int n_bin, int i /*1..n_bin*/) {
+#else
 __device__ __forceinline__ double grid_center(double gmin, double gmax, int n_bin, int i /*1..n_bin*/) {
+#endif
   const double c1 = exp(interp_linear_disc(log(gmin), log(gmax), 2 * n_bin + 1, 2));
   const double c2 = exp(interp_linear_disc(log(gmin), log(gmax), 2 * n_bin + 1, 2 * n_bin));
   if (i == 1) return c1;
@@ -351,7 +374,11 @@ __device__ __forceinline__ double weight_nc(int type, double mag, double ex, dou
   return mag * pow(radius, ex);
 }
 // aero_weight_array.F90:232-251: harmonic combination over groups of class c (1-based)
+#ifdef PMC_RNG_NOINLINE
+static __device__ __noinline__ double awa_nc_at_radius(const DevView& v, int cell, int c, double radius) {
+#else
 __device__ __forceinline__ double awa_nc_at_radius(const DevView& v, int cell, int c, double radius) {
+#endif
   const size_t base = ((size_t)cell * v.C + (c - 1)) * v.G;
   double s = 0.0;
   for (int g = 0; g < v.G; g++) s += 1.0 / weight_nc(v.wtype[base + g], v.wmag[base + g], v.wexp[base + g], radius);
