@@ -113,6 +113,15 @@ int pmcgpu_kernel_bounds(pmcgpu_ctx* ctx, int coag_kernel_type);
  * per-cell outputs [n_cells], may be NULL.  step addresses the random draws. */
 int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned int step, int* tot_n_samp,
                    int* tot_n_coag);
+/* aero_state_scale_weight (aero_state.F90:1832-1895) for (i_group, i_class) of every cell:
+ * weight_ratio[n_cells] (host or device; <= 0 or exactly 1 leaves a cell alone).  ratio > 1: magnitude x ratio,
+ * prob_round(n (1 - 1/ratio)) random particles of the class removed; ratio < 1: magnitude x ratio, every
+ * particle of the class duplicated prob_round(1/ratio) - 1 times.  Used by the reference for preweighting in
+ * transport (ratio > 1, also built into pmcgpu_wrf_pmc_trans_driver) and by aero_state_prepare_weight_for_add
+ * before emissions (:703-757). */
+int pmcgpu_aero_state_scale_weight(pmcgpu_ctx* ctx, int i_group, int i_class, const double* weight_ratio,
+                                   int allow_doubling, int allow_halving, unsigned step);
+
 /* Step number that addresses the random draws of the stand-alone condensation calls below (the
  * prob_round draws of aero_state_reweight, aero_state.F90:597-653, when weights depend on size);
  * pmcgpu_partmc_timestep uses its own `step` argument instead.  The reference has one global

@@ -289,3 +289,30 @@ def test_mc_coag_k2_single_box_bit_exact(mods, weight, n_group):
         assert (s, k) == (ns[0], nc[0])
         assert k > 5000
         common.assert_same_population(g, o, case)
+
+
+@pytest.mark.parametrize("n_spec,n_class,n_group", [(3, 2, 1), (1, 2, 2)])
+def test_scale_weight_both_branches_bit_exact(mods, n_spec, n_class, n_group):
+    """aero_state_scale_weight (aero_state.F90:1832-1895): ratio > 1 (random removals with the list surgery
+    of integer_rmap2_remove), ratio < 1 (backward duplication with new ids), ratio 1 and refused cases
+    (allow_halving / allow_doubling false), per (group, class), against the oracle."""
+    W, O = mods
+    n_cells = 8
+    case = common.make_cells(n_cells, 500, n_spec=n_spec, n_class=n_class, n_group=n_group, seed=21,
+                             weight="flat" if n_group == 1 else "nummass")
+    g = common.gpu_from_case(W, case, cell_capacity=8000)
+    o = common.oracle_from_case(O, case)
+    ratios = np.array([1.7, 0.4, 1.0, 3.2, 0.93, 1.01, 0.25, 2.0])
+    step = 0
+    for (gg, cc, ad, ah) in [(1, 1, True, True), (n_group, n_class, True, True), (1, n_class, False, True),
+                             (1, 1, True, False)]:
+        g.aero_state_scale_weight(gg, cc, ratios, allow_doubling=ad, allow_halving=ah, step=step)
+        for c in range(n_cells):
+            if ratios[c] != 1.0:
+                # the device keeps no lists between calls: every call starts from a fresh aero_state_sort
+                o.sort(c, force_resort=True, physical=False)
+                o.scale_weight(c, gg, cc, ratios[c], ad, ah, step=step)
+        common.assert_same_population(g, o, case)
+        assert np.array_equal(g.get_next_id(), [o.L.pmco_get_next_id(o.h, c) for c in range(n_cells)])
+        step += 1
+    assert not np.array_equal(g.counts(), case["counts"])

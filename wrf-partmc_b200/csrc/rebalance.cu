@@ -245,6 +245,152 @@ int pmc_reweight_async(pmcgpu_ctx* ctx, unsigned step, unsigned pass) {
   return PMCGPU_OK;
 }
 
+// aero_state_scale_weight (aero_state.F90:1832-1895) for (group g, class c) of every cell, ratio[cell]
+// (<= 0 or 1: leave the cell alone).  ratio > 1: magnitude x ratio and prob_round(n (1 - 1/ratio)) uniformly
+// chosen particles of the (group, class) list removed one after the other (swap-with-last in the particle
+// array AND in the list, integer_rmap2_remove :190-243) -- the draws are addressed (PH_SCALE, gc, removal
+// number), the index surgery is replayed by one lane on three integer arrays, the records then move in
+// parallel.  ratio < 1: magnitude x ratio and every particle of the list, backwards, keeps
+// prob_round(1 / ratio) copies (aero_state_dup_particle :488-539): decided 32 at a time, copies appended in
+// the reference's order with consecutive new ids.
+__global__ void __launch_bounds__(REB_WARPS * 32) k_scale_weight(DevView v, int g, int c, const double* __restrict__ ratio,
+                                                                  int allow_doubling, int allow_halving, unsigned step) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * REB_WARPS + warp;
+  if (cell >= v.n_cells) return;
+  if (v.status[cell] != 0) return;
+  const double weight_ratio = ratio[cell];
+  if (!(weight_ratio > 0.0) || weight_ratio == 1.0) return;
+  const int gc = (c - 1) * v.G + (g - 1);
+  const size_t base = (size_t)cell * v.cap;
+  const size_t NS = (size_t)v.n_cells * v.cap;
+  const int n0 = v.count[cell];
+  int* list = v.L + (size_t)cell * 3 * v.cap;  // slots of the (group, class) particles, ascending
+  int* listpos = list + v.cap;                  // slot -> position in list, -1 if not in it
+  int* orig = listpos + v.cap;                  // current slot -> original slot
+  int n_part = 0;
+  for (int p0 = 0; p0 < n0; p0 += 32) {
+    const int p = p0 + lane;
+    const bool is = (p < n0) && (v.wgc[base + p] == gc);
+    const unsigned b = __ballot_sync(0xffffffffu, is);
+    if (p < n0) {
+      orig[p] = p;
+      listpos[p] = -1;
+    }
+    if (is) {
+      const int idx = n_part + __popc(b & ((1u << lane) - 1u));
+      list[idx] = p;
+      listpos[p] = idx;
+    }
+    n_part += __popc(b);
+  }
+  __syncwarp();
+  const unsigned gcell = (unsigned)v.gcell[cell];
+  const size_t wi = (size_t)cell * v.C * v.G + gc;
+  int err = 0;
+  if ((weight_ratio > 1.0) && (allow_halving || (n_part == 0))) {
+    const int n_remove = prob_round((double)n_part * (1.0 - 1.0 / weight_ratio),
+                                    rng_uniform(RKey{v.seed, gcell, step, PH_SCALE, (unsigned)gc, 0u}, 0));
+    int n_cur = n0;
+    if (lane == 0) {
+      v.wmag[wi] *= weight_ratio;
+      int len = n_part;
+      for (int r = 1; r <= n_remove; r++) {
+        const int ie = pmc_rand_int(rng_uniform(RKey{v.seed, gcell, step, PH_SCALE, (unsigned)gc, (unsigned)r}, 0), len);
+        const int i = list[ie - 1];
+        const int old_pos = listpos[i];
+        const int last = n_cur - 1;
+        if (last != i) {
+          if (listpos[last] >= 0) list[listpos[last]] = i;
+          orig[i] = orig[last];
+          listpos[i] = listpos[last];
+        }
+        n_cur = last;
+        const int idx_fix = len - 1;
+        const int dom_fix = list[idx_fix];
+        if (old_pos < idx_fix) list[old_pos] = list[idx_fix];
+        len = idx_fix;
+        if (idx_fix != old_pos) listpos[dom_fix] = old_pos;
+      }
+    }
+    n_cur = __shfl_sync(0xffffffffu, n_cur, 0);
+    __syncwarp();
+    // sources are original slots >= n_cur, destinations < n_cur: disjoint
+    for (int p = lane; p < n_cur; p += 32) {
+      const int src = orig[p];
+      if (src != p) {
+        for (int s = 0; s < v.S; s++) v.vol[(size_t)s * NS + base + p] = v.vol[(size_t)s * NS + base + src];
+        v.id[base + p] = v.id[base + src];
+        v.wgc[base + p] = v.wgc[base + src];
+        v.nprim[base + p] = v.nprim[base + src];
+        v.hyst[base + p] = v.hyst[base + src];
+        v.lct[base + p] = v.lct[base + src];
+        v.gct[base + p] = v.gct[base + src];
+      }
+    }
+    if (lane == 0) v.count[cell] = n_cur;
+  } else if ((weight_ratio < 1.0) && (allow_doubling || (n_part == 0))) {
+    if (lane == 0) v.wmag[wi] *= weight_ratio;
+    int n_cur = n0;
+    long long nx = v.next_id[cell];
+    for (int hi = n_part; hi >= 1 && !err; hi -= 32) {
+      const int ie = hi - lane;  // 1-based list entry
+      int extra = 0, src = 0;
+      if (ie >= 1) {
+        src = list[ie - 1];
+        const RKey key{v.seed, gcell, step, PH_SCALE, (unsigned)gc, 0x40000000u + (unsigned)ie};
+        extra = prob_round(1.0 / weight_ratio, rng_uniform(key, 0)) - 1;
+      }
+      // exclusive prefix over the lanes (lane 0 = first processed entry)
+      int incl = extra;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      const int tot = __shfl_sync(0xffffffffu, incl, 31);
+      if (n_cur + tot > v.cap) {
+        err = PMCGPU_ERR_CAPACITY;
+        break;
+      }
+      const int first = n_cur + incl - extra;
+      for (int d = 0; d < extra; d++) {
+        const int dst = first + d;
+        for (int s = 0; s < v.S; s++) v.vol[(size_t)s * NS + base + dst] = v.vol[(size_t)s * NS + base + src];
+        v.id[base + dst] = (nx + (incl - extra) + d - 1) * v.n_cells_global + v.gcell[cell] + 1;
+        v.wgc[base + dst] = gc;
+        v.nprim[base + dst] = v.nprim[base + src];
+        v.hyst[base + dst] = v.hyst[base + src];
+        v.lct[base + dst] = v.lct[base + src];
+        v.gct[base + dst] = v.gct[base + src];
+      }
+      n_cur += tot;
+      nx += tot;
+    }
+    __syncwarp();
+    if (lane == 0) {
+      v.count[cell] = n_cur;
+      v.next_id[cell] = nx;
+      if (err && v.status[cell] == 0) v.status[cell] = err;
+    }
+  }
+}
+
+extern "C" int pmcgpu_aero_state_scale_weight(pmcgpu_ctx* ctx, int i_group, int i_class, const double* weight_ratio,
+                                              int allow_doubling, int allow_halving, unsigned step) {
+  if (!ctx || !weight_ratio) return PMCGPU_ERR_ARG;
+  DevView& v = ctx->v;
+  if (i_group < 1 || i_group > v.G || i_class < 1 || i_class > v.C) return PMCGPU_ERR_ARG;
+  // v.stage: [n_cells] staging doubles (also used by partmc_timestep for the new inverse density)
+  CUDA_OK(ctx, cudaMemcpyAsync(v.stage, weight_ratio, v.n_cells * sizeof(double), cudaMemcpyDefault, ctx->stream));
+  {
+    ProfScope ps_(ctx, "k_scale_weight");
+    const int blocks = (v.n_cells + REB_WARPS - 1) / REB_WARPS;
+    k_scale_weight<<<blocks, REB_WARPS * 32, 0, ctx->stream>>>(v, i_group, i_class, v.stage, allow_doubling, allow_halving, step);
+    LAUNCH_CHECK(ctx);
+  }
+  return pmc_first_status(ctx);
+}
+
 int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step) {
   DevView& v = ctx->v;
   const int blocks = (v.n_cells + REB_WARPS - 1) / REB_WARPS;

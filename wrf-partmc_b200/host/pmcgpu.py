@@ -326,6 +326,14 @@ class PartMCGPU:
         if no_wait and keep:
             self.synchronize()  # host copies made here must outlive the asynchronous upload
 
+    def aero_state_scale_weight(self, i_group, i_class, weight_ratio, allow_doubling=True, allow_halving=True, step=0):
+        """aero_state_scale_weight (aero_state.F90:1832) for (i_group, i_class) of every cell; weight_ratio[n_cells]"""
+        r = _f64(weight_ratio)
+        assert r.size == self.n_cells
+        self._chk(self.L.pmcgpu_aero_state_scale_weight(self.h, C.c_int(i_group), C.c_int(i_class), _p(r),
+                                                        C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)),
+                                                        C.c_uint(step)))
+
     def wrf_pmc_dep_dry_driver(self, rmol, znt, ust, ivgtyp, height, dt, step=0):
         """wrf_pmc_dep_dry_driver (interface/wrf_pmc_dep.F90:31): dry deposition in the lowest layer.
         2-D fields [ny][nx]: rmol, znt, ust (WRF reals), ivgtyp (USGS land use), height of the lowest layer."""
