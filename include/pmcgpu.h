@@ -122,6 +122,29 @@ int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned
 int pmcgpu_aero_state_scale_weight(pmcgpu_ctx* ctx, int i_group, int i_class, const double* weight_ratio,
                                    int allow_doubling, int allow_halving, unsigned step);
 
+/* aero_state_add_aero_dist_sample (aero_state.F90:758-831) for every cell: emission / inflow of new
+ * particles sampled from a distribution of modes (the reference's callers: emissions
+ * wrf_pmc_driver.F90:1767-1924, boundary inflow wrf_pmc_trans_aero.F90:689-766).  Per (group, mode):
+ * aero_state_prepare_weight_for_add (:703-757) rescales the class weight when the new count would leave
+ * [ideal/2, 2 ideal]; a Poisson number of particles is created with radii from the mode (aero_mode.F90:549)
+ * and volume fractions from aero_mode_sample_vols (:633).  All pointers host or device. */
+typedef struct {
+  int n_mode;
+  const int* mode_type;         /* [n_mode] 1 log-normal, 2 exponential, 3 mono-disperse (aero_mode.F90:26-34) */
+  const int* weight_class;      /* [n_mode] weight class of the mode's source, 1-based */
+  const double* char_radius;    /* [n_mode] geometric mean / mean-volume / mono radius (m) */
+  const double* log10_std_dev;  /* [n_mode] log10 of the geometric standard deviation (log-normal modes) */
+  const double* vol_frac;       /* [n_mode][n_spec] species volume fractions */
+  const double* vol_frac_std;   /* [n_mode][n_spec] their standard deviations, NULL = 0 */
+  const double* num_conc;       /* [n_cells][n_mode] number concentration of each mode in each cell (m^-3) */
+  const double* sample_prop;    /* [n_cells] fraction to sample, e.g. emission_rate_scale * dt / height */
+  double characteristic_factor; /* sample_timescale / dt (:771) */
+  double create_time;
+  int allow_doubling, allow_halving;
+  unsigned int step;            /* addresses the random draws */
+} pmcgpu_emit_args;
+int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmcgpu_emit_args* args, int* n_part_add /* [n_cells] or NULL */);
+
 /* Step number that addresses the random draws of the stand-alone condensation calls below (the
  * prob_round draws of aero_state_reweight, aero_state.F90:597-653, when weights depend on size);
  * pmcgpu_partmc_timestep uses its own `step` argument instead.  The reference has one global

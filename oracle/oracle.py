@@ -281,6 +281,21 @@ class Oracle:
             _p(a[0], C.c_float), _p(a[1], C.c_float), _p(a[2], C.c_float), _p(iv, C.c_int), _p(hg, C.c_double),
             C.c_double(dt), C.c_uint(step)))
 
+    def add_aero_dist_sample(self, cell, mode_type, weight_class, char_radius, log10_std_dev, vol_frac, num_conc,
+                             sample_prop, characteristic_factor, create_time=0.0, vol_frac_std=None,
+                             allow_doubling=True, allow_halving=True, step=0):
+        """aero_state_add_aero_dist_sample (aero_state.F90:758) for one cell; num_conc [n_mode]"""
+        ty, wc = _i32(mode_type), _i32(weight_class)
+        cr, ls, vf, nc = _f64(char_radius), _f64(log10_std_dev), _f64(vol_frac), _f64(num_conc)
+        vs = _f64(vol_frac_std) if vol_frac_std is not None else None
+        n = C.c_int(0)
+        self._chk(self.L.pmco_add_aero_dist_sample(
+            self.h, C.c_int(cell), C.c_int(ty.size), _p(ty, C.c_int), _p(wc, C.c_int), _p(cr, C.c_double),
+            _p(ls, C.c_double), _p(vf, C.c_double), _p(vs, C.c_double) if vs is not None else None,
+            _p(nc, C.c_double), C.c_double(sample_prop), C.c_double(characteristic_factor), C.c_double(create_time),
+            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step), C.byref(n)))
+        return n.value
+
     def scale_weight(self, cell, g, c, ratio, allow_doubling=True, allow_halving=True, step=0):
         self._chk(self.L.pmco_scale_weight(self.h, C.c_int(cell), C.c_int(g), C.c_int(c), C.c_double(ratio),
                                            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step)))

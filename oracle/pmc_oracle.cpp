@@ -819,9 +819,9 @@ void aero_state_rebalance(AeroState& st, bool allow_doubling, bool allow_halving
   }
 }
 void aero_state_scale_weight(AeroState& st, int g, int c, double weight_ratio, bool allow_doubling,
-                             bool allow_halving, const RunCtx& rc) {
+                             bool allow_halving, const RunCtx& rc, uint32_t salt) {
   aero_state_sort(st);
-  const uint32_t gc = (uint32_t)((c - 1) * st.awa.n_group + (g - 1));
+  const uint32_t gc = (uint32_t)((c - 1) * st.awa.n_group + (g - 1)) + 4096u * salt;
   const int n_part = st.sorted.group_class.inv(g, c).n_entry();
   if ((weight_ratio > 1.0) && (allow_halving || (n_part == 0))) {
     st.awa.at(g, c).magnitude *= weight_ratio;

@@ -72,7 +72,8 @@ enum Phase : uint32_t {
   PH_SCALE = 6,       // a = (group,class), b = 0 (count) / removal number
   PH_TRANS = 7,       // a = class*64 + direction slot, b = 0 (count) / transfer
   PH_INIT = 8,
-  PH_DEP = 9          // a = 0, b = particle index (dry deposition)
+  PH_DEP = 9,         // a = 0, b = particle index (dry deposition)
+  PH_EMIT = 10        // a = (group, mode), b = 0 (count) / sample number (aero_state_add_aero_dist_sample)
 };
 struct RngKey {
   uint32_t cell, step, phase, a, b;
@@ -276,8 +277,10 @@ void aero_state_dup_particle(AeroState& st, int i_part, double n_part_mean, bool
 void aero_state_double(AeroState& st, int g, int c);                         // :1695
 void aero_state_halve(AeroState& st, int g, int c, const RunCtx& rc, uint32_t pass);  // :1726
 void aero_state_rebalance(AeroState& st, bool allow_doubling, bool allow_halving, const RunCtx& rc);  // :1765-1825
+// salt: distinguishes the draw addresses of several calls for the same (group, class) inside one step
+// (emissions call it once per mode); 0 for a stand-alone call
 void aero_state_scale_weight(AeroState& st, int g, int c, double weight_ratio, bool allow_doubling,
-                             bool allow_halving, const RunCtx& rc);          // :1832-1895
+                             bool allow_halving, const RunCtx& rc, uint32_t salt = 0);          // :1832-1895
 void aero_state_reweight(AeroState& st, const std::vector<double>& reweight_num_conc, const RunCtx& rc,
                          uint32_t pass);                                     // :597-653
 

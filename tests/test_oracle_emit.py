@@ -1,0 +1,48 @@
+"""CPU tests of the emission-sampling restatement (aero_state_add_aero_dist_sample, aero_state.F90:758-831):
+the sampled population reproduces the mode it was drawn from."""
+import numpy as np
+
+import common
+from oracle import oracle as O
+
+
+def test_lognormal_emission_reproduces_the_mode():
+    """Flat weight: expected count N sample_prop / magnitude, log10 radius ~ Normal(log10 r_g, sigma) (up to the
+    tail threshold of rand_normal, here 1 / (characteristic_factor n_avg) << 1), composition = vol_frac."""
+    case = common.make_cells(1, 2000, n_spec=3, n_class=1, seed=3, n_part_ideal=4000.0, ragged=False)
+    o = common.oracle_from_case(O, case)
+    mag = case["wmag"][0, 0, 0]
+    vf = np.array([[0.2, 0.5, 0.3]])
+    n_target = 1500.0
+    added = o.add_aero_dist_sample(0, mode_type=[1], weight_class=[1], char_radius=[5e-8], log10_std_dev=[0.2],
+                                   vol_frac=vf, num_conc=[n_target * mag], sample_prop=1.0, characteristic_factor=60.0,
+                                   create_time=7.0, step=1)
+    assert abs(added - n_target) < 4 * np.sqrt(n_target)
+    q = o.get_cell(0)
+    new = q["vol"][:, 2000:]
+    assert new.shape[1] == added and o.count(0) == 2000 + added
+    r = (3 * new.sum(axis=0) / (4 * np.pi)) ** (1 / 3)
+    lr = np.log10(r)
+    assert abs(lr.mean() - np.log10(5e-8)) < 4 * 0.2 / np.sqrt(added)
+    assert abs(lr.std() - 0.2) < 0.015
+    np.testing.assert_allclose(new / new.sum(axis=0), np.repeat(vf.T, added, axis=1), rtol=1e-12)
+    assert (q["gct"][2000:] == 7.0).all() and (q["n_primary"][2000:] == 1).all()
+    assert len(set(q["id"].tolist())) == q["id"].size
+    _, m1, _ = o.get_weights(0)
+    assert m1[0] == mag  # 3500 particles is inside [ideal / 2, 2 ideal]: no rescaling
+
+
+def test_prepare_weight_for_add_rescales_when_the_cell_would_overflow():
+    case = common.make_cells(1, 900, n_spec=1, n_class=1, seed=3, n_part_ideal=500.0, ragged=False)
+    o = common.oracle_from_case(O, case)
+    mag = case["wmag"][0, 0, 0]
+    o.add_aero_dist_sample(0, mode_type=[3], weight_class=[1], char_radius=[1e-7], log10_std_dev=[0.0],
+                           vol_frac=[[1.0]], num_conc=[600.0 * mag], sample_prop=1.0, characteristic_factor=10.0, step=2)
+    _, m1, _ = o.get_weights(0)
+    # n_part_new = 900 + 600 = 1500 > 2 x 500: weight_ratio = 3, population thinned to ~ 300 + 200 new
+    np.testing.assert_allclose(m1[0], 3.0 * mag, rtol=1e-14)
+    assert 380 < o.count(0) < 620
+    q = o.get_cell(0)
+    r = (3 * q["vol"][0] / (4 * np.pi)) ** (1 / 3)
+    n_mono = int((np.abs(r / 1e-7 - 1) < 1e-12).sum())
+    assert abs(n_mono - 200) < 4 * np.sqrt(200)

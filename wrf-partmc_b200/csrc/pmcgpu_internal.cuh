@@ -14,7 +14,7 @@
 
 // draw-address phases; must agree with the documented stream layout
 enum : uint32_t {
-  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8, PH_DEP = 9
+  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8, PH_DEP = 9, PH_EMIT = 10
 };
 
 struct PmcConst {  // partmc/src/constants.F90:30-65

@@ -253,15 +253,12 @@ int pmc_reweight_async(pmcgpu_ctx* ctx, unsigned step, unsigned pass) {
 // parallel.  ratio < 1: magnitude x ratio and every particle of the list, backwards, keeps
 // prob_round(1 / ratio) copies (aero_state_dup_particle :488-539): decided 32 at a time, copies appended in
 // the reference's order with consecutive new ids.
-__global__ void __launch_bounds__(REB_WARPS * 32) k_scale_weight(DevView v, int g, int c, const double* __restrict__ ratio,
-                                                                  int allow_doubling, int allow_halving, unsigned step) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int cell = blockIdx.x * REB_WARPS + warp;
-  if (cell >= v.n_cells) return;
-  if (v.status[cell] != 0) return;
-  const double weight_ratio = ratio[cell];
+// salt: distinguishes the draw addresses of several calls for the same (group, class) inside one step
+__device__ void cell_scale_weight(const DevView& v, int cell, int lane, int g, int c, double weight_ratio,
+                                  int allow_doubling, int allow_halving, unsigned step, unsigned salt) {
   if (!(weight_ratio > 0.0) || weight_ratio == 1.0) return;
   const int gc = (c - 1) * v.G + (g - 1);
+  const unsigned gca = (unsigned)gc + 4096u * salt;  // draw address
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
   const int n0 = v.count[cell];
@@ -290,13 +287,13 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_scale_weight(DevView v, int 
   int err = 0;
   if ((weight_ratio > 1.0) && (allow_halving || (n_part == 0))) {
     const int n_remove = prob_round((double)n_part * (1.0 - 1.0 / weight_ratio),
-                                    rng_uniform(RKey{v.seed, gcell, step, PH_SCALE, (unsigned)gc, 0u}, 0));
+                                    rng_uniform(RKey{v.seed, gcell, step, PH_SCALE, gca, 0u}, 0));
     int n_cur = n0;
     if (lane == 0) {
       v.wmag[wi] *= weight_ratio;
       int len = n_part;
       for (int r = 1; r <= n_remove; r++) {
-        const int ie = pmc_rand_int(rng_uniform(RKey{v.seed, gcell, step, PH_SCALE, (unsigned)gc, (unsigned)r}, 0), len);
+        const int ie = pmc_rand_int(rng_uniform(RKey{v.seed, gcell, step, PH_SCALE, gca, (unsigned)r}, 0), len);
         const int i = list[ie - 1];
         const int old_pos = listpos[i];
         const int last = n_cur - 1;
@@ -338,7 +335,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_scale_weight(DevView v, int 
       int extra = 0, src = 0;
       if (ie >= 1) {
         src = list[ie - 1];
-        const RKey key{v.seed, gcell, step, PH_SCALE, (unsigned)gc, 0x40000000u + (unsigned)ie};
+        const RKey key{v.seed, gcell, step, PH_SCALE, gca, 0x40000000u + (unsigned)ie};
         extra = prob_round(1.0 / weight_ratio, rng_uniform(key, 0)) - 1;
       }
       // exclusive prefix over the lanes (lane 0 = first processed entry)
@@ -375,6 +372,15 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_scale_weight(DevView v, int 
   }
 }
 
+__global__ void __launch_bounds__(REB_WARPS * 32) k_scale_weight(DevView v, int g, int c, const double* __restrict__ ratio,
+                                                                  int allow_doubling, int allow_halving, unsigned step) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * REB_WARPS + warp;
+  if (cell >= v.n_cells) return;
+  if (v.status[cell] != 0) return;
+  cell_scale_weight(v, cell, lane, g, c, ratio[cell], allow_doubling, allow_halving, step, 0u);
+}
+
 extern "C" int pmcgpu_aero_state_scale_weight(pmcgpu_ctx* ctx, int i_group, int i_class, const double* weight_ratio,
                                               int allow_doubling, int allow_halving, unsigned step) {
   if (!ctx || !weight_ratio) return PMCGPU_ERR_ARG;
@@ -389,6 +395,215 @@ extern "C" int pmcgpu_aero_state_scale_weight(pmcgpu_ctx* ctx, int i_group, int 
     LAUNCH_CHECK(ctx);
   }
   return pmc_first_status(ctx);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// aero_state_add_aero_dist_sample (aero_state.F90:758-831): emission / inflow sampling of new particles
+// (SURVEY.md section 8f, N1).  Per cell, per (group, mode) in the reference's order:
+// aero_state_prepare_weight_for_add (:703-757, PMC_USE_WRF branch) -> cell_scale_weight when the new count
+// would leave [ideal / 2, 2 ideal]; Poisson number of new particles (draw (PH_EMIT, (group, mode), 0));
+// every new particle i has its own draw stream (PH_EMIT, (group, mode), i), so 32 particles are sampled at a
+// time: radius from the mode (aero_mode.F90:549-628, log-normal with the tail threshold of
+// rand.F90:410-474, exponential, mono-disperse), volume fractions by the accept-reject loop of :633-668.
+struct EmitDev {
+  int n_mode;
+  const int* type;             // [n_mode] 1 log-normal, 2 exponential, 3 mono-disperse
+  const int* wclass;           // [n_mode] weight class of the mode's source (1-based)
+  const double* char_radius;   // [n_mode]
+  const double* log10_std;     // [n_mode]
+  const double* vol_frac;      // [n_mode][S]
+  const double* vol_frac_std;  // [n_mode][S]
+  const double* num_conc;      // [n_cells][n_mode]
+  const double* sample_prop;   // [n_cells]
+  double char_factor, create_time;
+  int allow_doubling, allow_halving;
+  unsigned step;
+  int* n_add;                  // [n_cells]
+};
+
+// aero_mode_number (aero_mode.F90:496-544)
+__device__ __forceinline__ double aero_mode_number(int type, double num_conc, double char_radius, double lsd, int wtype,
+                                                   double wmag, double wexp) {
+  if (type == 1) {
+    if (wtype == PMCGPU_WEIGHT_NONE) return num_conc / wmag;
+    const double l10 = log10(char_radius);
+    const double x_mean_prime = l10 - wexp * (lsd * lsd) * log(10.0);
+    return num_conc / wmag * exp((x_mean_prime * x_mean_prime - l10 * l10) / (2.0 * (lsd * lsd)));
+  } else if (type == 2) {
+    return num_conc / wmag;
+  }
+  return num_conc / weight_nc(wtype, wmag, wexp, char_radius);
+}
+
+__global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * REB_WARPS + warp;
+  if (cell >= v.n_cells) return;
+  if (v.status[cell] != 0) return;
+  const size_t base = (size_t)cell * v.cap;
+  const size_t NS = (size_t)v.n_cells * v.cap;
+  const unsigned gcell = (unsigned)v.gcell[cell];
+  const double sample_prop = e.sample_prop[cell];
+  const double ideal = v.ideal;
+  int n_add = 0, err = 0;
+  for (int g = 1; g <= v.G && !err; g++)
+    for (int im = 1; im <= e.n_mode && !err; im++) {
+      const int type = e.type[im - 1], c = e.wclass[im - 1];
+      const double cr = e.char_radius[im - 1], lsd = e.log10_std[im - 1];
+      const double mode_nc = e.num_conc[(size_t)cell * e.n_mode + (im - 1)];
+      const unsigned a = (unsigned)((g - 1) * e.n_mode + (im - 1));
+      const int gc = (c - 1) * v.G + (g - 1);
+      const size_t wi = (size_t)cell * v.C * v.G + gc;
+      if (type == 2 && v.wtype[wi] != PMCGPU_WEIGHT_NONE) {
+        err = PMCGPU_ERR_ARG;  // "cannot use exponential modes with weighting"
+        break;
+      }
+      __syncwarp();
+      double n_samp_avg = sample_prop * aero_mode_number(type, mode_nc, cr, lsd, v.wtype[wi], v.wmag[wi], v.wexp[wi]);
+      {  // aero_state_prepare_weight_for_add
+        const int n_now = v.count[cell];
+        int m = 0;
+        for (int p = lane; p < n_now; p += 32) m += (v.wgc[base + p] == gc);
+        m = warp_sum(m);
+        const double n_part_new = (double)m + n_samp_avg;
+        if (n_part_new != 0.0 && ((n_part_new < ideal / 2.0) || (n_part_new > ideal * 2.0))) {
+          __syncwarp();
+          cell_scale_weight(v, cell, lane, g, c, n_part_new / ideal, e.allow_doubling, e.allow_halving, e.step, 1u + a);
+          __syncwarp();
+          if (v.status[cell] != 0) return;
+        }
+      }
+      if (n_samp_avg == 0.0) continue;
+      const int wt = v.wtype[wi];
+      const double wm = v.wmag[wi], we = v.wexp[wi];
+      n_samp_avg = sample_prop * aero_mode_number(type, mode_nc, cr, lsd, wt, wm, we);
+      RStream s0{RKey{v.seed, gcell, e.step, PH_EMIT, a, 0u}, 0u};
+      const int n_samp = rand_poisson(n_samp_avg, s0);
+      const double size_factor = fmin(1.0 / (e.char_factor * n_samp_avg), 0.32);
+      const int n_cur = v.count[cell];
+      if (n_cur + n_samp > v.cap) {
+        err = PMCGPU_ERR_CAPACITY;
+        break;
+      }
+      const long long nx = v.next_id[cell];
+      const double* vf = e.vol_frac + (size_t)(im - 1) * v.S;
+      const double* vs = e.vol_frac_std + (size_t)(im - 1) * v.S;
+      for (int i_samp = 1 + lane; i_samp <= n_samp; i_samp += 32) {
+        RStream s{RKey{v.seed, gcell, e.step, PH_EMIT, a, (unsigned)i_samp}, 0u};
+        // aero_mode_sample_radius
+        double radius = cr;
+        if (type == 1) {
+          double x_mean_prime = log10(cr);
+          if (wt != PMCGPU_WEIGHT_NONE) x_mean_prime = log10(cr) - we * (lsd * lsd) * log(10.0);
+          const double sqrt2 = (double)sqrtf(2.0f);  // 2.0**.5 is a default-real expression in rand.F90:463
+          double x;
+          for (;;) {
+            const double u1 = s.next();
+            const double u2 = s.next();
+            const double r = sqrt(-2.0 * log(u1));
+            const double theta = 2.0 * PmcConst::pi * u2;
+            const double z0 = r * cos(theta);
+            if (1.0 - fabs(erf(z0 / sqrt2)) >= size_factor) {
+              x = lsd * z0 + x_mean_prime;
+              break;
+            }
+          }
+          radius = pow(10.0, x);
+        } else if (type == 2) {
+          radius = vol2rad(-rad2vol(cr) * log(s.next()));
+        }
+        const double total_vol = rad2vol(radius);
+        // aero_mode_sample_vols
+        double vols[PMC_MAX_SPEC];
+        for (int it = 0; it < 1000000; it++) {
+          double sum = 0.0;
+          for (int k = 0; k < v.S; k++) {
+            vols[k] = rand_normal(vf[k], vs[k], s);
+            sum += vols[k];
+          }
+          const double offset = 1.0 - sum;
+          double mn = 1e300;
+          for (int k = 0; k < v.S; k++) {
+            vols[k] = vols[k] + offset * vf[k];
+            mn = fmin(mn, vols[k]);
+          }
+          if (mn >= 0.0) break;
+        }
+        double sum = 0.0;
+        for (int k = 0; k < v.S; k++) sum += vols[k];
+        const int slot = n_cur + i_samp - 1;
+        for (int k = 0; k < v.S; k++) v.vol[(size_t)k * NS + base + slot] = vols[k] / sum * total_vol;
+        v.id[base + slot] = (nx + (i_samp - 1) - 1) * v.n_cells_global + v.gcell[cell] + 1;
+        v.wgc[base + slot] = gc;
+        v.nprim[base + slot] = 1;
+        v.hyst[base + slot] = 0;
+        v.lct[base + slot] = e.create_time;
+        v.gct[base + slot] = e.create_time;
+      }
+      __syncwarp();
+      if (lane == 0) {
+        v.count[cell] = n_cur + n_samp;
+        v.next_id[cell] = nx + n_samp;
+      }
+      __syncwarp();
+      n_add += n_samp;
+    }
+  if (lane == 0) {
+    if (e.n_add) e.n_add[cell] = n_add;
+    if (err && v.status[cell] == 0) v.status[cell] = err;
+  }
+}
+
+extern "C" int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add) {
+  if (!ctx || !a || a->n_mode < 1 || !a->mode_type || !a->weight_class || !a->char_radius || !a->log10_std_dev ||
+      !a->vol_frac || !a->num_conc || !a->sample_prop || !(a->characteristic_factor > 0.0))
+    return PMCGPU_ERR_ARG;
+  DevView& v = ctx->v;
+  const size_t nm = (size_t)a->n_mode, S = (size_t)v.S, nc = (size_t)v.n_cells;
+  for (size_t m = 0; m < nm; m++)
+    if (a->weight_class[m] < 1 || a->weight_class[m] > v.C || a->mode_type[m] < 1 || a->mode_type[m] > 3) return PMCGPU_ERR_ARG;
+  // one device buffer per call (mode tables are tiny; num_conc is [n_cells][n_mode])
+  const size_t bytes = (2 * nm) * sizeof(int) + (2 * nm + 2 * nm * S + nc * nm + nc) * sizeof(double) + nc * sizeof(int) + 64;
+  char* buf = nullptr;
+  CUDA_OK(ctx, cudaMalloc((void**)&buf, bytes));
+  double* d_cr = (double*)buf;
+  double* d_ls = d_cr + nm;
+  double* d_vf = d_ls + nm;
+  double* d_vs = d_vf + nm * S;
+  double* d_nc = d_vs + nm * S;
+  double* d_sp = d_nc + nc * nm;
+  int* d_ty = (int*)(d_sp + nc);
+  int* d_wc = d_ty + nm;
+  int* d_na = d_wc + nm;
+  cudaStream_t st = ctx->stream;
+  CUDA_OK(ctx, cudaMemcpyAsync(d_cr, a->char_radius, nm * sizeof(double), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_ls, a->log10_std_dev, nm * sizeof(double), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_vf, a->vol_frac, nm * S * sizeof(double), cudaMemcpyDefault, st));
+  if (a->vol_frac_std)
+    CUDA_OK(ctx, cudaMemcpyAsync(d_vs, a->vol_frac_std, nm * S * sizeof(double), cudaMemcpyDefault, st));
+  else
+    CUDA_OK(ctx, cudaMemsetAsync(d_vs, 0, nm * S * sizeof(double), st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_nc, a->num_conc, nc * nm * sizeof(double), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_sp, a->sample_prop, nc * sizeof(double), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_ty, a->mode_type, nm * sizeof(int), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_wc, a->weight_class, nm * sizeof(int), cudaMemcpyDefault, st));
+  EmitDev e;
+  e.n_mode = a->n_mode;
+  e.type = d_ty; e.wclass = d_wc; e.char_radius = d_cr; e.log10_std = d_ls; e.vol_frac = d_vf; e.vol_frac_std = d_vs;
+  e.num_conc = d_nc; e.sample_prop = d_sp;
+  e.char_factor = a->characteristic_factor; e.create_time = a->create_time;
+  e.allow_doubling = a->allow_doubling; e.allow_halving = a->allow_halving; e.step = a->step;
+  e.n_add = d_na;
+  {
+    ProfScope ps_(ctx, "k_emit");
+    const int blocks = (v.n_cells + REB_WARPS - 1) / REB_WARPS;
+    k_emit<<<blocks, REB_WARPS * 32, 0, st>>>(v, e);
+    LAUNCH_CHECK(ctx);
+  }
+  if (n_part_add) CUDA_OK(ctx, cudaMemcpyAsync(n_part_add, d_na, nc * sizeof(int), cudaMemcpyDefault, st));
+  const int rc = pmc_first_status(ctx);  // synchronises the stream
+  cudaFree(buf);
+  return rc;
 }
 
 int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step) {

@@ -83,6 +83,14 @@ class _DepArgs(C.Structure):
                 ("height", C.c_void_p), ("dt", C.c_double), ("step", C.c_uint), ("no_wait", C.c_int)]
 
 
+class _EmitArgs(C.Structure):
+    _fields_ = [("n_mode", C.c_int), ("mode_type", C.c_void_p), ("weight_class", C.c_void_p),
+                ("char_radius", C.c_void_p), ("log10_std_dev", C.c_void_p), ("vol_frac", C.c_void_p),
+                ("vol_frac_std", C.c_void_p), ("num_conc", C.c_void_p), ("sample_prop", C.c_void_p),
+                ("characteristic_factor", C.c_double), ("create_time", C.c_double), ("allow_doubling", C.c_int),
+                ("allow_halving", C.c_int), ("step", C.c_uint)]
+
+
 class _TransArgs(C.Structure):
     _fields_ = [("u_flux", C.c_void_p), ("v_flux", C.c_void_p), ("w_flux", C.c_void_p), ("xkhh", C.c_void_p),
                 ("alt", C.c_void_p), ("z", C.c_void_p), ("z_at_w", C.c_void_p), ("exch_h", C.c_void_p),
@@ -325,6 +333,29 @@ class PartMCGPU:
         self._chk(self.L.pmcgpu_wrf_pmc_trans_driver(self.h, C.byref(a)))
         if no_wait and keep:
             self.synchronize()  # host copies made here must outlive the asynchronous upload
+
+    def aero_state_add_aero_dist_sample(self, mode_type, weight_class, char_radius, log10_std_dev, vol_frac, num_conc,
+                                        sample_prop, characteristic_factor, create_time=0.0, vol_frac_std=None,
+                                        allow_doubling=True, allow_halving=True, step=0):
+        """aero_state_add_aero_dist_sample (aero_state.F90:758) for every cell: modes described by arrays
+        [n_mode] (vol_frac [n_mode][n_spec]), num_conc [n_cells][n_mode], sample_prop [n_cells].
+        Returns the number of particles added per cell."""
+        a = _EmitArgs()
+        ty, wc = _i32(mode_type), _i32(weight_class)
+        cr, ls, vf = _f64(char_radius), _f64(log10_std_dev), _f64(vol_frac)
+        nc, sp = _f64(num_conc), _f64(sample_prop)
+        vs = _f64(vol_frac_std) if vol_frac_std is not None else None
+        nm = ty.size
+        assert wc.size == nm and cr.size == nm and ls.size == nm and vf.size == nm * self.data.n_spec
+        assert nc.size == self.n_cells * nm and sp.size == self.n_cells
+        a.n_mode = nm
+        a.mode_type, a.weight_class, a.char_radius, a.log10_std_dev = _addr(ty), _addr(wc), _addr(cr), _addr(ls)
+        a.vol_frac, a.vol_frac_std, a.num_conc, a.sample_prop = _addr(vf), _addr(vs), _addr(nc), _addr(sp)
+        a.characteristic_factor, a.create_time = float(characteristic_factor), float(create_time)
+        a.allow_doubling, a.allow_halving, a.step = int(allow_doubling), int(allow_halving), int(step)
+        n_add = np.zeros(self.n_cells, np.int32)
+        self._chk(self.L.pmcgpu_aero_state_add_aero_dist_sample(self.h, C.byref(a), _p(n_add)))
+        return n_add
 
     def aero_state_scale_weight(self, i_group, i_class, weight_ratio, allow_doubling=True, allow_halving=True, step=0):
         """aero_state_scale_weight (aero_state.F90:1832) for (i_group, i_class) of every cell; weight_ratio[n_cells]"""
