@@ -196,7 +196,7 @@ def algorithmic_bytes(kernel, n_part, n_cells, S, C, nbcap):
     """ALGORITHMIC bytes one launch of `kernel` has to move ("Kernels")."""
     P = 8 * S + 44  # record: vol[S] f64, id i64, (group, class) i32, n_primary i32, hyst i32, 2 create times f64, bin i32
     if kernel == "k_sort_cells":
-        return n_part * (8 * S + 2 * P)            # read vol (binning) + read record + write record
+        return n_part * 2 * P                      # read record + write record (species rows staged once in smem)
     if kernel == "k_mc_coag":
         return n_part * (4 + 4 + 8)                # read bin + class, write list index; + 16S per sample (small)
     if kernel == "k_condense":

@@ -48,13 +48,19 @@ def test_kernel_brown_device_vs_oracle(mods):
     assert rel.max() < 1e-10, rel.max()
 
 
+@pytest.mark.parametrize("staged_max", [None, "0", "300"])
 @pytest.mark.parametrize("n_spec,n_class,n_per,n_cells", [(1, 1, 1000, 6), (3, 2, 700, 9), (20, 3, 400, 5),
-                                                            (1, 1, 40000, 1)])
-def test_sort_bit_exact(mods, n_spec, n_class, n_per, n_cells):
+                                                            (20, 2, 1100, 3), (1, 1, 9000, 2), (1, 1, 40000, 1)])
+def test_sort_bit_exact(mods, monkeypatch, n_spec, n_class, n_per, n_cells, staged_max):
     """aero_state_sort: grid (n_bin, min, max), bin of every particle, per-(class, bin)
     counts and the permuted particle order all equal the oracle's, bit for bit.
-    Includes a ragged population and an empty cell."""
+    Includes a ragged population and an empty cell.  staged_max: None = the shared-memory staged (TMA)
+    variant takes every cell that fits, "0" = legacy variant only, "300" = the two variants split the cells."""
     W, O = mods
+    if staged_max is None:
+        monkeypatch.delenv("PMCGPU_SORT_STAGED_MAX", raising=False)
+    else:
+        monkeypatch.setenv("PMCGPU_SORT_STAGED_MAX", staged_max)
     case = common.make_cells(n_cells, n_per, n_spec=n_spec, n_class=n_class, seed=20 + n_spec)
     g = common.gpu_from_case(W, case)
     o = common.oracle_from_case(O, case)

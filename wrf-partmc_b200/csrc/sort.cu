@@ -13,31 +13,95 @@
 // read record + write record (permutation) = 8S + 2P bytes, P = 8S + 44.
 #include "pmcgpu_internal.cuh"
 
-#define SORT_THREADS 256
-#define SORT_WARPS (SORT_THREADS / 32)
+#define SORT_THREADS 256          // legacy (unstaged) variant
+#define SORT_THREADS_STAGED 512   // staged variant: one CTA per SM, so more warps per CTA
 
 static const double BINS_PER_DECADE = 10.0;   // aero_sorted.F90:69
 static const double BIN_OVER_FACTOR = 10.0;   // :71
 static const double BIN_SAFETY_FACTOR = 3.0;  // :73
 
-__global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge_recheck) {
+// mbarrier + 1-D bulk-copy (TMA) primitives of the staged variant
+__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_addr(dst)),
+               "l"(src), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  unsigned done;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+
+// STAGED: the cell's S species rows are pulled into shared memory once by bulk copies (TMA); radii, bins and
+// the permutation are computed from there and the records leave in destination order with coalesced stores,
+// so HBM sees each record once in and once out.  Handles the cells with n <= n_split; the legacy variant
+// (rows read twice, scattered stores) takes the cells with n > n_split (n_split = -1: every cell).
+template <bool STAGED, int NT>
+__global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, int n_split) {
+  constexpr int SORT_WARPS = NT / 32;
+  constexpr int SORT_THREADS_ = NT;
   const int cell = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = v.count[cell];
+  if (STAGED ? (n > n_split) : (n <= n_split)) return;
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
-  extern __shared__ int s_hist[];  // [SORT_WARPS][nk] then [nk] totals
+  extern __shared__ __align__(16) int s_hist[];  // [SORT_WARPS][nk] then [nk] totals (then the staged rows)
   __shared__ double s_min[SORT_WARPS], s_max[SORT_WARPS];
   __shared__ double s_lnmin, s_lnmax;
   __shared__ int s_nb, s_fail, s_redo;
+  __shared__ __align__(8) unsigned long long s_bar;
+  // staged layout after the histograms: vol rows [S][n2], ln r [n2] (later the inverse permutation), key [n2]
+  const int n2 = (n + 1) & ~1;  // rows are copied in 16-byte units
+  double* svol = (double*)(s_hist + (((SORT_WARPS + 1) * v.C * v.nbcap + 3) & ~3));
+  double* s_lnr = svol + (size_t)v.S * n2;
+  int* s_src = (int*)s_lnr;
+  int* s_key = (int*)(s_lnr + n2);
+  if (STAGED) {
+    if (tid == 0) mbar_init(&s_bar, 1);
+    __syncthreads();
+    if (n > 0) {
+      if (tid == 0) {
+        mbar_expect_tx(&s_bar, (unsigned)((size_t)v.S * n2 * sizeof(double)));
+        for (int s = 0; s < v.S; s++)
+          bulk_g2s(svol + (size_t)s * n2, v.vol + (size_t)s * NS + base, (unsigned)(n2 * sizeof(double)), &s_bar);
+      }
+      mbar_wait(&s_bar, 0);
+    }
+  }
 
   // ---- phase 1: radius of every particle, r_min / r_max (aero_sorted.F90:277-290)
   double rmin = 1e300, rmax = 0.0;
-  for (int p = tid; p < n; p += SORT_THREADS) {
+  for (int p = tid; p < n; p += SORT_THREADS_) {
     double vt = 0.0;
-    for (int s = 0; s < v.S; s++) vt += v.vol[(size_t)s * NS + base + p];  // aero_particle_volume
+    if (STAGED) {
+      for (int s = 0; s < v.S; s++) vt += svol[(size_t)s * n2 + p];
+    } else {
+      for (int s = 0; s < v.S; s++) vt += v.vol[(size_t)s * NS + base + p];  // aero_particle_volume
+    }
     const double r = vol2rad(vt);
-    v.lnr[base + p] = log(r);
+    if (STAGED)
+      s_lnr[p] = log(r);
+    else
+      v.lnr[base + p] = log(r);
     rmin = fmin(rmin, r);
     rmax = fmax(rmax, r);
   }
@@ -99,7 +163,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
   __syncthreads();
   // zero the published counts, (class, bin) -> bin_count[cell][c][b]
   int* bc = v.bin_count + (size_t)cell * v.C * v.nbcap;
-  for (int q = tid; q < v.C * v.nbcap; q += SORT_THREADS) bc[q] = 0;
+  for (int q = tid; q < v.C * v.nbcap; q += SORT_THREADS_) bc[q] = 0;
   if (s_nb == 0 || s_fail) return;
   if (edge_recheck == 2) return;  // grid decision only (end of trans_aero): the records stay where they are
   // ---- phase 2: bin of every particle (bin_grid.F90:143) + per-warp histograms.
@@ -121,23 +185,26 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
     myhist = s_hist + warp * nk;
     tot = s_hist + SORT_WARPS * nk;
     const double lnmin = s_lnmin, lnmax = s_lnmax;
-    for (int q = tid; q < (SORT_WARPS + 1) * nk; q += SORT_THREADS) s_hist[q] = 0;
+    for (int q = tid; q < (SORT_WARPS + 1) * nk; q += SORT_THREADS_) s_hist[q] = 0;
     __syncthreads();
     for (int p0 = lo; p0 < hi; p0 += 32) {
       const int p = p0 + lane;
       int key = -1;
       if (p < hi) {
-        int b = log_grid_find(lnmin, lnmax, nb, v.lnr[base + p]);
+        int b = log_grid_find(lnmin, lnmax, nb, STAGED ? s_lnr[p] : v.lnr[base + p]);
         b = min(max(b, 1), nb);  // unreachable clamp: the grid was just checked against r_min / r_max
-        v.pbin[base + p] = b;
         key = (v.wgc[base + p] / v.G) * nb + (b - 1);
+        if (STAGED)
+          s_key[p] = key;
+        else
+          v.pbin[base + p] = b;
       }
       const unsigned m = __match_any_sync(0xffffffffu, key);
       if (key >= 0 && (m & ((1u << lane) - 1u)) == 0) myhist[key] += __popc(m);
       __syncwarp();
     }
     __syncthreads();
-    for (int k = tid; k < nk; k += SORT_THREADS) {
+    for (int k = tid; k < nk; k += SORT_THREADS_) {
       int t = 0;
       for (int w = 0; w < SORT_WARPS; w++) t += s_hist[w * nk + k];
       tot[k] = t;
@@ -183,7 +250,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
     if (!s_redo) break;
   }
   // ---- exclusive scan: key-major, warp-minor
-  for (int k = tid; k < nk; k += SORT_THREADS) bc[(k / nb) * v.nbcap + (k % nb)] = tot[k];
+  for (int k = tid; k < nk; k += SORT_THREADS_) bc[(k / nb) * v.nbcap + (k % nb)] = tot[k];
   __syncthreads();
   if (warp == 0) {
     int carry = 0;
@@ -200,7 +267,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
     }
   }
   __syncthreads();
-  for (int k = tid; k < nk; k += SORT_THREADS) {
+  for (int k = tid; k < nk; k += SORT_THREADS_) {
     int run = tot[k];
     for (int w = 0; w < SORT_WARPS; w++) {
       const int c = s_hist[w * nk + k];
@@ -214,9 +281,13 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
     const int p = p0 + lane;
     int key = -1, b = 0, gc = 0;
     if (p < hi) {
-      b = v.pbin[base + p];
-      gc = v.wgc[base + p];
-      key = (gc / v.G) * nb + (b - 1);
+      if (STAGED) {
+        key = s_key[p];
+      } else {
+        b = v.pbin[base + p];
+        gc = v.wgc[base + p];
+        key = (gc / v.G) * nb + (b - 1);
+      }
     }
     const unsigned m = __match_any_sync(0xffffffffu, key);
     int dst = -1;
@@ -227,7 +298,9 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
     __syncwarp();
     if (key >= 0 && (m & ((1u << lane) - 1u)) == 0) myhist[key] += __popc(m);
     __syncwarp();
-    if (dst >= 0) {
+    if (STAGED) {
+      if (dst >= 0) s_src[dst] = p;  // ln r is dead: its space holds the inverse permutation
+    } else if (dst >= 0) {
       for (int s = 0; s < v.S; s++) v.vol_alt[(size_t)s * NS + base + dst] = v.vol[(size_t)s * NS + base + p];
       v.id_alt[base + dst] = v.id[base + p];
       v.wgc_alt[base + dst] = gc;
@@ -238,6 +311,22 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_cells(DevView v, int edge
       v.pbin_alt[base + dst] = b;
     }
   }
+  if (STAGED) {
+    // records leave in destination order: shared-memory gather, coalesced stores
+    __syncthreads();
+    for (int q = tid; q < n; q += SORT_THREADS_) {
+      const int src = s_src[q];
+#pragma unroll 4
+      for (int s = 0; s < v.S; s++) v.vol_alt[(size_t)s * NS + base + q] = svol[(size_t)s * n2 + src];
+      v.id_alt[base + q] = v.id[base + src];
+      v.wgc_alt[base + q] = v.wgc[base + src];
+      v.nprim_alt[base + q] = v.nprim[base + src];
+      v.hyst_alt[base + q] = v.hyst[base + src];
+      v.lct_alt[base + q] = v.lct[base + src];
+      v.gct_alt[base + q] = v.gct[base + src];
+      v.pbin_alt[base + q] = s_key[src] % nb + 1;
+    }
+  }
 }
 
 static void swap_slabs(DevView& v);
@@ -246,9 +335,9 @@ void pmc_swap_slabs(pmcgpu_ctx* ctx) { swap_slabs(ctx->v); }
 // aero_sorted_remake_if_needed only; the next mc_coag permutes the records anyway
 int pmc_sort_grid_only_async(pmcgpu_ctx* ctx) {
   DevView& v = ctx->v;
-  const size_t smem = (size_t)(SORT_WARPS + 1) * v.C * v.nbcap * sizeof(int);
+  const size_t smem = (size_t)(SORT_THREADS / 32 + 1) * v.C * v.nbcap * sizeof(int);
   ProfScope ps_(ctx, "k_sort_cells_grid");
-  k_sort_cells<<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, 2);
+  k_sort_cells<false, SORT_THREADS><<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, 2, -1);
   LAUNCH_CHECK(ctx);
   return PMCGPU_OK;
 }
@@ -263,22 +352,56 @@ static void swap_slabs(DevView& v) {
   std::swap(v.pbin, v.pbin_alt);
 }
 
+// Largest cell the staged variant takes: histograms + n (8 S + 12) bytes must fit the 227 KB of one CTA.
+// PMCGPU_SORT_STAGED_MAX (environment) lowers it (0: legacy variant only) -- used by the tests to reach both.
+static int sort_staged_limit(const DevView& v, size_t* smem_out) {
+  const size_t hist = ((size_t)(SORT_THREADS_STAGED / 32 + 1) * v.C * v.nbcap + 3) / 4 * 16;
+  const size_t budget = 224 * 1024;
+  const size_t per = 8 * (size_t)v.S + 12;
+  *smem_out = 0;
+  if ((v.cap & 1) || hist + 64 * per > budget) return -1;  // rows must start on 16-byte boundaries
+  long long nmax = (long long)((budget - hist) / per) & ~1LL;
+  if (nmax > v.cap) nmax = v.cap;
+  if (const char* e = getenv("PMCGPU_SORT_STAGED_MAX")) {
+    const long long lim = atoll(e) & ~1LL;
+    if (lim < nmax) nmax = lim;
+  }
+  if (nmax < 2) return -1;
+  *smem_out = hist + (size_t)nmax * per + 16;
+  return (int)nmax;
+}
+
 int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck) {
   DevView& v = ctx->v;
-  const size_t smem = (size_t)(SORT_WARPS + 1) * v.C * v.nbcap * sizeof(int);
+  const size_t smem = (size_t)(SORT_THREADS / 32 + 1) * v.C * v.nbcap * sizeof(int);
   if (smem > 200 * 1024) {
     ctx->err = "sort: n_class * max_bins too large for the shared-memory histogram";
     return PMCGPU_ERR_ARG;
   }
-  static size_t configured = 0;
+  static size_t configured = 0, configured_staged = 0;
   if (smem > 48 * 1024 && smem > configured) {
-    CUDA_OK(ctx, cudaFuncSetAttribute(k_sort_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_sort_cells<false, SORT_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem));
     configured = smem;
+  }
+  size_t smem_staged = 0;
+  const int n_split = sort_staged_limit(v, &smem_staged);
+  if (n_split > 0 && smem_staged > 48 * 1024 && smem_staged > configured_staged) {
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_sort_cells<true, SORT_THREADS_STAGED>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_staged));
+    configured_staged = smem_staged;
   }
   {
     ProfScope ps_(ctx, "k_sort_cells");
-    k_sort_cells<<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, edge_recheck);
-    LAUNCH_CHECK(ctx);
+    if (n_split > 0) {
+      k_sort_cells<true, SORT_THREADS_STAGED>
+          <<<v.n_cells, SORT_THREADS_STAGED, smem_staged, ctx->stream>>>(v, edge_recheck, n_split);
+      LAUNCH_CHECK(ctx);
+    }
+    if (n_split < v.cap) {
+      k_sort_cells<false, SORT_THREADS><<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, edge_recheck, n_split);
+      LAUNCH_CHECK(ctx);
+    }
   }
   // cells with an empty grid keep their (empty) slab: nothing to copy
   swap_slabs(v);
