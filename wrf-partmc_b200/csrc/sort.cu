@@ -114,12 +114,14 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
     s_max[warp] = rmax;
   }
   __syncthreads();
-  // ---- grid decision (thread 0), aero_sorted.F90:313-372 with valid_sort = .false.
-  if (tid == 0) {
-    double r_min = s_min[0], r_max = s_max[0];
-    for (int w = 1; w < SORT_WARPS; w++) {
-      r_min = fmin(r_min, s_min[w]);
-      r_max = fmax(r_max, s_max[w]);
+  // ---- grid decision, aero_sorted.F90:313-372 with valid_sort = .false.  Warp 0, every lane on the same
+  // values; the two logarithms of a pair are taken by lanes 0 and 1 side by side (half the serial latency).
+  if (warp == 0) {
+    double r_min = (lane < SORT_WARPS) ? s_min[lane] : 1e300;
+    double r_max = (lane < SORT_WARPS) ? s_max[lane] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) {
+      r_min = fmin(r_min, __shfl_xor_sync(0xffffffffu, r_min, o));
+      r_max = fmax(r_max, __shfl_xor_sync(0xffffffffu, r_max, o));
     }
     if (n == 0) {
       r_min = 0.0;
@@ -127,13 +129,14 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
     }
     int nb = v.grid_nb[cell];
     double gmin = v.grid_min[cell], gmax = v.grid_max[cell];
-    s_fail = 0;
+    int fail = 0;
+    bool new_grid = false;
     if (r_max == 0.0) {
       // no particles: bin_grid_make(n_bin = 0) + aero_sorted_set_bin_grid (:322-327)
       nb = 0;
       gmin = 0.0;
       gmax = 0.0;
-      v.bounds_valid[cell] = 0;
+      new_grid = true;
     } else {
       bool need_new = false;
       if (nb < 1) {
@@ -144,21 +147,28 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
       if (need_new) {
         gmin = r_min / BIN_OVER_FACTOR;
         gmax = r_max * BIN_OVER_FACTOR;
-        nb = (int)ceil((log10(gmax) - log10(gmin)) * BINS_PER_DECADE);
-        v.bounds_valid[cell] = 0;  // aero_sorted_set_bin_grid, :132
+        const double l10 = log10((lane & 1) ? gmin : gmax);
+        const double l10max = __shfl_sync(0xffffffffu, l10, 0), l10min = __shfl_sync(0xffffffffu, l10, 1);
+        nb = (int)ceil((l10max - l10min) * BINS_PER_DECADE);
+        new_grid = true;  // aero_sorted_set_bin_grid, :132
         if (nb > v.nbcap) {
-          s_fail = 1;
-          if (v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_NBINS;
+          fail = 1;
           nb = 0;
         }
       }
     }
-    v.grid_nb[cell] = nb;
-    v.grid_min[cell] = gmin;
-    v.grid_max[cell] = gmax;
-    s_nb = nb;
-    s_lnmin = (nb > 0) ? log(gmin) : 0.0;
-    s_lnmax = (nb > 0) ? log(gmax) : 0.0;
+    const double ln = (nb > 0) ? log((lane & 1) ? gmax : gmin) : 0.0;
+    if (lane == 0) {
+      if (new_grid) v.bounds_valid[cell] = 0;
+      if (fail && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_NBINS;
+      v.grid_nb[cell] = nb;
+      v.grid_min[cell] = gmin;
+      v.grid_max[cell] = gmax;
+      s_nb = nb;
+      s_fail = fail;
+      s_lnmin = ln;
+    }
+    if (lane == 1) s_lnmax = ln;
   }
   __syncthreads();
   // zero the published counts, (class, bin) -> bin_count[cell][c][b]
@@ -210,40 +220,55 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
       tot[k] = t;
     }
     __syncthreads();
-    if (tid == 0) {
-      s_redo = 0;
+    if (warp == 0) {
+      // edges of the lowest / highest occupied bins: occupancy by ballot over the bins, the two edges by
+      // lanes 0 and 1 side by side
+      int redo = 0;
       if (attempt == 0 && edge_recheck) {
         int i_min = 0, i_max = 0;
-        for (int b = 1; b <= nb; b++) {
+        for (int b0 = 0; b0 < nb; b0 += 32) {
+          const int b = b0 + lane;
           int t = 0;
-          for (int c = 0; c < v.C; c++) t += tot[c * nb + (b - 1)];
-          if (t > 0) {
-            if (i_min == 0) i_min = b;
-            i_max = b;
+          if (b < nb)
+            for (int c = 0; c < v.C; c++) t += tot[c * nb + b];
+          const unsigned occ = __ballot_sync(0xffffffffu, t > 0);
+          if (occ) {
+            if (i_min == 0) i_min = b0 + __ffs(occ);
+            i_max = b0 + 32 - __clz(occ);
           }
         }
         const double gmin = v.grid_min[cell], gmax = v.grid_max[cell];
-        const double r_min = grid_edge(gmin, gmax, nb, i_min);
-        const double r_max = grid_edge(gmin, gmax, nb, i_max + 1);
+        const double e = grid_edge(gmin, gmax, nb, (lane & 1) ? i_max + 1 : i_min);
+        const double r_min = __shfl_sync(0xffffffffu, e, 0), r_max = __shfl_sync(0xffffffffu, e, 1);
         if ((r_min / gmin < BIN_SAFETY_FACTOR) || (gmax / r_max < BIN_SAFETY_FACTOR)) {
           const double ngmin = r_min / BIN_OVER_FACTOR;
           const double ngmax = r_max * BIN_OVER_FACTOR;
-          int nnb = (int)ceil((log10(ngmax) - log10(ngmin)) * BINS_PER_DECADE);
-          v.bounds_valid[cell] = 0;
+          const double l10 = log10((lane & 1) ? ngmin : ngmax);
+          const double l10max = __shfl_sync(0xffffffffu, l10, 0), l10min = __shfl_sync(0xffffffffu, l10, 1);
+          int nnb = (int)ceil((l10max - l10min) * BINS_PER_DECADE);
+          int fail = 0;
           if (nnb > v.nbcap) {
-            s_fail = 1;
-            if (v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_NBINS;
+            fail = 1;
             nnb = 0;
           }
-          v.grid_nb[cell] = nnb;
-          v.grid_min[cell] = ngmin;
-          v.grid_max[cell] = ngmax;
-          s_nb = nnb;
-          s_lnmin = (nnb > 0) ? log(ngmin) : 0.0;
-          s_lnmax = (nnb > 0) ? log(ngmax) : 0.0;
-          s_redo = 1;
+          const double ln = (nnb > 0) ? log((lane & 1) ? ngmax : ngmin) : 0.0;
+          if (lane == 0) {
+            v.bounds_valid[cell] = 0;
+            if (fail) {
+              s_fail = 1;
+              if (v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_NBINS;
+            }
+            v.grid_nb[cell] = nnb;
+            v.grid_min[cell] = ngmin;
+            v.grid_max[cell] = ngmax;
+            s_nb = nnb;
+            s_lnmin = ln;
+          }
+          if (lane == 1) s_lnmax = ln;
+          redo = 1;
         }
       }
+      if (lane == 0) s_redo = redo;
     }
     __syncthreads();
     if (s_fail) return;
@@ -316,15 +341,20 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
     __syncthreads();
     for (int q = tid; q < n; q += SORT_THREADS_) {
       const int src = s_src[q];
+      // the gathered fields first (one round trip for all six), the staged rows while they are in flight
+      const long long r_id = v.id[base + src];
+      const int r_wgc = v.wgc[base + src], r_nprim = v.nprim[base + src], r_hyst = v.hyst[base + src];
+      const double r_lct = v.lct[base + src], r_gct = v.gct[base + src];
+      const int r_bin = s_key[src] % nb + 1;
 #pragma unroll 4
       for (int s = 0; s < v.S; s++) v.vol_alt[(size_t)s * NS + base + q] = svol[(size_t)s * n2 + src];
-      v.id_alt[base + q] = v.id[base + src];
-      v.wgc_alt[base + q] = v.wgc[base + src];
-      v.nprim_alt[base + q] = v.nprim[base + src];
-      v.hyst_alt[base + q] = v.hyst[base + src];
-      v.lct_alt[base + q] = v.lct[base + src];
-      v.gct_alt[base + q] = v.gct[base + src];
-      v.pbin_alt[base + q] = s_key[src] % nb + 1;
+      v.id_alt[base + q] = r_id;
+      v.wgc_alt[base + q] = r_wgc;
+      v.nprim_alt[base + q] = r_nprim;
+      v.hyst_alt[base + q] = r_hyst;
+      v.lct_alt[base + q] = r_lct;
+      v.gct_alt[base + q] = r_gct;
+      v.pbin_alt[base + q] = r_bin;
     }
   }
 }
