@@ -302,7 +302,8 @@ def run_b200(a):
     launches = g.launch_count() - launches0
     prof = g.profile_read(reset=True)
     g.profile_enable(False)
-    n_end = int(g.counts().sum())
+    cnt_end = g.counts()
+    n_end = int(cnt_end.sum())
     cst = g.condense_stats()
     csamp, ccoag = g.coag_stats()
     n_avg = 0.5 * (n_start + n_end)
@@ -383,6 +384,7 @@ def run_b200(a):
                            "phases": ["sort", "mc_coag(brownian)", "condense_particles", "rebalance", "partmc_to_wrf"] +
                                      (["trans_aero"] if has_transport else []),
                            "transport": bool(has_transport), "chem_dt_s": CHEM_DT,
+                           "cell_population_end": {"max": int(cnt_end.max()), "over_1024": float((cnt_end > 1024).mean())},
                            "l2": "inputs (%.1f GB of particle state per GPU) larger than L2" % (
                                n_avg * (8 * S + 44) / 1e9),
                            "particle_count": "mean of the population at the start and the end of the timed region",

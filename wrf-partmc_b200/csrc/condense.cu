@@ -1521,6 +1521,7 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 128)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 64)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 256)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 288>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 288)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<8, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(8, 256)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<2, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(2)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<4, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(4)));
@@ -1569,7 +1570,11 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     // threads each) instead of one CTA of 256 threads x 2 particles leaving half the register file idle
     if (cap > 256) { ROS_LAUNCH(4, 128, 256, 512); }
     if (cap > 512) { ROS_LAUNCH(4, 256, 512, 1024); }
-    if (cap > 1024) { ROS_LAUNCH(8, 256, 1024, 2048); }
+    // cells a little over 1024 particles (a 1000-particle population drifts there between rebalances):
+    // nine warps x 4 particles at 168 registers (three warps share a scheduler's 16384 registers; 422 bytes
+    // of spills) instead of 8 particles per thread (no predictor, 255 registers, 838 bytes of spills)
+    if (cap > 1024) { ROS_LAUNCH(4, 288, 1024, 1152); }
+    if (cap > 1152) { ROS_LAUNCH(8, 256, 1152, 2048); }
 #undef ROS_LAUNCH
   }
   if (cap > 2048) {

@@ -662,6 +662,20 @@ __global__ void k_tr_pack_copy(DevView v, TransView t, int side, const int* __re
 // arrivals into the alternate slab.  Arrival order = the order in which the reference's loops append to
 // delta_aero_states(dest): local sources in (j, k, i) order, then the four ghost receives.
 #define TR_MAXSEG 160
+// one particle's species rows from one slab to another (the slabs never overlap): loads in batches of eight
+// ahead of the stores
+__device__ __forceinline__ void tr_copy_rows(double* __restrict__ dst, size_t dstride, const double* __restrict__ src,
+                                             size_t sstride, int S) {
+  int s = 0;
+  for (; s + 8 <= S; s += 8) {
+    double a[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) a[u] = src[(size_t)(s + u) * sstride];
+#pragma unroll
+    for (int u = 0; u < 8; u++) dst[(size_t)(s + u) * dstride] = a[u];
+  }
+  for (; s < S; s++) dst[(size_t)s * dstride] = src[(size_t)s * sstride];
+}
 struct TrSeg {
   int kind;       // 0 survivors, 1 local out list, 2 halo slab
   int src;        // source cell (kind 0, 1) or side (kind 2)
@@ -674,39 +688,65 @@ __global__ void __launch_bounds__(128) k_tr_gather(DevView v, TransView t, TrSla
   const int i = cell % nx, k = (cell / nx) % nz, j = cell / (nx * nz);
   __shared__ TrSeg seg[TR_MAXSEG];
   __shared__ int s_nseg, s_total, s_fail;
-  if (threadIdx.x == 0) {
+  if (threadIdx.x < 32) {
+    // Candidate segments in arrival order: e = 0 the survivors, then (source cell, class) pairs of the local
+    // sources, then the four ghost receives.  Lanes read the candidates of a round side by side; the
+    // non-empty ones are appended in order (ballot compaction).
+    const int lane = threadIdx.x;
+    const int C = v.C;
+    const int n_src = nz + 3;  // y-, below (k), x-, x+, above (nz-1-k), y+
+    const int n_cand = 1 + n_src * C + 4;
     int ns = 0, tot = 0, fail = 0;
-    auto push = [&](int kind, int src, int off, int n) {
-      if (n <= 0) return;
-      if (ns >= TR_MAXSEG) { fail = 1; return; }
-      seg[ns].kind = kind; seg[ns].src = src; seg[ns].off = off; seg[ns].n = n;
-      ns++;
-      tot += n;
-    };
-    auto local = [&](int si, int sk, int sj, int slot) {
-      const int s = tr_cell(t, si, sk, sj);
-      for (int c = 0; c < v.C; c++) {
-        const int* od = t.out_dir + (((size_t)s * v.C + c) * nd + slot) * 2;
-        push(1, s, od[0], od[1]);
+    for (int e0 = 0; e0 < n_cand; e0 += 32) {
+      const int e = e0 + lane;
+      int kind = 0, src = 0, off = 0, cnt = 0;
+      if (e == 0) {
+        kind = 0; src = cell; off = 0; cnt = t.n_surv[cell];
+      } else if (e < 1 + n_src * C) {
+        const int u = (e - 1) / C, c = (e - 1) % C;
+        int si = i, sk = k, sj = j, slot = 0;
+        bool ok = true;
+        if (u == 0) { sj = j - 1; slot = 3; ok = (j - 1 >= 0); }
+        else if (u <= k) { sk = u - 1; slot = 4 + k; }
+        else if (u == k + 1) { si = i - 1; slot = 1; ok = (i - 1 >= 0); }
+        else if (u == k + 2) { si = i + 1; slot = 0; ok = (i + 1 <= nx - 1); }
+        else if (u <= nz + 1) { sk = u - 2; slot = 4 + k; }   // u = k+3 .. nz+1 -> sk = k+1 .. nz-1
+        else { sj = j + 1; slot = 2; ok = (j + 1 <= ny - 1); }
+        if (ok) {
+          const int sc = tr_cell(t, si, sk, sj);
+          const int* od = t.out_dir + (((size_t)sc * C + c) * nd + slot) * 2;
+          kind = 1; src = sc; off = od[0]; cnt = od[1];
+        }
+      } else if (e < n_cand) {
+        const int g = e - (1 + n_src * C);  // 0: side 1 (j == ny-1), 1: side 0 (j == 0), 2: side 3, 3: side 2
+        const int side = (g == 0) ? 1 : (g == 1 ? 0 : (g == 2 ? 3 : 2));
+        const bool ok = (g == 0) ? (j == ny - 1) : (g == 1 ? (j == 0) : (g == 2 ? (i == nx - 1) : (i == 0)));
+        if (ok) {
+          const int q = (side < 2) ? (k * nx + i) : (j * nz + k);
+          kind = 2; src = side; off = t.roff[side][q]; cnt = t.roff[side][q + 1] - off;
+        }
       }
-    };
-    push(0, cell, 0, t.n_surv[cell]);
-    if (j - 1 >= 0) local(i, k, j - 1, 3);
-    for (int sk = 0; sk < k; sk++) local(i, sk, j, 4 + k);
-    if (i - 1 >= 0) local(i - 1, k, j, 1);
-    if (i + 1 <= nx - 1) local(i + 1, k, j, 0);
-    for (int sk = k + 1; sk < nz; sk++) local(i, sk, j, 4 + k);
-    if (j + 1 <= ny - 1) local(i, k, j + 1, 2);
-    // ghost receives: what the y+ neighbour packed from its y- ghost row lands in my row ny-1, and so on
-    if (j == ny - 1) { const int q = k * nx + i; push(2, 1, t.roff[1][q], t.roff[1][q + 1] - t.roff[1][q]); }
-    if (j == 0) { const int q = k * nx + i; push(2, 0, t.roff[0][q], t.roff[0][q + 1] - t.roff[0][q]); }
-    if (i == nx - 1) { const int q = j * nz + k; push(2, 3, t.roff[3][q], t.roff[3][q + 1] - t.roff[3][q]); }
-    if (i == 0) { const int q = j * nz + k; push(2, 2, t.roff[2][q], t.roff[2][q + 1] - t.roff[2][q]); }
+      const bool have = cnt > 0;
+      const unsigned m = __ballot_sync(0xffffffffu, have);
+      const int pos = ns + __popc(m & ((1u << lane) - 1u));
+      if (have) {
+        if (pos < TR_MAXSEG) {
+          seg[pos].kind = kind; seg[pos].src = src; seg[pos].off = off; seg[pos].n = cnt;
+        }
+      }
+      int csum = have ? cnt : 0;
+      for (int o = 16; o > 0; o >>= 1) csum += __shfl_xor_sync(0xffffffffu, csum, o);
+      tot += csum;
+      ns += __popc(m);
+    }
+    if (ns > TR_MAXSEG) fail = 1;
     if (tot > v.cap) fail = 2;
-    s_nseg = ns;
-    s_total = tot;
-    s_fail = fail;
-    if (fail && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_CAPACITY;
+    if (lane == 0) {
+      s_nseg = ns;
+      s_total = tot;
+      s_fail = fail;
+      if (fail && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_CAPACITY;
+    }
   }
   __syncthreads();
   if (s_fail) return;
@@ -721,13 +761,16 @@ __global__ void __launch_bounds__(128) k_tr_gather(DevView v, TransView t, TrSla
     if (sg.kind == 2) {
       const TrSlab& sl = (sg.src == 0) ? r0 : (sg.src == 1 ? r1 : (sg.src == 2 ? r2 : r3));
       const size_t src = (size_t)sg.off + rel;
-      for (int s = 0; s < v.S; s++) v.vol_alt[(size_t)s * NS + dst] = sl.vol[(size_t)s * sl.cap + src];
-      v.id_alt[dst] = sl.id[src];
-      v.wgc_alt[dst] = sl.wgc[src];
-      v.nprim_alt[dst] = sl.nprim[src];
-      v.hyst_alt[dst] = sl.hyst[src];
-      v.lct_alt[dst] = sl.lct[src];
-      v.gct_alt[dst] = sl.gct[src];
+      const long long r_id = sl.id[src];
+      const int r_wgc = sl.wgc[src], r_nprim = sl.nprim[src], r_hyst = sl.hyst[src];
+      const double r_lct = sl.lct[src], r_gct = sl.gct[src];
+      tr_copy_rows(v.vol_alt + dst, NS, sl.vol + src, (size_t)sl.cap, v.S);
+      v.id_alt[dst] = r_id;
+      v.wgc_alt[dst] = r_wgc;
+      v.nprim_alt[dst] = r_nprim;
+      v.hyst_alt[dst] = r_hyst;
+      v.lct_alt[dst] = r_lct;
+      v.gct_alt[dst] = r_gct;
     } else {
       const size_t sbase = (size_t)sg.src * v.cap;
       size_t src;
@@ -738,13 +781,16 @@ __global__ void __launch_bounds__(128) k_tr_gather(DevView v, TransView t, TrSla
         src = sbase + t.out_slot[sbase + sg.off + rel];
         nid = t.out_newid[sbase + sg.off + rel];
       }
-      for (int s = 0; s < v.S; s++) v.vol_alt[(size_t)s * NS + dst] = v.vol[(size_t)s * NS + src];
-      v.id_alt[dst] = nid ? nid : v.id[src];
-      v.wgc_alt[dst] = v.wgc[src];
-      v.nprim_alt[dst] = v.nprim[src];
-      v.hyst_alt[dst] = v.hyst[src];
-      v.lct_alt[dst] = v.lct[src];
-      v.gct_alt[dst] = v.gct[src];
+      const long long r_id = nid ? nid : v.id[src];
+      const int r_wgc = v.wgc[src], r_nprim = v.nprim[src], r_hyst = v.hyst[src];
+      const double r_lct = v.lct[src], r_gct = v.gct[src];
+      tr_copy_rows(v.vol_alt + dst, NS, v.vol + src, NS, v.S);
+      v.id_alt[dst] = r_id;
+      v.wgc_alt[dst] = r_wgc;
+      v.nprim_alt[dst] = r_nprim;
+      v.hyst_alt[dst] = r_hyst;
+      v.lct_alt[dst] = r_lct;
+      v.gct_alt[dst] = r_gct;
     }
   }
   if (threadIdx.x == 0) {
