@@ -78,7 +78,9 @@ def test_probabilities_match_oracle(mods):
 
 
 @pytest.mark.parametrize("kw", [dict(), dict(uniform=True), dict(nx=3, nz=4, ny=2, n_per_cell=500, ragged=0.5),
-                                dict(nx=1, nz=3, ny=1, n_per_cell=300), dict(n_spec=20, nx=4, nz=6, ny=3)])
+                                dict(nx=1, nz=3, ny=1, n_per_cell=300), dict(n_spec=20, nx=4, nz=6, ny=3),
+                                # populations on both sides of half the capacity: both launches of the sampler
+                                dict(nx=3, nz=4, ny=2, n_per_cell=500, ragged=0.5, cap=800)])
 def test_trans_aero_bit_exact(mods, kw):
     W, O = mods
     case, g, o, f, fp = _setup(W, O, **kw)

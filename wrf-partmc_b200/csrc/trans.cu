@@ -384,17 +384,25 @@ __device__ __forceinline__ void tr_remove(TrIdx& x, int p) {
 }
 
 #define TR_CHUNK 32
-__global__ void k_tr_multisample(DevView v, TransView t, unsigned step, int warps_per_cta) {
+// The index state of a cell is sized by lcap (>= its population), not by the slab capacity: the launch for
+// the cells with n_lo < n <= n_hi = lcap keeps several CTAs per SM, a second launch (lcap = capacity) takes the
+// few larger cells.
+__global__ void k_tr_multisample(DevView v, TransView t, unsigned step, int warps_per_cta, int lcap, int n_lo,
+                                 int n_hi) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * warps_per_cta + warp;
   if (cell >= v.n_cells) return;
+  {
+    const int nn = v.count[cell];
+    if (nn <= n_lo || nn > n_hi) return;
+  }
   extern __shared__ int s_i[];
   const int nd = TR_ND(t.nz);
-  const int per_warp = (3 * v.cap + 2 * v.C + 3 * TR_CHUNK + 3 * nd + 1) & ~1;
+  const int per_warp = (3 * lcap + 2 * v.C + 3 * TR_CHUNK + 3 * nd + 1) & ~1;
   int* sm = s_i + (size_t)warp * per_warp;
   TrIdx x;
-  x.P2O = sm; x.LST = sm + v.cap; x.FXC = sm + 2 * v.cap;
-  x.len = sm + 3 * v.cap; x.off = x.len + v.C;
+  x.P2O = sm; x.LST = sm + lcap; x.FXC = sm + 2 * lcap;
+  x.len = sm + 3 * lcap; x.off = x.len + v.C;
   int* ch_entry = x.off + v.C;           // [TR_CHUNK] list entry (1-based) of every transfer of the chunk
   int* ch_flags = ch_entry + TR_CHUNK;   // bit 0 add, bit 1 remove
   int* sdir = ch_flags + TR_CHUNK;       // [nd] direction slot in sorted order
@@ -947,22 +955,32 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
   {
     ProfScope ps_(ctx, "k_tr_multisample");
     const int nd = TR_ND(t.nz);
-    const size_t per_warp_i = (3 * (size_t)v.cap + 2 * C + 3 * TR_CHUNK + 3 * nd + 1) & ~(size_t)1;
-    const size_t per_warp_b = per_warp_i * sizeof(int) + nd * sizeof(double);
-    int wpc = (int)std::min<size_t>(4, (200 * 1024) / per_warp_b);
-    if (wpc < 1) {
-      ctx->err = "cell_capacity too large for the shared-memory index state of the transport sampler";
-      return PMCGPU_ERR_ARG;
-    }
-    // the sorted probabilities (doubles) start behind the int regions of all warps
-    const size_t smem_total = (size_t)wpc * per_warp_i * sizeof(int) + (size_t)wpc * nd * sizeof(double);
     static size_t configured = 0;
-    if (smem_total > 48 * 1024 && smem_total > configured) {
-      CUDA_OK(ctx, cudaFuncSetAttribute(k_tr_multisample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total));
-      configured = smem_total;
+    // small cells (at most half the slab capacity) first, then the rest
+    const int lsmall = (v.cap > 512) ? ((v.cap / 2 + 1) & ~1) : v.cap;
+    for (int pass = 0; pass < 2; pass++) {
+      const int lcap = pass == 0 ? lsmall : v.cap;
+      const int n_lo = pass == 0 ? -1 : lsmall, n_hi = lcap;
+      if (pass == 1 && lsmall >= v.cap) break;
+      const size_t per_warp_i = (3 * (size_t)lcap + 2 * C + 3 * TR_CHUNK + 3 * nd + 1) & ~(size_t)1;
+      const size_t per_warp_b = per_warp_i * sizeof(int) + nd * sizeof(double);
+      // CTAs of at most 56 KB so that four or more share an SM when the lists are short
+      int wpc = (int)std::min<size_t>(4, (56 * 1024) / per_warp_b);
+      if (wpc < 1) wpc = 1;
+      if (per_warp_b > 200 * 1024) {
+        ctx->err = "cell_capacity too large for the shared-memory index state of the transport sampler";
+        return PMCGPU_ERR_ARG;
+      }
+      // the sorted probabilities (doubles) start behind the int regions of all warps
+      const size_t smem_total = (size_t)wpc * per_warp_i * sizeof(int) + (size_t)wpc * nd * sizeof(double);
+      if (smem_total > 48 * 1024 && smem_total > configured) {
+        CUDA_OK(ctx, cudaFuncSetAttribute(k_tr_multisample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total));
+        configured = smem_total;
+      }
+      k_tr_multisample<<<(unsigned)((nc + wpc - 1) / wpc), wpc * 32, smem_total, st>>>(v, t, a->step, wpc, lcap, n_lo,
+                                                                                       n_hi);
+      LAUNCH_CHECK(ctx);
     }
-    k_tr_multisample<<<(unsigned)((nc + wpc - 1) / wpc), wpc * 32, smem_total, st>>>(v, t, a->step, wpc);
-    LAUNCH_CHECK(ctx);
   }
   // ---- C4: ghost particles
   {
