@@ -23,6 +23,9 @@
 #define PMC_RNG_NOINLINE
 #include "pmcgpu_internal.cuh"
 
+#ifndef COAG_MIN_CTAS
+#define COAG_MIN_CTAS 12  // 40 registers: measured 28.2 (5) / 27.4 (6) / 23.3 (8) / 22.1 (10) / 20.2 (12) / 20.1 (16) ms per K4 step
+#endif
 #define COAG_WARPS 4
 static const double BETA_1 = 1000.0;
 static const double BETA_0 = 0.25 / (60.0 * 2e8);
@@ -604,7 +607,7 @@ __device__ __forceinline__ bool pair_advance_exact(int C, int nb, int& c1, int& 
   return true;
 }
 
-__global__ void __launch_bounds__(COAG_WARPS * 32, 8) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
+__global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * COAG_WARPS + warp;
   if (cell >= v.n_cells) return;
