@@ -674,15 +674,14 @@ __global__ void k_tr_pack_copy(DevView v, TransView t, int side, const int* __re
 // ahead of the stores
 __device__ __forceinline__ void tr_copy_rows(double* __restrict__ dst, size_t dstride, const double* __restrict__ src,
                                              size_t sstride, int S) {
-  int s = 0;
-  for (; s + 8 <= S; s += 8) {
+  for (int s = 0; s < S; s += 8) {  // the last batch is predicated, not serialised
     double a[8];
 #pragma unroll
-    for (int u = 0; u < 8; u++) a[u] = src[(size_t)(s + u) * sstride];
+    for (int u = 0; u < 8; u++) a[u] = (s + u < S) ? src[(size_t)(s + u) * sstride] : 0.0;
 #pragma unroll
-    for (int u = 0; u < 8; u++) dst[(size_t)(s + u) * dstride] = a[u];
+    for (int u = 0; u < 8; u++)
+      if (s + u < S) dst[(size_t)(s + u) * dstride] = a[u];
   }
-  for (; s < S; s++) dst[(size_t)s * dstride] = src[(size_t)s * sstride];
 }
 struct TrSeg {
   int kind;       // 0 survivors, 1 local out list, 2 halo slab
@@ -690,7 +689,7 @@ struct TrSeg {
   int off;        // offset in the list / slab
   int n;
 };
-__global__ void __launch_bounds__(128) k_tr_gather(DevView v, TransView t, TrSlab r0, TrSlab r1, TrSlab r2, TrSlab r3) {
+__global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, TrSlab r0, TrSlab r1, TrSlab r2, TrSlab r3) {
   const int cell = blockIdx.x;
   const int nx = t.nx, nz = t.nz, ny = t.ny, nd = TR_ND(t.nz);
   const int i = cell % nx, k = (cell / nx) % nz, j = cell / (nx * nz);
