@@ -358,7 +358,10 @@ def run_b200(a):
         dom = kern[0] if kern else None
         if dom and dom["kernel"] == "k_condense":
             roofline = {"kernel": "k_condense", "bound": "fp64", "achieved": cond_tflops, "peak": fp64_peak,
-                        "unit": "TFLOP/s", "frac": cond_tflops / fp64_peak if fp64_peak else None, "traffic": None,
+                        "unit": "TFLOP/s", "frac": cond_tflops / fp64_peak if fp64_peak else None,
+                        # dram__bytes_read + write of one ncu --set full capture of this kernel, scaled by the
+                        # particle count: 1.323 GB + 68 MB for 7.64e6 particles (profiles/r01_s14_condense_ncu.md)
+                        "traffic": 182.1 * n_avg, "traffic_unit": "bytes per launch (ncu capture, scaled)",
                         "peak_source": "FP64 FMA microbenchmark in this run (pmcgpu_measure_fp64_peak); "
                                        "MEASURED_PEAKS.json holds no FP64 figure",
                         "fp64_pipe_slots_used": cond_pipe,
@@ -375,7 +378,9 @@ def run_b200(a):
         roofline_hbm = None
         if sortk:
             roofline_hbm = {"kernel": "k_sort_cells", "bound": "hbm", "achieved": sortk["hbm_gbs"], "peak": hbm_peak,
-                            "unit": "GB/s", "frac": sortk["hbm_gbs"] / hbm_peak, "traffic": None,
+                            "unit": "GB/s", "frac": sortk["hbm_gbs"] / hbm_peak,
+                            # 1.536 GB + 1.497 GB for 7.64e6 records (profiles/r01_s15_sort_ncu.md)
+                            "traffic": 397.0 * n_avg, "traffic_unit": "bytes per launch (ncu capture, scaled)",
                             "peak_source": hbm_src}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": t_dev * 1e3 / a.steps, "higher_is_better": True, "scaling": "weak",
