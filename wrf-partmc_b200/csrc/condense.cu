@@ -30,6 +30,10 @@ struct CondEnv {  // cell-level terms of condense_rates that depend on (T, p) on
   double k_a, D_v, U, V, W, X, Y, Z, UV;
   double dP0_dT_div_P0;
   double vc;  // V_comp * num_conc = (T * p0) / (T0 * p)
+  // scalars every thread would otherwise divide out again in every rate evaluation
+  double g_coef;      // -2 pi / (V vc): Hdot_i = g_coef * num_conc * D^2 * Ddot
+  double invU;        // 1 / U
+  double pdot_div_p;  // pdot / p
 };
 __device__ __forceinline__ CondEnv cond_env(double T0, double p0, double Tdot, double pdot, double t) {
   CondEnv e;
@@ -53,6 +57,9 @@ __device__ __forceinline__ CondEnv cond_env(double T0, double p0, double Tdot, d
   e.Z = 2.0 * e.D_v / PmcConst::accom_coeff * sqrt(2.0 * PmcConst::pi * M_w / (PmcConst::univ_gas_const * e.T));
   e.UV = e.U * e.V;
   e.vc = (e.T * p0) / (T0 * e.p);
+  e.g_coef = -2.0 * PmcConst::pi / (e.V * e.vc);
+  e.invU = 1.0 / e.U;
+  e.pdot_div_p = pdot / e.p;
   return e;
 }
 
@@ -258,6 +265,9 @@ __device__ __forceinline__ CondEnv cond_env_fast(double T0, double p0, double Td
   e.Z = 2.0 * e.D_v / PmcConst::accom_coeff * (sqrt(2.0 * PmcConst::pi * M_w / R) * rsT);
   e.UV = e.U * e.V;
   e.vc = (e.T * p0) * invp / T0;
+  e.g_coef = -2.0 * PmcConst::pi / (e.V * e.vc);
+  e.invU = 1.0 / e.U;
+  e.pdot_div_p = pdot / e.p;
   return e;
 }
 
@@ -303,8 +313,8 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
                                                const double* D0 = nullptr, double H0 = 0.0, double dts = 0.0,
                                                bool write_uN = false) {
   constexpr int AS = PPT * NT;
-  const double g = -2.0 * PmcConst::pi / (e.V * e.vc);  // Hdot_i = g * num_conc * D^2 * Ddot
-  const double invU = 1.0 / e.U;
+  const double g = e.g_coef;  // Hdot_i = g * num_conc * D^2 * Ddot
+  const double invU = e.invU;
   double k_ap[PPT], UVD[PPT], a_w[PPT], XD[PPT], invD[PPT];
   double inv_dY[PPT], inv_dZ[PPT], inv_den[PPT];
   double u[PPT], A[PPT], kB[PPT], cW[PPT];
@@ -671,7 +681,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     }
     __syncthreads();
   };
-  auto env_H = [&](const CondEnv& e, double Hs) { return -e.dP0_dT_div_P0 * Tdot * Hs + Hs * pdot / e.p; };
+  auto env_H = [&](const CondEnv& e, double Hs) { return -e.dP0_dT_div_P0 * Tdot * Hs + Hs * e.pdot_div_p; };
 
   double h = del_t;  // replaced by the estimate below before the first step
   int n_evals = 0;
@@ -705,7 +715,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       }
       cell_red<3, NT, false, GRID>(acc, s_red, par, gr, s_g);
       f0H = acc[0] + env_H(s_env[0], H);
-      dd = acc[1] + (-s_env[0].dP0_dT_div_P0 * Tdot + pdot / s_env[0].p);
+      dd = acc[1] + (-s_env[0].dP0_dT_div_P0 * Tdot + s_env[0].pdot_div_p);
       dfdtH = ((acc[2] + env_H(s_env[1], H)) - f0H) / DT_FD;
     }
     if (n_steps + n_reject == 0) {
