@@ -773,7 +773,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
         if (tid + (poff + k) * NT < n) sden[0] += jc[k] * jb[k] * inv[k];
       }
       cell_red<1, NT, false, GRID>(sden, s_red, par, gr, s_g);
-      const double lhs_H = eps - dd - sden[0];
+      const double inv_lhs_H = 1.0 / (eps - dd - sden[0]);  // one division per attempt, not one per stage
 #pragma unroll 1
       for (int st = 0; st < ROS_S; st++) {
         // stage function value (stage 1 reuses f at (t, y))
@@ -822,7 +822,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
           fsH = acc[0] + env_H(s_env[st + 1], Hs);
         double rH = fsH + hg * dfdtH;
         for (int j = 0; j < st; j++) rH += (c_rosC[st][j] * inv_h) * KH[j];
-        KH[st] = (rH + acc[1]) / lhs_H;
+        KH[st] = (rH + acc[1]) * inv_lhs_H;
 #pragma unroll
         for (int k = 0; k < PPT; k++) SK(st, k) = (fs[k] + jb[k] * KH[st]) * inv[k];
       }
