@@ -692,7 +692,13 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
 
   while (t < del_t && !fail) {
     if (n_steps + n_reject >= prm.max_steps) { fail = 6; break; }
-    make_envs(t, h, 0, 1);
+    // After the first step h is known here, so the stage environments are built together with those of the
+    // Jacobian evaluation (one entry per warp, one barrier) instead of in a second round.
+    const bool first_step = (n_steps + n_reject == 0);
+    bool truncated = false;
+    if (!first_step && t + h > del_t * (1.0 - 1e-14)) { h_natural = h; h = del_t - t; truncated = true; }
+    make_envs(t, h, 0, first_step ? 1 : ROS_NENV - 1);
+    bool stage_envs_ready = !first_step;
     // f, Jacobian at (t, y) and f at (t + DT_FD, y)
     double f0[PPT], dfdt[PPT], ja[PPT], jb[PPT], jc[PPT];
     double f0H, dfdtH, dd;
@@ -718,7 +724,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       dd = acc[1] + (-s_env[0].dP0_dT_div_P0 * Tdot + s_env[0].pdot_div_p);
       dfdtH = ((acc[2] + env_H(s_env[1], H)) - f0H) / DT_FD;
     }
-    if (n_steps + n_reject == 0) {
+    if (first_step) {
       // first step size, after cvHin (cvode.c): h = 1/2 sqrt(2 / ||y''||), bounded by hub, times ROS_HIN_FACTOR
       // for a 4th-order method (small enough that the first step is never near rejection).  CVODE differences f along the solution; here y'' = J f + df/dt comes from the
       // Jacobian of this step, which carries no cancellation noise (a noisy first step would make two
@@ -757,11 +763,11 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       h = __longlong_as_double(__double_as_longlong(h) & 0x7FF0000000000000ll);
       h = fmin(del_t, h);
       h_natural = h;
+      if (t + h > del_t * (1.0 - 1e-14)) { h_natural = h; h = del_t - t; truncated = true; }
     }
-    bool truncated = false;
-    if (t + h > del_t * (1.0 - 1e-14)) { h_natural = h; h = del_t - t; truncated = true; }
     for (;;) {
-      make_envs(t, h, 2, ROS_NENV - 1);  // stage times of this attempt
+      if (!stage_envs_ready) make_envs(t, h, 2, ROS_NENV - 1);  // stage times of this attempt
+      stage_envs_ready = false;
       const double eps = 1.0 / (ROS_GAMMA * h);
       const double inv_h = 1.0 / h;
       double inv[PPT];
