@@ -346,10 +346,10 @@ def run_b200(a):
                          "alg_bytes_per_launch": by, "hbm_gbs": by / per_launch_s / 1e9 if per_launch_s > 0 else None})
         # FP64 work of the condensation integrator: rate evaluations x counted FP64 operations per evaluation
         evals_per_step = float((cst[:, 2].astype(np.float64) * case["counts"]).sum())
-        # counted by ncu on this kernel (profiles/r01_s14_condense_ncu.md): per rate evaluation and particle,
-        # integrator arithmetic included, 64.4 DFMA + 49.8 DMUL + 21.1 DADD thread instructions
-        FLOP_PER_RATE_EVAL = 199.7   # DFMA = 2 flop
-        FP64_INST_PER_RATE_EVAL = 135.3
+        # counted by ncu on this kernel (profiles/r01_s15_condense_ncu.md): per rate evaluation and particle,
+        # integrator arithmetic included, 58.5 DFMA + 49.5 DMUL + 20.8 DADD thread instructions
+        FLOP_PER_RATE_EVAL = 187.3   # DFMA = 2 flop
+        FP64_INST_PER_RATE_EVAL = 128.8
         cond_ms = prof.get("k_condense", (0.0, 1))[0] / a.steps
         cond_tflops = evals_per_step * FLOP_PER_RATE_EVAL / (cond_ms * 1e-3) / 1e12 if cond_ms > 0 else None
         # share of the FP64 pipe's issue slots in use (a DMUL or DADD takes the slot of a DFMA but counts one flop)
@@ -360,15 +360,15 @@ def run_b200(a):
             roofline = {"kernel": "k_condense", "bound": "fp64", "achieved": cond_tflops, "peak": fp64_peak,
                         "unit": "TFLOP/s", "frac": cond_tflops / fp64_peak if fp64_peak else None,
                         # dram__bytes_read + write of one ncu --set full capture of this kernel, scaled by the
-                        # particle count: 1.323 GB + 68 MB for 7.64e6 particles (profiles/r01_s14_condense_ncu.md)
-                        "traffic": 182.1 * n_avg, "traffic_unit": "bytes per launch (ncu capture, scaled)",
+                        # particle count: 1.323 GB + 64 MB for 7.64e6 particles (profiles/r01_s15_condense_ncu.md)
+                        "traffic": 181.6 * n_avg, "traffic_unit": "bytes per launch (ncu capture, scaled)",
                         "peak_source": "FP64 FMA microbenchmark in this run (pmcgpu_measure_fp64_peak); "
                                        "MEASURED_PEAKS.json holds no FP64 figure",
                         "fp64_pipe_slots_used": cond_pipe,
                         "note": "the dominant kernel is bounded by the FP64 pipe, not by HBM or the tensor cores "
                                 "(north star: no dense contraction on the path); achieved = rate evaluations x "
-                                "199.7 flop (ncu-counted, DFMA = 2) / kernel time; fp64_pipe_slots_used counts "
-                                "DFMA, DMUL and DADD alike (135.3 per evaluation) against peak / 2 instructions/s"}
+                                "187.3 flop (ncu-counted, DFMA = 2) / kernel time; fp64_pipe_slots_used counts "
+                                "DFMA, DMUL and DADD alike (128.8 per evaluation) against peak / 2 instructions/s"}
         elif dom:
             roofline = {"kernel": dom["kernel"], "bound": "hbm", "achieved": dom["hbm_gbs"], "peak": hbm_peak,
                         "unit": "GB/s", "frac": dom["hbm_gbs"] / hbm_peak, "traffic": None, "peak_source": hbm_src}
