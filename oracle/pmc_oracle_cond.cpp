@@ -624,7 +624,7 @@ int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const
   if (opt.method == 5)
     return condense_integrate_bdf(n, D, Hio, D_dry, kappa, num_conc, T0, p0, Tdot, pdot, del_t, opt, stats);
   const RosTableau tb = (opt.method == 4) ? tableau_rodas4() : tableau_rodas3();
-  const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.9, FAC_REJ = 0.1;
+  const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.95, FAC_REJ = 0.1;
   const double DT_FD = 1e-2;  // forward difference in t for df/dt (T and p are linear in t)
   CondSys sys{n, D_dry, kappa, num_conc, T0, p0, Tdot, pdot};
   const int S = tb.S;

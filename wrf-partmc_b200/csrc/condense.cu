@@ -668,7 +668,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     wsum = x[0];  // water_vol_conc_initial
   }
 
-  const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.9, FAC_REJ = 0.1;
+  const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.95, FAC_REJ = 0.1;
   const double DT_FD = COND_DT_FD;
   double u1[PPT], u2[PPT], u3[PPT], u4[PPT];  // unused outputs of the no-Jacobian evaluations
   const int warp = tid >> 5, lane = tid & 31;
