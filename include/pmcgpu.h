@@ -36,11 +36,11 @@ enum {
   PMCGPU_ERR_CAPACITY = 3,        /* a cell outgrew cell_capacity */
   PMCGPU_ERR_BIN_RANGE = 134572570, /* coagulated particle outside bin grid (aero_sorted.F90:434 die_msg code) */
   PMCGPU_ERR_NBINS = 5,           /* adaptive grid needs more than max_bins bins */
-  PMCGPU_ERR_ACCEL = 6,           /* try_per_particle_coag would be taken (coagulation.F90:150), not built yet */
+  PMCGPU_ERR_ACCEL = 6,           /* reserved (try_per_particle_coag, coagulation.F90:150, is built: never returned) */
   PMCGPU_ERR_CONDENSE = 7,        /* condensation integrator failed (condense.F90:331-363 codes) */
   PMCGPU_ERR_PROB = 414897881,    /* transport probabilities invalid (wrf_pmc_trans.F90:702-771 assert codes) */
   PMCGPU_ERR_NCCL = 9,
-  PMCGPU_ERR_REWEIGHT = 10        /* aero_state_reweight with size-dependent weights (aero_state.F90:597), not built yet */
+  PMCGPU_ERR_REWEIGHT = 10        /* reserved (aero_state_reweight, aero_state.F90:597, is built: never returned) */
 };
 
 /* coag_kernel.F90:24-40 type codes */
@@ -63,7 +63,8 @@ typedef struct {
   int global_nx, global_ny;    /* global horizontal extents */
   int i_offset, j_offset;      /* global index of local (0,0) */
   int periodic_x, periodic_y;
-  double n_part_ideal;         /* grid%num_particles, split evenly over (group, class) (aero_state.F90:241) */
+  double n_part_ideal;         /* grid%num_particles, split evenly over (group, class) (aero_state.F90:241);
+                                  per-(group, class) values: pmcgpu_set_n_part_ideal */
   int cell_capacity;           /* particle slots per cell (>= 2 * n_part_ideal + slack) */
   int max_bins;                /* capacity of the per-cell adaptive bin grid (<= 255) */
   unsigned int seed;           /* random_seed (wrf_pmc_init.F90:131) */
@@ -101,6 +102,9 @@ int pmcgpu_get_weights(pmcgpu_ctx* ctx, int* type, double* magnitude, double* ex
 int pmcgpu_set_env(pmcgpu_ctx* ctx, const double* temp, const double* pressure, const double* rel_humid,
                    const double* inverse_density, const double* cell_volume);
 int pmcgpu_get_rel_humid(pmcgpu_ctx* ctx, double* rel_humid);
+/* aero_state%n_part_ideal(n_group, n_class) (aero_state.F90:81, :241): one value per (group, class) for all
+ * cells, [(class - 1) * n_group + (group - 1)]; the default is pmcgpu_config.n_part_ideal split evenly. */
+int pmcgpu_set_n_part_ideal(pmcgpu_ctx* ctx, const double* n_part_ideal);
 
 /* ---- the path ---------------------------------------------------------- */
 /* aero_state_sort (aero_state.F90:3218) for every cell: adaptive bin grid
@@ -189,7 +193,9 @@ int pmcgpu_num_conc_by_class(pmcgpu_ctx* ctx, float* out);
 typedef struct {
   const double* temp;             /* env_state%temp            (wrf_to_partmc, :576-644) */
   const double* pressure;         /* env_state%pressure */
-  const double* rel_humid;        /* env_state%rel_humid; NULL keeps the integrator's value */
+  const double* rel_humid;        /* env_state%rel_humid; NULL keeps the integrator's value.  Installed only in steps
+                                     without condensation: condense_particles starts from old_env_states' value
+                                     (condense.F90:237) and overwrites the new one (:263) */
   const double* inverse_density;  /* grid%alt */
   const double* cell_volume;
   double elapsed_time;            /* seconds since simulation start (:126) */
@@ -285,6 +291,11 @@ int pmcgpu_get_cell_status(pmcgpu_ctx* ctx, int* status); /* [n_cells] first err
  * condense.F90:135-138 condense_count_vf / _solve) and of the last mc_coag (tot_n_samp, tot_n_coag) */
 int pmcgpu_get_condense_stats(pmcgpu_ctx* ctx, int* stats);
 int pmcgpu_get_coag_stats(pmcgpu_ctx* ctx, int* tot_n_samp, int* tot_n_coag);
+/* work counters accumulated on the device since the last reset (bench.py's roofline and metric):
+ * work[0] particle rate evaluations of condense_particles (rate evaluations x particles, over cells and calls),
+ * work[1] particles condense_particles integrated, work[2] particles at the start of every
+ * pmcgpu_partmc_timestep (particle-timesteps), work[3] unused */
+int pmcgpu_get_work(pmcgpu_ctx* ctx, unsigned long long* work, int reset);
 /* stand-alone evaluations of device functions, for known-answer tests */
 int pmcgpu_eval_kernel_brown(pmcgpu_ctx* ctx, int n, const double* v1, const double* d1, const double* v2,
                              const double* d2, const double* temp, const double* pressure, double* out);

@@ -131,8 +131,9 @@ int pmco_partmc_timestep(void* h, int cell_lo, int cell_hi, const double* T, con
           for (auto& w : st.awa.w) w.magnitude *= f;
         }
         if (chem && do_cond) {
+          // env_state_initial is old_env_states, the full copy made before wrf_to_partmc refreshed rel_humid
+          // (wrf_pmc_driver.F90:615-624): the integrator starts from the OLD relative humidity (condense.F90:237)
           EnvState e0 = old_env;
-          e0.rel_humid = env.rel_humid;
           EnvState e1 = env;
           CondenseOpts opt;
           if (d->cond_method > 0) opt.method = d->cond_method;

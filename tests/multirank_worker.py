@@ -17,21 +17,8 @@ sys.path.insert(0, HERE)
 
 
 def patch_case(case, i0, nxl, j0, nyl):
-    """the cells [i0, i0+nxl) x all k x [j0, j0+nyl) of a global case, in the patch's own cell order"""
-    gnx, nz = case["nx"], case["nz"]
-    cells = np.array([(i0 + il) + gnx * (k + nz * (j0 + jl)) for jl in range(nyl) for k in range(nz)
-                      for il in range(nxl)])
-    off = np.concatenate([[0], np.cumsum(case["counts"])])
-    idx = np.concatenate([np.arange(off[c], off[c + 1]) for c in cells])
-    out = dict(case)
-    out.update(n_cells=len(cells), nx=nxl, ny=nyl, counts=case["counts"][cells], vol=case["vol"][:, idx])
-    for k in ("wclass", "wgroup", "id", "n_primary", "hyst", "lct", "gct"):
-        out[k] = case[k][idx]
-    for k in ("wtype", "wmag", "wexp", "T", "P", "RH", "rrho", "cell_volume"):
-        if k in case:
-            out[k] = case[k][cells]
-    out["cells"] = cells
-    return out
+    from wrf_partmc_b200.host import decomp
+    return decomp.patch_case(case, i0, nxl, j0, nyl)
 
 
 def global_case(cfg):
@@ -48,8 +35,14 @@ def run_cpu(rank, world, port, out_dir):
     nb = decomp.neighbours(rank, px, py)
     ext = decomp.patch_extents(rank, px, py, 5, 3)
     t, n = decomp.reduce_job([1.0 + rank, 2.0 - rank], [100.0 * (rank + 1), 7.0])
+    # strong-scaling layout: one 7 x 5 domain (3 levels) cut unevenly; every rank contributes "global cell index"
+    # of its tile, gather_global must return 0 .. n-1 in WRF memory order on every rank
+    i0, nxl, j0, nyl = decomp.tile_of_rank(rank, px, py, 7, 5)
+    mine = decomp.tile_cells(7, 3, i0, nxl, j0, nyl).astype(np.float64)
+    glob = decomp.gather_global(np.stack([mine, 2.0 * mine], axis=1), 7, 3, 5, px, py)
     np.savez(os.path.join(out_dir, "cpu_%d.npz" % rank), uid=np.frombuffer(uid, np.uint8), nb=nb, px=px, py=py,
-             ext=np.array([ext["global_nx"], ext["global_ny"], ext["i_offset"], ext["j_offset"]]), t=t, n=n)
+             ext=np.array([ext["global_nx"], ext["global_ny"], ext["i_offset"], ext["j_offset"]]), t=t, n=n,
+             glob=glob, tile=np.array([i0, nxl, j0, nyl]))
     dist.barrier()
     dist.destroy_process_group()
 

@@ -48,6 +48,13 @@ def test_decomposition_host_logic_gloo(world):
         # max over ranks of the times, sum over ranks of the particles
         assert list(r[k]["t"]) == [float(world), 2.0]
         assert list(r[k]["n"]) == [100.0 * world * (world + 1) / 2, 7.0 * world]
+    # strong-scaling tiles of an uneven 7 x 5 domain cover it exactly once, and the gathered field is global order
+    cover = np.zeros((5, 7), int)
+    for k in range(world):
+        i0, nxl, j0, nyl = r[k]["tile"]
+        cover[j0:j0 + nyl, i0:i0 + nxl] += 1
+        assert np.array_equal(r[k]["glob"][:, 0], np.arange(7 * 3 * 5)) and np.array_equal(r[k]["glob"][:, 1], 2.0 * np.arange(105))
+    assert (cover == 1).all()
     # patches tile the global domain exactly once
     seen = set()
     for k in range(world):
@@ -57,6 +64,14 @@ def test_decomposition_host_logic_gloo(world):
                 assert (i, j) not in seen
                 seen.add((i, j))
     assert len(seen) == 5 * px * 3 * py
+
+
+def test_split_like_wrf():
+    from wrf_partmc_b200.host import decomp
+    assert decomp.split(150, 4) == [(0, 38), (38, 38), (76, 37), (113, 37)]
+    assert sum(m for _, m in decomp.split(40, 3)) == 40
+    c = decomp.tile_cells(6, 2, 2, 3, 1, 2)
+    assert c[0] == 2 + 6 * (0 + 2 * 1) and len(c) == 3 * 2 * 2 and c[3] == 2 + 6 * (1 + 2 * 1)
 
 
 def test_patch_slicing_matches_global_cell_order():

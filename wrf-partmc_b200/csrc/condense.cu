@@ -927,6 +927,8 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     stats[3 * cell + 0] = n_steps;
     stats[3 * cell + 1] = n_reject;
     stats[3 * cell + 2] = n_evals;  // rate evaluations per particle
+    atomicAdd(&v.work[0], (unsigned long long)n_evals * (unsigned long long)n);
+    atomicAdd(&v.work[1], (unsigned long long)n);
   }
     if (GRID) __syncthreads();
   }
@@ -1518,6 +1520,8 @@ __global__ void __launch_bounds__(NT) k_condense_bdf(DevView v, const double* T0
     stats[3 * cell + 0] = nst;
     stats[3 * cell + 1] = n_fail;
     stats[3 * cell + 2] = n_evals;  // rate evaluations per particle
+    atomicAdd(&v.work[0], (unsigned long long)n_evals * (unsigned long long)n);
+    atomicAdd(&v.work[1], (unsigned long long)n);
   }
 #undef ZN
 #undef S_ATOL
@@ -1532,8 +1536,7 @@ int pmc_reweight_async(pmcgpu_ctx* ctx, unsigned step, unsigned pass);
 
 int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, const double* dT1, const double* dp1,
                        double del_t, double reltol, unsigned step) {
-  static bool configured = false;
-  if (!configured) {
+  if (!ctx->cfg_cond) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 128)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 64)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 256)));
@@ -1542,7 +1545,7 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<2, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(2)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<4, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(4)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<8, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(8)));
-    configured = true;
+    ctx->cfg_cond = true;
   }
   DevView& v = ctx->v;
   DevView* cw = &v;
@@ -1596,8 +1599,9 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
   if (cap > 2048) {
     // single-box sized cells: the RODAS4 integrator with one cell spread over a co-resident grid
     // (both methods: the BDF restatement has no grid-wide variant)
-    static int n_sm = 0;
-    static int max_blk4 = 0, max_blk8 = 0;
+    int& n_sm = ctx->cond_n_sm;
+    int& max_blk4 = ctx->cond_max_blk4;
+    int& max_blk8 = ctx->cond_max_blk8;
     if (!n_sm) {
       int dev = 0;
       CUDA_OK(ctx, cudaGetDevice(&dev));

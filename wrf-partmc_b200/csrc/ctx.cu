@@ -100,7 +100,7 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   A(v.coag_samp, v.n_cells) A(v.coag_ncoag, v.n_cells)
   A(v.cond_T1, v.n_cells) A(v.cond_p1, v.n_cells) A(v.cond_h, v.n_cells) A(v.cond_stats, (size_t)3 * v.n_cells)
   A(v.cond_wre, v.n_cells) A(v.cond_T0, v.n_cells) A(v.cond_p0, v.n_cells) A(v.stage, (size_t)5 * v.n_cells)
-  A(v.numconc, (size_t)v.n_cells * v.C) A(ctx->d_flag, 1)
+  A(v.numconc, (size_t)v.n_cells * v.C) A(ctx->d_flag, 1) A(v.work, 4) A(v.ideal_gc, (size_t)v.C * v.G)
   double *d_density, *d_kappa, *d_molw;
   int* d_nions;
   A(d_density, v.S) A(d_kappa, v.S) A(d_molw, v.S) A(d_nions, v.S)
@@ -114,6 +114,11 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
                                cudaMemcpyHostToDevice, ctx->stream));
   CUDA_OK(ctx, cudaMemcpyAsync(d_nions, cfg->num_ions ? cfg->num_ions : zi.data(), v.S * sizeof(int),
                                cudaMemcpyHostToDevice, ctx->stream));
+  {
+    std::vector<double> ideal((size_t)v.C * v.G, v.ideal);
+    CUDA_OK(ctx, cudaMemcpyAsync(v.ideal_gc, ideal.data(), ideal.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  }
   v.density = d_density;
   v.kappa = d_kappa;
   v.molw = d_molw;
@@ -396,6 +401,36 @@ extern "C" int pmcgpu_get_condense_stats(pmcgpu_ctx* ctx, int* stats) {
   if (!ctx || !stats) return PMCGPU_ERR_ARG;
   D2H_OPT(stats, ctx->v.cond_stats, (size_t)3 * ctx->v.n_cells, int)
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}
+// n_part_ideal(n_group, n_class) (aero_state.F90:241 sets every entry to n_part / (n_group n_class); a host
+// may give each (group, class) its own value): n_part_ideal[(class - 1) * n_group + (group - 1)]
+extern "C" int pmcgpu_set_n_part_ideal(pmcgpu_ctx* ctx, const double* n_part_ideal) {
+  if (!ctx || !n_part_ideal) return PMCGPU_ERR_ARG;
+  const size_t n = (size_t)ctx->v.C * ctx->v.G;
+  for (size_t q = 0; q < n; q++)
+    if (!(n_part_ideal[q] > 0.0)) return PMCGPU_ERR_ARG;
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->v.ideal_gc, n_part_ideal, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}
+extern "C" int pmcgpu_get_work(pmcgpu_ctx* ctx, unsigned long long* work, int reset) {
+  if (!ctx || !work) return PMCGPU_ERR_ARG;
+  CUDA_OK(ctx, cudaMemcpyAsync(work, ctx->v.work, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+  if (reset) CUDA_OK(ctx, cudaMemsetAsync(ctx->v.work, 0, 4 * sizeof(unsigned long long), ctx->stream));
+  CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}
+// particles at the start of a partmc_timestep: the unit of the benchmark's metric (particle-timesteps)
+__global__ void k_count_particles(DevView v) {
+  unsigned long long t = 0;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < v.n_cells; c += gridDim.x * blockDim.x) t += (unsigned)v.count[c];
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+  if ((threadIdx.x & 31) == 0 && t) atomicAdd(&v.work[2], t);
+}
+int pmc_count_particles_async(pmcgpu_ctx* ctx) {
+  k_count_particles<<<std::min((ctx->v.n_cells + 255) / 256, 296), 256, 0, ctx->stream>>>(ctx->v);
+  LAUNCH_CHECK(ctx);
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_coag_stats(pmcgpu_ctx* ctx, int* tot_n_samp, int* tot_n_coag) {

@@ -49,6 +49,7 @@ extern "C" int pmcgpu_comm_init(pmcgpu_ctx* ctx, const char* unique_id, int n_ra
     NCCL_OK(ctx, ncclCommInitRank(&comm, n_ranks, id, rank));
     ctx->nccl_comm = comm;
   }
+  ctx->tot_valid = false;  // the neighbours changed: the next C4 messages use the full slab pitch
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_comm_destroy(pmcgpu_ctx* ctx) {
@@ -93,48 +94,10 @@ int pmc_exchange(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], cons
   return PMCGPU_OK;
 }
 
-// the particle slabs: n_send[s] records leave through side s, n_recv[s] arrive on side s
-int pmc_exchange_slabs(pmcgpu_ctx* ctx, const int* n_send, const int* n_recv) {
-  const int S = ctx->v.S;
-  // species volumes are [S][cap] with different capacities used: move the used prefix of every species row
-  for (int pass = 0; pass < 7; pass++) {
-    void* sp[4]; void* rp[4]; size_t by[4];
-    if (pass == 0) {
-      // one exchange per species row keeps every message contiguous
-      for (int sp_i = 0; sp_i < S; sp_i++) {
-        for (int s = 0; s < 4; s++) {
-          sp[s] = ctx->sslab[s].vol + (size_t)sp_i * ctx->sslab[s].cap;
-          rp[s] = ctx->rslab[s].vol + (size_t)sp_i * ctx->rslab[s].cap;
-          by[s] = (size_t)n_send[s] * sizeof(double);
-        }
-        int rc = pmc_exchange_sized(ctx, sp, rp, by, n_recv, sizeof(double));
-        if (rc) return rc;
-      }
-      continue;
-    }
-    size_t esz = 0;
-    for (int s = 0; s < 4; s++) {
-      TrSlab& a = ctx->sslab[s];
-      TrSlab& b = ctx->rslab[s];
-      switch (pass) {
-        case 1: sp[s] = a.id; rp[s] = b.id; esz = sizeof(long long); break;
-        case 2: sp[s] = a.wgc; rp[s] = b.wgc; esz = sizeof(int); break;
-        case 3: sp[s] = a.nprim; rp[s] = b.nprim; esz = sizeof(int); break;
-        case 4: sp[s] = a.hyst; rp[s] = b.hyst; esz = sizeof(int); break;
-        case 5: sp[s] = a.lct; rp[s] = b.lct; esz = sizeof(double); break;
-        default: sp[s] = a.gct; rp[s] = b.gct; esz = sizeof(double); break;
-      }
-      by[s] = (size_t)n_send[s] * esz;
-    }
-    int rc = pmc_exchange_sized(ctx, sp, rp, by, n_recv, esz);
-    if (rc) return rc;
-  }
-  return PMCGPU_OK;
-}
-
-// like pmc_exchange, with the size of every incoming message given explicitly (n_recv[s] elements)
+// like pmc_exchange, with the size of every incoming message given explicitly: the C4 particle messages
+// (one per neighbour: header + SoA records, trans.cu)
 int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], const size_t send_bytes[4],
-                       const int* n_recv, size_t elem) {
+                       const size_t recv_bytes[4]) {
   cudaStream_t st = ctx->stream;
   bool any_remote = false;
   for (int s = 0; s < 4; s++) {
@@ -158,8 +121,8 @@ int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4]
   const int order[4] = {1, 0, 3, 2};
   for (int q = 0; q < 4; q++) {
     const int s = order[q];
-    if (ctx->nb[s] != ctx->rank && n_recv[s])
-      NCCL_OK(ctx, ncclRecv(recv[s], (size_t)n_recv[s] * elem, ncclChar, ctx->nb[s], comm, st));
+    if (ctx->nb[s] != ctx->rank && recv_bytes[s])
+      NCCL_OK(ctx, ncclRecv(recv[s], recv_bytes[s], ncclChar, ctx->nb[s], comm, st));
   }
   NCCL_OK(ctx, ncclGroupEnd());
   ctx->launches++;

@@ -91,10 +91,14 @@ int pmc_kernel_bounds_async(pmcgpu_ctx* ctx, int ktype) {
     return 200724934;
   }
   const size_t smem = (size_t)v.nbcap * 9 * 4 * sizeof(double);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  if (smem > 48 * 1024 && smem > ctx->cfg_kmax_smem) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_kernel_bounds, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+    ctx->cfg_kmax_smem = smem;
+  }
+  // the per-cell tables belong to one kernel type: a call with another type rebuilds every cell's table
+  if (ctx->kmax_ktype != ktype) {
+    CUDA_OK(ctx, cudaMemsetAsync(v.bounds_valid, 0, v.n_cells * sizeof(int), ctx->stream));
+    ctx->kmax_ktype = ktype;
   }
   {
     ProfScope ps_(ctx, "k_kernel_bounds");

@@ -72,7 +72,8 @@ struct DevView {
   // species table
   const double* density; const double* kappa; const double* molw; const int* nions;
   double dens_min, dens_max;
-  double ideal;       // n_part_ideal per (group, class)
+  double ideal;       // n_part_ideal per (group, class) when split evenly (pmcgpu_config)
+  double* ideal_gc;   // [C][G] n_part_ideal(group, class) (aero_state.F90:241, pmcgpu_set_n_part_ideal)
   // coagulation work space
   int* L;             // [n_cells][3*cap] list arena
   int* fidx;          // [n_cells*cap] position of particle in its (bin, class) list
@@ -91,6 +92,10 @@ struct DevView {
   double* cond_p0;
   double* stage;      // [5][n_cells] H2D staging of wrf_to_partmc outputs
   float* numconc;     // [n_cells][C] partmc_to_wrf output
+  // work counters (pmcgpu_get_work): [0] particle rate evaluations of condense_particles (rate evaluations x
+  // particles of the cell, summed over cells and calls), [1] particles condense_particles integrated,
+  // [2] particles at the start of partmc_timestep (particle-timesteps), [3] spare
+  unsigned long long* work;
 };
 
 // Transport work space of one patch (trans.cu).  "ext" arrays carry a one-cell ghost ring in x and y:
@@ -150,8 +155,22 @@ struct pmcgpu_ctx {
   // transport
   TransView t;
   bool trans_ready = false;
-  TrSlab sslab[4], rslab[4];
-  int* h_tot = nullptr;  // pinned: particles sent / received per side
+  // C4 ghost particles: ONE contiguous message per side = int header (offsets of the side's ghost cells in the
+  // slab, last entry = record count) followed by the SoA record arrays with row pitch `pitch`
+  // ([S] vol rows, id, lct, gct: 8 bytes; wgc, nprim, hyst: 4 bytes).  The pitch of a step is derived from the
+  // counts of the PREVIOUS step (both ends of a link know them: the sender its own count, the receiver the
+  // count in the header it received), so no host read of device counts sits inside a transport step.
+  char* smsg[4] = {nullptr, nullptr, nullptr, nullptr};
+  char* rmsg[4] = {nullptr, nullptr, nullptr, nullptr};
+  int slab_cap[4] = {0, 0, 0, 0};   // largest pitch the buffers hold
+  int hdr_ints[4] = {0, 0, 0, 0};   // header length (multiple of 4 ints)
+  int* h_tot = nullptr;             // pinned: records sent [0..3] / received [4..7] per side in the last step
+  cudaEvent_t ev_tot = nullptr;     // completion of the copy into h_tot
+  bool tot_valid = false;           // h_tot holds the counts of the previous step
+  bool cfg_trans_smem = false, cfg_cond = false, cfg_cond_grid = false, cfg_sort = false;  // per-context (= per-device) opt-ins
+  int cond_n_sm = 0, cond_max_blk4 = 0, cond_max_blk8 = 0;
+  size_t cfg_msamp_smem = 0, cfg_kmax_smem = 0, cfg_sort_smem = 0, cfg_sort_staged_smem = 0;
+  int kmax_ktype = 0;               // kernel type the per-cell majorant tables were built for
   // patch neighbours (rank of the patch on side s; this rank itself on a periodic single patch)
   int rank = 0, n_ranks = 1, px = 1, py = 1;
   int nb[4] = {0, 0, 0, 0};
@@ -162,9 +181,23 @@ struct pmcgpu_ctx {
   unsigned rng_step = 0;     // step number addressing the draws of the stand-alone condensation calls (pmcgpu_set_rng_step)
   bool any_nonflat = false;  // some weight is size dependent (set by pmcgpu_set_weights): aero_state_reweight is not the identity
 };
-int pmc_exchange_slabs(pmcgpu_ctx* ctx, const int* n_send, const int* n_recv);
 int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], const size_t send_bytes[4],
-                       const int* n_recv, size_t elem);
+                       const size_t recv_bytes[4]);
+// bytes of one record in a C4 message and the SoA view of a message buffer with row pitch `pitch`
+static inline size_t tr_rec_bytes(int S) { return (size_t)8 * S + 8 * 3 + 4 * 3; }
+static inline TrSlab tr_slab_view(char* msg, int hdr_ints, int pitch, int S) {
+  TrSlab s;
+  s.cap = pitch;
+  char* p = msg + (size_t)hdr_ints * sizeof(int);
+  s.vol = (double*)p;       p += (size_t)8 * S * pitch;
+  s.id = (long long*)p;     p += (size_t)8 * pitch;
+  s.lct = (double*)p;       p += (size_t)8 * pitch;
+  s.gct = (double*)p;       p += (size_t)8 * pitch;
+  s.wgc = (int*)p;          p += (size_t)4 * pitch;
+  s.nprim = (int*)p;        p += (size_t)4 * pitch;
+  s.hyst = (int*)p;
+  return s;
+}
 
 #define CUDA_OK(ctx, call)                                                              \
   do {                                                                                  \

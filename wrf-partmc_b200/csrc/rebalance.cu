@@ -29,12 +29,12 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_rebalance(DevView v, int all
   int n_part = v.count[cell];
   int err = 0;
   int* map = v.L + (size_t)cell * 3 * v.cap;  // scratch: current slot -> original slot
-  const double ideal = v.ideal;
 
   if (allow_doubling) {
     for (int g = 1; g <= v.G && !err; g++)
       for (int c = 1; c <= v.C && !err; c++) {
         const int gc = (c - 1) * v.G + (g - 1);
+        const double ideal = v.ideal_gc[gc];
         for (;;) {
           int m = 0;
           for (int p = lane; p < n_part; p += 32) m += (v.wgc[base + p] == gc);
@@ -78,6 +78,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_rebalance(DevView v, int all
     for (int g = 1; g <= v.G; g++)
       for (int c = 1; c <= v.C; c++) {
         const int gc = (c - 1) * v.G + (g - 1);
+        const double ideal = v.ideal_gc[gc];
         unsigned pass = 0;
         for (;;) {
           int m = 0;
@@ -444,7 +445,6 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
   const size_t NS = (size_t)v.n_cells * v.cap;
   const unsigned gcell = (unsigned)v.gcell[cell];
   const double sample_prop = e.sample_prop[cell];
-  const double ideal = v.ideal;
   int n_add = 0, err = 0;
   for (int g = 1; g <= v.G && !err; g++)
     for (int im = 1; im <= e.n_mode && !err; im++) {
@@ -453,6 +453,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
       const double mode_nc = e.num_conc[(size_t)cell * e.n_mode + (im - 1)];
       const unsigned a = (unsigned)((g - 1) * e.n_mode + (im - 1));
       const int gc = (c - 1) * v.G + (g - 1);
+      const double ideal = v.ideal_gc[gc];
       const size_t wi = (size_t)cell * v.C * v.G + gc;
       if (type == 2 && v.wtype[wi] != PMCGPU_WEIGHT_NONE) {
         err = PMCGPU_ERR_ARG;  // "cannot use exponential modes with weighting"

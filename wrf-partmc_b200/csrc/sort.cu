@@ -408,18 +408,17 @@ int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck) {
     ctx->err = "sort: n_class * max_bins too large for the shared-memory histogram";
     return PMCGPU_ERR_ARG;
   }
-  static size_t configured = 0, configured_staged = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  if (smem > 48 * 1024 && smem > ctx->cfg_sort_smem) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_sort_cells<false, SORT_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)smem));
-    configured = smem;
+    ctx->cfg_sort_smem = smem;
   }
   size_t smem_staged = 0;
   const int n_split = sort_staged_limit(v, &smem_staged);
-  if (n_split > 0 && smem_staged > 48 * 1024 && smem_staged > configured_staged) {
+  if (n_split > 0 && smem_staged > 48 * 1024 && smem_staged > ctx->cfg_sort_staged_smem) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_sort_cells<true, SORT_THREADS_STAGED>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_staged));
-    configured_staged = smem_staged;
+    ctx->cfg_sort_staged_smem = smem_staged;
   }
   {
     ProfScope ps_(ctx, "k_sort_cells");

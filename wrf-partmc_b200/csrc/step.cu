@@ -21,6 +21,7 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
 int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step);
 int pmc_update_density_async(pmcgpu_ctx* ctx, const double* d_new_rrho);
 int pmc_num_conc_async(pmcgpu_ctx* ctx, float* d_out);
+int pmc_count_particles_async(pmcgpu_ctx* ctx);
 
 extern "C" int pmcgpu_partmc_timestep(pmcgpu_ctx* ctx, const pmcgpu_timestep_args* a) {
   if (!ctx || !a) return PMCGPU_ERR_ARG;
@@ -37,11 +38,15 @@ extern "C" int pmcgpu_partmc_timestep(pmcgpu_ctx* ctx, const pmcgpu_timestep_arg
   }
   if (a->temp) CUDA_OK(ctx, cudaMemcpyAsync(v.temp, a->temp, nb, cudaMemcpyDefault, st));
   if (a->pressure) CUDA_OK(ctx, cudaMemcpyAsync(v.pres, a->pressure, nb, cudaMemcpyDefault, st));
-  if (a->rel_humid) CUDA_OK(ctx, cudaMemcpyAsync(v.rh, a->rel_humid, nb, cudaMemcpyDefault, st));
+  // condense_particles starts from env_state_initial%rel_humid (condense.F90:237), i.e. from old_env_states
+  // (the copy made before wrf_to_partmc refreshes rel_humid, wrf_pmc_driver.F90:615-624), and overwrites the
+  // final state's rel_humid (condense.F90:263): WRF's new value only takes effect in steps without condensation
+  if (a->rel_humid && !cond) CUDA_OK(ctx, cudaMemcpyAsync(v.rh, a->rel_humid, nb, cudaMemcpyDefault, st));
   if (a->cell_volume) CUDA_OK(ctx, cudaMemcpyAsync(v.cellvol, a->cell_volume, nb, cudaMemcpyDefault, st));
   if (a->inverse_density)
     CUDA_OK(ctx, cudaMemcpyAsync(v.stage, a->inverse_density, nb, cudaMemcpyDefault, st));
   int rc;
+  if ((rc = pmc_count_particles_async(ctx))) return rc;
   // ---- mc_coag
   if (chem && a->do_coagulation) {
     if ((rc = pmc_sort_async(ctx, 1))) return rc;

@@ -344,8 +344,9 @@ __global__ void k_tr_preweight(DevView v, TransView t) {
   const double mag = v.wmag[wi];
   const double n_parts_new = acc / mag;
   double ratio = 0.0, new_mag = mag;
-  if (n_parts_new > 2.0 * v.ideal) {
-    ratio = n_parts_new / v.ideal;  // weight_ratio; aero_state_scale_weight, ratio > 1 branch
+  const double ideal = v.ideal_gc[c * v.G];  // group 1
+  if (n_parts_new > 2.0 * ideal) {
+    ratio = n_parts_new / ideal;  // weight_ratio; aero_state_scale_weight, ratio > 1 branch
     new_mag = mag * ratio;
     v.wmag[wi] = new_mag;
   }
@@ -643,7 +644,7 @@ __global__ void k_tr_pack_copy(DevView v, TransView t, int side, const int* __re
   const int nd = TR_ND(t.nz);
   const size_t base = (size_t)cell * v.cap, NS = (size_t)v.n_cells * v.cap;
   int o = off[q];
-  if (off[q + 1] > slab.cap) {
+  if (off[q + 1] > slab.cap) {  // beyond the pitch of this message: reported, the receiver skips the cell too
     if (threadIdx.x == 0 && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_CAPACITY;
     return;
   }
@@ -669,7 +670,8 @@ __global__ void k_tr_pack_copy(DevView v, TransView t, int side, const int* __re
 // ---- add the arrivals (:777-804 aero_state_add_particles): every destination cell pulls survivors and
 // arrivals into the alternate slab.  Arrival order = the order in which the reference's loops append to
 // delta_aero_states(dest): local sources in (j, k, i) order, then the four ghost receives.
-#define TR_MAXSEG 160
+// candidate segments of one destination cell: survivors, (nz + 3) source cells x C classes, four ghost sides
+static inline __host__ __device__ int tr_n_cand(int nz, int C) { return 1 + (nz + 3) * C + 4; }
 // one particle's species rows from one slab to another (the slabs never overlap): loads in batches of eight
 // ahead of the stores
 __device__ __forceinline__ void tr_copy_rows(double* __restrict__ dst, size_t dstride, const double* __restrict__ src,
@@ -693,8 +695,8 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
   const int cell = blockIdx.x;
   const int nx = t.nx, nz = t.nz, ny = t.ny, nd = TR_ND(t.nz);
   const int i = cell % nx, k = (cell / nx) % nz, j = cell / (nx * nz);
-  __shared__ TrSeg seg[TR_MAXSEG];
-  __shared__ int s_nseg, s_total, s_fail;
+  extern __shared__ TrSeg seg[];  // [tr_n_cand(nz, C)]
+  __shared__ int s_nseg, s_total;
   if (threadIdx.x < 32) {
     // Candidate segments in arrival order: e = 0 the survivors, then (source cell, class) pairs of the local
     // sources, then the four ghost receives.  Lanes read the candidates of a round side by side; the
@@ -704,6 +706,7 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
     const int n_src = nz + 3;  // y-, below (k), x-, x+, above (nz-1-k), y+
     const int n_cand = 1 + n_src * C + 4;
     int ns = 0, tot = 0, fail = 0;
+    const int cap = v.cap;
     for (int e0 = 0; e0 < n_cand; e0 += 32) {
       const int e = e0 + lane;
       int kind = 0, src = 0, off = 0, cnt = 0;
@@ -731,32 +734,38 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
         if (ok) {
           const int q = (side < 2) ? (k * nx + i) : (j * nz + k);
           kind = 2; src = side; off = t.roff[side][q]; cnt = t.roff[side][q + 1] - off;
+          const int pitch = (side == 0) ? r0.cap : (side == 1 ? r1.cap : (side == 2 ? r2.cap : r3.cap));
+          if (off + cnt > pitch) { cnt = 0; fail = 1; }  // the sender could not pack this cell (message pitch)
         }
       }
+      // a cell that would outgrow its slab keeps what fits (survivors first, then arrivals in order) and is
+      // reported: the device state stays consistent (count = records written)
+      int incl = cnt;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      const int room = cap - tot - (incl - cnt);
+      if (cnt > room) { cnt = room > 0 ? room : 0; fail = 1; }
       const bool have = cnt > 0;
       const unsigned m = __ballot_sync(0xffffffffu, have);
       const int pos = ns + __popc(m & ((1u << lane) - 1u));
       if (have) {
-        if (pos < TR_MAXSEG) {
-          seg[pos].kind = kind; seg[pos].src = src; seg[pos].off = off; seg[pos].n = cnt;
-        }
+        seg[pos].kind = kind; seg[pos].src = src; seg[pos].off = off; seg[pos].n = cnt;
       }
       int csum = have ? cnt : 0;
       for (int o = 16; o > 0; o >>= 1) csum += __shfl_xor_sync(0xffffffffu, csum, o);
       tot += csum;
       ns += __popc(m);
     }
-    if (ns > TR_MAXSEG) fail = 1;
-    if (tot > v.cap) fail = 2;
+    fail = __any_sync(0xffffffffu, fail);
     if (lane == 0) {
       s_nseg = ns;
       s_total = tot;
-      s_fail = fail;
       if (fail && v.status[cell] == 0) v.status[cell] = PMCGPU_ERR_CAPACITY;
     }
   }
   __syncthreads();
-  if (s_fail) return;
   const size_t NS = (size_t)v.n_cells * v.cap;
   const size_t dbase = (size_t)cell * v.cap;
   const int total = s_total, nseg = s_nseg;
@@ -823,19 +832,6 @@ static int tr_alloc(pmcgpu_ctx* ctx, T** p, size_t n) {
   *p = (T*)q;
   return 0;
 }
-static int slab_alloc(pmcgpu_ctx* ctx, TrSlab& s, int cap, int S) {
-  s.cap = cap;
-  int rc;
-  if ((rc = tr_alloc(ctx, &s.vol, (size_t)cap * S))) return rc;
-  if ((rc = tr_alloc(ctx, &s.id, cap))) return rc;
-  if ((rc = tr_alloc(ctx, &s.wgc, cap))) return rc;
-  if ((rc = tr_alloc(ctx, &s.nprim, cap))) return rc;
-  if ((rc = tr_alloc(ctx, &s.hyst, cap))) return rc;
-  if ((rc = tr_alloc(ctx, &s.lct, cap))) return rc;
-  if ((rc = tr_alloc(ctx, &s.gct, cap))) return rc;
-  return 0;
-}
-
 // allocate the transport work space on first use
 static int tr_setup(pmcgpu_ctx* ctx) {
   if (ctx->trans_ready) return PMCGPU_OK;
@@ -852,6 +848,10 @@ static int tr_setup(pmcgpu_ctx* ctx) {
     return PMCGPU_ERR_ARG;
   }
   if (t.nz < 2 || t.nz > 60 || v.C > 127) return PMCGPU_ERR_ARG;
+  if ((size_t)tr_n_cand(t.nz, v.C) * sizeof(TrSeg) > 160 * 1024) {
+    ctx->err = "transport: (nz + 3) * n_class + 5 arrival segments per cell exceed the shared memory of k_tr_gather";
+    return PMCGPU_ERR_ARG;
+  }
   const size_t nc = v.n_cells, C = v.C, nz = t.nz, nx = t.nx, ny = t.ny;
   const size_t n_ext = (nx + 2) * nz * (ny + 2);
   const int nd = TR_ND(t.nz);
@@ -866,16 +866,23 @@ static int tr_setup(pmcgpu_ctx* ctx) {
   for (int s = 0; s < 4; s++) {
     const size_t L = (s < 2) ? nx : ny;
     TA(t.sbuf[s], L * nz * C) TA(t.rbuf[s], L * nz * C)
-    TA(t.scnt[s], L * nz + 1) TA(t.soff[s], L * nz + 1) TA(t.roff[s], L * nz + 1)
-    // a quarter of the slots of every edge cell may cross one side in one step
-    const int slab_cap = (int)std::min<size_t>((size_t)L * nz * (size_t)std::max(v.cap / 4, 64), (size_t)1 << 30);
-    if ((rc = slab_alloc(ctx, ctx->sslab[s], slab_cap, v.S))) return rc;
-    if ((rc = slab_alloc(ctx, ctx->rslab[s], slab_cap, v.S))) return rc;
+    TA(t.scnt[s], L * nz + 1)
+    // a quarter of the slots of every edge cell may cross one side in one step (pitch: a multiple of 4 records)
+    int slab_cap = (int)std::min<size_t>(((size_t)L * nz * (size_t)std::max(v.cap / 4, 64) + 3) & ~(size_t)3, (size_t)1 << 30);
+    if (const char* e = getenv("PMCGPU_HALO_SLAB_CAP")) slab_cap = std::max(4, atoi(e) & ~3);  // tests: force an overflow
+    ctx->slab_cap[s] = slab_cap;
+    ctx->hdr_ints[s] = (int)((L * nz + 1 + 3) & ~(size_t)3);
+    const size_t bytes = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)slab_cap * tr_rec_bytes(v.S);
+    TA(ctx->smsg[s], bytes) TA(ctx->rmsg[s], bytes)
+    t.soff[s] = (int*)ctx->smsg[s];  // the offsets travel as the header of the particle message
+    t.roff[s] = (int*)ctx->rmsg[s];
   }
 #undef TA
   t.out_slot = v.fidx;                // free outside mc_coag
   t.out_newid = (long long*)v.lnr;    // free outside aero_state_sort
   CUDA_OK(ctx, cudaMallocHost((void**)&ctx->h_tot, 8 * sizeof(int)));
+  CUDA_OK(ctx, cudaEventCreateWithFlags(&ctx->ev_tot, cudaEventDisableTiming));
+  ctx->tot_valid = false;
   ctx->trans_ready = true;
   return PMCGPU_OK;
 }
@@ -954,7 +961,6 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
   {
     ProfScope ps_(ctx, "k_tr_multisample");
     const int nd = TR_ND(t.nz);
-    static size_t configured = 0;
     // small cells (at most half the slab capacity) first, then the rest
     const int lsmall = (v.cap > 512) ? ((v.cap / 2 + 1) & ~1) : v.cap;
     for (int pass = 0; pass < 2; pass++) {
@@ -972,48 +978,65 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
       }
       // the sorted probabilities (doubles) start behind the int regions of all warps
       const size_t smem_total = (size_t)wpc * per_warp_i * sizeof(int) + (size_t)wpc * nd * sizeof(double);
-      if (smem_total > 48 * 1024 && smem_total > configured) {
+      if (smem_total > 48 * 1024 && smem_total > ctx->cfg_msamp_smem) {
         CUDA_OK(ctx, cudaFuncSetAttribute(k_tr_multisample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total));
-        configured = smem_total;
+        ctx->cfg_msamp_smem = smem_total;
       }
       k_tr_multisample<<<(unsigned)((nc + wpc - 1) / wpc), wpc * 32, smem_total, st>>>(v, t, a->step, wpc, lcap, n_lo,
                                                                                        n_hi);
       LAUNCH_CHECK(ctx);
     }
   }
-  // ---- C4: ghost particles
+  // ---- C4: ghost particles: one message per neighbour (header with the per-cell offsets + SoA records), its
+  // row pitch derived from the counts of the previous step, so the host never waits for this step's counts
+  TrSlab rview[4];
   {
     ProfScope ps_(ctx, "k_tr_halo_particles");
-    void* sp[4]; void* rp[4]; size_t by[4];
+    int pitch_s[4], pitch_r[4];
+    if (ctx->tot_valid) CUDA_OK(ctx, cudaEventSynchronize(ctx->ev_tot));  // recorded a whole step ago
+    for (int s = 0; s < 4; s++) {
+      auto pitch_of = [&](int n_prev) {
+        if (!ctx->tot_valid || n_prev < 0) return ctx->slab_cap[s];
+        const long long want = ((long long)n_prev + n_prev / 2 + 2048 + 255) & ~255ll;
+        return (int)std::min<long long>(want, ctx->slab_cap[s]);
+      };
+      pitch_s[s] = pitch_of(ctx->h_tot[s]);
+      pitch_r[s] = pitch_of(ctx->h_tot[4 + s]);
+    }
+    void* sp[4]; void* rp[4]; size_t sby[4], rby[4];
     for (int s = 0; s < 4; s++) {
       const size_t L = (s < 2) ? nx : ny;
       k_tr_pack_count<<<blocks(L * nz), TB, 0, st>>>(v, t, s, t.scnt[s]);
       LAUNCH_CHECK(ctx);
       k_tr_scan<<<1, 1024, 0, st>>>((int)(L * nz), t.scnt[s], t.soff[s]);
       LAUNCH_CHECK(ctx);
-      k_tr_pack_copy<<<(unsigned)(L * nz), 128, 0, st>>>(v, t, s, t.soff[s], ctx->sslab[s]);
+      k_tr_pack_copy<<<(unsigned)(L * nz), 128, 0, st>>>(v, t, s, t.soff[s],
+                                                         tr_slab_view(ctx->smsg[s], ctx->hdr_ints[s], pitch_s[s], v.S));
       LAUNCH_CHECK(ctx);
-      sp[s] = t.soff[s]; rp[s] = t.roff[s]; by[s] = (L * nz + 1) * sizeof(int);
+      sp[s] = ctx->smsg[s]; rp[s] = ctx->rmsg[s];
+      sby[s] = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)pitch_s[s] * tr_rec_bytes(v.S);
+      rby[s] = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)pitch_r[s] * tr_rec_bytes(v.S);
+      rview[s] = tr_slab_view(ctx->rmsg[s], ctx->hdr_ints[s], pitch_r[s], v.S);
     }
-    if ((rc = pmc_exchange(ctx, sp, rp, by))) return rc;
-    // message sizes: totals of what is sent and of what arrives
+    if ((rc = pmc_exchange_sized(ctx, sp, rp, sby, rby))) return rc;
+    // the counts of this step size the messages of the next one
     for (int s = 0; s < 4; s++) {
       const size_t L = (s < 2) ? nx : ny;
       CUDA_OK(ctx, cudaMemcpyAsync(ctx->h_tot + s, t.soff[s] + L * nz, sizeof(int), cudaMemcpyDeviceToHost, st));
       CUDA_OK(ctx, cudaMemcpyAsync(ctx->h_tot + 4 + s, t.roff[s] + L * nz, sizeof(int), cudaMemcpyDeviceToHost, st));
     }
-    CUDA_OK(ctx, cudaStreamSynchronize(st));
-    for (int s = 0; s < 4; s++)
-      if (ctx->h_tot[s] > ctx->sslab[s].cap || ctx->h_tot[4 + s] > ctx->rslab[s].cap) {
-        ctx->err = "transport: more particles cross a patch side than the halo slab holds";
-        return PMCGPU_ERR_CAPACITY;
-      }
-    if ((rc = pmc_exchange_slabs(ctx, ctx->h_tot, ctx->h_tot + 4))) return rc;
+    CUDA_OK(ctx, cudaEventRecord(ctx->ev_tot, st));
+    ctx->tot_valid = true;
   }
   // ---- add + rebalance + sort
   {
     ProfScope ps_(ctx, "k_tr_gather");
-    k_tr_gather<<<(unsigned)nc, 128, 0, st>>>(v, t, ctx->rslab[0], ctx->rslab[1], ctx->rslab[2], ctx->rslab[3]);
+    const size_t seg_bytes = (size_t)tr_n_cand(t.nz, v.C) * sizeof(TrSeg);
+    if (seg_bytes > 40 * 1024 && !ctx->cfg_trans_smem) {
+      CUDA_OK(ctx, cudaFuncSetAttribute(k_tr_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seg_bytes));
+      ctx->cfg_trans_smem = true;
+    }
+    k_tr_gather<<<(unsigned)nc, 128, (size_t)tr_n_cand(t.nz, v.C) * sizeof(TrSeg), st>>>(v, t, rview[0], rview[1], rview[2], rview[3]);
     LAUNCH_CHECK(ctx);
     pmc_swap_slabs(ctx);
   }

@@ -401,6 +401,15 @@ class PartMCGPU:
         self._chk(self.L.pmcgpu_comm_init(self.h, unique_id, C.c_int(n_ranks), C.c_int(rank), C.c_int(px),
                                           C.c_int(py)))
 
+    def comm_destroy(self):
+        self._chk(self.L.pmcgpu_comm_destroy(self.h))
+
+    def set_n_part_ideal(self, n_part_ideal):
+        """n_part_ideal(group, class) (aero_state.F90:81): [n_class][n_group]"""
+        a = _f64(n_part_ideal)
+        assert a.size == self.n_class * self.n_group
+        self._chk(self.L.pmcgpu_set_n_part_ideal(self.h, _p(a)))
+
     def check_status(self):
         self._chk(self.L.pmcgpu_check_status(self.h))
 
@@ -433,6 +442,13 @@ class PartMCGPU:
         a, b = np.zeros(self.n_cells, np.int32), np.zeros(self.n_cells, np.int32)
         self._chk(self.L.pmcgpu_get_coag_stats(self.h, _p(a), _p(b)))
         return a, b
+
+    def work(self, reset=False):
+        """device work counters since the last reset: dict(cond_rate_evals = rate evaluations x particles of
+        condense_particles, cond_particles, particle_timesteps)"""
+        w = np.zeros(4, np.uint64)
+        self._chk(self.L.pmcgpu_get_work(self.h, _p(w), C.c_int(1 if reset else 0)))
+        return dict(cond_rate_evals=int(w[0]), cond_particles=int(w[1]), particle_timesteps=int(w[2]))
 
     def update_density(self, new_inverse_density):
         a = _f64(new_inverse_density)
