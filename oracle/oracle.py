@@ -318,6 +318,14 @@ def condense_rates(inputs):
     return out
 
 
+def condense_rates_dt(inputs):
+    """time derivatives of condense_rates at fixed (D, H): [n][3] = dDdot/dt, dHdot_i/dt, dHdot_env/dt"""
+    a = _f64(inputs).reshape(-1, 9)
+    out = np.zeros((a.shape[0], 3))
+    lib().pmco_condense_rates_dt(C.c_int(a.shape[0]), _p(a, C.c_double), _p(out, C.c_double))
+    return out
+
+
 def condense_integrate(D, H, D_dry, kappa, num_conc, T0, p0, Tdot, pdot, del_t, reltol=1e-8, abstol_scale=1e-8,
                        abstol_H=1e-10, h_init=0.0, method=4):
     D = _f64(D).copy()

@@ -81,6 +81,68 @@ void condense_rates(const CondenseRatesInputs& in, CondenseRatesOutputs& out) {
   out.dHdoti_dH = -2.0 * Const::pi / (V * in.V_comp) * (in.D * in.D) * out.dDdot_dH;
 }
 
+// Partial derivatives with respect to TIME of the outputs of condense_rates at fixed (D, H): T = T0 + t Tdot and
+// p = p0 + t pdot enter through the cell-level terms k_a, D_v, U, V, W, X, Y, Z (condense.F90:391-416), V_comp
+// through (T p0) / (T0 p).  delta* is defined implicitly by h(delta*; T, p) = 0 (:449-466), so
+// d delta* / dt = -(dh/dt) / (dh/ddelta).  Not a reference routine: the Rosenbrock integrator needs df/dt of the
+// non-autonomous system; the reference's CVODE does not.  Checked against a central difference of
+// condense_rates in tests/test_oracle_condense.py.
+void condense_rates_dt(const CondenseRatesInputs& in, double& dDdot_dt, double& dHdoti_dt, double& dHdotenv_dt) {
+  const double rho_w = Const::water_density;
+  const double M_w = Const::water_molec_weight;
+  const double T = in.T, p = in.p;
+  const double P_0 = Const::water_eq_vap_press * std::pow(10.0, 7.45 * (T - Const::water_freeze_temp) / (T - 38.0));
+  const double dP0_dT_div_P0 = 7.45 * std::log(10.0) * (Const::water_freeze_temp - 38.0) / ((T - 38.0) * (T - 38.0));
+  const double rho_air = Const::air_molec_weight * p / (Const::univ_gas_const * T);
+  const double k_a = 1e-3 * (4.39 + 0.071 * T);
+  const double D_v = 0.211e-4 / (p / Const::air_std_press) * std::pow(T / 273.0, 1.94);
+  const double U = Const::water_latent_heat * rho_w / (4.0 * T);
+  const double V = 4.0 * M_w * P_0 / (rho_w * Const::univ_gas_const * T);
+  const double W = Const::water_latent_heat * M_w / (Const::univ_gas_const * T);
+  const double X = 4.0 * M_w * Const::water_surf_eng / (Const::univ_gas_const * T * rho_w);
+  const double Y = 2.0 * k_a / (Const::accom_coeff * rho_air * Const::air_spec_heat) *
+                   std::sqrt(2.0 * Const::pi * Const::air_molec_weight / (Const::univ_gas_const * T));
+  const double Z = 2.0 * D_v / Const::accom_coeff * std::sqrt(2.0 * Const::pi * M_w / (Const::univ_gas_const * T));
+  // logarithmic time derivatives of the cell-level terms
+  const double lT = in.Tdot / T, lp = in.pdot / p;
+  const double ka_t = 1e-3 * 0.071 * in.Tdot;
+  const double lDv = 1.94 * lT - lp;
+  const double lU = -lT;
+  const double lV = dP0_dT_div_P0 * in.Tdot - lT;
+  const double W_t = -W * lT, X_t = -X * lT;
+  const double Y_t = Y * (ka_t / k_a + 0.5 * lT - lp);
+  const double Z_t = Z * (lDv - 0.5 * lT);
+  const double lG = -(lV + lT - lp);  // G = -2 pi / (V V_comp), V_comp ~ T / p
+  dHdotenv_dt = 2.0 * dP0_dT_div_P0 / (T - 38.0) * in.Tdot * in.Tdot * in.H - in.H * lp * lp;
+  const double G = -2.0 * Const::pi / (V * in.V_comp);
+  if (in.D <= in.D_dry) {
+    const double D_vp = D_v / (1.0 + Z / in.D_dry);
+    const double Ddot = V * D_vp * in.H / in.D_dry;
+    dDdot_dt = Ddot * (lV + lDv - Z_t / (in.D_dry + Z));
+    dHdoti_dt = G * (in.D_dry * in.D_dry) * (Ddot * lG + dDdot_dt);
+    return;
+  }
+  CondenseRatesOutputs out{};
+  condense_rates(in, out);
+  const double D = in.D;
+  const double D3 = D * D * D, Dd3 = in.D_dry * in.D_dry * in.D_dry;
+  const double k_ap = k_a / (1.0 + Y / D);
+  const double D_vp = D_v / (1.0 + Z / D);
+  const double a_w = (D3 - Dd3) / (D3 + (in.kappa - 1.0) * Dd3);
+  const double delta = out.Ddot * (U * D) / k_ap;
+  const double q = 1.0 / (1.0 + delta);
+  const double E = std::exp((W * delta + X / D) * q);
+  const double UVD = U * V * D_vp;
+  const double kap_t = k_ap * (ka_t / k_a - Y_t / (D + Y));
+  const double UVD_t = UVD * (lU + lV + lDv - Z_t / (D + Z));
+  const double E_t = E * q * (W_t * delta + X_t / D);
+  const double h_t = kap_t * delta - UVD_t * (in.H - a_w * q * E) + UVD * a_w * q * E_t;
+  const double dh_ddelta = k_ap - UVD * a_w * (q * q) * (1.0 - W * q + (X / D) * q) * E;
+  const double delta_t = -h_t / dh_ddelta;
+  dDdot_dt = out.Ddot * (kap_t / k_ap - lU) + k_ap * delta_t / (U * D);
+  dHdoti_dt = G * (D * D) * (out.Ddot * lG + dDdot_dt);
+}
+
 // condense.F90:701-739
 void condense_equilib_particle(const EnvState& env, const AeroData& d, Particle& p) {
   const double X = 4.0 * Const::water_molec_weight * Const::water_surf_eng /
@@ -116,7 +178,7 @@ struct CondSys {
   double T0, p0, Tdot, pdot;
   // f and the arrow-head Jacobian at (t, D, H): condense_vf_f / condense_jac (condense.F90:509-616)
   void eval(double t, const double* D, double H, double* fD, double& fH, double* a, double* b, double* c, double& dd,
-            int& n_rates, bool jac) const {
+            int& n_rates, bool jac, double* dfdt = nullptr, double* dfdtH = nullptr) const {
     CondenseRatesInputs in;
     CondenseRatesOutputs out{};
     in.T = T0 + t * Tdot;
@@ -124,7 +186,7 @@ struct CondSys {
     in.Tdot = Tdot;
     in.pdot = pdot;
     in.H = H;
-    double Hdot = 0.0, dHdot_dH = 0.0;
+    double Hdot = 0.0, dHdot_dH = 0.0, Hdot_t = 0.0, env_t = 0.0;
     for (int i = 0; i < n; i++) {
       in.D = D[i];
       in.D_dry = D_dry[i];
@@ -133,6 +195,11 @@ struct CondSys {
       condense_rates(in, out);
       fD[i] = out.Ddot;
       Hdot += out.Hdot_i;
+      if (dfdt) {  // analytic df/dt at fixed (D, H) for the Rosenbrock stages
+        double hi_t;
+        condense_rates_dt(in, dfdt[i], hi_t, env_t);
+        Hdot_t += hi_t;
+      }
       if (jac) {
         a[i] = out.dDdot_dD;
         b[i] = out.dDdot_dH;
@@ -146,9 +213,14 @@ struct CondSys {
       in.V_comp = 1.0;
       in.kappa = 0.0;
       condense_rates(in, out);
+      if (dfdt) {
+        double d0, h0;
+        condense_rates_dt(in, d0, h0, env_t);
+      }
     }
     n_rates += n;
     fH = Hdot + out.Hdot_env;
+    if (dfdtH) *dfdtH = Hdot_t + env_t;
     if (jac) dd = dHdot_dH + out.dHdotenv_dH;  // (an empty cell has no arrays but still has dH'/dH)
   }
 };
@@ -625,10 +697,9 @@ int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const
     return condense_integrate_bdf(n, D, Hio, D_dry, kappa, num_conc, T0, p0, Tdot, pdot, del_t, opt, stats);
   const RosTableau tb = (opt.method == 4) ? tableau_rodas4() : tableau_rodas3();
   const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.95, FAC_REJ = 0.1;
-  const double DT_FD = 1e-2;  // forward difference in t for df/dt (T and p are linear in t)
   CondSys sys{n, D_dry, kappa, num_conc, T0, p0, Tdot, pdot};
   const int S = tb.S;
-  std::vector<double> atol((size_t)n), f0((size_t)n), ft((size_t)n), a((size_t)n), b((size_t)n), c((size_t)n),
+  std::vector<double> atol((size_t)n), f0((size_t)n), a((size_t)n), b((size_t)n), c((size_t)n),
       y((size_t)n), fs((size_t)n), dfdt((size_t)n), r((size_t)n);
   std::vector<std::vector<double>> K((size_t)S, std::vector<double>((size_t)n));
   double KH[6];
@@ -641,11 +712,9 @@ int condense_integrate(int n, double* D, double* Hio, const double* D_dry, const
   bool reject_last = false, reject_more = false;
   while (t < del_t) {
     if (stats.n_steps + stats.n_reject >= opt.max_steps) return 6;  // PMC_CONDENSE_SOLVER_SET_MAX_STEPS-like
-    double f0H, ftH, dd, dummy;
-    sys.eval(t, D, H, f0.data(), f0H, a.data(), b.data(), c.data(), dd, stats.n_rates, true);
-    sys.eval(t + DT_FD, D, H, ft.data(), ftH, nullptr, nullptr, nullptr, dummy, stats.n_rates, false);
-    for (int i = 0; i < n; i++) dfdt[i] = (ft[i] - f0[i]) / DT_FD;
-    const double dfdtH = (ftH - f0H) / DT_FD;
+    // f, the arrow-head Jacobian and the analytic df/dt (T and p are linear in t) at (t, y): ONE rate evaluation
+    double f0H, dfdtH, dd, dummy;
+    sys.eval(t, D, H, f0.data(), f0H, a.data(), b.data(), c.data(), dd, stats.n_rates, true, dfdt.data(), &dfdtH);
     if (stats.n_steps + stats.n_reject == 0 && !(opt.h_init > 0.0)) {
       // first step size, after cvHin (cvode.c): h = 1/2 sqrt(2 / ||y''||), bounded by hub, times 4 for a
       // 4th-order method; y'' = J f + df/dt from the Jacobian of this step (no differencing noise)

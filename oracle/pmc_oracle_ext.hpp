@@ -13,6 +13,7 @@ struct CondenseRatesOutputs {  // condense.F90:74-84
   double Ddot, Hdot_i, Hdot_env, dDdot_dD, dDdot_dH, dHdoti_dD, dHdoti_dH, dHdotenv_dD, dHdotenv_dH;
 };
 void condense_rates(const CondenseRatesInputs& in, CondenseRatesOutputs& out);  // condense.F90:371-502
+void condense_rates_dt(const CondenseRatesInputs& in, double& dDdot_dt, double& dHdoti_dt, double& dHdotenv_dt);
 double sat_vapor_pressure(double temp);                                         // env_state.F90:163-172
 void condense_equilib_particle(const EnvState& env, const AeroData& d, Particle& p);  // condense.F90:701-739
 

@@ -19,6 +19,15 @@ int pmco_condense_rates(int n, const double* in, double* out) {
   }
   return 0;
 }
+// time derivatives at fixed (D, H): out[3] = dDdot/dt, dHdot_i/dt, dHdot_env/dt
+int pmco_condense_rates_dt(int n, const double* in, double* out) {
+  for (int i = 0; i < n; i++) {
+    CondenseRatesInputs ci{in[9 * i + 0], in[9 * i + 1], in[9 * i + 2], in[9 * i + 3], in[9 * i + 4],
+                           in[9 * i + 5], in[9 * i + 6], in[9 * i + 7], in[9 * i + 8]};
+    condense_rates_dt(ci, out[3 * i + 0], out[3 * i + 1], out[3 * i + 2]);
+  }
+  return 0;
+}
 // bare integrator on arrays; stats: n_steps, n_reject, n_rates
 int pmco_condense_integrate(int n, double* D, double* H, const double* D_dry, const double* kappa,
                             const double* num_conc, double T0, double p0, double Tdot, double pdot, double del_t,

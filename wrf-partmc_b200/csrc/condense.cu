@@ -34,7 +34,29 @@ struct CondEnv {  // cell-level terms of condense_rates that depend on (T, p) on
   double g_coef;      // -2 pi / (V vc): Hdot_i = g_coef * num_conc * D^2 * Ddot
   double invU;        // 1 / U
   double pdot_div_p;  // pdot / p
+  // time derivatives of the terms above at fixed (D, H) (T and p are linear in t): what the analytic df/dt of the
+  // Rosenbrock stages needs (the oracle's condense_rates_dt states the same formulas)
+  double lka;     // (dk_a/dt) / k_a
+  double Y_t, Z_t, W_t, X_t;
+  double luvd;    // d ln(U V D_v) / dt
+  double lU;      // d ln U / dt
+  double lG;      // d ln(-2 pi / (V vc)) / dt
+  double envH_t;  // (d Hdot_env / dt) / H
 };
+__device__ __forceinline__ void cond_env_dt(CondEnv& e) {
+  const double lT = e.Tdot / e.T, lp = e.pdot / e.p;
+  const double lDv = 1.94 * lT - lp;
+  const double lV = e.dP0_dT_div_P0 * e.Tdot - lT;
+  e.lka = 1e-3 * 0.071 * e.Tdot / e.k_a;
+  e.lU = -lT;
+  e.W_t = -e.W * lT;
+  e.X_t = -e.X * lT;
+  e.Y_t = e.Y * (e.lka + 0.5 * lT - lp);
+  e.Z_t = e.Z * (lDv - 0.5 * lT);
+  e.luvd = e.lU + lV + lDv;
+  e.lG = -(lV + lT - lp);
+  e.envH_t = 2.0 * e.dP0_dT_div_P0 / (e.T - 38.0) * e.Tdot * e.Tdot - lp * lp;
+}
 __device__ __forceinline__ CondEnv cond_env(double T0, double p0, double Tdot, double pdot, double t) {
   CondEnv e;
   e.T = T0 + t * Tdot;
@@ -60,6 +82,7 @@ __device__ __forceinline__ CondEnv cond_env(double T0, double p0, double Tdot, d
   e.g_coef = -2.0 * PmcConst::pi / (e.V * e.vc);
   e.invU = 1.0 / e.U;
   e.pdot_div_p = pdot / e.p;
+  cond_env_dt(e);
   return e;
 }
 
@@ -268,6 +291,7 @@ __device__ __forceinline__ CondEnv cond_env_fast(double T0, double p0, double Td
   e.g_coef = -2.0 * PmcConst::pi / (e.V * e.vc);
   e.invU = 1.0 / e.U;
   e.pdot_div_p = pdot / e.p;
+  cond_env_dt(e);
   return e;
 }
 
@@ -298,12 +322,11 @@ __device__ __forceinline__ CondEnv cond_env_fast(double T0, double p0, double Td
 //   0  cold, from 0 (the BDF kernel)
 //   1  f at (t, y) with the Jacobian: starts from uN (root at the end of the previous step); leaves u0 and
 //      the sensitivities du/dD, du/dH of the root (from d delta* / dD, d delta* / dH, which the Jacobian needs anyway)
-//   2  f at (t + DT_FD, y): starts from u0; leaves du/dt = (u - u0) / DT_FD
+//      and du/dt from the analytic time derivative
 //   3  stage values: starts from the first-order prediction u0 + du/dD (y - D) + du/dH (Hs - H) + du/dt dts
 //      (the error of the start is second order in the stage increment, so one update usually suffices);
 //      write_uN: the last stage (state at t + h) leaves its root in uN
 //   5  plain warm start from / to sw[0] (8 particles per thread: no room for the sensitivities)
-#define COND_DT_FD 1e-2
 template <int PPT, bool WITH_JAC, int NT = COND_THREADS, int MODE = 0>
 __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, const CondEnv& e, double H,
                                                const double (&D)[PPT], const double* __restrict__ sDdry, const double* __restrict__ sKap,
@@ -311,7 +334,7 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
                                                double (&Hd)[PPT], double (&a)[PPT], double (&b)[PPT],
                                                double (&c)[PPT], double (&dH)[PPT], double* sw = nullptr,
                                                const double* D0 = nullptr, double H0 = 0.0, double dts = 0.0,
-                                               bool write_uN = false) {
+                                               bool write_uN = false, double* ft = nullptr, double* hdt = nullptr) {
   constexpr int AS = PPT * NT;
   const double g = e.g_coef;  // Hdot_i = g * num_conc * D^2 * Ddot
   const double invU = e.invU;
@@ -339,10 +362,6 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
     u[k] = 0.0;
     if (MODE == 1 || MODE == 5) {
       const double up = sw[(MODE == 1 ? 4 : 0) * AS + k * NT];
-      if (fabs(up) < 0.5) u[k] = up;
-    }
-    if (MODE == 2) {  // u0 + (du/dt of the previous step) DT_FD
-      const double up = fma(sw[3 * AS + k * NT], COND_DT_FD, sw[k * NT]);
       if (fabs(up) < 0.5) u[k] = up;
     }
     if (MODE == 3) {
@@ -438,10 +457,6 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
 #pragma unroll
     for (int k = 0; k < PPT; k++) sw[k * NT] = u[k];
   }
-  if (MODE == 2) {
-#pragma unroll
-    for (int k = 0; k < PPT; k++) sw[3 * AS + k * NT] = (u[k] - sw[k * NT]) * (1.0 / COND_DT_FD);
-  }
   if (MODE == 3 && write_uN) {
 #pragma unroll
     for (int k = 0; k < PPT; k++) sw[4 * AS + k * NT] = u[k];
@@ -469,6 +484,19 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
       const double inv_dh = fast_rcp(dhd);
       const double ddeltastar_dD = -dh_dD * inv_dh;
       const double ddeltastar_dH = UVD[k] * inv_dh;
+      // analytic df/dt at fixed (D, H): d delta*/dt = -(dh/dt) / (dh/ddelta), see cond_env_dt
+      if (ft != nullptr) {  // (the BDF kernel has no use for df/dt)
+        const double rk = e.lka - e.Y_t * inv_dY[k];     // d ln k_a' / dt
+        const double ru = e.luvd - e.Z_t * inv_dZ[k];    // d ln(U V D_v') / dt
+        const double qE = q * ex;
+        const double h_t = k_ap[k] * rk * delta - UVD[k] * ru * (H - a_w[k] * qE) +
+                           A[k] * qE * (q * fma(e.W_t, delta, e.X_t * invD[k]));
+        const double delta_t = -h_t * inv_dh;
+        const double Ddot_t = fma(Ddot[k], rk - e.lU, kU * delta_t);
+        ft[k] = Ddot_t;
+        hdt[k] = hf * (d * d) * fma(Ddot[k], e.lG, Ddot_t);
+        if (MODE == 1) sw[3 * AS + k * NT] = (q * q) * delta_t;
+      }
       if (MODE == 1) {  // du = q^2 d delta
         sw[1 * AS + k * NT] = (q * q) * ddeltastar_dD;
         sw[2 * AS + k * NT] = (q * q) * ddeltastar_dH;
@@ -495,6 +523,11 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
         b[k] = kd / (e.U * dd) * (e.UV * Dvd / kd);
         c[k] = 0.0;
         dH[k] = hf * (dd * dd) * b[k];
+        if (ft != nullptr) {
+          const double Ddot_t = Ddot[k] * ((e.luvd - e.lU) - e.Z_t / (dd + e.Z));
+          ft[k] = Ddot_t;
+          hdt[k] = hf * (dd * dd) * fma(Ddot[k], e.lG, Ddot_t);
+        }
       }
     }
   }
@@ -504,7 +537,7 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
 // (u0, du/dD, du/dH, du/dt, uN with the predictor; one array without)
 #define COND_PRED(PPT) ((PPT) <= 4)
 #define COND_NARR(PPT) (ROS_S + 4 + (COND_PRED(PPT) ? 5 : 1))
-#define ROS_NENV 7             // (T, p) terms of one step: t, t + DT_FD, t + alpha_i h (i = 2..6)
+#define ROS_NENV 6             // (T, p) terms of one step: t, then t + alpha_i h of the stages i = 2..6
 #define ROS_HIN_FACTOR 4.0     // first step = 4 x CVODE's first-order estimate (a 4th-order method), rounded down to 2^k
 // ---- cells larger than one CTA holds (single-box runs, 1e4..1e5 particles): the same integrator with the
 // particles of ONE cell spread over all CTAs of a co-resident (cooperatively launched) grid.  Every cell-wide
@@ -669,13 +702,12 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   }
 
   const double FAC_MIN = 0.2, FAC_MAX = 6.0, FAC_SAFE = 0.95, FAC_REJ = 0.1;
-  const double DT_FD = COND_DT_FD;
   double u1[PPT], u2[PPT], u3[PPT], u4[PPT];  // unused outputs of the no-Jacobian evaluations
   const int warp = tid >> 5, lane = tid & 31;
   // the (T, p) terms of condense_rates at the ROS_NENV times of a step: warp w evaluates entry w
   auto make_envs = [&](double t, double h, int first, int last) {
     for (int w = first + warp; w <= last; w += NT / 32) {  // entry w by warp (w - first) mod (NT / 32)
-      const double tt = (w == 0) ? t : (w == 1) ? t + DT_FD : t + c_rosAlpha[w - 1] * h;
+      const double tt = (w == 0) ? t : t + c_rosAlpha[w] * h;
       const CondEnv e = cond_env_fast(T0, p0, Tdot, pdot, tt);
       if (lane == 0) s_env[w] = e;
     }
@@ -697,32 +729,31 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
     const bool first_step = (n_steps + n_reject == 0);
     bool truncated = false;
     if (!first_step && t + h > del_t * (1.0 - 1e-14)) { h_natural = h; h = del_t - t; truncated = true; }
-    make_envs(t, h, 0, first_step ? 1 : ROS_NENV - 1);
+    make_envs(t, h, 0, first_step ? 0 : ROS_NENV - 1);
     bool stage_envs_ready = !first_step;
-    // f, Jacobian at (t, y) and f at (t + DT_FD, y)
+    // f, the Jacobian and the analytic df/dt at (t, y): one rate evaluation
     double f0[PPT], dfdt[PPT], ja[PPT], jb[PPT], jc[PPT];
     double f0H, dfdtH, dd;
     {
-      double hd[PPT], dh[PPT], f1[PPT], hd1[PPT];
-      cond_rates_vec<PPT, true, NT, PRED ? 1 : 5>(s_etab, s_env[0], H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh, sUw);
-      cond_rates_vec<PPT, false, NT, PRED ? 2 : 5>(s_etab, s_env[1], H, D, sDdry, sKap, sNc, f1, hd1, u1, u2, u3, u4, sUw);
-      n_evals += 2;
+      double hd[PPT], dh[PPT], hdt[PPT];
+      cond_rates_vec<PPT, true, NT, PRED ? 1 : 5>(s_etab, s_env[0], H, D, sDdry, sKap, sNc, f0, hd, ja, jb, jc, dh, sUw,
+                                                   nullptr, 0.0, 0.0, false, dfdt, hdt);
+      n_evals += 1;
       double acc[3] = {0.0, 0.0, 0.0};
 #pragma unroll
       for (int k = 0; k < PPT; k++) {
         const bool live = tid + (poff + k) * NT < n;
-        dfdt[k] = (f1[k] - f0[k]) * (1.0 / DT_FD);
         if (!live) { f0[k] = 0.0; dfdt[k] = 0.0; ja[k] = 0.0; jb[k] = 0.0; jc[k] = 0.0; }
         if (live) {
           acc[0] += hd[k];
           acc[1] += dh[k];
-          acc[2] += hd1[k];
+          acc[2] += hdt[k];
         }
       }
       cell_red<3, NT, false, GRID>(acc, s_red, par, gr, s_g);
       f0H = acc[0] + env_H(s_env[0], H);
       dd = acc[1] + (-s_env[0].dP0_dT_div_P0 * Tdot + s_env[0].pdot_div_p);
-      dfdtH = ((acc[2] + env_H(s_env[1], H)) - f0H) / DT_FD;
+      dfdtH = acc[2] + s_env[0].envH_t * H;
     }
     if (first_step) {
       // first step size, after cvHin (cvode.c): h = 1/2 sqrt(2 / ||y''||), bounded by hub, times ROS_HIN_FACTOR
@@ -766,7 +797,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       if (t + h > del_t * (1.0 - 1e-14)) { h_natural = h; h = del_t - t; truncated = true; }
     }
     for (;;) {
-      if (!stage_envs_ready) make_envs(t, h, 2, ROS_NENV - 1);  // stage times of this attempt
+      if (!stage_envs_ready) make_envs(t, h, 1, ROS_NENV - 1);  // stage times of this attempt
       stage_envs_ready = false;
       const double eps = 1.0 / (ROS_GAMMA * h);
       const double inv_h = 1.0 / h;
@@ -796,7 +827,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
 #pragma unroll
             for (int k = 0; k < PPT; k++) y[k] += aj * SK(j, k);
           }
-          cond_rates_vec<PPT, false, NT, PRED ? 3 : 5>(s_etab, s_env[st + 1], Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4, sUw,
+          cond_rates_vec<PPT, false, NT, PRED ? 3 : 5>(s_etab, s_env[st], Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4, sUw,
                                                          D, H, c_rosAlpha[st] * h, st == ROS_S - 1);
           n_evals++;
         } else {
@@ -825,7 +856,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
         if (st == 0)
           fsH = f0H;
         else
-          fsH = acc[0] + env_H(s_env[st + 1], Hs);
+          fsH = acc[0] + env_H(s_env[st], Hs);
         double rH = fsH + hg * dfdtH;
         for (int j = 0; j < st; j++) rH += (c_rosC[st][j] * inv_h) * KH[j];
         KH[st] = (rH + acc[1]) * inv_lhs_H;
