@@ -253,12 +253,18 @@ __device__ __forceinline__ void block_red(double (&x)[NV], double* s_red /*[2][4
     if (lane == 0) buf[k * (NT / 32) + warp] = t;
   }
   __syncthreads();
+  // the NT/32 partials of every value are added pairwise (depth log2 instead of a serial chain of NT/32 adds
+  // that every thread would wait for)
 #pragma unroll
   for (int k = 0; k < NV; k++) {
-    double t = buf[k * (NT / 32)];
+    double pw[NT / 32];
 #pragma unroll
-    for (int w = 1; w < NT / 32; w++) t = IS_MAX ? fmax(t, buf[k * (NT / 32) + w]) : t + buf[k * (NT / 32) + w];
-    x[k] = t;
+    for (int w = 0; w < NT / 32; w++) pw[w] = buf[k * (NT / 32) + w];
+#pragma unroll
+    for (int sd = 1; sd < NT / 32; sd *= 2)
+#pragma unroll
+      for (int i = 0; i + sd < NT / 32; i += 2 * sd) pw[i] = IS_MAX ? fmax(pw[i], pw[i + sd]) : pw[i] + pw[i + sd];
+    x[k] = pw[0];
   }
   par ^= 1;
 }
@@ -448,7 +454,9 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
 #pragma unroll
     for (int k = 0; k < PPT; k++) {
       const double du = hh[k] * rc[k];
-      small = small && (NEWTON_K * du * du <= NEWTON_TOL * fmax(fabs(u[k]), NEWTON_FLOOR));
+      // NEWTON_K du^2 <= NEWTON_TOL max(|u|, NEWTON_FLOOR), written as two comparisons (no FP64 max)
+      const double du2 = du * du;
+      small = small && ((du2 <= (NEWTON_TOL / NEWTON_K) * fabs(u[k])) || (du2 <= (NEWTON_TOL / NEWTON_K) * NEWTON_FLOOR));
       u[k] -= du;
     }
     if (__all_sync(0xffffffffu, small)) break;
@@ -507,7 +515,12 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
       dH[k] = hf * (d * d) * b[k];
     }
   }
-  // dry particles (D <= D_dry, condense.F90:418-436): rare, handled one by one
+  // dry particles (D <= D_dry, condense.F90:418-436): rare; the whole block sits behind a warp-uniform branch so
+  // that its divisions are not issued (predicated off) in every evaluation
+  bool any_dry = false;
+#pragma unroll
+  for (int k = 0; k < PPT; k++) any_dry = any_dry || (D[k] <= sDdry[k * NT]);
+  if (__any_sync(0xffffffffu, any_dry)) {
 #pragma unroll
   for (int k = 0; k < PPT; k++) {
     const double dd = sDdry[k * NT];
@@ -530,6 +543,7 @@ __device__ __forceinline__ void cond_rates_vec(const double* __restrict__ etab, 
         }
       }
     }
+  }
   }
 }
 
@@ -596,6 +610,21 @@ __device__ __forceinline__ void cell_red(double (&x)[NV], double* s_red, int& pa
   }
 }
 
+// One stage's linear combination of the earlier stage vectors, stage index ST a compile-time constant:
+//   C_FORM false: y += sum_j A[ST][j] K_j,              H part: Hs += sum_j A[ST][j] KH[j]
+//   C_FORM true : f += sum_j (C[ST][j] * inv_h) K_j,    H part: rH += sum_j (C[ST][j] * inv_h) KH[j]
+template <int ST, int PPT, int NT, bool C_FORM>
+__device__ __forceinline__ void ros_combo(const double* __restrict__ s_K, int tid, const double (&KH)[ROS_S], double inv_h,
+                                          double (&y)[PPT], double& yH) {
+#pragma unroll
+  for (int j = 0; j < ST; j++) {
+    const double cj = C_FORM ? c_rosC[ST][j] * inv_h : c_rosA[ST][j];
+#pragma unroll
+    for (int k = 0; k < PPT; k++) y[k] += cj * s_K[(j * PPT + k) * NT + tid];
+    yH += cj * KH[j];
+  }
+}
+
 template <int PPT, int NT, bool GRID = false>
 __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /* may alias v.temp */,
                                                            const double* p0a,
@@ -648,50 +677,68 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   double H = H0;
 
   // ---- set-up (condense.F90:196-237): kappa, D_dry, num_conc, D, abstol per particle.
-  // Slots past the population hold a harmless wet dummy particle that never enters a sum.
+  // Slots past the population hold a harmless wet dummy particle with number concentration 0: its Hdot_i and
+  // every Jacobian entry that couples it to H vanish, so it enters no cell-wide sum and needs no masking there.
   double D[PPT];
   double wsum = 0.0;
+  {
+    // species rows: the loads of all PPT particles and of four species at a time are in flight together
+    // (one serial chain of S dependent DRAM round trips per particle before); sums in species order as before
+    double vt[PPT], vs[PPT], ks[PPT], wv[PPT];
 #pragma unroll
-  for (int k = 0; k < PPT; k++) {
-    const int p = tid + (poff + k) * NT;
-    D[k] = 2.0;
-    S_ATOL(k) = 1.0;
-    SK(ROS_S + 1, k) = 1.0;
-    SK(ROS_S + 2, k) = 0.5;
-    SK(ROS_S + 3, k) = 1.0;
-    SK(ROS_S + 4, k) = 0.0;
-    if (PRED) {
-      SK(ROS_S + 5, k) = 0.0;
-      SK(ROS_S + 6, k) = 0.0;
-      SK(ROS_S + 7, k) = 0.0;
-      SK(ROS_S + 8, k) = 0.0;
-    }
-    if (p < n) {
-      // aero_particle_solute_kappa (aero_particle.F90:724-755), solute volume, total volume
-      double vt = 0.0, vs = 0.0, ks = 0.0;
-      const double M_w = v.molw[iw], rho_w = v.density[iw];
-      for (int s = 0; s < v.S; s++) {
-        const double x = v.vol[(size_t)s * NS + base + p];
-        vt += x;
+    for (int k = 0; k < PPT; k++) { vt[k] = 0.0; vs[k] = 0.0; ks[k] = 0.0; wv[k] = 0.0; }
+    const double M_w = v.molw[iw], rho_w = v.density[iw];
+#pragma unroll 4
+    for (int s = 0; s < v.S; s++) {
+      // aero_particle_solute_kappa (aero_particle.F90:724-755)
+      const double kp = (v.nions[s] > 0) ? M_w * v.density[s] / (v.molw[s] * rho_w) * (double)v.nions[s] : v.kappa[s];
+      double x[PPT];
+#pragma unroll
+      for (int k = 0; k < PPT; k++) {
+        const int p = tid + (poff + k) * NT;
+        x[k] = (p < n) ? v.vol[(size_t)s * NS + base + p] : 0.0;
+      }
+#pragma unroll
+      for (int k = 0; k < PPT; k++) {
+        vt[k] += x[k];
         if (s != iw) {
-          vs += x;
-          const double kp = (v.nions[s] > 0) ? M_w * v.density[s] / (v.molw[s] * rho_w) * (double)v.nions[s] : v.kappa[s];
-          ks += x * kp;
+          vs[k] += x[k];
+          ks[k] += x[k] * kp;
+        } else {
+          wv[k] = x[k];
         }
       }
-      const int gc = v.wgc[base + p];
-      const double r = vol2rad(vt);
-      const double ddry = 2.0 * vol2rad(vs);
-      const double ncp = awa_nc_at_radius(v, cell, gc / v.G + 1, r);
-      SK(ROS_S + 1, k) = ddry;
-      SK(ROS_S + 2, k) = ks / vs;
-      SK(ROS_S + 3, k) = ncp;
-      D[k] = 2.0 * r;
-      S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (D[k] - ddry));
-      wsum += v.vol[(size_t)iw * NS + base + p] * ncp;
-      if (nonflat) {
-        const size_t wi = (size_t)cell * v.C * v.G + gc;
-        v.lnr[base + p] = weight_nc(v.wtype[wi], v.wmag[wi], v.wexp[wi], r);
+    }
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+      const int p = tid + (poff + k) * NT;
+      D[k] = 2.0;
+      S_ATOL(k) = 1.0;
+      SK(ROS_S + 1, k) = 1.0;
+      SK(ROS_S + 2, k) = 0.5;
+      SK(ROS_S + 3, k) = 0.0;
+      SK(ROS_S + 4, k) = 0.0;
+      if (PRED) {
+        SK(ROS_S + 5, k) = 0.0;
+        SK(ROS_S + 6, k) = 0.0;
+        SK(ROS_S + 7, k) = 0.0;
+        SK(ROS_S + 8, k) = 0.0;
+      }
+      if (p < n) {
+        const int gc = v.wgc[base + p];
+        const double r = vol2rad(vt[k]);
+        const double ddry = 2.0 * vol2rad(vs[k]);
+        const double ncp = awa_nc_at_radius(v, cell, gc / v.G + 1, r);
+        SK(ROS_S + 1, k) = ddry;
+        SK(ROS_S + 2, k) = ks[k] / vs[k];
+        SK(ROS_S + 3, k) = ncp;
+        D[k] = 2.0 * r;
+        S_ATOL(k) = fmax(1e-30, prm.abstol_scale * (D[k] - ddry));
+        wsum += wv[k] * ncp;
+        if (nonflat) {
+          const size_t wi = (size_t)cell * v.C * v.G + gc;
+          v.lnr[base + p] = weight_nc(v.wtype[wi], v.wmag[wi], v.wexp[wi], r);
+        }
       }
     }
   }
@@ -744,11 +791,9 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       for (int k = 0; k < PPT; k++) {
         const bool live = tid + (poff + k) * NT < n;
         if (!live) { f0[k] = 0.0; dfdt[k] = 0.0; ja[k] = 0.0; jb[k] = 0.0; jc[k] = 0.0; }
-        if (live) {
-          acc[0] += hd[k];
-          acc[1] += dh[k];
-          acc[2] += hdt[k];
-        }
+        acc[0] += hd[k];  // (exactly zero for the dummy slots: their number concentration is 0)
+        acc[1] += dh[k];
+        acc[2] += hdt[k];
       }
       cell_red<3, NT, false, GRID>(acc, s_red, par, gr, s_g);
       f0H = acc[0] + env_H(s_env[0], H);
@@ -802,66 +847,73 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
       const double eps = 1.0 / (ROS_GAMMA * h);
       const double inv_h = 1.0 / h;
       double inv[PPT];
-      double KH[ROS_S];
-      double sden[1] = {0.0};
+      double KH[ROS_S];  // indexed by compile-time constants only (registers)
+      // Stage 1 needs no rate evaluation (f at (t, y) is known), so its Schur sum travels in the same
+      // reduction as the Schur complement of the attempt.
+      double fs[PPT];
+      {
+        double r2[2] = {0.0, 0.0};
+        const double hg = h * c_rosGam[0];
 #pragma unroll
-      for (int k = 0; k < PPT; k++) {
-        inv[k] = fast_rcp(eps - ja[k]);
-        if (tid + (poff + k) * NT < n) sden[0] += jc[k] * jb[k] * inv[k];
-      }
-      cell_red<1, NT, false, GRID>(sden, s_red, par, gr, s_g);
-      const double inv_lhs_H = 1.0 / (eps - dd - sden[0]);  // one division per attempt, not one per stage
+        for (int k = 0; k < PPT; k++) {
+          inv[k] = fast_rcp(eps - ja[k]);
+          fs[k] = f0[k] + hg * dfdt[k];
+          r2[0] += jc[k] * jb[k] * inv[k];  // jc = 0 in the dummy slots
+          r2[1] += jc[k] * fs[k] * inv[k];
+        }
+        cell_red<2, NT, false, GRID>(r2, s_red, par, gr, s_g);
+        const double inv_lhs_H = 1.0 / (eps - dd - r2[0]);  // one division per attempt, not one per stage
+        KH[0] = ((f0H + hg * dfdtH) + r2[1]) * inv_lhs_H;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) SK(0, k) = (fs[k] + jb[k] * KH[0]) * inv[k];
 #pragma unroll 1
-      for (int st = 0; st < ROS_S; st++) {
-        // stage function value (stage 1 reuses f at (t, y))
-        double fs[PPT], hd[PPT];
-        double acc[2] = {0.0, 0.0};
-        double Hs = H;
-        for (int j = 0; j < st; j++) Hs += c_rosA[st][j] * KH[j];
-        if (st > 0) {
-          double y[PPT];
+        for (int st = 1; st < ROS_S; st++) {
+          double hd[PPT], y[PPT];
+          double acc[2] = {0.0, 0.0};
+          double Hs = H;
 #pragma unroll
           for (int k = 0; k < PPT; k++) y[k] = D[k];
-          for (int j = 0; j < st; j++) {
-            const double aj = c_rosA[st][j];
-#pragma unroll
-            for (int k = 0; k < PPT; k++) y[k] += aj * SK(j, k);
+          // y + sum_j A_ij K_j with the stage index as a compile-time constant: the K_j loads of a stage are
+          // issued together and the coefficients are constant-bank operands
+          switch (st) {
+            case 1: ros_combo<1, PPT, NT, false>(s_K, tid, KH, 1.0, y, Hs); break;
+            case 2: ros_combo<2, PPT, NT, false>(s_K, tid, KH, 1.0, y, Hs); break;
+            case 3: ros_combo<3, PPT, NT, false>(s_K, tid, KH, 1.0, y, Hs); break;
+            case 4: ros_combo<4, PPT, NT, false>(s_K, tid, KH, 1.0, y, Hs); break;
+            default: ros_combo<5, PPT, NT, false>(s_K, tid, KH, 1.0, y, Hs); break;
           }
           cond_rates_vec<PPT, false, NT, PRED ? 3 : 5>(s_etab, s_env[st], Hs, y, sDdry, sKap, sNc, fs, hd, u1, u2, u3, u4, sUw,
                                                          D, H, c_rosAlpha[st] * h, st == ROS_S - 1);
           n_evals++;
-        } else {
+          const double hgs = h * c_rosGam[st];
+          double rH = 0.0;
 #pragma unroll
-          for (int k = 0; k < PPT; k++) { fs[k] = f0[k]; hd[k] = 0.0; }
-        }
-        const double hg = h * c_rosGam[st];
-#pragma unroll
-        for (int k = 0; k < PPT; k++) fs[k] = fs[k] + hg * dfdt[k];
-        for (int j = 0; j < st; j++) {
-          const double cj = c_rosC[st][j] * inv_h;
-#pragma unroll
-          for (int k = 0; k < PPT; k++) fs[k] += cj * SK(j, k);
-        }
-#pragma unroll
-        for (int k = 0; k < PPT; k++) {
-          if (tid + (poff + k) * NT < n) {
-            acc[0] += hd[k];
-            acc[1] += jc[k] * fs[k] * inv[k];
-          } else {
-            fs[k] = 0.0;
+          for (int k = 0; k < PPT; k++) fs[k] = fs[k] + hgs * dfdt[k];
+          switch (st) {
+            case 1: ros_combo<1, PPT, NT, true>(s_K, tid, KH, inv_h, fs, rH); break;
+            case 2: ros_combo<2, PPT, NT, true>(s_K, tid, KH, inv_h, fs, rH); break;
+            case 3: ros_combo<3, PPT, NT, true>(s_K, tid, KH, inv_h, fs, rH); break;
+            case 4: ros_combo<4, PPT, NT, true>(s_K, tid, KH, inv_h, fs, rH); break;
+            default: ros_combo<5, PPT, NT, true>(s_K, tid, KH, inv_h, fs, rH); break;
           }
-        }
-        cell_red<2, NT, false, GRID>(acc, s_red, par, gr, s_g);
-        double fsH;
-        if (st == 0)
-          fsH = f0H;
-        else
-          fsH = acc[0] + env_H(s_env[st], Hs);
-        double rH = fsH + hg * dfdtH;
-        for (int j = 0; j < st; j++) rH += (c_rosC[st][j] * inv_h) * KH[j];
-        KH[st] = (rH + acc[1]) * inv_lhs_H;
 #pragma unroll
-        for (int k = 0; k < PPT; k++) SK(st, k) = (fs[k] + jb[k] * KH[st]) * inv[k];
+          for (int k = 0; k < PPT; k++) {
+            acc[0] += hd[k];                     // zero in the dummy slots (number concentration 0)
+            acc[1] += jc[k] * fs[k] * inv[k];    // jc = 0 there
+          }
+          cell_red<2, NT, false, GRID>(acc, s_red, par, gr, s_g);
+          const double fsH = acc[0] + env_H(s_env[st], Hs);
+          const double kh = (((fsH + hgs * dfdtH) + rH) + acc[1]) * inv_lhs_H;
+          switch (st) {
+            case 1: KH[1] = kh; break;
+            case 2: KH[2] = kh; break;
+            case 3: KH[3] = kh; break;
+            case 4: KH[4] = kh; break;
+            default: KH[5] = kh; break;
+          }
+#pragma unroll
+          for (int k = 0; k < PPT; k++) SK(st, k) = (fs[k] + jb[k] * kh) * inv[k];
+        }
       }
       // new state and weighted RMS error norm (E = last stage for RODAS4)
       double esum[1] = {0.0};
@@ -1571,6 +1623,7 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 128)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 64)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 256)));
+
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 288>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 288)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<8, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(8, 256)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense_bdf<2, COND_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bdf_smem(2)));
@@ -1619,6 +1672,8 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     // 257..512 particles: 128 threads x 4 particles, so that two cells share an SM (244 registers x 128
     // threads each) instead of one CTA of 256 threads x 2 particles leaving half the register file idle
     if (cap > 256) { ROS_LAUNCH(4, 128, 256, 512); }
+    // (round 2: 3 particles x 384 threads -- a third warp per scheduler at 168 registers -- measured 224.7 ms per
+    // K4 step, 2 x 512 236.8 ms, against 206.0 ms for 4 x 256: profiles/r02_condense_notes.md)
     if (cap > 512) { ROS_LAUNCH(4, 256, 512, 1024); }
     // cells a little over 1024 particles (a 1000-particle population drifts there between rebalances):
     // nine warps x 4 particles at 168 registers (three warps share a scheduler's 16384 registers; 422 bytes
