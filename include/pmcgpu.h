@@ -182,6 +182,28 @@ int pmcgpu_update_density(pmcgpu_ctx* ctx, const double* new_inverse_density);
 /* partmc_to_wrf (wrf_pmc_driver.F90:1704-1719): out[cell*n_class + c] = max(count*magnitude*alt, 1e-16) */
 int pmcgpu_num_conc_by_class(pmcgpu_ctx* ctx, float* out);
 
+/* wrf_to_partmc (interface/wrf_pmc_driver.F90:576-644) + rel_hum (:649-666) + get_grid_cell_volume (:2002-2020)
+ * for every cell of the patch, on the device: WRF's single-precision fields in, the env_state of every cell out.
+ * Arithmetic types follow the Fortran statement by statement: p + pb and t_2 + t0 are single-precision sums,
+ * temperature = theta (p / p0)**rcp in double with WRF's single-precision constants (t0 = 300., p0 = 100000.,
+ * rcp = r_d / cp = 287. / (7. * 287. / 2.), share/module_model_constants.F:23-43), rh =
+ * qv / (3.8 exp(17.27 (T - 273) / (T - 36)) / (.01 p)) with the literals 17.27 and .01 in single precision,
+ * clamped to [0.1, 0.95]; height = z_at_w(k+1) - z_at_w(k) (single); cell_volume = dx dy dz with
+ * dx = (1 / rdx) / msftx.  All arrays are WRF `real`, patch-sized, WRF memory order, host or device pointers:
+ *   p, pb, t_2, qv, alt, z [nx nz ny];  z_at_w [nx (nz+1) ny];  msftx, msfty [nx ny] (NULL = 1).
+ * The new fields are kept in a staging area and become the env_state of the NEXT pmcgpu_partmc_timestep whose
+ * temp / pressure / rel_humid / inverse_density / cell_volume pointers are NULL (the old state is then kept as
+ * old_env_states, :615, exactly as when host arrays are passed).  pmcgpu_get_env_staging copies them out
+ * ([n_cells] each, any pointer may be NULL) for inspection. */
+typedef struct {
+  const float* p; const float* pb; const float* t_2; const float* qv; const float* alt; const float* z;
+  const float* z_at_w; const float* msftx; const float* msfty;
+  float rdx, rdy;                 /* grid%rdx, grid%rdy */
+} pmcgpu_wrf_fields;
+int pmcgpu_wrf_to_partmc(pmcgpu_ctx* ctx, const pmcgpu_wrf_fields* f);
+int pmcgpu_get_env_staging(pmcgpu_ctx* ctx, double* temp, double* pressure, double* rel_humid,
+                           double* inverse_density, double* cell_volume, double* height);
+
 /* partmc_timestep (interface/wrf_pmc_driver.F90:46-290) for every cell of the patch, as one
  * asynchronous chain on the context's stream: wrf_to_partmc (new env_state from the host arrays below,
  * the previous one becomes old_env_states), mc_coag when mod(elapsed_time, chem_dt) == 0 and

@@ -318,6 +318,20 @@ def condense_rates(inputs):
     return out
 
 
+def wrf_to_partmc(nx, nz, ny, p, pb, t_2, qv, alt, z_at_w, rdx, rdy, msftx=None, msfty=None):
+    """wrf_to_partmc + rel_hum + get_grid_cell_volume (wrf_pmc_driver.F90:576-666, 2002-2020) for a patch of WRF
+    `real` fields; returns dict(temp, pressure, rel_humid, inverse_density, cell_volume, height) of [n_cells]"""
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+    a = [f32(x) for x in (p, pb, t_2, qv, alt, z_at_w, msftx, msfty)]
+    n = nx * nz * ny
+    out = np.zeros((6, n))
+    L = lib()
+    L.pmco_wrf_to_partmc.argtypes = [C.c_int] * 3 + [C.c_void_p] * 8 + [C.c_float, C.c_float, C.c_void_p]
+    L.pmco_wrf_to_partmc(nx, nz, ny, *[None if x is None else x.ctypes.data for x in a], float(rdx), float(rdy),
+                         out.ctypes.data)
+    return dict(zip(("temp", "pressure", "rel_humid", "inverse_density", "cell_volume", "height"), out))
+
+
 def condense_rates_dt(inputs):
     """time derivatives of condense_rates at fixed (D, H): [n][3] = dDdot/dt, dHdot_i/dt, dHdot_env/dt"""
     a = _f64(inputs).reshape(-1, 9)

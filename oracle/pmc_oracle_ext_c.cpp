@@ -19,6 +19,46 @@ int pmco_condense_rates(int n, const double* in, double* out) {
   }
   return 0;
 }
+// wrf_to_partmc (interface/wrf_pmc_driver.F90:576-644), rel_hum (:649-666), get_grid_cell_volume (:2002-2020)
+// for every cell of a patch; out[6][n] = temp, pressure, rel_humid, inverse_density, cell_volume, height.
+// Every intermediate carries the type the Fortran gives it: WRF fields are `real`, `grid%p + grid%pb` and
+// `grid%t_2 + t0` are single-precision sums assigned to real(dp) variables, t0 = 300., p0 = 100000.,
+// rcp = r_d / cp = 287. / (7. * 287. / 2.) are single-precision parameters (module_model_constants.F:23-43)
+// promoted to double where they meet a double; the literals 17.27 and .01 of rel_hum are default reals.
+int pmco_wrf_to_partmc(int nx, int nz, int ny, const float* p, const float* pb, const float* t_2, const float* qv,
+                       const float* alt, const float* z_at_w, const float* msftx, const float* msfty, float rdx,
+                       float rdy, double* out) {
+  const size_t n = (size_t)nx * nz * ny;
+  const float t0 = 300.f, p0 = 100000.f, r_d = 287.f;
+  const float cp = 7.f * r_d / 2.f;
+  const float rcp = r_d / cp;
+  for (int j = 0; j < ny; j++)
+    for (int k = 0; k < nz; k++)
+      for (int i = 0; i < nx; i++) {
+        const size_t c = (size_t)i + (size_t)nx * ((size_t)k + (size_t)nz * j);
+        volatile float psum = p[c] + pb[c];    // :617 single-precision sum
+        volatile float thsum = t_2[c] + t0;    // :619
+        const double pressure = (double)psum;
+        const double potential_temp = (double)thsum;
+        const double temperature = potential_temp * std::pow(pressure / (double)p0, (double)rcp);  // :620
+        const double q = (double)qv[c];
+        double rh = q / (3.8 * std::exp((double)17.27f * (temperature - 273.0) / (temperature - 36.0)) /
+                         ((double).01f * pressure));                                                   // :662
+        rh = std::max(0.1, std::min(rh, 0.95));                                                        // :664
+        const size_t w = (size_t)i + (size_t)nx * ((size_t)k + (size_t)(nz + 1) * j);
+        volatile float dzf = z_at_w[w + nx] - z_at_w[w];  // :627, :2015
+        const double dz = (double)dzf;
+        const double dx = (1.0 / (double)rdx) / (double)(msftx ? msftx[i + (size_t)nx * j] : 1.f);  // :2016
+        const double dy = (1.0 / (double)rdy) / (double)(msfty ? msfty[i + (size_t)nx * j] : 1.f);  // :2017
+        out[c] = temperature;
+        out[n + c] = pressure;
+        out[2 * n + c] = rh;
+        out[3 * n + c] = (double)alt[c];  // :635
+        out[4 * n + c] = dx * dy * dz;    // :2019
+        out[5 * n + c] = dz;
+      }
+  return 0;
+}
 // time derivatives at fixed (D, H): out[3] = dDdot/dt, dHdot_i/dt, dHdot_env/dt
 int pmco_condense_rates_dt(int n, const double* in, double* out) {
   for (int i = 0; i < n; i++) {

@@ -173,3 +173,32 @@ def test_n_part_ideal_per_class(mods):
         w = P["wclass"][off[c]:off[c + 1]]
         assert (w == 1).sum() == cnt0[c, 0]
         assert (w == 2).sum() == 2 * cnt0[c, 1]
+
+
+def test_wrf_to_partmc_on_device(mods):
+    """pmcgpu_wrf_to_partmc (wrf_pmc_driver.F90:576-666, 2002-2020) against the oracle on the same WRF `real`
+    fields: pressure, height, 1/rho exact (single-precision sums), T / RH / volume to 1e-14 (pow, exp of the two
+    math libraries); and the staged fields become the env_state of the next partmc_timestep."""
+    W, O = mods
+    rng = np.random.default_rng(8)
+    nx, nz, ny = 6, 5, 4
+    case = common.make_cells(n_cells=nx * nz * ny, n_per_cell=50, n_spec=3, n_class=1, seed=2, nx=nx, nz=nz, ny=ny)
+    g = common.gpu_from_case(W, case)
+    pb = (9.5e4 * np.exp(-np.arange(nz) / 9.0))[None, :, None] * np.ones((ny, 1, nx))
+    p = rng.normal(0, 300, (ny, nz, nx))
+    t_2 = rng.normal(-8, 6, (ny, nz, nx))
+    qv = rng.uniform(1e-4, 2.2e-2, (ny, nz, nx))
+    alt = rng.uniform(0.8, 1.3, (ny, nz, nx))
+    zw = np.cumsum(rng.uniform(40, 200, (ny, nz + 1, nx)), axis=1)
+    msftx, msfty = rng.uniform(0.9, 1.1, (ny, nx)), rng.uniform(0.9, 1.1, (ny, nx))
+    rdx, rdy = 1.0 / 4000.0, 1.0 / 3000.0
+    d = g.wrf_to_partmc(p, pb, t_2, qv, alt, zw, rdx, rdy, msftx=msftx, msfty=msfty)
+    r = O.wrf_to_partmc(nx, nz, ny, p, pb, t_2, qv, alt, zw, rdx, rdy, msftx, msfty)
+    for k in ("pressure", "height", "inverse_density"):
+        assert np.array_equal(d[k], r[k]), k
+    for k in ("temp", "rel_humid", "cell_volume"):
+        np.testing.assert_allclose(d[k], r[k], rtol=1e-14, err_msg=k)
+    assert (d["rel_humid"] == 0.95).any() and (d["rel_humid"] == 0.1).any()
+    # a step without met arrays installs the staged env_state (no condensation: the new RH is installed too)
+    g.partmc_timestep(elapsed_time=0.0, dt=60.0, chem_dt=60.0, do_coagulation=False, do_condensation=False, step=1)
+    assert np.array_equal(g.rel_humid(), d["rel_humid"])

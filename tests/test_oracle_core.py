@@ -198,3 +198,42 @@ def test_reference_sort_c_matches_numpy():
     L.double_sort_c(C.c_int(57), data.ctypes.data_as(C.c_void_p), perm.ctypes.data_as(C.c_void_p))
     assert np.array_equal(data, np.sort(x))
     assert np.array_equal(x[perm - 1], data)
+
+
+def test_wrf_to_partmc_types_follow_the_fortran():
+    """wrf_to_partmc / rel_hum / get_grid_cell_volume (interface/wrf_pmc_driver.F90:576-666, 2002-2020): the
+    oracle against an independent numpy statement of the same typed arithmetic (float32 sums, float32 constants
+    promoted to double), the RH clamp to [0.1, 0.95] and the cell volume."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(3)
+    nx, nz, ny = 5, 4, 3
+    n = nx * nz * ny
+    pb = (9.0e4 * np.exp(-np.arange(nz) / 8.0))[None, :, None] * np.ones((ny, 1, nx))
+    p = rng.normal(0, 300, (ny, nz, nx))
+    t_2 = rng.normal(-5, 8, (ny, nz, nx))
+    qv = rng.uniform(1e-4, 2.5e-2, (ny, nz, nx))
+    alt = rng.uniform(0.8, 1.3, (ny, nz, nx))
+    zw = np.cumsum(rng.uniform(40, 200, (ny, nz + 1, nx)), axis=1)
+    msftx = rng.uniform(0.9, 1.1, (ny, nx))
+    msfty = rng.uniform(0.9, 1.1, (ny, nx))
+    rdx, rdy = 1.0 / 4000.0, 1.0 / 3000.0
+    r = O.wrf_to_partmc(nx, nz, ny, p, pb, t_2, qv, alt, zw, rdx, rdy, msftx, msfty)
+    f = np.float32
+    pres = (f(p) + f(pb)).astype(np.float64).ravel()
+    theta = (f(t_2) + f(300.0)).astype(np.float64).ravel()
+    rcp = np.float64(f(287.0) / (f(7.0) * f(287.0) / f(2.0)))
+    T = theta * (pres / 1e5) ** rcp
+    rh = f(qv).astype(np.float64).ravel() / (3.8 * np.exp(np.float64(f(17.27)) * (T - 273.0) / (T - 36.0)) /
+                                           (np.float64(f(0.01)) * pres))
+    rh = np.clip(rh, 0.1, 0.95)
+    dz = (f(zw)[:, 1:, :] - f(zw)[:, :-1, :]).astype(np.float64)
+    dx = (1.0 / np.float64(f(rdx))) / f(msftx).astype(np.float64)
+    dy = (1.0 / np.float64(f(rdy))) / f(msfty).astype(np.float64)
+    vol = (dx * dy)[:, None, :] * dz
+    np.testing.assert_allclose(r["pressure"], pres, rtol=0, atol=0)
+    np.testing.assert_allclose(r["temp"], T, rtol=1e-15)
+    np.testing.assert_allclose(r["rel_humid"], rh, rtol=1e-14)
+    assert (r["rel_humid"] == 0.95).any() and (r["rel_humid"] == 0.1).any() and ((r["rel_humid"] > 0.1) & (r["rel_humid"] < 0.95)).any()
+    np.testing.assert_allclose(r["height"], dz.ravel(), rtol=0, atol=0)
+    np.testing.assert_allclose(r["cell_volume"], vol.ravel(), rtol=1e-15)
+    np.testing.assert_array_equal(r["inverse_density"], f(alt).astype(np.float64).ravel())

@@ -100,7 +100,7 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   A(v.coag_samp, v.n_cells) A(v.coag_ncoag, v.n_cells)
   A(v.cond_T1, v.n_cells) A(v.cond_p1, v.n_cells) A(v.cond_h, v.n_cells) A(v.cond_stats, (size_t)3 * v.n_cells)
   A(v.cond_wre, v.n_cells) A(v.cond_T0, v.n_cells) A(v.cond_p0, v.n_cells) A(v.stage, (size_t)5 * v.n_cells)
-  A(v.numconc, (size_t)v.n_cells * v.C) A(ctx->d_flag, 1) A(v.work, 4) A(v.ideal_gc, (size_t)v.C * v.G)
+  A(v.numconc, (size_t)v.n_cells * v.C) A(ctx->d_flag, 1) A(v.work, 4) A(v.ideal_gc, (size_t)v.C * v.G) A(v.w2p, (size_t)6 * v.n_cells)
   double *d_density, *d_kappa, *d_molw;
   int* d_nions;
   A(d_density, v.S) A(d_kappa, v.S) A(d_molw, v.S) A(d_nions, v.S)
@@ -210,20 +210,6 @@ __global__ void k_gather_particles(DevView v, const long long* __restrict__ off,
   }
 }
 
-template <typename T>
-struct TmpDev {
-  T* p = nullptr;
-  ~TmpDev() {
-    if (p) cudaFree(p);
-  }
-  cudaError_t upload(const T* h, size_t n, cudaStream_t s) {
-    if (!h) return cudaSuccess;
-    cudaError_t e = cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(T));
-    if (e != cudaSuccess) return e;
-    return cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s);
-  }
-  cudaError_t alloc(size_t n) { return cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(T)); }
-};
 
 extern "C" int pmcgpu_set_particles(pmcgpu_ctx* ctx, const int* cell_count, const double* vol, const int* wgroup,
                                     const int* wclass, const int64_t* id, const int* n_primary, const int* hyst,

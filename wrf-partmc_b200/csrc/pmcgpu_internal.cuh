@@ -91,6 +91,7 @@ struct DevView {
   double* cond_T0;    // [n_cells] env_state_initial of the step (old_env_states, wrf_pmc_driver.F90:120)
   double* cond_p0;
   double* stage;      // [5][n_cells] H2D staging of wrf_to_partmc outputs
+  double* w2p;        // [6][n_cells] wrf_to_partmc on the device: T, p, RH, 1/rho, cell volume, height
   float* numconc;     // [n_cells][C] partmc_to_wrf output
   // work counters (pmcgpu_get_work): [0] particle rate evaluations of condense_particles (rate evaluations x
   // particles of the cell, summed over cells and calls), [1] particles condense_particles integrated,
@@ -170,6 +171,7 @@ struct pmcgpu_ctx {
   bool cfg_trans_smem = false, cfg_cond = false, cfg_cond_grid = false, cfg_sort = false;  // per-context (= per-device) opt-ins
   int cond_n_sm = 0, cond_max_blk4 = 0, cond_max_blk8 = 0;
   size_t cfg_msamp_smem = 0, cfg_kmax_smem = 0, cfg_sort_smem = 0, cfg_sort_staged_smem = 0;
+  bool w2p_ready = false;           // pmcgpu_wrf_to_partmc has staged an env_state for the next partmc_timestep
   int kmax_ktype = 0;               // kernel type the per-cell majorant tables were built for
   // patch neighbours (rank of the patch on side s; this rank itself on a periodic single patch)
   int rank = 0, n_ranks = 1, px = 1, py = 1;
@@ -217,6 +219,22 @@ static inline TrSlab tr_slab_view(char* msg, int hdr_ints, int pitch, int S) {
       return PMCGPU_ERR_CUDA;                                                           \
     }                                                                                   \
   } while (0)
+
+// a device buffer that lives for one call
+template <typename T>
+struct TmpDev {
+  T* p = nullptr;
+  ~TmpDev() {
+    if (p) cudaFree(p);
+  }
+  cudaError_t upload(const T* h, size_t n, cudaStream_t s) {
+    if (!h) return cudaSuccess;
+    cudaError_t e = cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(T));
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s);
+  }
+  cudaError_t alloc(size_t n) { return cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(T)); }
+};
 
 int pmc_first_status(pmcgpu_ctx* ctx);
 // brackets the launches of one scope with a pair of events on the context's stream

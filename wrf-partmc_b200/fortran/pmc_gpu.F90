@@ -1,29 +1,42 @@
-! pmc_gpu.F90 -- ISO_C_BINDING layer between WRF-PartMC's interface/ code and
-! libpmcgpu.so (include/pmcgpu.h).
+! pmc_gpu.F90 -- the host side of the drop-in: Fortran routines with the reference's OWN names and argument
+! lists that forward to libpmcgpu.so (include/pmcgpu.h) through the generated ISO_C_BINDING mirror
+! pmc_gpu_c.F90.  A WRF-PartMC build compiles pmc_gpu_c.F90 and this file and replaces the `use` of the
+! reference modules for these routines by `use pmc_gpu`:
 !
-! This is the only host code a WRF-PartMC build adds: it keeps the argument lists of
-!   partmc_timestep       (interface/wrf_pmc_driver.F90:46-87)
-!   wrf_pmc_trans_driver  (interface/wrf_pmc_trans.F90:37-76)
-! and forwards them to the device library, which owns all particles of the patch.
-! Conventions follow the reference's own C boundary (partmc/src/condense.F90:183-195):
-! scalars by value, arrays through c_loc of a contiguous target, int return code with
-! 0 = success, a non-zero code is handed to die_msg (util.F90:134).
+!   WRF level (all cells of the patch, the library owns the particles)
+!     partmc_timestep       interface/wrf_pmc_driver.F90:46-87       -> pmcgpu_wrf_to_partmc + pmcgpu_partmc_timestep
+!     wrf_pmc_trans_driver  interface/wrf_pmc_trans.F90:37-76        -> pmcgpu_wrf_pmc_trans_driver (+ dry deposition)
+!     trans_aero            interface/wrf_pmc_trans_aero.F90:40-76   -> (reached through wrf_pmc_trans_driver)
+!     wrf_pmc_dep_dry_driver interface/wrf_pmc_dep.F90:31            -> pmcgpu_wrf_pmc_dep_dry_driver
+!   PartMC level (ONE aero_state, e.g. run_part.F90:583,599): a one-cell context per call
+!     mc_coag               partmc/src/coagulation.F90:43-59         -> pmcgpu_mc_coag
+!     condense_particles    partmc/src/condense.F90:147-161          -> pmcgpu_condense_particles
+!     aero_state_sort       partmc/src/aero_state.F90:3218           -> pmcgpu_aero_state_sort
+!     aero_state_rebalance  partmc/src/aero_state.F90:1765           -> pmcgpu_aero_state_rebalance
 !
-! NOTE: no Fortran compiler exists in the build image of this repository (gfortran,
-! flang, nvfortran, ifx all absent), so this file is written against the Fortran 2003
-! standard and the header but has NOT been compiled; tests drive the same C symbols
-! through wrf-partmc_b200/host/pmcgpu.py.  INTEGRATION.md lists the build line.
+! Conventions follow the reference's own C boundary (partmc/src/condense.F90:183-195): scalars by value, arrays
+! through c_loc of a contiguous target, int return code with 0 = success, a non-zero code goes to die_msg
+! (util.F90:134).  What does NOT cross the boundary (DESIGN.md section 2): aero_particle_t%component(:) source
+! lists and the optical fields (absorb/scatter_cross_sect, asymmetry, refract_*, core_vol) stay on the host
+! mirror and are zero after pmc_gpu_download_aero_states; gas chemistry, emissions, MOSAIC and optics keep
+! running on the host (SURVEY.md section 8f).
+!
+! NOTE: no Fortran compiler exists in the build image of this repository (gfortran, flang, nvfortran, ifx all
+! absent), so this file is written against the Fortran 2003 standard and the generated interfaces but has NOT
+! been compiled; tests/test_abi.py checks the struct layouts and symbol coverage of pmc_gpu_c.F90, and the
+! tests drive the same C symbols through wrf-partmc_b200/host/pmcgpu.py.  INTEGRATION.md lists the build line.
 module pmc_gpu
 
   use, intrinsic :: iso_c_binding
+  use pmc_gpu_c
   implicit none
   private
 
-  public :: pmcgpu_config_t, pmcgpu_timestep_args_t, pmcgpu_trans_args_t
   public :: pmc_gpu_init, pmc_gpu_finalize, pmc_gpu_upload_aero_states, &
-       pmc_gpu_download_aero_states, pmc_gpu_partmc_timestep, &
-       pmc_gpu_wrf_pmc_trans_driver, pmc_gpu_check
-  public :: pmc_gpu_handle
+       pmc_gpu_download_aero_states, pmc_gpu_check, pmc_gpu_handle
+  ! the reference's entry points
+  public :: partmc_timestep, wrf_pmc_trans_driver, trans_aero, wrf_pmc_dep_dry_driver
+  public :: mc_coag, condense_particles, aero_state_sort, aero_state_rebalance
 
   integer, parameter :: dp = c_double
 
@@ -31,136 +44,12 @@ module pmc_gpu
   integer(c_int), parameter, public :: PMCGPU_KERNEL_ADDITIVE = 2, &
        PMCGPU_KERNEL_CONSTANT = 3, PMCGPU_KERNEL_BROWN = 4, PMCGPU_KERNEL_ZERO = 5
 
-  !> pmcgpu_config (include/pmcgpu.h); member order must match the C struct.
-  type, bind(c) :: pmcgpu_config_t
-     integer(c_int) :: n_spec
-     type(c_ptr) :: density, kappa, molec_weight, num_ions
-     integer(c_int) :: i_water
-     integer(c_int) :: n_group, n_class
-     integer(c_int) :: nx, nz, ny
-     integer(c_int) :: global_nx, global_ny
-     integer(c_int) :: i_offset, j_offset
-     integer(c_int) :: periodic_x, periodic_y
-     real(c_double) :: n_part_ideal
-     integer(c_int) :: cell_capacity
-     integer(c_int) :: max_bins
-     integer(c_int) :: seed          ! unsigned int on the C side (same size)
-     integer(c_int) :: device
-  end type pmcgpu_config_t
-
-  !> pmcgpu_timestep_args (include/pmcgpu.h)
-  type, bind(c) :: pmcgpu_timestep_args_t
-     type(c_ptr) :: temp, pressure, rel_humid, inverse_density, cell_volume
-     real(c_double) :: elapsed_time, dt, chem_dt
-     integer(c_int) :: do_coagulation, coag_kernel_type, do_condensation
-     integer(c_int) :: allow_doubling, allow_halving
-     integer(c_int) :: step
-     type(c_ptr) :: num_conc_out, rel_humid_out
-     integer(c_int) :: no_wait
-  end type pmcgpu_timestep_args_t
-
-  !> pmcgpu_trans_args (include/pmcgpu.h)
-  type, bind(c) :: pmcgpu_trans_args_t
-     type(c_ptr) :: u_flux, v_flux, w_flux, xkhh, alt, z, z_at_w, exch_h
-     real(c_float) :: dx, dy, dt
-     integer(c_int) :: vertmix_onoff, allow_doubling, allow_halving
-     integer(c_int) :: step
-     integer(c_int) :: no_wait
-  end type pmcgpu_trans_args_t
-
-  !> pmcgpu_dep_args (include/pmcgpu.h)
-  type, bind(c) :: pmcgpu_dep_args_t
-     type(c_ptr) :: rmol, znt, ust, ivgtyp, height
-     real(c_double) :: dt
-     integer(c_int) :: step
-     integer(c_int) :: no_wait
-  end type pmcgpu_dep_args_t
-
   !> Opaque device context of this MPI rank (one GPU per rank).
   type(c_ptr), save :: pmc_gpu_handle = c_null_ptr
   !> Counter that addresses the random draws: two values per WRF step.
   integer(c_int), save :: pmc_gpu_step = 0
-
-  interface
-     integer(c_int) function pmcgpu_create(cfg, ctx) bind(c, name='pmcgpu_create')
-       import :: c_int, c_ptr, pmcgpu_config_t
-       type(pmcgpu_config_t), intent(in) :: cfg
-       type(c_ptr), intent(out) :: ctx
-     end function pmcgpu_create
-     integer(c_int) function pmcgpu_destroy(ctx) bind(c, name='pmcgpu_destroy')
-       import :: c_int, c_ptr
-       type(c_ptr), value :: ctx
-     end function pmcgpu_destroy
-     type(c_ptr) function pmcgpu_last_error(ctx) bind(c, name='pmcgpu_last_error')
-       import :: c_ptr
-       type(c_ptr), value :: ctx
-     end function pmcgpu_last_error
-     integer(c_int) function pmcgpu_set_particles(ctx, cell_count, vol, wgroup, wclass, id, &
-          n_primary, hyst, lct, gct) bind(c, name='pmcgpu_set_particles')
-       import :: c_int, c_ptr
-       type(c_ptr), value :: ctx, cell_count, vol, wgroup, wclass, id, n_primary, hyst, lct, gct
-     end function pmcgpu_set_particles
-     integer(c_int) function pmcgpu_get_counts(ctx, cell_count) bind(c, name='pmcgpu_get_counts')
-       import :: c_int, c_ptr
-       type(c_ptr), value :: ctx, cell_count
-     end function pmcgpu_get_counts
-     integer(c_int) function pmcgpu_get_particles(ctx, n_total, vol, wgroup, wclass, id, &
-          n_primary, hyst, lct, gct) bind(c, name='pmcgpu_get_particles')
-       import :: c_int, c_ptr, c_long_long
-       type(c_ptr), value :: ctx
-       integer(c_long_long), value :: n_total
-       type(c_ptr), value :: vol, wgroup, wclass, id, n_primary, hyst, lct, gct
-     end function pmcgpu_get_particles
-     integer(c_int) function pmcgpu_set_weights(ctx, wtype, magnitude, exponent) &
-          bind(c, name='pmcgpu_set_weights')
-       import :: c_int, c_ptr
-       type(c_ptr), value :: ctx, wtype, magnitude, exponent
-     end function pmcgpu_set_weights
-     integer(c_int) function pmcgpu_get_weights(ctx, wtype, magnitude, exponent) &
-          bind(c, name='pmcgpu_get_weights')
-       import :: c_int, c_ptr
-       type(c_ptr), value :: ctx, wtype, magnitude, exponent
-     end function pmcgpu_get_weights
-     integer(c_int) function pmcgpu_set_env(ctx, temp, pressure, rel_humid, inverse_density, &
-          cell_volume) bind(c, name='pmcgpu_set_env')
-       import :: c_int, c_ptr
-       type(c_ptr), value :: ctx, temp, pressure, rel_humid, inverse_density, cell_volume
-     end function pmcgpu_set_env
-     integer(c_int) function pmcgpu_partmc_timestep(ctx, args) &
-          bind(c, name='pmcgpu_partmc_timestep')
-       import :: c_int, c_ptr, pmcgpu_timestep_args_t
-       type(c_ptr), value :: ctx
-       type(pmcgpu_timestep_args_t), intent(in) :: args
-     end function pmcgpu_partmc_timestep
-     integer(c_int) function pmcgpu_wrf_pmc_trans_driver(ctx, args) &
-          bind(c, name='pmcgpu_wrf_pmc_trans_driver')
-       import :: c_int, c_ptr, pmcgpu_trans_args_t
-       type(c_ptr), value :: ctx
-       type(pmcgpu_trans_args_t), intent(in) :: args
-     end function pmcgpu_wrf_pmc_trans_driver
-     integer(c_int) function pmcgpu_wrf_pmc_dep_dry_driver(ctx, args) &
-          bind(c, name='pmcgpu_wrf_pmc_dep_dry_driver')
-       import :: c_int, c_ptr, pmcgpu_dep_args_t
-       type(c_ptr), value :: ctx
-       type(pmcgpu_dep_args_t), intent(in) :: args
-     end function pmcgpu_wrf_pmc_dep_dry_driver
-     integer(c_int) function pmcgpu_check_status(ctx) bind(c, name='pmcgpu_check_status')
-       import :: c_int, c_ptr
-       type(c_ptr), value :: ctx
-     end function pmcgpu_check_status
-     integer(c_int) function pmcgpu_comm_unique_id(out, len) bind(c, name='pmcgpu_comm_unique_id')
-       import :: c_int, c_char
-       character(kind=c_char), intent(out) :: out(*)
-       integer(c_int), value :: len
-     end function pmcgpu_comm_unique_id
-     integer(c_int) function pmcgpu_comm_init(ctx, unique_id, n_ranks, rank, px, py) &
-          bind(c, name='pmcgpu_comm_init')
-       import :: c_int, c_ptr, c_char
-       type(c_ptr), value :: ctx
-       character(kind=c_char), intent(in) :: unique_id(*)
-       integer(c_int), value :: n_ranks, rank, px, py
-     end function pmcgpu_comm_init
-  end interface
+  !> The Fortran aero_states array is a mirror: .true. once the device holds the particles.
+  logical, save :: pmc_gpu_resident = .false.
 
 contains
 
@@ -364,70 +253,112 @@ contains
     end do
   end subroutine pmc_gpu_download_aero_states
 
-  !> Drop-in for partmc_timestep (interface/wrf_pmc_driver.F90:46-290): same argument list
-  !! (gas_data / gas_states / scenario are passed through untouched: gas chemistry, emissions
-  !! and MOSAIC are outside this library, SURVEY.md section 8f).
-  subroutine pmc_gpu_partmc_timestep(grid, config_flags, env_states, pmc_is, pmc_ie, pmc_js, &
-       pmc_je, pmc_ks, pmc_ke, global_nx, global_ny, global_nz)
+  !> partmc_timestep (interface/wrf_pmc_driver.F90:46-87), same name and argument list.  scenario, gas_data
+  !! and gas_states are passed through untouched: gas chemistry, emissions and MOSAIC are outside this
+  !! library (SURVEY.md section 8f) and keep their host code.
+  subroutine partmc_timestep(grid, config_flags, scenario, env_states, aero_data, aero_states, gas_data, &
+       gas_states, pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke, global_nx, global_ny, global_nz)
     use module_domain, only: domain, domain_get_time_since_sim_start
     use module_configure, only: grid_config_rec_type, p_qv
-    use module_model_constants, only: t0, p0 => p1000mb, rcp
     use pmc_env_state
+    use pmc_aero_data
+    use pmc_aero_state
+    use pmc_gas_data
+    use pmc_gas_state
+    use pmc_scenario
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
     type(domain), intent(inout) :: grid
     type(grid_config_rec_type), intent(in) :: config_flags
-    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
-    type(env_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), &
-         intent(inout) :: env_states
+    type(scenario_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: scenario
+    type(env_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: env_states
+    type(aero_data_t), intent(in) :: aero_data
+    type(aero_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: aero_states
+    type(gas_data_t), intent(in) :: gas_data
+    type(gas_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: gas_states
     integer, intent(in) :: global_nx, global_ny, global_nz
 
     type(pmcgpu_timestep_args_t) :: args
+    type(pmcgpu_wrf_fields_t) :: wf
     integer :: i, j, k, c, n_cells, n_class
-    real(c_double), allocatable, target :: temp(:), pres(:), rh(:), alt(:), cvol(:)
+    real(c_float), allocatable, target :: p(:,:,:), pb(:,:,:), t_2(:,:,:), qv(:,:,:), alt(:,:,:), z(:,:,:)
+    real(c_float), allocatable, target :: zw(:,:,:), msftx(:,:), msfty(:,:)
+    real(c_double), allocatable, target :: temp(:), pres(:), rh(:), rrho(:), cvol(:), height(:)
     real(c_float), allocatable, target :: num_conc(:)
-    real(kind=dp) :: pressure, qsat
     real :: real_time
 
     n_cells = (pmc_ie - pmc_is + 1) * (pmc_ke - pmc_ks + 1) * (pmc_je - pmc_js + 1)
-    n_class = size(grid%u_flux, 4) - 1
-    allocate(temp(n_cells), pres(n_cells), rh(n_cells), alt(n_cells), cvol(n_cells))
-    allocate(num_conc(n_cells * n_class))
-    ! wrf_to_partmc (wrf_pmc_driver.F90:576-644): the host part is the conversion of WRF's
-    ! perturbation fields; old_env_states is kept by the library
+    n_class = size(aero_states(pmc_is,pmc_ks,pmc_js)%awa%weight, 2)
+    if (.not. pmc_gpu_resident) then   ! first call: the particles move to the device and stay there
+       call pmc_gpu_upload_aero_states(aero_states, env_states, pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke)
+       pmc_gpu_resident = .true.
+    end if
+    ! wrf_to_partmc (wrf_pmc_driver.F90:576-644) on the device: contiguous copies of WRF's patch sections in
+    p = grid%p(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je)
+    pb = grid%pb(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je)
+    t_2 = grid%t_2(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je)
+    qv = grid%moist(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je, p_qv)
+    alt = grid%alt(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je)
+    z = grid%z(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je)
+    zw = grid%z_at_w(pmc_is:pmc_ie, pmc_ks:pmc_ke + 1, pmc_js:pmc_je)
+    msftx = grid%msftx(pmc_is:pmc_ie, pmc_js:pmc_je)
+    msfty = grid%msfty(pmc_is:pmc_ie, pmc_js:pmc_je)
+    wf%p = c_loc(p)
+    wf%pb = c_loc(pb)
+    wf%t_2 = c_loc(t_2)
+    wf%qv = c_loc(qv)
+    wf%alt = c_loc(alt)
+    wf%z = c_loc(z)
+    wf%z_at_w = c_loc(zw)
+    wf%msftx = c_loc(msftx)
+    wf%msfty = c_loc(msfty)
+    wf%rdx = grid%rdx
+    wf%rdy = grid%rdy
+    call pmc_gpu_check(pmcgpu_wrf_to_partmc(pmc_gpu_handle, wf), 'pmcgpu_wrf_to_partmc')
+    ! the host mirror of env_states (gas chemistry and emissions on the host read it)
+    allocate(temp(n_cells), pres(n_cells), rh(n_cells), rrho(n_cells), cvol(n_cells), height(n_cells))
+    call pmc_gpu_check(pmcgpu_get_env_staging(pmc_gpu_handle, c_loc(temp), c_loc(pres), c_loc(rh), &
+         c_loc(rrho), c_loc(cvol), c_loc(height)), 'pmcgpu_get_env_staging')
     c = 0
     do j = pmc_js, pmc_je
     do k = pmc_ks, pmc_ke
     do i = pmc_is, pmc_ie
        c = c + 1
-       pressure = grid%p(i,k,j) + grid%pb(i,k,j)
-       pres(c) = pressure
-       temp(c) = (grid%t_2(i,k,j) + t0) * (pressure / p0)**rcp
-       qsat = 3.8d0 * exp(17.27 * (temp(c) - 273.0d0) / (temp(c) - 36.0d0)) / (.01 * pressure)
-       rh(c) = max(.1d0, min(real(grid%moist(i,k,j,p_qv), dp) / qsat, .95d0))   ! rel_hum, :649-666
-       alt(c) = grid%alt(i,k,j)
-       cvol(c) = env_states(i,k,j)%cell_volume
+       env_states(i,k,j)%temp = temp(c)
+       env_states(i,k,j)%pressure = pres(c)
+       env_states(i,k,j)%rel_humid = rh(c)
+       env_states(i,k,j)%inverse_density = rrho(c)
+       env_states(i,k,j)%cell_volume = cvol(c)
+       env_states(i,k,j)%height = height(c)
+       env_states(i,k,j)%altitude = grid%z(i,k,j)
+       env_states(i,k,j)%z_min = grid%z_at_w(i,k,j)
+       env_states(i,k,j)%z_max = grid%z_at_w(i,k+1,j)
+       env_states(i,k,j)%elapsed_time = real(real_time(domain_get_time_since_sim_start(grid)), kind=dp)
     end do
     end do
     end do
-    args%temp = c_loc(temp)
-    args%pressure = c_loc(pres)
-    args%rel_humid = c_null_ptr          ! water uptake carries RH from step to step
-    args%inverse_density = c_loc(alt)
-    args%cell_volume = c_loc(cvol)
+    allocate(num_conc(n_cells * n_class))
+    ! NULL met pointers: the env_state staged by pmcgpu_wrf_to_partmc is installed, the previous one is kept as
+    ! old_env_states (wrf_pmc_driver.F90:615)
+    args%temp = c_null_ptr
+    args%pressure = c_null_ptr
+    args%rel_humid = c_null_ptr
+    args%inverse_density = c_null_ptr
+    args%cell_volume = c_null_ptr
     args%elapsed_time = real(real_time(domain_get_time_since_sim_start(grid)), kind=dp)
     args%dt = real(grid%dt, dp)
     args%chem_dt = real(grid%partmc_chem_dt, dp)
     args%do_coagulation = merge(1, 0, grid%do_coagulation)
     args%coag_kernel_type = PMCGPU_KERNEL_BROWN   ! wrf_pmc_driver.F90:192
     args%do_condensation = merge(1, 0, grid%do_mosaic)
-    args%allow_doubling = merge(1, 0, grid%allow_doubling)
-    args%allow_halving = merge(1, 0, grid%allow_halving)
+    args%allow_doubling = 1                       ! aero_state_rebalance(..., .true., .true., ...), :248
+    args%allow_halving = 1
     args%step = pmc_gpu_step
     args%num_conc_out = c_loc(num_conc)
-    args%rel_humid_out = c_null_ptr
+    args%rel_humid_out = c_loc(rh)
     args%no_wait = 0
     pmc_gpu_step = pmc_gpu_step + 1
     call pmc_gpu_check(pmcgpu_partmc_timestep(pmc_gpu_handle, args), 'pmcgpu_partmc_timestep')
-    ! partmc_to_wrf (wrf_pmc_driver.F90:1704-1719)
+    ! partmc_to_wrf (wrf_pmc_driver.F90:1704-1719), and the relative humidity the water uptake leaves behind
     c = 0
     do j = pmc_js, pmc_je
     do k = pmc_ks, pmc_ke
@@ -435,21 +366,32 @@ contains
        grid%chem(i,k,j,p_NUM_CONC_a01:p_NUM_CONC_a01 + n_class - 1) = &
             num_conc(c * n_class + 1:(c + 1) * n_class)
        c = c + 1
+       env_states(i,k,j)%rel_humid = rh(c)
     end do
     end do
     end do
-  end subroutine pmc_gpu_partmc_timestep
+  end subroutine partmc_timestep
 
-  !> Drop-in for wrf_pmc_trans_driver (interface/wrf_pmc_trans.F90:37-200): WRF's per-class
+  !> wrf_pmc_trans_driver (interface/wrf_pmc_trans.F90:37-76), same name and argument list: WRF's per-class
   !! advective fluxes and mixing coefficients of the patch (memory order i, k, j, class) go to
   !! the device; probabilities, sampling, ghost exchange and add + rebalance + sort run there.
-  subroutine pmc_gpu_wrf_pmc_trans_driver(grid, config_flags, pmc_is, pmc_ie, pmc_js, pmc_je, &
-       pmc_ks, pmc_ke, global_nx, global_ny, global_nz)
+  subroutine wrf_pmc_trans_driver(grid, config_flags, env_states, scenario, aero_data, aero_states, &
+       gas_states, pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke, global_nx, global_ny, global_nz)
     use module_domain, only: domain
     use module_configure, only: grid_config_rec_type
+    use pmc_env_state
+    use pmc_aero_data
+    use pmc_aero_state
+    use pmc_gas_state
+    use pmc_scenario
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
     type(domain), intent(inout) :: grid
     type(grid_config_rec_type), intent(in) :: config_flags
-    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    type(env_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: env_states
+    type(scenario_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: scenario
+    type(aero_data_t), intent(in) :: aero_data
+    type(aero_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: aero_states
+    type(gas_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: gas_states
     integer, intent(in) :: global_nx, global_ny, global_nz
 
     type(pmcgpu_trans_args_t) :: args
@@ -489,13 +431,13 @@ contains
          'pmcgpu_wrf_pmc_trans_driver')
     ! Do deposition on lowest layer (wrf_pmc_trans.F90:183-197)
     if (pmc_ks == 1 .and. grid%do_deposition) then
-       call pmc_gpu_wrf_pmc_dep_dry_driver(grid, pmc_is, pmc_ie, pmc_js, pmc_je)
+       call pmc_gpu_dep_dry(grid, pmc_is, pmc_ie, pmc_js, pmc_je)
     end if
-  end subroutine pmc_gpu_wrf_pmc_trans_driver
+  end subroutine wrf_pmc_trans_driver
 
   !> Drop-in for wrf_pmc_dep_dry_driver (interface/wrf_pmc_dep.F90:31): only the 2-D surface fields
   !> cross the boundary; the particles of the lowest layer are already on the device.
-  subroutine pmc_gpu_wrf_pmc_dep_dry_driver(grid, pmc_is, pmc_ie, pmc_js, pmc_je)
+  subroutine pmc_gpu_dep_dry(grid, pmc_is, pmc_ie, pmc_js, pmc_je)
     use module_domain, only: domain
     type(domain), intent(inout) :: grid
     integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je
@@ -523,6 +465,289 @@ contains
     pmc_gpu_step = pmc_gpu_step + 1
     call pmc_gpu_check(pmcgpu_wrf_pmc_dep_dry_driver(pmc_gpu_handle, args), &
          'pmcgpu_wrf_pmc_dep_dry_driver')
-  end subroutine pmc_gpu_wrf_pmc_dep_dry_driver
+  end subroutine pmc_gpu_dep_dry
+
+  !> wrf_pmc_dep_dry_driver (interface/wrf_pmc_dep.F90:31-60), same name and argument list.
+  subroutine wrf_pmc_dep_dry_driver(grid, config_flags, aero_data, aero_states, gas_states, env_states, &
+       pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke)
+    use module_domain, only: domain
+    use module_configure, only: grid_config_rec_type
+    use pmc_env_state
+    use pmc_aero_data
+    use pmc_aero_state
+    use pmc_gas_state
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    type(domain), intent(inout) :: grid
+    type(grid_config_rec_type), intent(in) :: config_flags
+    type(aero_data_t), intent(in) :: aero_data
+    type(aero_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: aero_states
+    type(gas_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: gas_states
+    type(env_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: env_states
+    call pmc_gpu_dep_dry(grid, pmc_is, pmc_ie, pmc_js, pmc_je)
+  end subroutine wrf_pmc_dep_dry_driver
+
+  !> trans_aero (interface/wrf_pmc_trans_aero.F90:40-76), same name and argument list (note k before j).  The
+  !! move probabilities it reads from module state in the reference (wrf_pmc_trans.F90:140-176) are computed
+  !! inside pmcgpu_wrf_pmc_trans_driver from the fields of `grid`, so this entry forwards to the driver.
+  subroutine trans_aero(grid, config_flags, aero_data, scenario, env_states, aero_states, pmc_is, pmc_ie, &
+       pmc_ks, pmc_ke, pmc_js, pmc_je, global_nx, global_ny, global_nz)
+    use module_domain, only: domain
+    use module_configure, only: grid_config_rec_type
+    use pmc_env_state
+    use pmc_aero_data
+    use pmc_aero_state
+    use pmc_gas_state
+    use pmc_scenario
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    type(domain), intent(inout) :: grid
+    type(grid_config_rec_type), intent(in) :: config_flags
+    type(aero_data_t), intent(in) :: aero_data
+    type(scenario_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: scenario
+    type(env_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: env_states
+    type(aero_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(inout) :: aero_states
+    integer, intent(in) :: global_nx, global_ny, global_nz
+    type(gas_state_t), allocatable :: no_gas(:,:,:)
+    allocate(no_gas(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je))
+    call wrf_pmc_trans_driver(grid, config_flags, env_states, scenario, aero_data, aero_states, no_gas, &
+         pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke, global_nx, global_ny, global_nz)
+  end subroutine trans_aero
+
+  ! ------------------------------------------------------------------------------------------------
+  ! PartMC-level entry points: one aero_state_t in, the same aero_state_t out.  Each call builds a one-cell
+  ! context (pmcgpu_create with nx = nz = ny = 1), uploads the state, runs the device routine for that cell
+  ! and copies the result back: the form run_part.F90 (:583 mc_coag, :599 condense_particles) needs.  A WRF
+  ! build never comes through here (its particles stay resident behind pmc_gpu_handle).
+  ! ------------------------------------------------------------------------------------------------
+
+  !> aero_state_t + env_state_t -> a fresh one-cell device context
+  subroutine box_open(aero_state, aero_data, env_state, box)
+    use pmc_aero_state
+    use pmc_aero_data
+    use pmc_env_state
+    type(aero_state_t), intent(in) :: aero_state
+    type(aero_data_t), intent(in), target :: aero_data
+    type(env_state_t), intent(in) :: env_state
+    type(c_ptr), intent(out) :: box
+
+    type(pmcgpu_config_t) :: cfg
+    integer :: p, n, n_spec, n_group, n_class, g, c
+    real(c_double), allocatable, target :: density(:), kappa(:), molec_weight(:), vol(:,:), lct(:), gct(:)
+    real(c_double), allocatable, target :: wmag(:), wexp(:), ideal(:), env1(:)
+    integer(c_int), allocatable, target :: num_ions(:), counts(:), wgroup(:), wclass(:), nprim(:), hyst(:), wtype(:)
+    integer(c_int64_t), allocatable, target :: ids(:)
+
+    n = aero_state_n_part(aero_state)
+    n_spec = aero_data_n_spec(aero_data)
+    n_group = size(aero_state%awa%weight, 1)
+    n_class = size(aero_state%awa%weight, 2)
+    density = aero_data%density
+    kappa = aero_data%kappa
+    molec_weight = aero_data%molec_weight
+    num_ions = aero_data%num_ions
+    cfg%n_spec = n_spec
+    cfg%density = c_loc(density)
+    cfg%kappa = c_loc(kappa)
+    cfg%molec_weight = c_loc(molec_weight)
+    cfg%num_ions = c_loc(num_ions)
+    cfg%i_water = aero_data%i_water
+    cfg%n_group = n_group
+    cfg%n_class = n_class
+    cfg%nx = 1
+    cfg%nz = 1
+    cfg%ny = 1
+    cfg%global_nx = 1
+    cfg%global_ny = 1
+    cfg%i_offset = 0
+    cfg%j_offset = 0
+    cfg%periodic_x = 1
+    cfg%periodic_y = 1
+    cfg%n_part_ideal = sum(aero_state%n_part_ideal)
+    cfg%cell_capacity = max(4 * n, int(2.5d0 * cfg%n_part_ideal)) + 64
+    cfg%max_bins = 255
+    cfg%seed = 1
+    cfg%device = 0
+    call pmc_gpu_check(pmcgpu_create(cfg, box), 'pmcgpu_create')
+    allocate(counts(1), vol(max(n, 1), n_spec), wgroup(max(n, 1)), wclass(max(n, 1)), ids(max(n, 1)), &
+         nprim(max(n, 1)), hyst(max(n, 1)), lct(max(n, 1)), gct(max(n, 1)))
+    counts(1) = n
+    do p = 1, n
+       vol(p, :) = aero_state%apa%particle(p)%vol
+       wgroup(p) = aero_state%apa%particle(p)%weight_group
+       wclass(p) = aero_state%apa%particle(p)%weight_class
+       ids(p) = aero_state%apa%particle(p)%id
+       nprim(p) = aero_state%apa%particle(p)%n_primary_parts
+       hyst(p) = aero_state%apa%particle(p)%water_hyst_leg
+       lct(p) = aero_state%apa%particle(p)%least_create_time
+       gct(p) = aero_state%apa%particle(p)%greatest_create_time
+    end do
+    call pmc_gpu_check(pmcgpu_set_particles(box, c_loc(counts), c_loc(vol), c_loc(wgroup), c_loc(wclass), &
+         c_loc(ids), c_loc(nprim), c_loc(hyst), c_loc(lct), c_loc(gct)), 'pmcgpu_set_particles')
+    allocate(wtype(n_group * n_class), wmag(n_group * n_class), wexp(n_group * n_class), ideal(n_group * n_class))
+    do c = 1, n_class
+       do g = 1, n_group      ! [class][group], group fastest (include/pmcgpu.h)
+          wtype((c - 1) * n_group + g) = aero_state%awa%weight(g, c)%type
+          wmag((c - 1) * n_group + g) = aero_state%awa%weight(g, c)%magnitude
+          wexp((c - 1) * n_group + g) = aero_state%awa%weight(g, c)%exponent
+          ideal((c - 1) * n_group + g) = aero_state%n_part_ideal(g, c)
+       end do
+    end do
+    call pmc_gpu_check(pmcgpu_set_weights(box, c_loc(wtype), c_loc(wmag), c_loc(wexp)), 'pmcgpu_set_weights')
+    call pmc_gpu_check(pmcgpu_set_n_part_ideal(box, c_loc(ideal)), 'pmcgpu_set_n_part_ideal')
+    allocate(env1(5))
+    env1 = (/ env_state%temp, env_state%pressure, env_state%rel_humid, env_state%inverse_density, &
+         env_state%cell_volume /)
+    call pmc_gpu_check(pmcgpu_set_env(box, c_loc(env1(1:1)), c_loc(env1(2:2)), c_loc(env1(3:3)), &
+         c_loc(env1(4:4)), c_loc(env1(5:5))), 'pmcgpu_set_env')
+  end subroutine box_open
+
+  !> device cell -> aero_state_t (particles and weight magnitudes), then the context is destroyed
+  subroutine box_close(box, aero_state, aero_data)
+    use pmc_aero_state
+    use pmc_aero_data
+    use pmc_aero_particle
+    type(c_ptr), intent(inout) :: box
+    type(aero_state_t), intent(inout) :: aero_state
+    type(aero_data_t), intent(in) :: aero_data
+
+    integer :: p, n, n_spec, n_group, n_class, g, c
+    integer(c_int), allocatable, target :: counts(:), wgroup(:), wclass(:), nprim(:), hyst(:), wtype(:)
+    integer(c_int64_t), allocatable, target :: ids(:)
+    real(c_double), allocatable, target :: vol(:,:), lct(:), gct(:), wmag(:), wexp(:)
+    type(aero_particle_t) :: particle
+
+    n_spec = aero_data_n_spec(aero_data)
+    n_group = size(aero_state%awa%weight, 1)
+    n_class = size(aero_state%awa%weight, 2)
+    allocate(counts(1))
+    call pmc_gpu_check(pmcgpu_get_counts(box, c_loc(counts)), 'pmcgpu_get_counts')
+    n = counts(1)
+    allocate(vol(max(n, 1), n_spec), wgroup(max(n, 1)), wclass(max(n, 1)), ids(max(n, 1)), nprim(max(n, 1)), &
+         hyst(max(n, 1)), lct(max(n, 1)), gct(max(n, 1)))
+    allocate(wtype(n_group * n_class), wmag(n_group * n_class), wexp(n_group * n_class))
+    call pmc_gpu_check(pmcgpu_get_particles(box, int(n, c_long_long), c_loc(vol), c_loc(wgroup), c_loc(wclass), &
+         c_loc(ids), c_loc(nprim), c_loc(hyst), c_loc(lct), c_loc(gct)), 'pmcgpu_get_particles')
+    call pmc_gpu_check(pmcgpu_get_weights(box, c_loc(wtype), c_loc(wmag), c_loc(wexp)), 'pmcgpu_get_weights')
+    call aero_state_zero(aero_state)        ! keeps awa and n_part_ideal
+    do c = 1, n_class
+       do g = 1, n_group
+          aero_state%awa%weight(g, c)%magnitude = wmag((c - 1) * n_group + g)
+       end do
+    end do
+    do p = 1, n
+       call aero_particle_zero(particle, aero_data)
+       particle%vol = vol(p, :)
+       particle%weight_group = wgroup(p)
+       particle%weight_class = wclass(p)
+       particle%id = ids(p)
+       particle%n_primary_parts = nprim(p)
+       particle%water_hyst_leg = hyst(p)
+       particle%least_create_time = lct(p)
+       particle%greatest_create_time = gct(p)
+       call aero_state_add_particle(aero_state, particle, aero_data, allow_resort=.false.)
+    end do
+    call pmc_gpu_check(pmcgpu_destroy(box), 'pmcgpu_destroy')
+    box = c_null_ptr
+  end subroutine box_close
+
+  !> mc_coag (partmc/src/coagulation.F90:43-59), same name and argument list.
+  subroutine mc_coag(coag_kernel_type, env_state, aero_data, aero_state, del_t, tot_n_samp, tot_n_coag)
+    use pmc_aero_state
+    use pmc_aero_data
+    use pmc_env_state
+    integer, intent(in) :: coag_kernel_type
+    type(env_state_t), intent(in) :: env_state
+    type(aero_data_t), intent(in) :: aero_data
+    type(aero_state_t), intent(inout) :: aero_state
+    real(kind=dp) :: del_t
+    integer, intent(out) :: tot_n_samp
+    integer, intent(out) :: tot_n_coag
+    type(c_ptr) :: box
+    integer(c_int), target :: ns(1), nc(1)
+    call box_open(aero_state, aero_data, env_state, box)
+    call pmc_gpu_check(pmcgpu_mc_coag(box, int(coag_kernel_type, c_int), del_t, pmc_gpu_step, c_loc(ns), &
+         c_loc(nc)), 'pmcgpu_mc_coag')
+    pmc_gpu_step = pmc_gpu_step + 1
+    tot_n_samp = ns(1)
+    tot_n_coag = nc(1)
+    call box_close(box, aero_state, aero_data)
+    aero_state%valid_sort = .false.
+  end subroutine mc_coag
+
+  !> condense_particles (partmc/src/condense.F90:147-161), same name and argument list;
+  !! env_state_final%rel_humid is overwritten with the integrator's value (:263).
+  subroutine condense_particles(aero_state, aero_data, env_state_initial, env_state_final, del_t)
+    use pmc_aero_state
+    use pmc_aero_data
+    use pmc_env_state
+    type(aero_state_t), intent(inout) :: aero_state
+    type(aero_data_t), intent(in) :: aero_data
+    type(env_state_t), intent(in) :: env_state_initial
+    type(env_state_t), intent(inout) :: env_state_final
+    real(kind=dp), intent(in) :: del_t
+    type(c_ptr) :: box
+    real(c_double), target :: t1(1), p1(1), rh(1)
+    call box_open(aero_state, aero_data, env_state_initial, box)
+    t1(1) = env_state_final%temp
+    p1(1) = env_state_final%pressure
+    call pmc_gpu_check(pmcgpu_set_rng_step(box, pmc_gpu_step), 'pmcgpu_set_rng_step')
+    pmc_gpu_step = pmc_gpu_step + 1
+    call pmc_gpu_check(pmcgpu_condense_particles(box, c_loc(t1), c_loc(p1), del_t, 0d0, c_loc(rh), &
+         c_null_ptr, c_null_ptr), 'pmcgpu_condense_particles')
+    env_state_final%rel_humid = rh(1)
+    call box_close(box, aero_state, aero_data)
+    aero_state%valid_sort = .false.     ! condense.F90:759
+  end subroutine condense_particles
+
+  !> aero_state_sort (partmc/src/aero_state.F90:3218), same name and argument list.  The device keeps its own
+  !! (class, bin)-ordered layout; on return the particle ARRAY is in that order and the host-side
+  !! aero_sorted of the mirror is rebuilt by the reference's own routine on next use (valid_sort = .false.).
+  !! A caller-supplied bin_grid / all_procs_same is not forwarded: the device always uses the adaptive
+  !! per-cell grid of aero_sorted_remake_if_needed (:214-373).
+  subroutine aero_state_sort(aero_state, aero_data, bin_grid, all_procs_same)
+    use pmc_aero_state
+    use pmc_aero_data
+    use pmc_bin_grid
+    use pmc_env_state
+    type(aero_state_t), intent(inout) :: aero_state
+    type(aero_data_t), intent(in) :: aero_data
+    type(bin_grid_t), optional, intent(in) :: bin_grid
+    logical, optional, intent(in) :: all_procs_same
+    type(c_ptr) :: box
+    type(env_state_t) :: env_state
+    env_state%temp = 288d0
+    env_state%pressure = 1d5
+    env_state%rel_humid = 0.5d0
+    env_state%inverse_density = 1d0
+    env_state%cell_volume = 1d0
+    call box_open(aero_state, aero_data, env_state, box)
+    call pmc_gpu_check(pmcgpu_aero_state_sort(box), 'pmcgpu_aero_state_sort')
+    call box_close(box, aero_state, aero_data)
+    aero_state%valid_sort = .false.
+  end subroutine aero_state_sort
+
+  !> aero_state_rebalance (partmc/src/aero_state.F90:1765), same name and argument list.
+  subroutine aero_state_rebalance(aero_state, aero_data, allow_doubling, allow_halving, initial_state_warning)
+    use pmc_aero_state
+    use pmc_aero_data
+    use pmc_env_state
+    type(aero_state_t), intent(inout) :: aero_state
+    type(aero_data_t), intent(in) :: aero_data
+    logical, intent(in) :: allow_doubling
+    logical, intent(in) :: allow_halving
+    logical, intent(in) :: initial_state_warning
+    type(c_ptr) :: box
+    type(env_state_t) :: env_state
+    env_state%temp = 288d0
+    env_state%pressure = 1d5
+    env_state%rel_humid = 0.5d0
+    env_state%inverse_density = 1d0
+    env_state%cell_volume = 1d0
+    call box_open(aero_state, aero_data, env_state, box)
+    call pmc_gpu_check(pmcgpu_aero_state_rebalance(box, merge(1, 0, allow_doubling), merge(1, 0, allow_halving), &
+         pmc_gpu_step), 'pmcgpu_aero_state_rebalance')
+    pmc_gpu_step = pmc_gpu_step + 1
+    call box_close(box, aero_state, aero_data)
+    aero_state%valid_sort = .false.
+  end subroutine aero_state_rebalance
 
 end module pmc_gpu

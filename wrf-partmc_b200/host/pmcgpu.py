@@ -78,6 +78,12 @@ class _TimestepArgs(C.Structure):
                 ("rel_humid_out", C.c_void_p), ("no_wait", C.c_int)]
 
 
+class _WrfFields(C.Structure):
+    _fields_ = [("p", C.c_void_p), ("pb", C.c_void_p), ("t_2", C.c_void_p), ("qv", C.c_void_p), ("alt", C.c_void_p),
+                ("z", C.c_void_p), ("z_at_w", C.c_void_p), ("msftx", C.c_void_p), ("msfty", C.c_void_p),
+                ("rdx", C.c_float), ("rdy", C.c_float)]
+
+
 class _DepArgs(C.Structure):
     _fields_ = [("rmol", C.c_void_p), ("znt", C.c_void_p), ("ust", C.c_void_p), ("ivgtyp", C.c_void_p),
                 ("height", C.c_void_p), ("dt", C.c_double), ("step", C.c_uint), ("no_wait", C.c_int)]
@@ -310,6 +316,24 @@ class PartMCGPU:
         a.num_conc_out, a.rel_humid_out = _addr(num_conc_out), _addr(rel_humid_out)
         a.no_wait = int(no_wait)
         self._chk(self.L.pmcgpu_partmc_timestep(self.h, C.byref(a)))
+
+    def wrf_to_partmc(self, p, pb, t_2, qv, alt, z_at_w, rdx, rdy, z=None, msftx=None, msfty=None):
+        """wrf_to_partmc (interface/wrf_pmc_driver.F90:576) on the device from WRF's `real` fields of the patch;
+        the result becomes the env_state of the next partmc_timestep called without met arrays.  Returns the
+        staged fields as a dict of [n_cells] arrays."""
+        a = _WrfFields()
+        keep = []
+        for k, x in (("p", p), ("pb", pb), ("t_2", t_2), ("qv", qv), ("alt", alt), ("z", z), ("z_at_w", z_at_w),
+                     ("msftx", msftx), ("msfty", msfty)):
+            if x is not None and isinstance(x, np.ndarray):
+                x = np.ascontiguousarray(x, dtype=np.float32)
+                keep.append(x)
+            setattr(a, k, _addr(x))
+        a.rdx, a.rdy = float(rdx), float(rdy)
+        self._chk(self.L.pmcgpu_wrf_to_partmc(self.h, C.byref(a)))
+        out = [np.zeros(self.n_cells) for _ in range(6)]
+        self._chk(self.L.pmcgpu_get_env_staging(self.h, *[_p(x) for x in out]))
+        return dict(zip(("temp", "pressure", "rel_humid", "inverse_density", "cell_volume", "height"), out))
 
     def wrf_pmc_trans_driver(self, fields, step=0, vertmix_onoff=1, allow_doubling=True, allow_halving=True,
                              no_wait=False):
