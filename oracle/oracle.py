@@ -233,6 +233,23 @@ class Oracle:
         self._chk(self.L.pmco_trans_setup(self.h, C.c_int(gnx), C.c_int(nz), C.c_int(gny), C.c_int(px), C.c_int(py),
                                           C.c_float(dx), C.c_float(dy), C.c_int(vertmix)))
 
+    def trans_set_boundary(self, open_domain, mode_type=None, weight_class=None, char_radius=None, log10_std_dev=None,
+                           vol_frac=None, num_conc=None, outflow=None, throw_away=None, vol_frac_std=None):
+        """open (non-periodic) domain and its boundary conditions: background modes (arrays [n_mode], vol_frac
+        [n_mode][n_spec]), num_conc [n_cells][n_mode], outflow / throw_away [n_cells] (global cell order)"""
+        if not open_domain:
+            self._chk(self.L.pmco_trans_set_boundary(self.h, C.c_int(0), C.c_int(0), *([None] * 9)))
+            return
+        ty, wc = _i32(mode_type), _i32(weight_class)
+        cr, ls, vf = _f64(char_radius), _f64(log10_std_dev), _f64(vol_frac)
+        vs = _f64(vol_frac_std)
+        nc, of, ta = _f64(num_conc), _i32(outflow), _i32(throw_away)
+        assert nc.size == self.n_cells * len(ty) and of.size == self.n_cells and ta.size == self.n_cells
+        self._chk(self.L.pmco_trans_set_boundary(self.h, C.c_int(1), C.c_int(len(ty)), _p(ty, C.c_int), _p(wc, C.c_int),
+                                                 _p(cr, C.c_double), _p(ls, C.c_double), _p(vf, C.c_double),
+                                                 _p(vs, C.c_double), _p(nc, C.c_double), _p(of, C.c_int),
+                                                 _p(ta, C.c_int)))
+
     def trans_set_met(self, f):
         """f: the dict of synthetic.transport_fields (global float32 arrays)"""
         a = [np.ascontiguousarray(f[k], dtype=np.float32) for k in

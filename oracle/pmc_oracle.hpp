@@ -73,7 +73,9 @@ enum Phase : uint32_t {
   PH_TRANS = 7,       // a = class*64 + direction slot, b = 0 (count) / transfer
   PH_INIT = 8,
   PH_DEP = 9,         // a = 0, b = particle index (dry deposition)
-  PH_EMIT = 10        // a = (group, mode), b = 0 (count) / sample number (aero_state_add_aero_dist_sample)
+  PH_EMIT = 10,       // a = (group, mode), b = 0 (count) / sample number (aero_state_add_aero_dist_sample)
+  PH_BND = 11         // aero_state_resample of a boundary cell: a = (group, class): b = 0 count, b >= 1 removal;
+                      // a = 1000 + (group, class) n_mode + mode: b = 0 count of the mode, b >= 1 new particle
 };
 struct RngKey {
   uint32_t cell, step, phase, a, b;

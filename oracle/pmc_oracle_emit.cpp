@@ -17,15 +17,6 @@
 
 namespace pmco {
 
-enum { MODE_LOG_NORMAL = 1, MODE_EXP = 2, MODE_MONO = 3 };  // aero_mode.F90:26-34
-
-struct AeroMode {
-  int type = MODE_LOG_NORMAL;
-  int weight_class = 1;
-  double char_radius = 1e-7, log10_std_dev_radius = 0.2, num_conc = 0.0;
-  std::vector<double> vol_frac, vol_frac_std;
-};
-
 // aero_mode.F90:496-544
 static double aero_mode_number(const AeroMode& m, const Weight& w) {
   if (m.type == MODE_LOG_NORMAL) {
@@ -59,7 +50,7 @@ static double rand_normal_threshold(double mean, double stddev, double prob_thre
 }
 
 // aero_mode.F90:549-628
-static double aero_mode_sample_radius(const AeroMode& m, const Weight& w, double prob_threshold, Stream& s) {
+double aero_mode_sample_radius(const AeroMode& m, const Weight& w, double prob_threshold, Stream& s) {
   if (m.type == MODE_LOG_NORMAL) {
     double x_mean_prime = std::log10(m.char_radius);
     if (w.type != WEIGHT_NONE)
@@ -74,7 +65,7 @@ static double aero_mode_sample_radius(const AeroMode& m, const Weight& w, double
 }
 
 // aero_mode.F90:633-668: accept-reject on non-negative volumes after projecting out the mean direction
-static void aero_mode_sample_vols(const AeroMode& m, double total_vol, std::vector<double>& vols, Stream& s) {
+void aero_mode_sample_vols(const AeroMode& m, double total_vol, std::vector<double>& vols, Stream& s) {
   const size_t S = m.vol_frac.size();
   vols.assign(S, 0.0);
   for (int i_sample = 1; i_sample <= 1000000; i_sample++) {

@@ -48,6 +48,20 @@ int condense_integrate(int n, double* D, double* H, const double* D_dry, const d
                        double T0, double p0, double Tdot, double pdot, double del_t, const CondenseOpts& opt,
                        CondenseStats& stats);
 
+// ---------------------------------------------------------------- emission / inflow sampling (pmc_oracle_emit.cpp)
+enum { MODE_LOG_NORMAL = 1, MODE_EXP = 2, MODE_MONO = 3 };  // aero_mode.F90:26-34
+struct AeroMode {
+  int type = MODE_LOG_NORMAL;
+  int weight_class = 1;
+  double char_radius = 1e-7, log10_std_dev_radius = 0.2, num_conc = 0.0;
+  std::vector<double> vol_frac, vol_frac_std;
+};
+double aero_mode_sample_radius(const AeroMode& m, const Weight& w, double prob_threshold, Stream& s);  // aero_mode.F90:549
+void aero_mode_sample_vols(const AeroMode& m, double total_vol, std::vector<double>& vols, Stream& s);  // :633
+int aero_state_add_aero_dist_sample(AeroState& st, const AeroData& d, const std::vector<AeroMode>& modes,
+                                    double sample_prop, double characteristic_factor, double create_time,
+                                    bool allow_doubling, bool allow_halving, const RunCtx& rc);         // aero_state.F90:758
+
 // ---------------------------------------------------------------- transport (pmc_oracle_trans.cpp)
 // Global doubly periodic domain of gnx x nz x gny cells, emulated px x py patch decomposition.
 // Indices are 1-based like the Fortran; fields are WRF `real` (float), class index slowest.
@@ -55,12 +69,34 @@ struct TransDomain {
   int gnx = 0, nz = 0, gny = 0, px = 1, py = 1, n_class = 1;
   float dx = 100.f, dy = 100.f, dt = 1.f;
   int vertmix = 1;
+  // open (non-periodic) domain: the outermost ring of cells holds the boundary condition
+  // (wrf_pmc_driver.F90:157-167, wrf_pmc_trans.F90:116-136, wrf_pmc_trans_aero.F90:689-766, 811-955)
+  bool open = false;
+  std::vector<AeroMode> bnd_modes;     // background aerosol (scenario%aero_background at the current time)
+  std::vector<double> bnd_num_conc;    // [cell][mode] number concentration of every mode in every boundary cell
+  std::vector<int> bnd_outflow;        // [cell] 1: the wind blows out of the domain there (dup from the neighbour)
+  std::vector<int> bnd_throw;          // [cell] 1: throw_away_previous (wind reversed / background changed)
+  // 0 interior, 1 west, 2 east, 3 south, 4 north edge, 5 corner (1-based global indices)
+  int kind(int i, int j) const {
+    if (!open) return 0;
+    const bool bi = (i == 1 || i == gnx), bj = (j == 1 || j == gny);
+    if (bi && bj) return 5;
+    if (i == 1) return 1;
+    if (i == gnx) return 2;
+    if (j == 1) return 3;
+    if (j == gny) return 4;
+    return 0;
+  }
   std::vector<float> u_flux, v_flux, w_flux, xkhh, alt, z, z_at_w, exch_h;
   // probabilities per (cell, class): adv -x +x -y +y -z +z; diff -x +x -y +y; vert[nz] (row of B* A)
   std::vector<double> adv, diff, vert;
   void setup(int gnx_, int nz_, int gny_, int px_, int py_, int n_class_);
   size_t cell(int i, int k, int j) const { return (size_t)(i - 1) + (size_t)gnx * ((size_t)(k - 1) + (size_t)nz * (j - 1)); }
   size_t cell_wrap(int i, int k, int j) const {
+    if (open) {  // fields beyond the domain: the host hands the nearest cell's value (zero-gradient halo)
+      const int ic = i < 1 ? 1 : (i > gnx ? gnx : i), jc = j < 1 ? 1 : (j > gny ? gny : j);
+      return cell(ic, k, jc);
+    }
     const int iw = ((i - 1) % gnx + gnx) % gnx + 1, jw = ((j - 1) % gny + gny) % gny + 1;
     return cell(iw, k, jw);
   }

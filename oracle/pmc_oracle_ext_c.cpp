@@ -162,6 +162,21 @@ int pmco_partmc_timestep(void* h, int cell_lo, int cell_hi, const double* T, con
         if (rrho) env.inverse_density = rrho[c];
         env.elapsed_time = elapsed_time;
         AeroState& st = d->cells[c];
+        if (d->trans.open) {
+          // open domain: wrf_to_partmc covers every cell, the aerosol step only the interior ones
+          // (wrf_pmc_driver.F90:157-167).  The device sorts every cell before mc_coag (particle ORDER only), so the
+          // boundary cells are sorted here too.
+          const int gi = c % d->trans.gnx + 1, gj = c / (d->trans.gnx * d->trans.nz) + 1;
+          if (d->trans.kind(gi, gj) != 0) {
+            if (chem && do_coag) {
+              st.valid_sort = false;
+              aero_state_sort(st);
+              aero_state_sort(st);
+              aero_state_physical_sort(st);
+            }
+            continue;
+          }
+        }
         if (chem && do_coag) {
           CoagStats cs;
           // the device keeps no sorting between steps: full sort (valid_sort = .false.), the bin-edge

@@ -214,8 +214,10 @@ void trans_compute_probs(OracleDomain& d) {
         compute_advect_probs_wrf(d, i, k, j);
         compute_diffusion_probs(d, i, k, j);
       }
+  std::fill(t.vert.begin(), t.vert.end(), 0.0);  // prob_vert_diffusion = 0 (wrf_pmc_trans.F90:104)
   for (int j = 1; j <= t.gny; j++)
-    for (int i = 1; i <= t.gnx; i++) compute_vertical_probs(d, i, j);
+    for (int i = 1; i <= t.gnx; i++)
+      if (t.kind(i, j) == 0) compute_vertical_probs(d, i, j);  // interior columns only in open domains (:116-136)
   for (int j = 1; j <= t.gny; j++)
     for (int k = 1; k <= t.nz; k++)
       for (int i = 1; i <= t.gnx; i++)
@@ -248,6 +250,146 @@ struct PreweightWork {
   std::vector<double> num_conc_new;             // [cell global][class], only owned cells used
   std::vector<double> ghost;                    // [4][edge cell][nz][class]
 };
+
+// aero_state_sample_particles_by_class (wrf_pmc_trans_aero.F90:2181-2322): particles of class c of cell g move
+// to (or are copied into) `out`, the delta state of cell gd, with probability adjusted_prob each; draw address
+// a = (c - 1) 64 + s.  Returns the number of records added to `out`.
+static long long sample_particles_by_class(OracleDomain& d, size_t g, size_t gd, int c, double adjusted_prob, int s,
+                                           std::vector<Particle>* out, const RunCtx& rc) {
+  AeroState& from = d.cells[g];
+  const double source_vol = d.env[g].cell_volume, dest_vol = d.env[gd].cell_volume;
+  pmc_assert(721006963, adjusted_prob >= 0.0 && adjusted_prob <= 1.0);
+  const double factor = source_vol / dest_vol;
+  const double mag_to = d.cells[gd].awa.at(1, c).magnitude * (1.0 / factor);
+  if (!from.valid_sort) aero_state_sort(from);
+  const double ratio = (mag_to / 1.0) / (from.awa.at(1, c).magnitude / 1.0);
+  const int n_part_from = aero_state_total_particles(from, 1, c);
+  const uint32_t a = (uint32_t)(c - 1) * 64u + (uint32_t)s;
+  Stream s0(rc.rng, rc.key(PH_TRANS, a, 0));
+  int n_transfer;
+  if (ratio >= 1.0) n_transfer = rand_binomial(n_part_from, adjusted_prob, s0);
+  else n_transfer = rand_poisson((double)n_part_from * (adjusted_prob / ratio), s0);
+  long long moved = 0;
+  int i_transfer = 0;
+  while (i_transfer < n_transfer) {
+    IntVarray& lst = from.sorted.group_class.inv(1, c);
+    if (lst.n_entry() <= 0) break;
+    i_transfer++;
+    const RngKey key = rc.key(PH_TRANS, a, (uint32_t)i_transfer);
+    const int i_entry = pmc_rand_int(rc.rng->uniform(key, 0), lst.n_entry());
+    const int i_part = lst.at(i_entry);
+    const Particle& pt = from.apa[i_part - 1];
+    // flat weights: num_conc = magnitude (aero_weight_array_num_conc, aero_weight_array.F90:257)
+    const double mix_rat_from = awa_num_conc(from.awa, pt);
+    Weight wto = d.cells[gd].awa.at(pt.weight_group, c);
+    wto.magnitude = wto.magnitude * (1.0 / factor);  // aero_weight_array_scale(awa, 1 / factor)
+    const double mix_rat_to = weight_num_conc_at_radius(wto, particle_radius(pt));
+    bool do_add, do_remove;
+    if (mix_rat_to == mix_rat_from) {
+      do_add = true; do_remove = true;
+    } else if (mix_rat_to < mix_rat_from) {
+      do_add = true;
+      do_remove = rc.rng->uniform(key, 1) < mix_rat_to / mix_rat_from;
+    } else {
+      do_add = rc.rng->uniform(key, 1) < mix_rat_from / mix_rat_to;
+      do_remove = true;
+    }
+    if (do_add) {
+      out->push_back(pt);
+      if (!do_remove) out->back().id = from.idgen.new_id();
+      moved++;
+    }
+    if (do_remove) aero_state_remove_particle(from, i_part);
+  }
+  return moved;
+}
+
+// aero_state_dup_all_particles (partmc/src/aero_state.F90:3529-3551): the whole state of `from` (particles,
+// weights, sorting, n_part_ideal) becomes the state of `to`, every particle with a new id; the id counter of
+// `to` is its own (one counter per cell: DESIGN.md section 2).
+static void aero_state_dup_all_particles(const AeroState& from, AeroState& to) {
+  const IdGen keep = to.idgen;
+  if (from.n_part() > 0) {
+    to = from;
+    to.idgen = keep;
+    for (Particle& p : to.apa) p.id = to.idgen.new_id();
+  } else {
+    to.apa.clear();  // aero_state_zero
+    to.valid_sort = false;
+    to.n_part_ideal = from.n_part_ideal;
+  }
+}
+
+// aero_state_resample (wrf_pmc_trans_aero.F90:976-1098): bring a boundary cell back to the background
+// distribution.  density = 1 / inverse_density, sample_prop = 1, create_time = 0, allow_doubling = allow_halving
+// = .true. at all call sites (:839-842).  Starts from a fresh sort (the device keeps no lists between phases).
+static int aero_state_resample(AeroState& st, const AeroData& data, const std::vector<AeroMode>& modes, double density,
+                               double create_time, bool throw_away_previous, const RunCtx& rc) {
+  const double sample_timescale = 1.0, factor = 0.1;
+  int n_part_add = 0;
+  if (throw_away_previous) {
+    st.apa.clear();  // aero_state_zero keeps awa and n_part_ideal
+    st.valid_sort = false;
+    return aero_state_add_aero_dist_sample(st, data, modes, density, sample_timescale, create_time, true, true, rc);
+  }
+  st.valid_sort = false;
+  aero_state_sort(st);
+  const int n_group = st.awa.n_group, n_class = st.awa.n_class, n_mode = (int)modes.size();
+  std::vector<double> vols;
+  for (int g = 1; g <= n_group; g++)
+    for (int c = 1; c <= n_class; c++) {
+      const uint32_t gc = (uint32_t)((c - 1) * n_group + (g - 1));
+      const int n_part_before = aero_state_total_particles(st, g, c);
+      double total_num_conc = 0.0;
+      for (const AeroMode& m : modes)
+        if (m.weight_class == c) total_num_conc = total_num_conc + m.num_conc * density;  // aero_mode_total_num_conc
+      const double n_parts_new = total_num_conc / st.awa.at(g, c).magnitude;
+      Stream s0(rc.rng, rc.key(PH_BND, gc, 0u));
+      const int n_samp = rand_poisson(n_parts_new, s0);
+      const int n_parts_to_add = n_samp - n_part_before;
+      if (n_parts_to_add > 0) {
+        for (int im = 1; im <= n_mode; im++) {
+          const AeroMode& m = modes[im - 1];
+          if (m.weight_class != c) continue;
+          const uint32_t am = 1000u + gc * (uint32_t)n_mode + (uint32_t)(im - 1);
+          const double sample_proportion = (density * m.num_conc) / total_num_conc;
+          Stream sm(rc.rng, rc.key(PH_BND, am, 0u));
+          const int n_samp_mode = rand_poisson(sample_proportion * (double)n_parts_to_add, sm);
+          const double n_samp_avg = sample_proportion * (double)n_parts_to_add;
+          const double num_conc_threshold = (density * m.num_conc / n_samp_avg) * factor;
+          const double size_factor = std::min(1.0 / (sample_timescale * n_samp_avg), 0.32);
+          for (int i_samp = 1; i_samp <= n_samp_mode; i_samp++) {
+            Stream s(rc.rng, rc.key(PH_BND, am, (uint32_t)i_samp));
+            const double radius = aero_mode_sample_radius(m, st.awa.at(g, c), size_factor, s);
+            const double total_vol = sphere_rad2vol(radius);
+            aero_mode_sample_vols(m, total_vol, vols, s);
+            Particle p;
+            p.vol = vols;
+            p.id = st.idgen.new_id();  // (an id is consumed whether or not the particle is kept, :1067)
+            p.weight_group = g;
+            p.weight_class = c;
+            p.least_create_time = create_time;
+            p.greatest_create_time = create_time;
+            p.n_primary_parts = 1;
+            p.water_hyst_leg = 0;
+            if (awa_num_conc(st.awa, p) > num_conc_threshold) {
+              aero_state_add_particle(st, p, true);
+              n_part_add++;
+            }
+          }
+        }
+      } else {
+        const int n_part = st.sorted.group_class.inv(g, c).n_entry();
+        const int n_rm = std::min(-n_parts_to_add, n_part);
+        for (int i_samp = 1; i_samp <= n_rm; i_samp++) {
+          IntVarray& lst = st.sorted.group_class.inv(g, c);
+          const int i_entry = pmc_rand_int(rc.rng->uniform(rc.key(PH_BND, gc, (uint32_t)i_samp), 0), lst.n_entry());
+          aero_state_remove_particle(st, lst.at(i_entry));
+        }
+      }
+    }
+  return n_part_add;
+}
 
 void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool allow_halving, int n_threads,
                     long long* n_moved_out) {
@@ -302,33 +444,35 @@ void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool al
       for (int k = 1; k <= nz; k++)
         for (int i = p.is; i <= p.ie; i++)
           for (int c = 1; c <= C; c++) {
-            // compute_fluxes (:1428-1624), ideal branch
+            // compute_fluxes (:1428-1624): ideal branch, or the "real case" branch of an open domain, where a
+            // boundary-edge cell only feeds its interior neighbour and a corner cell feeds nobody (:1517-1572)
             const size_t g = t.cell(i, k, j);
             const double nco = num_old[g * C + (c - 1)];
             const double source_vol = d.env[g].cell_volume;
             double& self = num_new[g * C + (c - 1)];
-            for (int dj = -1; dj <= 1; dj += 2) {
-              const double dest_vol = d.env[t.cell_wrap(i, k, j + dj)].cell_volume;
-              const double prob = hprob(t, g, c, dj < 0 ? 2 : 3);
+            const int kd = t.kind(i, j);
+            auto horizontal = [&](int di, int dj) {
+              const double dest_vol = d.env[t.cell_wrap(i + di, k, j + dj)].cell_volume;
+              const double prob = hprob(t, g, c, di < 0 ? 0 : (di > 0 ? 1 : (dj < 0 ? 2 : 3)));
               const double flux = prob * nco;
               double* dst;
               if (j + dj < p.js) dst = &gh[(size_t)r * 4 + 0][((size_t)(i - p.is) * nz + (k - 1)) * C + (c - 1)];
               else if (j + dj > p.je) dst = &gh[(size_t)r * 4 + 1][((size_t)(i - p.is) * nz + (k - 1)) * C + (c - 1)];
-              else dst = &num_new[t.cell(i, k, j + dj) * C + (c - 1)];
-              *dst = *dst + flux * (dest_vol / source_vol);
-              self = self - flux;
-            }
-            for (int di = -1; di <= 1; di += 2) {
-              const double dest_vol = d.env[t.cell_wrap(i + di, k, j)].cell_volume;
-              const double prob = hprob(t, g, c, di < 0 ? 0 : 1);
-              const double flux = prob * nco;
-              double* dst;
-              if (i + di < p.is) dst = &gh[(size_t)r * 4 + 2][((size_t)(j - p.js) * nz + (k - 1)) * C + (c - 1)];
+              else if (i + di < p.is) dst = &gh[(size_t)r * 4 + 2][((size_t)(j - p.js) * nz + (k - 1)) * C + (c - 1)];
               else if (i + di > p.ie) dst = &gh[(size_t)r * 4 + 3][((size_t)(j - p.js) * nz + (k - 1)) * C + (c - 1)];
-              else dst = &num_new[t.cell(i + di, k, j) * C + (c - 1)];
+              else dst = &num_new[t.cell(i + di, k, j + dj) * C + (c - 1)];
               *dst = *dst + flux * (dest_vol / source_vol);
               self = self - flux;
-            }
+            };
+            if (kd == 1) { horizontal(1, 0); continue; }
+            if (kd == 2) { horizontal(-1, 0); continue; }
+            if (kd == 3) { horizontal(0, 1); continue; }
+            if (kd == 4) { horizontal(0, -1); continue; }
+            if (kd == 5) continue;
+            horizontal(0, -1);
+            horizontal(0, 1);
+            horizontal(-1, 0);
+            horizontal(1, 0);
             for (int kk = 1; kk <= nz; kk++) {
               if (kk == k) continue;
               const double prob = t.vert[(g * C + (c - 1)) * nz + (kk - 1)];
@@ -348,6 +492,7 @@ void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool al
       const std::vector<double>& G = gh[(size_t)r * 4 + side];
       if (side < 2) {
         const int jd = (side == 0) ? p.js - 1 : p.je + 1;
+        if (t.open && (jd < 1 || jd > gny)) continue;
         for (int k = 1; k <= nz; k++)
           for (int i = p.is; i <= p.ie; i++)
             for (int c = 0; c < C; c++) {
@@ -357,6 +502,7 @@ void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool al
         (void)lx;
       } else {
         const int id = (side == 2) ? p.is - 1 : p.ie + 1;
+        if (t.open && (id < 1 || id > gnx)) continue;
         for (int j = p.js; j <= p.je; j++)
           for (int k = 1; k <= nz; k++)
             for (int c = 0; c < C; c++) {
@@ -403,6 +549,7 @@ void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool al
       for (int j = p.js; j <= p.je; j++)
         for (int k = 1; k <= nz; k++)
           for (int i = p.is; i <= p.ie; i++) {
+            if (t.kind(i, j) != 0) continue;  // open domain: interior cells only (:497-506)
             // aero_state_multisample (:2351-2482)
             const size_t g = t.cell(i, k, j);
             AeroState& from = d.cells[g];
@@ -431,56 +578,13 @@ void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool al
                 int di = 0, dj = 0, dk = k;
                 if (q < 4) { di = dir_di(q); dj = dir_dj(q); } else { dk = q - 4 + 1; }
                 const size_t gd = t.cell_wrap(i + di, dk, j + dj);
-                const double source_vol = d.env[g].cell_volume, dest_vol = d.env[gd].cell_volume;
-                // aero_state_sample_particles_by_class (:2181-2322)
-                pmc_assert(721006963, adjusted_prob >= 0.0 && adjusted_prob <= 1.0);
-                const double factor = source_vol / dest_vol;
-                const double mag_to = d.cells[gd].awa.at(1, c).magnitude * (1.0 / factor);
-                if (!from.valid_sort) aero_state_sort(from);
-                const double ratio = (mag_to / 1.0) / (from.awa.at(1, c).magnitude / 1.0);
-                const int n_part_from = aero_state_total_particles(from, 1, c);
-                const uint32_t a = (uint32_t)(c - 1) * 64u + (uint32_t)s;
-                Stream s0(rc.rng, rc.key(PH_TRANS, a, 0));
-                int n_transfer;
-                if (ratio >= 1.0) n_transfer = rand_binomial(n_part_from, adjusted_prob, s0);
-                else n_transfer = rand_poisson((double)n_part_from * (adjusted_prob / ratio), s0);
                 std::vector<Particle>* out;
                 if (j + dj < p.js) out = &halo[gd * 4 + 0];
                 else if (j + dj > p.je) out = &halo[gd * 4 + 1];
                 else if (i + di < p.is) out = &halo[gd * 4 + 2];
                 else if (i + di > p.ie) out = &halo[gd * 4 + 3];
                 else out = &delta[gd];
-                int i_transfer = 0;
-                while (i_transfer < n_transfer) {
-                  IntVarray& lst = from.sorted.group_class.inv(1, c);
-                  if (lst.n_entry() <= 0) break;
-                  i_transfer++;
-                  const RngKey key = rc.key(PH_TRANS, a, (uint32_t)i_transfer);
-                  const int i_entry = pmc_rand_int(rc.rng->uniform(key, 0), lst.n_entry());
-                  const int i_part = lst.at(i_entry);
-                  const Particle& pt = from.apa[i_part - 1];
-                  // flat weights: num_conc = magnitude (aero_weight_array_num_conc, aero_weight_array.F90:257)
-                  const double mix_rat_from = awa_num_conc(from.awa, pt);
-                  Weight wto = d.cells[gd].awa.at(pt.weight_group, c);
-                  wto.magnitude = wto.magnitude * (1.0 / factor);  // aero_weight_array_scale(awa, 1 / factor)
-                  const double mix_rat_to = weight_num_conc_at_radius(wto, particle_radius(pt));
-                  bool do_add, do_remove;
-                  if (mix_rat_to == mix_rat_from) {
-                    do_add = true; do_remove = true;
-                  } else if (mix_rat_to < mix_rat_from) {
-                    do_add = true;
-                    do_remove = rc.rng->uniform(key, 1) < mix_rat_to / mix_rat_from;
-                  } else {
-                    do_add = rc.rng->uniform(key, 1) < mix_rat_from / mix_rat_to;
-                    do_remove = true;
-                  }
-                  if (do_add) {
-                    out->push_back(pt);
-                    if (!do_remove) out->back().id = from.idgen.new_id();
-                    moved[r]++;
-                  }
-                  if (do_remove) aero_state_remove_particle(from, i_part);
-                }
+                moved[r] += sample_particles_by_class(d, g, gd, c, adjusted_prob, s, out, rc);
                 remainder_prob = remainder_prob - prob;
               }
             }
@@ -498,13 +602,39 @@ void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool al
       delta[g].insert(delta[g].end(), h.begin(), h.end());
       h.clear();
     }
-  // ---- add, rebalance, sort (:777-804)
+  // ---- open domain: inflow from the boundary cells into their interior neighbours (:689-766), appended behind
+  // the ghost arrivals, in the order west, east, south, north
+  if (t.open) {
+    for (int r = 0; r < n_rank; r++) {
+      const Patch p = patch_of(t, r);
+      auto inflow = [&](int i, int j, int di, int dj, int dslot) {
+        for (int k = 1; k <= nz; k++) {
+          const size_t g = t.cell(i, k, j), gd = t.cell(i + di, k, j + dj);
+          RunCtx rc{d.rng.get(), (uint32_t)d.global_cell[g], step};
+          for (int c = 1; c <= C; c++) {
+            const double prob = std::min(hprob(t, g, c, dslot), 1.0);
+            moved[r] += sample_particles_by_class(d, g, gd, c, prob, 0, &delta[gd], rc);
+          }
+        }
+      };
+      if (p.is == 1)
+        for (int j = std::max(p.js, 2); j <= std::min(p.je, gny - 1); j++) inflow(1, j, 1, 0, 1);
+      if (p.ie == gnx)
+        for (int j = std::max(p.js, 2); j <= std::min(p.je, gny - 1); j++) inflow(gnx, j, -1, 0, 0);
+      if (p.js == 1)
+        for (int i = std::max(p.is, 2); i <= std::min(p.ie, gnx - 1); i++) inflow(i, 1, 0, 1, 3);
+      if (p.je == gny)
+        for (int i = std::max(p.is, 2); i <= std::min(p.ie, gnx - 1); i++) inflow(i, gny, 0, -1, 2);
+    }
+  }
+  // ---- add, rebalance, sort (:777-804): interior cells (all cells of a periodic domain)
   par_ranks([&](int r) {
     const Patch p = patch_of(t, r);
     try {
       for (int j = p.js; j <= p.je; j++)
         for (int k = 1; k <= nz; k++)
           for (int i = p.is; i <= p.ie; i++) {
+            if (t.kind(i, j) != 0) continue;
             const size_t g = t.cell(i, k, j);
             AeroState& st = d.cells[g];
             RunCtx rc{d.rng.get(), (uint32_t)d.global_cell[g], step};
@@ -521,6 +651,33 @@ void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool al
   });
   for (int r = 0; r < n_rank; r++)
     if (err[r]) throw PmcError(err[r], "trans_aero add/rebalance/sort failed");
+  // ---- open domain: refresh of the boundary cells (:811-955): a copy of the interior neighbour where the wind
+  // blows out of the domain, a resample of the background distribution where it blows in
+  if (t.open) {
+    if (t.bnd_outflow.size() != n_cells || t.bnd_throw.size() != n_cells ||
+        t.bnd_num_conc.size() != n_cells * t.bnd_modes.size())
+      throw PmcError(-2, "open domain: boundary conditions not set (pmco_trans_set_boundary)");
+    try {
+      for (int j = 1; j <= gny; j++)
+        for (int k = 1; k <= nz; k++)
+          for (int i = 1; i <= gnx; i++) {
+            const int kd = t.kind(i, j);
+            if (kd < 1 || kd > 4) continue;
+            const size_t g = t.cell(i, k, j);
+            const size_t gn = t.cell(i + (kd == 1 ? 1 : (kd == 2 ? -1 : 0)), k, j + (kd == 3 ? 1 : (kd == 4 ? -1 : 0)));
+            RunCtx rc{d.rng.get(), (uint32_t)d.global_cell[g], step};
+            if (t.bnd_outflow[g]) {
+              aero_state_dup_all_particles(d.cells[gn], d.cells[g]);
+            } else {
+              std::vector<AeroMode> modes = t.bnd_modes;
+              for (size_t m = 0; m < modes.size(); m++) modes[m].num_conc = t.bnd_num_conc[g * modes.size() + m];
+              aero_state_resample(d.cells[g], d.data, modes, 1.0 / d.env[g].inverse_density, 0.0, t.bnd_throw[g] != 0, rc);
+            }
+          }
+    } catch (const PmcError& e) {
+      throw PmcError(e.code ? e.code : -1, "boundary refresh failed");
+    }
+  }
   if (n_moved_out) {
     long long m = 0;
     for (int r = 0; r < n_rank; r++) m += moved[r];
@@ -560,6 +717,33 @@ int pmco_trans_set_met(void* h, const float* u_flux, const float* v_flux, const 
   t.z.assign(z, z + nx * nz * ny);
   t.z_at_w.assign(z_at_w, z_at_w + nx * (nz + 1) * ny);
   t.exch_h.assign(exch_h, exch_h + nx * (nz + 1) * ny);
+  return 0;
+}
+// open domain: switch + boundary conditions.  Mode tables like pmco_add_aero_dist_sample; num_conc [n_cells][n_mode],
+// outflow / throw_away [n_cells] (read for the boundary-edge cells only), all in global cell order.
+int pmco_trans_set_boundary(void* h, int open, int n_mode, const int* type, const int* weight_class,
+                            const double* char_radius, const double* log10_std, const double* vol_frac,
+                            const double* vol_frac_std, const double* num_conc, const int* outflow,
+                            const int* throw_away) {
+  OracleDomain* d = (OracleDomain*)h;
+  TransDomain& t = d->trans;
+  t.open = open != 0;
+  if (!t.open) return 0;
+  const size_t S = (size_t)d->data.n_spec, nc = d->cells.size();
+  t.bnd_modes.assign((size_t)n_mode, AeroMode());
+  for (int m = 0; m < n_mode; m++) {
+    AeroMode& am = t.bnd_modes[m];
+    am.type = type[m];
+    am.weight_class = weight_class[m];
+    am.char_radius = char_radius[m];
+    am.log10_std_dev_radius = log10_std[m];
+    am.vol_frac.assign(vol_frac + (size_t)m * S, vol_frac + (size_t)(m + 1) * S);
+    if (vol_frac_std) am.vol_frac_std.assign(vol_frac_std + (size_t)m * S, vol_frac_std + (size_t)(m + 1) * S);
+    else am.vol_frac_std.assign(S, 0.0);
+  }
+  t.bnd_num_conc.assign(num_conc, num_conc + nc * (size_t)n_mode);
+  t.bnd_outflow.assign(outflow, outflow + nc);
+  t.bnd_throw.assign(throw_away, throw_away + nc);
   return 0;
 }
 int pmco_trans_probs(void* h, float dt) {

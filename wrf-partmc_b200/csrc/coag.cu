@@ -635,7 +635,7 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevV
   cx.err = 0;
   int tot_n_samp = 0, tot_n_coag = 0;
   const int nb = cx.nb;
-  if (v.status[cell] != 0 || nb < 1 || cx.n_part == 0) {
+  if (v.status[cell] != 0 || nb < 1 || cx.n_part == 0 || cell_is_boundary(v, cell)) {
     if (lane == 0) {
       v.coag_samp[cell] = 0;
       v.coag_ncoag[cell] = 0;

@@ -644,7 +644,7 @@ __global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /*
   for (int cell = GRID ? 0 : blockIdx.x; cell < (GRID ? v.n_cells : (int)blockIdx.x + 1); cell++) {
   const int n = v.count[cell];
   if (n <= n_limit_lo || n > n_limit_hi) continue;  // another instantiation owns this cell
-  if (v.status[cell] != 0) continue;
+  if (v.status[cell] != 0 || cell_is_boundary(v, cell)) continue;
   const int tid = threadIdx.x;
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
@@ -1069,7 +1069,7 @@ __global__ void __launch_bounds__(NT) k_condense_bdf(DevView v, const double* T0
   const int cell = blockIdx.x;
   const int n = v.count[cell];
   if (n <= n_limit_lo || n > n_limit_hi) return;  // another instantiation owns this cell
-  if (v.status[cell] != 0) return;
+  if (v.status[cell] != 0 || cell_is_boundary(v, cell)) return;
   const int tid = threadIdx.x;
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;

@@ -104,7 +104,6 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   double *d_density, *d_kappa, *d_molw;
   int* d_nions;
   A(d_density, v.S) A(d_kappa, v.S) A(d_molw, v.S) A(d_nions, v.S)
-#undef A
   CUDA_OK(ctx, cudaMemcpyAsync(d_density, cfg->density, v.S * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   std::vector<double> zero((size_t)v.S, 0.0), mw((size_t)v.S, 18e-3);
   std::vector<int> zi((size_t)v.S, 0);
@@ -126,6 +125,33 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   ctx->h_density.assign(cfg->density, cfg->density + v.S);
   v.dens_min = *std::min_element(ctx->h_density.begin(), ctx->h_density.end());
   v.dens_max = *std::max_element(ctx->h_density.begin(), ctx->h_density.end());
+  if (!cfg->periodic_x || !cfg->periodic_y) {
+    // The reference treats every domain that is not doubly periodic as open in both directions
+    // (get_array_extents, wrf_pmc_trans_aero.F90:1665-1705)
+    if (cfg->periodic_x || cfg->periodic_y) {
+      ctx->err = "a domain periodic in one direction only is not supported (the reference treats it as open in both)";
+      *out = ctx;
+      return PMCGPU_ERR_ARG;
+    }
+    if (cfg->global_nx < 3 || cfg->global_ny < 3 || (cfg->i_offset == 0 && cfg->nx < 2) || (cfg->j_offset == 0 && cfg->ny < 2) ||
+        (cfg->i_offset + cfg->nx == cfg->global_nx && cfg->nx < 2) || (cfg->j_offset + cfg->ny == cfg->global_ny && cfg->ny < 2)) {
+      ctx->err = "open domain: a patch on the domain edge must hold the boundary cells and their interior neighbours";
+      *out = ctx;
+      return PMCGPU_ERR_ARG;
+    }
+    std::vector<unsigned char> kind((size_t)v.n_cells, 0);
+    for (int c = 0; c < v.n_cells; c++) {
+      const int gi = cfg->i_offset + c % cfg->nx, gj = cfg->j_offset + c / (cfg->nx * cfg->nz);
+      const bool bi = (gi == 0 || gi == cfg->global_nx - 1), bj = (gj == 0 || gj == cfg->global_ny - 1);
+      kind[c] = (bi && bj) ? 5 : (gi == 0 ? 1 : (gi == cfg->global_nx - 1 ? 2 : (gj == 0 ? 3 : (gj == cfg->global_ny - 1 ? 4 : 0))));
+    }
+    unsigned char* dk = nullptr;
+    A(dk, (size_t)v.n_cells)
+    CUDA_OK(ctx, cudaMemcpyAsync(dk, kind.data(), kind.size(), cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+    v.kind = dk;
+  }
+#undef A
   k_init_cells<<<(v.n_cells + 255) / 256, 256, 0, ctx->stream>>>(v, cfg->i_offset, cfg->j_offset, cfg->nx, cfg->nz,
                                                                   cfg->ny, cfg->global_nx);
   LAUNCH_CHECK(ctx);
@@ -457,6 +483,10 @@ int pmc_first_status(pmcgpu_ctx* ctx) {
 __global__ void k_update_density(DevView v, const double* __restrict__ new_rrho) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= v.n_cells) return;
+  if (cell_is_boundary(v, c)) {  // scenario_update_aero_state runs for interior cells only; env_state is set everywhere
+    v.rrho[c] = new_rrho[c];
+    return;
+  }
   const double f = v.rrho[c] * (1.0 / new_rrho[c]);
   for (int q = 0; q < v.C * v.G; q++) v.wmag[(size_t)c * v.C * v.G + q] *= f;
   v.rrho[c] = new_rrho[c];

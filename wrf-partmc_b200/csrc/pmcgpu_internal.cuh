@@ -14,7 +14,7 @@
 
 // draw-address phases; must agree with the documented stream layout
 enum : uint32_t {
-  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8, PH_DEP = 9, PH_EMIT = 10
+  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8, PH_DEP = 9, PH_EMIT = 10, PH_BND = 11
 };
 
 struct PmcConst {  // partmc/src/constants.F90:30-65
@@ -97,6 +97,11 @@ struct DevView {
   // particles of the cell, summed over cells and calls), [1] particles condense_particles integrated,
   // [2] particles at the start of partmc_timestep (particle-timesteps), [3] spare
   unsigned long long* work;
+  // open (non-periodic) domain: kind of every cell, nullptr for a doubly periodic domain.  0 interior, 1 west,
+  // 2 east, 3 south, 4 north edge of the GLOBAL domain, 5 corner.  The outermost ring holds the boundary condition:
+  // the aerosol step and the multinomial transport sampling cover interior cells only
+  // (wrf_pmc_driver.F90:157-167, wrf_pmc_trans.F90:116-136, wrf_pmc_trans_aero.F90:497-506)
+  const unsigned char* kind;
 };
 
 // Transport work space of one patch (trans.cu).  "ext" arrays carry a one-cell ghost ring in x and y:
@@ -171,6 +176,11 @@ struct pmcgpu_ctx {
   bool cfg_trans_smem = false, cfg_cond = false, cfg_cond_grid = false, cfg_sort = false;  // per-context (= per-device) opt-ins
   int cond_n_sm = 0, cond_max_blk4 = 0, cond_max_blk8 = 0;
   size_t cfg_msamp_smem = 0, cfg_kmax_smem = 0, cfg_sort_smem = 0, cfg_sort_staged_smem = 0;
+  // boundary conditions of an open domain (pmcgpu_set_boundary): device copies
+  int bnd_n_mode = 0;
+  char* bnd_buf = nullptr;
+  int *bnd_type = nullptr, *bnd_wclass = nullptr, *bnd_outflow = nullptr, *bnd_throw = nullptr;
+  double *bnd_cr = nullptr, *bnd_ls = nullptr, *bnd_vf = nullptr, *bnd_vs = nullptr, *bnd_nc = nullptr;
   bool w2p_ready = false;           // pmcgpu_wrf_to_partmc has staged an env_state for the next partmc_timestep
   int kmax_ktype = 0;               // kernel type the per-cell majorant tables were built for
   // patch neighbours (rank of the patch on side s; this rank itself on a periodic single patch)
@@ -266,6 +276,8 @@ struct ProfScope {
 // device math
 // ---------------------------------------------------------------------------
 #ifdef __CUDACC__
+// cell of an open domain that takes no part in the aerosol step (a boundary-condition cell)
+__device__ __forceinline__ bool cell_is_boundary(const DevView& v, int cell) { return v.kind != nullptr && v.kind[cell] != 0; }
 
 // Philox4x32-10 (Salmon et al. SC'11).  Address = (cell, step, phase, a, b, j):
 // counter = (j>>1, b, a, cell), key = (seed, step*16 + phase); one block yields

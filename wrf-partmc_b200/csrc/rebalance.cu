@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_rebalance(DevView v, int all
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * REB_WARPS + warp;
   if (cell >= v.n_cells) return;
-  if (v.status[cell] != 0) return;
+  if (v.status[cell] != 0 || cell_is_boundary(v, cell)) return;
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
   int n_part = v.count[cell];
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_reweight(DevView v, unsigned
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * REB_WARPS + warp;
   if (cell >= v.n_cells) return;
-  if (v.status[cell] != 0) return;
+  if (v.status[cell] != 0 || cell_is_boundary(v, cell)) return;
   const int ngc = v.C * v.G;
   const size_t wb = (size_t)cell * ngc;
   bool nonflat = false;

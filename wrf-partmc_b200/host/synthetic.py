@@ -109,7 +109,7 @@ def met_sequence(case, n_steps, dT=-0.4, dp=-400.0, period=8):
 
 
 def transport_fields(case, num_conc, courant_x=0.3, courant_y=0.2, courant_z=0.05, xkhh=10.0, dx=100.0, dy=100.0,
-                     dt=6.0, seed=3):
+                     dt=6.0, seed=3, periodic=True):
     """WRF-side inputs of wrf_pmc_trans_driver for the doubly periodic patch of `case`, as global arrays in WRF
     memory order (i fastest, then k, then j; class slowest), all float32 like WRF's `real`:
       u_flux [(nx+1), nz, ny, C], v_flux [nx, nz, (ny+1), C], w_flux [nx, (nz+1), ny, C]  per-class advective
@@ -136,11 +136,17 @@ def transport_fields(case, num_conc, courant_x=0.3, courant_y=0.2, courant_z=0.0
     w_flux = np.zeros((C, ny, nz + 1, nx), np.float32)
     for c in range(C):
         qc = q[:, :, :, c]
-        left = np.concatenate([qc[:, :, -1:], qc], axis=2)   # cell i-1 of face i (periodic)
-        right = np.concatenate([qc, qc[:, :, :1]], axis=2)   # cell i of face i
+        if periodic:
+            left = np.concatenate([qc[:, :, -1:], qc], axis=2)   # cell i-1 of face i (periodic)
+            right = np.concatenate([qc, qc[:, :, :1]], axis=2)   # cell i of face i
+            south = np.concatenate([qc[-1:], qc], axis=0)
+            north = np.concatenate([qc, qc[:1]], axis=0)
+        else:  # open domain: the outermost cells stand for what lies beyond the domain faces
+            left = np.concatenate([qc[:, :, :1], qc], axis=2)
+            right = np.concatenate([qc, qc[:, :, -1:]], axis=2)
+            south = np.concatenate([qc[:1], qc], axis=0)
+            north = np.concatenate([qc, qc[-1:]], axis=0)
         u_flux[c] = np.where(cx > 0, cx * left, cx * right)
-        south = np.concatenate([qc[-1:], qc], axis=0)
-        north = np.concatenate([qc, qc[:1]], axis=0)
         v_flux[c] = np.where(cy > 0, cy * south, cy * north)
         below = np.concatenate([qc[:, :1], qc], axis=1)
         above = np.concatenate([qc, qc[:, -1:]], axis=1)
@@ -156,14 +162,19 @@ def transport_fields(case, num_conc, courant_x=0.3, courant_y=0.2, courant_z=0.0
                 dx=np.float32(dx), dy=np.float32(dy), dt=np.float32(dt))
 
 
-def patch_fields(f, i0, nxl, j0, nyl):
+def patch_fields(f, i0, nxl, j0, nyl, periodic=True):
     """The slabs of the global transport fields a rank owning cells [i0, i0+nxl) x [j0, j0+nyl) hands to the
-    library: staggered flux arrays of the patch, xkhh / alt with a one-cell periodic halo in x and y."""
+    library: staggered flux arrays of the patch, xkhh / alt with a one-cell halo in x and y (periodic wrap, or
+    the nearest cell's value beyond the faces of an open domain)."""
     ny, nz, nx = f["alt"].shape
     ii = np.arange(i0, i0 + nxl)
     jj = np.arange(j0, j0 + nyl)
-    iih = np.arange(i0 - 1, i0 + nxl + 1) % nx
-    jjh = np.arange(j0 - 1, j0 + nyl + 1) % ny
+    if periodic:
+        iih = np.arange(i0 - 1, i0 + nxl + 1) % nx
+        jjh = np.arange(j0 - 1, j0 + nyl + 1) % ny
+    else:
+        iih = np.clip(np.arange(i0 - 1, i0 + nxl + 1), 0, nx - 1)
+        jjh = np.clip(np.arange(j0 - 1, j0 + nyl + 1), 0, ny - 1)
     out = dict(dx=f["dx"], dy=f["dy"], dt=f["dt"])
     out["u_flux"] = np.ascontiguousarray(f["u_flux"][:, jj][:, :, :, np.arange(i0, i0 + nxl + 1)])
     out["v_flux"] = np.ascontiguousarray(f["v_flux"][:, np.arange(j0, j0 + nyl + 1)][:, :, :, ii])
