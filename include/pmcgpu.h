@@ -240,7 +240,7 @@ int pmcgpu_check_status(pmcgpu_ctx* ctx);
  * (compute_advect_probs_wrf :205, compute_diffusion_probs :358, compute_vertical_probs :414, normalize_probs
  * :692) from WRF's per-class advective fluxes and mixing coefficients, then trans_aero
  * (interface/wrf_pmc_trans_aero.F90:40-971: preweighting, multinomial sampling of the moves, ghost exchange,
- * add + rebalance + sort).  Doubly periodic domains (config_flags%periodic_x .and. periodic_y).
+ * add + rebalance + sort).  Doubly periodic domains, or open domains (see pmcgpu_set_boundary).
  * Field slabs are WRF `real` arrays of the patch in WRF memory order (i fastest, then k, then j; the class
  * index slowest), in host or device memory; NULL keeps the previous call's values:
  *   u_flux [(nx+1) nz ny n_class]   grid%u_flux(i, k, j, 1 + class), staggered in x (faces i .. i+1)
@@ -261,6 +261,34 @@ typedef struct {
   int no_wait;
 } pmcgpu_trans_args;
 int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_args* args);
+
+/* Open (non-periodic) domains: pmcgpu_config.periodic_x = periodic_y = 0.  The outermost ring of cells of the GLOBAL
+ * domain then holds the boundary condition, like in the reference: pmcgpu_partmc_timestep runs the aerosol step
+ * on interior cells only (wrf_pmc_driver.F90:157-167), pmcgpu_wrf_pmc_trans_driver samples the multinomial moves of
+ * interior cells only (wrf_pmc_trans.F90:116-136, wrf_pmc_trans_aero.F90:497-506), feeds the first interior cells
+ * from the boundary cells (boundary inflow, :689-766), and finally refreshes every boundary-edge cell (:811-955):
+ *   outflow[cell] != 0 (the wind blows out of the domain there: u_2 < 0 on the west face, ...):
+ *       aero_state_dup_all_particles (aero_state.F90:3529) from the interior neighbour;
+ *   else aero_state_resample (wrf_pmc_trans_aero.F90:976-1098) towards the background distribution, with
+ *       throw_away[cell] != 0 (wind reversed since the last step, or the background changed) discarding the cell
+ *       first.  density = 1 / inverse_density, allow_doubling = allow_halving = true as at the reference's call sites.
+ * The background (scenario%aero_background interpolated to the current time, aero_dist_interp_1d) is a list of modes
+ * like pmcgpu_emit_args; num_conc [n_cells][n_mode], outflow and throw_away [n_cells] are read for boundary-edge
+ * cells only.  The fields xkhh / alt of pmcgpu_trans_args carry WRF's halo values beyond the domain faces.
+ * Call before every pmcgpu_wrf_pmc_trans_driver whose boundary data changed (host or device pointers). */
+typedef struct {
+  int n_mode;
+  const int* mode_type;         /* [n_mode] 1 log-normal, 2 exponential, 3 mono-disperse */
+  const int* weight_class;      /* [n_mode] 1-based */
+  const double* char_radius;    /* [n_mode] */
+  const double* log10_std_dev;  /* [n_mode] */
+  const double* vol_frac;       /* [n_mode][n_spec] */
+  const double* vol_frac_std;   /* [n_mode][n_spec], NULL = 0 */
+  const double* num_conc;       /* [n_cells][n_mode] */
+  const int* outflow;           /* [n_cells] */
+  const int* throw_away;        /* [n_cells] */
+} pmcgpu_boundary_args;
+int pmcgpu_set_boundary(pmcgpu_ctx* ctx, const pmcgpu_boundary_args* args);
 
 /* wrf_pmc_dep_dry_driver (interface/wrf_pmc_dep.F90:31-97, called from wrf_pmc_trans_driver when
  * grid%do_deposition, wrf_pmc_trans.F90:183-197): dry deposition of particles in the lowest layer.

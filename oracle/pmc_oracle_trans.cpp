@@ -673,6 +673,9 @@ void trans_aero_run(OracleDomain& d, unsigned step, bool allow_doubling, bool al
               for (size_t m = 0; m < modes.size(); m++) modes[m].num_conc = t.bnd_num_conc[g * modes.size() + m];
               aero_state_resample(d.cells[g], d.data, modes, 1.0 / d.env[g].inverse_density, 0.0, t.bnd_throw[g] != 0, rc);
             }
+            // the device decides the bin grid of every refreshed boundary cell from its final population
+            d.cells[g].valid_sort = false;
+            aero_state_sort(d.cells[g]);
           }
     } catch (const PmcError& e) {
       throw PmcError(e.code ? e.code : -1, "boundary refresh failed");

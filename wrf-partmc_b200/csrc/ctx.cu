@@ -150,6 +150,7 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
     CUDA_OK(ctx, cudaMemcpyAsync(dk, kind.data(), kind.size(), cudaMemcpyHostToDevice, ctx->stream));
     CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
     v.kind = dk;
+    for (int s = 0; s < 4; s++) ctx->nb[s] = -1;  // a single open patch has no neighbours
   }
 #undef A
   k_init_cells<<<(v.n_cells + 255) / 256, 256, 0, ctx->stream>>>(v, cfg->i_offset, cfg->j_offset, cfg->nx, cfg->nz,
@@ -171,6 +172,7 @@ extern "C" int pmcgpu_destroy(pmcgpu_ctx* ctx) {
   for (void* p : ctx->allocs) cudaFree(p);
   if (ctx->h_flag) cudaFreeHost(ctx->h_flag);
   if (ctx->h_tot) cudaFreeHost(ctx->h_tot);
+  if (ctx->bnd_buf) cudaFree(ctx->bnd_buf);
   pmcgpu_comm_destroy(ctx);
   cudaStreamDestroy(ctx->stream);
   delete ctx;

@@ -40,6 +40,12 @@ extern "C" int pmcgpu_comm_init(pmcgpu_ctx* ctx, const char* unique_id, int n_ra
   ctx->nb[1] = rx + px * ((ry + 1) % py);
   ctx->nb[2] = (rx - 1 + px) % px + px * ry;
   ctx->nb[3] = (rx + 1) % px + px * ry;
+  if (ctx->v.kind) {  // open domain: no neighbour beyond the domain faces (MPI_PROC_NULL in the reference)
+    if (ry == 0) ctx->nb[0] = -1;
+    if (ry == py - 1) ctx->nb[1] = -1;
+    if (rx == 0) ctx->nb[2] = -1;
+    if (rx == px - 1) ctx->nb[3] = -1;
+  }
   if (n_ranks > 1) {
     if (!unique_id) return PMCGPU_ERR_ARG;
     ncclUniqueId id;
@@ -65,6 +71,7 @@ int pmc_exchange(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], cons
   cudaStream_t st = ctx->stream;
   bool any_remote = false;
   for (int s = 0; s < 4; s++) {
+    if (ctx->nb[s] < 0) continue;  // open domain face: nothing arrives (the receive buffer keeps its zeros)
     if (ctx->nb[s] == ctx->rank) {
       // the periodic neighbour is this patch: what left through side s ^ 1 arrives on side s
       if (bytes[s ^ 1]) CUDA_OK(ctx, cudaMemcpyAsync(recv[s], send[s ^ 1], bytes[s ^ 1], cudaMemcpyDeviceToDevice, st));
@@ -80,13 +87,13 @@ int pmc_exchange(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], cons
   }
   NCCL_OK(ctx, ncclGroupStart());
   for (int s = 0; s < 4; s++)
-    if (ctx->nb[s] != ctx->rank && bytes[s]) NCCL_OK(ctx, ncclSend(send[s], bytes[s], ncclChar, ctx->nb[s], comm, st));
+    if (ctx->nb[s] >= 0 && ctx->nb[s] != ctx->rank && bytes[s]) NCCL_OK(ctx, ncclSend(send[s], bytes[s], ncclChar, ctx->nb[s], comm, st));
   // receives are posted in the order 1, 0, 3, 2: when both neighbours of a direction are the same rank,
   // its first send (side 0 / 2) is the message for this rank's side 1 / 3
   const int order[4] = {1, 0, 3, 2};
   for (int q = 0; q < 4; q++) {
     const int s = order[q];
-    if (ctx->nb[s] != ctx->rank && bytes[s ^ 1])
+    if (ctx->nb[s] >= 0 && ctx->nb[s] != ctx->rank && bytes[s ^ 1])
       NCCL_OK(ctx, ncclRecv(recv[s], bytes[s ^ 1], ncclChar, ctx->nb[s], comm, st));
   }
   NCCL_OK(ctx, ncclGroupEnd());
@@ -101,6 +108,7 @@ int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4]
   cudaStream_t st = ctx->stream;
   bool any_remote = false;
   for (int s = 0; s < 4; s++) {
+    if (ctx->nb[s] < 0) continue;  // open domain face
     if (ctx->nb[s] == ctx->rank) {
       if (send_bytes[s ^ 1])
         CUDA_OK(ctx, cudaMemcpyAsync(recv[s], send[s ^ 1], send_bytes[s ^ 1], cudaMemcpyDeviceToDevice, st));
@@ -116,12 +124,12 @@ int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4]
   }
   NCCL_OK(ctx, ncclGroupStart());
   for (int s = 0; s < 4; s++)
-    if (ctx->nb[s] != ctx->rank && send_bytes[s])
+    if (ctx->nb[s] >= 0 && ctx->nb[s] != ctx->rank && send_bytes[s])
       NCCL_OK(ctx, ncclSend(send[s], send_bytes[s], ncclChar, ctx->nb[s], comm, st));
   const int order[4] = {1, 0, 3, 2};
   for (int q = 0; q < 4; q++) {
     const int s = order[q];
-    if (ctx->nb[s] != ctx->rank && recv_bytes[s])
+    if (ctx->nb[s] >= 0 && ctx->nb[s] != ctx->rank && recv_bytes[s])
       NCCL_OK(ctx, ncclRecv(recv[s], recv_bytes[s], ncclChar, ctx->nb[s], comm, st));
   }
   NCCL_OK(ctx, ncclGroupEnd());

@@ -436,21 +436,69 @@ __device__ __forceinline__ double aero_mode_number(int type, double num_conc, do
   return num_conc / weight_nc(wtype, wmag, wexp, char_radius);
 }
 
-__global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int cell = blockIdx.x * REB_WARPS + warp;
-  if (cell >= v.n_cells) return;
-  if (v.status[cell] != 0) return;
+// aero_mode_sample_radius (aero_mode.F90:549-628: log-normal with the tail threshold of rand.F90:410-474,
+// exponential, mono-disperse) + aero_mode_sample_vols (:633-668) for one new particle with its own draw stream;
+// vols[S] receives the species volumes, the radius is returned
+__device__ double sample_mode_particle(int S, int type, double cr, double lsd, int wt, double we, double size_factor,
+                                       const double* __restrict__ vf, const double* __restrict__ vs, RStream& s,
+                                       double* vols) {
+  // aero_mode_sample_radius
+  double radius = cr;
+  if (type == 1) {
+    double x_mean_prime = log10(cr);
+    if (wt != PMCGPU_WEIGHT_NONE) x_mean_prime = log10(cr) - we * (lsd * lsd) * log(10.0);
+    const double sqrt2 = (double)sqrtf(2.0f);  // 2.0**.5 is a default-real expression in rand.F90:463
+    double x;
+    for (;;) {
+      const double u1 = s.next();
+      const double u2 = s.next();
+      const double r = sqrt(-2.0 * log(u1));
+      const double theta = 2.0 * PmcConst::pi * u2;
+      const double z0 = r * cos(theta);
+      if (1.0 - fabs(erf(z0 / sqrt2)) >= size_factor) {
+        x = lsd * z0 + x_mean_prime;
+        break;
+      }
+    }
+    radius = pow(10.0, x);
+  } else if (type == 2) {
+    radius = vol2rad(-rad2vol(cr) * log(s.next()));
+  }
+  const double total_vol = rad2vol(radius);
+  // aero_mode_sample_vols
+    for (int it = 0; it < 1000000; it++) {
+    double sum = 0.0;
+    for (int k = 0; k < S; k++) {
+      vols[k] = rand_normal(vf[k], vs[k], s);
+      sum += vols[k];
+    }
+    const double offset = 1.0 - sum;
+    double mn = 1e300;
+    for (int k = 0; k < S; k++) {
+      vols[k] = vols[k] + offset * vf[k];
+      mn = fmin(mn, vols[k]);
+    }
+    if (mn >= 0.0) break;
+  }
+  double sum = 0.0;
+  for (int k = 0; k < S; k++) sum += vols[k];
+  for (int k = 0; k < S; k++) vols[k] = vols[k] / sum * total_vol;
+  return radius;
+}
+
+// aero_state_add_aero_dist_sample for ONE cell (warp-cooperative); mode_nc[n_mode] = number concentration of every
+// mode in this cell.  Returns the number of particles added; err receives a status.
+__device__ int emit_cell(DevView& v, const EmitDev& e, int cell, int lane, double sample_prop,
+                         const double* __restrict__ mode_nc_row, int& err) {
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
   const unsigned gcell = (unsigned)v.gcell[cell];
-  const double sample_prop = e.sample_prop[cell];
-  int n_add = 0, err = 0;
+  int n_add = 0;
   for (int g = 1; g <= v.G && !err; g++)
     for (int im = 1; im <= e.n_mode && !err; im++) {
       const int type = e.type[im - 1], c = e.wclass[im - 1];
       const double cr = e.char_radius[im - 1], lsd = e.log10_std[im - 1];
-      const double mode_nc = e.num_conc[(size_t)cell * e.n_mode + (im - 1)];
+      const double mode_nc = mode_nc_row[im - 1];
       const unsigned a = (unsigned)((g - 1) * e.n_mode + (im - 1));
       const int gc = (c - 1) * v.G + (g - 1);
       const double ideal = v.ideal_gc[gc];
@@ -471,7 +519,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
           __syncwarp();
           cell_scale_weight(v, cell, lane, g, c, n_part_new / ideal, e.allow_doubling, e.allow_halving, e.step, 1u + a);
           __syncwarp();
-          if (v.status[cell] != 0) return;
+          if (v.status[cell] != 0) return n_add;
         }
       }
       if (n_samp_avg == 0.0) continue;
@@ -491,49 +539,11 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
       const double* vs = e.vol_frac_std + (size_t)(im - 1) * v.S;
       for (int i_samp = 1 + lane; i_samp <= n_samp; i_samp += 32) {
         RStream s{RKey{v.seed, gcell, e.step, PH_EMIT, a, (unsigned)i_samp}, 0u};
-        // aero_mode_sample_radius
-        double radius = cr;
-        if (type == 1) {
-          double x_mean_prime = log10(cr);
-          if (wt != PMCGPU_WEIGHT_NONE) x_mean_prime = log10(cr) - we * (lsd * lsd) * log(10.0);
-          const double sqrt2 = (double)sqrtf(2.0f);  // 2.0**.5 is a default-real expression in rand.F90:463
-          double x;
-          for (;;) {
-            const double u1 = s.next();
-            const double u2 = s.next();
-            const double r = sqrt(-2.0 * log(u1));
-            const double theta = 2.0 * PmcConst::pi * u2;
-            const double z0 = r * cos(theta);
-            if (1.0 - fabs(erf(z0 / sqrt2)) >= size_factor) {
-              x = lsd * z0 + x_mean_prime;
-              break;
-            }
-          }
-          radius = pow(10.0, x);
-        } else if (type == 2) {
-          radius = vol2rad(-rad2vol(cr) * log(s.next()));
-        }
-        const double total_vol = rad2vol(radius);
-        // aero_mode_sample_vols
         double vols[PMC_MAX_SPEC];
-        for (int it = 0; it < 1000000; it++) {
-          double sum = 0.0;
-          for (int k = 0; k < v.S; k++) {
-            vols[k] = rand_normal(vf[k], vs[k], s);
-            sum += vols[k];
-          }
-          const double offset = 1.0 - sum;
-          double mn = 1e300;
-          for (int k = 0; k < v.S; k++) {
-            vols[k] = vols[k] + offset * vf[k];
-            mn = fmin(mn, vols[k]);
-          }
-          if (mn >= 0.0) break;
-        }
-        double sum = 0.0;
-        for (int k = 0; k < v.S; k++) sum += vols[k];
+        const double radius = sample_mode_particle(v.S, type, cr, lsd, wt, we, size_factor, vf, vs, s, vols);
+        (void)radius;
         const int slot = n_cur + i_samp - 1;
-        for (int k = 0; k < v.S; k++) v.vol[(size_t)k * NS + base + slot] = vols[k] / sum * total_vol;
+        for (int k = 0; k < v.S; k++) v.vol[(size_t)k * NS + base + slot] = vols[k];
         v.id[base + slot] = (nx + (i_samp - 1) - 1) * v.n_cells_global + v.gcell[cell] + 1;
         v.wgc[base + slot] = gc;
         v.nprim[base + slot] = 1;
@@ -549,6 +559,16 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
       __syncwarp();
       n_add += n_samp;
     }
+  return n_add;
+}
+
+__global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * REB_WARPS + warp;
+  if (cell >= v.n_cells) return;
+  if (v.status[cell] != 0) return;
+  int err = 0;
+  const int n_add = emit_cell(v, e, cell, lane, e.sample_prop[cell], e.num_conc + (size_t)cell * e.n_mode, err);
   if (lane == 0) {
     if (e.n_add) e.n_add[cell] = n_add;
     if (err && v.status[cell] == 0) v.status[cell] = err;
@@ -624,4 +644,278 @@ extern "C" int pmcgpu_aero_state_rebalance(pmcgpu_ctx* ctx, int allow_doubling, 
   int rc = pmc_rebalance_async(ctx, allow_doubling, allow_halving, step);
   if (rc) return rc;
   return pmc_first_status(ctx);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Open domains: boundary conditions (include/pmcgpu.h, pmcgpu_set_boundary) and the refresh of the boundary
+// cells at the end of trans_aero (interface/wrf_pmc_trans_aero.F90:811-955).
+// ---------------------------------------------------------------------------------------------------
+extern "C" int pmcgpu_set_boundary(pmcgpu_ctx* ctx, const pmcgpu_boundary_args* a) {
+  if (!ctx || !a || a->n_mode < 1 || !a->mode_type || !a->weight_class || !a->char_radius || !a->log10_std_dev ||
+      !a->vol_frac || !a->num_conc || !a->outflow || !a->throw_away)
+    return PMCGPU_ERR_ARG;
+  DevView& v = ctx->v;
+  if (!v.kind) {
+    ctx->err = "pmcgpu_set_boundary: the domain is doubly periodic";
+    return PMCGPU_ERR_ARG;
+  }
+  const size_t nm = (size_t)a->n_mode, S = (size_t)v.S, nc = (size_t)v.n_cells;
+  if (ctx->bnd_buf && ctx->bnd_n_mode != a->n_mode) {
+    cudaFree(ctx->bnd_buf);
+    ctx->bnd_buf = nullptr;
+  }
+  if (!ctx->bnd_buf) {
+    const size_t bytes = (2 * nm + 2 * nm * S + nc * nm) * sizeof(double) + (2 * nm + 2 * nc) * sizeof(int) + 64;
+    CUDA_OK(ctx, cudaMalloc((void**)&ctx->bnd_buf, bytes));
+    ctx->bnd_n_mode = a->n_mode;
+    ctx->bnd_cr = (double*)ctx->bnd_buf;
+    ctx->bnd_ls = ctx->bnd_cr + nm;
+    ctx->bnd_vf = ctx->bnd_ls + nm;
+    ctx->bnd_vs = ctx->bnd_vf + nm * S;
+    ctx->bnd_nc = ctx->bnd_vs + nm * S;
+    ctx->bnd_type = (int*)(ctx->bnd_nc + nc * nm);
+    ctx->bnd_wclass = ctx->bnd_type + nm;
+    ctx->bnd_outflow = ctx->bnd_wclass + nm;
+    ctx->bnd_throw = ctx->bnd_outflow + nc;
+  }
+  cudaStream_t st = ctx->stream;
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_cr, a->char_radius, nm * sizeof(double), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_ls, a->log10_std_dev, nm * sizeof(double), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_vf, a->vol_frac, nm * S * sizeof(double), cudaMemcpyDefault, st));
+  if (a->vol_frac_std)
+    CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_vs, a->vol_frac_std, nm * S * sizeof(double), cudaMemcpyDefault, st));
+  else
+    CUDA_OK(ctx, cudaMemsetAsync(ctx->bnd_vs, 0, nm * S * sizeof(double), st));
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_nc, a->num_conc, nc * nm * sizeof(double), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_type, a->mode_type, nm * sizeof(int), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_wclass, a->weight_class, nm * sizeof(int), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_outflow, a->outflow, nc * sizeof(int), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(ctx->bnd_throw, a->throw_away, nc * sizeof(int), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaStreamSynchronize(st));
+  return PMCGPU_OK;
+}
+
+struct BndDev {
+  EmitDev e;             // background modes (num_conc / sample_prop per cell are taken from here and from 1 / rrho)
+  const int* outflow;    // [n_cells]
+  const int* throw_away; // [n_cells]
+  int nx, nz;
+};
+
+// record `src` of cell `from_base` -> slot `dst` of cell `to_base` (warp-cooperative, the id is set by the caller)
+__device__ __forceinline__ void bnd_copy_record(DevView& v, size_t NS, size_t to, size_t from, int lane) {
+  for (int s = lane; s < v.S; s += 32) v.vol[(size_t)s * NS + to] = v.vol[(size_t)s * NS + from];
+  if (lane == 0) v.wgc[to] = v.wgc[from];
+  if (lane == 1) v.nprim[to] = v.nprim[from];
+  if (lane == 2) v.hyst[to] = v.hyst[from];
+  if (lane == 3) v.lct[to] = v.lct[from];
+  if (lane == 4) v.gct[to] = v.gct[from];
+  if (lane == 5) v.pbin[to] = v.pbin[from];
+}
+
+// One warp (= one CTA) per boundary-edge cell.  Shared memory: LST[cap] class lists (positions), FXC[cap]
+// position -> (class << 24 | index in its list) or -1 for particles appended by this call, len[C], off[C].
+__global__ void __launch_bounds__(32) k_bnd_refresh(DevView v, BndDev b, unsigned step) {
+  const int cell = blockIdx.x, lane = threadIdx.x;
+  const int kind = v.kind[cell];
+  if (kind < 1 || kind > 4) return;
+  if (v.status[cell] != 0) return;
+  extern __shared__ int s_b[];
+  int* LST = s_b;
+  int* FXC = LST + v.cap;
+  int* len = FXC + v.cap;
+  int* off = len + v.C;
+  const size_t NS = (size_t)v.n_cells * v.cap;
+  const size_t base = (size_t)cell * v.cap;
+  const int nbr = cell + (kind == 1 ? 1 : (kind == 2 ? -1 : (kind == 3 ? b.nx * b.nz : -b.nx * b.nz)));
+  const unsigned gcell = (unsigned)v.gcell[cell];
+  int err = 0;
+  if (b.outflow[cell]) {
+    // ---- aero_state_dup_all_particles (aero_state.F90:3529-3551): the state of the interior neighbour, new ids
+    const int n = v.count[nbr];
+    if (n > 0) {
+      const size_t nbase = (size_t)nbr * v.cap;
+      const long long nxid = v.next_id[cell];
+      for (int p = 0; p < n; p++) bnd_copy_record(v, NS, base + p, nbase + p, lane);
+      for (int p = lane; p < n; p += 32) v.id[base + p] = (nxid + p - 1) * v.n_cells_global + v.gcell[cell] + 1;
+      const int ncg = v.C * v.G;
+      for (int q = lane; q < ncg; q += 32) {
+        v.wtype[(size_t)cell * ncg + q] = v.wtype[(size_t)nbr * ncg + q];
+        v.wmag[(size_t)cell * ncg + q] = v.wmag[(size_t)nbr * ncg + q];
+        v.wexp[(size_t)cell * ncg + q] = v.wexp[(size_t)nbr * ncg + q];
+      }
+      for (int q = lane; q < v.C * v.nbcap; q += 32)
+        v.bin_count[(size_t)cell * v.C * v.nbcap + q] = v.bin_count[(size_t)nbr * v.C * v.nbcap + q];
+      if (lane == 0) {
+        v.next_id[cell] = nxid + n;
+        v.grid_nb[cell] = v.grid_nb[nbr];
+        v.grid_min[cell] = v.grid_min[nbr];
+        v.grid_max[cell] = v.grid_max[nbr];
+        v.bounds_valid[cell] = 0;
+      }
+    }
+    if (lane == 0) v.count[cell] = n;  // an empty neighbour: aero_state_zero
+    return;
+  }
+  const double density = 1.0 / v.rrho[cell];
+  const double* mode_nc = b.e.num_conc + (size_t)cell * b.e.n_mode;
+  if (b.throw_away[cell]) {
+    // ---- aero_state_resample, throw_away_previous (:1028-1032): aero_state_zero + aero_state_add_aero_dist_sample
+    // (density, sample_timescale = 1, create_time, allow_doubling, allow_halving)
+    if (lane == 0) v.count[cell] = 0;
+    __syncwarp();
+    emit_cell(v, b.e, cell, lane, density, mode_nc, err);
+    if (lane == 0 && err && v.status[cell] == 0) v.status[cell] = err;
+    return;
+  }
+  // ---- aero_state_resample (:1033-1095) from fresh class lists (ascending positions, a fresh aero_state_sort)
+  int n_cur = v.count[cell];
+  {
+    int run = 0;
+    for (int c = 0; c < v.C; c++) {
+      if (lane == 0) off[c] = run;
+      int m = 0;
+      for (int p0 = 0; p0 < n_cur; p0 += 32) {
+        const int p = p0 + lane;
+        const bool is = (p < n_cur) && (v.wgc[base + p] == c * v.G);
+        const unsigned bm = __ballot_sync(0xffffffffu, is);
+        if (is) {
+          const int idx = m + __popc(bm & ((1u << lane) - 1u));
+          LST[run + idx] = p;
+          FXC[p] = (c << 24) | idx;
+        }
+        m += __popc(bm);
+      }
+      if (lane == 0) len[c] = m;
+      run += m;
+    }
+    if (run != n_cur) err = PMCGPU_ERR_ARG;  // one weight group in WRF
+  }
+  __syncwarp();
+  const double sample_timescale = 1.0, factor = 0.1;
+  for (int c = 0; c < v.C && !err; c++) {
+    const unsigned gc = (unsigned)(c * v.G);  // group 1
+    const size_t wi = (size_t)cell * v.C * v.G + gc;
+    const int wt = v.wtype[wi];
+    const double wm = v.wmag[wi], we = v.wexp[wi];
+    const int n_part_before = len[c];
+    double total_num_conc = 0.0;
+    for (int im = 0; im < b.e.n_mode; im++)
+      if (b.e.wclass[im] == c + 1) total_num_conc = total_num_conc + mode_nc[im] * density;
+    const double n_parts_new = total_num_conc / wm;
+    RStream s0{RKey{v.seed, gcell, step, PH_BND, gc, 0u}, 0u};
+    const int n_samp = rand_poisson(n_parts_new, s0);
+    const int n_parts_to_add = n_samp - n_part_before;
+    if (n_parts_to_add > 0) {
+      for (int im = 0; im < b.e.n_mode && !err; im++) {
+        if (b.e.wclass[im] != c + 1) continue;
+        const unsigned am = 1000u + gc * (unsigned)b.e.n_mode + (unsigned)im;
+        const int type = b.e.type[im];
+        const double cr = b.e.char_radius[im], lsd = b.e.log10_std[im];
+        const double sample_proportion = (density * mode_nc[im]) / total_num_conc;
+        RStream sm{RKey{v.seed, gcell, step, PH_BND, am, 0u}, 0u};
+        const int n_samp_mode = rand_poisson(sample_proportion * (double)n_parts_to_add, sm);
+        const double n_samp_avg = sample_proportion * (double)n_parts_to_add;
+        const double num_conc_threshold = (density * mode_nc[im] / n_samp_avg) * factor;
+        const double size_factor = fmin(1.0 / (sample_timescale * n_samp_avg), 0.32);
+        const double* vf = b.e.vol_frac + (size_t)im * v.S;
+        const double* vs = b.e.vol_frac_std + (size_t)im * v.S;
+        const long long nxid = v.next_id[cell];
+        for (int i0 = 0; i0 < n_samp_mode && !err; i0 += 32) {
+          const int i_samp = i0 + lane + 1;
+          const bool active = i_samp <= n_samp_mode;
+          double vols[PMC_MAX_SPEC];
+          bool keep = false;
+          if (active) {
+            RStream s{RKey{v.seed, gcell, step, PH_BND, am, (unsigned)i_samp}, 0u};
+            const double radius = sample_mode_particle(v.S, type, cr, lsd, wt, we, size_factor, vf, vs, s, vols);
+            keep = weight_nc(wt, wm, we, radius) > num_conc_threshold;  // :1069-1073
+          }
+          const unsigned km = __ballot_sync(0xffffffffu, keep);
+          const int slot = n_cur + __popc(km & ((1u << lane) - 1u));
+          if (n_cur + __popc(km) > v.cap) { err = PMCGPU_ERR_CAPACITY; break; }
+          if (keep) {
+            for (int k = 0; k < v.S; k++) v.vol[(size_t)k * NS + base + slot] = vols[k];
+            v.id[base + slot] = (nxid + (i_samp - 1) - 1) * v.n_cells_global + v.gcell[cell] + 1;  // an id per SAMPLE (:1067)
+            v.wgc[base + slot] = (int)gc;
+            v.nprim[base + slot] = 1;
+            v.hyst[base + slot] = 0;
+            v.lct[base + slot] = b.e.create_time;
+            v.gct[base + slot] = b.e.create_time;
+            FXC[slot] = -1;  // not in any list of this call
+          }
+          n_cur += __popc(km);
+        }
+        __syncwarp();
+        if (lane == 0) v.next_id[cell] = nxid + n_samp_mode;
+        __syncwarp();
+      }
+    } else {
+      // removal of min(-n_parts_to_add, n_part) random entries of the (group, class) list (:1080-1091):
+      // aero_particle_array swap-with-last + integer_rmap2_remove (integer_rmap2.F90:190-243)
+      const int n_rm = min(-n_parts_to_add, len[c]);
+      for (int r = 1; r <= n_rm; r++) {
+        const int ne = len[c];
+        const int ie = pmc_rand_int(rng_uniform(RKey{v.seed, gcell, step, PH_BND, gc, (unsigned)r}, 0), ne);
+        const int p = LST[off[c] + ie - 1];
+        const int last = n_cur - 1;
+        __syncwarp();
+        if (lane == 0) {
+          const int pos_old = FXC[p] & 0xffffff;
+          if (last != p) {
+            const int ff = FXC[last];
+            if (ff >= 0) LST[off[ff >> 24] + (ff & 0xffffff)] = p;
+            FXC[p] = ff;
+          }
+          const int lp = off[c];
+          const int pos_last = len[c] - 1;
+          const int dom_fix = LST[lp + pos_last];
+          if (pos_old < pos_last) LST[lp + pos_old] = dom_fix;
+          len[c] = pos_last;
+          if (pos_last != pos_old) FXC[dom_fix] = (c << 24) | pos_old;
+        }
+        __syncwarp();
+        if (last != p) {
+          bnd_copy_record(v, NS, base + p, base + last, lane);
+          if (lane == 6) v.id[base + p] = v.id[base + last];
+        }
+        n_cur = last;
+        __syncwarp();
+      }
+    }
+  }
+  if (lane == 0) {
+    v.count[cell] = n_cur;
+    if (err && v.status[cell] == 0) v.status[cell] = err;
+  }
+}
+
+int pmc_boundary_refresh_async(pmcgpu_ctx* ctx, unsigned step) {
+  DevView& v = ctx->v;
+  if (!v.kind || !ctx->bnd_buf) return PMCGPU_ERR_ARG;
+  BndDev b;
+  b.e.n_mode = ctx->bnd_n_mode;
+  b.e.type = ctx->bnd_type; b.e.wclass = ctx->bnd_wclass; b.e.char_radius = ctx->bnd_cr; b.e.log10_std = ctx->bnd_ls;
+  b.e.vol_frac = ctx->bnd_vf; b.e.vol_frac_std = ctx->bnd_vs; b.e.num_conc = ctx->bnd_nc; b.e.sample_prop = nullptr;
+  b.e.char_factor = 1.0; b.e.create_time = 0.0;   // sample_timescale, create_time of the call sites (:839-842)
+  b.e.allow_doubling = 1; b.e.allow_halving = 1; b.e.step = step; b.e.n_add = nullptr;
+  b.outflow = ctx->bnd_outflow; b.throw_away = ctx->bnd_throw;
+  b.nx = ctx->cfg.nx; b.nz = ctx->cfg.nz;
+  const size_t smem = ((size_t)2 * v.cap + 2 * v.C) * sizeof(int);
+  if (smem > 200 * 1024) {
+    ctx->err = "cell_capacity too large for the class lists of the boundary refresh";
+    return PMCGPU_ERR_ARG;
+  }
+  if (smem > 48 * 1024 && smem > ctx->cfg_bnd_smem) {
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_bnd_refresh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ctx->cfg_bnd_smem = smem;
+  }
+  {
+    ProfScope ps_(ctx, "k_bnd_refresh");
+    k_bnd_refresh<<<v.n_cells, 32, smem, ctx->stream>>>(v, b, step);
+    LAUNCH_CHECK(ctx);
+  }
+  // the bin-grid decision of the refreshed cells (a fresh aero_state_sort of every boundary cell)
+  int pmc_sort_grid_only_async(pmcgpu_ctx*, int);
+  return pmc_sort_grid_only_async(ctx, 2);
 }

@@ -62,6 +62,13 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = v.count[cell];
   if (STAGED ? (n > n_split) : (n <= n_split)) return;
+  if (edge_recheck == 3) {  // grid decision only, interior cells of an open domain only (wrf_pmc_trans_aero.F90:777-804)
+    if (cell_is_boundary(v, cell)) return;
+    edge_recheck = 2;
+  } else if (edge_recheck == 4) {  // grid decision only, boundary-edge cells only (after their refresh)
+    if (!v.kind || v.kind[cell] < 1 || v.kind[cell] > 4) return;
+    edge_recheck = 2;
+  }
   const size_t base = (size_t)cell * v.cap;
   const size_t NS = (size_t)v.n_cells * v.cap;
   extern __shared__ __align__(16) int s_hist[];  // [SORT_WARPS][nk] then [nk] totals (then the staged rows)
@@ -363,11 +370,11 @@ static void swap_slabs(DevView& v);
 void pmc_swap_slabs(pmcgpu_ctx* ctx) { swap_slabs(ctx->v); }
 // aero_state_sort at the end of trans_aero (wrf_pmc_trans_aero.F90:803): the bin-grid decision of
 // aero_sorted_remake_if_needed only; the next mc_coag permutes the records anyway
-int pmc_sort_grid_only_async(pmcgpu_ctx* ctx) {
+int pmc_sort_grid_only_async(pmcgpu_ctx* ctx, int interior_only) {
   DevView& v = ctx->v;
   const size_t smem = (size_t)(SORT_THREADS / 32 + 1) * v.C * v.nbcap * sizeof(int);
   ProfScope ps_(ctx, "k_sort_cells_grid");
-  k_sort_cells<false, SORT_THREADS><<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, 2, -1);
+  k_sort_cells<false, SORT_THREADS><<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, interior_only == 1 ? 3 : (interior_only == 2 ? 4 : 2), -1);
   LAUNCH_CHECK(ctx);
   return PMCGPU_OK;
 }

@@ -39,6 +39,14 @@ __device__ __forceinline__ double tr_hprob(const TransView& t, int cell, int c, 
   return t.padv[((size_t)cell * t.C + c) * 6 + q] + t.pdiff[((size_t)cell * t.C + c) * 4 + q];
 }
 
+// open domain (compute_fluxes "real case", wrf_pmc_trans_aero.F90:1517-1623; boundary inflow :689-766): a west-edge
+// cell only feeds its east neighbour (slot 1), east -> slot 0, south -> slot 3, north -> slot 2, a corner nobody
+__device__ __forceinline__ int tr_kind(const DevView& v, int cell) { return v.kind ? (int)v.kind[cell] : 0; }
+__device__ __forceinline__ bool tr_allowed(int kind, int slot) {
+  return kind == 0 || (kind == 1 && slot == 1) || (kind == 2 && slot == 0) || (kind == 3 && slot == 3) ||
+         (kind == 4 && slot == 2);
+}
+
 // ---- particles of (group 1, class c) per cell: aero_state_total_particles(aero_state, 1, i_class)
 __global__ void k_tr_counts(DevView v, TransView t) {
   const int lane = threadIdx.x & 31;
@@ -117,6 +125,7 @@ __global__ void __launch_bounds__(256) k_tr_vprobs(DevView v, TransView t) {
   __shared__ int s_num_steps;
   auto cidx = [&](int k) { return (size_t)i + (size_t)t.nx * (k + (size_t)nz * j); };
   auto widx = [&](int k) { return (size_t)i + (size_t)t.nx * (k + (size_t)(nz + 1) * j); };
+  const bool bcol = tr_kind(v, tr_cell(t, i, 0, j)) != 0;
   for (int k = tid; k < nz; k += blockDim.x) {
     z_mass[k] = (double)t.zc[cidx(k)];
     rho_mass[k] = 1.0 / (double)t.alt[(size_t)(i + 1) + (size_t)(t.nx + 2) * (k + (size_t)nz * (j + 1))];
@@ -213,7 +222,8 @@ __global__ void __launch_bounds__(256) k_tr_vprobs(DevView v, TransView t) {
       } else {
         val = A[q];
       }
-      t.pvert[((size_t)tr_cell(t, i, r, j) * v.C + cl) * nz + c] = val;
+      // prob_vert_diffusion stays 0 in the boundary columns of an open domain (wrf_pmc_trans.F90:104, 116-136)
+      t.pvert[((size_t)tr_cell(t, i, r, j) * v.C + cl) * nz + c] = bcol ? 0.0 : val;
     }
     __syncthreads();
     // normalize_probs for (k = r, class cl)
@@ -298,7 +308,7 @@ __global__ void k_tr_edge_flux(DevView v, TransView t, int side, double* __restr
   const int cell = tr_cell(t, i, k, j);
   const double source_vol = t.cellvol_ext[tr_ext(t, i, k, j)], dest_vol = t.cellvol_ext[tr_ext(t, gi, k, gj)];
   const double flux = tr_hprob(t, cell, c, slot) * t.num_old[(size_t)cell * v.C + c];
-  out[q] = flux * (dest_vol / source_vol);
+  out[q] = tr_allowed(tr_kind(v, cell), slot) ? flux * (dest_vol / source_vol) : 0.0;
 }
 
 // ---- trans_aero_preweight (:1103-1423): expected number concentration of every (cell, class) gathered in
@@ -312,8 +322,10 @@ __global__ void k_tr_preweight(DevView v, TransView t) {
   const double volD = t.cellvol_ext[tr_ext(t, i, k, j)];
   const double ncoD = t.num_old[q];
   double acc = ncoD;
+  const int kindD = tr_kind(v, cell);
   auto from_h = [&](int si, int sj, int slot) {
     const int s = tr_cell(t, si, k, sj);
+    if (!tr_allowed(tr_kind(v, s), slot)) return;
     const double flux = tr_hprob(t, s, c, slot) * t.num_old[(size_t)s * v.C + c];
     acc = acc + flux * (volD / t.cellvol_ext[tr_ext(t, si, k, sj)]);
   };
@@ -323,17 +335,21 @@ __global__ void k_tr_preweight(DevView v, TransView t) {
     acc = acc + flux * (volD / t.cellvol_ext[tr_ext(t, i, sk, j)]);
   };
   if (j - 1 >= 0) from_h(i, j - 1, 3);
-  for (int sk = 0; sk < k; sk++) from_v(sk);
+  if (kindD == 0)
+    for (int sk = 0; sk < k; sk++) from_v(sk);
   if (i - 1 >= 0) from_h(i - 1, j, 1);
-  // the cell's own losses, in the order of compute_fluxes: -y, +y, -x, +x, then the vertical levels
-  acc = acc - tr_hprob(t, cell, c, 2) * ncoD;
-  acc = acc - tr_hprob(t, cell, c, 3) * ncoD;
-  acc = acc - tr_hprob(t, cell, c, 0) * ncoD;
-  acc = acc - tr_hprob(t, cell, c, 1) * ncoD;
-  for (int kk = 0; kk < nz; kk++)
-    if (kk != k) acc = acc - t.pvert[((size_t)cell * v.C + c) * nz + kk] * ncoD;
+  // the cell's own losses, in the order of compute_fluxes: -y, +y, -x, +x, then the vertical levels (a boundary
+  // cell of an open domain only loses towards its interior neighbour, a corner nothing)
+  if (tr_allowed(kindD, 2)) acc = acc - tr_hprob(t, cell, c, 2) * ncoD;
+  if (tr_allowed(kindD, 3)) acc = acc - tr_hprob(t, cell, c, 3) * ncoD;
+  if (tr_allowed(kindD, 0)) acc = acc - tr_hprob(t, cell, c, 0) * ncoD;
+  if (tr_allowed(kindD, 1)) acc = acc - tr_hprob(t, cell, c, 1) * ncoD;
+  if (kindD == 0)
+    for (int kk = 0; kk < nz; kk++)
+      if (kk != k) acc = acc - t.pvert[((size_t)cell * v.C + c) * nz + kk] * ncoD;
   if (i + 1 <= nx - 1) from_h(i + 1, j, 0);
-  for (int sk = k + 1; sk < nz; sk++) from_v(sk);
+  if (kindD == 0)
+    for (int sk = k + 1; sk < nz; sk++) from_v(sk);
   if (j + 1 <= ny - 1) from_h(i, j + 1, 2);
   // ghost sums of the neighbours, in the order the reference receives them: sender side y-, y+, x-, x+
   if (j == ny - 1) acc = acc + t.rbuf[1][((size_t)i * nz + k) * v.C + c];  // neighbour y+ sent its y- ghost row
@@ -476,7 +492,17 @@ __global__ void k_tr_multisample(DevView v, TransView t, unsigned step, int warp
     }
     // ---- move probabilities of this class, ascending, ties in collection order (real_sort, util.F90:1612)
     int count = 0;
-    if (lane == 0) {
+    const int kindS = tr_kind(v, cell);
+    if (lane == 0 && kindS != 0) {
+      // boundary cell of an open domain: no multinomial sampling; the edge cells feed their interior neighbour with
+      // probability min(advection + diffusion, 1) (boundary inflow, wrf_pmc_trans_aero.F90:689-766), corners nothing
+      if (kindS <= 4) {
+        const int q = (kindS == 1) ? 1 : (kindS == 2 ? 0 : (kindS == 3 ? 3 : 2));
+        const double pr = fmin(tr_hprob(t, cell, c, q), 1.0);
+        if (pr > 0.0) { sprob[0] = pr; sdir[0] = q; count = 1; }
+      }
+    }
+    if (lane == 0 && kindS == 0) {
       for (int q = 0; q < 4; q++) {
         const double pr = tr_hprob(t, cell, c, q);
         if (pr > 0.0) { sprob[count] = pr; sdir[count] = q; count++; }
@@ -671,7 +697,8 @@ __global__ void k_tr_pack_copy(DevView v, TransView t, int side, const int* __re
 // arrivals into the alternate slab.  Arrival order = the order in which the reference's loops append to
 // delta_aero_states(dest): local sources in (j, k, i) order, then the four ghost receives.
 // candidate segments of one destination cell: survivors, (nz + 3) source cells x C classes, four ghost sides
-static inline __host__ __device__ int tr_n_cand(int nz, int C) { return 1 + (nz + 3) * C + 4; }
+// (+ 4 C boundary-inflow candidates of an open domain: west, east, south, north boundary neighbour x class)
+static inline __host__ __device__ int tr_n_cand(int nz, int C) { return 1 + (nz + 3) * C + 4 + 4 * C; }
 // one particle's species rows from one slab to another (the slabs never overlap): loads in batches of eight
 // ahead of the stores
 __device__ __forceinline__ void tr_copy_rows(double* __restrict__ dst, size_t dstride, const double* __restrict__ src,
@@ -704,7 +731,9 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
     const int lane = threadIdx.x;
     const int C = v.C;
     const int n_src = nz + 3;  // y-, below (k), x-, x+, above (nz-1-k), y+
-    const int n_cand = 1 + n_src * C + 4;
+    const int n_main = 1 + n_src * C + 4;
+    const int n_cand = n_main + 4 * C;
+    const int kindD = tr_kind(v, cell);
     int ns = 0, tot = 0, fail = 0;
     const int cap = v.cap;
     for (int e0 = 0; e0 < n_cand; e0 += 32) {
@@ -712,6 +741,8 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
       int kind = 0, src = 0, off = 0, cnt = 0;
       if (e == 0) {
         kind = 0; src = cell; off = 0; cnt = t.n_surv[cell];
+      } else if (kindD != 0) {
+        // boundary cell of an open domain: what moves into it leaves the domain (never added, :777-804)
       } else if (e < 1 + n_src * C) {
         const int u = (e - 1) / C, c = (e - 1) % C;
         int si = i, sk = k, sj = j, slot = 0;
@@ -724,10 +755,13 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
         else { sj = j + 1; slot = 2; ok = (j + 1 <= ny - 1); }
         if (ok) {
           const int sc = tr_cell(t, si, sk, sj);
-          const int* od = t.out_dir + (((size_t)sc * C + c) * nd + slot) * 2;
-          kind = 1; src = sc; off = od[0]; cnt = od[1];
+          // a boundary cell is not part of the multinomial sampling: its inflow arrives behind the ghost sides
+          if (tr_kind(v, sc) == 0) {
+            const int* od = t.out_dir + (((size_t)sc * C + c) * nd + slot) * 2;
+            kind = 1; src = sc; off = od[0]; cnt = od[1];
+          }
         }
-      } else if (e < n_cand) {
+      } else if (e < n_main) {
         const int g = e - (1 + n_src * C);  // 0: side 1 (j == ny-1), 1: side 0 (j == 0), 2: side 3, 3: side 2
         const int side = (g == 0) ? 1 : (g == 1 ? 0 : (g == 2 ? 3 : 2));
         const bool ok = (g == 0) ? (j == ny - 1) : (g == 1 ? (j == 0) : (g == 2 ? (i == nx - 1) : (i == 0)));
@@ -736,6 +770,21 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
           kind = 2; src = side; off = t.roff[side][q]; cnt = t.roff[side][q + 1] - off;
           const int pitch = (side == 0) ? r0.cap : (side == 1 ? r1.cap : (side == 2 ? r2.cap : r3.cap));
           if (off + cnt > pitch) { cnt = 0; fail = 1; }  // the sender could not pack this cell (message pitch)
+        }
+      } else if (e < n_cand && v.kind) {
+        // boundary inflow (:689-766), after the ghost receives: west, east, south, north boundary neighbour
+        const int b = (e - n_main) / C, c = (e - n_main) % C;
+        int si = i, sj = j, slot = 0, want = 0;
+        if (b == 0) { si = i - 1; slot = 1; want = 1; }
+        else if (b == 1) { si = i + 1; slot = 0; want = 2; }
+        else if (b == 2) { sj = j - 1; slot = 3; want = 3; }
+        else { sj = j + 1; slot = 2; want = 4; }
+        if (si >= 0 && si <= nx - 1 && sj >= 0 && sj <= ny - 1) {
+          const int sc = tr_cell(t, si, k, sj);
+          if (tr_kind(v, sc) == want) {
+            const int* od = t.out_dir + (((size_t)sc * C + c) * nd + slot) * 2;
+            kind = 1; src = sc; off = od[0]; cnt = od[1];
+          }
         }
       }
       // a cell that would outgrow its slab keeps what fits (survivors first, then arrivals in order) and is
@@ -818,7 +867,8 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-int pmc_sort_grid_only_async(pmcgpu_ctx* ctx);
+int pmc_sort_grid_only_async(pmcgpu_ctx* ctx, int interior_only);
+int pmc_boundary_refresh_async(pmcgpu_ctx* ctx, unsigned step);
 int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step);
 void pmc_swap_slabs(pmcgpu_ctx* ctx);
 int pmc_exchange(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], const size_t bytes[4]);
@@ -841,10 +891,6 @@ static int tr_setup(pmcgpu_ctx* ctx) {
   t.nx = ctx->cfg.nx; t.nz = ctx->cfg.nz; t.ny = ctx->cfg.ny; t.C = v.C;
   if (v.G != 1) {
     ctx->err = "transport samples weight group 1 only (wrf_pmc_trans_aero.F90:2229); n_group must be 1";
-    return PMCGPU_ERR_ARG;
-  }
-  if (!ctx->cfg.periodic_x || !ctx->cfg.periodic_y) {
-    ctx->err = "transport is built for the doubly periodic domain; open boundaries are not built yet";
     return PMCGPU_ERR_ARG;
   }
   if (t.nz < 2 || t.nz > 60 || v.C > 127) return PMCGPU_ERR_ARG;
@@ -907,7 +953,11 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
   auto blocks = [&](size_t n) { return (unsigned)((n + TB - 1) / TB); };
   // ---- aero_state_sort of every cell at the top of trans_aero_preweight (:1210): only its bin-grid
   // decision has an effect that outlives the call
-  if ((rc = pmc_sort_grid_only_async(ctx))) return rc;
+  if (v.kind && !ctx->bnd_buf) {
+    ctx->err = "open domain: call pmcgpu_set_boundary before pmcgpu_wrf_pmc_trans_driver";
+    return PMCGPU_ERR_ARG;
+  }
+  if ((rc = pmc_sort_grid_only_async(ctx, 0))) return rc;
   // ---- probabilities
   {
     ProfScope ps_(ctx, "k_tr_probs");
@@ -1041,7 +1091,9 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
     pmc_swap_slabs(ctx);
   }
   if ((rc = pmc_rebalance_async(ctx, a->allow_doubling, a->allow_halving, a->step))) return rc;
-  if ((rc = pmc_sort_grid_only_async(ctx))) return rc;
+  if ((rc = pmc_sort_grid_only_async(ctx, 1))) return rc;
+  // ---- open domain: refresh of the boundary cells (wrf_pmc_trans_aero.F90:811-955)
+  if (v.kind && (rc = pmc_boundary_refresh_async(ctx, a->step))) return rc;
   if (a->no_wait) return PMCGPU_OK;
   return pmc_first_status(ctx);
 }

@@ -84,6 +84,13 @@ class _WrfFields(C.Structure):
                 ("rdx", C.c_float), ("rdy", C.c_float)]
 
 
+class _BoundaryArgs(C.Structure):
+    _fields_ = [("n_mode", C.c_int), ("mode_type", C.c_void_p), ("weight_class", C.c_void_p),
+                ("char_radius", C.c_void_p), ("log10_std_dev", C.c_void_p), ("vol_frac", C.c_void_p),
+                ("vol_frac_std", C.c_void_p), ("num_conc", C.c_void_p), ("outflow", C.c_void_p),
+                ("throw_away", C.c_void_p)]
+
+
 class _DepArgs(C.Structure):
     _fields_ = [("rmol", C.c_void_p), ("znt", C.c_void_p), ("ust", C.c_void_p), ("ivgtyp", C.c_void_p),
                 ("height", C.c_void_p), ("dt", C.c_double), ("step", C.c_uint), ("no_wait", C.c_int)]
@@ -424,6 +431,22 @@ class PartMCGPU:
         """patch decomposition px x py of the periodic domain, one rank per patch (pmcgpu_comm_init)"""
         self._chk(self.L.pmcgpu_comm_init(self.h, unique_id, C.c_int(n_ranks), C.c_int(rank), C.c_int(px),
                                           C.c_int(py)))
+
+    def set_boundary(self, mode_type, weight_class, char_radius, log10_std_dev, vol_frac, num_conc, outflow, throw_away,
+                     vol_frac_std=None):
+        """boundary conditions of an open domain (pmcgpu_set_boundary): background modes ([n_mode] arrays, vol_frac
+        [n_mode][n_spec]), num_conc [n_cells][n_mode], outflow / throw_away [n_cells] of THIS patch's cells"""
+        a = _BoundaryArgs()
+        ty, wc = _i32(mode_type), _i32(weight_class)
+        cr, ls, vf, vs = _f64(char_radius), _f64(log10_std_dev), _f64(vol_frac), _f64(vol_frac_std)
+        nc, of, ta = _f64(num_conc), _i32(outflow), _i32(throw_away)
+        assert nc.size == self.n_cells * len(ty) and of.size == self.n_cells and ta.size == self.n_cells
+        a.n_mode = len(ty)
+        a.mode_type, a.weight_class = ty.ctypes.data, wc.ctypes.data
+        a.char_radius, a.log10_std_dev, a.vol_frac = cr.ctypes.data, ls.ctypes.data, vf.ctypes.data
+        a.vol_frac_std = None if vs is None else vs.ctypes.data
+        a.num_conc, a.outflow, a.throw_away = nc.ctypes.data, of.ctypes.data, ta.ctypes.data
+        self._chk(self.L.pmcgpu_set_boundary(self.h, C.byref(a)))
 
     def comm_destroy(self):
         self._chk(self.L.pmcgpu_comm_destroy(self.h))
