@@ -473,8 +473,10 @@ __global__ void k_tr_multisample(DevView v, TransView t, unsigned step, int warp
   __syncwarp();
   const double source_vol = t.cellvol_ext[tr_ext(t, i, k, j)];
 
+  // ---- aero_state_scale_weight removals decided by the preweighting (magnitude already scaled): all classes first,
+  // like trans_aero_preweight (:1373-1400), which runs before any particle is sampled (the order of the
+  // swap-with-last removals decides the particle order the sampling sees)
   for (int c = 0; c < v.C && !err; c++) {
-    // ---- aero_state_scale_weight removals decided by the preweighting (magnitude already scaled)
     const double sr = t.scale_ratio[(size_t)cell * v.C + c];
     if (sr > 0.0) {
       const unsigned gc = (unsigned)(c * v.G);
@@ -490,6 +492,8 @@ __global__ void k_tr_multisample(DevView v, TransView t, unsigned step, int warp
       x.n_cur = __shfl_sync(0xffffffffu, x.n_cur, 0);
       __syncwarp();
     }
+  }
+  for (int c = 0; c < v.C && !err; c++) {
     // ---- move probabilities of this class, ascending, ties in collection order (real_sort, util.F90:1612)
     int count = 0;
     const int kindS = tr_kind(v, cell);
