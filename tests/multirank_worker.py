@@ -26,6 +26,21 @@ def global_case(cfg):
     return synthetic.make_patch(cfg["gnx"], cfg["nz"], cfg["gny"], cfg["n_per_cell"], cfg["n_spec"], seed=cfg["seed"])
 
 
+def open_boundary(case):
+    """boundary conditions of the open test domain in GLOBAL cell order (wind from the south-west)"""
+    n_cells, nx, nz, ny, S = case["n_cells"], case["nx"], case["nz"], case["ny"], case["n_spec"]
+    vf = np.zeros((2, S))
+    vf[0, 0], vf[0, 2] = 0.6, 0.4
+    vf[1, 1], vf[1, 2] = 0.5, 0.5
+    gi = np.arange(n_cells) % nx
+    gj = np.arange(n_cells) // (nx * nz)
+    throw = np.zeros(n_cells, np.int32)
+    throw[(gi == 0) & (gj == 1)] = 1
+    return dict(mode_type=[1, 1], weight_class=[1, 2], char_radius=[1e-8, 5.8e-8], log10_std_dev=[0.161, 0.217],
+                vol_frac=vf, num_conc=np.tile(np.array([3.2e10, 2.9e10]) * 1.3, (n_cells, 1)) * case["rrho"][:, None],
+                outflow=((gi == nx - 1) | (gj == ny - 1)).astype(np.int32), throw_away=throw)
+
+
 def run_cpu(rank, world, port, out_dir):
     import torch.distributed as dist
     from wrf_partmc_b200.host import decomp
@@ -59,9 +74,11 @@ def run_gpu(rank, world, port, out_dir, cfg):
     pc = patch_case(case, rx * nxl, nxl, ry * nyl, nyl)
     sp = case["sp"]
     data = W.AeroData(sp["density"], sp["kappa"], sp["molec_weight"], sp["num_ions"], sp["i_water"])
+    is_open = bool(cfg.get("open"))
     g = W.PartMCGPU(data, nx=nxl, nz=cfg["nz"], ny=nyl, n_group=1, n_class=case["n_class"],
                     n_part_ideal=case["n_part_ideal"], cell_capacity=3 * cfg["n_per_cell"] + 64, seed=case["seed"],
-                    device=rank, global_nx=cfg["gnx"], global_ny=cfg["gny"], i_offset=rx * nxl, j_offset=ry * nyl)
+                    device=rank, global_nx=cfg["gnx"], global_ny=cfg["gny"], i_offset=rx * nxl, j_offset=ry * nyl,
+                    periodic_x=not is_open, periodic_y=not is_open)
     g.set_particles(pc["counts"], pc["vol"], pc["wgroup"], pc["wclass"], pc["id"], pc["n_primary"], pc["hyst"],
                     pc["lct"], pc["gct"])
     g.set_weights(pc["wtype"], pc["wmag"], pc["wexp"])
@@ -72,8 +89,13 @@ def run_gpu(rank, world, port, out_dir, cfg):
     uid = decomp.broadcast_unique_id(W.comm_unique_id, rank)
     g.comm_init(uid, world, rank, px, py)
     nc = np.load(os.path.join(out_dir, "num_conc.npy"))
-    f = synthetic.transport_fields(case, nc)
-    fp = synthetic.patch_fields(f, rx * nxl, nxl, ry * nyl, nyl)
+    f = synthetic.transport_fields(case, nc, periodic=not is_open)
+    fp = synthetic.patch_fields(f, rx * nxl, nxl, ry * nyl, nyl, periodic=not is_open)
+    if is_open:
+        b = open_boundary(case)
+        cells = pc["cells"]
+        g.set_boundary(b["mode_type"], b["weight_class"], b["char_radius"], b["log10_std_dev"], b["vol_frac"],
+                       b["num_conc"][cells], b["outflow"][cells], b["throw_away"][cells])
     moved = 0
     for step in range(1, cfg["n_steps"] + 1):
         g.wrf_pmc_trans_driver(fp, step=step)
