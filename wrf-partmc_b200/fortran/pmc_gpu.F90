@@ -400,6 +400,10 @@ contains
     real(c_float), allocatable, target :: xkhh(:,:,:), alt(:,:,:), z(:,:,:), zw(:,:,:), kv(:,:,:)
 
     n_class = size(grid%u_flux, 4) - 1
+    if (.not. (config_flags%periodic_x .and. config_flags%periodic_y)) then
+       call pmc_gpu_boundary_from_wrf(grid, scenario, env_states, pmc_is, pmc_ie, pmc_js, pmc_je, &
+            pmc_ks, pmc_ke, global_nx, global_ny)
+    end if
     ! contiguous copies of the patch sections (the flux arrays carry the class index last; index 1
     ! of that dimension is WRF's dummy scalar, wrf_pmc_trans.F90:229)
     u = grid%u_flux(pmc_is:pmc_ie + 1, pmc_ks:pmc_ke, pmc_js:pmc_je, 2:n_class + 1)
@@ -466,6 +470,102 @@ contains
     call pmc_gpu_check(pmcgpu_wrf_pmc_dep_dry_driver(pmc_gpu_handle, args), &
          'pmcgpu_wrf_pmc_dep_dry_driver')
   end subroutine pmc_gpu_dep_dry
+
+  !> Open domain: the boundary conditions trans_aero derives per step (wrf_pmc_trans_aero.F90:811-955) --
+  !! which boundary cells see outflow (u_2 < 0 on the west face, u_2(i+1) > 0 on the east face, v_2 likewise),
+  !! which are thrown away (the wind changed sign since the last step, or the background changed), and the
+  !! background aerosol interpolated to the current time (aero_dist_interp_1d) -- handed to pmcgpu_set_boundary.
+  subroutine pmc_gpu_boundary_from_wrf(grid, scenario, env_states, pmc_is, pmc_ie, pmc_js, pmc_je, &
+       pmc_ks, pmc_ke, global_nx, global_ny)
+    use module_domain, only: domain
+    use pmc_env_state
+    use pmc_scenario
+    use pmc_aero_dist
+    use pmc_aero_mode
+    use pmc_util, only: find_1d
+    type(domain), intent(in) :: grid
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke, global_nx, global_ny
+    type(scenario_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(in) :: scenario
+    type(env_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), intent(in) :: env_states
+
+    type(pmcgpu_boundary_args_t) :: b
+    type(aero_dist_t) :: background
+    real(kind=dp) :: dilution_rate, u2, u1
+    integer :: i, j, k, c, m, n_cells, n_mode, n_spec, p_t, p_tm1
+    logical :: edge, change_bc
+    integer(c_int), allocatable, target :: mode_type(:), weight_class(:), outflow(:), throw_away(:)
+    real(c_double), allocatable, target :: char_radius(:), log10_std(:), vol_frac(:,:), vol_frac_std(:,:), &
+         num_conc(:,:)
+
+    n_cells = (pmc_ie - pmc_is + 1) * (pmc_ke - pmc_ks + 1) * (pmc_je - pmc_js + 1)
+    call aero_dist_interp_1d(scenario(pmc_is,pmc_ks,pmc_js)%aero_background, &
+         scenario(pmc_is,pmc_ks,pmc_js)%aero_dilution_time, scenario(pmc_is,pmc_ks,pmc_js)%aero_dilution_rate, &
+         env_states(pmc_is,pmc_ks,pmc_js)%elapsed_time, background, dilution_rate)
+    n_mode = aero_dist_n_mode(background)
+    n_spec = size(background%mode(1)%vol_frac)
+    allocate(mode_type(n_mode), weight_class(n_mode), char_radius(n_mode), log10_std(n_mode), &
+         vol_frac(n_spec, n_mode), vol_frac_std(n_spec, n_mode), num_conc(n_mode, n_cells), &
+         outflow(n_cells), throw_away(n_cells))
+    do m = 1, n_mode
+       mode_type(m) = background%mode(m)%type          ! aero_mode.F90:26-34 (1 log-normal, 2 exp, 3 mono)
+       weight_class(m) = background%mode(m)%weight_class
+       char_radius(m) = background%mode(m)%char_radius
+       log10_std(m) = background%mode(m)%log10_std_dev_radius
+       vol_frac(:, m) = background%mode(m)%vol_frac
+       vol_frac_std(:, m) = background%mode(m)%vol_frac_std
+    end do
+    outflow = 0
+    throw_away = 0
+    num_conc = 0d0
+    c = 0
+    do j = pmc_js, pmc_je
+    do k = pmc_ks, pmc_ke
+    do i = pmc_is, pmc_ie
+       c = c + 1
+       edge = .true.
+       if (i == 1 .and. j > 1 .and. j < global_ny) then
+          u2 = grid%u_2(i,k,j); u1 = grid%u_1(i,k,j)
+          if (u2 < 0.0d0) outflow(c) = 1
+       else if (i == global_nx .and. j > 1 .and. j < global_ny) then
+          u2 = grid%u_2(i+1,k,j); u1 = grid%u_1(i+1,k,j)
+          if (u2 > 0.0d0) outflow(c) = 1
+       else if (j == 1 .and. i > 1 .and. i < global_nx) then
+          u2 = grid%v_2(i,k,j); u1 = grid%v_1(i,k,j)
+          if (u2 < 0.0d0) outflow(c) = 1
+       else if (j == global_ny .and. i > 1 .and. i < global_nx) then
+          u2 = grid%v_2(i,k,j+1); u1 = grid%v_1(i,k,j+1)
+          if (u2 > 0.0d0) outflow(c) = 1
+       else
+          edge = .false.
+       end if
+       if (.not. edge) cycle
+       ! change_boundary_conditions (:816-826) and the wind reversal test (:836)
+       p_tm1 = find_1d(size(scenario(i,k,j)%aero_background), scenario(i,k,j)%aero_dilution_time, &
+            env_states(i,k,j)%elapsed_time - real(grid%dt, dp))
+       p_t = find_1d(size(scenario(i,k,j)%aero_background), scenario(i,k,j)%aero_dilution_time, &
+            env_states(i,k,j)%elapsed_time)
+       change_bc = (p_t > p_tm1 .and. p_t > 1)
+       if (u2 * u1 < 0.0d0 .or. change_bc) throw_away(c) = 1
+       call aero_dist_interp_1d(scenario(i,k,j)%aero_background, scenario(i,k,j)%aero_dilution_time, &
+            scenario(i,k,j)%aero_dilution_rate, env_states(i,k,j)%elapsed_time, background, dilution_rate)
+       do m = 1, n_mode
+          num_conc(m, c) = aero_mode_total_num_conc(background%mode(m))
+       end do
+    end do
+    end do
+    end do
+    b%n_mode = n_mode
+    b%mode_type = c_loc(mode_type)
+    b%weight_class = c_loc(weight_class)
+    b%char_radius = c_loc(char_radius)
+    b%log10_std_dev = c_loc(log10_std)
+    b%vol_frac = c_loc(vol_frac)
+    b%vol_frac_std = c_loc(vol_frac_std)
+    b%num_conc = c_loc(num_conc)
+    b%outflow = c_loc(outflow)
+    b%throw_away = c_loc(throw_away)
+    call pmc_gpu_check(pmcgpu_set_boundary(pmc_gpu_handle, b), 'pmcgpu_set_boundary')
+  end subroutine pmc_gpu_boundary_from_wrf
 
   !> wrf_pmc_dep_dry_driver (interface/wrf_pmc_dep.F90:31-60), same name and argument list.
   subroutine wrf_pmc_dep_dry_driver(grid, config_flags, aero_data, aero_states, gas_states, env_states, &
