@@ -349,6 +349,20 @@ def wrf_to_partmc(nx, nz, ny, p, pb, t_2, qv, alt, z_at_w, rdx, rdy, msftx=None,
     return dict(zip(("temp", "pressure", "rel_humid", "inverse_density", "cell_volume", "height"), out))
 
 
+def run_sect(n_bin, d_min, d_max, density, total_num_conc, geom_mean_diam, log10_sigma, kernel_type, temp, pressure,
+             t_max, del_t, t_output):
+    """the reference's sectional coagulation solver (run_sect.F90:56-362) for one log-normal mode of a one-species
+    aerosol; returns (num, mass) densities per ln(r), [n_out][n_bin], at t = 0, t_output, ..."""
+    n_out = int(round(t_max / t_output)) + 1
+    num, mass = np.zeros((n_out, n_bin)), np.zeros((n_out, n_bin))
+    L = lib()
+    L.pmco_run_sect.argtypes = [C.c_int] + [C.c_double] * 6 + [C.c_int] + [C.c_double] * 5 + [C.c_void_p, C.c_void_p, C.c_int]
+    n = L.pmco_run_sect(n_bin, d_min, d_max, density, total_num_conc, geom_mean_diam, log10_sigma, kernel_type, temp,
+                        pressure, t_max, del_t, t_output, num.ctypes.data, mass.ctypes.data, n_out)
+    assert n == n_out, n
+    return num, mass
+
+
 def condense_rates_dt(inputs):
     """time derivatives of condense_rates at fixed (D, H): [n][3] = dDdot/dt, dHdot_i/dt, dHdot_env/dt"""
     a = _f64(inputs).reshape(-1, 9)

@@ -202,3 +202,37 @@ def test_wrf_to_partmc_on_device(mods):
     # a step without met arrays installs the staged env_state (no condensation: the new RH is installed too)
     g.partmc_timestep(elapsed_time=0.0, dt=60.0, chem_dt=60.0, do_coagulation=False, do_condensation=False, step=1)
     assert np.array_equal(g.rel_humid(), d["rel_humid"])
+
+
+def test_device_brownian_against_the_sectional_solver(mods):
+    """partmc/test/brownian on the device: 9 repeats x 1000 particles, del_t = 600 s, 24 h, against the restatement
+    of run_sect.F90 at the reference's tolerances (0.2 number, 0.3 mass, per output time, 2-norm)"""
+    W, O = mods
+    import test_oracle_sect as TS
+    case = TS.brownian_case()
+    case["T"][:] = 288.0
+    case["P"][:] = 1e5
+    case["wmag"][:] = 1e11 / 1000.0
+    g = common.gpu_from_case(W, case, cell_capacity=2200)
+    num_s, mass_s = TS.sectional()
+    num_p, mass_p = np.zeros_like(num_s), np.zeros_like(mass_s)
+    n_cells = case["n_cells"]
+
+    def record(row):
+        P = g.get_particles()
+        _, m, _ = g.get_weights()
+        nc = np.repeat(m[:, 0, 0], P["count"])
+        a, b = TS.size_dists(P["vol"][0], nc)
+        num_p[row] = a / n_cells
+        mass_p[row] = b / n_cells
+
+    record(0)
+    every = int(TS.T_OUT / TS.DEL_T_PART)
+    for k in range(1, int(TS.T_MAX / TS.DEL_T_PART) + 1):
+        g.mc_coag(W.KERNEL_BROWN, TS.DEL_T_PART, step=k)
+        g.aero_state_rebalance(step=k)
+        if k % every == 0:
+            record(k // every)
+    e_num, e_mass = TS.rel_col_err(num_s, num_p), TS.rel_col_err(mass_s, mass_p)
+    assert e_num.max() < 0.2, e_num
+    assert e_mass.max() < 0.3, e_mass
