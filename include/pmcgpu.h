@@ -323,6 +323,18 @@ int pmcgpu_comm_destroy(pmcgpu_ctx* ctx);
 int pmcgpu_get_trans_probs(pmcgpu_ctx* ctx, double* adv, double* diff, double* vert);
 int pmcgpu_get_trans_moved(pmcgpu_ctx* ctx, int* n_moved);
 
+/* The per-cell diagnostics of partmc_process (interface/wrf_pmc_driver.F90:826-944) as device reductions, so that
+ * a history alarm does not pull the particles to the host: total number concentration (:840), wet number
+ * concentration (aero_state_total_num_conc_wet), total mass concentration (:846-848), number and mass size
+ * distributions over the DRY diameter on the logarithmic grid bin_grid_make(LOG, n_bin, d_min, d_max) (the
+ * reference uses 100, 1d-9, 1d-3; bin_grid_histogram_1d, bin_grid.F90:225-248: weights divided by the bin width in
+ * ln d), number concentration per weight class (= source in WRF, :858-861) and mass concentration of every species
+ * (sum of species mass x number concentration; :865-930 picks its named species from this table).
+ * Outputs are [n_cells], [n_cells][n_bin], [n_cells][n_class], [n_cells][n_spec]; host or device; any may be NULL. */
+int pmcgpu_partmc_process(pmcgpu_ctx* ctx, int n_bin, double d_min, double d_max, double* tot_num_conc,
+                          double* tot_wet_num_conc, double* tot_mass_conc, double* num_dist, double* mass_dist,
+                          double* num_conc_by_class, double* species_mass_conc);
+
 /* ---- measurement ---------------------------------------------------------
  * per-kernel CUDA-event timing on the context's stream; pmcgpu_profile_read writes one
  * "kernel_name total_ms launches" line per kernel into buf. */

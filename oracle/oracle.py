@@ -349,6 +349,29 @@ def wrf_to_partmc(nx, nz, ny, p, pb, t_2, qv, alt, z_at_w, rdx, rdy, msftx=None,
     return dict(zip(("temp", "pressure", "rel_humid", "inverse_density", "cell_volume", "height"), out))
 
 
+def partmc_process_cell(vol, wclass, num_conc, density, i_water, n_class, n_bin=100, d_min=1e-9, d_max=1e-3):
+    """the per-cell diagnostics of partmc_process (interface/wrf_pmc_driver.F90:826-944) for one cell, statement by
+    statement in numpy: vol [S][n], wclass [n] (1-based), num_conc [n] (aero_state_num_concs), density [S]"""
+    vol = np.asarray(vol, np.float64)
+    density = np.asarray(density, np.float64)
+    S, n = vol.shape
+    masses = (vol * density[:, None]).sum(axis=0)                      # aero_state_masses
+    dry = np.ones(S, bool)
+    if i_water > 0:
+        dry[i_water - 1] = False
+    dry_diam = 2.0 * (3.0 * vol[dry].sum(axis=0) / (4.0 * np.pi)) ** (1.0 / 3.0)  # aero_state_dry_diameters
+    out = dict(tot_num_conc=num_conc.sum(), tot_mass_conc=(masses * num_conc).sum(),
+               tot_wet_num_conc=num_conc[vol[i_water - 1] > 0].sum() if i_water > 0 else 0.0)
+    width = (np.log(d_max) - np.log(d_min)) / n_bin                    # bin_grid_make, log grid
+    b = bin_grid_find(n_bin, d_min, d_max, dry_diam).astype(int)      # bin_grid_find (bin_grid.F90:143)
+    ok = (b >= 1) & (b <= n_bin)
+    out["num_dist"] = np.bincount(b[ok] - 1, weights=num_conc[ok] / width, minlength=n_bin)      # bin_grid_histogram_1d
+    out["mass_dist"] = np.bincount(b[ok] - 1, weights=(num_conc * masses)[ok] / width, minlength=n_bin)
+    out["num_conc_by_class"] = np.bincount(np.asarray(wclass) - 1, weights=num_conc, minlength=n_class)
+    out["species_mass_conc"] = (vol * density[:, None] * num_conc[None, :]).sum(axis=1)
+    return out
+
+
 def run_sect(n_bin, d_min, d_max, density, total_num_conc, geom_mean_diam, log10_sigma, kernel_type, temp, pressure,
              t_max, del_t, t_output):
     """the reference's sectional coagulation solver (run_sect.F90:56-362) for one log-normal mode of a one-species

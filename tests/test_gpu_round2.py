@@ -236,3 +236,23 @@ def test_device_brownian_against_the_sectional_solver(mods):
     e_num, e_mass = TS.rel_col_err(num_s, num_p), TS.rel_col_err(mass_s, mass_p)
     assert e_num.max() < 0.2, e_num
     assert e_mass.max() < 0.3, e_mass
+
+
+def test_partmc_process_diagnostics_on_device(mods):
+    """pmcgpu_partmc_process (interface/wrf_pmc_driver.F90:826-944) against the numpy statement of the same
+    reductions: totals, wet number, size distributions over the dry diameter, per class, per species (1e-12)"""
+    W, O = mods
+    case = common.make_cells(n_cells=5, n_per_cell=400, n_spec=4, n_class=2, seed=12)
+    case["vol"][3, ::7] = 0.0  # some particles without water
+    g = common.gpu_from_case(W, case)
+    d = g.partmc_process(n_bin=100, d_min=1e-9, d_max=1e-3)
+    off = np.concatenate([[0], np.cumsum(case["counts"])])
+    sp = case["sp"]
+    for c in range(case["n_cells"]):
+        a, b = off[c], off[c + 1]
+        nc = case["wmag"][c, case["wclass"][a:b] - 1, 0]
+        r = O.partmc_process_cell(case["vol"][:, a:b], case["wclass"][a:b], nc, sp["density"], sp["i_water"], 2)
+        for k in ("tot_num_conc", "tot_wet_num_conc", "tot_mass_conc", "num_dist", "mass_dist", "num_conc_by_class",
+                  "species_mass_conc"):
+            np.testing.assert_allclose(d[k][c], r[k], rtol=1e-12, atol=0, err_msg="%d %s" % (c, k))
+    assert d["tot_num_conc"][3] == 0.0 and (d["tot_wet_num_conc"] < d["tot_num_conc"])[[0, 1, 2, 4]].all()
