@@ -135,3 +135,43 @@ def test_two_rank_transport_bit_exact(n_spec, is_open):
             assert x["next_id"][lc] == o.L.pmco_get_next_id(o.h, int(c))
             n_checked += 1
     assert n_checked == case["n_cells"]
+
+
+@pytest.mark.gpu
+def test_two_contexts_on_two_devices_in_one_process():
+    """kernel attributes (shared memory above 48 KB) and occupancy figures are kept per context, and every entry
+    point selects the context's device: two contexts on two devices in ONE process give the same results"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    import common
+    import wrf_partmc_b200 as W
+    from wrf_partmc_b200.host import synthetic
+    case = synthetic.make_patch(4, 3, 3, 900, 20, seed=3)
+    sp = case["sp"]
+    res = []
+    gs = []
+    for dev in (0, 1):
+        data = W.AeroData(sp["density"], sp["kappa"], sp["molec_weight"], sp["num_ions"], sp["i_water"])
+        g = W.PartMCGPU(data, nx=4, nz=3, ny=3, n_group=1, n_class=2, n_part_ideal=case["n_part_ideal"],
+                        cell_capacity=2400, seed=case["seed"], device=dev)
+        gs.append(g)
+    f = None
+    for g in gs:  # interleaved use of the two contexts
+        g.set_particles(case["counts"], case["vol"], case["wgroup"], case["wclass"], case["id"], case["n_primary"],
+                        case["hyst"], case["lct"], case["gct"])
+        g.set_weights(case["wtype"], case["wmag"], case["wexp"])
+        g.set_env(temp=case["T"], pressure=case["P"], rel_humid=case["RH"], inverse_density=case["rrho"],
+                  cell_volume=case["cell_volume"])
+        g.condense_equilib_particles()
+    f = synthetic.patch_fields(synthetic.transport_fields(case, gs[0].partmc_to_wrf()), 0, 4, 0, 3)
+    for step in range(2):
+        for g in gs:
+            g.partmc_timestep(temp=case["T"] - 0.1, pressure=case["P"] - 100.0, elapsed_time=step * 60.0, dt=60.0,
+                              chem_dt=60.0, do_coagulation=True, coag_kernel_type=W.KERNEL_BROWN,
+                              do_condensation=True, step=2 * step)
+            g.wrf_pmc_trans_driver(f, step=2 * step + 1)
+    P0, P1 = gs[0].get_particles(), gs[1].get_particles()
+    assert np.array_equal(P0["count"], P1["count"]) and np.array_equal(P0["id"], P1["id"])
+    assert np.array_equal(P0["vol"], P1["vol"])
+    assert np.array_equal(gs[0].rel_humid(), gs[1].rel_humid())

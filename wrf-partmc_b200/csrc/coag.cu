@@ -869,6 +869,7 @@ int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck);
 
 extern "C" int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_t, unsigned int step,
                               int* tot_n_samp, int* tot_n_coag) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   // mc_coag starts with aero_state_sort (coagulation.F90:63).  The device state is
   // unsorted between steps, so this is a full sort (valid_sort = .false.) followed by

@@ -1731,6 +1731,7 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
 }
 
 extern "C" int pmcgpu_set_condense_method(pmcgpu_ctx* ctx, int method) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || (method != 4 && method != 5)) return PMCGPU_ERR_ARG;
   ctx->cond_method = method;
   return PMCGPU_OK;
@@ -1739,6 +1740,7 @@ extern "C" int pmcgpu_set_condense_method(pmcgpu_ctx* ctx, int method) {
 extern "C" int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_final, const double* pressure_final,
                                          double del_t, double reltol, double* rel_humid_out, int* stats_out,
                                          double* water_rel_error_out) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !temp_final || !pressure_final || !(del_t > 0.0)) return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;
   DevView* cw = &v;
@@ -1813,6 +1815,7 @@ __global__ void k_condense_equilib(DevView v) {
   }
 }
 extern "C" int pmcgpu_condense_equilib_particles(pmcgpu_ctx* ctx) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   if (ctx->v.i_water < 1) return PMCGPU_ERR_ARG;
   k_condense_equilib<<<ctx->v.n_cells, 128, 0, ctx->stream>>>(ctx->v);
@@ -1838,6 +1841,7 @@ __global__ void k_eval_cond_rates(int n, const double* __restrict__ in, double* 
   o[0] = Ddot; o[1] = Hd; o[2] = a; o[3] = b; o[4] = c; o[5] = dH;
 }
 extern "C" int pmcgpu_eval_condense_rates(pmcgpu_ctx* ctx, int n, const double* in, double* out) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || n < 0 || !in || !out) return PMCGPU_ERR_ARG;
   double *di = nullptr, *dout = nullptr;
   CUDA_OK(ctx, cudaMalloc((void**)&di, (size_t)n * 9 * sizeof(double)));

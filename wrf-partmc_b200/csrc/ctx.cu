@@ -167,6 +167,7 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
 }
 
 extern "C" int pmcgpu_destroy(pmcgpu_ctx* ctx) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   cudaStreamSynchronize(ctx->stream);
   for (void* p : ctx->allocs) cudaFree(p);
@@ -182,6 +183,7 @@ extern "C" const char* pmcgpu_last_error(pmcgpu_ctx* ctx) { return ctx ? ctx->er
 extern "C" long long pmcgpu_launch_count(pmcgpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
 extern "C" void* pmcgpu_stream(pmcgpu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 extern "C" int pmcgpu_synchronize(pmcgpu_ctx* ctx) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
   return PMCGPU_OK;
 }
@@ -242,6 +244,7 @@ __global__ void k_gather_particles(DevView v, const long long* __restrict__ off,
 extern "C" int pmcgpu_set_particles(pmcgpu_ctx* ctx, const int* cell_count, const double* vol, const int* wgroup,
                                     const int* wclass, const int64_t* id, const int* n_primary, const int* hyst,
                                     const double* lct, const double* gct) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !cell_count) return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;
   std::vector<long long> off((size_t)v.n_cells + 1, 0);
@@ -275,6 +278,7 @@ extern "C" int pmcgpu_set_particles(pmcgpu_ctx* ctx, const int* cell_count, cons
 }
 
 extern "C" int pmcgpu_get_counts(pmcgpu_ctx* ctx, int* cell_count) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !cell_count) return PMCGPU_ERR_ARG;
   CUDA_OK(ctx, cudaMemcpyAsync(cell_count, ctx->v.count, ctx->v.n_cells * sizeof(int), cudaMemcpyDeviceToHost,
                                ctx->stream));
@@ -323,10 +327,12 @@ static int gather_impl(pmcgpu_ctx* ctx, long long n_total, double* vol, int* wgr
 }
 extern "C" int pmcgpu_get_particles(pmcgpu_ctx* ctx, long long n_total, double* vol, int* wgroup, int* wclass,
                                     int64_t* id, int* n_primary, int* hyst, double* lct, double* gct) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   return gather_impl(ctx, n_total, vol, wgroup, wclass, id, n_primary, hyst, lct, gct, nullptr);
 }
 extern "C" int pmcgpu_get_bins(pmcgpu_ctx* ctx, long long n_total, int* bin_of_particle) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !bin_of_particle) return PMCGPU_ERR_ARG;
   return gather_impl(ctx, n_total, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
                      bin_of_particle);
@@ -338,18 +344,21 @@ extern "C" int pmcgpu_get_bins(pmcgpu_ctx* ctx, long long n_total, int* bin_of_p
   if (dst) CUDA_OK(ctx, cudaMemcpyAsync(dst, src, (size_t)(n) * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
 
 extern "C" int pmcgpu_set_next_id(pmcgpu_ctx* ctx, const int64_t* next_id) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !next_id) return PMCGPU_ERR_ARG;
   H2D_OPT(ctx->v.next_id, next_id, ctx->v.n_cells, long long)
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_next_id(pmcgpu_ctx* ctx, int64_t* next_id) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !next_id) return PMCGPU_ERR_ARG;
   D2H_OPT(next_id, ctx->v.next_id, ctx->v.n_cells, long long)
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_set_weights(pmcgpu_ctx* ctx, const int* type, const double* magnitude, const double* exponent) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   const size_t n = (size_t)ctx->v.n_cells * ctx->v.C * ctx->v.G;
   H2D_OPT(ctx->v.wtype, type, n, int) H2D_OPT(ctx->v.wmag, magnitude, n, double) H2D_OPT(ctx->v.wexp, exponent, n, double)
@@ -362,11 +371,13 @@ extern "C" int pmcgpu_set_weights(pmcgpu_ctx* ctx, const int* type, const double
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_set_rng_step(pmcgpu_ctx* ctx, unsigned step) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   ctx->rng_step = step;
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_weights(pmcgpu_ctx* ctx, int* type, double* magnitude, double* exponent) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   const size_t n = (size_t)ctx->v.n_cells * ctx->v.C * ctx->v.G;
   D2H_OPT(type, ctx->v.wtype, n, int) D2H_OPT(magnitude, ctx->v.wmag, n, double) D2H_OPT(exponent, ctx->v.wexp, n, double)
@@ -375,6 +386,7 @@ extern "C" int pmcgpu_get_weights(pmcgpu_ctx* ctx, int* type, double* magnitude,
 }
 extern "C" int pmcgpu_set_env(pmcgpu_ctx* ctx, const double* temp, const double* pressure, const double* rel_humid,
                               const double* inverse_density, const double* cell_volume) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   const size_t n = ctx->v.n_cells;
   H2D_OPT(ctx->v.temp, temp, n, double) H2D_OPT(ctx->v.pres, pressure, n, double) H2D_OPT(ctx->v.rh, rel_humid, n, double)
@@ -383,12 +395,14 @@ extern "C" int pmcgpu_set_env(pmcgpu_ctx* ctx, const double* temp, const double*
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_rel_humid(pmcgpu_ctx* ctx, double* rel_humid) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !rel_humid) return PMCGPU_ERR_ARG;
   D2H_OPT(rel_humid, ctx->v.rh, ctx->v.n_cells, double)
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_grid(pmcgpu_ctx* ctx, int* n_bin, double* grid_min, double* grid_max) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   const size_t n = ctx->v.n_cells;
   D2H_OPT(n_bin, ctx->v.grid_nb, n, int) D2H_OPT(grid_min, ctx->v.grid_min, n, double)
@@ -397,12 +411,14 @@ extern "C" int pmcgpu_get_grid(pmcgpu_ctx* ctx, int* n_bin, double* grid_min, do
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_bin_counts(pmcgpu_ctx* ctx, int* counts) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !counts) return PMCGPU_ERR_ARG;
   D2H_OPT(counts, ctx->v.bin_count, (size_t)ctx->v.n_cells * ctx->v.C * ctx->v.nbcap, int)
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_kernel_max(pmcgpu_ctx* ctx, int cell, double* kmax) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !kmax || cell < 0 || cell >= ctx->v.n_cells) return PMCGPU_ERR_ARG;
   int nb = 0;
   CUDA_OK(ctx, cudaMemcpyAsync(&nb, ctx->v.grid_nb + cell, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
@@ -412,6 +428,7 @@ extern "C" int pmcgpu_get_kernel_max(pmcgpu_ctx* ctx, int cell, double* kmax) {
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_condense_stats(pmcgpu_ctx* ctx, int* stats) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !stats) return PMCGPU_ERR_ARG;
   D2H_OPT(stats, ctx->v.cond_stats, (size_t)3 * ctx->v.n_cells, int)
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -420,6 +437,7 @@ extern "C" int pmcgpu_get_condense_stats(pmcgpu_ctx* ctx, int* stats) {
 // n_part_ideal(n_group, n_class) (aero_state.F90:241 sets every entry to n_part / (n_group n_class); a host
 // may give each (group, class) its own value): n_part_ideal[(class - 1) * n_group + (group - 1)]
 extern "C" int pmcgpu_set_n_part_ideal(pmcgpu_ctx* ctx, const double* n_part_ideal) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !n_part_ideal) return PMCGPU_ERR_ARG;
   const size_t n = (size_t)ctx->v.C * ctx->v.G;
   for (size_t q = 0; q < n; q++)
@@ -429,6 +447,7 @@ extern "C" int pmcgpu_set_n_part_ideal(pmcgpu_ctx* ctx, const double* n_part_ide
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_work(pmcgpu_ctx* ctx, unsigned long long* work, int reset) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !work) return PMCGPU_ERR_ARG;
   CUDA_OK(ctx, cudaMemcpyAsync(work, ctx->v.work, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
   if (reset) CUDA_OK(ctx, cudaMemsetAsync(ctx->v.work, 0, 4 * sizeof(unsigned long long), ctx->stream));
@@ -448,6 +467,7 @@ int pmc_count_particles_async(pmcgpu_ctx* ctx) {
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_coag_stats(pmcgpu_ctx* ctx, int* tot_n_samp, int* tot_n_coag) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   D2H_OPT(tot_n_samp, ctx->v.coag_samp, ctx->v.n_cells, int)
   D2H_OPT(tot_n_coag, ctx->v.coag_ncoag, ctx->v.n_cells, int)
@@ -455,6 +475,7 @@ extern "C" int pmcgpu_get_coag_stats(pmcgpu_ctx* ctx, int* tot_n_samp, int* tot_
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_cell_status(pmcgpu_ctx* ctx, int* status) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !status) return PMCGPU_ERR_ARG;
   D2H_OPT(status, ctx->v.status, ctx->v.n_cells, int)
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -499,6 +520,7 @@ int pmc_update_density_async(pmcgpu_ctx* ctx, const double* d_new_rrho) {
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_update_density(pmcgpu_ctx* ctx, const double* new_inverse_density) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !new_inverse_density) return PMCGPU_ERR_ARG;
   TmpDev<double> d;
   CUDA_OK(ctx, d.upload(new_inverse_density, ctx->v.n_cells, ctx->stream));
@@ -533,6 +555,7 @@ int pmc_num_conc_async(pmcgpu_ctx* ctx, float* d_out) {
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_num_conc_by_class(pmcgpu_ctx* ctx, float* out) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !out) return PMCGPU_ERR_ARG;
   TmpDev<float> d;
   const size_t n = (size_t)ctx->v.n_cells * ctx->v.C;
@@ -554,6 +577,7 @@ __global__ void k_eval_brown(int n, const double* v1, const double* d1, const do
 }
 extern "C" int pmcgpu_eval_kernel_brown(pmcgpu_ctx* ctx, int n, const double* v1, const double* d1, const double* v2,
                                         const double* d2, const double* temp, const double* pressure, double* out) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || n < 0) return PMCGPU_ERR_ARG;
   TmpDev<double> a, b, c, d, t, p, o;
   CUDA_OK(ctx, a.upload(v1, n, ctx->stream));
@@ -579,6 +603,7 @@ __global__ void k_eval_philox(unsigned seed, int n, const unsigned* cell, const 
 extern "C" int pmcgpu_eval_philox(pmcgpu_ctx* ctx, int n, const unsigned int* cell, const unsigned int* step,
                                   const unsigned int* phase, const unsigned int* a, const unsigned int* b,
                                   const unsigned int* j, double* out) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || n < 0) return PMCGPU_ERR_ARG;
   TmpDev<unsigned> c, s, p, aa, bb, jj;
   TmpDev<double> o;
@@ -598,6 +623,7 @@ extern "C" int pmcgpu_eval_philox(pmcgpu_ctx* ctx, int n, const unsigned int* ce
 
 // ---- per-kernel timing with CUDA events on the launching stream (bench.py's roofline)
 extern "C" int pmcgpu_profile_enable(pmcgpu_ctx* ctx, int on) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   ctx->prof_on = on != 0;
   return PMCGPU_OK;
@@ -618,6 +644,7 @@ static int prof_drain(pmcgpu_ctx* ctx) {
 }
 // writes "name ms launches\n" lines into buf; reset != 0 clears the accumulators afterwards
 extern "C" int pmcgpu_profile_read(pmcgpu_ctx* ctx, char* buf, int buf_len, int reset) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !buf || buf_len < 1) return PMCGPU_ERR_ARG;
   int rc = prof_drain(ctx);
   if (rc) return rc;

@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(DEP_WARPS * 32) k_dep_dry(DevView v, int nx, i
 }
 
 extern "C" int pmcgpu_wrf_pmc_dep_dry_driver(pmcgpu_ctx* ctx, const pmcgpu_dep_args* a) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !a || !a->rmol || !a->znt || !a->ust || !a->ivgtyp || !a->height || !(a->dt > 0.0)) return PMCGPU_ERR_ARG;
   const pmcgpu_config& cfg = ctx->cfg;
   const size_t n2 = (size_t)cfg.nx * cfg.ny;
@@ -182,6 +183,7 @@ __global__ void k_dep_eval(int n, const double* __restrict__ in, double* __restr
   out[3 * k + 2] = p;
 }
 extern "C" int pmcgpu_eval_dep(pmcgpu_ctx* ctx, int n, const double* in, double* out) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || n < 0 || !in || !out) return PMCGPU_ERR_ARG;
   double *di = nullptr, *dout = nullptr;
   CUDA_OK(ctx, cudaMalloc((void**)&di, (size_t)n * 10 * sizeof(double)));

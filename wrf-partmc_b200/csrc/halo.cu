@@ -30,6 +30,7 @@ extern "C" int pmcgpu_comm_unique_id(char* out, int len) {
 // patches tile the periodic domain px x py, rank = rx + px * ry (WRF's 2-D x-y decomposition,
 // WRFV3/main/module_wrf_top.F:505-510)
 extern "C" int pmcgpu_comm_init(pmcgpu_ctx* ctx, const char* unique_id, int n_ranks, int rank, int px, int py) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || n_ranks < 1 || rank < 0 || rank >= n_ranks || px * py != n_ranks) return PMCGPU_ERR_ARG;
   ctx->rank = rank;
   ctx->n_ranks = n_ranks;
@@ -59,6 +60,7 @@ extern "C" int pmcgpu_comm_init(pmcgpu_ctx* ctx, const char* unique_id, int n_ra
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_comm_destroy(pmcgpu_ctx* ctx) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   if (ctx->nccl_comm) {
     ncclCommDestroy((ncclComm_t)ctx->nccl_comm);

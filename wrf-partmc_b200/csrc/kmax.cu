@@ -109,6 +109,7 @@ int pmc_kernel_bounds_async(pmcgpu_ctx* ctx, int ktype) {
 }
 
 extern "C" int pmcgpu_kernel_bounds(pmcgpu_ctx* ctx, int coag_kernel_type) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   int rc = pmc_kernel_bounds_async(ctx, coag_kernel_type);
   if (rc) return rc;

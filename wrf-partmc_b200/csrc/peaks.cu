@@ -15,6 +15,7 @@ __global__ void __launch_bounds__(256) k_dfma_peak(double* out, int iters, doubl
 
 // tflops = 2 * FMAs / best-of-5 event time, FP64
 extern "C" int pmcgpu_measure_fp64_peak(pmcgpu_ctx* ctx, double* tflops) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !tflops) return PMCGPU_ERR_ARG;
   cudaDeviceProp pr;
   CUDA_OK(ctx, cudaGetDeviceProperties(&pr, ctx->cfg.device));

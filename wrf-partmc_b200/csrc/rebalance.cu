@@ -384,6 +384,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_scale_weight(DevView v, int 
 
 extern "C" int pmcgpu_aero_state_scale_weight(pmcgpu_ctx* ctx, int i_group, int i_class, const double* weight_ratio,
                                               int allow_doubling, int allow_halving, unsigned step) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !weight_ratio) return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;
   if (i_group < 1 || i_group > v.G || i_class < 1 || i_class > v.C) return PMCGPU_ERR_ARG;
@@ -576,6 +577,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
 }
 
 extern "C" int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !a || a->n_mode < 1 || !a->mode_type || !a->weight_class || !a->char_radius || !a->log10_std_dev ||
       !a->vol_frac || !a->num_conc || !a->sample_prop || !(a->characteristic_factor > 0.0))
     return PMCGPU_ERR_ARG;
@@ -640,6 +642,7 @@ int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, 
 
 extern "C" int pmcgpu_aero_state_rebalance(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving,
                                            unsigned int step) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   int rc = pmc_rebalance_async(ctx, allow_doubling, allow_halving, step);
   if (rc) return rc;
@@ -651,6 +654,7 @@ extern "C" int pmcgpu_aero_state_rebalance(pmcgpu_ctx* ctx, int allow_doubling, 
 // cells at the end of trans_aero (interface/wrf_pmc_trans_aero.F90:811-955).
 // ---------------------------------------------------------------------------------------------------
 extern "C" int pmcgpu_set_boundary(pmcgpu_ctx* ctx, const pmcgpu_boundary_args* a) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !a || a->n_mode < 1 || !a->mode_type || !a->weight_class || !a->char_radius || !a->log10_std_dev ||
       !a->vol_frac || !a->num_conc || !a->outflow || !a->throw_away)
     return PMCGPU_ERR_ARG;

@@ -445,6 +445,7 @@ int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck) {
 }
 
 extern "C" int pmcgpu_aero_state_sort(pmcgpu_ctx* ctx) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   int rc = pmc_sort_async(ctx, 0);
   if (rc) return rc;

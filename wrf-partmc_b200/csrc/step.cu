@@ -56,6 +56,7 @@ __global__ void k_wrf_to_partmc(int nx, int nz, int ny, const float* __restrict_
 }
 
 extern "C" int pmcgpu_wrf_to_partmc(pmcgpu_ctx* ctx, const pmcgpu_wrf_fields* f) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !f || !f->p || !f->pb || !f->t_2 || !f->qv || !f->alt || !f->z_at_w || !(f->rdx > 0.f) || !(f->rdy > 0.f))
     return PMCGPU_ERR_ARG;
   CUDA_OK(ctx, cudaSetDevice(ctx->cfg.device));
@@ -85,6 +86,7 @@ extern "C" int pmcgpu_wrf_to_partmc(pmcgpu_ctx* ctx, const pmcgpu_wrf_fields* f)
 }
 extern "C" int pmcgpu_get_env_staging(pmcgpu_ctx* ctx, double* temp, double* pressure, double* rel_humid,
                                       double* inverse_density, double* cell_volume, double* height) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !ctx->w2p_ready) return PMCGPU_ERR_ARG;
   const size_t n = (size_t)ctx->v.n_cells;
   double* out[6] = {temp, pressure, rel_humid, inverse_density, cell_volume, height};
@@ -95,6 +97,7 @@ extern "C" int pmcgpu_get_env_staging(pmcgpu_ctx* ctx, double* temp, double* pre
 }
 
 extern "C" int pmcgpu_partmc_timestep(pmcgpu_ctx* ctx, const pmcgpu_timestep_args* a0) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !a0) return PMCGPU_ERR_ARG;
   if (!(a0->chem_dt > 0.0)) return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;
@@ -159,6 +162,7 @@ extern "C" int pmcgpu_partmc_timestep(pmcgpu_ctx* ctx, const pmcgpu_timestep_arg
 }
 
 extern "C" int pmcgpu_check_status(pmcgpu_ctx* ctx) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   return pmc_first_status(ctx);
 }

@@ -938,6 +938,7 @@ static int tr_setup(pmcgpu_ctx* ctx) {
 }
 
 extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_args* a) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !a) return PMCGPU_ERR_ARG;
   int rc = tr_setup(ctx);
   if (rc) return rc;
@@ -1103,6 +1104,7 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
 }
 
 extern "C" int pmcgpu_get_trans_probs(pmcgpu_ctx* ctx, double* adv, double* diff, double* vert) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !ctx->trans_ready) return PMCGPU_ERR_ARG;
   const size_t n = (size_t)ctx->v.n_cells * ctx->v.C;
   if (adv) CUDA_OK(ctx, cudaMemcpyAsync(adv, ctx->t.padv, n * 6 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1112,6 +1114,7 @@ extern "C" int pmcgpu_get_trans_probs(pmcgpu_ctx* ctx, double* adv, double* diff
   return PMCGPU_OK;
 }
 extern "C" int pmcgpu_get_trans_moved(pmcgpu_ctx* ctx, int* n_moved) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !ctx->trans_ready || !n_moved) return PMCGPU_ERR_ARG;
   CUDA_OK(ctx, cudaMemcpyAsync(n_moved, ctx->t.n_moved, ctx->v.n_cells * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
