@@ -97,6 +97,20 @@ def run_gpu(rank, world, port, out_dir, cfg):
         g.set_boundary(b["mode_type"], b["weight_class"], b["char_radius"], b["log10_std_dev"], b["vol_frac"],
                        b["num_conc"][cells], b["outflow"][cells], b["throw_away"][cells])
     moved = 0
+    if cfg.get("expect_overflow"):
+        # the halo message of this job is too small (PMCGPU_HALO_SLAB_CAP): every rank must come back from the
+        # collective exchange with PMCGPU_ERR_CAPACITY on the rank(s) that saw the overflow -- nobody may hang
+        code = 0
+        try:
+            g.wrf_pmc_trans_driver(fp, step=1)
+        except W.PmcGpuError as e:
+            code = e.code
+        P = g.get_particles()
+        np.savez(os.path.join(out_dir, "gpu_%d.npz" % rank), code=code, unique=len(np.unique(P["id"])) == len(P["id"]),
+                 max_count=int(P["count"].max()))
+        dist.barrier()
+        dist.destroy_process_group()
+        return
     for step in range(1, cfg["n_steps"] + 1):
         g.wrf_pmc_trans_driver(fp, step=step)
         moved += int(g.trans_moved().sum())

@@ -138,6 +138,34 @@ def test_two_rank_transport_bit_exact(n_spec, is_open):
 
 
 @pytest.mark.gpu
+def test_two_rank_halo_overflow_returns_on_every_rank():
+    """one particle message too small for what crosses the patch side: the exchange still completes on both ranks
+    (no rank-local early return between two collective exchanges), the overflow is a status, the state consistent"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    import common
+    from oracle import oracle as O
+    cfg = dict(gnx=8, nz=4, gny=3, px=2, py=1, n_per_cell=200, n_spec=4, seed=5, n_steps=1, expect_overflow=True)
+    case = MW.global_case(cfg)
+    o = common.oracle_from_case(O, case)
+    for c in range(case["n_cells"]):
+        o.set_env(c, T=case["T"][c], p=case["P"][c], RH=case["RH"][c], rrho=case["rrho"][c],
+                  cell_volume=case["cell_volume"][c])
+    os.environ["PMCGPU_HALO_SLAB_CAP"] = "8"
+    try:
+        with tempfile.TemporaryDirectory() as d:
+            np.save(os.path.join(d, "num_conc.npy"), o.num_conc_by_class())
+            _spawn("gpu", 2, d, cfg)   # returns only if neither rank hangs
+            r = [dict(np.load(os.path.join(d, "gpu_%d.npz" % k))) for k in range(2)]
+    finally:
+        del os.environ["PMCGPU_HALO_SLAB_CAP"]
+    assert any(int(x["code"]) == 3 for x in r)            # PMCGPU_ERR_CAPACITY where the overflow was seen
+    assert all(bool(x["unique"]) for x in r)              # no record duplicated
+    assert all(int(x["max_count"]) <= 3 * 200 + 64 for x in r)
+
+
+@pytest.mark.gpu
 def test_two_contexts_on_two_devices_in_one_process():
     """kernel attributes (shared memory above 48 KB) and occupancy figures are kept per context, and every entry
     point selects the context's device: two contexts on two devices in ONE process give the same results"""
