@@ -335,6 +335,13 @@ int pmcgpu_partmc_process(pmcgpu_ctx* ctx, int n_bin, double d_min, double d_max
                           double* tot_wet_num_conc, double* tot_mass_conc, double* num_dist, double* mass_dist,
                           double* num_conc_by_class, double* species_mass_conc);
 
+/* Checkpoint / restart of the whole device state of a context (what WRF's restart alarm needs; the reference
+ * writes netCDF, partmc/src/output.F90:827-967): one flat binary file per rank with the particle records in cell
+ * order, weights, env_state, id counters, bin grids and majorant tables.  Draws are counter-based, so a context of
+ * the same geometry that reads the file continues bit for bit. */
+int pmcgpu_checkpoint_write(pmcgpu_ctx* ctx, const char* path);
+int pmcgpu_checkpoint_read(pmcgpu_ctx* ctx, const char* path);
+
 /* ---- measurement ---------------------------------------------------------
  * per-kernel CUDA-event timing on the context's stream; pmcgpu_profile_read writes one
  * "kernel_name total_ms launches" line per kernel into buf. */

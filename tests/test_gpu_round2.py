@@ -256,3 +256,41 @@ def test_partmc_process_diagnostics_on_device(mods):
                   "species_mass_conc"):
             np.testing.assert_allclose(d[k][c], r[k], rtol=1e-12, atol=0, err_msg="%d %s" % (c, k))
     assert d["tot_num_conc"][3] == 0.0 and (d["tot_wet_num_conc"] < d["tot_num_conc"])[[0, 1, 2, 4]].all()
+
+
+def test_checkpoint_restart_continues_bit_for_bit(mods, tmp_path):
+    """pmcgpu_checkpoint_write / _read: a second context restored from the file continues exactly like the first
+    (particles, order, ids, weights, RH, bin grids) through coagulation, condensation and transport"""
+    W, O = mods
+    from wrf_partmc_b200.host import synthetic
+    case, g, fp = _trans_case(W, npc=300, seed=8, nx=4, nz=3, ny=3)
+    g.condense_equilib_particles()
+    met = synthetic.met_sequence(case, 4)
+
+    def steps(ctx, k0, k1):
+        for k in range(k0, k1):
+            T, P_, rrho = met[k]
+            ctx.partmc_timestep(temp=T, pressure=P_, inverse_density=rrho, elapsed_time=k * 60.0, dt=60.0, chem_dt=60.0,
+                                do_coagulation=True, coag_kernel_type=W.KERNEL_BROWN, do_condensation=True, step=2 * k)
+            ctx.wrf_pmc_trans_driver(fp, step=2 * k + 1)
+
+    steps(g, 0, 2)
+    path = str(tmp_path / "ck.bin")
+    g.checkpoint_write(path)
+    steps(g, 2, 4)
+    sp = case["sp"]
+    data = W.AeroData(sp["density"], sp["kappa"], sp["molec_weight"], sp["num_ions"], sp["i_water"])
+    g2 = W.PartMCGPU(data, nx=4, nz=3, ny=3, n_group=1, n_class=2, n_part_ideal=case["n_part_ideal"],
+                     cell_capacity=g.cell_capacity, seed=case["seed"])
+    g2.checkpoint_read(path)
+    steps(g2, 2, 4)
+    A, B = g.get_particles(), g2.get_particles()
+    for k in ("count", "id", "wclass", "vol", "n_primary", "hyst", "lct", "gct"):
+        assert np.array_equal(A[k], B[k]), k
+    assert np.array_equal(g.get_weights()[1], g2.get_weights()[1])
+    assert np.array_equal(g.rel_humid(), g2.rel_humid())
+    assert all(np.array_equal(a, b) for a, b in zip(g.grid(), g2.grid()))
+    assert np.array_equal(g.get_next_id(), g2.get_next_id())
+    g3 = W.PartMCGPU(data, nx=3, nz=3, ny=4, n_group=1, n_class=2, cell_capacity=g.cell_capacity)
+    with pytest.raises(W.PmcGpuError):
+        g3.checkpoint_read(path)  # another geometry

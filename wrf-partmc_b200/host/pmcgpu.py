@@ -460,6 +460,12 @@ class PartMCGPU:
             "species_mass_conc")]))
         return out
 
+    def checkpoint_write(self, path):
+        self._chk(self.L.pmcgpu_checkpoint_write(self.h, C.c_char_p(path.encode())))
+
+    def checkpoint_read(self, path):
+        self._chk(self.L.pmcgpu_checkpoint_read(self.h, C.c_char_p(path.encode())))
+
     def comm_destroy(self):
         self._chk(self.L.pmcgpu_comm_destroy(self.h))
 
