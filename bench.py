@@ -574,7 +574,7 @@ def run_b200(a):
         if dom and dom["kernel"] == "k_condense":
             roofline = {"kernel": "k_condense", "bound": "fp64", "achieved": cond_tflops, "peak": fp64_peak,
                         "unit": "TFLOP/s", "frac": cond_tflops / fp64_peak if fp64_peak else None,
-                        "traffic": 181.6 * cond_particles_per_step,
+                        "traffic": 173.7 * cond_particles_per_step,  # ncu r02_c4: 1.272 GB read + 63 MB written for 7.686e6 particles
                         "traffic_unit": "bytes per launch (ncu capture, scaled by the particle count)",
                         "peak_source": "FP64 FMA microbenchmark in this run (pmcgpu_measure_fp64_peak); "
                                        "MEASURED_PEAKS.json holds no FP64 figure",
