@@ -44,7 +44,7 @@ enum {
 };
 
 /* coag_kernel.F90:24-40 type codes */
-enum { PMCGPU_KERNEL_ADDITIVE = 2, PMCGPU_KERNEL_CONSTANT = 3, PMCGPU_KERNEL_BROWN = 4, PMCGPU_KERNEL_ZERO = 5 };
+enum { PMCGPU_KERNEL_SEDI = 1, PMCGPU_KERNEL_ADDITIVE = 2, PMCGPU_KERNEL_CONSTANT = 3, PMCGPU_KERNEL_BROWN = 4, PMCGPU_KERNEL_ZERO = 5 };
 /* aero_weight.F90:25-30 */
 enum { PMCGPU_WEIGHT_NONE = 1, PMCGPU_WEIGHT_POWER = 2, PMCGPU_WEIGHT_MFA = 3 };
 

@@ -63,7 +63,7 @@ def _i64(a):
     return None if a is None else np.ascontiguousarray(a, dtype=np.int64)
 
 
-KERNEL_ADDITIVE, KERNEL_CONSTANT, KERNEL_BROWN, KERNEL_ZERO = 2, 3, 4, 5
+KERNEL_SEDI, KERNEL_ADDITIVE, KERNEL_CONSTANT, KERNEL_BROWN, KERNEL_ZERO = 1, 2, 3, 4, 5
 WEIGHT_NONE, WEIGHT_POWER = 1, 2
 
 
@@ -406,6 +406,14 @@ def condense_integrate(D, H, D_dry, kappa, num_conc, T0, p0, Tdot, pdot, del_t, 
                                        C.c_double(abstol_scale), C.c_double(abstol_H), C.c_double(h_init),
                                        C.c_int(method), _p(st, C.c_int))
     return rc, D, Hc.value, st
+
+
+def kernel_sedi(v1, v2):
+    """kernel_sedi_helper (coag_kernel_sedi.F90:79-103)"""
+    L = lib()
+    L.pmco_kernel_sedi.restype = C.c_double
+    L.pmco_kernel_sedi.argtypes = [C.c_double, C.c_double]
+    return L.pmco_kernel_sedi(float(v1), float(v2))
 
 
 def kernel_brown(v1, d1, v2, d2, T, p):

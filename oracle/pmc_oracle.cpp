@@ -384,6 +384,86 @@ double kernel_brown_helper(double vol_i, double den_i, double vol_j, double den_
   tmp2 = 4.0 * diffus_sum / (rad_sum * std::sqrt(speedsq_i + speedsq_j));
   return 4.0 * Const::pi * rad_sum * diffus_sum / (tmp1 + tmp2);
 }
+// ---- sedimentation kernel (coag_kernel_sedi.F90): terminal velocities of Beard (1976) as coded in fall_g (:112-173),
+// Hall (1980) collision efficiencies with two-dimensional linear interpolation as coded in effic (:180-291)
+#include "pmc_oracle_sedi_table.hpp"
+// x**n for an integer n >= 0 the way gfortran forms it (libgcc __powidf2: square and multiply)
+static double sedi_powi(double x, int m) {
+  unsigned n = (unsigned)m;
+  double y = (n & 1u) ? x : 1.0;
+  while (n >>= 1) {
+    x = x * x;
+    if (n & 1u) y = y * x;
+  }
+  return y;
+}
+static double sedi_fall_g(double r) {  // r in m, result in m/s
+  static const double b[7] = {-0.318657e1, 0.992696e0, -0.153193e-2, -0.987059e-3, -0.578878e-3, 0.855176e-4, -0.327815e-5};
+  static const double c[6] = {-0.500015e1, 0.523778e1, -0.204914e1, 0.475294e0, -0.542819e-1, 0.238449e-2};
+  const double eta = 1.818e-4, xlamb = 6.62e-6, rhow = 1.0, rhoa = 1.225e-3, grav = 980.665;
+  const double cunh = 1.257 * xlamb, t0 = 273.15;
+  const double sigma = 76.1 - 0.155 * (293.15 - t0);
+  const double stok = 2.0 * grav * (rhow - rhoa) / (9.0 * eta);
+  const double stb = 32.0 * rhoa * (rhow - rhoa) * grav / (3.0 * eta * eta);
+  const double phy = sigma * sigma * sigma * rhoa * rhoa / (sedi_powi(eta, 4) * grav * (rhow - rhoa));
+  const double py = std::pow(phy, 1.0 / 6.0);
+  const double rr = r * 1e2;  // cm
+  double w_inf = 0.0;
+  if (rr <= 1e-3) {
+    w_inf = stok * (rr * rr + cunh * rr);
+  } else if (rr > 1e-3 && rr <= 5.35e-2) {
+    const double x = std::log(stb * rr * rr * rr);
+    double y = 0.0;
+    for (int i = 1; i <= 7; i++) y = y + b[i - 1] * sedi_powi(x, i - 1);
+    const double xrey = (1.0 + cunh / rr) * std::exp(y);
+    w_inf = xrey * eta / (2.0 * rhoa * rr);
+  } else if (rr > 5.35e-2) {
+    double bond = grav * (rhow - rhoa) * (rr * rr) / sigma;
+    if (rr > 0.35) bond = grav * (rhow - rhoa) * (0.35 * 0.35) / sigma;
+    const double x = std::log(16.0 * bond * py / 3.0);
+    double y = 0.0;
+    for (int i = 1; i <= 6; i++) y = y + c[i - 1] * sedi_powi(x, i - 1);
+    const double xrey = py * std::exp(y);
+    w_inf = xrey * eta / (2.0 * rhoa * rr);
+    if (rr > 0.35) w_inf = xrey * eta / (2.0 * rhoa * 0.35);
+  }
+  return w_inf / 100.0;
+}
+static double sedi_effic(double r1, double r2) {
+  const double r_small = std::min(r1 * 1e6, r2 * 1e6), r_big = std::max(r1 * 1e6, r2 * 1e6);
+  const double rq = r_small / r_big;
+  int ir = 1, iq = 1;
+  for (int k = 1; k <= 15; k++)
+    if (r_big > sedi_r0[k - 1]) ir = k + 1;
+  for (int kk = 1; kk <= 21; kk++)
+    if (rq > sedi_rat[kk - 1]) iq = kk + 1;
+  auto E = [&](int i, int j) { return sedi_ecoll[(j - 1) * 15 + (i - 1)]; };
+  double ec;
+  if (ir < 16) {
+    if (ir >= 2) {
+      const double p = (r_big - sedi_r0[ir - 2]) / (sedi_r0[ir - 1] - sedi_r0[ir - 2]);
+      const double q = (rq - sedi_rat[iq - 2]) / (sedi_rat[iq - 1] - sedi_rat[iq - 2]);
+      ec = (1.0 - p) * (1.0 - q) * E(ir - 1, iq - 1) + p * (1.0 - q) * E(ir, iq - 1) + q * (1.0 - p) * E(ir - 1, iq) +
+           p * q * E(ir, iq);
+    } else {
+      const double q = (rq - sedi_rat[iq - 2]) / (sedi_rat[iq - 1] - sedi_rat[iq - 2]);
+      ec = (1.0 - q) * E(1, iq - 1) + q * E(1, iq);
+    }
+  } else {
+    const double q = (rq - sedi_rat[iq - 2]) / (sedi_rat[iq - 1] - sedi_rat[iq - 2]);
+    const double ek = (1.0 - q) * E(15, iq - 1) + q * E(15, iq);
+    ec = std::min(ek, 1.0);
+  }
+  if (ec < 1e-20) die_msg(99, "effic: collision efficiency vanishes");  // :289 pmc_stop(99)
+  return ec;
+}
+// kernel_sedi_helper (coag_kernel_sedi.F90:79-103); spherical particles: the mobility radius is the radius
+double kernel_sedi_helper(double v1, double v2) {
+  const double r1 = sphere_vol2rad(v1), r2 = sphere_vol2rad(v2);
+  const double winf1 = sedi_fall_g(r1), winf2 = sedi_fall_g(r2);
+  const double ec = sedi_effic(r1, r2);
+  return ec * Const::pi * ((r1 + r2) * (r1 + r2)) * std::fabs(winf1 - winf2);
+}
 static const double beta_1 = 1000.0;  // coag_kernel_additive.F90:23
 static const double beta_0 = 0.25 / (60.0 * 2e8);  // coag_kernel_constant.F90:22
 
@@ -421,6 +501,9 @@ void kernel_minmax(int type, double v1, double v2, const AeroData& d, const EnvS
   } else if (type == KERNEL_ZERO) {
     kmin = 0.0;
     kmax = 0.0;
+  } else if (type == KERNEL_SEDI) {
+    kmin = kernel_sedi_helper(v1, v2);  // kernel_sedi_minmax (coag_kernel_sedi.F90:52-73)
+    kmax = kmin;
   } else {
     die_msg(330498208, "Unknown kernel type");
   }
@@ -429,6 +512,7 @@ double kernel(int type, const Particle& p1, const Particle& p2, const AeroData& 
   if (type == KERNEL_ADDITIVE) return beta_1 * (particle_volume(p1) + particle_volume(p2));
   if (type == KERNEL_CONSTANT) return beta_0;
   if (type == KERNEL_ZERO) return 0.0;
+  if (type == KERNEL_SEDI) return kernel_sedi_helper(particle_volume(p1), particle_volume(p2));
   if (type == KERNEL_BROWN) {
     const double v1 = particle_volume(p1), v2 = particle_volume(p2);
     const double d1 = particle_density(p1, d), d2 = particle_density(p2, d);

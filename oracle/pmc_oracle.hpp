@@ -239,6 +239,7 @@ double awa_single_num_conc(const WeightArray& a, const Particle& p);  // :218-22
 
 // ---------------------------------------------------------------- coagulation kernels
 enum { KERNEL_SEDI = 1, KERNEL_ADDITIVE = 2, KERNEL_CONSTANT = 3, KERNEL_BROWN = 4, KERNEL_ZERO = 5 };
+double kernel_sedi_helper(double v1, double v2);  // coag_kernel_sedi.F90:79-103
 double kernel_brown_helper(double vol_i, double den_i, double vol_j, double den_j, double temp,
                            double pressure);  // coag_kernel_brown.F90:111-197
 void kernel_minmax(int type, double v1, double v2, const AeroData& d, const EnvState& e, double& kmin,

@@ -190,6 +190,7 @@ int pmco_kernel_bounds(void* h, int cell, int kernel_type, double* kmin, double*
   if (kmax) std::memcpy(kmax, mx.data(), mx.size() * sizeof(double));
   ORACLE_CATCH(d)
 }
+double pmco_kernel_sedi(double v1, double v2) { return kernel_sedi_helper(v1, v2); }
 double pmco_kernel_brown(double v1, double d1, double v2, double d2, double T, double p) {
   return kernel_brown_helper(v1, d1, v2, d2, T, p);
 }

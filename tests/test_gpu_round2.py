@@ -238,11 +238,15 @@ def test_device_brownian_against_the_sectional_solver(mods):
     assert e_mass.max() < 0.3, e_mass
 
 
-def test_partmc_process_diagnostics_on_device(mods):
+@pytest.mark.parametrize("weight", ["flat", "nummass"])
+def test_partmc_process_diagnostics_on_device(mods, weight):
     """pmcgpu_partmc_process (interface/wrf_pmc_driver.F90:826-944) against the numpy statement of the same
-    reductions: totals, wet number, size distributions over the dry diameter, per class, per species (1e-12)"""
+    reductions: totals, wet number, size distributions over the dry diameter, per class, per species (1e-12).
+    With two weight groups a particle's number concentration is the harmonic combination over the groups of its
+    class (aero_weight_array_num_conc, aero_weight_array.F90:232-271), not its own group's weight."""
     W, O = mods
-    case = common.make_cells(n_cells=5, n_per_cell=400, n_spec=4, n_class=2, seed=12)
+    case = common.make_cells(n_cells=5, n_per_cell=400, n_spec=4, n_class=2, seed=12, weight=weight,
+                             n_group=2 if weight == "nummass" else 1)
     case["vol"][3, ::7] = 0.0  # some particles without water
     g = common.gpu_from_case(W, case)
     d = g.partmc_process(n_bin=100, d_min=1e-9, d_max=1e-3)
@@ -251,6 +255,9 @@ def test_partmc_process_diagnostics_on_device(mods):
     for c in range(case["n_cells"]):
         a, b = off[c], off[c + 1]
         nc = case["wmag"][c, case["wclass"][a:b] - 1, 0]
+        if weight == "nummass":
+            rad = (3.0 * case["vol"][:, a:b].sum(axis=0) / (4.0 * np.pi)) ** (1.0 / 3.0)
+            nc = 1.0 / (1.0 / nc + 1.0 / (case["wmag"][c, case["wclass"][a:b] - 1, 1] * rad ** -3.0))
         r = O.partmc_process_cell(case["vol"][:, a:b], case["wclass"][a:b], nc, sp["density"], sp["i_water"], 2)
         for k in ("tot_num_conc", "tot_wet_num_conc", "tot_mass_conc", "num_dist", "mass_dist", "num_conc_by_class",
                   "species_mass_conc"):
@@ -294,3 +301,66 @@ def test_checkpoint_restart_continues_bit_for_bit(mods, tmp_path):
     g3 = W.PartMCGPU(data, nx=3, nz=3, ny=4, n_group=1, n_class=2, cell_capacity=g.cell_capacity)
     with pytest.raises(W.PmcGpuError):
         g3.checkpoint_read(path)  # another geometry
+
+
+def test_sedi_kernel_bounds_table(mods):
+    """est_k_minmax_binned_unweighted with the sedimentation kernel (coag_kernel_sedi.F90:52-103): 1e-10 relative
+    wherever the majorant is not zero (equal radii give exactly zero in both)"""
+    W, O = mods
+    case = common.make_cells(3, 400, n_spec=1, seed=21, ragged=False, num_conc=1e9, r_g=1e-5, log10_sigma=0.35)
+    g = common.gpu_from_case(W, case)
+    o = common.oracle_from_case(O, case)
+    g.aero_state_sort()
+    g.kernel_bounds(W.KERNEL_SEDI)
+    for c in range(3):
+        o.sort(c)
+        _, kmax = o.kernel_bounds(c, O.KERNEL_SEDI)
+        dev = g.kernel_max(c)
+        assert dev.shape == kmax.shape and (kmax > 0).any()
+        assert np.array_equal(dev == 0.0, kmax == 0.0)
+        nz = kmax > 0
+        assert (np.abs(dev[nz] - kmax[nz]) / kmax[nz]).max() < 1e-10
+
+
+@pytest.mark.parametrize("weight", ["flat", "nummass"])
+def test_mc_coag_sedi_bit_exact(mods, weight):
+    """mc_coag with the sedimentation kernel on cloud droplets (test/sedi: D_g = 20 um, 1e9 m^-3), with rebalancing:
+    same sample / event counts and the same surviving particles as the oracle, step by step"""
+    W, O = mods
+    case = common.make_cells(4, 1000, n_spec=1, seed=17, num_conc=1e9, r_g=1e-5, log10_sigma=0.2, weight=weight,
+                             n_group=2 if weight == "nummass" else 1)
+    g = common.gpu_from_case(W, case, cell_capacity=4096)
+    o = common.oracle_from_case(O, case)
+    events = 0
+    for step in range(1, 25):
+        ns, nc = g.mc_coag(W.KERNEL_SEDI, 5.0, step=step)
+        g.aero_state_rebalance(True, True, step=step)
+        for c in range(case["n_cells"]):
+            o.sort(c, force_resort=True, physical=True, edge_recheck=True)
+            s, k, _ = o.mc_coag(c, O.KERNEL_SEDI, 5.0, step=step)
+            o.rebalance(c, True, True, step=step)
+            assert (s, k) == (ns[c], nc[c]), "cell %d step %d: oracle (%d,%d) device (%d,%d)" % (c, step, s, k, ns[c], nc[c])
+        events += int(nc.sum())
+    assert events > 200
+    common.assert_same_population(g, o, case)
+
+
+def test_bidisperse_on_device_against_ode(mods):
+    """partmc/test/bidisperse on the device: 10000 droplets of 10 um and one of 100 um, del_t = 1 s, 600 s, no
+    doubling; small-droplet number and big-drop mass against the one-variable ODE at 0.3 (test_bidisperse_1.sh)"""
+    W, O = mods
+    import test_oracle_sedi as T
+    t_out = np.arange(0.0, 601.0, 10.0)
+    ode, comp_vol = T.bidisperse_ode(t_out)
+    case = T.bidisperse_case()
+    g = common.gpu_from_case(W, case, cell_capacity=T.N_SMALL + 64)
+    rows = [(0.0,) + T.bidisperse_columns(case["vol"][0], comp_vol)]
+    for k in range(1, 601):
+        g.mc_coag(W.KERNEL_SEDI, 1.0, step=k)
+        if k % 10 == 0:
+            rows.append((float(k),) + T.bidisperse_columns(g.get_particles()["vol"][0], comp_vol))
+    part = np.array(rows)
+    err = T.rel_col_err(ode[:, 1:], part[:, 1:])
+    assert err.max() < 0.3, err
+    assert part[-1, 1] < 0.5 * part[0, 1]
+    assert g.get_particles()["vol"].sum() == pytest.approx(case["vol"].sum(), rel=1e-12)

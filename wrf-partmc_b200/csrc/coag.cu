@@ -22,6 +22,7 @@
 // same swap-with-last bookkeeping as integer_rmap2_remove (:190-243).
 #define PMC_RNG_NOINLINE
 #include "pmcgpu_internal.cuh"
+#include "sedi.cuh"
 
 #ifndef COAG_MIN_CTAS
 #define COAG_MIN_CTAS 12  // 40 registers: measured 28.2 (5) / 27.4 (6) / 23.3 (8) / 22.1 (10) / 20.2 (12) / 20.1 (16) ms per K4 step
@@ -154,6 +155,8 @@ __device__ __forceinline__ double unweighted_kernel(int ktype, const BrownEnv& b
     return BETA_1 * (v1 + v2);
   } else if (ktype == PMCGPU_KERNEL_CONSTANT) {
     return BETA_0;
+  } else if (ktype == PMCGPU_KERNEL_SEDI) {
+    return kernel_sedi(v1, v2);
   }
   return 0.0;
 }

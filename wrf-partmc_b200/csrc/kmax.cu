@@ -3,7 +3,8 @@
 // est_k_minmax_binned_unweighted (partmc/src/coag_kernel.F90:253-280) ->
 // est_k_minmax_for_bin_unweighted (:286-341: 3x3 linear-in-volume samples of
 // the two bins, over_scale = 2) -> kernel_brown_minmax
-// (coag_kernel_brown.F90:58-101: 3x3 densities in [min rho, max rho]).
+// (coag_kernel_brown.F90:58-101: 3x3 densities in [min rho, max rho]); the additive, constant, zero and
+// sedimentation (coag_kernel_sedi.F90:52-73, sedi.cuh) kernels take the generic 3x3 volume samples.
 // Like the reference, a cell's table is rebuilt only when its bin grid was
 // remade (coag_kernel_bounds_valid, aero_sorted.F90:132, coagulation.F90:64).
 //
@@ -14,6 +15,7 @@
 // 81-sample maxima from shared memory: nb*9 heavy evaluations instead of
 // nb^2*81.  FP64-pipe bound; k_min is never read on the path and is not kept.
 #include "pmcgpu_internal.cuh"
+#include "sedi.cuh"
 
 #define KMAX_THREADS 256
 static const double BETA_1 = 1000.0;                 // coag_kernel_additive.F90:23
@@ -61,14 +63,14 @@ __global__ void __launch_bounds__(KMAX_THREADS) k_kernel_bounds(DevView v, int k
     for (int q = threadIdx.x; q < nb * nb; q += blockDim.x) {
       const int b1 = q % nb + 1, b2 = q / nb + 1;
       double kmax = 0.0;
-      if (ktype == PMCGPU_KERNEL_ADDITIVE) {
+      if (ktype == PMCGPU_KERNEL_ADDITIVE || ktype == PMCGPU_KERNEL_SEDI) {
         const double v1l = rad2vol(grid_edge(gmin, gmax, nb, b1)), v1h = rad2vol(grid_edge(gmin, gmax, nb, b1 + 1));
         const double v2l = rad2vol(grid_edge(gmin, gmax, nb, b2)), v2h = rad2vol(grid_edge(gmin, gmax, nb, b2 + 1));
         for (int i = 1; i <= 3; i++)
           for (int j = 1; j <= 3; j++) {
             const double v1 = interp_linear_disc(v1l, v1h, 3, i);
             const double v2 = interp_linear_disc(v2l, v2h, 3, j);
-            const double k = BETA_1 * (v1 + v2);
+            const double k = (ktype == PMCGPU_KERNEL_SEDI) ? kernel_sedi(v1, v2) : BETA_1 * (v1 + v2);
             kmax = (i == 1 && j == 1) ? k : fmax(kmax, k);
           }
       } else if (ktype == PMCGPU_KERNEL_CONSTANT) {
@@ -86,7 +88,7 @@ __global__ void __launch_bounds__(KMAX_THREADS) k_kernel_bounds(DevView v, int k
 int pmc_kernel_bounds_async(pmcgpu_ctx* ctx, int ktype) {
   DevView& v = ctx->v;
   if (ktype != PMCGPU_KERNEL_BROWN && ktype != PMCGPU_KERNEL_ADDITIVE && ktype != PMCGPU_KERNEL_CONSTANT &&
-      ktype != PMCGPU_KERNEL_ZERO) {
+      ktype != PMCGPU_KERNEL_ZERO && ktype != PMCGPU_KERNEL_SEDI) {
     ctx->err = "unknown kernel type";  // coag_kernel.F90:121 die_msg(200724934)
     return 200724934;
   }

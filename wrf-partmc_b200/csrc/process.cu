@@ -53,8 +53,8 @@ __global__ void __launch_bounds__(PROC_THREADS) k_partmc_process(DevView v, int 
       mass += x * v.density[s];  // aero_particle_mass (aero_particle.F90:252)
       if (s == iw) water = x; else vdry += x;
     }
-    const size_t wi = (size_t)cell * v.C * v.G + gc;
-    const double nc = weight_nc(v.wtype[wi], v.wmag[wi], v.wexp[wi], vol2rad(vt));  // aero_weight_array_num_conc
+    // aero_weight_array_num_conc (aero_weight_array.F90:257-271): harmonic over the groups of the particle's class
+    const double nc = awa_nc_at_radius(v, cell, gc / v.G + 1, vol2rad(vt));
     t_num += nc;
     if (water > 0.0) t_wet += nc;
     t_mass += mass * nc;

@@ -16,7 +16,7 @@ import os
 
 import numpy as np
 
-KERNEL_ADDITIVE, KERNEL_CONSTANT, KERNEL_BROWN, KERNEL_ZERO = 2, 3, 4, 5
+KERNEL_SEDI, KERNEL_ADDITIVE, KERNEL_CONSTANT, KERNEL_BROWN, KERNEL_ZERO = 1, 2, 3, 4, 5
 WEIGHT_NONE, WEIGHT_POWER = 1, 2
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
