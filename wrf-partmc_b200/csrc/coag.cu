@@ -147,8 +147,12 @@ __device__ __noinline__ void cell_list_append(CellCtx& cx, int c, int b, int slo
   __syncwarp();
 }
 
+// KT: the kernel type when it is known at compile time (the Brownian instance carries no code of the other
+// kernels: mc_coag is instruction-fetch bound), 0 = decided by ktype at run time
+template <int KT>
 __device__ __forceinline__ double unweighted_kernel(int ktype, const BrownEnv& be, double v1, double m1, double v2,
                                                     double m2) {
+  if (KT == PMCGPU_KERNEL_BROWN) return brown_pair(brown_part(be, v1, m1 / v1), brown_part(be, v2, m2 / v2));
   if (ktype == PMCGPU_KERNEL_BROWN) {
     return brown_pair(brown_part(be, v1, m1 / v1), brown_part(be, v2, m2 / v2));
   } else if (ktype == PMCGPU_KERNEL_ADDITIVE) {
@@ -413,6 +417,7 @@ __device__ __noinline__ void cell_dup_particle(CellCtx& cx, int p, int c, double
 // evaluate the kernel of 32 candidate samples ahead (their draws are addressed by sample number), the
 // warp then consumes them in order with the running sums held one species per lane; a removal of a
 // source particle invalidates the candidates behind it, which are re-evaluated.
+template <int KT>
 __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const BrownEnv& be, double k_max, double del_t, unsigned step,
                                 unsigned pid, int bt, int bs, int ct, int cs, int cc, int& tot_n_samp,
                                 int& tot_n_coag) {
@@ -463,7 +468,7 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
         double v_i, m_i;
         part_vol_mass(cx, i_part, v_i, m_i);
         const double r_i = vol2rad(v_i);
-        const double uk = unweighted_kernel(ktype, be, v_i, m_i, v_t, m_t);
+        const double uk = unweighted_kernel<KT>(ktype, be, v_i, m_i, v_t, m_t);
         prob_coag = (uk * coag_num_conc_factor(cx, r_i, r_t, cs, ct, ct)) * accept_factor;
         u_acc = rng_uniform(skey, j0 + 1);
         u_rem = rng_uniform(skey, j0 + 2);
@@ -610,6 +615,7 @@ __device__ __forceinline__ bool pair_advance_exact(int C, int nb, int& c1, int& 
   return true;
 }
 
+template <int KT>
 __global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * COAG_WARPS + warp;
@@ -773,7 +779,7 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevV
               const bool pflat = all_flat || (flat[p_c1 - 1] && flat[p_c2 - 1]);
               int bt = 0, bs = 0, ct = 0, cs = 0;
               accel_target_source(cx, pflat, hm, p_b1, pb2, p_c1, p_c2, p_cc, bt, bs, ct, cs);
-              cell_accel_pair(cx, ktype, be, p_kmax, del_t, step, apid, bt, bs, ct, cs, p_cc, tot_n_samp, tot_n_coag);
+              cell_accel_pair<KT>(cx, ktype, be, p_kmax, del_t, step, apid, bt, bs, ct, cs, p_cc, tot_n_samp, tot_n_coag);
               rescan = true;  // counts changed: pairs behind this one must be rescanned
               cu_c1 = p_c1; cu_c2 = p_c2; cu_b1 = p_b1; cu_b2 = pb2;
               more = pair_advance_exact(v.C, nb, cu_c1, cu_c2, cu_b1, cu_b2);
@@ -809,7 +815,7 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevV
                 double v1, ms1, v2, ms2;
                 part_vol_mass(cx, p1, v1, ms1);
                 part_vol_mass(cx, p2, v2, ms2);
-                const double uk = unweighted_kernel(ktype, be, v1, ms1, v2, ms2);
+                const double uk = unweighted_kernel<KT>(ktype, be, v1, ms1, v2, ms2);
                 const double k = uk * coag_num_conc_factor(cx, vol2rad(v1), vol2rad(v2), p_c1, p_c2, p_cc);
                 accept = rng_uniform(key, 2) < k * accept_factor;  // maybe_coag_pair :753
               }
@@ -862,7 +868,10 @@ int pmc_mc_coag_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step) {
   const int blocks = (v.n_cells + COAG_WARPS - 1) / COAG_WARPS;
   {
     ProfScope ps_(ctx, "k_mc_coag");
-    k_mc_coag<<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+    if (ktype == PMCGPU_KERNEL_BROWN)
+      k_mc_coag<PMCGPU_KERNEL_BROWN><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+    else
+      k_mc_coag<0><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
     LAUNCH_CHECK(ctx);
   }
   return PMCGPU_OK;
