@@ -58,6 +58,9 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-transport", action="store_true")
+    ap.add_argument("--courant-scale", type=float, default=1.0,
+                    help="scales the Courant numbers 0.3 / 0.2 / 0.05 and the diffusivity of the transport call "
+                         "(1/6 = em_les' own 1 s step instead of the 6 s of the benchmark step)")
     ap.add_argument("--no-parity", action="store_true", help="skip the multi-rank parity check (N > 1)")
     ap.add_argument("--k5", default="auto", choices=["auto", "on", "off"],
                     help="K5 (150x150x40 cells x 500 particles) as an extra key; auto = at N = 8")
@@ -108,7 +111,7 @@ def time_oracle(a, nx_s, ny_s, steps, warmup, n_threads, transport, method):
         while nx_s % px:
             px -= 1
         o.trans_setup(nx_s, a.nz, ny_s, px=px, py=1)
-        f = synthetic.transport_fields(case, o.num_conc_by_class(), dt=TRANS_DT)
+        f = synthetic.transport_fields(case, o.num_conc_by_class(), dt=TRANS_DT, **courant_kw(a.courant_scale))
     t_total, pts = 0.0, 0
     for k in range(warmup + steps):
         T, P, rrho = met[k]
@@ -230,7 +233,11 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------
 # the B200 arm
 # ----------------------------------------------------------------------------------------------
-def algorithmic_bytes(kernel, n_part, n_cells, S, C, nbcap):
+def courant_kw(scale):
+    return dict(courant_x=0.3 * scale, courant_y=0.2 * scale, courant_z=0.05 * scale, xkhh=10.0 * scale)
+
+
+def algorithmic_bytes(kernel, n_part, n_cells, S, C, nbcap, n_moved=0):
     """ALGORITHMIC bytes one launch of `kernel` has to move ("Kernels")."""
     P = 8 * S + 44  # record: vol[S] f64, id i64, (group, class) i32, n_primary i32, hyst i32, 2 create times f64, bin i32
     if kernel == "k_sort_cells":
@@ -245,8 +252,10 @@ def algorithmic_bytes(kernel, n_part, n_cells, S, C, nbcap):
         return n_part * 4 + n_cells * C * 4
     if kernel == "k_kernel_bounds":
         return n_cells * 8 * nbcap * nbcap / 8     # tables only for cells with a new grid (rare)
-    if kernel == "k_tr_gather":
-        return n_part * 2 * (P - 4)                # every resident record read once and written once
+    if kernel in ("k_tr_gather", "k_tr_stage"):
+        # survivors stay in place: the sampled records are staged once (k_tr_stage) and appended once behind the
+        # survivors (k_tr_gather; the holes the removals left are filled from the tail: up to as many moves again)
+        return n_moved * 2 * (P - 4)
     return 0
 
 
@@ -254,7 +263,7 @@ class Patch:
     """One rank's tile of a doubly periodic domain on its GPU, with the WRF-side fields of the transport driver."""
 
     def __init__(self, W, synthetic, decomp, torch, dist, rank, world, local, gnx, gny, nz, n_per_cell, S, scaling,
-                 has_transport, seed0=1, cap_factor=2.5, condense_method=4, comm=True):
+                 has_transport, seed0=1, cap_factor=2.5, condense_method=4, comm=True, courant_scale=1.0):
         self.W, self.torch, self.dist, self.decomp = W, torch, dist, decomp
         self.rank, self.world, self.local = rank, world, local
         self.dev = torch.device("cuda", local)
@@ -295,7 +304,7 @@ class Patch:
                                            device=self.dev)
             rrho_glob = decomp.gather_global(case["rrho"], gnx, nz, gny, px, py, device=self.dev)
             gcase = dict(nx=gnx, nz=nz, ny=gny, n_class=self.C, rrho=rrho_glob)
-            f_glob = synthetic.transport_fields(gcase, nc_glob, dt=TRANS_DT)
+            f_glob = synthetic.transport_fields(gcase, nc_glob, dt=TRANS_DT, **courant_kw(courant_scale))
             self.f_patch = synthetic.patch_fields(f_glob, i0, nxl, j0, nyl)
             if world > 1 and comm:
                 uid = decomp.broadcast_unique_id(W.comm_unique_id, rank, device=self.dev)
@@ -355,7 +364,7 @@ class Patch:
         g.check_status()
         out = dict(ms=ms, clocks=clk, launches=g.launch_count() - launches0, prof=g.profile_read(reset=True),
                    work=g.work(reset=True), counts_end=g.counts(), cond_stats=g.condense_stats(),
-                   coag_stats=g.coag_stats())
+                   coag_stats=g.coag_stats(), n_moved=int(g.trans_moved().sum()) if self.has_transport else 0)
         g.profile_enable(False)
         # ---- end to end through the C ABI with host buffers (wall clock)
         self.barrier()
@@ -501,7 +510,7 @@ def run_b200(a):
 
     scaling = a.scaling
     pt = Patch(W, synthetic, decomp, torch, dist, rank, world, local, a.nx, a.ny, a.nz, a.n_per_cell, S, scaling,
-               has_transport, condense_method=a.condense_method)
+               has_transport, condense_method=a.condense_method, courant_scale=a.courant_scale)
     g = pt.g
     n_cells, n_class = pt.n_cells, pt.C
     m = pt.measure(synthetic, a.steps, a.warmup)
@@ -555,7 +564,7 @@ def run_b200(a):
         kern = []
         for name, (kms, nl) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
             per_launch_s = kms * 1e-3 / max(nl, 1)
-            by = algorithmic_bytes(name, n_mean, n_cells, S, n_class, 64)
+            by = algorithmic_bytes(name, n_mean, n_cells, S, n_class, 64, n_moved=m.get("n_moved", 0))
             kern.append({"kernel": name, "ms_per_step": kms / a.steps, "share": kms / ms, "launches": nl,
                          "alg_bytes_per_launch": by, "hbm_gbs": by / per_launch_s / 1e9 if per_launch_s > 0 else None})
         # FP64 work of the condensation integrator, counted on the device: sum over cells and steps of

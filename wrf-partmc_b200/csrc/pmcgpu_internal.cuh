@@ -124,6 +124,7 @@ struct TransView {
   int* out_slot;                    // [n_cells][cap] original slot of every transported particle
   long long* out_newid;             // [n_cells][cap] new id when a copy stays behind, else 0
   int* n_surv;                      // [n_cells]
+  int* n_out;                       // [n_cells] entries of the cell's out list (all classes and directions)
   int* n_moved;                     // [n_cells] arrivals of the last call
   double* sbuf[4];                  // edge exchange buffers
   double* rbuf[4];

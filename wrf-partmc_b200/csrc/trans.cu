@@ -14,11 +14,13 @@
 //   C4 ghost particles (MPI_Pack)                               k_tr_pack_* -> SoA slabs -> exchange (NCCL send/recv
 //                                                               between ranks, device copy when the neighbour is
 //                                                               this rank itself)
-//   add + rebalance + sort                                      k_tr_gather: every destination cell pulls its
-//                                                               survivors and arrivals, in the reference's arrival
-//                                                               order, into the alternate slab (move-and-compact,
-//                                                               no atomics), then k_rebalance and the bin-grid
-//                                                               decision of aero_state_sort
+//   add + rebalance + sort                                      k_tr_stage: the sampled records of every cell to the
+//                                                               alternate slab; k_tr_gather: survivors stay in
+//                                                               place (holes filled from the tail), every
+//                                                               destination cell appends its arrivals in the
+//                                                               reference's arrival order (no atomics); then
+//                                                               k_rebalance and the bin-grid decision of
+//                                                               aero_state_sort
 // Sides: 0 = y-, 1 = y+, 2 = x-, 3 = x+ (the order of get_array_index_for_send_recv_from_ghost, :1826-1933).
 // Direction slots of a cell: 0 -x, 1 +x, 2 -y, 3 +y, 4 + k for the vertical level k (0-based).
 #include "pmcgpu_internal.cuh"
@@ -438,7 +440,10 @@ __global__ void k_tr_multisample(DevView v, TransView t, unsigned step, int warp
   if (v.status[cell] != 0) {  // a failed cell neither sends nor loses particles
     int* surv0 = v.L + (size_t)cell * 3 * v.cap;
     for (int p = lane; p < n0; p += 32) surv0[p] = p;
-    if (lane == 0) t.n_surv[cell] = n0;
+    if (lane == 0) {
+      t.n_surv[cell] = n0;
+      t.n_out[cell] = 0;
+    }
     return;
   }
   // ---- class lists: positions of class c in ascending order (a fresh aero_state_sort, aero_sorted.F90:185-209)
@@ -612,6 +617,7 @@ __global__ void k_tr_multisample(DevView v, TransView t, unsigned step, int warp
   for (int p = lane; p < x.n_cur; p += 32) surv[p] = x.P2O[p];
   if (lane == 0) {
     t.n_surv[cell] = x.n_cur;
+    t.n_out[cell] = n_out;
     if (err && v.status[cell] == 0) v.status[cell] = err;
   }
 }
@@ -682,16 +688,15 @@ __global__ void k_tr_pack_copy(DevView v, TransView t, int side, const int* __re
     const int lo = t.out_dir[(((size_t)cell * v.C + c) * nd + slot) * 2 + 0];
     const int m = t.out_dir[(((size_t)cell * v.C + c) * nd + slot) * 2 + 1];
     for (int e = threadIdx.x; e < m; e += blockDim.x) {
-      const size_t src = base + t.out_slot[base + lo + e];
-      const long long nid = t.out_newid[base + lo + e];
+      const size_t src = base + lo + e;  // staged out list (k_tr_stage): contiguous entries, new ids applied
       const size_t dst = (size_t)o + e;
-      for (int s = 0; s < v.S; s++) slab.vol[(size_t)s * slab.cap + dst] = v.vol[(size_t)s * NS + src];
-      slab.id[dst] = nid ? nid : v.id[src];
-      slab.wgc[dst] = v.wgc[src];
-      slab.nprim[dst] = v.nprim[src];
-      slab.hyst[dst] = v.hyst[src];
-      slab.lct[dst] = v.lct[src];
-      slab.gct[dst] = v.gct[src];
+      for (int s = 0; s < v.S; s++) slab.vol[(size_t)s * slab.cap + dst] = v.vol_alt[(size_t)s * NS + src];
+      slab.id[dst] = v.id_alt[src];
+      slab.wgc[dst] = v.wgc_alt[src];
+      slab.nprim[dst] = v.nprim_alt[src];
+      slab.hyst[dst] = v.hyst_alt[src];
+      slab.lct[dst] = v.lct_alt[src];
+      slab.gct[dst] = v.gct_alt[src];
     }
     o += m;
   }
@@ -714,6 +719,28 @@ __device__ __forceinline__ void tr_copy_rows(double* __restrict__ dst, size_t ds
 #pragma unroll
     for (int u = 0; u < 8; u++)
       if (s + u < S) dst[(size_t)(s + u) * dstride] = a[u];
+  }
+}
+// ---- the out list of every cell (sampled particles of all classes and directions, in list order) copied to the
+// ALTERNATE slab at [cell][entry], ids of copies applied: the destination cells read their arrivals from there, so the
+// main slab of a cell is touched by its own CTA only and survivors need not move (k_tr_gather)
+__global__ void __launch_bounds__(128) k_tr_stage(DevView v, TransView t) {
+  const int cell = blockIdx.x;
+  const int n_out = t.n_out[cell];
+  const size_t base = (size_t)cell * v.cap, NS = (size_t)v.n_cells * v.cap;
+  for (int e = threadIdx.x; e < n_out; e += blockDim.x) {
+    const size_t src = base + t.out_slot[base + e], dst = base + e;
+    const long long nid = t.out_newid[base + e];
+    const long long r_id = nid ? nid : v.id[src];
+    const int r_wgc = v.wgc[src], r_nprim = v.nprim[src], r_hyst = v.hyst[src];
+    const double r_lct = v.lct[src], r_gct = v.gct[src];
+    tr_copy_rows(v.vol_alt + dst, NS, v.vol + src, NS, v.S);
+    v.id_alt[dst] = r_id;
+    v.wgc_alt[dst] = r_wgc;
+    v.nprim_alt[dst] = r_nprim;
+    v.hyst_alt[dst] = r_hyst;
+    v.lct_alt[dst] = r_lct;
+    v.gct_alt[dst] = r_gct;
   }
 }
 struct TrSeg {
@@ -822,45 +849,58 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
   const size_t NS = (size_t)v.n_cells * v.cap;
   const size_t dbase = (size_t)cell * v.cap;
   const int total = s_total, nseg = s_nseg;
-  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-    int sgi = 0, rel = idx;
+  // ---- survivors stay where they are.  The swap-with-last removals only ever move records out of the tail
+  // [n_surv, n_old) into holes below n_surv (a record at slot s < n_surv is never the last one while a removal is
+  // still to come), so the holes are filled in place: reads from the tail, writes below it, no overlap.
+  const bool have_surv = nseg > 0 && seg[0].kind == 0;  // always the first segment when there are survivors
+  const int n_surv = have_surv ? seg[0].n : 0;
+  {
+    const int* __restrict__ surv = v.L + (size_t)cell * 3 * v.cap;
+    for (int idx = threadIdx.x; idx < n_surv; idx += blockDim.x) {
+      const int from = surv[idx];
+      if (from == idx) continue;
+      const size_t src = dbase + from, dst = dbase + idx;
+      const long long r_id = v.id[src];
+      const int r_wgc = v.wgc[src], r_nprim = v.nprim[src], r_hyst = v.hyst[src];
+      const double r_lct = v.lct[src], r_gct = v.gct[src];
+      tr_copy_rows(v.vol + dst, NS, v.vol + src, NS, v.S);
+      v.id[dst] = r_id;
+      v.wgc[dst] = r_wgc;
+      v.nprim[dst] = r_nprim;
+      v.hyst[dst] = r_hyst;
+      v.lct[dst] = r_lct;
+      v.gct[dst] = r_gct;
+    }
+  }
+  __syncthreads();  // the tail has been read: arrivals may overwrite it
+  // ---- arrivals behind the survivors, from the staged out lists of the source cells (alternate slab, written by
+  // k_tr_stage: this cell's own main-slab records are read by nobody else) and from the halo messages
+  for (int idx = n_surv + threadIdx.x; idx < total; idx += blockDim.x) {
+    int sgi = have_surv ? 1 : 0, rel = idx - n_surv;
     while (sgi < nseg - 1 && rel >= seg[sgi].n) { rel -= seg[sgi].n; sgi++; }
     const TrSeg sg = seg[sgi];
     const size_t dst = dbase + idx;
+    long long r_id;
+    int r_wgc, r_nprim, r_hyst;
+    double r_lct, r_gct;
     if (sg.kind == 2) {
       const TrSlab& sl = (sg.src == 0) ? r0 : (sg.src == 1 ? r1 : (sg.src == 2 ? r2 : r3));
       const size_t src = (size_t)sg.off + rel;
-      const long long r_id = sl.id[src];
-      const int r_wgc = sl.wgc[src], r_nprim = sl.nprim[src], r_hyst = sl.hyst[src];
-      const double r_lct = sl.lct[src], r_gct = sl.gct[src];
-      tr_copy_rows(v.vol_alt + dst, NS, sl.vol + src, (size_t)sl.cap, v.S);
-      v.id_alt[dst] = r_id;
-      v.wgc_alt[dst] = r_wgc;
-      v.nprim_alt[dst] = r_nprim;
-      v.hyst_alt[dst] = r_hyst;
-      v.lct_alt[dst] = r_lct;
-      v.gct_alt[dst] = r_gct;
+      r_id = sl.id[src]; r_wgc = sl.wgc[src]; r_nprim = sl.nprim[src]; r_hyst = sl.hyst[src];
+      r_lct = sl.lct[src]; r_gct = sl.gct[src];
+      tr_copy_rows(v.vol + dst, NS, sl.vol + src, (size_t)sl.cap, v.S);
     } else {
-      const size_t sbase = (size_t)sg.src * v.cap;
-      size_t src;
-      long long nid = 0;
-      if (sg.kind == 0) {
-        src = sbase + (v.L + (size_t)sg.src * 3 * v.cap)[rel];
-      } else {
-        src = sbase + t.out_slot[sbase + sg.off + rel];
-        nid = t.out_newid[sbase + sg.off + rel];
-      }
-      const long long r_id = nid ? nid : v.id[src];
-      const int r_wgc = v.wgc[src], r_nprim = v.nprim[src], r_hyst = v.hyst[src];
-      const double r_lct = v.lct[src], r_gct = v.gct[src];
-      tr_copy_rows(v.vol_alt + dst, NS, v.vol + src, NS, v.S);
-      v.id_alt[dst] = r_id;
-      v.wgc_alt[dst] = r_wgc;
-      v.nprim_alt[dst] = r_nprim;
-      v.hyst_alt[dst] = r_hyst;
-      v.lct_alt[dst] = r_lct;
-      v.gct_alt[dst] = r_gct;
+      const size_t src = (size_t)sg.src * v.cap + sg.off + rel;  // entry of the source cell's staged out list
+      r_id = v.id_alt[src]; r_wgc = v.wgc_alt[src]; r_nprim = v.nprim_alt[src]; r_hyst = v.hyst_alt[src];
+      r_lct = v.lct_alt[src]; r_gct = v.gct_alt[src];
+      tr_copy_rows(v.vol + dst, NS, v.vol_alt + src, NS, v.S);
     }
+    v.id[dst] = r_id;
+    v.wgc[dst] = r_wgc;
+    v.nprim[dst] = r_nprim;
+    v.hyst[dst] = r_hyst;
+    v.lct[dst] = r_lct;
+    v.gct[dst] = r_gct;
   }
   if (threadIdx.x == 0) {
     v.count[cell] = total;
@@ -912,7 +952,7 @@ static int tr_setup(pmcgpu_ctx* ctx) {
   TA(t.ccount, nc * C) TA(t.num_old, nc * C) TA(t.scale_ratio, nc * C)
   TA(t.padv, nc * C * 6) TA(t.pdiff, nc * C * 4) TA(t.pvert, nc * C * nz)
   TA(t.cellvol_ext, n_ext) TA(t.wmag_ext, n_ext * C)
-  TA(t.out_dir, nc * C * nd * 2) TA(t.n_surv, nc) TA(t.n_moved, nc)
+  TA(t.out_dir, nc * C * nd * 2) TA(t.n_surv, nc) TA(t.n_out, nc) TA(t.n_moved, nc)
   for (int s = 0; s < 4; s++) {
     const size_t L = (s < 2) ? nx : ny;
     TA(t.sbuf[s], L * nz * C) TA(t.rbuf[s], L * nz * C)
@@ -1042,6 +1082,12 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
       LAUNCH_CHECK(ctx);
     }
   }
+  {
+    // the sampled records of every cell, in list order, to the alternate slab
+    ProfScope ps_(ctx, "k_tr_stage");
+    k_tr_stage<<<(unsigned)nc, 128, 0, st>>>(v, t);
+    LAUNCH_CHECK(ctx);
+  }
   // ---- C4: ghost particles: one message per neighbour (header with the per-cell offsets + SoA records), its
   // row pitch derived from the counts of the previous step, so the host never waits for this step's counts
   TrSlab rview[4];
@@ -1093,7 +1139,6 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
     }
     k_tr_gather<<<(unsigned)nc, 128, (size_t)tr_n_cand(t.nz, v.C) * sizeof(TrSeg), st>>>(v, t, rview[0], rview[1], rview[2], rview[3]);
     LAUNCH_CHECK(ctx);
-    pmc_swap_slabs(ctx);
   }
   if ((rc = pmc_rebalance_async(ctx, a->allow_doubling, a->allow_halving, a->step))) return rc;
   if ((rc = pmc_sort_grid_only_async(ctx, 1))) return rc;
