@@ -146,8 +146,34 @@ typedef struct {
   double create_time;
   int allow_doubling, allow_halving;
   unsigned int step;            /* addresses the random draws */
+  unsigned int stream;          /* added to the (group, mode) part of the draw address: 0 for scenario emissions; callers
+                                   that sample in the same cells in the same step use different values (sea salt: 1024) */
 } pmcgpu_emit_args;
 int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmcgpu_emit_args* args, int* n_part_add /* [n_cells] or NULL */);
+
+/* seasalt_emissions (interface/wrf_pmc_driver.F90:1767-1924) as partmc_timestep calls it (:212-223): for every cell
+ * of the lowest level (k = 1) over water (grid%xland > 1.5), wind_speed = (u10^2 + v10^2)**.5 in single precision,
+ * log-normal sea salt modes of Na / Cl (volume fractions mw_na / (mw_na + mw_cl) and the rest) sampled with
+ * p = emission_rate_scale * dt / env_state%height and characteristic_factor = max(1, min(3600, elapsed_time)) / dt
+ * through aero_state_add_aero_dist_sample.  sea_salt_opt (grid%partmc_seasalt_param): 1 = Gong (2003) matched to the
+ * two MAM3 modes (number fluxes 73.7 / 10.2 x wind_speed**3.41), 2 = Ovadnevaite et al. (2014), five modes with the
+ * Reynolds number the reference fixes at 3.1e6.  weight_class [2 or 5]: classes of the sources "sea_salt_01" ...
+ * Fields are 2-D [ny][nx], i fastest, host or device pointers.  Call after pmcgpu_partmc_timestep's emissions slot;
+ * the draws use stream 1024 of the emission phase. */
+typedef struct {
+  const float* u10;        /* grid%u10 */
+  const float* v10;        /* grid%v10 */
+  const float* xland;      /* grid%xland: 1 land, 2 water */
+  const double* height;    /* env_states(i,1,j)%height */
+  int sea_salt_opt;
+  int i_na, i_cl;          /* species numbers of "Na" and "Cl", 1-based */
+  const int* weight_class; /* [n_modes] 1-based */
+  double dt;               /* grid%dt */
+  double elapsed_time;     /* env_state%elapsed_time: creation time of the new particles */
+  int allow_doubling, allow_halving;
+  unsigned int step;       /* addresses the random draws */
+} pmcgpu_seasalt_args;
+int pmcgpu_seasalt_emissions(pmcgpu_ctx* ctx, const pmcgpu_seasalt_args* args, int* n_part_add /* [n_cells] or NULL */);
 
 /* Step number that addresses the random draws of the stand-alone condensation calls below (the
  * prob_round draws of aero_state_reweight, aero_state.F90:597-653, when weights depend on size);

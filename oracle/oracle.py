@@ -313,9 +313,33 @@ class Oracle:
             C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step), C.byref(n)))
         return n.value
 
+    def seasalt_emissions(self, nx, nz, ny, u10, v10, xland, height, sea_salt_opt, i_na, i_cl, weight_class, dt,
+                          elapsed_time, allow_doubling=True, allow_halving=True, step=0):
+        """the sea salt block of partmc_timestep (interface/wrf_pmc_driver.F90:212-223, :1767-1924)"""
+        u, v, xl = [np.ascontiguousarray(x, np.float32) for x in (u10, v10, xland)]
+        hg, wc = _f64(height), _i32(weight_class)
+        n_add = np.zeros(nx * nz * ny, np.int32)
+        self._chk(self.L.pmco_seasalt_emissions(
+            self.h, C.c_int(nx), C.c_int(nz), C.c_int(ny), _p(u, C.c_float), _p(v, C.c_float), _p(xl, C.c_float),
+            _p(hg, C.c_double), C.c_int(sea_salt_opt), C.c_int(i_na), C.c_int(i_cl), _p(wc, C.c_int), C.c_double(dt),
+            C.c_double(elapsed_time), C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step),
+            _p(n_add, C.c_int)))
+        return n_add
+
     def scale_weight(self, cell, g, c, ratio, allow_doubling=True, allow_halving=True, step=0):
         self._chk(self.L.pmco_scale_weight(self.h, C.c_int(cell), C.c_int(g), C.c_int(c), C.c_double(ratio),
                                            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step)))
+
+
+def seasalt_modes(sea_salt_opt, n_spec, i_na, i_cl):
+    """mode table of seasalt_emissions: char_radius, log10 sigma, number flux, vol_frac [n_modes][n_spec]"""
+    L = lib()
+    cr, ls, fl, vf = np.zeros(5), np.zeros(5), np.zeros(5), np.zeros(5 * n_spec)
+    n = L.pmco_seasalt_modes(C.c_int(sea_salt_opt), C.c_int(n_spec), C.c_int(i_na), C.c_int(i_cl), _p(cr, C.c_double),
+                             _p(ls, C.c_double), _p(fl, C.c_double), _p(vf, C.c_double))
+    if n < 0:
+        raise ValueError("invalid sea salt option")
+    return cr[:n], ls[:n], fl[:n], vf[:n * n_spec].reshape(n, n_spec)
 
 
 def dep_eval(inputs):

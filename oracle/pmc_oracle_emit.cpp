@@ -8,7 +8,8 @@
 // TEST INFRASTRUCTURE ONLY (see pmc_oracle.hpp).
 //
 // Draw addresses (PH_EMIT): a = (group - 1) n_mode + (mode - 1), b = 0: the Poisson count; b = i_samp >= 1:
-// the sequential stream of new particle i_samp (radius attempts, then volume-fraction attempts).
+// the sequential stream of new particle i_samp (radius attempts, then volume-fraction attempts).  `stream` is added
+// to a: callers that sample in the same cell and step (scenario emissions, then sea salt) use different streams.
 // Deviation that changes particle ORDER only: every aero_state_scale_weight inside starts from a fresh
 // aero_state_sort (the device keeps no lists between phases).
 #include "pmc_oracle_domain.hpp"
@@ -103,7 +104,7 @@ static void aero_state_prepare_weight_for_add(AeroState& st, int g, int c, doubl
 // aero_state.F90:758-831
 int aero_state_add_aero_dist_sample(AeroState& st, const AeroData& d, const std::vector<AeroMode>& modes,
                                     double sample_prop, double characteristic_factor, double create_time,
-                                    bool allow_doubling, bool allow_halving, const RunCtx& rc) {
+                                    bool allow_doubling, bool allow_halving, const RunCtx& rc, uint32_t stream) {
   const int n_group = st.awa.n_group;
   const int n_mode = (int)modes.size();
   int n_part_add = 0;
@@ -112,7 +113,7 @@ int aero_state_add_aero_dist_sample(AeroState& st, const AeroData& d, const std:
     for (int im = 1; im <= n_mode; im++) {
       const AeroMode& m = modes[im - 1];
       const int c = m.weight_class;
-      const uint32_t a = (uint32_t)((g - 1) * n_mode + (im - 1));
+      const uint32_t a = stream + (uint32_t)((g - 1) * n_mode + (im - 1));
       double n_samp_avg = sample_prop * aero_mode_number(m, st.awa.at(g, c));
       aero_state_prepare_weight_for_add(st, g, c, n_samp_avg, allow_doubling, allow_halving, rc, 1u + a);
       if (n_samp_avg == 0.0) continue;
@@ -139,6 +140,60 @@ int aero_state_add_aero_dist_sample(AeroState& st, const AeroData& d, const std:
       }
     }
   return n_part_add;
+}
+
+// ---- sea salt (interface/wrf_pmc_driver.F90:1767-1924).  The Fortran declares its tables as real(kind=dp) arrays
+// initialised with DEFAULT-REAL literals, so every tabulated number is the single-precision value widened to double;
+// `wind_speed**3.41` has a single-precision exponent as well.  match_mam3_modes is a compile-time .true. (:1816), so
+// the 25-bin sampled Gong spectrum (seasalt_emissions_1bin) is dead code in the reference and not restated.
+static const int SEASALT_STREAM = 1024;  // keeps the draws apart from scenario emissions in the same cell and step
+int seasalt_n_modes(int sea_salt_opt) { return sea_salt_opt == 1 ? 2 : (sea_salt_opt == 2 ? 5 : 0); }
+void seasalt_modes(int sea_salt_opt, int n_spec, int i_na, int i_cl, const int* weight_class,
+                   std::vector<AeroMode>& modes) {
+  const double mw_na = 22.990, mw_cl = 35.450;
+  const int n_modes = seasalt_n_modes(sea_salt_opt);
+  if (n_modes == 0) die_msg(1767, "invalid sea salt option");
+  modes.assign((size_t)n_modes, AeroMode());
+  for (int m = 0; m < n_modes; m++) {
+    AeroMode& md = modes[m];
+    md.type = MODE_LOG_NORMAL;
+    md.vol_frac.assign((size_t)n_spec, 0.0);
+    md.vol_frac_std.assign((size_t)n_spec, 0.0);
+    md.vol_frac[i_na - 1] = mw_na / (mw_na + mw_cl);
+    md.vol_frac[i_cl - 1] = 1.0 - (mw_na / (mw_na + mw_cl));
+    md.weight_class = weight_class[m];
+    if (sea_salt_opt == 1) {  // Gong (2003) flux matched to the two MAM3 modes (:1826-1848)
+      static const float flux[2] = {73.7095947f, 10.1706810f};
+      static const float diam[2] = {2.03347408e-07f, 1.09840811e-06f};
+      static const float sd[2] = {2.0f, 2.2f};
+      md.char_radius = (double)diam[m] / 2;
+      md.log10_std_dev_radius = std::log10((double)sd[m]);
+      md.num_conc = (double)flux[m];
+    } else {  // Ovadnevaite et al. (2014), five modes (:1880-1909); Re is fixed to 3.1e6 by the reference
+      static const float sigma[5] = {1.37f, 1.5f, 1.42f, 1.53f, 1.85f};
+      static const float CMD[5] = {.018f, .041f, .09f, .23f, .83f};
+      static const float coef[5] = {104.5f, .0442f, 149.6f, 2.96f, .51f};
+      static const double offset[5] = {1e5, 1e5, 1e5, 1e5, 2e5};
+      static const float expon[5] = {.556f, 1.08f, .545f, .79f, .87f};
+      md.char_radius = .5 * (double)CMD[m] * 1e-6;
+      md.log10_std_dev_radius = std::log10((double)sigma[m]);
+      const double Re = 3.1e6;
+      md.num_conc = (double)coef[m] * std::pow(Re - offset[m], (double)expon[m]);
+    }
+  }
+}
+int seasalt_emissions(AeroState& st, const AeroData& d, double wind_speed, double height, double elapsed_time,
+                      double delta_t, bool allow_doubling, bool allow_halving, int sea_salt_opt, int i_na, int i_cl,
+                      const int* weight_class, const RunCtx& rc) {
+  std::vector<AeroMode> modes;
+  seasalt_modes(sea_salt_opt, d.n_spec, i_na, i_cl, weight_class, modes);
+  const double emission_rate_scale = (sea_salt_opt == 1) ? std::pow(wind_speed, (double)3.41f) : 1.0;
+  const double p = emission_rate_scale * delta_t / height;
+  const double sample_timescale = 3600.0;
+  const double effective = std::max(1.0, std::min(sample_timescale, elapsed_time));
+  const double characteristic_factor = effective / delta_t;
+  return aero_state_add_aero_dist_sample(st, d, modes, p, characteristic_factor, elapsed_time, allow_doubling,
+                                         allow_halving, rc, SEASALT_STREAM);
 }
 
 }  // namespace pmco
@@ -172,5 +227,49 @@ int pmco_add_aero_dist_sample(void* h, int cell, int n_mode, const int* type, co
                                                 create_time, allow_doubling != 0, allow_halving != 0, rc);
   if (n_part_add) *n_part_add = n;
   ORACLE_CATCH(D)
+}
+
+// partmc_timestep's sea salt block (wrf_pmc_driver.F90:212-223) for the cells of this oracle: lowest level (k == 1),
+// xland > 1.5 (water); wind = (u10^2 + v10^2)**.5 in single precision.  u10, v10, xland [ny][nx] float,
+// height [ny][nx] double; cell index = i + nx (k + nz j).  n_add [n_cells] (may be NULL).
+int pmco_seasalt_emissions(void* h, int nx, int nz, int ny, const float* u10, const float* v10, const float* xland,
+                           const double* height, int sea_salt_opt, int i_na, int i_cl, const int* weight_class,
+                           double dt, double elapsed_time, int allow_doubling, int allow_halving, unsigned step,
+                           int* n_add) {
+  OracleDomain* D = (OracleDomain*)h;
+  ORACLE_TRY
+  if (n_add)
+    for (int c = 0; c < nx * nz * ny; c++) n_add[c] = 0;
+  for (int j = 0; j < ny; j++)
+    for (int i = 0; i < nx; i++) {
+      if (!(xland[j * nx + i] > 1.5f)) continue;
+      const float u = u10[j * nx + i], v = v10[j * nx + i];
+      const float w2 = u * u + v * v;
+      const double wind_speed = (double)std::sqrt(w2);  // **.5 of a default real
+      const int cell = i + nx * (0 + nz * j);
+      RunCtx rc{D->rng.get(), (uint32_t)D->global_cell[cell], step};
+      const int n = seasalt_emissions(D->cells[cell], D->data, wind_speed, height[j * nx + i], elapsed_time, dt,
+                                      allow_doubling != 0, allow_halving != 0, sea_salt_opt, i_na, i_cl, weight_class, rc);
+      if (n_add) n_add[cell] = n;
+    }
+  ORACLE_CATCH(D)
+}
+// the mode table itself (char_radius, log10 sigma, flux, vol_frac [n_modes][n_spec]) for known-answer tests
+int pmco_seasalt_modes(int sea_salt_opt, int n_spec, int i_na, int i_cl, double* char_radius, double* log10_std,
+                       double* flux, double* vol_frac) {
+  std::vector<AeroMode> modes;
+  std::vector<int> wc((size_t)5, 1);
+  try {
+    seasalt_modes(sea_salt_opt, n_spec, i_na, i_cl, wc.data(), modes);
+  } catch (...) {
+    return -1;
+  }
+  for (size_t m = 0; m < modes.size(); m++) {
+    char_radius[m] = modes[m].char_radius;
+    log10_std[m] = modes[m].log10_std_dev_radius;
+    flux[m] = modes[m].num_conc;
+    for (int k = 0; k < n_spec; k++) vol_frac[m * n_spec + k] = modes[m].vol_frac[k];
+  }
+  return (int)modes.size();
 }
 }

@@ -60,7 +60,15 @@ double aero_mode_sample_radius(const AeroMode& m, const Weight& w, double prob_t
 void aero_mode_sample_vols(const AeroMode& m, double total_vol, std::vector<double>& vols, Stream& s);  // :633
 int aero_state_add_aero_dist_sample(AeroState& st, const AeroData& d, const std::vector<AeroMode>& modes,
                                     double sample_prop, double characteristic_factor, double create_time,
-                                    bool allow_doubling, bool allow_halving, const RunCtx& rc);         // aero_state.F90:758
+                                    bool allow_doubling, bool allow_halving, const RunCtx& rc,
+                                    uint32_t stream = 0u);                                              // aero_state.F90:758
+// seasalt_emissions (interface/wrf_pmc_driver.F90:1767-1924) for one surface ocean cell
+int seasalt_emissions(AeroState& st, const AeroData& d, double wind_speed, double height, double elapsed_time,
+                      double delta_t, bool allow_doubling, bool allow_halving, int sea_salt_opt, int i_na, int i_cl,
+                      const int* weight_class, const RunCtx& rc);
+int seasalt_n_modes(int sea_salt_opt);
+void seasalt_modes(int sea_salt_opt, int n_spec, int i_na, int i_cl, const int* weight_class,
+                   std::vector<AeroMode>& modes);
 
 // ---------------------------------------------------------------- transport (pmc_oracle_trans.cpp)
 // Global doubly periodic domain of gnx x nz x gny cells, emulated px x py patch decomposition.

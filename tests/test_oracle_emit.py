@@ -1,6 +1,7 @@
 """CPU tests of the emission-sampling restatement (aero_state_add_aero_dist_sample, aero_state.F90:758-831):
 the sampled population reproduces the mode it was drawn from."""
 import numpy as np
+import pytest
 
 import common
 from oracle import oracle as O
@@ -46,3 +47,42 @@ def test_prepare_weight_for_add_rescales_when_the_cell_would_overflow():
     r = (3 * q["vol"][0] / (4 * np.pi)) ** (1 / 3)
     n_mono = int((np.abs(r / 1e-7 - 1) < 1e-12).sum())
     assert abs(n_mono - 200) < 4 * np.sqrt(200)
+
+
+def test_seasalt_mode_tables():
+    """single-precision literals of the Fortran tables widened to double (real(kind=dp) :: x = [ .018, ... ])"""
+    from oracle import oracle as O
+    cr, ls, fl, vf = O.seasalt_modes(1, 20, 5, 4)
+    assert cr[0] == float(np.float32(2.03347408e-07)) / 2 and ls[1] == np.log10(float(np.float32(2.2)))
+    assert fl[0] == float(np.float32(73.7095947))
+    cr, ls, fl, vf = O.seasalt_modes(2, 3, 1, 2)
+    assert cr[4] == 0.5 * float(np.float32(.83)) * 1e-6
+    assert fl[1] == pytest.approx(float(np.float32(.0442)) * (3.1e6 - 1e5) ** float(np.float32(1.08)), rel=1e-14)
+    np.testing.assert_allclose(vf.sum(axis=1), 1.0, rtol=1e-15)
+
+
+def test_seasalt_emissions_expected_number():
+    """seasalt_emissions (wrf_pmc_driver.F90:1767): over water at k = 1 the expected number of new computational
+    particles is sum_modes flux wind**3.41 dt / height / magnitude; nothing over land or aloft"""
+    nx, nz, ny = 4, 2, 3
+    case = common.make_cells(nx * nz * ny, 200, n_spec=20, n_class=2, seed=5, nx=nx, nz=nz, ny=ny, ragged=False,
+                             num_conc=2e5, n_part_ideal=1000.0)
+    o = common.oracle_from_case(O, case)
+    u10 = np.full((ny, nx), 8.0, np.float32)
+    v10 = np.full((ny, nx), 6.0, np.float32)  # wind speed 10 m/s
+    xland = np.full((ny, nx), 2.0, np.float32)
+    xland[0, 0] = 1.0
+    height = np.full((ny, nx), 50.0)
+    n_add = np.zeros(nx * nz * ny)
+    n_rep = 40
+    for step in range(n_rep):
+        n_add += o.seasalt_emissions(nx, nz, ny, u10, v10, xland, height, 1, 5, 4, [1, 2], 60.0, 600.0, step=step,
+                                     allow_doubling=False, allow_halving=False)
+    n_add = n_add.reshape(ny, nz, nx)
+    assert n_add[:, 1, :].sum() == 0 and n_add[0, 0, 0] == 0
+    mag = case["wmag"].reshape(ny, nz, nx, 2)[:, 0, :, :]
+    scale = 10.0 ** float(np.float32(3.41)) * 60.0 / 50.0
+    expect = n_rep * scale * (float(np.float32(73.7095947)) / mag[..., 0] + float(np.float32(10.1706810)) / mag[..., 1])
+    expect[0, 0] = 0.0
+    tot, exp_tot = n_add[:, 0, :].sum(), expect.sum()
+    assert abs(tot - exp_tot) < 5.0 * np.sqrt(exp_tot), (tot, exp_tot)

@@ -10,6 +10,8 @@
 // parallel, the swap-with-last permutation is then replayed serially on
 // indices only, and the records move in parallel.
 #include "pmcgpu_internal.cuh"
+#include <cstring>
+#include <vector>
 
 #define REB_WARPS 4
 
@@ -420,6 +422,7 @@ struct EmitDev {
   double char_factor, create_time;
   int allow_doubling, allow_halving;
   unsigned step;
+  unsigned stream;             // added to the draw address a = (group, mode): keeps several callers of one step apart
   int* n_add;                  // [n_cells]
 };
 
@@ -500,7 +503,7 @@ __device__ int emit_cell(DevView& v, const EmitDev& e, int cell, int lane, doubl
       const int type = e.type[im - 1], c = e.wclass[im - 1];
       const double cr = e.char_radius[im - 1], lsd = e.log10_std[im - 1];
       const double mode_nc = mode_nc_row[im - 1];
-      const unsigned a = (unsigned)((g - 1) * e.n_mode + (im - 1));
+      const unsigned a = e.stream + (unsigned)((g - 1) * e.n_mode + (im - 1));
       const int gc = (c - 1) * v.G + (g - 1);
       const double ideal = v.ideal_gc[gc];
       const size_t wi = (size_t)cell * v.C * v.G + gc;
@@ -576,8 +579,12 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
   }
 }
 
+static int emit_run(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add);
 extern "C" int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add) {
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
+  return emit_run(ctx, a, n_part_add);
+}
+static int emit_run(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add) {
   if (!ctx || !a || a->n_mode < 1 || !a->mode_type || !a->weight_class || !a->char_radius || !a->log10_std_dev ||
       !a->vol_frac || !a->num_conc || !a->sample_prop || !(a->characteristic_factor > 0.0))
     return PMCGPU_ERR_ARG;
@@ -616,6 +623,7 @@ extern "C" int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmc
   e.num_conc = d_nc; e.sample_prop = d_sp;
   e.char_factor = a->characteristic_factor; e.create_time = a->create_time;
   e.allow_doubling = a->allow_doubling; e.allow_halving = a->allow_halving; e.step = a->step;
+  e.stream = a->stream;
   e.n_add = d_na;
   {
     ProfScope ps_(ctx, "k_emit");
@@ -627,6 +635,107 @@ extern "C" int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmc
   const int rc = pmc_first_status(ctx);  // synchronises the stream
   cudaFree(buf);
   return rc;
+}
+
+// ---- sea salt (interface/wrf_pmc_driver.F90:212-223, :1767-1924): the per-cell sampling proportion and mode
+// fluxes on the device, then the emission kernel above.  Tabulated numbers are DEFAULT-REAL literals in the Fortran
+// (single precision widened to double), like the exponent of wind_speed**3.41.
+__global__ void k_seasalt_prop(int nx, int nz, int ny, const float* __restrict__ u10, const float* __restrict__ v10,
+                               const float* __restrict__ xland, const double* __restrict__ height, int opt, double dt,
+                               int n_mode, const double* __restrict__ flux, double* __restrict__ sample_prop,
+                               double* __restrict__ num_conc) {
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= nx * nz * ny) return;
+  const int i = cell % nx, k = (cell / nx) % nz, j = cell / (nx * nz);
+  double p = 0.0;
+  if (k == 0 && xland[j * nx + i] > 1.5f) {
+    const float u = u10[j * nx + i], w = v10[j * nx + i];
+    const float w2 = __fadd_rn(__fmul_rn(u, u), __fmul_rn(w, w));  // no contraction: the products round first
+    const double wind_speed = (double)__fsqrt_rn(w2);
+    const double scale = (opt == 1) ? pow(wind_speed, (double)3.41f) : 1.0;
+    p = scale * dt / height[j * nx + i];
+  }
+  sample_prop[cell] = p;
+  for (int m = 0; m < n_mode; m++) num_conc[(size_t)cell * n_mode + m] = flux[m];
+}
+
+extern "C" int pmcgpu_seasalt_emissions(pmcgpu_ctx* ctx, const pmcgpu_seasalt_args* a, int* n_part_add) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
+  if (!ctx || !a || !a->u10 || !a->v10 || !a->xland || !a->height || !a->weight_class || !(a->dt > 0.0)) return PMCGPU_ERR_ARG;
+  DevView& v = ctx->v;
+  const int n_mode = a->sea_salt_opt == 1 ? 2 : (a->sea_salt_opt == 2 ? 5 : 0);
+  if (n_mode == 0) {
+    ctx->err = "invalid sea salt option";  // wrf_pmc_driver.F90:1911
+    return PMCGPU_ERR_ARG;
+  }
+  if (a->i_na < 1 || a->i_na > v.S || a->i_cl < 1 || a->i_cl > v.S || a->i_na == a->i_cl) return PMCGPU_ERR_ARG;
+  const int nx = ctx->cfg.nx, nz = ctx->cfg.nz, ny = ctx->cfg.ny;
+  const size_t n2 = (size_t)nx * ny, nc = (size_t)v.n_cells;
+  // mode tables (host)
+  int type[5], wclass[5];
+  double cr[5], ls[5], flux[5];
+  std::vector<double> vf((size_t)n_mode * v.S, 0.0);
+  const double mw_na = 22.990, mw_cl = 35.450;
+  for (int m = 0; m < n_mode; m++) {
+    type[m] = 1;
+    wclass[m] = a->weight_class[m];
+    vf[(size_t)m * v.S + a->i_na - 1] = mw_na / (mw_na + mw_cl);
+    vf[(size_t)m * v.S + a->i_cl - 1] = 1.0 - (mw_na / (mw_na + mw_cl));
+    if (a->sea_salt_opt == 1) {
+      static const float f[2] = {73.7095947f, 10.1706810f};
+      static const float diam[2] = {2.03347408e-07f, 1.09840811e-06f};
+      static const float sd[2] = {2.0f, 2.2f};
+      cr[m] = (double)diam[m] / 2;
+      ls[m] = log10((double)sd[m]);
+      flux[m] = (double)f[m];
+    } else {
+      static const float sigma[5] = {1.37f, 1.5f, 1.42f, 1.53f, 1.85f};
+      static const float CMD[5] = {.018f, .041f, .09f, .23f, .83f};
+      static const float coef[5] = {104.5f, .0442f, 149.6f, 2.96f, .51f};
+      static const double offset[5] = {1e5, 1e5, 1e5, 1e5, 2e5};
+      static const float expon[5] = {.556f, 1.08f, .545f, .79f, .87f};
+      cr[m] = .5 * (double)CMD[m] * 1e-6;
+      ls[m] = log10((double)sigma[m]);
+      flux[m] = (double)coef[m] * pow(3.1e6 - offset[m], (double)expon[m]);
+    }
+  }
+  TmpDev<float> f32;
+  TmpDev<double> f64;
+  CUDA_OK(ctx, f32.alloc(3 * n2));
+  CUDA_OK(ctx, f64.alloc(n2 + 5 + nc + nc * n_mode));
+  float* d_u = f32.p;
+  float* d_v = d_u + n2;
+  float* d_x = d_v + n2;
+  double* d_h = f64.p;
+  double* d_flux = d_h + n2;
+  double* d_sp = d_flux + 5;
+  double* d_nc = d_sp + nc;
+  cudaStream_t st = ctx->stream;
+  CUDA_OK(ctx, cudaMemcpyAsync(d_u, a->u10, n2 * sizeof(float), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_v, a->v10, n2 * sizeof(float), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_x, a->xland, n2 * sizeof(float), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_h, a->height, n2 * sizeof(double), cudaMemcpyDefault, st));
+  CUDA_OK(ctx, cudaMemcpyAsync(d_flux, flux, n_mode * sizeof(double), cudaMemcpyHostToDevice, st));
+  {
+    ProfScope ps_(ctx, "k_seasalt_prop");
+    k_seasalt_prop<<<(unsigned)((nc + 255) / 256), 256, 0, st>>>(nx, nz, ny, d_u, d_v, d_x, d_h, a->sea_salt_opt, a->dt,
+                                                                 n_mode, d_flux, d_sp, d_nc);
+    LAUNCH_CHECK(ctx);
+  }
+  CUDA_OK(ctx, cudaStreamSynchronize(st));  // `flux` is a stack array
+  pmcgpu_emit_args e;
+  memset(&e, 0, sizeof(e));
+  e.n_mode = n_mode;
+  e.mode_type = type; e.weight_class = wclass; e.char_radius = cr; e.log10_std_dev = ls;
+  e.vol_frac = vf.data(); e.vol_frac_std = nullptr;
+  e.num_conc = d_nc; e.sample_prop = d_sp;
+  const double sample_timescale = 3600.0;
+  e.characteristic_factor = fmax(1.0, fmin(sample_timescale, a->elapsed_time)) / a->dt;
+  e.create_time = a->elapsed_time;
+  e.allow_doubling = a->allow_doubling; e.allow_halving = a->allow_halving;
+  e.step = a->step;
+  e.stream = 1024u;
+  return emit_run(ctx, &e, n_part_add);
 }
 
 int pmc_rebalance_async(pmcgpu_ctx* ctx, int allow_doubling, int allow_halving, unsigned step) {
@@ -902,7 +1011,7 @@ int pmc_boundary_refresh_async(pmcgpu_ctx* ctx, unsigned step) {
   b.e.type = ctx->bnd_type; b.e.wclass = ctx->bnd_wclass; b.e.char_radius = ctx->bnd_cr; b.e.log10_std = ctx->bnd_ls;
   b.e.vol_frac = ctx->bnd_vf; b.e.vol_frac_std = ctx->bnd_vs; b.e.num_conc = ctx->bnd_nc; b.e.sample_prop = nullptr;
   b.e.char_factor = 1.0; b.e.create_time = 0.0;   // sample_timescale, create_time of the call sites (:839-842)
-  b.e.allow_doubling = 1; b.e.allow_halving = 1; b.e.step = step; b.e.n_add = nullptr;
+  b.e.allow_doubling = 1; b.e.allow_halving = 1; b.e.step = step; b.e.stream = 0u; b.e.n_add = nullptr;
   b.outflow = ctx->bnd_outflow; b.throw_away = ctx->bnd_throw;
   b.nx = ctx->cfg.nx; b.nz = ctx->cfg.nz;
   const size_t smem = ((size_t)2 * v.cap + 2 * v.C) * sizeof(int);

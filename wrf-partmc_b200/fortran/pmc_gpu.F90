@@ -471,6 +471,53 @@ contains
          'pmcgpu_wrf_pmc_dep_dry_driver')
   end subroutine pmc_gpu_dep_dry
 
+  !> The sea salt block of partmc_timestep (interface/wrf_pmc_driver.F90:212-223 -> seasalt_emissions, :1767):
+  !> the surface fields cross the boundary once per step; wind speed, sampling proportion and the sampling of the
+  !> new Na / Cl particles run on the device for all water cells of the lowest level.
+  subroutine pmc_gpu_seasalt_emissions(grid, aero_data, env_states, pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke)
+    use module_domain, only: domain
+    use pmc_env_state
+    use pmc_aero_data
+    use pmc_util, only: string_array_find
+    type(domain), intent(inout) :: grid
+    type(aero_data_t), intent(in) :: aero_data
+    integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
+    type(env_state_t), intent(in) :: env_states(pmc_is:pmc_ie, pmc_ks:pmc_ke, pmc_js:pmc_je)
+
+    type(pmcgpu_seasalt_args_t) :: args
+    real(c_float), allocatable, target :: u10(:,:), v10(:,:), xland(:,:)
+    real(c_double), allocatable, target :: height(:,:)
+    integer(c_int), target :: weight_class(5)
+    character(len=AERO_SOURCE_NAME_LEN) :: mode_name
+    integer :: i_mode, n_modes
+
+    if (grid%partmc_seasalt_param <= 0) return
+    n_modes = merge(2, 5, grid%partmc_seasalt_param == 1)
+    do i_mode = 1,n_modes
+       write(mode_name,'(a,i2.2)') 'sea_salt_', i_mode
+       weight_class(i_mode) = string_array_find(aero_data%weight_class_name, mode_name)
+    end do
+    u10 = grid%u10(pmc_is:pmc_ie, pmc_js:pmc_je)
+    v10 = grid%v10(pmc_is:pmc_ie, pmc_js:pmc_je)
+    xland = grid%xland(pmc_is:pmc_ie, pmc_js:pmc_je)
+    height = env_states(pmc_is:pmc_ie, pmc_ks, pmc_js:pmc_je)%height
+    args%u10 = c_loc(u10)
+    args%v10 = c_loc(v10)
+    args%xland = c_loc(xland)
+    args%height = c_loc(height)
+    args%sea_salt_opt = grid%partmc_seasalt_param
+    args%i_na = aero_data_spec_by_name(aero_data, "Na")
+    args%i_cl = aero_data_spec_by_name(aero_data, "Cl")
+    args%weight_class = c_loc(weight_class)
+    args%dt = real(grid%dt, c_double)
+    args%elapsed_time = env_states(pmc_is, pmc_ks, pmc_js)%elapsed_time
+    args%allow_doubling = merge(1, 0, grid%allow_doubling)
+    args%allow_halving = merge(1, 0, grid%allow_halving)
+    args%step = pmc_gpu_step
+    pmc_gpu_step = pmc_gpu_step + 1
+    call pmc_gpu_check(pmcgpu_seasalt_emissions(pmc_gpu_handle, args, c_null_ptr), 'pmcgpu_seasalt_emissions')
+  end subroutine pmc_gpu_seasalt_emissions
+
   !> Open domain: the boundary conditions trans_aero derives per step (wrf_pmc_trans_aero.F90:811-955) --
   !! which boundary cells see outflow (u_2 < 0 on the west face, u_2(i+1) > 0 on the east face, v_2 likewise),
   !! which are thrown away (the wind changed sign since the last step, or the background changed), and the

@@ -101,6 +101,13 @@ class _EmitArgs(C.Structure):
                 ("char_radius", C.c_void_p), ("log10_std_dev", C.c_void_p), ("vol_frac", C.c_void_p),
                 ("vol_frac_std", C.c_void_p), ("num_conc", C.c_void_p), ("sample_prop", C.c_void_p),
                 ("characteristic_factor", C.c_double), ("create_time", C.c_double), ("allow_doubling", C.c_int),
+                ("allow_halving", C.c_int), ("step", C.c_uint), ("stream", C.c_uint)]
+
+
+class _SeasaltArgs(C.Structure):
+    _fields_ = [("u10", C.c_void_p), ("v10", C.c_void_p), ("xland", C.c_void_p), ("height", C.c_void_p),
+                ("sea_salt_opt", C.c_int), ("i_na", C.c_int), ("i_cl", C.c_int), ("weight_class", C.c_void_p),
+                ("dt", C.c_double), ("elapsed_time", C.c_double), ("allow_doubling", C.c_int),
                 ("allow_halving", C.c_int), ("step", C.c_uint)]
 
 
@@ -367,7 +374,7 @@ class PartMCGPU:
 
     def aero_state_add_aero_dist_sample(self, mode_type, weight_class, char_radius, log10_std_dev, vol_frac, num_conc,
                                         sample_prop, characteristic_factor, create_time=0.0, vol_frac_std=None,
-                                        allow_doubling=True, allow_halving=True, step=0):
+                                        allow_doubling=True, allow_halving=True, step=0, stream=0):
         """aero_state_add_aero_dist_sample (aero_state.F90:758) for every cell: modes described by arrays
         [n_mode] (vol_frac [n_mode][n_spec]), num_conc [n_cells][n_mode], sample_prop [n_cells].
         Returns the number of particles added per cell."""
@@ -384,8 +391,25 @@ class PartMCGPU:
         a.vol_frac, a.vol_frac_std, a.num_conc, a.sample_prop = _addr(vf), _addr(vs), _addr(nc), _addr(sp)
         a.characteristic_factor, a.create_time = float(characteristic_factor), float(create_time)
         a.allow_doubling, a.allow_halving, a.step = int(allow_doubling), int(allow_halving), int(step)
+        a.stream = int(stream)
         n_add = np.zeros(self.n_cells, np.int32)
         self._chk(self.L.pmcgpu_aero_state_add_aero_dist_sample(self.h, C.byref(a), _p(n_add)))
+        return n_add
+
+    def seasalt_emissions(self, u10, v10, xland, height, sea_salt_opt, i_na, i_cl, weight_class, dt, elapsed_time,
+                          allow_doubling=True, allow_halving=True, step=0):
+        """seasalt_emissions (interface/wrf_pmc_driver.F90:1767) as partmc_timestep calls it (:212-223): 2-D fields
+        [ny][nx] u10, v10, xland (WRF reals) and the height of the lowest layer; returns particles added per cell."""
+        a = _SeasaltArgs()
+        keep = [np.ascontiguousarray(x, dtype=np.float32) for x in (u10, v10, xland)]
+        keep.append(np.ascontiguousarray(height, dtype=np.float64))
+        keep.append(_i32(weight_class))
+        a.u10, a.v10, a.xland, a.height, a.weight_class = [_addr(x) for x in keep]
+        a.sea_salt_opt, a.i_na, a.i_cl = int(sea_salt_opt), int(i_na), int(i_cl)
+        a.dt, a.elapsed_time = float(dt), float(elapsed_time)
+        a.allow_doubling, a.allow_halving, a.step = int(allow_doubling), int(allow_halving), int(step)
+        n_add = np.zeros(self.n_cells, np.int32)
+        self._chk(self.L.pmcgpu_seasalt_emissions(self.h, C.byref(a), _p(n_add)))
         return n_add
 
     def aero_state_scale_weight(self, i_group, i_class, weight_ratio, allow_doubling=True, allow_halving=True, step=0):
