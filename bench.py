@@ -193,10 +193,28 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
+        self.mark_line = 0
+
+    def _lines(self):
+        try:
+            with open(self.f.name) as fh:
+                return fh.read().splitlines()
+        except OSError:
+            return []
+
+    def mark(self):
+        """start of the timed region: the sampler was started before the warm-up steps (nvidia-smi needs a few
+        hundred ms to deliver its first line; a strongly scaled timed region is shorter than that)"""
+        if self.p is None:
+            return
+        t0 = time.time()
+        while not self._lines() and time.time() - t0 < 3.0:
+            time.sleep(0.02)
+        self.mark_line = len(self._lines())
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
@@ -210,7 +228,14 @@ class ClockSampler:
         self.f.flush()
         self.f.seek(0)
         sm, mx, reasons, power = [], [], set(), []
-        for line in self.f.read().splitlines():
+        lines = self.f.read().splitlines()
+        window = "timed region"
+        if len(lines) > self.mark_line:
+            lines = lines[self.mark_line:]
+        else:  # a timed region shorter than the sampling period: the last warm-up samples (same load)
+            lines = lines[-3:]
+            window = "last warm-up steps (the timed region is shorter than the 50 ms sampling period)"
+        for line in lines:
             q = [x.strip() for x in line.split(",")]
             if len(q) < 9:
                 continue
@@ -226,7 +251,7 @@ class ClockSampler:
         os.unlink(self.f.name)
         if sm:
             out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                   "power_w_max": max(power), "samples": len(sm)}
+                   "power_w_max": max(power), "samples": len(sm), "window": window}
         return out
 
 
@@ -344,6 +369,7 @@ class Patch:
         torch, g = self.torch, self.g
         n_seq = warmup + steps
         self.prepare(synthetic, n_seq, steps)
+        clocks = ClockSampler(self.local) if sample_clocks else None
         for k in range(warmup):
             self.one_step(k, self.met_dev[k], self.numconc_dev, self.f_dev)
         g.check_status()
@@ -351,8 +377,9 @@ class Patch:
         g.profile_read(reset=True)
         g.profile_enable(True)
         launches0 = g.launch_count()
+        if clocks:
+            clocks.mark()
         self.barrier()
-        clocks = ClockSampler(self.local) if sample_clocks else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(self.stream)
         for k in range(warmup, n_seq):
