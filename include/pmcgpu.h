@@ -360,6 +360,18 @@ int pmcgpu_get_trans_moved(pmcgpu_ctx* ctx, int* n_moved);
 int pmcgpu_partmc_process(pmcgpu_ctx* ctx, int n_bin, double d_min, double d_max, double* tot_num_conc,
                           double* tot_wet_num_conc, double* tot_mass_conc, double* num_dist, double* mass_dist,
                           double* num_conc_by_class, double* species_mass_conc);
+/* pmcgpu_partmc_process without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments, same results.  The per-cell result table the kernel fills before it is copied to the caller's
+ * arrays lives in a file-scope device array of PMCGPU_PROCESS_STATIC_MAX_DOUBLES doubles (8 MiB, held by every GPU
+ * that loads the library until exit): n_cells (3 + 2 n_bin + n_class + n_spec) beyond that returns
+ * PMCGPU_ERR_CAPACITY with a message in pmcgpu_last_error.  All calls on one GPU share the array; it keeps the last
+ * call's contents (every entry used by a call is rewritten by that call), and calls that overlap on the GPU -- two
+ * contexts on one device, two host threads -- race on it: serialise them. */
+#define PMCGPU_PROCESS_STATIC_MAX_DOUBLES (1 << 20)
+int pmcgpu_partmc_process_static(pmcgpu_ctx* ctx, int n_bin, double d_min, double d_max, double* tot_num_conc,
+                                 double* tot_wet_num_conc, double* tot_mass_conc, double* num_dist,
+                                 double* mass_dist, double* num_conc_by_class, double* species_mass_conc);
 
 /* Checkpoint / restart of the whole device state of a context (what WRF's restart alarm needs; the reference
  * writes netCDF, partmc/src/output.F90:827-967): one flat binary file per rank with the particle records in cell

@@ -130,3 +130,66 @@ extern "C" int pmcgpu_partmc_process(pmcgpu_ctx* ctx, int n_bin, double d_min, d
   CUDA_OK(ctx, cudaStreamSynchronize(st));
   return PMCGPU_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// pmcgpu_partmc_process_static: the same diagnostics for callers that may not allocate (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The scratch that pmcgpu_partmc_process takes from cudaMalloc (the per-cell result
+// table the kernel writes before it is copied to the caller's host or device arrays) lives in a file-scope device
+// array of PMCGPU_PROCESS_STATIC_MAX_DOUBLES doubles (8 MiB), held by every GPU that loads the library until exit.
+//   * n_cells (3 + 2 n_bin + n_class + n_spec) beyond that maximum is rejected with PMCGPU_ERR_CAPACITY.
+//   * The array is shared by every call and every context of the process on that GPU and keeps the last call's
+//     contents: the kernel writes EVERY entry of the table it is given (totals, all bins, all classes, all species of
+//     every cell, zeros for empty cells), so nothing has to be cleared; calls that overlap on the GPU (two contexts
+//     = two streams on one device, or two host threads) race on it and must be serialised by the caller.
+//   * In host code the name of the array is a host-side stand-in, not a device address: its device address is taken
+//     once per device, with that device current, by cudaGetSymbolAddress and handed to the kernel.
+// No cudaMalloc / cudaFree / allocating library call on this path (ProfScope is left out: it may create events).
+#define PMC_PROC_MAX_DEVICES 64
+static __device__ __align__(256) double g_proc_scratch[PMCGPU_PROCESS_STATIC_MAX_DOUBLES];
+static double* g_proc_scratch_addr[PMC_PROC_MAX_DEVICES];  // device address per device ordinal, nullptr = not taken yet
+
+extern "C" int pmcgpu_partmc_process_static(pmcgpu_ctx* ctx, int n_bin, double d_min, double d_max,
+                                            double* tot_num_conc, double* tot_wet_num_conc, double* tot_mass_conc,
+                                            double* num_dist, double* mass_dist, double* num_conc_by_class,
+                                            double* species_mass_conc) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
+  if (!ctx || n_bin < 1 || n_bin > 2000 || !(d_min > 0.0) || !(d_max > d_min)) return PMCGPU_ERR_ARG;
+  DevView& v = ctx->v;
+  const size_t nc = (size_t)v.n_cells;
+  const size_t n_out = nc * (3 + 2 * (size_t)n_bin + v.C + v.S);
+  if (n_out > (size_t)PMCGPU_PROCESS_STATIC_MAX_DOUBLES) {
+    ctx->err = "pmcgpu_partmc_process_static: n_cells (3 + 2 n_bin + n_class + n_spec) = " + std::to_string(n_out) +
+               " doubles exceed the static scratch of " + std::to_string((size_t)PMCGPU_PROCESS_STATIC_MAX_DOUBLES) +
+               " doubles; use pmcgpu_partmc_process or fewer bins";
+    return PMCGPU_ERR_CAPACITY;
+  }
+  const int dev = ctx->cfg.device;
+  if (dev < 0 || dev >= PMC_PROC_MAX_DEVICES) return PMCGPU_ERR_ARG;
+  if (g_proc_scratch_addr[dev] == nullptr) {  // set-up, once per device, with that device current
+    double* p = nullptr;
+    CUDA_OK(ctx, cudaGetSymbolAddress((void**)&p, g_proc_scratch));
+    g_proc_scratch_addr[dev] = p;
+  }
+  double* buf = g_proc_scratch_addr[dev];
+  ProcOut o;
+  o.tot_num_conc = buf;
+  o.tot_wet_num_conc = o.tot_num_conc + nc;
+  o.tot_mass_conc = o.tot_wet_num_conc + nc;
+  o.num_dist = o.tot_mass_conc + nc;
+  o.mass_dist = o.num_dist + nc * n_bin;
+  o.num_conc_by_class = o.mass_dist + nc * n_bin;
+  o.species_mass_conc = o.num_conc_by_class + nc * v.C;
+  const size_t smem = (size_t)(2 * n_bin + v.C + v.S + 3 * (PROC_THREADS / 32)) * sizeof(double);  // < 48 KB
+  cudaStream_t st = ctx->stream;
+  k_partmc_process<<<v.n_cells, PROC_THREADS, smem, st>>>(v, n_bin, d_min, d_max, o);
+  LAUNCH_CHECK(ctx);
+#define OUT(dst, src, n) \
+  if (dst) CUDA_OK(ctx, cudaMemcpyAsync(dst, src, (size_t)(n) * sizeof(double), cudaMemcpyDefault, st));
+  OUT(tot_num_conc, o.tot_num_conc, nc) OUT(tot_wet_num_conc, o.tot_wet_num_conc, nc)
+  OUT(tot_mass_conc, o.tot_mass_conc, nc) OUT(num_dist, o.num_dist, nc * n_bin) OUT(mass_dist, o.mass_dist, nc * n_bin)
+  OUT(num_conc_by_class, o.num_conc_by_class, nc * v.C) OUT(species_mass_conc, o.species_mass_conc, nc * v.S)
+#undef OUT
+  CUDA_OK(ctx, cudaStreamSynchronize(st));
+  return PMCGPU_OK;
+}

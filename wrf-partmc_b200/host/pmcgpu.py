@@ -472,14 +472,16 @@ class PartMCGPU:
         a.num_conc, a.outflow, a.throw_away = nc.ctypes.data, of.ctypes.data, ta.ctypes.data
         self._chk(self.L.pmcgpu_set_boundary(self.h, C.byref(a)))
 
-    def partmc_process(self, n_bin=100, d_min=1e-9, d_max=1e-3):
-        """per-cell diagnostics of partmc_process (interface/wrf_pmc_driver.F90:826-944), reduced on the device"""
+    def partmc_process(self, n_bin=100, d_min=1e-9, d_max=1e-3, static=False):
+        """per-cell diagnostics of partmc_process (interface/wrf_pmc_driver.F90:826-944), reduced on the device;
+        static=True: pmcgpu_partmc_process_static (no allocation, result table in a static device array)"""
         n, S, Cc = self.n_cells, self.data.n_spec, self.n_class
         out = dict(tot_num_conc=np.zeros(n), tot_wet_num_conc=np.zeros(n), tot_mass_conc=np.zeros(n),
                    num_dist=np.zeros((n, n_bin)), mass_dist=np.zeros((n, n_bin)), num_conc_by_class=np.zeros((n, Cc)),
                    species_mass_conc=np.zeros((n, S)))
-        self.L.pmcgpu_partmc_process.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double] + [C.c_void_p] * 7
-        self._chk(self.L.pmcgpu_partmc_process(self.h, n_bin, d_min, d_max, *[out[k].ctypes.data for k in (
+        fn = self.L.pmcgpu_partmc_process_static if static else self.L.pmcgpu_partmc_process
+        fn.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double] + [C.c_void_p] * 7
+        self._chk(fn(self.h, n_bin, d_min, d_max, *[out[k].ctypes.data for k in (
             "tot_num_conc", "tot_wet_num_conc", "tot_mass_conc", "num_dist", "mass_dist", "num_conc_by_class",
             "species_mass_conc")]))
         return out
