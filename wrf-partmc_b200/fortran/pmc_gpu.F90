@@ -120,7 +120,9 @@ contains
   subroutine pmc_gpu_upload_aero_states(aero_states, env_states, pmc_is, pmc_ie, pmc_js, &
        pmc_je, pmc_ks, pmc_ke)
     use pmc_aero_state
+    use pmc_aero_particle, only: aero_particle_n_components
     use pmc_env_state
+    use pmc_util, only: warn_assert_msg, integer_to_string
     integer, intent(in) :: pmc_is, pmc_ie, pmc_js, pmc_je, pmc_ks, pmc_ke
     type(aero_state_t), dimension(pmc_is:pmc_ie,pmc_ks:pmc_ke,pmc_js:pmc_je), &
          intent(in) :: aero_states
@@ -128,6 +130,7 @@ contains
          intent(in) :: env_states
 
     integer :: i, j, k, c, p, n_cells, n_spec, n_class, n_tot, q, i_class
+    integer :: n_lost_comp, n_lost_optics
     integer(c_int), allocatable, target :: counts(:), wgroup(:), wclass(:), nprim(:), hyst(:), wtype(:)
     integer(c_int64_t), allocatable, target :: ids(:)
     real(c_double), allocatable, target :: vol(:,:), lct(:), gct(:), wmag(:), wexp(:)
@@ -155,12 +158,22 @@ contains
     allocate(temp(n_cells), pres(n_cells), rh(n_cells), alt(n_cells), cvol(n_cells))
     c = 0
     q = 0
+    n_lost_comp = 0
+    n_lost_optics = 0
     do j = pmc_js, pmc_je
     do k = pmc_ks, pmc_ke
     do i = pmc_is, pmc_ie
        c = c + 1
        do p = 1, counts(c)
           q = q + 1
+          ! what the device record does not carry (DESIGN.md section 2): count it, report it below
+          if (aero_particle_n_components(aero_states(i,k,j)%apa%particle(p)) > 1) &
+               n_lost_comp = n_lost_comp + 1
+          if (allocated(aero_states(i,k,j)%apa%particle(p)%absorb_cross_sect)) then
+             if (any(aero_states(i,k,j)%apa%particle(p)%absorb_cross_sect /= 0d0) &
+                  .or. any(aero_states(i,k,j)%apa%particle(p)%scatter_cross_sect /= 0d0)) &
+                  n_lost_optics = n_lost_optics + 1
+          end if
           vol(q, :) = aero_states(i,k,j)%apa%particle(p)%vol     ! species-major: vol(q, s)
           wgroup(q) = aero_states(i,k,j)%apa%particle(p)%weight_group
           wclass(q) = aero_states(i,k,j)%apa%particle(p)%weight_class
@@ -183,6 +196,14 @@ contains
     end do
     end do
     end do
+    ! non-fatal, the reference's convention for recoverable conditions (util.F90 warn_assert_msg): the device
+    ! state keeps least / greatest_create_time and n_primary_parts, not the per-component source lists and optics
+    call warn_assert_msg(731204655, n_lost_comp == 0, &
+         'pmc_gpu_upload_aero_states: ' // trim(integer_to_string(n_lost_comp)) &
+         // ' particles carry more than one aero_component; the device record keeps one (DESIGN.md section 2)')
+    call warn_assert_msg(731204656, n_lost_optics == 0, &
+         'pmc_gpu_upload_aero_states: ' // trim(integer_to_string(n_lost_optics)) &
+         // ' particles carry optical properties; they are recomputed on the host after a download')
     call pmc_gpu_check(pmcgpu_set_particles(pmc_gpu_handle, c_loc(counts), c_loc(vol), &
          c_loc(wgroup), c_loc(wclass), c_loc(ids), c_loc(nprim), c_loc(hyst), c_loc(lct), &
          c_loc(gct)), 'pmcgpu_set_particles')
