@@ -92,6 +92,27 @@ int pmcgpu_set_particles(pmcgpu_ctx* ctx, const int* cell_count, const double* v
 int pmcgpu_get_counts(pmcgpu_ctx* ctx, int* cell_count);
 int pmcgpu_get_particles(pmcgpu_ctx* ctx, long long n_total, double* vol, int* wgroup, int* wclass, int64_t* id,
                          int* n_primary, int* hyst, double* least_create_time, double* greatest_create_time);
+/* The cold part of the particle record (aero_particle.F90:38-54), opt-in because it more than doubles the record:
+ * component(:) = up to PMCGPU_MAX_COMPONENTS {source_id, create_time} pairs (MAX_AERO_COMPONENT_SIZE, :22) and
+ * n_opaque doubles per particle that the device moves but never interprets (the optical fields absorb_cross_sect,
+ * scatter_cross_sect, asymmetry, refract_shell, refract_core, core_vol of do_optical runs).  After
+ * pmcgpu_track_components every record move carries them: sort, rebalance, reweight, scale_weight, deposition,
+ * transport (also across ranks: the halo record grows by 4 + 20 * 12 + 8 n_opaque bytes), checkpoints; new particles
+ * get one component {weight class of their mode as source (one class per source in WRF), create time} and zero
+ * optics (aero_particle_set_component, aero_state.F90:823); coagulation concatenates the two lists or keeps 20 of
+ * them split in proportion to n_primary_parts (aero_particle_coagulate, aero_particle.F90:955-972, and the
+ * accelerated path's resampling, coagulation.F90:472-508) and zeroes the optics (:920-929).
+ * Call once per context, before pmcgpu_comm_init and before the first transport step; particles already uploaded get
+ * the default one component {weight class, least_create_time}, like every later pmcgpu_set_particles. */
+#define PMCGPU_MAX_COMPONENTS 20
+int pmcgpu_track_components(pmcgpu_ctx* ctx, int n_opaque /* 0..64 */);
+/* packed like pmcgpu_get_particles (cell by cell, particle order): n_comp [n_total], source and create_time
+ * [n_total][PMCGPU_MAX_COMPONENTS] (entries beyond n_comp ignored / returned as 0), opaque [n_total][n_opaque]
+ * (may be NULL).  n_total must equal the device population. */
+int pmcgpu_set_components(pmcgpu_ctx* ctx, long long n_total, const int* n_comp, const int* source,
+                          const double* create_time, const double* opaque);
+int pmcgpu_get_components(pmcgpu_ctx* ctx, long long n_total, int* n_comp, int* source, double* create_time,
+                          double* opaque);
 /* per-cell id counters (aero_particle.F90:64 next_id, one per cell on the device) */
 int pmcgpu_set_next_id(pmcgpu_ctx* ctx, const int64_t* next_id);
 int pmcgpu_get_next_id(pmcgpu_ctx* ctx, int64_t* next_id);

@@ -132,6 +132,23 @@ class Oracle:
                              _p(out["hyst"], C.c_int), _p(out["lct"], C.c_double), _p(out["gct"], C.c_double))
         return out
 
+    def set_components(self, cell, n_comp, source, create_time, opaque=None):
+        """component(:) lists of a cell's particles: n_comp [n], source / create_time [n][20]; opaque [n][n_opq]"""
+        nc, src, tm = _i32(n_comp), _i32(source), _f64(create_time)
+        oq = _f64(opaque) if opaque is not None else None
+        n_opq = 0 if oq is None or nc.size == 0 else oq.size // nc.size
+        self._chk(self.L.pmco_set_components(self.h, C.c_int(cell), _p(nc, C.c_int), _p(src, C.c_int),
+                                             _p(tm, C.c_double), C.c_int(n_opq),
+                                             _p(oq, C.c_double) if oq is not None else None))
+
+    def get_components(self, cell, n_opq=0):
+        n = self.count(cell)
+        nc, src, tm = np.zeros(n, np.int32), np.zeros((n, 20), np.int32), np.zeros((n, 20))
+        oq = np.zeros((n, n_opq))
+        self._chk(self.L.pmco_get_components(self.h, C.c_int(cell), _p(nc, C.c_int), _p(src, C.c_int),
+                                             _p(tm, C.c_double), C.c_int(n_opq), _p(oq, C.c_double)))
+        return nc, src, tm, oq
+
     def set_weights(self, cell, wtype, magnitude, exponent):
         t, m, e = _i32(wtype).ravel(), _f64(magnitude).ravel(), _f64(exponent).ravel()
         self.L.pmco_set_weights(self.h, C.c_int(cell), _p(t, C.c_int), _p(m, C.c_double), _p(e, C.c_double))

@@ -318,8 +318,50 @@ double particle_solute_kappa(const Particle& p, const AeroData& d) {
   }
   return total_solute_quantity(p, d, kappa.data()) / total_solute_quantity(p, d, nullptr);
 }
-void particle_coagulate(const Particle& p1, const Particle& p2, Particle& pn) {
+// rand.F90:515-542 (selection sampling; 1-based indices in ascending order)
+std::vector<int> sample_without_replacement(int sample_size, int population_size, Stream& s) {
+  std::vector<int> sample((size_t)std::max(sample_size, 0));
+  int t = 0, m = 0;
+  while (m < sample_size && t < 64) {  // (the guard only matters for sample_size > population_size: out of bounds upstream)
+    const double r = s.next();
+    if ((double)(population_size - t) * r >= (double)(sample_size - m)) {
+      t = t + 1;
+    } else {
+      t = t + 1;
+      m = m + 1;
+      sample[m - 1] = t;
+    }
+  }
+  sample.resize((size_t)m);
+  return sample;
+}
+void particle_coagulate(const Particle& p1, const Particle& p2, Particle& pn, Rng* rng, RngKey ckey, uint32_t j0) {
   pmc_assert(203741686, p1.vol.size() == p2.vol.size());
+  // components (:940-972): concatenate, or keep MAX_AERO_COMPONENT_SIZE split in proportion to n_primary_parts
+  std::vector<int> csrc;
+  std::vector<double> ctime;
+  {
+    const int n1 = (int)p1.comp_src.size(), n2 = (int)p2.comp_src.size();
+    if (n1 + n2 > MAX_AERO_COMPONENT_SIZE && rng) {
+      ckey.phase = PH_COMP;
+      Stream s0(rng, ckey, j0);
+      int n1_new = prob_round((double)p1.n_primary_parts / (double)(p1.n_primary_parts + p2.n_primary_parts) *
+                                  (double)MAX_AERO_COMPONENT_SIZE, s0.next());
+      n1_new = std::min(n1_new, n1);  // holds upstream whenever n_components = min(n_primary_parts, 20)
+      int n2_new = std::min(MAX_AERO_COMPONENT_SIZE - n1_new, n2);
+      Stream sa(rng, ckey, j0 + 1), sb(rng, ckey, j0 + 33);
+      const std::vector<int> pick1 = sample_without_replacement(n1_new, n1, sa);
+      const std::vector<int> pick2 = sample_without_replacement(n2_new, n2, sb);
+      for (int i : pick1) { csrc.push_back(p1.comp_src[i - 1]); ctime.push_back(p1.comp_time[i - 1]); }
+      for (int i : pick2) { csrc.push_back(p2.comp_src[i - 1]); ctime.push_back(p2.comp_time[i - 1]); }
+    } else {
+      csrc = p1.comp_src;
+      ctime = p1.comp_time;
+      csrc.insert(csrc.end(), p2.comp_src.begin(), p2.comp_src.end());
+      ctime.insert(ctime.end(), p2.comp_time.begin(), p2.comp_time.end());
+    }
+  }
+  const size_t n_opq = std::max(p1.opq.size(), p2.opq.size());
   std::vector<double> v(p1.vol.size());
   for (size_t i = 0; i < v.size(); i++) v[i] = p1.vol[i] + p2.vol[i];
   const int hyst = (p1.water_hyst_leg == 1 && p2.water_hyst_leg == 1) ? 1 : 0;
@@ -335,6 +377,9 @@ void particle_coagulate(const Particle& p1, const Particle& p2, Particle& pn) {
   // aero_particle_t carries the default (we use min, documented in DESIGN.md)
   pn.least_create_time = std::min(p1.least_create_time, p2.least_create_time);
   pn.n_primary_parts = npp;
+  pn.comp_src = csrc;
+  pn.comp_time = ctime;
+  pn.opq.assign(n_opq, 0.0);  // optics of a coagulated particle are zero until recomputed (:920-929)
 }
 double awa_num_conc(const WeightArray& a, const Particle& p) {
   return awa_num_conc_at_radius(a, p.weight_class, particle_radius(p));
@@ -1016,7 +1061,7 @@ static void coagulate_weighting(const Particle& pt1, const Particle& pt2, Partic
     id_2_lost = remove_2;
   }
   if (create_new) {
-    particle_coagulate(pt1, pt2, ptc);
+    particle_coagulate(pt1, pt2, ptc, s.rng, s.key, 0u);
     ptc.weight_group = new_group;
     ptc.weight_class = cc;
     if (remove_1 && !id_1_lost) {
@@ -1106,7 +1151,7 @@ static void per_set_coag(int type, double k_max, const EnvState& env, const Aero
   }
 }
 
-// coagulation.F90:333-517 (components are cold data and not carried)
+// coagulation.F90:333-517
 static void sample_source_particle(AeroState& st, const AeroData& d, const EnvState& env, int type, int bs, int cs,
                                    const Particle& coag_particle, double n_samp_mean, double accept_factor,
                                    Stream& s, Stream& ss, int& n_samp, int& n_coag, int& n_remove, Particle& source) {
@@ -1163,7 +1208,10 @@ static void sample_source_particle(AeroState& st, const AeroData& d, const EnvSt
     if (ss.next() < prob_coag) {
       n_avg = n_avg + 1;
       Particle tmp;
-      particle_coagulate(source, st.apa[i_part - 1], tmp);
+      {
+        RngKey ck = ss.key;
+        particle_coagulate(source, st.apa[i_part - 1], tmp, ss.rng, ck, 128u * (uint32_t)i_samp);
+      }
       source = tmp;
       for (int q = 0; q < S; q++) vol_sq[q] += st.apa[i_part - 1].vol[q] * st.apa[i_part - 1].vol[q];
       if (i_samp <= n_samp_remove) {
@@ -1185,16 +1233,55 @@ static void sample_source_particle(AeroState& st, const AeroData& d, const EnvSt
   const double f = (double)n_coag / (double)n_avg;
   for (int q = 0; q < S; q++) source.vol[q] = source.vol[q] * f;
   source.n_primary_parts = prob_round((double)source.n_primary_parts * ((double)n_coag / n_avg), s.next());
+  // components of the averaged source (:472-508): down to min(n_primary_parts, 20) by sampling without replacement,
+  // or up to it by whole copies plus a sample of the rest (draws: PH_COMP, key of the sample stream, j = 1 + t)
+  {
+    const int n_comp = (int)source.comp_src.size();
+    const int n_comp_new = std::min(source.n_primary_parts, MAX_AERO_COMPONENT_SIZE);
+    RngKey ck = ss.key;
+    ck.phase = PH_COMP;
+    Stream sc(ss.rng, ck, 1u);
+    std::vector<int> nsrc;
+    std::vector<double> ntime;
+    if (n_comp_new < n_comp) {
+      for (int i : sample_without_replacement(n_comp_new, n_comp, sc)) {
+        nsrc.push_back(source.comp_src[i - 1]);
+        ntime.push_back(source.comp_time[i - 1]);
+      }
+      source.comp_src = nsrc;
+      source.comp_time = ntime;
+    } else if (n_comp < MAX_AERO_COMPONENT_SIZE && n_comp > 0) {
+      int i_comp = 1;
+      while (i_comp <= n_comp_new) {
+        if (i_comp + n_comp <= n_comp_new) {
+          for (int i = 1; i <= n_comp; i++) {
+            nsrc.push_back(source.comp_src[i - 1]);
+            ntime.push_back(source.comp_time[i - 1]);
+          }
+          i_comp = i_comp + n_comp;
+        } else {
+          const int sample_size = n_comp_new - i_comp + 1;
+          for (int i : sample_without_replacement(sample_size, n_comp, sc)) {
+            nsrc.push_back(source.comp_src[i - 1]);
+            ntime.push_back(source.comp_time[i - 1]);
+          }
+          i_comp = n_comp_new + 1;
+        }
+      }
+      source.comp_src = nsrc;
+      source.comp_time = ntime;
+    }
+  }
 }
 // coagulation.F90:522-582
 static void coag_target_with_source(AeroState& st, int bt, int ct, int target_unif_entry, const Particle& source,
-                                    int cc, Stream& s) {
+                                    int cc, Stream& s, const RngKey& ckey) {
   const int target_part = st.sorted.size_class.inv(bt, ct).at(target_unif_entry);
   Particle& tp = st.apa[target_part - 1];
   const int64_t target_id = tp.id;
   const double old_num_conc_target = awa_num_conc(st.awa, tp);
   Particle merged;
-  particle_coagulate(tp, source, merged);
+  particle_coagulate(tp, source, merged, s.rng, ckey, 64u);
   merged.id = target_id;
   const int new_group = awa_rand_group(st.awa, cc, particle_radius(merged), s);
   merged.weight_group = new_group;
@@ -1235,7 +1322,7 @@ static bool try_per_particle_coag(int type, double k_max, const EnvState& env, c
     Particle source;
     sample_source_particle(st, d, env, type, bs, cs, target_particle, n_source_per_target, accept_factor, s, ss, n_samp,
                            n_coag, n_remove, source);
-    if (n_coag > 0) coag_target_with_source(st, bt, ct, e, source, cc, s);
+    if (n_coag > 0) coag_target_with_source(st, bt, ct, e, source, cc, s, ss.key);
     out.tot_n_samp += n_samp;
     out.tot_n_coag += n_coag;
   }

@@ -74,6 +74,9 @@ enum Phase : uint32_t {
   PH_INIT = 8,
   PH_DEP = 9,         // a = 0, b = particle index (dry deposition)
   PH_EMIT = 10,       // a = (group, mode), b = 0 (count) / sample number (aero_state_add_aero_dist_sample)
+  PH_COMP = 12,       // subsampling of component lists: (a, b) of the coagulation event (accelerated path: a | 2^31),
+                      // j = j0 + {0 prob_round, 1 + t first sample_without_replacement, 33 + t second}; j0 = 0 event,
+                      // accelerated path: 128 i_samp per accepted sample, 0 the resampling, 64 the target merge
   PH_BND = 11         // aero_state_resample of a boundary cell: a = (group, class): b = 0 count, b >= 1 removal;
                       // a = 1000 + (group, class) n_mode + mode: b = 0 count of the mode, b >= 1 new particle
 };
@@ -159,7 +162,13 @@ struct Particle {  // aero_particle.F90:30-61 (hot fields; optics/components are
   int64_t id = 0;
   double least_create_time = 0.0, greatest_create_time = 0.0;
   int n_primary_parts = 1;
+  // cold part (aero_particle.F90:38-54): component(:) = {source_id, create_time} pairs, at most
+  // MAX_AERO_COMPONENT_SIZE = 20 (:22), and the optical fields as an opaque vector
+  std::vector<int> comp_src;
+  std::vector<double> comp_time;
+  std::vector<double> opq;
 };
+static const int MAX_AERO_COMPONENT_SIZE = 20;
 struct BinGrid {  // bin_grid.F90 (log type only, as aero_sorted uses)
   std::vector<double> edges, centers;
   int size() const { return edges.empty() ? 0 : (int)edges.size() - 1; }
@@ -233,7 +242,9 @@ double particle_mass(const Particle& p, const AeroData& d);      // :252
 double particle_density(const Particle& p, const AeroData& d);   // :474
 double particle_solute_volume(const Particle& p, const AeroData& d);  // :687
 double particle_solute_kappa(const Particle& p, const AeroData& d);   // :724-755
-void particle_coagulate(const Particle& p1, const Particle& p2, Particle& pn);  // :900-980
+void particle_coagulate(const Particle& p1, const Particle& p2, Particle& pn, Rng* rng = nullptr,
+                        RngKey ckey = RngKey{0, 0, 0, 0, 0}, uint32_t j0 = 0);  // :900-980
+std::vector<int> sample_without_replacement(int sample_size, int population_size, Stream& s);  // rand.F90:515-542
 double awa_num_conc(const WeightArray& a, const Particle& p);    // aero_weight_array.F90:257
 double awa_single_num_conc(const WeightArray& a, const Particle& p);  // :218-227
 

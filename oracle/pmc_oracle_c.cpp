@@ -63,9 +63,40 @@ int pmco_set_cell(void* h, int cell, int n, const double* vol, const int* wgroup
     p.water_hyst_leg = hyst ? hyst[i] : 0;
     p.least_create_time = lct ? lct[i] : 0.0;
     p.greatest_create_time = gct ? gct[i] : 0.0;
+    p.comp_src.assign(1, p.weight_class);  // default cold part, like pmcgpu_set_particles
+    p.comp_time.assign(1, p.least_create_time);
   }
   st.valid_sort = false;
   ORACLE_CATCH(d)
+}
+// components / opaque optics of a cell's particles: n_comp [n], source / create_time [n][20], opaque [n][n_opq]
+int pmco_set_components(void* h, int cell, const int* n_comp, const int* source, const double* create_time,
+                        int n_opq, const double* opaque) {
+  AeroState& st = ((OracleDomain*)h)->cells[cell];
+  for (int i = 0; i < st.n_part(); i++) {
+    Particle& p = st.apa[i];
+    const int nc = std::max(0, std::min(n_comp[i], MAX_AERO_COMPONENT_SIZE));
+    p.comp_src.assign(source + (size_t)i * MAX_AERO_COMPONENT_SIZE, source + (size_t)i * MAX_AERO_COMPONENT_SIZE + nc);
+    p.comp_time.assign(create_time + (size_t)i * MAX_AERO_COMPONENT_SIZE,
+                       create_time + (size_t)i * MAX_AERO_COMPONENT_SIZE + nc);
+    if (opaque && n_opq > 0) p.opq.assign(opaque + (size_t)i * n_opq, opaque + (size_t)(i + 1) * n_opq);
+  }
+  return 0;
+}
+int pmco_get_components(void* h, int cell, int* n_comp, int* source, double* create_time, int n_opq, double* opaque) {
+  const AeroState& st = ((OracleDomain*)h)->cells[cell];
+  for (int i = 0; i < st.n_part(); i++) {
+    const Particle& p = st.apa[i];
+    const int nc = (int)p.comp_src.size();
+    n_comp[i] = nc;
+    for (int q = 0; q < MAX_AERO_COMPONENT_SIZE; q++) {
+      source[(size_t)i * MAX_AERO_COMPONENT_SIZE + q] = q < nc ? p.comp_src[q] : 0;
+      create_time[(size_t)i * MAX_AERO_COMPONENT_SIZE + q] = q < nc ? p.comp_time[q] : 0.0;
+    }
+    if (opaque)
+      for (int q = 0; q < n_opq; q++) opaque[(size_t)i * n_opq + q] = q < (int)p.opq.size() ? p.opq[q] : 0.0;
+  }
+  return 0;
 }
 int pmco_set_next_id(void* h, int cell, long long next_id) {
   ((OracleDomain*)h)->cells[cell].idgen.next_id = next_id;

@@ -136,6 +136,8 @@ int aero_state_add_aero_dist_sample(AeroState& st, const AeroData& d, const std:
         p.greatest_create_time = create_time;
         p.n_primary_parts = 1;
         p.water_hyst_leg = 0;
+        p.comp_src.assign(1, c);  // aero_particle_set_component (:823); source = weight class (one per source in WRF)
+        p.comp_time.assign(1, create_time);
         aero_state_add_particle(st, p, true);
       }
     }

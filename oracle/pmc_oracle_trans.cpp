@@ -372,6 +372,8 @@ static int aero_state_resample(AeroState& st, const AeroData& data, const std::v
             p.greatest_create_time = create_time;
             p.n_primary_parts = 1;
             p.water_hyst_leg = 0;
+            p.comp_src.assign(1, c);
+            p.comp_time.assign(1, create_time);
             if (awa_num_conc(st.awa, p) > num_conc_threshold) {
               aero_state_add_particle(st, p, true);
               n_part_add++;

@@ -62,6 +62,17 @@ def run_cpu(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
+def components_of_ids(ids):
+    """deterministic component lists from the particle ids (both sides of the 2-rank component test use it)"""
+    ids = np.asarray(ids, np.int64)
+    nc = (1 + ids % 3).astype(np.int32)
+    q = np.arange(20)[None, :]
+    src = ((ids[:, None] + q) % 7 + 1).astype(np.int32)
+    tm = ids[:, None] * 0.5 + q
+    opq = (ids * 0.25)[:, None]
+    return nc, src, tm, opq
+
+
 def run_gpu(rank, world, port, out_dir, cfg):
     import torch.distributed as dist
     import wrf_partmc_b200 as W
@@ -86,6 +97,9 @@ def run_gpu(rank, world, port, out_dir, cfg):
               cell_volume=pc["cell_volume"])
     N = int(case["counts"].sum())
     g.set_next_id(np.full(pc["n_cells"], N // case["n_cells"] + 2, np.int64))
+    if cfg.get("components"):  # before comm_init: the halo record carries the cold part
+        g.track_components(1)
+        g.set_components(*components_of_ids(pc["id"]))
     uid = decomp.broadcast_unique_id(W.comm_unique_id, rank)
     g.comm_init(uid, world, rank, px, py)
     nc = np.load(os.path.join(out_dir, "num_conc.npy"))
@@ -117,9 +131,13 @@ def run_gpu(rank, world, port, out_dir, cfg):
     P = g.get_particles()
     _, m, _ = g.get_weights()
     nb, gmin, gmax = g.grid()
+    extra = {}
+    if cfg.get("components"):
+        cn, cs, ct, cq = g.get_components()
+        extra = dict(comp_n=cn, comp_src=cs, comp_time=ct, comp_opq=cq)
     np.savez(os.path.join(out_dir, "gpu_%d.npz" % rank), cells=pc["cells"], count=P["count"], vol=P["vol"], id=P["id"],
              wclass=P["wclass"], n_primary=P["n_primary"], wmag=m, nb=nb, gmin=gmin, gmax=gmax, moved=moved,
-             next_id=g.get_next_id())
+             next_id=g.get_next_id(), **extra)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -90,8 +90,9 @@ def test_patch_slicing_matches_global_cell_order():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n_spec,is_open", [(4, False), (20, False), (4, True)])
-def test_two_rank_transport_bit_exact(n_spec, is_open):
+@pytest.mark.parametrize("n_spec,is_open,comps", [(4, False, False), (20, False, False), (4, True, False),
+                                                  (4, False, True), (4, True, True)])
+def test_two_rank_transport_bit_exact(n_spec, is_open, comps):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (gpurun --gpus 2)")
@@ -99,9 +100,13 @@ def test_two_rank_transport_bit_exact(n_spec, is_open):
     from oracle import oracle as O
     from wrf_partmc_b200.host import synthetic
     cfg = dict(gnx=8, nz=4, gny=4 if is_open else 3, px=2, py=1, n_per_cell=200, n_spec=n_spec, seed=5, n_steps=3,
-               open=is_open)
+               open=is_open, components=comps)
     case = MW.global_case(cfg)
     o = common.oracle_from_case(O, case)
+    if comps:  # component lists and one opaque double per particle cross the rank boundary with their records
+        off0 = np.concatenate([[0], np.cumsum(case["counts"])])
+        for c in range(case["n_cells"]):
+            o.set_components(c, *MW.components_of_ids(case["id"][off0[c]:off0[c + 1]]))
     for c in range(case["n_cells"]):
         o.set_env(c, T=case["T"][c], p=case["P"][c], RH=case["RH"][c], rrho=case["rrho"][c],
                   cell_volume=case["cell_volume"][c])
@@ -133,6 +138,10 @@ def test_two_rank_transport_bit_exact(n_spec, is_open):
             onb, omin, omax, _ = o.grid(int(c))
             assert x["nb"][lc] == onb
             assert x["next_id"][lc] == o.L.pmco_get_next_id(o.h, int(c))
+            if comps:
+                onc, osrc, otm, oopq = o.get_components(int(c), 1)
+                assert np.array_equal(x["comp_n"][a:b], onc) and np.array_equal(x["comp_src"][a:b], osrc)
+                assert np.array_equal(x["comp_time"][a:b], otm) and np.array_equal(x["comp_opq"][a:b], oopq)
             n_checked += 1
     assert n_checked == case["n_cells"]
 

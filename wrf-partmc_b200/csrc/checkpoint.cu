@@ -12,12 +12,13 @@
 #include <vector>
 
 namespace {
-const char CK_MAGIC[8] = {'P', 'M', 'C', 'G', 'P', 'U', '0', '2'};
+const char CK_MAGIC[8] = {'P', 'M', 'C', 'G', 'P', 'U', '0', '3'};
 struct CkHeader {
   char magic[8];
   int n_cells, cap, S, G, C, nbcap;
   int nx, nz, ny, global_nx, global_ny, i_offset, j_offset, periodic_x, periodic_y;
   int kmax_ktype, any_nonflat;
+  int cold, n_opq;  // component lists / opaque optics carried (pmcgpu_track_components)
   long long n_particles;
 };
 template <typename T>
@@ -69,6 +70,7 @@ extern "C" int pmcgpu_checkpoint_write(pmcgpu_ctx* ctx, const char* path) {
   h.global_ny = ctx->cfg.global_ny; h.i_offset = ctx->cfg.i_offset; h.j_offset = ctx->cfg.j_offset;
   h.periodic_x = ctx->cfg.periodic_x; h.periodic_y = ctx->cfg.periodic_y;
   h.kmax_ktype = ctx->kmax_ktype; h.any_nonflat = ctx->any_nonflat ? 1 : 0;
+  h.cold = v.cold.n ? 1 : 0; h.n_opq = v.n_opq;
   h.n_particles = N;
   if (fwrite(&h, sizeof(h), 1, f) != 1 || fwrite(counts.data(), sizeof(int), nc, f) != nc) {
     fclose(f);
@@ -88,6 +90,18 @@ extern "C" int pmcgpu_checkpoint_write(pmcgpu_ctx* ctx, const char* path) {
     if (!ok) {
       fclose(f);
       return PMCGPU_ERR_ARG;
+    }
+    if (v.cold.n) {  // cold part of the records: [N] counts, [N][20] sources and times, [N][n_opq] opaque
+      std::vector<int> ncmp(n), src(n * PMC_MAX_COMP);
+      std::vector<double> tim(n * PMC_MAX_COMP), opq(std::max<size_t>(n * v.n_opq, 1));
+      CK(pmcgpu_get_components(ctx, N, ncmp.data(), src.data(), tim.data(), opq.data()));
+      ok = fwrite(ncmp.data(), sizeof(int), m, f) == m && fwrite(src.data(), sizeof(int), m * PMC_MAX_COMP, f) == m * PMC_MAX_COMP &&
+           fwrite(tim.data(), sizeof(double), m * PMC_MAX_COMP, f) == m * PMC_MAX_COMP &&
+           fwrite(opq.data(), sizeof(double), m * v.n_opq, f) == m * v.n_opq;
+      if (!ok) {
+        fclose(f);
+        return PMCGPU_ERR_ARG;
+      }
     }
   }
   const size_t ncg = nc * v.C * v.G;
@@ -147,6 +161,19 @@ extern "C" int pmcgpu_checkpoint_read(pmcgpu_ctx* ctx, const char* path) {
     }
     CK(pmcgpu_set_particles(ctx, counts.data(), vol.data(), wg.data(), wc.data(), id.data(), np.data(), hy.data(),
                             lct.data(), gct.data()));
+    if (h.cold) {
+      CK(pmcgpu_track_components(ctx, h.n_opq));  // no-op when already enabled with the same width
+      std::vector<int> ncmp(n), src(n * PMC_MAX_COMP);
+      std::vector<double> tim(n * PMC_MAX_COMP), opq(std::max<size_t>(n * h.n_opq, 1));
+      ok = fread(ncmp.data(), sizeof(int), m, f) == m && fread(src.data(), sizeof(int), m * PMC_MAX_COMP, f) == m * PMC_MAX_COMP &&
+           fread(tim.data(), sizeof(double), m * PMC_MAX_COMP, f) == m * PMC_MAX_COMP &&
+           fread(opq.data(), sizeof(double), m * h.n_opq, f) == m * h.n_opq;
+      if (!ok) {
+        fclose(f);
+        return PMCGPU_ERR_ARG;
+      }
+      CK(pmcgpu_set_components(ctx, (long long)m, ncmp.data(), src.data(), tim.data(), opq.data()));
+    }
   }
   const size_t ncg = nc * v.C * v.G;
   CK(get(ctx, f, v.wtype, ncg)); CK(get(ctx, f, v.wmag, ncg)); CK(get(ctx, f, v.wexp, ncg));

@@ -85,6 +85,100 @@ __device__ __forceinline__ void move_record(CellCtx& cx, int dst, int src) {
   if (cx.lane == 3) v.hyst[cx.base + dst] = v.hyst[cx.base + src];
   if (cx.lane == 4) v.lct[cx.base + dst] = v.lct[cx.base + src];
   if (cx.lane == 5) v.gct[cx.base + dst] = v.gct[cx.base + src];
+  if (v.cold.n) cold_copy_warp(v.cold, cx.NS, cx.base + dst, v.cold, cx.NS, cx.base + src, v.n_opq, cx.lane);
+}
+
+// ---- component lists (aero_particle.F90:53-54) held by the lanes of the warp: lane q has component q (q < n).
+// Only the COLD instances of the kernel (pmcgpu_track_components) reach this code.
+struct LaneComp {
+  int n;
+  int src;
+  double time;
+};
+__device__ __forceinline__ LaneComp comp_load(const CellCtx& cx, int slot) {
+  const DevView& v = *cx.v;
+  LaneComp c;
+  c.n = v.cold.n[cx.base + slot];
+  c.src = (cx.lane < c.n) ? v.cold.src[(size_t)cx.lane * cx.NS + cx.base + slot] : 0;
+  c.time = (cx.lane < c.n) ? v.cold.time[(size_t)cx.lane * cx.NS + cx.base + slot] : 0.0;
+  return c;
+}
+// the list of a coagulated particle; its optics are zero until the host recomputes them (aero_particle.F90:920-929)
+__device__ __forceinline__ void comp_store(const CellCtx& cx, int slot, const LaneComp& c) {
+  const DevView& v = *cx.v;
+  if (cx.lane < c.n) {
+    v.cold.src[(size_t)cx.lane * cx.NS + cx.base + slot] = c.src;
+    v.cold.time[(size_t)cx.lane * cx.NS + cx.base + slot] = c.time;
+  }
+  for (int q = cx.lane; q < v.n_opq; q += 32) v.cold.opq[(size_t)q * cx.NS + cx.base + slot] = 0.0;
+  if (cx.lane == 0) v.cold.n[cx.base + slot] = c.n;
+}
+// sample_without_replacement (rand.F90:515-542): the 0-based population index of sample number `want` (0-based),
+// -1 when want is outside the sample; draws key, j0 + t for the t-th member of the population.  Uniform control flow.
+__device__ __noinline__ int swr_pick(int sample_size, int population_size, const RKey& key, unsigned j0, int want) {
+  int t = 0, m = 0, res = -1;
+  while (m < sample_size && t < 64) {
+    const double r = rng_uniform(key, j0 + (unsigned)t);
+    if ((double)(population_size - t) * r >= (double)(sample_size - m)) {
+      t = t + 1;
+    } else {
+      if (m == want) res = t;
+      t = t + 1;
+      m = m + 1;
+    }
+  }
+  return res;
+}
+// aero_particle_coagulate's rule (:955-972): concatenation, or PMC_MAX_COMP components split between the two
+// particles in proportion to their n_primary_parts.  Draws: j0 prob_round, j0 + 1 + t / j0 + 33 + t the two samples.
+__device__ __noinline__ LaneComp comp_merge(const LaneComp& A, int nprim_a, const LaneComp& B, int nprim_b,
+                                            const RKey& key, unsigned j0, int lane) {
+  LaneComp R;
+  int pick_a, pick_b, n_a;
+  if (A.n + B.n <= PMC_MAX_COMP) {
+    n_a = A.n;
+    R.n = A.n + B.n;
+    pick_a = lane;
+    pick_b = lane - A.n;
+  } else {
+    n_a = prob_round((double)nprim_a / (double)(nprim_a + nprim_b) * (double)PMC_MAX_COMP, rng_uniform(key, j0));
+    n_a = min(n_a, A.n);  // holds upstream whenever n_components = min(n_primary_parts, 20)
+    const int n_b = min(PMC_MAX_COMP - n_a, B.n);
+    R.n = n_a + n_b;
+    pick_a = swr_pick(n_a, A.n, key, j0 + 1u, lane);
+    pick_b = swr_pick(n_b, B.n, key, j0 + 33u, lane - n_a);
+  }
+  const int sa = __shfl_sync(0xffffffffu, A.src, pick_a & 31), sb = __shfl_sync(0xffffffffu, B.src, pick_b & 31);
+  const double ta = __shfl_sync(0xffffffffu, A.time, pick_a & 31), tb = __shfl_sync(0xffffffffu, B.time, pick_b & 31);
+  R.src = (lane < n_a) ? sa : sb;
+  R.time = (lane < n_a) ? ta : tb;
+  return R;
+}
+// the averaged source of the accelerated path after its n_primary_parts were rescaled (coagulation.F90:472-508):
+// down to min(n_primary_parts, 20) components by sampling, or up to it by whole copies plus a sample of the rest
+__device__ __noinline__ LaneComp comp_resample(const LaneComp& S, int nprim_new, const RKey& key, int lane) {
+  const int n = S.n, n_new = min(nprim_new, PMC_MAX_COMP);
+  int pick = lane;
+  LaneComp R = S;
+  if (n_new < n) {
+    pick = swr_pick(n_new, n, key, 1u, lane);
+    R.n = n_new;
+  } else if (n < PMC_MAX_COMP && n > 0) {
+    int i_comp = 1, n_whole = 0;
+    while (i_comp + n <= n_new) {
+      n_whole++;
+      i_comp += n;
+    }
+    const int left = (i_comp <= n_new) ? n_new - i_comp + 1 : 0;
+    const int lp = swr_pick(left, n, key, 1u, lane - n_whole * n);
+    pick = (lane < n_whole * n) ? lane % n : lp;
+    R.n = n_whole * n + left;
+  } else {
+    return R;
+  }
+  R.src = __shfl_sync(0xffffffffu, S.src, pick & 31);
+  R.time = __shfl_sync(0xffffffffu, S.time, pick & 31);
+  return R;
 }
 
 // aero_sorted_remove_particle (aero_sorted.F90:455-470): apa swap-with-last +
@@ -167,6 +261,7 @@ __device__ __forceinline__ double unweighted_kernel(int ktype, const BrownEnv& b
 
 // coagulate (coagulation.F90:928-985) + coagulate_weighting (:810-922) for the
 // particles in slots p1, p2 (0-based); warp-cooperative, uniform arguments.
+template <bool COLD>
 __device__ __noinline__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1, int c2, int cc, const RKey& key) {
   const DevView& v = *cx.v;
   double v1, m1, v2, m2;
@@ -213,6 +308,13 @@ __device__ __noinline__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1,
   long long idc = 0;
   int hystc = 0, nprimc = 0;
   double lctc = 0.0, gctc = 0.0;
+  LaneComp compc{0, 0, 0.0};
+  if (COLD && create_new) {
+    RKey ckey = key;
+    ckey.phase = PH_COMP;
+    compc = comp_merge(comp_load(cx, p1), v.nprim[cx.base + p1], comp_load(cx, p2), v.nprim[cx.base + p2], ckey, 0u,
+                       cx.lane);
+  }
   if (create_new) {
 #pragma unroll
     for (int q = 0; q < (PMC_MAX_SPEC + 31) / 32; q++) {
@@ -273,6 +375,7 @@ __device__ __noinline__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1,
       v.gct[cx.base + slot] = gctc;
       v.pbin[cx.base + slot] = b_new;
     }
+    if (COLD) comp_store(cx, slot, compc);
     cx.n_part = slot + 1;
     __syncwarp();
     cell_list_append(cx, cc, b_new, slot);
@@ -417,7 +520,7 @@ __device__ __noinline__ void cell_dup_particle(CellCtx& cx, int p, int c, double
 // evaluate the kernel of 32 candidate samples ahead (their draws are addressed by sample number), the
 // warp then consumes them in order with the running sums held one species per lane; a removal of a
 // source particle invalidates the candidates behind it, which are re-evaluated.
-template <int KT>
+template <int KT, bool COLD>
 __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const BrownEnv& be, double k_max, double del_t, unsigned step,
                                 unsigned pid, int bt, int bs, int ct, int cs, int cc, int& tot_n_samp,
                                 int& tot_n_coag) {
@@ -452,6 +555,9 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
     for (int q = 0; q < NQ; q++) { src_vol[q] = 0.0; vol_sq[q] = 0.0; }
     int src_nprim = 0;
     double src_lct = 0.0, src_gct = 0.0;  // aero_particle_zero
+    LaneComp src_comp{0, 0, 0.0};
+    RKey ckey = skey;
+    ckey.phase = PH_COMP;
     int i_samp = 1;
     bool done = false;
     while (i_samp <= n_samp_total && !done) {
@@ -498,6 +604,9 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
         if (__shfl_sync(0xffffffffu, u_acc, l) < pc) {
           n_avg++;
           const int ip = __shfl_sync(0xffffffffu, i_part, l);
+          if (COLD)
+            src_comp = comp_merge(src_comp, src_nprim, comp_load(cx, ip), v.nprim[cx.base + ip], ckey,
+                                  128u * (unsigned)(i_samp + l), cx.lane);
 #pragma unroll
           for (int q = 0; q < NQ; q++) {
             const int sp = q * 32 + cx.lane;
@@ -531,6 +640,7 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
 #pragma unroll
       for (int q = 0; q < NQ; q++) src_vol[q] = src_vol[q] * f;
       src_nprim = prob_round((double)src_nprim * ((double)n_coag / n_avg), s.next());
+      if (COLD) src_comp = comp_resample(src_comp, src_nprim, ckey, cx.lane);
     }
     if (n_coag > 0) {
       // ---- coag_target_with_source (coagulation.F90:522-582)
@@ -540,6 +650,11 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
       part_vol_mass(cx, tp, v_old, m_old);
       const double old_num_conc_target = awa_nc_at_radius(v, cx.cell, ct, vol2rad(v_old));
       __syncwarp();
+      if (COLD) {
+        const LaneComp merged = comp_merge(comp_load(cx, tp), v.nprim[cx.base + tp], src_comp, src_nprim, ckey, 64u, cx.lane);
+        __syncwarp();
+        comp_store(cx, tp, merged);
+      }
 #pragma unroll
       for (int q = 0; q < NQ; q++) {
         const int sp = q * 32 + cx.lane;
@@ -615,7 +730,7 @@ __device__ __forceinline__ bool pair_advance_exact(int C, int nb, int& c1, int& 
   return true;
 }
 
-template <int KT>
+template <int KT, bool COLD>
 __global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * COAG_WARPS + warp;
@@ -779,7 +894,7 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevV
               const bool pflat = all_flat || (flat[p_c1 - 1] && flat[p_c2 - 1]);
               int bt = 0, bs = 0, ct = 0, cs = 0;
               accel_target_source(cx, pflat, hm, p_b1, pb2, p_c1, p_c2, p_cc, bt, bs, ct, cs);
-              cell_accel_pair<KT>(cx, ktype, be, p_kmax, del_t, step, apid, bt, bs, ct, cs, p_cc, tot_n_samp, tot_n_coag);
+              cell_accel_pair<KT, COLD>(cx, ktype, be, p_kmax, del_t, step, apid, bt, bs, ct, cs, p_cc, tot_n_samp, tot_n_coag);
               rescan = true;  // counts changed: pairs behind this one must be rescanned
               cu_c1 = p_c1; cu_c2 = p_c2; cu_b1 = p_b1; cu_b2 = pb2;
               more = pair_advance_exact(v.C, nb, cu_c1, cu_c2, cu_b1, cu_b2);
@@ -828,7 +943,7 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevV
               const int e1 = __shfl_sync(0xffffffffu, p1, fa);
               const int e2 = __shfl_sync(0xffffffffu, p2, fa);
               const RKey ekey{v.seed, (unsigned)v.gcell[cell], step, PH_COAG, pid, (unsigned)(d + fa)};
-              cell_coagulate(cx, e1, e2, p_c1, p_c2, p_cc, ekey);
+              cell_coagulate<COLD>(cx, e1, e2, p_c1, p_c2, p_cc, ekey);
               tot_n_coag += 1;
               rescan = true;  // counts changed: pairs behind this one must be rescanned
               d = d + fa + 1;
@@ -868,10 +983,12 @@ int pmc_mc_coag_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step) {
   const int blocks = (v.n_cells + COAG_WARPS - 1) / COAG_WARPS;
   {
     ProfScope ps_(ctx, "k_mc_coag");
-    if (ktype == PMCGPU_KERNEL_BROWN)
-      k_mc_coag<PMCGPU_KERNEL_BROWN><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+    if (v.cold.n)  // component lists are tracked (pmcgpu_track_components): the instance that merges them
+      k_mc_coag<0, true><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+    else if (ktype == PMCGPU_KERNEL_BROWN)
+      k_mc_coag<PMCGPU_KERNEL_BROWN, false><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
     else
-      k_mc_coag<0><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+      k_mc_coag<0, false><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
     LAUNCH_CHECK(ctx);
   }
   return PMCGPU_OK;

@@ -211,6 +211,8 @@ __global__ void k_scatter_particles(DevView v, const long long* __restrict__ off
     v.hyst[base + p] = hyst ? hyst[o + p] : 0;
     v.lct[base + p] = lct ? lct[o + p] : 0.0;
     v.gct[base + p] = gct ? gct[o + p] : 0.0;
+    // default cold part: one component {class as source, least_create_time}; pmcgpu_set_components overrides
+    if (v.cold.n) cold_new(v.cold, NS, base + p, c, lct ? lct[o + p] : 0.0, v.n_opq);
   }
   if (threadIdx.x == 0) {
     v.count[cell] = n;

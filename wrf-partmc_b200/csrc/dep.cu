@@ -132,6 +132,7 @@ __global__ void __launch_bounds__(DEP_WARPS * 32) k_dep_dry(DevView v, int nx, i
       v.hyst[base + p] = v.hyst[base + src];
       v.lct[base + p] = v.lct[base + src];
       v.gct[base + p] = v.gct[base + src];
+      if (v.cold.n) cold_copy(v.cold, NS, base + p, v.cold, NS, base + src, v.n_opq);
     }
   }
   if (lane == 0) v.count[cell] = n_cur;

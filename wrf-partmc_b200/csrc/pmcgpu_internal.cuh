@@ -14,7 +14,7 @@
 
 // draw-address phases; must agree with the documented stream layout
 enum : uint32_t {
-  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8, PH_DEP = 9, PH_EMIT = 10, PH_BND = 11
+  PH_COAG = 1, PH_COAG_ACCEL = 2, PH_REWEIGHT = 3, PH_HALVE = 4, PH_DOUBLE = 5, PH_SCALE = 6, PH_TRANS = 7, PH_INIT = 8, PH_DEP = 9, PH_EMIT = 10, PH_BND = 11, PH_COMP = 12
 };
 
 struct PmcConst {  // partmc/src/constants.F90:30-65
@@ -34,6 +34,18 @@ struct PmcConst {  // partmc/src/constants.F90:30-65
   static constexpr double air_std_press = 101325.0;
 };
 
+// Cold part of the particle record (aero_particle.F90:53-61), carried only after pmcgpu_track_components:
+// component(:) = up to PMC_MAX_COMP {source_id, create_time} pairs (MAX_AERO_COMPONENT_SIZE, aero_particle.F90:22)
+// and n_opq opaque doubles per particle (the optical fields absorb / scatter_cross_sect, asymmetry, refract_*,
+// core_vol, which only the host's optics module interprets).  Rows have the stride of the slab they belong to.
+#define PMC_MAX_COMP 20
+struct ColdSlab {
+  int* n;        // [stride] number of components; nullptr = the cold part is not carried
+  int* src;      // [PMC_MAX_COMP][stride]
+  double* time;  // [PMC_MAX_COMP][stride]
+  double* opq;   // [n_opq][stride]
+};
+
 // Device view of one patch: structure-of-arrays particle slabs, one fixed-size
 // slab of `cap` slots per grid cell, so no phase needs a global compaction.
 struct DevView {
@@ -50,6 +62,8 @@ struct DevView {
   double* lct;
   double* gct;
   double* vol_alt; long long* id_alt; int* wgc_alt; int* nprim_alt; int* hyst_alt; double* lct_alt; double* gct_alt;
+  ColdSlab cold, cold_alt;  // stride n_cells*cap; cold.n == nullptr unless pmcgpu_track_components was called
+  int n_opq;
   int* count;         // [n_cells]
   long long* next_id; // [n_cells]
   long long* gcell;   // [n_cells] global cell index
@@ -138,7 +152,39 @@ struct TrSlab {  // SoA particle records crossing one side
   long long* id;
   int* wgc; int* nprim; int* hyst;
   double* lct; double* gct;
+  ColdSlab cold;  // stride cap; cold.n == nullptr when the cold part is not carried
 };
+
+// one record's cold part from slot `src` of slab `from` (row stride sstride) to slot `dst` of slab `to`
+__device__ __forceinline__ void cold_copy(const ColdSlab& to, size_t dstride, size_t dst, const ColdSlab& from,
+                                          size_t sstride, size_t src, int n_opq) {
+  const int n = from.n[src];
+  to.n[dst] = n;
+  for (int q = 0; q < n; q++) {
+    to.src[(size_t)q * dstride + dst] = from.src[(size_t)q * sstride + src];
+    to.time[(size_t)q * dstride + dst] = from.time[(size_t)q * sstride + src];
+  }
+  for (int q = 0; q < n_opq; q++) to.opq[(size_t)q * dstride + dst] = from.opq[(size_t)q * sstride + src];
+}
+// the same by the lanes of a warp (lane q takes component q; PMC_MAX_COMP <= 32)
+__device__ __forceinline__ void cold_copy_warp(const ColdSlab& to, size_t dstride, size_t dst, const ColdSlab& from,
+                                               size_t sstride, size_t src, int n_opq, int lane) {
+  const int n = from.n[src];
+  if (lane < n) {
+    to.src[(size_t)lane * dstride + dst] = from.src[(size_t)lane * sstride + src];
+    to.time[(size_t)lane * dstride + dst] = from.time[(size_t)lane * sstride + src];
+  }
+  for (int q = lane; q < n_opq; q += 32) to.opq[(size_t)q * dstride + dst] = from.opq[(size_t)q * sstride + src];
+  if (lane == 0) to.n[dst] = n;
+}
+// a fresh particle (aero_particle_set_component, aero_particle.F90:169-183; optics zero, :114-124)
+__device__ __forceinline__ void cold_new(const ColdSlab& to, size_t stride, size_t dst, int source, double create_time,
+                                         int n_opq) {
+  to.n[dst] = 1;
+  to.src[dst] = source;
+  to.time[dst] = create_time;
+  for (int q = 0; q < n_opq; q++) to.opq[(size_t)q * stride + dst] = 0.0;
+}
 
 struct ProfEntry {
   const char* name;
@@ -197,8 +243,10 @@ struct pmcgpu_ctx {
 int pmc_exchange_sized(pmcgpu_ctx* ctx, void* const send[4], void* const recv[4], const size_t send_bytes[4],
                        const size_t recv_bytes[4]);
 // bytes of one record in a C4 message and the SoA view of a message buffer with row pitch `pitch`
-static inline size_t tr_rec_bytes(int S) { return (size_t)8 * S + 8 * 3 + 4 * 3; }
-static inline TrSlab tr_slab_view(char* msg, int hdr_ints, int pitch, int S) {
+static inline size_t tr_rec_bytes(int S, bool cold = false, int n_opq = 0) {
+  return (size_t)8 * S + 8 * 3 + 4 * 3 + (cold ? (size_t)8 * (PMC_MAX_COMP + n_opq) + 4 * (1 + PMC_MAX_COMP) + 4 /* pad */ : 0);
+}
+static inline TrSlab tr_slab_view(char* msg, int hdr_ints, int pitch, int S, bool cold = false, int n_opq = 0) {
   TrSlab s;
   s.cap = pitch;
   char* p = msg + (size_t)hdr_ints * sizeof(int);
@@ -208,7 +256,15 @@ static inline TrSlab tr_slab_view(char* msg, int hdr_ints, int pitch, int S) {
   s.gct = (double*)p;       p += (size_t)8 * pitch;
   s.wgc = (int*)p;          p += (size_t)4 * pitch;
   s.nprim = (int*)p;        p += (size_t)4 * pitch;
-  s.hyst = (int*)p;
+  s.hyst = (int*)p;         p += (size_t)4 * pitch;
+  s.cold.n = nullptr; s.cold.src = nullptr; s.cold.time = nullptr; s.cold.opq = nullptr;
+  if (cold) {  // pitch is a multiple of 256: the 8-byte rows stay aligned behind the three 4-byte rows
+    p += (size_t)4 * pitch;  // pad to 8 bytes
+    s.cold.time = (double*)p; p += (size_t)8 * PMC_MAX_COMP * pitch;
+    s.cold.opq = (double*)p;  p += (size_t)8 * n_opq * pitch;
+    s.cold.n = (int*)p;       p += (size_t)4 * pitch;
+    s.cold.src = (int*)p;
+  }
   return s;
 }
 

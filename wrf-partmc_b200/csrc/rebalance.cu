@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_rebalance(DevView v, int all
               v.hyst[base + dst] = v.hyst[base + p];
               v.lct[base + dst] = v.lct[base + p];
               v.gct[base + dst] = v.gct[base + p];
+              if (v.cold.n) cold_copy(v.cold, NS, base + dst, v.cold, NS, base + p, v.n_opq);
             }
             run += __popc(bm);
           }
@@ -120,6 +121,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_rebalance(DevView v, int all
               v.hyst[base + p] = v.hyst[base + src];
               v.lct[base + p] = v.lct[base + src];
               v.gct[base + p] = v.gct[base + src];
+              if (v.cold.n) cold_copy(v.cold, NS, base + p, v.cold, NS, base + src, v.n_opq);
             }
           }
           __syncwarp();
@@ -206,6 +208,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_reweight(DevView v, unsigned
             v.lct[base + ii] = v.lct[base + last];
             v.gct[base + ii] = v.gct[base + last];
           }
+          if (v.cold.n) cold_copy_warp(v.cold, NS, base + ii, v.cold, NS, base + last, v.n_opq, lane);
         }
         n_part = last;
       } else {
@@ -225,6 +228,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_reweight(DevView v, unsigned
             v.lct[base + dst] = v.lct[base + ii];
             v.gct[base + dst] = v.gct[base + ii];
           }
+          if (v.cold.n) cold_copy_warp(v.cold, NS, base + dst, v.cold, NS, base + ii, v.n_opq, lane);
         }
         __syncwarp();
         if (lane == 0) v.next_id[cell] = nx + (nc - 1);
@@ -326,6 +330,7 @@ __device__ void cell_scale_weight(const DevView& v, int cell, int lane, int g, i
         v.hyst[base + p] = v.hyst[base + src];
         v.lct[base + p] = v.lct[base + src];
         v.gct[base + p] = v.gct[base + src];
+        if (v.cold.n) cold_copy(v.cold, NS, base + p, v.cold, NS, base + src, v.n_opq);
       }
     }
     if (lane == 0) v.count[cell] = n_cur;
@@ -362,6 +367,7 @@ __device__ void cell_scale_weight(const DevView& v, int cell, int lane, int g, i
         v.hyst[base + dst] = v.hyst[base + src];
         v.lct[base + dst] = v.lct[base + src];
         v.gct[base + dst] = v.gct[base + src];
+        if (v.cold.n) cold_copy(v.cold, NS, base + dst, v.cold, NS, base + src, v.n_opq);
       }
       n_cur += tot;
       nx += tot;
@@ -554,6 +560,9 @@ __device__ int emit_cell(DevView& v, const EmitDev& e, int cell, int lane, doubl
         v.hyst[base + slot] = 0;
         v.lct[base + slot] = e.create_time;
         v.gct[base + slot] = e.create_time;
+        // aero_particle_set_component (aero_state.F90:823); the source of a mode is its weight class (one class
+        // per source in WRF, aero_state_weight_class_for_source)
+        if (v.cold.n) cold_new(v.cold, NS, base + slot, c, e.create_time, v.n_opq);
       }
       __syncwarp();
       if (lane == 0) {
@@ -824,6 +833,7 @@ __device__ __forceinline__ void bnd_copy_record(DevView& v, size_t NS, size_t to
   if (lane == 3) v.lct[to] = v.lct[from];
   if (lane == 4) v.gct[to] = v.gct[from];
   if (lane == 5) v.pbin[to] = v.pbin[from];
+  if (v.cold.n) cold_copy_warp(v.cold, NS, to, v.cold, NS, from, v.n_opq, lane);
 }
 
 // One warp (= one CTA) per boundary-edge cell.  Shared memory: LST[cap] class lists (positions), FXC[cap]
@@ -955,6 +965,7 @@ __global__ void __launch_bounds__(32) k_bnd_refresh(DevView v, BndDev b, unsigne
             v.hyst[base + slot] = 0;
             v.lct[base + slot] = b.e.create_time;
             v.gct[base + slot] = b.e.create_time;
+            if (v.cold.n) cold_new(v.cold, NS, base + slot, (int)gc / v.G + 1, b.e.create_time, v.n_opq);
             FXC[slot] = -1;  // not in any list of this call
           }
           n_cur += __popc(km);

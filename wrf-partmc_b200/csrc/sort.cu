@@ -341,6 +341,7 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
       v.lct_alt[base + dst] = v.lct[base + p];
       v.gct_alt[base + dst] = v.gct[base + p];
       v.pbin_alt[base + dst] = b;
+      if (v.cold.n) cold_copy(v.cold_alt, NS, base + dst, v.cold, NS, base + p, v.n_opq);
     }
   }
   if (STAGED) {
@@ -362,6 +363,7 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
       v.lct_alt[base + q] = r_lct;
       v.gct_alt[base + q] = r_gct;
       v.pbin_alt[base + q] = r_bin;
+      if (v.cold.n) cold_copy(v.cold_alt, NS, base + q, v.cold, NS, base + src, v.n_opq);
     }
   }
 }
@@ -387,6 +389,7 @@ static void swap_slabs(DevView& v) {
   std::swap(v.lct, v.lct_alt);
   std::swap(v.gct, v.gct_alt);
   std::swap(v.pbin, v.pbin_alt);
+  std::swap(v.cold, v.cold_alt);
 }
 
 // Largest cell the staged variant takes: histograms + n (8 S + 12) bytes must fit the 227 KB of one CTA.

@@ -697,6 +697,7 @@ __global__ void k_tr_pack_copy(DevView v, TransView t, int side, const int* __re
       slab.hyst[dst] = v.hyst_alt[src];
       slab.lct[dst] = v.lct_alt[src];
       slab.gct[dst] = v.gct_alt[src];
+      if (v.cold.n) cold_copy(slab.cold, (size_t)slab.cap, dst, v.cold_alt, NS, src, v.n_opq);
     }
     o += m;
   }
@@ -741,6 +742,7 @@ __global__ void __launch_bounds__(128) k_tr_stage(DevView v, TransView t) {
     v.hyst_alt[dst] = r_hyst;
     v.lct_alt[dst] = r_lct;
     v.gct_alt[dst] = r_gct;
+    if (v.cold.n) cold_copy(v.cold_alt, NS, dst, v.cold, NS, src, v.n_opq);
   }
 }
 struct TrSeg {
@@ -870,6 +872,7 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
       v.hyst[dst] = r_hyst;
       v.lct[dst] = r_lct;
       v.gct[dst] = r_gct;
+      if (v.cold.n) cold_copy(v.cold, NS, dst, v.cold, NS, src, v.n_opq);
     }
   }
   __syncthreads();  // the tail has been read: arrivals may overwrite it
@@ -889,11 +892,13 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
       r_id = sl.id[src]; r_wgc = sl.wgc[src]; r_nprim = sl.nprim[src]; r_hyst = sl.hyst[src];
       r_lct = sl.lct[src]; r_gct = sl.gct[src];
       tr_copy_rows(v.vol + dst, NS, sl.vol + src, (size_t)sl.cap, v.S);
+      if (v.cold.n) cold_copy(v.cold, NS, dst, sl.cold, (size_t)sl.cap, src, v.n_opq);
     } else {
       const size_t src = (size_t)sg.src * v.cap + sg.off + rel;  // entry of the source cell's staged out list
       r_id = v.id_alt[src]; r_wgc = v.wgc_alt[src]; r_nprim = v.nprim_alt[src]; r_hyst = v.hyst_alt[src];
       r_lct = v.lct_alt[src]; r_gct = v.gct_alt[src];
       tr_copy_rows(v.vol + dst, NS, v.vol_alt + src, NS, v.S);
+      if (v.cold.n) cold_copy(v.cold, NS, dst, v.cold_alt, NS, src, v.n_opq);
     }
     v.id[dst] = r_id;
     v.wgc[dst] = r_wgc;
@@ -962,7 +967,7 @@ static int tr_setup(pmcgpu_ctx* ctx) {
     if (const char* e = getenv("PMCGPU_HALO_SLAB_CAP")) slab_cap = std::max(4, atoi(e) & ~3);  // tests: force an overflow
     ctx->slab_cap[s] = slab_cap;
     ctx->hdr_ints[s] = (int)((L * nz + 1 + 3) & ~(size_t)3);
-    const size_t bytes = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)slab_cap * tr_rec_bytes(v.S);
+    const size_t bytes = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)slab_cap * tr_rec_bytes(v.S, v.cold.n != nullptr, v.n_opq);
     TA(ctx->smsg[s], bytes) TA(ctx->rmsg[s], bytes)
     t.soff[s] = (int*)ctx->smsg[s];  // the offsets travel as the header of the particle message
     t.roff[s] = (int*)ctx->rmsg[s];
@@ -1112,12 +1117,12 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
       k_tr_scan<<<1, 1024, 0, st>>>((int)(L * nz), t.scnt[s], t.soff[s]);
       LAUNCH_CHECK(ctx);
       k_tr_pack_copy<<<(unsigned)(L * nz), 128, 0, st>>>(v, t, s, t.soff[s],
-                                                         tr_slab_view(ctx->smsg[s], ctx->hdr_ints[s], pitch_s[s], v.S));
+                                                         tr_slab_view(ctx->smsg[s], ctx->hdr_ints[s], pitch_s[s], v.S, v.cold.n != nullptr, v.n_opq));
       LAUNCH_CHECK(ctx);
       sp[s] = ctx->smsg[s]; rp[s] = ctx->rmsg[s];
-      sby[s] = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)pitch_s[s] * tr_rec_bytes(v.S);
-      rby[s] = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)pitch_r[s] * tr_rec_bytes(v.S);
-      rview[s] = tr_slab_view(ctx->rmsg[s], ctx->hdr_ints[s], pitch_r[s], v.S);
+      sby[s] = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)pitch_s[s] * tr_rec_bytes(v.S, v.cold.n != nullptr, v.n_opq);
+      rby[s] = (size_t)ctx->hdr_ints[s] * sizeof(int) + (size_t)pitch_r[s] * tr_rec_bytes(v.S, v.cold.n != nullptr, v.n_opq);
+      rview[s] = tr_slab_view(ctx->rmsg[s], ctx->hdr_ints[s], pitch_r[s], v.S, v.cold.n != nullptr, v.n_opq);
     }
     if ((rc = pmc_exchange_sized(ctx, sp, rp, sby, rby))) return rc;
     // the counts of this step size the messages of the next one

@@ -472,6 +472,27 @@ class PartMCGPU:
         a.num_conc, a.outflow, a.throw_away = nc.ctypes.data, of.ctypes.data, ta.ctypes.data
         self._chk(self.L.pmcgpu_set_boundary(self.h, C.byref(a)))
 
+    def track_components(self, n_opaque=0):
+        """carry aero_particle_t%component(:) and n_opaque opaque doubles (optics) with every particle record"""
+        self._chk(self.L.pmcgpu_track_components(self.h, C.c_int(n_opaque)))
+        self.n_opaque = int(n_opaque)
+
+    def set_components(self, n_comp, source, create_time, opaque=None):
+        """n_comp [N], source / create_time [N][20], opaque [N][n_opaque], particles in get_particles order"""
+        nc, src, tm = _i32(n_comp), _i32(source), _f64(create_time)
+        oq = _f64(opaque) if opaque is not None else None
+        assert src.size == nc.size * 20 and tm.size == nc.size * 20
+        self._chk(self.L.pmcgpu_set_components(self.h, C.c_longlong(nc.size), _p(nc), _p(src), _p(tm),
+                                               _p(oq) if oq is not None else None))
+
+    def get_components(self):
+        n = int(self.counts().sum())
+        no = getattr(self, "n_opaque", 0)
+        nc, src, tm, oq = np.zeros(n, np.int32), np.zeros((n, 20), np.int32), np.zeros((n, 20)), np.zeros((n, no))
+        self._chk(self.L.pmcgpu_get_components(self.h, C.c_longlong(n), _p(nc), _p(src), _p(tm),
+                                               _p(oq) if no else None))
+        return nc, src, tm, oq
+
     def partmc_process(self, n_bin=100, d_min=1e-9, d_max=1e-3, static=False):
         """per-cell diagnostics of partmc_process (interface/wrf_pmc_driver.F90:826-944), reduced on the device;
         static=True: pmcgpu_partmc_process_static (no allocation, result table in a static device array)"""
