@@ -75,7 +75,14 @@ __device__ __noinline__ double coag_num_conc_factor(const CellCtx& cx, double i_
   return i_nc * j_nc / nc_min;
 }
 
-// move the record of slot `src` into slot `dst` (aero_particle_array.F90:178-200), all lanes
+// the cold part of a record, out of line: the instances without component tracking only carry the call
+__device__ __noinline__ void move_record_cold(const DevView& v, size_t NS, size_t dst, size_t src, int lane) {
+  cold_copy_warp(v.cold, NS, dst, v.cold, NS, src, v.n_opq, lane);
+}
+// move the record of slot `src` into slot `dst` (aero_particle_array.F90:178-200), all lanes.  COLD is a template
+// argument down to here so that the instances without component tracking are the code they were before it existed
+// (mc_coag is bound by instruction fetch: 4 KB more code cost 1.7 ms per K4 step).
+template <bool COLD>
 __device__ __forceinline__ void move_record(CellCtx& cx, int dst, int src) {
   const DevView& v = *cx.v;
   for (int s = cx.lane; s < v.S; s += 32) v.vol[(size_t)s * cx.NS + cx.base + dst] = v.vol[(size_t)s * cx.NS + cx.base + src];
@@ -85,7 +92,7 @@ __device__ __forceinline__ void move_record(CellCtx& cx, int dst, int src) {
   if (cx.lane == 3) v.hyst[cx.base + dst] = v.hyst[cx.base + src];
   if (cx.lane == 4) v.lct[cx.base + dst] = v.lct[cx.base + src];
   if (cx.lane == 5) v.gct[cx.base + dst] = v.gct[cx.base + src];
-  if (v.cold.n) cold_copy_warp(v.cold, cx.NS, cx.base + dst, v.cold, cx.NS, cx.base + src, v.n_opq, cx.lane);
+  if (COLD) move_record_cold(v, cx.NS, cx.base + dst, cx.base + src, cx.lane);
 }
 
 // ---- component lists (aero_particle.F90:53-54) held by the lanes of the warp: lane q has component q (q < n).
@@ -183,6 +190,7 @@ __device__ __noinline__ LaneComp comp_resample(const LaneComp& S, int nprim_new,
 
 // aero_sorted_remove_particle (aero_sorted.F90:455-470): apa swap-with-last +
 // integer_rmap2_remove on size_class.  p is a 0-based slot.
+template <bool COLD>
 __device__ __noinline__ void cell_remove_particle(CellCtx& cx, int p) {
   const DevView& v = *cx.v;
   const int last = cx.n_part - 1;
@@ -207,7 +215,7 @@ __device__ __noinline__ void cell_remove_particle(CellCtx& cx, int p) {
     if (pos_last != pos_old) v.fidx[cx.base + dom_fix] = pos_old;
   }
   __syncwarp();
-  if (last != p) move_record(cx, p, last);
+  if (last != p) move_record<COLD>(cx, p, last);
   cx.n_part = last;
   __syncwarp();
 }
@@ -341,11 +349,11 @@ __device__ __noinline__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1,
   __syncwarp();
   // remove old particles (coagulation.F90:948-970)
   if (p2 > p1) {
-    if (remove_2) cell_remove_particle(cx, p2);
-    if (remove_1) cell_remove_particle(cx, p1);
+    if (remove_2) cell_remove_particle<COLD>(cx, p2);
+    if (remove_1) cell_remove_particle<COLD>(cx, p1);
   } else {
-    if (remove_1) cell_remove_particle(cx, p1);
-    if (remove_2) cell_remove_particle(cx, p2);
+    if (remove_1) cell_remove_particle<COLD>(cx, p1);
+    if (remove_2) cell_remove_particle<COLD>(cx, p2);
   }
   // add new particle, allow_resort = .false. (aero_sorted.F90:397-449)
   if (create_new) {
@@ -476,12 +484,13 @@ __device__ __noinline__ void cell_change_bin(CellCtx& cx, int p, int c, int new_
 }
 
 // aero_state_dup_particle (aero_state.F90:488-539) for the sorted state of mc_coag: slot p of class c
+template <bool COLD>
 __device__ __noinline__ void cell_dup_particle(CellCtx& cx, int p, int c, double n_part_mean, bool random_weight_group,
                                   RStream& s) {
   const DevView& v = *cx.v;
   const int n_copies = prob_round(n_part_mean, s.next());
   if (n_copies == 0) {
-    cell_remove_particle(cx, p);
+    cell_remove_particle<COLD>(cx, p);
     return;
   }
   for (int i_dup = 1; i_dup <= n_copies - 1 && !cx.err; i_dup++) {
@@ -498,7 +507,7 @@ __device__ __noinline__ void cell_dup_particle(CellCtx& cx, int p, int c, double
     const int slot = cx.n_part;
     const int b = v.pbin[cx.base + p];
     __syncwarp();
-    move_record(cx, slot, p);
+    move_record<COLD>(cx, slot, p);
     __syncwarp();
     if (cx.lane == 0) {
       // aero_particle_new_id (aero_particle.F90:141-149) with one counter per cell
@@ -620,7 +629,7 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
           if (i_samp + l <= n_samp_remove) {
             const double prob_remove_i = num_conc_target / __shfl_sync(0xffffffffu, nc_i, l);
             if (__shfl_sync(0xffffffffu, u_rem, l) < prob_remove_i / prob_remove_source_max) {
-              cell_remove_particle(cx, ip);
+              cell_remove_particle<COLD>(cx, ip);
               l++;
               break;  // the source bin changed: candidates behind this one are stale
             }
@@ -679,7 +688,7 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
       }
       cell_change_bin(cx, tp, cc, new_bin);
       const double new_num_conc_target = awa_nc_at_radius(v, cx.cell, cc, r_new);
-      cell_dup_particle(cx, tp, cc, old_num_conc_target / new_num_conc_target, true, s);
+      cell_dup_particle<COLD>(cx, tp, cc, old_num_conc_target / new_num_conc_target, true, s);
     }
     tot_n_samp += n_samp;
     tot_n_coag += n_coag;

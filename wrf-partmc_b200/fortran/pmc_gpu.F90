@@ -16,7 +16,7 @@
 !
 ! Conventions follow the reference's own C boundary (partmc/src/condense.F90:183-195): scalars by value, arrays
 ! through c_loc of a contiguous target, int return code with 0 = success, a non-zero code goes to die_msg
-! (util.F90:134).  What does NOT cross the boundary (DESIGN.md section 2): aero_particle_t%component(:) source
+! (util.F90:134).  What crosses the boundary only with pmc_gpu_track_cold = .true. (DESIGN.md section 2): aero_particle_t%component(:) source
 ! lists and the optical fields (absorb/scatter_cross_sect, asymmetry, refract_*, core_vol) stay on the host
 ! mirror and are zero after pmc_gpu_download_aero_states; gas chemistry, emissions, MOSAIC and optics keep
 ! running on the host (SURVEY.md section 8f).
@@ -50,6 +50,11 @@ module pmc_gpu
   integer(c_int), save :: pmc_gpu_step = 0
   !> The Fortran aero_states array is a mirror: .true. once the device holds the particles.
   logical, save :: pmc_gpu_resident = .false.
+  !> Carry aero_particle_t%component(:) and the optical fields on the device (pmcgpu_track_components): set it
+  !! before pmc_gpu_upload_aero_states.  n_swbands doubles each for absorb / scatter_cross_sect and asymmetry,
+  !! 2 n_swbands each for refract_shell / refract_core, one for core_vol.
+  logical, save, public :: pmc_gpu_track_cold = .false.
+  integer, save :: pmc_gpu_n_swbands = 0
 
 contains
 
@@ -130,7 +135,9 @@ contains
          intent(in) :: env_states
 
     integer :: i, j, k, c, p, n_cells, n_spec, n_class, n_tot, q, i_class
-    integer :: n_lost_comp, n_lost_optics
+    integer :: n_lost_comp, n_lost_optics, n_opaque, n_comp_p, b
+    integer(c_int), allocatable, target :: n_comp(:), comp_src(:,:)
+    real(c_double), allocatable, target :: comp_time(:,:), opaque(:,:)
     integer(c_int), allocatable, target :: counts(:), wgroup(:), wclass(:), nprim(:), hyst(:), wtype(:)
     integer(c_int64_t), allocatable, target :: ids(:)
     real(c_double), allocatable, target :: vol(:,:), lct(:), gct(:), wmag(:), wexp(:)
@@ -156,6 +163,27 @@ contains
          hyst(n_tot), lct(n_tot), gct(n_tot))
     allocate(wtype(n_cells * n_class), wmag(n_cells * n_class), wexp(n_cells * n_class))
     allocate(temp(n_cells), pres(n_cells), rh(n_cells), alt(n_cells), cvol(n_cells))
+    if (pmc_gpu_track_cold) then
+       pmc_gpu_n_swbands = 0
+       if (n_tot > 0) then
+          do j = pmc_js, pmc_je
+          do k = pmc_ks, pmc_ke
+          do i = pmc_is, pmc_ie
+             if (aero_state_n_part(aero_states(i,k,j)) > 0 .and. pmc_gpu_n_swbands == 0) then
+                if (allocated(aero_states(i,k,j)%apa%particle(1)%absorb_cross_sect)) &
+                     pmc_gpu_n_swbands = size(aero_states(i,k,j)%apa%particle(1)%absorb_cross_sect)
+             end if
+          end do
+          end do
+          end do
+       end if
+       n_opaque = 7 * pmc_gpu_n_swbands + 1
+       allocate(n_comp(n_tot), comp_src(20, n_tot), comp_time(20, n_tot), opaque(n_opaque, n_tot))
+       comp_src = 0
+       comp_time = 0d0
+       opaque = 0d0
+       call pmc_gpu_check(pmcgpu_track_components(pmc_gpu_handle, int(n_opaque, c_int)), 'pmcgpu_track_components')
+    end if
     c = 0
     q = 0
     n_lost_comp = 0
@@ -173,6 +201,15 @@ contains
              if (any(aero_states(i,k,j)%apa%particle(p)%absorb_cross_sect /= 0d0) &
                   .or. any(aero_states(i,k,j)%apa%particle(p)%scatter_cross_sect /= 0d0)) &
                   n_lost_optics = n_lost_optics + 1
+          end if
+          if (pmc_gpu_track_cold) then
+             n_comp_p = max(0, aero_particle_n_components(aero_states(i,k,j)%apa%particle(p)))
+             n_comp(q) = n_comp_p
+             do b = 1, n_comp_p
+                comp_src(b, q) = aero_states(i,k,j)%apa%particle(p)%component(b)%source_id
+                comp_time(b, q) = aero_states(i,k,j)%apa%particle(p)%component(b)%create_time
+             end do
+             call pmc_gpu_pack_optics(aero_states(i,k,j)%apa%particle(p), pmc_gpu_n_swbands, opaque(:, q))
           end if
           vol(q, :) = aero_states(i,k,j)%apa%particle(p)%vol     ! species-major: vol(q, s)
           wgroup(q) = aero_states(i,k,j)%apa%particle(p)%weight_group
@@ -198,6 +235,10 @@ contains
     end do
     ! non-fatal, the reference's convention for recoverable conditions (util.F90 warn_assert_msg): the device
     ! state keeps least / greatest_create_time and n_primary_parts, not the per-component source lists and optics
+    if (pmc_gpu_track_cold) then
+       n_lost_comp = 0
+       n_lost_optics = 0
+    end if
     call warn_assert_msg(731204655, n_lost_comp == 0, &
          'pmc_gpu_upload_aero_states: ' // trim(integer_to_string(n_lost_comp)) &
          // ' particles carry more than one aero_component; the device record keeps one (DESIGN.md section 2)')
@@ -207,11 +248,48 @@ contains
     call pmc_gpu_check(pmcgpu_set_particles(pmc_gpu_handle, c_loc(counts), c_loc(vol), &
          c_loc(wgroup), c_loc(wclass), c_loc(ids), c_loc(nprim), c_loc(hyst), c_loc(lct), &
          c_loc(gct)), 'pmcgpu_set_particles')
+    ! the C side is [n_total][20] row-major = (20, n_total) column-major
+    if (pmc_gpu_track_cold) call pmc_gpu_check(pmcgpu_set_components(pmc_gpu_handle, int(n_tot, c_long_long), &
+         c_loc(n_comp), c_loc(comp_src), c_loc(comp_time), c_loc(opaque)), 'pmcgpu_set_components')
     call pmc_gpu_check(pmcgpu_set_weights(pmc_gpu_handle, c_loc(wtype), c_loc(wmag), &
          c_loc(wexp)), 'pmcgpu_set_weights')
     call pmc_gpu_check(pmcgpu_set_env(pmc_gpu_handle, c_loc(temp), c_loc(pres), c_loc(rh), &
          c_loc(alt), c_loc(cvol)), 'pmcgpu_set_env')
   end subroutine pmc_gpu_upload_aero_states
+
+  !> The optical fields of a particle as the opaque blob of the device record and back (aero_particle.F90:38-49).
+  subroutine pmc_gpu_pack_optics(particle, n_sw, blob)
+    use pmc_aero_particle
+    type(aero_particle_t), intent(in) :: particle
+    integer, intent(in) :: n_sw
+    real(c_double), intent(out) :: blob(:)
+    blob = 0d0
+    if (n_sw > 0 .and. allocated(particle%absorb_cross_sect)) then
+       blob(1:n_sw) = particle%absorb_cross_sect
+       blob(n_sw+1:2*n_sw) = particle%scatter_cross_sect
+       blob(2*n_sw+1:3*n_sw) = particle%asymmetry
+       blob(3*n_sw+1:4*n_sw) = real(particle%refract_shell, c_double)
+       blob(4*n_sw+1:5*n_sw) = aimag(particle%refract_shell)
+       blob(5*n_sw+1:6*n_sw) = real(particle%refract_core, c_double)
+       blob(6*n_sw+1:7*n_sw) = aimag(particle%refract_core)
+    end if
+    blob(7*n_sw+1) = particle%core_vol
+  end subroutine pmc_gpu_pack_optics
+
+  subroutine pmc_gpu_unpack_optics(blob, n_sw, particle)
+    use pmc_aero_particle
+    real(c_double), intent(in) :: blob(:)
+    integer, intent(in) :: n_sw
+    type(aero_particle_t), intent(inout) :: particle
+    if (n_sw > 0) then
+       particle%absorb_cross_sect = blob(1:n_sw)
+       particle%scatter_cross_sect = blob(n_sw+1:2*n_sw)
+       particle%asymmetry = blob(2*n_sw+1:3*n_sw)
+       particle%refract_shell = cmplx(blob(3*n_sw+1:4*n_sw), blob(4*n_sw+1:5*n_sw), kind=c_double)
+       particle%refract_core = cmplx(blob(5*n_sw+1:6*n_sw), blob(6*n_sw+1:7*n_sw), kind=c_double)
+    end if
+    particle%core_vol = blob(7*n_sw+1)
+  end subroutine pmc_gpu_unpack_optics
 
   !> Device SoA -> aero_states(i,k,j): refresh of the Fortran mirror when a WRF history or
   !! restart alarm needs it (partmc_before_solve_io, wrf_pmc_driver.F90:369-384).
@@ -230,6 +308,9 @@ contains
     integer(c_int64_t), allocatable, target :: ids(:)
     real(c_double), allocatable, target :: vol(:,:), lct(:), gct(:), wmag(:), wexp(:)
     type(aero_particle_t) :: particle
+    integer :: n_opaque, b
+    integer(c_int), allocatable, target :: n_comp(:), comp_src(:,:)
+    real(c_double), allocatable, target :: comp_time(:,:), opaque(:,:)
 
     n_cells = size(aero_states)
     n_spec = aero_data_n_spec(aero_data)
@@ -245,6 +326,12 @@ contains
          c_loc(gct)), 'pmcgpu_get_particles')
     call pmc_gpu_check(pmcgpu_get_weights(pmc_gpu_handle, c_loc(wtype), c_loc(wmag), &
          c_loc(wexp)), 'pmcgpu_get_weights')
+    if (pmc_gpu_track_cold) then
+       n_opaque = 7 * pmc_gpu_n_swbands + 1
+       allocate(n_comp(n_tot), comp_src(20, n_tot), comp_time(20, n_tot), opaque(n_opaque, n_tot))
+       call pmc_gpu_check(pmcgpu_get_components(pmc_gpu_handle, int(n_tot, c_long_long), c_loc(n_comp), &
+            c_loc(comp_src), c_loc(comp_time), c_loc(opaque)), 'pmcgpu_get_components')
+    end if
     c = 0
     q = 0
     do j = pmc_js, pmc_je
@@ -266,6 +353,18 @@ contains
           particle%water_hyst_leg = hyst(q)
           particle%least_create_time = lct(q)
           particle%greatest_create_time = gct(q)
+          if (pmc_gpu_track_cold) then
+             if (allocated(particle%component)) deallocate(particle%component)
+             allocate(particle%component(n_comp(q)))
+             do b = 1, n_comp(q)
+                particle%component(b)%source_id = comp_src(b, q)
+                particle%component(b)%create_time = comp_time(b, q)
+             end do
+             call pmc_gpu_unpack_optics(opaque(:, q), pmc_gpu_n_swbands, particle)
+          else
+             ! one component: the weight class as source (one class per source in WRF), least_create_time
+             call aero_particle_set_component(particle, wclass(q), lct(q))
+          end if
           call aero_state_add_particle(aero_states(i,k,j), particle, aero_data, &
                allow_resort=.false.)
        end do
