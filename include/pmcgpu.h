@@ -113,6 +113,10 @@ int pmcgpu_set_components(pmcgpu_ctx* ctx, long long n_total, const int* n_comp,
                           const double* create_time, const double* opaque);
 int pmcgpu_get_components(pmcgpu_ctx* ctx, long long n_total, int* n_comp, int* source, double* create_time,
                           double* opaque);
+/* aero_state_num_concs_by_source (aero_state.F90:1310-1347) for every cell: out [n_cells][n_source] (host or device),
+ * sources 1..n_source; every component credits its source with num_conc * (n_primary_parts / n_components), the
+ * quotient being the Fortran's integer division.  Needs pmcgpu_track_components. */
+int pmcgpu_num_concs_by_source(pmcgpu_ctx* ctx, int n_source, double* out);
 /* per-cell id counters (aero_particle.F90:64 next_id, one per cell on the device) */
 int pmcgpu_set_next_id(pmcgpu_ctx* ctx, const int64_t* next_id);
 int pmcgpu_get_next_id(pmcgpu_ctx* ctx, int64_t* next_id);

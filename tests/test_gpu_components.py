@@ -91,6 +91,26 @@ def test_default_components_and_round_trip(mods):
     assert np.array_equal(nc3, nc2[perm]) and np.array_equal(src3, src2[perm]) and np.array_equal(opq3, opq2[perm])
 
 
+def test_num_concs_by_source(mods):
+    """aero_state_num_concs_by_source (aero_state.F90:1310-1347), integer quotient n_primary_parts / n_components kept"""
+    W, O = mods
+    case = common.make_cells(5, 150, n_spec=2, n_class=2, seed=4)
+    comps = random_components(case, 11, 0, max_comp=5)
+    case["n_primary"] = (comps[0] * 2 + 1).astype(np.int32)  # quotient 2 except for one component (3)
+    g, _ = upload(W, O, case, comps, 0)
+    got = g.num_concs_by_source(8)
+    nc, src, tm, _ = comps
+    off = np.concatenate([[0], np.cumsum(case["counts"])])
+    want = np.zeros((5, 8))
+    for c in range(5):
+        for p in range(off[c], off[c + 1]):
+            num_conc = case["wmag"][c, case["wclass"][p] - 1, 0]
+            for q in range(nc[p]):
+                want[c, src[p, q] - 1] += num_conc * (case["n_primary"][p] // nc[p])
+    np.testing.assert_allclose(got, want, rtol=1e-14)
+    assert want[3].sum() == 0 and got[3].sum() == 0 and want.sum() > 0
+
+
 @pytest.mark.parametrize("weight,n_class,n_group,dt,accel", [("flat", 1, 1, 3600.0, False), ("flat", 2, 1, 7200.0, True),
                                                               ("nummass", 1, 2, 3600.0, True)])
 def test_coagulation_merges_component_lists(mods, weight, n_class, n_group, dt, accel):

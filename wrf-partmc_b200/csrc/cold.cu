@@ -151,3 +151,47 @@ extern "C" int pmcgpu_get_components(pmcgpu_ctx* ctx, long long n_total, int* n_
   if (!ctx) return PMCGPU_ERR_ARG;
   return cold_xfer(ctx, n_total, 1, n_comp, source, create_time, opaque);
 }
+
+// aero_state_num_concs_by_source (aero_state.F90:1310-1347): every component of a particle credits its source with
+// num_conc * (n_primary_parts / n_components) -- an INTEGER quotient in the Fortran, kept.  One thread per
+// (cell, source) walks the particles and their components in order, so the sums are the reference's, term by term.
+__global__ void k_num_concs_by_source(DevView v, int n_source, double* __restrict__ out) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= v.n_cells * n_source) return;
+  const int cell = q / n_source, source = q % n_source + 1;
+  const size_t base = (size_t)cell * v.cap, NS = (size_t)v.n_cells * v.cap;
+  const int n = v.count[cell];
+  double acc = 0.0;
+  for (int p = 0; p < n; p++) {
+    const int nc = v.cold.n[base + p];
+    if (nc <= 0) continue;
+    double vt = 0.0;
+    bool hit = false;
+    for (int k = 0; k < nc; k++) hit = hit || (v.cold.src[(size_t)k * NS + base + p] == source);
+    if (!hit) continue;
+    for (int s = 0; s < v.S; s++) vt += v.vol[(size_t)s * NS + base + p];
+    const double num_conc = awa_nc_at_radius(v, cell, v.wgc[base + p] / v.G + 1, vol2rad(vt));
+    const double term = num_conc * (double)(v.nprim[base + p] / nc);
+    for (int k = 0; k < nc; k++)
+      if (v.cold.src[(size_t)k * NS + base + p] == source) acc = acc + term;
+  }
+  out[q] = acc;
+}
+
+extern "C" int pmcgpu_num_concs_by_source(pmcgpu_ctx* ctx, int n_source, double* out) {
+  if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
+  if (!ctx || n_source < 1 || !out) return PMCGPU_ERR_ARG;
+  DevView& v = ctx->v;
+  if (!v.cold.n) {
+    ctx->err = "components are not tracked: call pmcgpu_track_components first";
+    return PMCGPU_ERR_ARG;
+  }
+  const size_t n = (size_t)v.n_cells * n_source;
+  TmpDev<double> d;
+  CUDA_OK(ctx, d.alloc(n));
+  k_num_concs_by_source<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(v, n_source, d.p);
+  LAUNCH_CHECK(ctx);
+  CUDA_OK(ctx, cudaMemcpyAsync(out, d.p, n * sizeof(double), cudaMemcpyDefault, ctx->stream));
+  CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}

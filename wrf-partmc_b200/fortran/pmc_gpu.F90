@@ -16,9 +16,10 @@
 !
 ! Conventions follow the reference's own C boundary (partmc/src/condense.F90:183-195): scalars by value, arrays
 ! through c_loc of a contiguous target, int return code with 0 = success, a non-zero code goes to die_msg
-! (util.F90:134).  What crosses the boundary only with pmc_gpu_track_cold = .true. (DESIGN.md section 2): aero_particle_t%component(:) source
-! lists and the optical fields (absorb/scatter_cross_sect, asymmetry, refract_*, core_vol) stay on the host
-! mirror and are zero after pmc_gpu_download_aero_states; gas chemistry, emissions, MOSAIC and optics keep
+! (util.F90:134).  The cold part of the record (DESIGN.md section 2) -- aero_particle_t%component(:) source lists and
+! the optical fields (absorb/scatter_cross_sect, asymmetry, refract_*, core_vol) -- crosses the boundary only with
+! pmc_gpu_track_cold = .true.; otherwise the downloaded mirror has one component per particle and zero optics and the
+! upload reports how many particles that concerns.  Gas chemistry, emissions, MOSAIC and optics keep
 ! running on the host (SURVEY.md section 8f).
 !
 ! NOTE: no Fortran compiler exists in the build image of this repository (gfortran, flang, nvfortran, ifx all

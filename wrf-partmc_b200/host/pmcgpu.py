@@ -493,6 +493,12 @@ class PartMCGPU:
                                                _p(oq) if no else None))
         return nc, src, tm, oq
 
+    def num_concs_by_source(self, n_source):
+        """aero_state_num_concs_by_source (aero_state.F90:1310) per cell: [n_cells][n_source]"""
+        out = np.zeros((self.n_cells, n_source))
+        self._chk(self.L.pmcgpu_num_concs_by_source(self.h, C.c_int(n_source), _p(out)))
+        return out
+
     def partmc_process(self, n_bin=100, d_min=1e-9, d_max=1e-3, static=False):
         """per-cell diagnostics of partmc_process (interface/wrf_pmc_driver.F90:826-944), reduced on the device;
         static=True: pmcgpu_partmc_process_static (no allocation, result table in a static device array)"""
