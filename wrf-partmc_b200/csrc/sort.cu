@@ -54,14 +54,16 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
 // the permutation are computed from there and the records leave in destination order with coalesced stores,
 // so HBM sees each record once in and once out.  Handles the cells with n <= n_split; the legacy variant
 // (rows read twice, scattered stores) takes the cells with n > n_split (n_split = -1: every cell).
+// s_st: how many of the S species rows the staged variant keeps in shared memory (the first s_st); the others are
+// streamed from HBM for the radius and gathered from the cell's own, just-read rows when the records leave.
 template <bool STAGED, int NT>
-__global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, int n_split) {
+__global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, int n_split, int s_st, int n_lo) {
   constexpr int SORT_WARPS = NT / 32;
   constexpr int SORT_THREADS_ = NT;
   const int cell = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = v.count[cell];
-  if (STAGED ? (n > n_split) : (n <= n_split)) return;
+  if (STAGED ? (n > n_split || n <= n_lo) : (n <= n_split)) return;  // staged: cells with n_lo < n <= n_split
   if (edge_recheck == 3) {  // grid decision only, interior cells of an open domain only (wrf_pmc_trans_aero.F90:777-804)
     if (cell_is_boundary(v, cell)) return;
     edge_recheck = 2;
@@ -79,16 +81,16 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
   // staged layout after the histograms: vol rows [S][n2], ln r [n2] (later the inverse permutation), key [n2]
   const int n2 = (n + 1) & ~1;  // rows are copied in 16-byte units
   double* svol = (double*)(s_hist + (((SORT_WARPS + 1) * v.C * v.nbcap + 3) & ~3));
-  double* s_lnr = svol + (size_t)v.S * n2;
+  double* s_lnr = svol + (size_t)s_st * n2;
   int* s_src = (int*)s_lnr;
   int* s_key = (int*)(s_lnr + n2);
   if (STAGED) {
     if (tid == 0) mbar_init(&s_bar, 1);
     __syncthreads();
-    if (n > 0) {
+    if (n > 0 && s_st > 0) {
       if (tid == 0) {
-        mbar_expect_tx(&s_bar, (unsigned)((size_t)v.S * n2 * sizeof(double)));
-        for (int s = 0; s < v.S; s++)
+        mbar_expect_tx(&s_bar, (unsigned)((size_t)s_st * n2 * sizeof(double)));
+        for (int s = 0; s < s_st; s++)
           bulk_g2s(svol + (size_t)s * n2, v.vol + (size_t)s * NS + base, (unsigned)(n2 * sizeof(double)), &s_bar);
       }
       mbar_wait(&s_bar, 0);
@@ -100,7 +102,9 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
   for (int p = tid; p < n; p += SORT_THREADS_) {
     double vt = 0.0;
     if (STAGED) {
-      for (int s = 0; s < v.S; s++) vt += svol[(size_t)s * n2 + p];
+      // rows below s_st from shared memory, the others straight from HBM (same order of the additions)
+      for (int s = 0; s < s_st; s++) vt += svol[(size_t)s * n2 + p];
+      for (int s = s_st; s < v.S; s++) vt += v.vol[(size_t)s * NS + base + p];
     } else {
       for (int s = 0; s < v.S; s++) vt += v.vol[(size_t)s * NS + base + p];  // aero_particle_volume
     }
@@ -355,7 +359,16 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
       const double r_lct = v.lct[base + src], r_gct = v.gct[base + src];
       const int r_bin = s_key[src] % nb + 1;
 #pragma unroll 4
-      for (int s = 0; s < v.S; s++) v.vol_alt[(size_t)s * NS + base + q] = svol[(size_t)s * n2 + src];
+      for (int s = 0; s < s_st; s++) v.vol_alt[(size_t)s * NS + base + q] = svol[(size_t)s * n2 + src];
+      // the unstaged rows: gathered from the cell's own rows, which this CTA has just streamed (cache hits)
+      for (int s = s_st; s < v.S; s += 4) {
+        double a[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) a[u] = (s + u < v.S) ? v.vol[(size_t)(s + u) * NS + base + src] : 0.0;
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (s + u < v.S) v.vol_alt[(size_t)(s + u) * NS + base + q] = a[u];
+      }
       v.id_alt[base + q] = r_id;
       v.wgc_alt[base + q] = r_wgc;
       v.nprim_alt[base + q] = r_nprim;
@@ -376,7 +389,7 @@ int pmc_sort_grid_only_async(pmcgpu_ctx* ctx, int interior_only) {
   DevView& v = ctx->v;
   const size_t smem = (size_t)(SORT_THREADS / 32 + 1) * v.C * v.nbcap * sizeof(int);
   ProfScope ps_(ctx, "k_sort_cells_grid");
-  k_sort_cells<false, SORT_THREADS><<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, interior_only == 1 ? 3 : (interior_only == 2 ? 4 : 2), -1);
+  k_sort_cells<false, SORT_THREADS><<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, interior_only == 1 ? 3 : (interior_only == 2 ? 4 : 2), -1, 0, -1);
   LAUNCH_CHECK(ctx);
   return PMCGPU_OK;
 }
@@ -394,10 +407,9 @@ static void swap_slabs(DevView& v) {
 
 // Largest cell the staged variant takes: histograms + n (8 S + 12) bytes must fit the 227 KB of one CTA.
 // PMCGPU_SORT_STAGED_MAX (environment) lowers it (0: legacy variant only) -- used by the tests to reach both.
-static int sort_staged_limit(const DevView& v, size_t* smem_out) {
+static int sort_staged_limit(const DevView& v, size_t* smem_out, int s_st, size_t budget) {
   const size_t hist = ((size_t)(SORT_THREADS_STAGED / 32 + 1) * v.C * v.nbcap + 3) / 4 * 16;
-  const size_t budget = 224 * 1024;
-  const size_t per = 8 * (size_t)v.S + 12;
+  const size_t per = 8 * (size_t)s_st + 12;
   *smem_out = 0;
   if ((v.cap & 1) || hist + 64 * per > budget) return -1;  // rows must start on 16-byte boundaries
   long long nmax = (long long)((budget - hist) / per) & ~1LL;
@@ -423,22 +435,40 @@ int pmc_sort_async(pmcgpu_ctx* ctx, int edge_recheck) {
                                       (int)smem));
     ctx->cfg_sort_smem = smem;
   }
-  size_t smem_staged = 0;
-  const int n_split = sort_staged_limit(v, &smem_staged);
-  if (n_split > 0 && smem_staged > 48 * 1024 && smem_staged > ctx->cfg_sort_staged_smem) {
+  // Staged rows and shared memory per CTA: 4 rows in <= 56 KB, i.e. 4 CTAs of 512 threads per SM whose load, compute
+  // and store phases overlap (measured on K4, S = 20: 3.08 ms; all 20 rows in 224 KB = one CTA per SM: 3.51 ms;
+  // 10 rows / 112 KB 3.21; 2 rows / 50 KB 3.31; none 3.20 -- profiles/r02_sort_staging_sweep.txt).
+  // PMCGPU_SORT_STAGED_ROWS / PMCGPU_SORT_SMEM_KB (environment) override for measurements.
+  size_t smem_small = 0, smem_big = 0;
+  int s_st = std::min(v.S, 4);
+  size_t budget = 56 * 1024;
+  if (const char* e = getenv("PMCGPU_SORT_STAGED_ROWS")) s_st = std::max(0, std::min(v.S, atoi(e)));
+  if (const char* e = getenv("PMCGPU_SORT_SMEM_KB")) budget = (size_t)std::max(16, std::min(224, atoi(e))) * 1024;
+  // two staged launches: cells that fit the small budget (several CTAs per SM), then the larger ones with up to
+  // 224 KB (one CTA per SM); what is larger still takes the legacy variant
+  const int n_small = sort_staged_limit(v, &smem_small, s_st, budget);
+  const int n_big = (n_small > 0 && n_small < v.cap) ? sort_staged_limit(v, &smem_big, s_st, 224 * 1024) : n_small;
+  const int n_split = std::max(n_small, n_big);
+  const size_t smem_max = std::max(smem_small, smem_big);
+  if (n_split > 0 && smem_max > 48 * 1024 && smem_max > ctx->cfg_sort_staged_smem) {
     CUDA_OK(ctx, cudaFuncSetAttribute(k_sort_cells<true, SORT_THREADS_STAGED>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_staged));
-    ctx->cfg_sort_staged_smem = smem_staged;
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+    ctx->cfg_sort_staged_smem = smem_max;
   }
   {
     ProfScope ps_(ctx, "k_sort_cells");
-    if (n_split > 0) {
+    if (n_small > 0) {
       k_sort_cells<true, SORT_THREADS_STAGED>
-          <<<v.n_cells, SORT_THREADS_STAGED, smem_staged, ctx->stream>>>(v, edge_recheck, n_split);
+          <<<v.n_cells, SORT_THREADS_STAGED, smem_small, ctx->stream>>>(v, edge_recheck, n_small, s_st, -1);
+      LAUNCH_CHECK(ctx);
+    }
+    if (n_big > n_small) {
+      k_sort_cells<true, SORT_THREADS_STAGED>
+          <<<v.n_cells, SORT_THREADS_STAGED, smem_big, ctx->stream>>>(v, edge_recheck, n_big, s_st, n_small);
       LAUNCH_CHECK(ctx);
     }
     if (n_split < v.cap) {
-      k_sort_cells<false, SORT_THREADS><<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, edge_recheck, n_split);
+      k_sort_cells<false, SORT_THREADS><<<v.n_cells, SORT_THREADS, smem, ctx->stream>>>(v, edge_recheck, n_split, 0, -1);
       LAUNCH_CHECK(ctx);
     }
   }
