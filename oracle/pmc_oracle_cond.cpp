@@ -213,7 +213,7 @@ struct CondSys {
       in.V_comp = 1.0;
       in.kappa = 0.0;
       condense_rates(in, out);
-      if (dfdt) {
+      if (dfdtH) {  // (not `dfdt`: the per-particle array of an empty cell is a null pointer)
         double d0, h0;
         condense_rates_dt(in, d0, h0, env_t);
       }

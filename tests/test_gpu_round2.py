@@ -364,3 +364,26 @@ def test_bidisperse_on_device_against_ode(mods):
     assert err.max() < 0.3, err
     assert part[-1, 1] < 0.5 * part[0, 1]
     assert g.get_particles()["vol"].sum() == pytest.approx(case["vol"].sum(), rel=1e-12)
+
+
+def test_empty_cell_relative_humidity_closed_form(mods):
+    """condense_particles in a cell without particles (the smoke case has one): device, oracle and the closed form
+    H0 exp(int (-dlnP0/dT Tdot + pdot / p) dt) of Hdot_env (condense.F90:446-449) agree"""
+    from scipy.integrate import quad
+    W, O = mods
+    case = common.make_cells(n_cells=4, n_per_cell=50, n_spec=3, n_class=1, seed=2)  # cell 3 is empty
+    assert case["counts"][3] == 0
+    g = common.gpu_from_case(W, case)
+    o = common.oracle_from_case(O, case)
+    T1, P1 = case["T"] - 0.2, case["P"] - 200.0
+    rh, st, _ = g.condense_particles(T1, P1, 600.0, step=1)
+    o.condense_particles(3, T1[3], P1[3], 600.0, step=1)
+    T0, p0, Td, pd = case["T"][3], case["P"][3], -0.2 / 600.0, -200.0 / 600.0
+
+    def lam(t):
+        T, p = T0 + t * Td, p0 + t * pd
+        return -7.45 * np.log(10.0) * (273.15 - 38.0) / (T - 38.0) ** 2 * Td + pd / p
+
+    exact = 0.5 * np.exp(quad(lam, 0.0, 600.0, epsabs=1e-16, epsrel=1e-13)[0])
+    assert abs(rh[3] / exact - 1.0) < 1e-12 and st[3, 0] <= 6
+    assert abs(o.env_rel_humid(3) / rh[3] - 1.0) < 1e-13

@@ -110,3 +110,21 @@ def test_condense_golden_rel_humid():
     errw = np.linalg.norm(np.array(water) - gw) / np.linalg.norm(gw)
     assert errw < 0.05, errw
     assert wre_max < 1e-6  # condense.F90:317 water-balance bound
+
+
+def test_empty_cell_relative_humidity_closed_form():
+    """A cell without particles: dH/dt = H (-dlnP0/dT Tdot + pdot / p) (condense.F90:446-449, Hdot_env) has the closed
+    form H0 exp(int lambda dt); the integrator (with the d/dt term of the non-autonomous Rosenbrock stages) must
+    reproduce it far below the tolerance, in a handful of steps."""
+    from scipy.integrate import quad
+    from oracle import oracle as O
+    T0, p0, Td, pd = 288.0, 1e5, -0.2 / 600.0, -200.0 / 600.0
+
+    def lam(t):
+        T, p = T0 + t * Td, p0 + t * pd
+        return -7.45 * np.log(10.0) * (273.15 - 38.0) / (T - 38.0) ** 2 * Td + pd / p
+
+    exact = 0.5 * np.exp(quad(lam, 0.0, 600.0, epsabs=1e-16, epsrel=1e-13)[0])
+    e = np.zeros(0)
+    rc, _, H, st = O.condense_integrate(e, 0.5, e, e, e, T0, p0, Td, pd, 600.0)
+    assert rc == 0 and abs(H / exact - 1.0) < 1e-12 and st[0] <= 6, (H, exact, st)
