@@ -159,7 +159,7 @@ int pmcgpu_aero_state_scale_weight(pmcgpu_ctx* ctx, int i_group, int i_class, co
  * and volume fractions from aero_mode_sample_vols (:633).  All pointers host or device. */
 typedef struct {
   int n_mode;
-  const int* mode_type;         /* [n_mode] 1 log-normal, 2 exponential, 3 mono-disperse (aero_mode.F90:26-34) */
+  const int* mode_type;         /* [n_mode] 1 log-normal, 2 exponential, 3 mono-disperse, 4 sampled (aero_mode.F90:26-37) */
   const int* weight_class;      /* [n_mode] weight class of the mode's source, 1-based */
   const double* char_radius;    /* [n_mode] geometric mean / mean-volume / mono radius (m) */
   const double* log10_std_dev;  /* [n_mode] log10 of the geometric standard deviation (log-normal modes) */
@@ -173,6 +173,13 @@ typedef struct {
   unsigned int step;            /* addresses the random draws */
   unsigned int stream;          /* added to the (group, mode) part of the draw address: 0 for scenario emissions; callers
                                    that sample in the same cells in the same step use different values (sea salt: 1024) */
+  /* sampled (tabulated) modes, mode_type 4 (aero_mode.F90:456-491, 533-538, 581-608): every mode has a row of
+   * n_sample_bins + 1 bin-edge radii (m) and n_sample_bins number concentrations (m^-3) (rows of other mode types are
+   * ignored; all pointers may be NULL / 0 when no mode is sampled); num_conc[cell][mode] of a sampled mode is a
+   * dimensionless factor on its table (1 = as tabulated) */
+  int n_sample_bins;
+  const double* sample_radius;    /* [n_mode][n_sample_bins + 1] */
+  const double* sample_num_conc;  /* [n_mode][n_sample_bins] */
 } pmcgpu_emit_args;
 int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmcgpu_emit_args* args, int* n_part_add /* [n_cells] or NULL */);
 

@@ -317,8 +317,9 @@ class Oracle:
 
     def add_aero_dist_sample(self, cell, mode_type, weight_class, char_radius, log10_std_dev, vol_frac, num_conc,
                              sample_prop, characteristic_factor, create_time=0.0, vol_frac_std=None,
-                             allow_doubling=True, allow_halving=True, step=0):
-        """aero_state_add_aero_dist_sample (aero_state.F90:758) for one cell; num_conc [n_mode]"""
+                             allow_doubling=True, allow_halving=True, step=0, sample_radius=None, sample_num_conc=None):
+        """aero_state_add_aero_dist_sample (aero_state.F90:758) for one cell; num_conc [n_mode]; sampled modes
+        (type 4): sample_radius [n_mode][nb + 1], sample_num_conc [n_mode][nb]"""
         ty, wc = _i32(mode_type), _i32(weight_class)
         cr, ls, vf, nc = _f64(char_radius), _f64(log10_std_dev), _f64(vol_frac), _f64(num_conc)
         vs = _f64(vol_frac_std) if vol_frac_std is not None else None
@@ -327,7 +328,10 @@ class Oracle:
             self.h, C.c_int(cell), C.c_int(ty.size), _p(ty, C.c_int), _p(wc, C.c_int), _p(cr, C.c_double),
             _p(ls, C.c_double), _p(vf, C.c_double), _p(vs, C.c_double) if vs is not None else None,
             _p(nc, C.c_double), C.c_double(sample_prop), C.c_double(characteristic_factor), C.c_double(create_time),
-            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step), C.byref(n)))
+            C.c_int(int(allow_doubling)), C.c_int(int(allow_halving)), C.c_uint(step), C.byref(n),
+            C.c_int(0 if sample_num_conc is None else _f64(sample_num_conc).size // ty.size),
+            _p(_f64(sample_radius), C.c_double) if sample_radius is not None else None,
+            _p(_f64(sample_num_conc), C.c_double) if sample_num_conc is not None else None))
         return n.value
 
     def seasalt_emissions(self, nx, nz, ny, u10, v10, xland, height, sea_salt_opt, i_na, i_cl, weight_class, dt,

@@ -18,8 +18,26 @@
 
 namespace pmco {
 
+// aero_mode_weighted_sampled_num_conc (aero_mode.F90:456-491)
+static std::vector<double> weighted_sampled_num_conc(const AeroMode& m, const Weight& w) {
+  std::vector<double> out(m.sample_num_conc.size());
+  for (size_t i = 0; i < out.size(); i++) {
+    if (w.type == WEIGHT_NONE) {
+      out[i] = m.sample_num_conc[i];
+    } else {
+      const double x0 = std::log(m.sample_radius[i]), x1 = std::log(m.sample_radius[i + 1]);
+      out[i] = m.sample_num_conc[i] / w.exponent * (std::exp(-w.exponent * x0) - std::exp(-w.exponent * x1)) / (x1 - x0);
+    }
+  }
+  return out;
+}
 // aero_mode.F90:496-544
 static double aero_mode_number(const AeroMode& m, const Weight& w) {
+  if (m.type == MODE_SAMPLED) {  // :533-538
+    double sum = 0.0;
+    for (double x : weighted_sampled_num_conc(m, w)) sum = sum + x;
+    return m.num_conc * (sum / w.magnitude);
+  }
   if (m.type == MODE_LOG_NORMAL) {
     if (w.type == WEIGHT_NONE) return m.num_conc / w.magnitude;
     const double x_mean_prime =
@@ -52,6 +70,19 @@ static double rand_normal_threshold(double mean, double stddev, double prob_thre
 
 // aero_mode.F90:549-628
 double aero_mode_sample_radius(const AeroMode& m, const Weight& w, double prob_threshold, Stream& s) {
+  if (m.type == MODE_SAMPLED) {  // :581-608
+    const std::vector<double> pdf = weighted_sampled_num_conc(m, w);
+    const int i_sample = sample_cts_pdf(pdf, s);
+    const double r = s.next();
+    if (w.type == WEIGHT_NONE || w.exponent == 0.0) {
+      const double x0 = std::log(m.sample_radius[i_sample - 1]), x1 = std::log(m.sample_radius[i_sample]);
+      return std::exp((1.0 - r) * x0 + r * x1);
+    }
+    const double inv_nc0 = 1.0 / weight_num_conc_at_radius(w, m.sample_radius[i_sample - 1]);
+    const double inv_nc1 = 1.0 / weight_num_conc_at_radius(w, m.sample_radius[i_sample]);
+    const double inv_nc = (1.0 - r) * inv_nc0 + r * inv_nc1;
+    return std::exp(std::log((1.0 / inv_nc) / w.magnitude) / w.exponent);  // aero_weight_radius_at_num_conc
+  }
   if (m.type == MODE_LOG_NORMAL) {
     double x_mean_prime = std::log10(m.char_radius);
     if (w.type != WEIGHT_NONE)
@@ -207,7 +238,8 @@ int pmco_add_aero_dist_sample(void* h, int cell, int n_mode, const int* type, co
                               const double* char_radius, const double* log10_std, const double* vol_frac,
                               const double* vol_frac_std, const double* num_conc, double sample_prop,
                               double characteristic_factor, double create_time, int allow_doubling,
-                              int allow_halving, unsigned step, int* n_part_add) {
+                              int allow_halving, unsigned step, int* n_part_add, int n_sample_bins,
+                              const double* sample_radius, const double* sample_num_conc) {
   OracleDomain* D = (OracleDomain*)h;
   ORACLE_TRY
   const int S = D->data.n_spec;
@@ -218,6 +250,12 @@ int pmco_add_aero_dist_sample(void* h, int cell, int n_mode, const int* type, co
     modes[m].char_radius = char_radius[m];
     modes[m].log10_std_dev_radius = log10_std[m];
     modes[m].num_conc = num_conc[m];
+    if (type[m] == MODE_SAMPLED) {
+      modes[m].sample_radius.assign(sample_radius + (size_t)m * (n_sample_bins + 1),
+                                    sample_radius + (size_t)(m + 1) * (n_sample_bins + 1));
+      modes[m].sample_num_conc.assign(sample_num_conc + (size_t)m * n_sample_bins,
+                                      sample_num_conc + (size_t)(m + 1) * n_sample_bins);
+    }
     modes[m].vol_frac.assign(vol_frac + (size_t)m * S, vol_frac + (size_t)(m + 1) * S);
     if (vol_frac_std)
       modes[m].vol_frac_std.assign(vol_frac_std + (size_t)m * S, vol_frac_std + (size_t)(m + 1) * S);

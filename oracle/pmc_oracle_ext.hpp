@@ -49,12 +49,14 @@ int condense_integrate(int n, double* D, double* H, const double* D_dry, const d
                        CondenseStats& stats);
 
 // ---------------------------------------------------------------- emission / inflow sampling (pmc_oracle_emit.cpp)
-enum { MODE_LOG_NORMAL = 1, MODE_EXP = 2, MODE_MONO = 3 };  // aero_mode.F90:26-34
+enum { MODE_LOG_NORMAL = 1, MODE_EXP = 2, MODE_MONO = 3, MODE_SAMPLED = 4 };  // aero_mode.F90:26-37
 struct AeroMode {
   int type = MODE_LOG_NORMAL;
   int weight_class = 1;
   double char_radius = 1e-7, log10_std_dev_radius = 0.2, num_conc = 0.0;
   std::vector<double> vol_frac, vol_frac_std;
+  // sampled mode (:70-74): bin-edge radii [n + 1] and number concentrations [n]; num_conc is a factor on the table
+  std::vector<double> sample_radius, sample_num_conc;
 };
 double aero_mode_sample_radius(const AeroMode& m, const Weight& w, double prob_threshold, Stream& s);  // aero_mode.F90:549
 void aero_mode_sample_vols(const AeroMode& m, double total_vol, std::vector<double>& vols, Stream& s);  // :633

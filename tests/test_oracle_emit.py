@@ -86,3 +86,25 @@ def test_seasalt_emissions_expected_number():
     expect[0, 0] = 0.0
     tot, exp_tot = n_add[:, 0, :].sum(), expect.sum()
     assert abs(tot - exp_tot) < 5.0 * np.sqrt(exp_tot), (tot, exp_tot)
+
+
+def test_sampled_mode_reproduces_its_table():
+    """mode_type sampled (aero_mode.F90:456-491, 533-538, 581-608): expected count sum(n_k) sample_prop / magnitude,
+    every bin populated in proportion to its tabulated number concentration, radii log-uniform inside a bin"""
+    case = common.make_cells(1, 10, n_spec=2, n_class=1, seed=3, n_part_ideal=1e6, ragged=False)
+    o = common.oracle_from_case(O, case)
+    mag = case["wmag"][0, 0, 0]
+    edges = np.logspace(-8, -6, 6)                      # 5 bins
+    table = np.array([1.0, 4.0, 2.0, 0.0, 3.0]) * 4000.0 * mag
+    n = o.add_aero_dist_sample(0, mode_type=[4], weight_class=[1], char_radius=[0.0], log10_std_dev=[0.0],
+                               vol_frac=[[0.3, 0.7]], num_conc=[1.0], sample_prop=1.0, characteristic_factor=10.0,
+                               step=1, allow_doubling=False, allow_halving=False, sample_radius=[edges],
+                               sample_num_conc=[table])
+    assert abs(n - 40000) < 5 * np.sqrt(40000)
+    q = o.get_cell(0)
+    r = (3 * q["vol"].sum(axis=0)[10:] / (4 * np.pi)) ** (1 / 3)
+    hist = np.histogram(r, edges)[0]
+    expect = table / table.sum() * n
+    assert hist[3] == 0 and np.all(np.abs(hist - expect) < 5 * np.sqrt(expect + 1))
+    inside = (np.log(r[(r > edges[1]) & (r < edges[2])]) - np.log(edges[1])) / np.log(edges[2] / edges[1])
+    assert abs(inside.mean() - 0.5) < 0.02 and abs(inside.std() - 12 ** -0.5) < 0.02

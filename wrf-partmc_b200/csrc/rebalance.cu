@@ -430,11 +430,32 @@ struct EmitDev {
   unsigned step;
   unsigned stream;             // added to the draw address a = (group, mode): keeps several callers of one step apart
   int* n_add;                  // [n_cells]
+  // sampled (tabulated) modes, type 4 (aero_mode.F90:37): per mode n_sbin + 1 bin-edge radii and n_sbin number
+  // concentrations; num_conc[cell][mode] is then a dimensionless factor on the table
+  int n_sbin;
+  const double* sample_radius;    // [n_mode][n_sbin + 1]
+  const double* sample_num_conc;  // [n_mode][n_sbin]
 };
+struct SampTab {
+  int nbin;
+  const double* rad;
+  const double* nc;
+};
+// aero_mode_weighted_sampled_num_conc (aero_mode.F90:456-491), entry k (0-based)
+__device__ __forceinline__ double sampled_weighted_nc(const SampTab& t, int k, int wtype, double wexp) {
+  if (wtype == PMCGPU_WEIGHT_NONE) return t.nc[k];
+  const double x0 = log(t.rad[k]), x1 = log(t.rad[k + 1]);
+  return t.nc[k] / wexp * (exp(-wexp * x0) - exp(-wexp * x1)) / (x1 - x0);
+}
 
 // aero_mode_number (aero_mode.F90:496-544)
 __device__ __forceinline__ double aero_mode_number(int type, double num_conc, double char_radius, double lsd, int wtype,
-                                                   double wmag, double wexp) {
+                                                   double wmag, double wexp, const SampTab& tab) {
+  if (type == 4) {  // :533-538: sum(weighted_num_conc) / magnitude, scaled by the cell's factor
+    double sum = 0.0;
+    for (int k = 0; k < tab.nbin; k++) sum = sum + sampled_weighted_nc(tab, k, wtype, wexp);
+    return num_conc * (sum / wmag);
+  }
   if (type == 1) {
     if (wtype == PMCGPU_WEIGHT_NONE) return num_conc / wmag;
     const double l10 = log10(char_radius);
@@ -451,10 +472,31 @@ __device__ __forceinline__ double aero_mode_number(int type, double num_conc, do
 // vols[S] receives the species volumes, the radius is returned
 __device__ double sample_mode_particle(int S, int type, double cr, double lsd, int wt, double we, double size_factor,
                                        const double* __restrict__ vf, const double* __restrict__ vs, RStream& s,
-                                       double* vols) {
+                                       double* vols, const SampTab& tab = SampTab{0, nullptr, nullptr},
+                                       double wm = 1.0) {
   // aero_mode_sample_radius
   double radius = cr;
-  if (type == 1) {
+  if (type == 4) {
+    // sampled mode (:581-608): bin by sample_cts_pdf (rand.F90:550-576) on the weighted table, then a radius
+    // log-uniform in the bin (flat weight) or uniform in 1 / num_conc (power weight)
+    double pdf_max = 0.0;
+    for (int k = 0; k < tab.nbin; k++) pdf_max = fmax(pdf_max, sampled_weighted_nc(tab, k, wt, we));
+    int ks;
+    for (;;) {
+      ks = pmc_rand_int(s.next(), tab.nbin) - 1;
+      if (s.next() < sampled_weighted_nc(tab, ks, wt, we) / pdf_max) break;
+    }
+    const double r = s.next();
+    if (wt == PMCGPU_WEIGHT_NONE || we == 0.0) {
+      const double x0 = log(tab.rad[ks]), x1 = log(tab.rad[ks + 1]);
+      radius = exp((1.0 - r) * x0 + r * x1);
+    } else {
+      const double inv_nc0 = 1.0 / weight_nc(wt, wm, we, tab.rad[ks]);
+      const double inv_nc1 = 1.0 / weight_nc(wt, wm, we, tab.rad[ks + 1]);
+      const double inv_nc = (1.0 - r) * inv_nc0 + r * inv_nc1;
+      radius = exp(log((1.0 / inv_nc) / wm) / we);  // aero_weight_radius_at_num_conc (aero_weight.F90:170-191)
+    }
+  } else if (type == 1) {
     double x_mean_prime = log10(cr);
     if (wt != PMCGPU_WEIGHT_NONE) x_mean_prime = log10(cr) - we * (lsd * lsd) * log(10.0);
     const double sqrt2 = (double)sqrtf(2.0f);  // 2.0**.5 is a default-real expression in rand.F90:463
@@ -509,6 +551,9 @@ __device__ int emit_cell(DevView& v, const EmitDev& e, int cell, int lane, doubl
       const int type = e.type[im - 1], c = e.wclass[im - 1];
       const double cr = e.char_radius[im - 1], lsd = e.log10_std[im - 1];
       const double mode_nc = mode_nc_row[im - 1];
+      const SampTab tab{type == 4 ? e.n_sbin : 0,
+                        type == 4 ? e.sample_radius + (size_t)(im - 1) * (e.n_sbin + 1) : nullptr,
+                        type == 4 ? e.sample_num_conc + (size_t)(im - 1) * e.n_sbin : nullptr};
       const unsigned a = e.stream + (unsigned)((g - 1) * e.n_mode + (im - 1));
       const int gc = (c - 1) * v.G + (g - 1);
       const double ideal = v.ideal_gc[gc];
@@ -518,7 +563,7 @@ __device__ int emit_cell(DevView& v, const EmitDev& e, int cell, int lane, doubl
         break;
       }
       __syncwarp();
-      double n_samp_avg = sample_prop * aero_mode_number(type, mode_nc, cr, lsd, v.wtype[wi], v.wmag[wi], v.wexp[wi]);
+      double n_samp_avg = sample_prop * aero_mode_number(type, mode_nc, cr, lsd, v.wtype[wi], v.wmag[wi], v.wexp[wi], tab);
       {  // aero_state_prepare_weight_for_add
         const int n_now = v.count[cell];
         int m = 0;
@@ -535,7 +580,7 @@ __device__ int emit_cell(DevView& v, const EmitDev& e, int cell, int lane, doubl
       if (n_samp_avg == 0.0) continue;
       const int wt = v.wtype[wi];
       const double wm = v.wmag[wi], we = v.wexp[wi];
-      n_samp_avg = sample_prop * aero_mode_number(type, mode_nc, cr, lsd, wt, wm, we);
+      n_samp_avg = sample_prop * aero_mode_number(type, mode_nc, cr, lsd, wt, wm, we, tab);
       RStream s0{RKey{v.seed, gcell, e.step, PH_EMIT, a, 0u}, 0u};
       const int n_samp = rand_poisson(n_samp_avg, s0);
       const double size_factor = fmin(1.0 / (e.char_factor * n_samp_avg), 0.32);
@@ -550,7 +595,7 @@ __device__ int emit_cell(DevView& v, const EmitDev& e, int cell, int lane, doubl
       for (int i_samp = 1 + lane; i_samp <= n_samp; i_samp += 32) {
         RStream s{RKey{v.seed, gcell, e.step, PH_EMIT, a, (unsigned)i_samp}, 0u};
         double vols[PMC_MAX_SPEC];
-        const double radius = sample_mode_particle(v.S, type, cr, lsd, wt, we, size_factor, vf, vs, s, vols);
+        const double radius = sample_mode_particle(v.S, type, cr, lsd, wt, we, size_factor, vf, vs, s, vols, tab, wm);
         (void)radius;
         const int slot = n_cur + i_samp - 1;
         for (int k = 0; k < v.S; k++) v.vol[(size_t)k * NS + base + slot] = vols[k];
@@ -599,10 +644,19 @@ static int emit_run(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add)
     return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;
   const size_t nm = (size_t)a->n_mode, S = (size_t)v.S, nc = (size_t)v.n_cells;
-  for (size_t m = 0; m < nm; m++)
-    if (a->weight_class[m] < 1 || a->weight_class[m] > v.C || a->mode_type[m] < 1 || a->mode_type[m] > 3) return PMCGPU_ERR_ARG;
+  bool any_sampled = false;
+  for (size_t m = 0; m < nm; m++) {
+    if (a->weight_class[m] < 1 || a->weight_class[m] > v.C || a->mode_type[m] < 1 || a->mode_type[m] > 4) return PMCGPU_ERR_ARG;
+    any_sampled = any_sampled || a->mode_type[m] == 4;
+  }
+  if (any_sampled && (a->n_sample_bins < 1 || a->n_sample_bins > 4096 || !a->sample_radius || !a->sample_num_conc)) {
+    ctx->err = "sampled mode (type 4) without its table (n_sample_bins, sample_radius, sample_num_conc)";
+    return PMCGPU_ERR_ARG;
+  }
+  const size_t nsb = any_sampled ? (size_t)a->n_sample_bins : 0;
   // one device buffer per call (mode tables are tiny; num_conc is [n_cells][n_mode])
-  const size_t bytes = (2 * nm) * sizeof(int) + (2 * nm + 2 * nm * S + nc * nm + nc) * sizeof(double) + nc * sizeof(int) + 64;
+  const size_t bytes = (2 * nm) * sizeof(int) + (2 * nm + 2 * nm * S + nc * nm + nc + nm * (2 * nsb + 1)) * sizeof(double) +
+                       nc * sizeof(int) + 64;
   char* buf = nullptr;
   CUDA_OK(ctx, cudaMalloc((void**)&buf, bytes));
   double* d_cr = (double*)buf;
@@ -611,7 +665,9 @@ static int emit_run(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add)
   double* d_vs = d_vf + nm * S;
   double* d_nc = d_vs + nm * S;
   double* d_sp = d_nc + nc * nm;
-  int* d_ty = (int*)(d_sp + nc);
+  double* d_sr = d_sp + nc;                // [n_mode][nsb + 1]
+  double* d_sn = d_sr + nm * (nsb + 1);    // [n_mode][nsb]
+  int* d_ty = (int*)(d_sn + nm * nsb);
   int* d_wc = d_ty + nm;
   int* d_na = d_wc + nm;
   cudaStream_t st = ctx->stream;
@@ -624,6 +680,10 @@ static int emit_run(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add)
     CUDA_OK(ctx, cudaMemsetAsync(d_vs, 0, nm * S * sizeof(double), st));
   CUDA_OK(ctx, cudaMemcpyAsync(d_nc, a->num_conc, nc * nm * sizeof(double), cudaMemcpyDefault, st));
   CUDA_OK(ctx, cudaMemcpyAsync(d_sp, a->sample_prop, nc * sizeof(double), cudaMemcpyDefault, st));
+  if (any_sampled) {
+    CUDA_OK(ctx, cudaMemcpyAsync(d_sr, a->sample_radius, nm * (nsb + 1) * sizeof(double), cudaMemcpyDefault, st));
+    CUDA_OK(ctx, cudaMemcpyAsync(d_sn, a->sample_num_conc, nm * nsb * sizeof(double), cudaMemcpyDefault, st));
+  }
   CUDA_OK(ctx, cudaMemcpyAsync(d_ty, a->mode_type, nm * sizeof(int), cudaMemcpyDefault, st));
   CUDA_OK(ctx, cudaMemcpyAsync(d_wc, a->weight_class, nm * sizeof(int), cudaMemcpyDefault, st));
   EmitDev e;
@@ -633,6 +693,7 @@ static int emit_run(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add)
   e.char_factor = a->characteristic_factor; e.create_time = a->create_time;
   e.allow_doubling = a->allow_doubling; e.allow_halving = a->allow_halving; e.step = a->step;
   e.stream = a->stream;
+  e.n_sbin = (int)nsb; e.sample_radius = d_sr; e.sample_num_conc = d_sn;
   e.n_add = d_na;
   {
     ProfScope ps_(ctx, "k_emit");
@@ -1023,6 +1084,7 @@ int pmc_boundary_refresh_async(pmcgpu_ctx* ctx, unsigned step) {
   b.e.vol_frac = ctx->bnd_vf; b.e.vol_frac_std = ctx->bnd_vs; b.e.num_conc = ctx->bnd_nc; b.e.sample_prop = nullptr;
   b.e.char_factor = 1.0; b.e.create_time = 0.0;   // sample_timescale, create_time of the call sites (:839-842)
   b.e.allow_doubling = 1; b.e.allow_halving = 1; b.e.step = step; b.e.stream = 0u; b.e.n_add = nullptr;
+  b.e.n_sbin = 0; b.e.sample_radius = nullptr; b.e.sample_num_conc = nullptr;
   b.outflow = ctx->bnd_outflow; b.throw_away = ctx->bnd_throw;
   b.nx = ctx->cfg.nx; b.nz = ctx->cfg.nz;
   const size_t smem = ((size_t)2 * v.cap + 2 * v.C) * sizeof(int);

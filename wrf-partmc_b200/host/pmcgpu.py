@@ -101,7 +101,8 @@ class _EmitArgs(C.Structure):
                 ("char_radius", C.c_void_p), ("log10_std_dev", C.c_void_p), ("vol_frac", C.c_void_p),
                 ("vol_frac_std", C.c_void_p), ("num_conc", C.c_void_p), ("sample_prop", C.c_void_p),
                 ("characteristic_factor", C.c_double), ("create_time", C.c_double), ("allow_doubling", C.c_int),
-                ("allow_halving", C.c_int), ("step", C.c_uint), ("stream", C.c_uint)]
+                ("allow_halving", C.c_int), ("step", C.c_uint), ("stream", C.c_uint), ("n_sample_bins", C.c_int),
+                ("sample_radius", C.c_void_p), ("sample_num_conc", C.c_void_p)]
 
 
 class _SeasaltArgs(C.Structure):
@@ -374,7 +375,8 @@ class PartMCGPU:
 
     def aero_state_add_aero_dist_sample(self, mode_type, weight_class, char_radius, log10_std_dev, vol_frac, num_conc,
                                         sample_prop, characteristic_factor, create_time=0.0, vol_frac_std=None,
-                                        allow_doubling=True, allow_halving=True, step=0, stream=0):
+                                        allow_doubling=True, allow_halving=True, step=0, stream=0,
+                                        sample_radius=None, sample_num_conc=None):
         """aero_state_add_aero_dist_sample (aero_state.F90:758) for every cell: modes described by arrays
         [n_mode] (vol_frac [n_mode][n_spec]), num_conc [n_cells][n_mode], sample_prop [n_cells].
         Returns the number of particles added per cell."""
@@ -392,6 +394,11 @@ class PartMCGPU:
         a.characteristic_factor, a.create_time = float(characteristic_factor), float(create_time)
         a.allow_doubling, a.allow_halving, a.step = int(allow_doubling), int(allow_halving), int(step)
         a.stream = int(stream)
+        sr, sn = _f64(sample_radius), _f64(sample_num_conc)  # sampled modes (type 4): [n_mode][nb + 1], [n_mode][nb]
+        if sr is not None:
+            a.n_sample_bins = sn.size // nm
+            assert sr.size == nm * (a.n_sample_bins + 1)
+            a.sample_radius, a.sample_num_conc = _addr(sr), _addr(sn)
         n_add = np.zeros(self.n_cells, np.int32)
         self._chk(self.L.pmcgpu_aero_state_add_aero_dist_sample(self.h, C.byref(a), _p(n_add)))
         return n_add
