@@ -740,7 +740,7 @@ __device__ __forceinline__ bool pair_advance_exact(int C, int nb, int& c1, int& 
 }
 
 template <int KT, bool COLD>
-__global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(DevView v, int ktype, double del_t, unsigned step) {
+__global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(const __grid_constant__ DevView v, int ktype, double del_t, unsigned step) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * COAG_WARPS + warp;
   if (cell >= v.n_cells) return;
