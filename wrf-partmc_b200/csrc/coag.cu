@@ -739,8 +739,8 @@ __device__ __forceinline__ bool pair_advance_exact(int C, int nb, int& c1, int& 
   return true;
 }
 
-template <int KT, bool COLD>
-__global__ void __launch_bounds__(COAG_WARPS * 32, COAG_MIN_CTAS) k_mc_coag(const __grid_constant__ DevView v, int ktype, double del_t, unsigned step) {
+template <int KT, bool COLD, int MIN_CTAS>
+__global__ void __launch_bounds__(COAG_WARPS * 32, MIN_CTAS) k_mc_coag(const __grid_constant__ DevView v, int ktype, double del_t, unsigned step) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cell = blockIdx.x * COAG_WARPS + warp;
   if (cell >= v.n_cells) return;
@@ -992,12 +992,22 @@ int pmc_mc_coag_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step) {
   const int blocks = (v.n_cells + COAG_WARPS - 1) / COAG_WARPS;
   {
     ProfScope ps_(ctx, "k_mc_coag");
+    // Resident CTAs per SM (= registers per thread) of the Brownian instance: the variant with the MOST registers whose
+    // single wave still holds every CTA (8 CTAs per SM at 64 registers, 12 at 40, 16 at 32); 16 when nothing fits in
+    // one wave.  Measured ms per K4-type step, cells = 4000 / 6000 / 8000 / 16 000 / 32 000:
+    //   8 CTAs: 2.94 / 4.45 / 5.34 / 10.18 / 19.7;  12 CTAs: 3.21 / 3.92 / 5.51 / 9.55 / 17.9;  16 CTAs: 3.41 / 4.17 /
+    //   4.90 / 9.02 / 17.3  (fewer spills against more warps to hide the instruction fetch, and wave quantisation)
+    const int n_sm = 148;
     if (v.cold.n)  // component lists are tracked (pmcgpu_track_components): the instance that merges them
-      k_mc_coag<0, true><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+      k_mc_coag<0, true, COAG_MIN_CTAS><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+    else if (ktype == PMCGPU_KERNEL_BROWN && blocks <= n_sm * 8)
+      k_mc_coag<PMCGPU_KERNEL_BROWN, false, 8><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+    else if (ktype == PMCGPU_KERNEL_BROWN && blocks > n_sm * 12)
+      k_mc_coag<PMCGPU_KERNEL_BROWN, false, 16><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
     else if (ktype == PMCGPU_KERNEL_BROWN)
-      k_mc_coag<PMCGPU_KERNEL_BROWN, false><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+      k_mc_coag<PMCGPU_KERNEL_BROWN, false, COAG_MIN_CTAS><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
     else
-      k_mc_coag<0, false><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+      k_mc_coag<0, false, COAG_MIN_CTAS><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
     LAUNCH_CHECK(ctx);
   }
   return PMCGPU_OK;
