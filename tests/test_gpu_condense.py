@@ -46,7 +46,7 @@ def test_condense_equilib_device_vs_oracle(mods):
     common.assert_same_population(g, o, case, exact_fp=False, rtol=1e-10)
 
 
-@pytest.mark.parametrize("n_per_mode,n_cells,method", [(100, 4, 4), (200, 3, 4), (400, 3, 4), (540, 2, 4), (900, 2, 4), (100, 4, 5), (400, 3, 5), (900, 2, 5)])
+@pytest.mark.parametrize("n_per_mode,n_cells,method", [(100, 4, 4), (200, 3, 4), (300, 2, 4), (350, 2, 4), (400, 3, 4), (540, 2, 4), (900, 2, 4), (100, 4, 5), (400, 3, 5), (900, 2, 5)])
 def test_condense_particles_device_vs_oracle(mods, n_per_mode, n_cells, method):
     """condense_particles over several steps through activation: per-particle water volume, RH and
     the number of internal steps agree with the oracle (1e-10 relative on RH and on wet diameters).

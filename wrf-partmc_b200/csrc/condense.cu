@@ -626,7 +626,7 @@ __device__ __forceinline__ void ros_combo(const double* __restrict__ s_K, int ti
 }
 
 template <int PPT, int NT, bool GRID = false>
-__global__ void __launch_bounds__(NT) k_condense(DevView v, const double* T0a /* may alias v.temp */,
+__global__ void __launch_bounds__(NT, (NT == 160 || NT == 192) ? 2 : 1) k_condense(DevView v, const double* T0a /* may alias v.temp */,
                                                            const double* p0a,
                                                            const double* T1 /* may alias v.temp */,
                                                            const double* p1, CondParams prm,
@@ -1623,6 +1623,8 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 128)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 64)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 256)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 160>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 160)));
+    CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 192>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 192)));
 
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<4, 288>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(4, 288)));
     CUDA_OK(ctx, cudaFuncSetAttribute(k_condense<8, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ros_smem(8, 256)));
@@ -1674,7 +1676,12 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     if (cap > 256) { ROS_LAUNCH(4, 128, 256, 512); }
     // (round 2: 3 particles x 384 threads -- a third warp per scheduler at 168 registers -- measured 224.7 ms per
     // K4 step, 2 x 512 236.8 ms, against 206.0 ms for 4 x 256: profiles/r02_condense_notes.md)
-    if (cap > 512) { ROS_LAUNCH(4, 256, 512, 1024); }
+    // 513..768 particles (a 500-particle population between rebalances, config K5): five / six warps x 4 particles with
+    // TWO cells per SM (launch bounds: 204 / 170 registers) instead of one cell on a 256-thread CTA at twice the cost
+    static const bool mid = getenv("PMCGPU_COND_NO_MID") == nullptr;  // measurements only
+    if (cap > 512 && mid) { ROS_LAUNCH(4, 160, 512, 640); }
+    if (cap > 640 && mid) { ROS_LAUNCH(4, 192, 640, 768); }
+    if (cap > 512) { ROS_LAUNCH(4, 256, mid ? 768 : 512, 1024); }
     // cells a little over 1024 particles (a 1000-particle population drifts there between rebalances):
     // nine warps x 4 particles at 168 registers (three warps share a scheduler's 16384 registers; 422 bytes
     // of spills) instead of 8 particles per thread (no predictor, 255 registers, 838 bytes of spills)
