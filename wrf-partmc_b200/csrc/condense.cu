@@ -1664,10 +1664,35 @@ int pmc_condense_async(pmcgpu_ctx* ctx, const double* dT0, const double* dp0, co
     if (cap > 1024) { BDF_LAUNCH(8, 1024, 2048); }
 #undef BDF_LAUNCH
   } else {
+    // the variants touch disjoint cells: each goes to its own side stream between a fork and a join on the context's
+    // stream (serialised, every launch ends with SMs idling behind its last ~0.9 ms cells: +1.1 ms per step on a
+    // 4000-cell patch with seven launches)
+    static const bool side = getenv("PMCGPU_COND_SERIAL") == nullptr;  // measurements only
+    if (side && !ctx->cond_fork) {
+      CUDA_OK(ctx, cudaEventCreateWithFlags(&ctx->cond_fork, cudaEventDisableTiming));
+      for (int q = 0; q < 8; q++) {
+        CUDA_OK(ctx, cudaStreamCreateWithFlags(&ctx->cond_stream[q], cudaStreamNonBlocking));
+        CUDA_OK(ctx, cudaEventCreateWithFlags(&ctx->cond_join[q], cudaEventDisableTiming));
+      }
+    }
+    int n_side = 0;
+    if (side) CUDA_OK(ctx, cudaEventRecord(ctx->cond_fork, ctx->stream));
 #define ROS_LAUNCH(PPT, NT, LO, HI)                                                                               \
-  k_condense<PPT, NT><<<v.n_cells, NT, ros_smem(PPT, NT), ctx->stream>>>(v, dT0, dp0, dT1, dp1, prm,             \
-                                                                           cw->cond_stats, cw->cond_wre, LO, HI, GridRed{}); \
-  LAUNCH_CHECK(ctx)
+  {                                                                                                               \
+    cudaStream_t st_ = ctx->stream;                                                                               \
+    if (side) {                                                                                                   \
+      st_ = ctx->cond_stream[n_side];                                                                             \
+      CUDA_OK(ctx, cudaStreamWaitEvent(st_, ctx->cond_fork, 0));                                                  \
+    }                                                                                                             \
+    k_condense<PPT, NT><<<v.n_cells, NT, ros_smem(PPT, NT), st_>>>(v, dT0, dp0, dT1, dp1, prm, cw->cond_stats,   \
+                                                                   cw->cond_wre, LO, HI, GridRed{});             \
+    LAUNCH_CHECK(ctx);                                                                                            \
+    if (side) {                                                                                                   \
+      CUDA_OK(ctx, cudaEventRecord(ctx->cond_join[n_side], st_));                                                 \
+      CUDA_OK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->cond_join[n_side], 0));                                  \
+      n_side++;                                                                                                   \
+    }                                                                                                             \
+  }
     // 256 threads x 4 particles per thread measured faster than 512 x 2 at ~1000 particles per cell
     // (300 vs 318 ms per K4 step): instruction-level parallelism beats the extra warps here
     ROS_LAUNCH(4, 64, -1, 256);  // small cells: four CTAs of 64 threads per SM

@@ -175,6 +175,11 @@ extern "C" int pmcgpu_destroy(pmcgpu_ctx* ctx) {
   if (ctx->h_tot) cudaFreeHost(ctx->h_tot);
   if (ctx->bnd_buf) cudaFree(ctx->bnd_buf);
   pmcgpu_comm_destroy(ctx);
+  for (int q = 0; q < 8; q++) {
+    if (ctx->cond_stream[q]) cudaStreamDestroy(ctx->cond_stream[q]);
+    if (ctx->cond_join[q]) cudaEventDestroy(ctx->cond_join[q]);
+  }
+  if (ctx->cond_fork) cudaEventDestroy(ctx->cond_fork);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
   return PMCGPU_OK;

@@ -222,6 +222,10 @@ struct pmcgpu_ctx {
   bool tot_valid = false;           // h_tot holds the counts of the previous step
   bool cfg_trans_smem = false, cfg_cond = false, cfg_cond_grid = false, cfg_sort = false;  // per-context (= per-device) opt-ins
   int cond_n_sm = 0, cond_max_blk4 = 0, cond_max_blk8 = 0;
+  // side streams of condense_particles: the population-size variants of k_condense run side by side, so that the
+  // tail of one launch (SMs idling behind its last cells) is filled by the next
+  cudaStream_t cond_stream[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t cond_fork = nullptr, cond_join[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   size_t cfg_msamp_smem = 0, cfg_kmax_smem = 0, cfg_bnd_smem = 0, cfg_sort_smem = 0, cfg_sort_staged_smem = 0;
   // boundary conditions of an open domain (pmcgpu_set_boundary): device copies
   int bnd_n_mode = 0;
