@@ -320,6 +320,29 @@ double pmco_philox_uniform(unsigned seed, unsigned cell, unsigned step, unsigned
   return philox_uniform(seed, k, j);
 }
 void pmco_philox_raw(const unsigned* ctr, const unsigned* key, unsigned* out) { philox4x32_10(ctr, key, out); }
+// sample_without_replacement (rand.F90:515-542) with the MT generator: out[sample_size] 1-based indices; returns the count
+int pmco_sample_without_replacement(int sample_size, int population_size, unsigned seed, int* out) {
+  RngMT mt(seed);
+  Stream s(&mt, RngKey{0, 0, 0, 0, 0});
+  const std::vector<int> v = sample_without_replacement(sample_size, population_size, s);
+  for (size_t i = 0; i < v.size(); i++) out[i] = v[i];
+  return (int)v.size();
+}
+// the component rule of aero_particle_coagulate (aero_particle.F90:940-972) for two particles with n1 / n2 components
+// (sources 1000 + i and 2000 + i) and n_primary_parts np1 / np2; out_src[<= 20]; returns the new component count
+int pmco_coagulate_components(int n1, int np1, int n2, int np2, unsigned seed, int* out_src) {
+  Particle p1, p2, pn;
+  p1.vol.assign(1, 1.0);
+  p2.vol.assign(1, 2.0);
+  p1.n_primary_parts = np1;
+  p2.n_primary_parts = np2;
+  for (int i = 0; i < n1; i++) { p1.comp_src.push_back(1000 + i); p1.comp_time.push_back((double)i); }
+  for (int i = 0; i < n2; i++) { p2.comp_src.push_back(2000 + i); p2.comp_time.push_back((double)i); }
+  RngPhilox rng(seed);
+  particle_coagulate(p1, p2, pn, &rng, RngKey{1, 2, PH_COAG, 3, 4}, 0u);
+  for (size_t i = 0; i < pn.comp_src.size(); i++) out_src[i] = pn.comp_src[i];
+  return (int)pn.comp_src.size();
+}
 unsigned pmco_mt_u32(unsigned seed, int skip) {
   RngMT mt(seed);
   for (int i = 0; i < skip; i++) mt.next_u32();

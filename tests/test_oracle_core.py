@@ -237,3 +237,43 @@ def test_wrf_to_partmc_types_follow_the_fortran():
     np.testing.assert_allclose(r["height"], dz.ravel(), rtol=0, atol=0)
     np.testing.assert_allclose(r["cell_volume"], vol.ravel(), rtol=1e-15)
     np.testing.assert_array_equal(r["inverse_density"], f(alt).astype(np.float64).ravel())
+
+
+def test_sample_without_replacement_is_uniform_over_subsets():
+    """rand.F90:515-542 (selection sampling): ascending distinct indices, every element equally likely"""
+    import ctypes as C
+    L = O.lib()
+    n_pop, k, n_rep = 12, 5, 6000
+    hits = np.zeros(n_pop)
+    out = (C.c_int * k)()
+    for seed in range(n_rep):
+        n = L.pmco_sample_without_replacement(k, n_pop, seed + 1, out)
+        idx = np.array(out[:n])
+        assert n == k and (np.diff(idx) > 0).all() and idx.min() >= 1 and idx.max() <= n_pop
+        hits[idx - 1] += 1
+    expect = n_rep * k / n_pop
+    assert np.abs(hits - expect).max() < 5 * np.sqrt(expect)
+    assert L.pmco_sample_without_replacement(n_pop, n_pop, 7, (C.c_int * n_pop)()) == n_pop  # the whole population
+
+
+def test_coagulated_component_lists():
+    """aero_particle_coagulate (aero_particle.F90:940-972): lists are concatenated (first particle first); beyond 20 the
+    new list keeps prob_round(np1 / (np1 + np2) * 20) components of the first particle and the rest of the second,
+    each a sample without replacement in the original order"""
+    import ctypes as C
+    L = O.lib()
+    out = (C.c_int * 20)()
+    n = L.pmco_coagulate_components(3, 3, 4, 4, 1, out)
+    assert list(out[:n]) == [1000, 1001, 1002, 2000, 2001, 2002, 2003]
+    n = L.pmco_coagulate_components(12, 12, 8, 8, 1, out)
+    assert n == 20 and list(out[:20]) == list(range(1000, 1012)) + list(range(2000, 2008))
+    firsts = []
+    for seed in range(400):
+        n = L.pmco_coagulate_components(15, 30, 10, 10, seed, out)   # 25 > 20: 30 / 40 * 20 = 15 exactly
+        a = [x for x in out[:n] if x < 2000]
+        b = [x for x in out[:n] if x >= 2000]
+        assert n == 20 and len(a) == 15 and len(b) == 5 and a == sorted(a) and b == sorted(b) and out[14] < 2000 <= out[15]
+        n = L.pmco_coagulate_components(18, 18, 7, 7, seed, out)     # 18 / 25 * 20 = 14.4 -> 14 or 15
+        firsts.append(sum(1 for x in out[:n] if x < 2000))
+        assert n == 20 and firsts[-1] in (14, 15)
+    assert abs(np.mean(firsts) - 14.4) < 0.1
