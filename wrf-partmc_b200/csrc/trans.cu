@@ -425,9 +425,7 @@ __global__ void k_tr_multisample(DevView v, TransView t, unsigned step, int warp
   int* ch_entry = x.off + v.C;           // [TR_CHUNK] list entry (1-based) of every transfer of the chunk
   int* ch_flags = ch_entry + TR_CHUNK;   // bit 0 add, bit 1 remove
   int* sdir = ch_flags + TR_CHUNK;       // [nd] direction slot in sorted order
-  int* spidx = sdir + nd;                // [nd] scratch
-  float* unused = (float*)(spidx + nd);  // keeps the layout explicit
-  (void)unused;
+  // (sdir + nd .. sdir + 3 nd: scratch, part of per_warp)
   double* sprob = (double*)(s_i + (size_t)warps_per_cta * per_warp) + (size_t)warp * nd;  // [nd] sorted probabilities
 
   const size_t base = (size_t)cell * v.cap;
