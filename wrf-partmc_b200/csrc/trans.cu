@@ -723,17 +723,35 @@ __device__ __forceinline__ void tr_copy_rows(double* __restrict__ dst, size_t ds
 // ---- the out list of every cell (sampled particles of all classes and directions, in list order) copied to the
 // ALTERNATE slab at [cell][entry], ids of copies applied: the destination cells read their arrivals from there, so the
 // main slab of a cell is touched by its own CTA only and survivors need not move (k_tr_gather)
-__global__ void __launch_bounds__(128) k_tr_stage(DevView v, TransView t) {
+// Species rows: when a third or more of the cell's particles were sampled, the scattered 8-byte reads would pull more
+// 32-byte sectors than the rows hold, so the CTA streams every row once through shared memory (coalesced) and picks
+// the sampled slots from there; sparse out lists read their slots directly.  `dense_ok`: the launch carries
+// cap doubles of dynamic shared memory.
+#define TR_STAGE_THREADS 256
+__global__ void __launch_bounds__(TR_STAGE_THREADS) k_tr_stage(DevView v, TransView t, int dense_ok) {
   const int cell = blockIdx.x;
   const int n_out = t.n_out[cell];
+  if (n_out == 0) return;
+  const int n = v.count[cell];  // still the population before transport (k_tr_gather sets the new one)
   const size_t base = (size_t)cell * v.cap, NS = (size_t)v.n_cells * v.cap;
-  for (int e = threadIdx.x; e < n_out; e += blockDim.x) {
+  extern __shared__ double s_row[];  // [cap] when dense_ok
+  const bool dense = dense_ok && 3 * n_out >= n;
+  if (dense) {
+    for (int sp = 0; sp < v.S; sp++) {
+      for (int p = threadIdx.x; p < n; p += TR_STAGE_THREADS) s_row[p] = v.vol[(size_t)sp * NS + base + p];
+      __syncthreads();
+      for (int e = threadIdx.x; e < n_out; e += TR_STAGE_THREADS)
+        v.vol_alt[(size_t)sp * NS + base + e] = s_row[t.out_slot[base + e]];
+      __syncthreads();
+    }
+  }
+  for (int e = threadIdx.x; e < n_out; e += TR_STAGE_THREADS) {
     const size_t src = base + t.out_slot[base + e], dst = base + e;
     const long long nid = t.out_newid[base + e];
     const long long r_id = nid ? nid : v.id[src];
     const int r_wgc = v.wgc[src], r_nprim = v.nprim[src], r_hyst = v.hyst[src];
     const double r_lct = v.lct[src], r_gct = v.gct[src];
-    tr_copy_rows(v.vol_alt + dst, NS, v.vol + src, NS, v.S);
+    if (!dense) tr_copy_rows(v.vol_alt + dst, NS, v.vol + src, NS, v.S);
     v.id_alt[dst] = r_id;
     v.wgc_alt[dst] = r_wgc;
     v.nprim_alt[dst] = r_nprim;
@@ -1088,7 +1106,9 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
   {
     // the sampled records of every cell, in list order, to the alternate slab
     ProfScope ps_(ctx, "k_tr_stage");
-    k_tr_stage<<<(unsigned)nc, 128, 0, st>>>(v, t);
+    const size_t row_bytes = (size_t)v.cap * sizeof(double);
+    const int dense_ok = row_bytes <= 48 * 1024;
+    k_tr_stage<<<(unsigned)nc, TR_STAGE_THREADS, dense_ok ? row_bytes : 0, st>>>(v, t, dense_ok);
     LAUNCH_CHECK(ctx);
   }
   // ---- C4: ghost particles: one message per neighbour (header with the per-cell offsets + SoA records), its
