@@ -43,8 +43,9 @@ enum {
   PMCGPU_ERR_REWEIGHT = 10        /* reserved (aero_state_reweight, aero_state.F90:597, is built: never returned) */
 };
 
-/* coag_kernel.F90:24-40 type codes */
-enum { PMCGPU_KERNEL_SEDI = 1, PMCGPU_KERNEL_ADDITIVE = 2, PMCGPU_KERNEL_CONSTANT = 3, PMCGPU_KERNEL_BROWN = 4, PMCGPU_KERNEL_ZERO = 5 };
+/* coag_kernel.F90:24-45 type codes */
+enum { PMCGPU_KERNEL_SEDI = 1, PMCGPU_KERNEL_ADDITIVE = 2, PMCGPU_KERNEL_CONSTANT = 3, PMCGPU_KERNEL_BROWN = 4, PMCGPU_KERNEL_ZERO = 5,
+       PMCGPU_KERNEL_BROWN_FREE = 6, PMCGPU_KERNEL_BROWN_CONT = 7 };
 /* aero_weight.F90:25-30 */
 enum { PMCGPU_WEIGHT_NONE = 1, PMCGPU_WEIGHT_POWER = 2, PMCGPU_WEIGHT_MFA = 3 };
 
@@ -130,6 +131,15 @@ int pmcgpu_get_rel_humid(pmcgpu_ctx* ctx, double* rel_humid);
 /* aero_state%n_part_ideal(n_group, n_class) (aero_state.F90:81, :241): one value per (group, class) for all
  * cells, [(class - 1) * n_group + (group - 1)]; the default is pmcgpu_config.n_part_ideal split evenly. */
 int pmcgpu_set_n_part_ideal(pmcgpu_ctx* ctx, const double* n_part_ideal);
+/* aero_data%fractal (fractal.F90:55-66; spec file do_fractal / frac_dim / prime_radius / vol_fill_factor,
+ * spec_file_read_fractal fractal.F90:546-566).  Default: spherical particles (3, 1e-8, 1), which is what WRF-PartMC
+ * runs with.  A non-spherical setting changes the geometric radius (fractal_vol2rad / fractal_rad2vol,
+ * fractal.F90:106-158) that the sort, the majorant tables and mc_coag use, for the kernels brown_free, brown_cont,
+ * additive, constant and zero.  NOT built for fractal particles: the mobility radius (fractal.F90:239-440), i.e. the
+ * Brownian and sedimentation kernels (mc_coag returns PMCGPU_ERR_ARG) and condensation, dry deposition, emissions,
+ * transport and the diagnostics, which return PMCGPU_ERR_ARG while a non-spherical setting is active.  Call before
+ * the first sort of a run; every cell gets a new bin grid at its next sort. */
+int pmcgpu_set_fractal(pmcgpu_ctx* ctx, double frac_dim, double prime_radius, double vol_fill_factor);
 
 /* ---- the path ---------------------------------------------------------- */
 /* aero_state_sort (aero_state.F90:3218) for every cell: adaptive bin grid

@@ -64,6 +64,7 @@ def _i64(a):
 
 
 KERNEL_SEDI, KERNEL_ADDITIVE, KERNEL_CONSTANT, KERNEL_BROWN, KERNEL_ZERO = 1, 2, 3, 4, 5
+KERNEL_BROWN_FREE, KERNEL_BROWN_CONT = 6, 7  # coag_kernel.F90:42-45
 WEIGHT_NONE, WEIGHT_POWER = 1, 2
 
 
@@ -459,6 +460,37 @@ def kernel_sedi(v1, v2):
     L.pmco_kernel_sedi.restype = C.c_double
     L.pmco_kernel_sedi.argtypes = [C.c_double, C.c_double]
     return L.pmco_kernel_sedi(float(v1), float(v2))
+
+
+def set_fractal(frac_dim=3.0, prime_radius=1e-8, vol_fill_factor=1.0):
+    """aero_data%fractal (fractal.F90:55-82) for the whole process; no arguments = spherical"""
+    lib().pmco_set_fractal(C.c_double(frac_dim), C.c_double(prime_radius), C.c_double(vol_fill_factor))
+
+
+def aero_vol2rad(v):
+    L = lib()
+    L.pmco_aero_vol2rad.restype = C.c_double
+    return L.pmco_aero_vol2rad(C.c_double(v))
+
+
+def aero_rad2vol(r):
+    L = lib()
+    L.pmco_aero_rad2vol.restype = C.c_double
+    return L.pmco_aero_rad2vol(C.c_double(r))
+
+
+def kernel_brown_free(v1, d1, v2, d2, T):
+    """kernel_brown_free_helper (coag_kernel_brown_free.F90:118-147)"""
+    L = lib()
+    L.pmco_kernel_brown_free.restype = C.c_double
+    return L.pmco_kernel_brown_free(*[C.c_double(x) for x in (v1, d1, v2, d2, T)])
+
+
+def kernel_brown_cont(v1, d1, v2, d2, T):
+    """kernel_brown_cont_helper (coag_kernel_brown_cont.F90:117-144)"""
+    L = lib()
+    L.pmco_kernel_brown_cont.restype = C.c_double
+    return L.pmco_kernel_brown_cont(*[C.c_double(x) for x in (v1, d1, v2, d2, T)])
 
 
 def kernel_brown(v1, d1, v2, d2, T, p):

@@ -168,6 +168,33 @@ double binomial_pmf(int n, double p, int k) {
 double sphere_vol2rad(double v) { return std::pow(3.0 * v / 4.0 / Const::pi, 1.0 / 3.0); }
 double sphere_rad2vol(double r) { return 4.0 * Const::pi * (r * r * r) / 3.0; }
 
+// ======================================================================= fractal.F90 (geometric radius only)
+static Fractal g_fractal;
+void set_fractal(double frac_dim, double prime_radius, double vol_fill_factor) {
+  g_fractal.frac_dim = frac_dim;
+  g_fractal.prime_radius = prime_radius;
+  g_fractal.vol_fill_factor = vol_fill_factor;
+}
+const Fractal& fractal() { return g_fractal; }
+bool fractal_is_spherical() { return g_fractal.frac_dim == 3.0 && g_fractal.vol_fill_factor == 1.0; }
+double fractal_vol_to_num_of_monomers(double v) {
+  const double x = sphere_vol2rad(v) / g_fractal.prime_radius;
+  return x * x * x;  // **3
+}
+double aero_vol2rad(double v) {
+  if (fractal_is_spherical()) return sphere_vol2rad(v);
+  return g_fractal.prime_radius *
+         std::pow(fractal_vol_to_num_of_monomers(v) * g_fractal.vol_fill_factor, 1.0 / g_fractal.frac_dim);
+}
+double aero_rad2vol(double r) {
+  if (fractal_is_spherical()) return sphere_rad2vol(r);
+  return sphere_rad2vol(g_fractal.prime_radius) * std::pow(r / g_fractal.prime_radius, g_fractal.frac_dim) /
+         g_fractal.vol_fill_factor;
+}
+static void require_spherical(const char* what) {
+  if (!fractal_is_spherical()) die_msg(0, std::string(what) + ": the mobility radius of fractal particles is not restated");
+}
+
 std::vector<double> linspace(double min_x, double max_x, int n) {
   std::vector<double> x((size_t)std::max(n, 0));
   pmc_assert(999299119, n >= 0);
@@ -286,7 +313,7 @@ double particle_volume(const Particle& p) {
   for (double v : p.vol) s += v;
   return s;
 }
-double particle_radius(const Particle& p) { return sphere_vol2rad(particle_volume(p)); }
+double particle_radius(const Particle& p) { return aero_vol2rad(particle_volume(p)); }
 double particle_mass(const Particle& p, const AeroData& d) {
   double s = 0.0;
   for (int i = 0; i < d.n_spec; i++) s += p.vol[i] * d.density[i];
@@ -509,6 +536,25 @@ double kernel_sedi_helper(double v1, double v2) {
   const double ec = sedi_effic(r1, r2);
   return ec * Const::pi * ((r1 + r2) * (r1 + r2)) * std::fabs(winf1 - winf2);
 }
+// kernel_brown_free_helper (coag_kernel_brown_free.F90:118-147), Eq. 4 of Vemury and Pratsinis [1995]
+double kernel_brown_free_helper(double v1, double d1, double v2, double d2, double temp) {
+  const Fractal& f = fractal();
+  const double rho = (v1 / (v1 + v2)) * d1 + (v2 / (v1 + v2)) * d2;
+  const double N_i = fractal_vol_to_num_of_monomers(v1), N_j = fractal_vol_to_num_of_monomers(v2);
+  const double N_i_inv_df = std::pow(N_i, 1.0 / f.frac_dim), N_j_inv_df = std::pow(N_j, 1.0 / f.frac_dim);
+  const double t = N_i_inv_df + N_j_inv_df;
+  return std::sqrt(6.0 * Const::boltzmann * temp * f.prime_radius / rho * (1.0 / N_i + 1.0 / N_j)) * (t * t);
+}
+// kernel_brown_cont_helper (coag_kernel_brown_cont.F90:117-144), Eq. 6 of Vemury and Pratsinis [1995]
+double kernel_brown_cont_helper(double v1, double d1, double v2, double d2, double temp) {
+  (void)d1;
+  (void)d2;
+  const Fractal& f = fractal();
+  const double N_i = fractal_vol_to_num_of_monomers(v1), N_j = fractal_vol_to_num_of_monomers(v2);
+  const double N_i_inv_df = std::pow(N_i, 1.0 / f.frac_dim), N_j_inv_df = std::pow(N_j, 1.0 / f.frac_dim);
+  return 2.0 * Const::boltzmann * temp / 3.0 / Const::air_dyn_visc * (1.0 / N_i_inv_df + 1.0 / N_j_inv_df) *
+         (N_i_inv_df + N_j_inv_df);
+}
 static const double beta_1 = 1000.0;  // coag_kernel_additive.F90:23
 static const double beta_0 = 0.25 / (60.0 * 2e8);  // coag_kernel_constant.F90:22
 
@@ -534,8 +580,35 @@ static void kernel_brown_minmax(double v1, double v2, const AeroData& d, const E
       }
     }
 }
+// kernel_brown_free_minmax / kernel_brown_cont_minmax (coag_kernel_brown_free.F90:62-108, _cont.F90:62-107): 3 x 3
+// densities in [min rho, max rho]
+static void kernel_brown_fc_minmax(int type, double v1, double v2, const AeroData& d, const EnvState& e, double& k_min,
+                                   double& k_max) {
+  const int n_sample = 3;
+  double d_min = d.density[0], d_max = d.density[0];
+  for (double x : d.density) { d_min = std::min(d_min, x); d_max = std::max(d_max, x); }
+  bool first = true;
+  for (int i = 1; i <= n_sample; i++)
+    for (int j = 1; j <= n_sample; j++) {
+      const double d1 = interp_linear_disc(d_min, d_max, n_sample, i);
+      const double d2 = interp_linear_disc(d_min, d_max, n_sample, j);
+      const double k = type == KERNEL_BROWN_FREE ? kernel_brown_free_helper(v1, d1, v2, d2, e.temp)
+                                                 : kernel_brown_cont_helper(v1, d1, v2, d2, e.temp);
+      if (first) {
+        first = false;
+        k_min = k;
+        k_max = k;
+      } else {
+        k_min = std::min(k_min, k);
+        k_max = std::max(k_max, k);
+      }
+    }
+}
 void kernel_minmax(int type, double v1, double v2, const AeroData& d, const EnvState& e, double& kmin, double& kmax) {
-  if (type == KERNEL_ADDITIVE) {
+  if (type == KERNEL_BROWN || type == KERNEL_SEDI) require_spherical("kernel_minmax (brown / sedi)");
+  if (type == KERNEL_BROWN_FREE || type == KERNEL_BROWN_CONT) {
+    kernel_brown_fc_minmax(type, v1, v2, d, e, kmin, kmax);
+  } else if (type == KERNEL_ADDITIVE) {
     kmin = beta_1 * (v1 + v2);  // coag_kernel_additive.F90:52-70
     kmax = kmin;
   } else if (type == KERNEL_CONSTANT) {
@@ -557,10 +630,13 @@ double kernel(int type, const Particle& p1, const Particle& p2, const AeroData& 
   if (type == KERNEL_ADDITIVE) return beta_1 * (particle_volume(p1) + particle_volume(p2));
   if (type == KERNEL_CONSTANT) return beta_0;
   if (type == KERNEL_ZERO) return 0.0;
+  if (type == KERNEL_BROWN || type == KERNEL_SEDI) require_spherical("kernel (brown / sedi)");
   if (type == KERNEL_SEDI) return kernel_sedi_helper(particle_volume(p1), particle_volume(p2));
-  if (type == KERNEL_BROWN) {
+  if (type == KERNEL_BROWN || type == KERNEL_BROWN_FREE || type == KERNEL_BROWN_CONT) {
     const double v1 = particle_volume(p1), v2 = particle_volume(p2);
     const double d1 = particle_density(p1, d), d2 = particle_density(p2, d);
+    if (type == KERNEL_BROWN_FREE) return kernel_brown_free_helper(v1, d1, v2, d2, e.temp);
+    if (type == KERNEL_BROWN_CONT) return kernel_brown_cont_helper(v1, d1, v2, d2, e.temp);
     return kernel_brown_helper(v1, d1, v2, d2, e.temp, e.pressure);
   }
   die_msg(200724934, "Unknown kernel type");
@@ -571,10 +647,10 @@ static void est_k_minmax_for_bin_unweighted(const BinGrid& g, int type, int b1, 
                                             const EnvState& e, double& k_min, double& k_max) {
   const int n_sample = 3;
   const double over_scale = 2.0;
-  const double v1_low = sphere_rad2vol(g.edges[b1 - 1]);
-  const double v1_high = sphere_rad2vol(g.edges[b1]);
-  const double v2_low = sphere_rad2vol(g.edges[b2 - 1]);
-  const double v2_high = sphere_rad2vol(g.edges[b2]);
+  const double v1_low = aero_rad2vol(g.edges[b1 - 1]);
+  const double v1_high = aero_rad2vol(g.edges[b1]);
+  const double v2_low = aero_rad2vol(g.edges[b2 - 1]);
+  const double v2_high = aero_rad2vol(g.edges[b2]);
   for (int i = 1; i <= n_sample; i++)
     for (int j = 1; j <= n_sample; j++) {
       const double v1 = interp_linear_disc(v1_low, v1_high, n_sample, i);
@@ -602,7 +678,7 @@ void est_k_minmax_binned_unweighted(const BinGrid& g, int type, const AeroData& 
                                       kmax[(size_t)(j - 1) * nb + (i - 1)]);
 }
 double coag_num_conc_factor(const WeightArray& a, double i_r, double j_r, int ic, int jc, int ijc) {
-  const double ij_r = sphere_vol2rad(sphere_rad2vol(i_r) + sphere_rad2vol(j_r));
+  const double ij_r = aero_vol2rad(aero_rad2vol(i_r) + aero_rad2vol(j_r));
   const double i_nc = awa_num_conc_at_radius(a, ic, i_r);
   const double j_nc = awa_num_conc_at_radius(a, jc, j_r);
   const double ij_nc = awa_num_conc_at_radius(a, ijc, ij_r);
@@ -613,7 +689,7 @@ int coag_dest_class(const WeightArray& a, const BinGrid& g, int ib, int jb, int 
   (void)jb;
   const double i_r = g.centers[ib - 1];
   const double j_r = g.centers[ib - 1];  // sic: coag_kernel.F90:403 uses i_bin for j_r
-  const double ij_r = sphere_vol2rad(sphere_rad2vol(i_r) + sphere_rad2vol(j_r));
+  const double ij_r = aero_vol2rad(aero_rad2vol(i_r) + aero_rad2vol(j_r));
   const double ij_nc_i = awa_num_conc_at_radius(a, ic, ij_r);
   const double ij_nc_j = awa_num_conc_at_radius(a, jc, ij_r);
   return (ij_nc_i < ij_nc_j) ? ic : jc;
@@ -1034,7 +1110,7 @@ static void coagulate_weighting(const Particle& pt1, const Particle& pt2, Partic
   pmc_assert(371947172, pt1.id != pt2.id);
   const double r1 = particle_radius(pt1);
   const double r2 = particle_radius(pt2);
-  const double rc = sphere_vol2rad(sphere_rad2vol(r1) + sphere_rad2vol(r2));
+  const double rc = aero_vol2rad(aero_rad2vol(r1) + aero_rad2vol(r2));
   const double nc1 = awa_num_conc_at_radius(awa, c1, r1);
   const double nc2 = awa_num_conc_at_radius(awa, c2, r2);
   const double ncc = awa_num_conc_at_radius(awa, cc, rc);
@@ -1307,8 +1383,8 @@ static bool try_per_particle_coag(int type, double k_max, const EnvState& env, c
   const double n_source_per_target = k_max * del_t * (double)st.sorted.size_class.inv(bs, cs).n_entry();
   const double accept_factor = 1.0 / k_max;
   if (n_source_per_target < COAG_ACCEL_N_EVENT) return false;
-  const double min_target_vol = sphere_rad2vol(st.sorted.bin_grid.edges[bt - 1]);
-  const double max_source_vol = sphere_rad2vol(st.sorted.bin_grid.edges[bs]);
+  const double min_target_vol = aero_rad2vol(st.sorted.bin_grid.edges[bt - 1]);
+  const double max_source_vol = aero_rad2vol(st.sorted.bin_grid.edges[bs]);
   const double max_new_target_vol = min_target_vol + max_source_vol * n_source_per_target;
   const double max_target_growth_factor = max_new_target_vol / min_target_vol;
   if (max_target_growth_factor > MAX_ALLOWABLE_GROWTH_FACTOR) return false;

@@ -31,6 +31,7 @@ struct Const {
   static constexpr double pi = 3.14159265358979323846;
   static constexpr double boltzmann = 1.3806505e-23;
   static constexpr double avagadro = 6.02214179e23;
+  static constexpr double air_dyn_visc = 1.78e-5;  // constants.F90:65
   static constexpr double univ_gas_const = 8.314472;
   static constexpr double accom_coeff = 1.0;
   static constexpr double water_eq_vap_press = 611.0;
@@ -125,6 +126,21 @@ double binomial_pmf(int n, double p, int k);       // test/rand/test_binomial_sa
 // ---------------------------------------------------------------- util.F90
 double sphere_vol2rad(double v);                   // util.F90:240
 double sphere_rad2vol(double r);                   // util.F90:265
+// ---------------------------------------------------------------- fractal.F90
+// aero_data%fractal (fractal.F90:55-66): ONE setting per run in the reference; here one per process (set_fractal),
+// read by every radius <-> volume conversion of the sort / coagulation path (aero_data_vol2rad, aero_data_rad2vol,
+// aero_data.F90:101-140).  Defaults = fractal_set_spherical (fractal.F90:73-82).  The mobility-radius conversions
+// (fractal.F90:239-440) that the Brownian and sedimentation kernels and dry deposition apply to non-spherical
+// particles are NOT restated: those functions die when the setting is not spherical.
+struct Fractal {
+  double frac_dim = 3.0, prime_radius = 1e-8, vol_fill_factor = 1.0;
+};
+void set_fractal(double frac_dim, double prime_radius, double vol_fill_factor);
+const Fractal& fractal();
+bool fractal_is_spherical();                        // fractal.F90:296-307
+double fractal_vol_to_num_of_monomers(double v);    // fractal.F90:90-100
+double aero_vol2rad(double v);                      // fractal_vol2rad, fractal.F90:106-121
+double aero_rad2vol(double r);                      // fractal_rad2vol, fractal.F90:142-158
 std::vector<double> linspace(double min_x, double max_x, int n);  // util.F90:460
 std::vector<double> logspace(double min_x, double max_x, int n);  // util.F90:492
 int linspace_find(double min_x, double max_x, int n, double x);   // util.F90:532
@@ -237,7 +253,7 @@ int awa_rand_group(const WeightArray& a, int i_class, double radius, Stream& s);
 
 // ---------------------------------------------------------------- particle
 double particle_volume(const Particle& p);                       // aero_particle.F90:316
-double particle_radius(const Particle& p);                       // :388 (spherical, fractal.F90:113)
+double particle_radius(const Particle& p);                       // :388-399 (aero_data_vol2rad)
 double particle_mass(const Particle& p, const AeroData& d);      // :252
 double particle_density(const Particle& p, const AeroData& d);   // :474
 double particle_solute_volume(const Particle& p, const AeroData& d);  // :687
@@ -249,7 +265,10 @@ double awa_num_conc(const WeightArray& a, const Particle& p);    // aero_weight_
 double awa_single_num_conc(const WeightArray& a, const Particle& p);  // :218-227
 
 // ---------------------------------------------------------------- coagulation kernels
-enum { KERNEL_SEDI = 1, KERNEL_ADDITIVE = 2, KERNEL_CONSTANT = 3, KERNEL_BROWN = 4, KERNEL_ZERO = 5 };
+enum { KERNEL_SEDI = 1, KERNEL_ADDITIVE = 2, KERNEL_CONSTANT = 3, KERNEL_BROWN = 4, KERNEL_ZERO = 5,
+       KERNEL_BROWN_FREE = 6, KERNEL_BROWN_CONT = 7 };  // coag_kernel.F90:29-45
+double kernel_brown_free_helper(double v1, double d1, double v2, double d2, double temp);  // coag_kernel_brown_free.F90:118-147
+double kernel_brown_cont_helper(double v1, double d1, double v2, double d2, double temp);  // coag_kernel_brown_cont.F90:117-144
 double kernel_sedi_helper(double v1, double v2);  // coag_kernel_sedi.F90:79-103
 double kernel_brown_helper(double vol_i, double den_i, double vol_j, double den_j, double temp,
                            double pressure);  // coag_kernel_brown.F90:111-197

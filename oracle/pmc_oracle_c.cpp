@@ -222,6 +222,18 @@ int pmco_kernel_bounds(void* h, int cell, int kernel_type, double* kmin, double*
   ORACLE_CATCH(d)
 }
 double pmco_kernel_sedi(double v1, double v2) { return kernel_sedi_helper(v1, v2); }
+// process-wide fractal setting (aero_data%fractal); spherical = (3, 1e-8, 1)
+void pmco_set_fractal(double frac_dim, double prime_radius, double vol_fill_factor) {
+  set_fractal(frac_dim, prime_radius, vol_fill_factor);
+}
+double pmco_aero_vol2rad(double v) { return aero_vol2rad(v); }
+double pmco_aero_rad2vol(double r) { return aero_rad2vol(r); }
+double pmco_kernel_brown_free(double v1, double d1, double v2, double d2, double T) {
+  return kernel_brown_free_helper(v1, d1, v2, d2, T);
+}
+double pmco_kernel_brown_cont(double v1, double d1, double v2, double d2, double T) {
+  return kernel_brown_cont_helper(v1, d1, v2, d2, T);
+}
 double pmco_kernel_brown(double v1, double d1, double v2, double d2, double T, double p) {
   return kernel_brown_helper(v1, d1, v2, d2, T, p);
 }

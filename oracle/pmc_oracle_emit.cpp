@@ -91,7 +91,7 @@ double aero_mode_sample_radius(const AeroMode& m, const Weight& w, double prob_t
     return std::pow(10.0, rand_normal_threshold(x_mean_prime, m.log10_std_dev_radius, prob_threshold, s));
   } else if (m.type == MODE_EXP) {
     if (w.type != WEIGHT_NONE) die_msg(678481276, "cannot use exponential modes with weighting");
-    return sphere_vol2rad(-sphere_rad2vol(m.char_radius) * std::log(s.next()));
+    return aero_vol2rad(-aero_rad2vol(m.char_radius) * std::log(s.next()));  // aero_mode.F90:611
   }
   return m.char_radius;
 }
@@ -156,7 +156,7 @@ int aero_state_add_aero_dist_sample(AeroState& st, const AeroData& d, const std:
       for (int i_samp = 1; i_samp <= n_samp; i_samp++) {
         Stream s(rc.rng, rc.key(PH_EMIT, a, (uint32_t)i_samp));
         const double radius = aero_mode_sample_radius(m, st.awa.at(g, c), size_factor, s);
-        const double total_vol = sphere_rad2vol(radius);
+        const double total_vol = aero_rad2vol(radius);  // aero_state.F90:817
         aero_mode_sample_vols(m, total_vol, vols, s);
         Particle p;  // aero_particle_zero
         p.vol = vols;

@@ -361,7 +361,7 @@ static int aero_state_resample(AeroState& st, const AeroData& data, const std::v
           for (int i_samp = 1; i_samp <= n_samp_mode; i_samp++) {
             Stream s(rc.rng, rc.key(PH_BND, am, (uint32_t)i_samp));
             const double radius = aero_mode_sample_radius(m, st.awa.at(g, c), size_factor, s);
-            const double total_vol = sphere_rad2vol(radius);
+            const double total_vol = aero_rad2vol(radius);
             aero_mode_sample_vols(m, total_vol, vols, s);
             Particle p;
             p.vol = vols;

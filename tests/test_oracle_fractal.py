@@ -1,0 +1,183 @@
+"""Fractal particles on the coagulation path and the two kernels of Vemury and Pratsinis [1995]
+(partmc/src/fractal.F90:55-158, coag_kernel_brown_free.F90, coag_kernel_brown_cont.F90): the oracle against the
+reference's own tests partmc/test/fractal:
+  * test_fractal_1 (test_fractal_radii_conversion.F90), geometric-radius half: vol2rad(rad2vol(R)) == R for
+    d_f in 1.8..3, f in {1, 1.43}, R0 in 1e-10..1e-7 (the mobility-radius half is not restated);
+  * test_fractal_2 / test_fractal_3: decay of the number concentration from a mono-disperse start, free molecular
+    regime d_f = 2.4 and continuum regime d_f = 1.8, against the golden tables (tests/golden/fractal_dimless_time.json,
+    copied from the reference by tests/golden/make_fractal_golden.py), numeric_diff --by col --rel-tol 0.1.
+The helpers are shared with tests/test_gpu_fractal.py."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import common
+
+KB, AIR_DYN_VISC = 1.3806505e-23, 1.78e-5  # constants.F90:35, :65
+N_PART, N_INIT, DENSITY = 10000, 1e14, 4200.0  # run_part_brown_*_upto1000s.spec, aero_init_dist_*.dat, aero_data.dat
+
+REGIMES = {
+    # frac_dim, prime_radius (= initial geometric radius, diam 1e-9 / 5e-7), temp_free.dat / temp_cont.dat
+    "free_df_2_4": dict(df=2.4, R0=5e-10, T=1800.0),
+    "cont_df_1_8": dict(df=1.8, R0=2.5e-7, T=300.0),
+}
+
+
+def golden():
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fractal_dimless_time.json")) as f:
+        return json.load(f)
+
+
+def kernel_type(M, regime):
+    return M.KERNEL_BROWN_FREE if regime.startswith("free") else M.KERNEL_BROWN_CONT
+
+
+def time_scale(regime):
+    """test_fractal_dimless_time.F90:126-135"""
+    p = REGIMES[regime]
+    if regime.startswith("free"):
+        return (6.0 * KB * p["T"] * p["R0"] / DENSITY) ** 0.5 * N_INIT
+    return 2.0 * KB * p["T"] / 3.0 / AIR_DYN_VISC * N_INIT
+
+
+def initial_oracle(O, regime, seed, n_part=N_PART):
+    """do_select_weighting no -> AERO_STATE_WEIGHT_NUMMASS_SOURCE (partmc.F90:480-483): a flat and a power -3 weight
+    group, each sampling the mono-disperse initial mode (aero_state_add_aero_dist_sample); O.set_fractal must be
+    active (the caller resets it)"""
+    p = REGIMES[regime]
+    data = O.AeroData([DENSITY], [0.0], [1e-3], [0], 0)
+    o = O.Oracle(1, data, n_group=2, n_class=1, n_part_ideal=float(n_part), seed=seed)
+    o.set_weights(0, np.array([[1, 2]], np.int32), np.array([[1.0, 1.0]]), np.array([[0.0, -3.0]]))
+    o.set_env(0, T=p["T"], p=1e5)
+    n = o.add_aero_dist_sample(0, [3], [1], [p["R0"]], [0.0], [[1.0]], [N_INIT], 1.0, 1.0)
+    assert 0.85 * n_part < n < 1.15 * n_part
+    return o
+
+
+def geometric_radius(vol, p):
+    """fractal_vol2rad (fractal.F90:106-121) with vol_fill_factor 1"""
+    n_mono = ((3.0 * vol / (4.0 * np.pi)) ** (1.0 / 3.0) / p["R0"]) ** 3
+    return p["R0"] * n_mono ** (1.0 / p["df"])
+
+
+def total_num_conc(vol, weights, p):
+    """aero_state_total_num_conc: harmonic combination of the groups' weights at the particle's geometric radius
+    (aero_weight_array_num_conc_at_radius, aero_weight_array.F90:232-251)"""
+    wt, wm, we = [np.asarray(a).ravel() for a in weights]
+    radius = geometric_radius(np.asarray(vol).ravel(), p)
+    inv = sum(1.0 / (wm[g] * (radius ** we[g] if wt[g] == 2 else 1.0)) for g in range(wt.size))
+    return float((1.0 / inv).sum())
+
+
+def schedule():
+    """(del_t, steps, output every) of run_part_brown_*_upto1000s.spec and of the restart run"""
+    return ((10.0, 100, 5), (100.0, 650, 50))
+
+
+def rel_col_err(ref, got):
+    """numeric_diff --by col: norm of the column difference over the norm of the reference column"""
+    ref, got = np.asarray(ref), np.asarray(got)
+    return np.sqrt(((ref - got) ** 2).sum(axis=0)) / np.sqrt((ref ** 2).sum(axis=0))
+
+
+@pytest.fixture
+def fractal_setting():
+    """the oracle's fractal setting is process-wide (like aero_data%fractal, one per run): always reset"""
+    from oracle import oracle as O
+    yield O
+    O.set_fractal()
+
+
+def test_geometric_radius_round_trip(fractal_setting):
+    O = fractal_setting
+    for R0 in (1e-10, 1e-9, 1e-8, 1e-7):
+        for f in (1.0, 1.43):
+            for df in (1.8, 2.0, 2.2, 2.4, 2.6, 2.8, 3.0):
+                O.set_fractal(df, R0, f)
+                for R in np.exp(np.linspace(np.log(R0), np.log(R0 * 1e3), 100)):
+                    back = O.aero_vol2rad(O.aero_rad2vol(R))
+                    assert abs(back - R) <= 1e-8 * abs(back + R) / 2.0, (R0, f, df, R)  # almost_equal (util.F90)
+    # one monomer has the prime radius whatever the dimension; the spherical setting is the sphere formula
+    O.set_fractal(2.1, 3e-9, 1.0)
+    assert O.aero_vol2rad(4.0 * np.pi * 3e-9 ** 3 / 3.0) == pytest.approx(3e-9, rel=1e-14)
+    O.set_fractal()
+    assert O.aero_rad2vol(2e-8) == 4.0 * np.pi * (2e-8 * 2e-8 * 2e-8) / 3.0
+
+
+def test_kernel_values(fractal_setting):
+    """monomer-monomer values follow from Eq. 4 / Eq. 6 directly; homogeneity in the monomer numbers"""
+    O = fractal_setting
+    R0, df, T, rho = 5e-10, 2.4, 1800.0, DENSITY
+    O.set_fractal(df, R0, 1.0)
+    v1 = O.aero_rad2vol(R0)
+    assert O.kernel_brown_free(v1, rho, v1, rho, T) == pytest.approx((6 * KB * T * R0 / rho * 2.0) ** 0.5 * 4.0, rel=1e-13)
+    assert O.kernel_brown_cont(v1, rho, v1, rho, T) == pytest.approx(2 * KB * T / 3 / AIR_DYN_VISC * 4.0, rel=1e-13)
+    # continuum regime: equal particles always give 4 x the prefactor; unequal ones more
+    v8, v27 = 8.0 * v1, 27.0 * v1
+    k88 = O.kernel_brown_cont(v8, rho, v8, rho, T)
+    assert k88 == pytest.approx(2 * KB * T / 3 / AIR_DYN_VISC * 4.0, rel=1e-12)
+    assert O.kernel_brown_cont(v8, rho, v27, rho, T) > k88
+    assert O.kernel_brown_cont(v8, rho, v27, rho, T) == O.kernel_brown_cont(v27, 1.0, v8, 9.9, T)  # no density in Eq. 6
+    # free regime: N monomers each -> sqrt(2 / N) * (2 N^(1/df))^2 times the monomer prefactor
+    n = 8.0
+    want = (6 * KB * T * R0 / rho * (2.0 / n)) ** 0.5 * (2.0 * n ** (1.0 / df)) ** 2
+    assert O.kernel_brown_free(v8, rho, v8, rho, T) == pytest.approx(want, rel=1e-12)
+    # the density of the pair is the volume-weighted mean
+    k_mix = O.kernel_brown_free(v8, 1000.0, v27, 2000.0, T)
+    rho_mix = (8.0 * 1000.0 + 27.0 * 2000.0) / 35.0
+    assert k_mix == pytest.approx(O.kernel_brown_free(v8, rho_mix, v27, rho_mix, T), rel=1e-13)
+
+
+def run_reference_case(O, regime, seed):
+    p = REGIMES[regime]
+    O.set_fractal(p["df"], p["R0"], 1.0)
+    o = initial_oracle(O, regime, seed)
+    kt, scale = kernel_type(O, regime), time_scale(regime)
+    rows = [(0.0, total_num_conc(o.get_cell(0)["vol"], o.get_weights(0), p) / N_INIT)]
+    t, step = 0.0, 0
+    for del_t, n_step, every in schedule():
+        for k in range(1, n_step + 1):
+            step += 1
+            o.sort(0, force_resort=True, physical=True, edge_recheck=True)
+            o.mc_coag(0, kt, del_t, step=step)
+            o.rebalance(0, True, True, step=step)  # allow_doubling / allow_halving yes
+            t += del_t
+            if k % every == 0:
+                rows.append((scale * t, total_num_conc(o.get_cell(0)["vol"], o.get_weights(0), p) / N_INIT))
+    return np.array(rows), o
+
+
+@pytest.mark.parametrize("regime", ["free_df_2_4", "cont_df_1_8"])
+def test_oracle_against_reference_tables(fractal_setting, regime):
+    """test_fractal_2.sh / test_fractal_3.sh.  The tables come from the literature curves, the particle run carries
+    the first-order time discretisation of mc_coag (bin pairs visited later in a step see the particles the earlier
+    ones made): seeds 1..5 give column errors of 0.092-0.099 here (0.090-0.107 when the run starts from an uploaded copy
+    of the sampled state, tests/test_gpu_fractal.py), around the reference's bound of 0.1
+    (the reference's own run takes a random seed, rand_init 0)."""
+    O = fractal_setting
+    got, o = run_reference_case(O, regime, seed=1)
+    ref = np.array(golden()[regime])
+    assert got.shape == ref.shape == (34, 2)
+    err = rel_col_err(ref, got)
+    assert err[0] < 0.01 and err[1] < 0.1, err
+    # three to five decades of decay with ~10^4 computational particles throughout (doubling)
+    assert got[-1, 1] < 5e-4 and 4000 < o.count(0) < 12000
+    # mass is conserved by coagulation and, on average, by doubling: within the sampling noise
+    q, (wt, wm, we) = o.get_cell(0), [np.asarray(a).ravel() for a in o.get_weights(0)]
+    p = REGIMES[regime]
+    radius = geometric_radius(q["vol"][0], p)
+    nc = 1.0 / sum(1.0 / (wm[g] * (radius ** we[g] if wt[g] == 2 else 1.0)) for g in range(2))
+    mass0 = N_INIT * 4.0 * np.pi * p["R0"] ** 3 / 3.0
+    assert (nc * q["vol"][0]).sum() == pytest.approx(mass0, rel=0.1)
+
+
+def test_mobility_radius_kernels_refuse_fractal_particles(fractal_setting):
+    O = fractal_setting
+    O.set_fractal(2.4, 5e-10, 1.0)
+    o = initial_oracle(O, "free_df_2_4", seed=3, n_part=500)
+    o.sort(0, force_resort=True, physical=True, edge_recheck=True)
+    for kt in (O.KERNEL_BROWN, O.KERNEL_SEDI):
+        with pytest.raises(Exception):
+            o.mc_coag(0, kt, 1.0, step=1)

@@ -8,4 +8,4 @@ fallback: importing works anywhere, but every call needs the built library and
 a CUDA device.
 """
 from .host.pmcgpu import (AeroData, PartMCGPU, PmcGpuError, comm_unique_id, library_path, load_library,  # noqa: F401
-                          KERNEL_ADDITIVE, KERNEL_BROWN, KERNEL_CONSTANT, KERNEL_SEDI, KERNEL_ZERO, WEIGHT_NONE, WEIGHT_POWER)
+                          KERNEL_ADDITIVE, KERNEL_BROWN, KERNEL_BROWN_CONT, KERNEL_BROWN_FREE, KERNEL_CONSTANT, KERNEL_SEDI, KERNEL_ZERO, WEIGHT_NONE, WEIGHT_POWER)

@@ -24,6 +24,23 @@
 #include "pmcgpu_internal.cuh"
 #include "sedi.cuh"
 
+// This file is compiled twice.  Plain (coag.o): spherical particles, the conversions below are the sphere
+// formulas and nothing of the fractal treatment is in the code of the WRF path (k_mc_coag is bound by instruction
+// fetch).  With PMC_COAG_FRACTAL (coag_fractal.cu includes this file): aero_data_vol2rad / aero_data_rad2vol
+// (aero_data.F90:101-140) with the fractal parameters of the context, plus the brown_free / brown_cont kernels;
+// pmc_mc_coag_async hands over to that build when pmcgpu_set_fractal made the particles non-spherical or one of
+// the two kernels is asked for.  Each build lives in its own namespace (the kernel templates would collide).
+#ifdef PMC_COAG_FRACTAL
+#define PMC_COAG_NS coag_fractal
+#define CX_VOL2RAD(x) fr_vol2rad(*cx.v, (x))
+#define CX_RAD2VOL(x) fr_rad2vol(*cx.v, (x))
+#else
+#define PMC_COAG_NS coag_sphere
+#define CX_VOL2RAD(x) vol2rad(x)
+#define CX_RAD2VOL(x) rad2vol(x)
+#endif
+namespace PMC_COAG_NS {
+
 #ifndef COAG_MIN_CTAS
 #define COAG_MIN_CTAS 12  // 40 registers: measured 28.2 (5) / 27.4 (6) / 23.3 (8) / 22.1 (10) / 20.2 (12) / 20.1 (16) ms per K4 step
 #endif
@@ -67,7 +84,7 @@ __device__ __forceinline__ void part_vol_mass(const CellCtx& cx, int p, double& 
 // coag_kernel.F90:346-377
 __device__ __noinline__ double coag_num_conc_factor(const CellCtx& cx, double i_r, double j_r, int ic, int jc,
                                                        int ijc) {
-  const double ij_r = vol2rad(rad2vol(i_r) + rad2vol(j_r));
+  const double ij_r = CX_VOL2RAD(CX_RAD2VOL(i_r) + CX_RAD2VOL(j_r));
   const double i_nc = awa_nc_at_radius(*cx.v, cx.cell, ic, i_r);
   const double j_nc = awa_nc_at_radius(*cx.v, cx.cell, jc, j_r);
   const double ij_nc = awa_nc_at_radius(*cx.v, cx.cell, ijc, ij_r);
@@ -251,6 +268,11 @@ __device__ __noinline__ void cell_list_append(CellCtx& cx, int c, int b, int slo
 
 // KT: the kernel type when it is known at compile time (the Brownian instance carries no code of the other
 // kernels: mc_coag is instruction-fetch bound), 0 = decided by ktype at run time
+#ifdef PMC_COAG_FRACTAL
+#define UNWEIGHTED_KERNEL(ktype, be, v1, m1, v2, m2) unweighted_kernel_fr(*cx.v, cx.cell, ktype, be, v1, m1, v2, m2)
+#else
+#define UNWEIGHTED_KERNEL(ktype, be, v1, m1, v2, m2) unweighted_kernel<KT>(ktype, be, v1, m1, v2, m2)
+#endif
 template <int KT>
 __device__ __forceinline__ double unweighted_kernel(int ktype, const BrownEnv& be, double v1, double m1, double v2,
                                                     double m2) {
@@ -266,6 +288,15 @@ __device__ __forceinline__ double unweighted_kernel(int ktype, const BrownEnv& b
   }
   return 0.0;
 }
+#ifdef PMC_COAG_FRACTAL
+// kernel (coag_kernel.F90:99-124) with the two kernels of Vemury and Pratsinis [1995]; densities = mass / volume
+__device__ __noinline__ double unweighted_kernel_fr(const DevView& v, int cell, int ktype, const BrownEnv& be, double v1,
+                                                    double m1, double v2, double m2) {
+  if (ktype == PMCGPU_KERNEL_BROWN_FREE) return kernel_brown_free(v, v1, m1 / v1, v2, m2 / v2, v.temp[cell]);
+  if (ktype == PMCGPU_KERNEL_BROWN_CONT) return kernel_brown_cont(v, v1, v2, v.temp[cell]);
+  return unweighted_kernel<0>(ktype, be, v1, m1, v2, m2);
+}
+#endif
 
 // coagulate (coagulation.F90:928-985) + coagulate_weighting (:810-922) for the
 // particles in slots p1, p2 (0-based); warp-cooperative, uniform arguments.
@@ -275,8 +306,8 @@ __device__ __noinline__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1,
   double v1, m1, v2, m2;
   part_vol_mass(cx, p1, v1, m1);
   part_vol_mass(cx, p2, v2, m2);
-  const double r1 = vol2rad(v1), r2 = vol2rad(v2);
-  const double rc = vol2rad(rad2vol(r1) + rad2vol(r2));
+  const double r1 = CX_VOL2RAD(v1), r2 = CX_VOL2RAD(v2);
+  const double rc = CX_VOL2RAD(CX_RAD2VOL(r1) + CX_RAD2VOL(r2));
   const double nc1 = awa_nc_at_radius(v, cx.cell, c1, r1);
   const double nc2 = awa_nc_at_radius(v, cx.cell, c2, r2);
   const double ncc = awa_nc_at_radius(v, cx.cell, cc, rc);
@@ -359,7 +390,7 @@ __device__ __noinline__ void cell_coagulate(CellCtx& cx, int p1, int p2, int c1,
   if (create_new) {
     double vt = 0.0;
     for (int s = 0; s < v.S; s++) vt += __shfl_sync(0xffffffffu, volc[s >> 5], s & 31);
-    const int b_new = log_grid_find(cx.lnmin, cx.lnmax, cx.nb, log(vol2rad(vt)));
+    const int b_new = log_grid_find(cx.lnmin, cx.lnmax, cx.nb, log(CX_VOL2RAD(vt)));
     if (b_new < 1 || b_new > cx.nb) {
       cx.err = PMCGPU_ERR_BIN_RANGE;
       return;
@@ -498,7 +529,7 @@ __device__ __noinline__ void cell_dup_particle(CellCtx& cx, int p, int c, double
     if (random_weight_group) {
       double vt, mt;
       part_vol_mass(cx, p, vt, mt);
-      new_group = rand_group_seq(cx, c, vol2rad(vt), s);
+      new_group = rand_group_seq(cx, c, CX_VOL2RAD(vt), s);
     }
     if (cx.n_part >= v.cap) {
       cx.err = PMCGPU_ERR_CAPACITY;
@@ -543,7 +574,7 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
     const int target0 = cx.L[cx.lptr[kt] + e - 1];
     double v_t, m_t;
     part_vol_mass(cx, target0, v_t, m_t);
-    const double r_t = vol2rad(v_t);
+    const double r_t = CX_VOL2RAD(v_t);
     RStream s{RKey{v.seed, (unsigned)v.gcell[cx.cell], step, PH_COAG_ACCEL, pid, (unsigned)e}, 0u};
     const RKey skey{v.seed, (unsigned)v.gcell[cx.cell], step, PH_COAG_ACCEL, pid | 0x80000000u, (unsigned)e};
     int n_samp = 0, n_coag = 0, n_avg = 0;
@@ -582,8 +613,8 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
         i_part = cx.L[cx.lptr[ks] + pmc_rand_int(rng_uniform(skey, j0), ne) - 1];
         double v_i, m_i;
         part_vol_mass(cx, i_part, v_i, m_i);
-        const double r_i = vol2rad(v_i);
-        const double uk = unweighted_kernel<KT>(ktype, be, v_i, m_i, v_t, m_t);
+        const double r_i = CX_VOL2RAD(v_i);
+        const double uk = UNWEIGHTED_KERNEL(ktype, be, v_i, m_i, v_t, m_t);
         prob_coag = (uk * coag_num_conc_factor(cx, r_i, r_t, cs, ct, ct)) * accept_factor;
         u_acc = rng_uniform(skey, j0 + 1);
         u_rem = rng_uniform(skey, j0 + 2);
@@ -657,7 +688,7 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
       const int tp = cx.L[cx.lptr[kt] + e - 1];  // re-read: removals may have moved the target
       double v_old, m_old;
       part_vol_mass(cx, tp, v_old, m_old);
-      const double old_num_conc_target = awa_nc_at_radius(v, cx.cell, ct, vol2rad(v_old));
+      const double old_num_conc_target = awa_nc_at_radius(v, cx.cell, ct, CX_VOL2RAD(v_old));
       __syncwarp();
       if (COLD) {
         const LaneComp merged = comp_merge(comp_load(cx, tp), v.nprim[cx.base + tp], src_comp, src_nprim, ckey, 64u, cx.lane);
@@ -678,7 +709,7 @@ __device__ __noinline__ void cell_accel_pair(CellCtx& cx, int ktype, const Brown
       __syncwarp();
       double v_new, m_new;
       part_vol_mass(cx, tp, v_new, m_new);
-      const double r_new = vol2rad(v_new);
+      const double r_new = CX_VOL2RAD(v_new);
       const int new_group = rand_group_seq(cx, cc, r_new, s);
       if (cx.lane == 0) v.wgc[cx.base + tp] = (cc - 1) * v.G + (new_group - 1);
       const int new_bin = log_grid_find(cx.lnmin, cx.lnmax, cx.nb, log(r_new));
@@ -850,7 +881,7 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, MIN_CTAS) k_mc_coag(const __g
             } else {
               // coag_dest_class: sic, both radii from bin b1 (coag_kernel.F90:402-403)
               const double i_r = grid_center(cx.gmin, cx.gmax, nb, b1);
-              const double ij_r = vol2rad(rad2vol(i_r) + rad2vol(i_r));
+              const double ij_r = CX_VOL2RAD(CX_RAD2VOL(i_r) + CX_RAD2VOL(i_r));
               cc = (awa_nc_at_radius(v, cell, c1, ij_r) < awa_nc_at_radius(v, cell, c2, ij_r)) ? c1 : c2;
               const double i_lo = grid_edge(cx.gmin, cx.gmax, nb, b1), i_hi = grid_edge(cx.gmin, cx.gmax, nb, b1 + 1);
               const double j_lo = grid_edge(cx.gmin, cx.gmax, nb, my_b2), j_hi = grid_edge(cx.gmin, cx.gmax, nb, my_b2 + 1);
@@ -869,8 +900,8 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, MIN_CTAS) k_mc_coag(const __g
               if (accel_target_source(cx, pair_flat, hm, b1, my_b2, c1, c2, cc, bt, bs, ct, cs)) {
                 const double n_source_per_target = k_max * del_t * (double)((bs == b1 && cs == c1) ? n1 : n2);
                 if (!(n_source_per_target < COAG_ACCEL_N_EVENT)) {
-                  const double min_target_vol = rad2vol(grid_edge(cx.gmin, cx.gmax, nb, bt));
-                  const double max_source_vol = rad2vol(grid_edge(cx.gmin, cx.gmax, nb, bs + 1));
+                  const double min_target_vol = CX_RAD2VOL(grid_edge(cx.gmin, cx.gmax, nb, bt));
+                  const double max_source_vol = CX_RAD2VOL(grid_edge(cx.gmin, cx.gmax, nb, bs + 1));
                   const double growth = (min_target_vol + max_source_vol * n_source_per_target) / min_target_vol;
                   if (!(growth > MAX_ALLOWABLE_GROWTH_FACTOR)) accel = 1;
                 }
@@ -939,8 +970,8 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, MIN_CTAS) k_mc_coag(const __g
                 double v1, ms1, v2, ms2;
                 part_vol_mass(cx, p1, v1, ms1);
                 part_vol_mass(cx, p2, v2, ms2);
-                const double uk = unweighted_kernel<KT>(ktype, be, v1, ms1, v2, ms2);
-                const double k = uk * coag_num_conc_factor(cx, vol2rad(v1), vol2rad(v2), p_c1, p_c2, p_cc);
+                const double uk = UNWEIGHTED_KERNEL(ktype, be, v1, ms1, v2, ms2);
+                const double k = uk * coag_num_conc_factor(cx, CX_VOL2RAD(v1), CX_VOL2RAD(v2), p_c1, p_c2, p_cc);
                 accept = rng_uniform(key, 2) < k * accept_factor;  // maybe_coag_pair :753
               }
               const unsigned acc = __ballot_sync(0xffffffffu, accept);
@@ -981,10 +1012,33 @@ __global__ void __launch_bounds__(COAG_WARPS * 32, MIN_CTAS) k_mc_coag(const __g
   }
 }
 
+}  // namespace PMC_COAG_NS
+using namespace PMC_COAG_NS;
+
 int pmc_kernel_bounds_async(pmcgpu_ctx* ctx, int ktype);
 
+#ifdef PMC_COAG_FRACTAL
+// mc_coag for fractal particles and / or the brown_free and brown_cont kernels (called by pmc_mc_coag_async)
+int pmc_mc_coag_fractal_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step) {
+  DevView& v = ctx->v;
+  int rc = pmc_kernel_bounds_async(ctx, ktype);  // rejects the kernels that need the mobility radius
+  if (rc) return rc;
+  const size_t smem = (size_t)COAG_WARPS * v.C * (sizeof(double) + sizeof(int));
+  const int blocks = (v.n_cells + COAG_WARPS - 1) / COAG_WARPS;
+  ProfScope ps_(ctx, "k_mc_coag");
+  if (v.cold.n)
+    k_mc_coag<0, true, COAG_MIN_CTAS><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+  else
+    k_mc_coag<0, false, COAG_MIN_CTAS><<<blocks, COAG_WARPS * 32, smem, ctx->stream>>>(v, ktype, del_t, step);
+  LAUNCH_CHECK(ctx);
+  return PMCGPU_OK;
+}
+#else
+int pmc_mc_coag_fractal_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step);
 int pmc_mc_coag_async(pmcgpu_ctx* ctx, int ktype, double del_t, unsigned step) {
   DevView& v = ctx->v;
+  if (v.fr_on || ktype == PMCGPU_KERNEL_BROWN_FREE || ktype == PMCGPU_KERNEL_BROWN_CONT)
+    return pmc_mc_coag_fractal_async(ctx, ktype, del_t, step);
   // coagulation.F90:64-70: bounds are (re)computed only when the grid was remade
   int rc = pmc_kernel_bounds_async(ctx, ktype);
   if (rc) return rc;
@@ -1034,3 +1088,4 @@ extern "C" int pmcgpu_mc_coag(pmcgpu_ctx* ctx, int coag_kernel_type, double del_
                                  ctx->stream));
   return pmc_first_status(ctx);
 }
+#endif  // PMC_COAG_FRACTAL

@@ -179,6 +179,7 @@ __global__ void k_num_concs_by_source(DevView v, int n_source, double* __restric
 }
 
 extern "C" int pmcgpu_num_concs_by_source(pmcgpu_ctx* ctx, int n_source, double* out) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_num_concs_by_source");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || n_source < 1 || !out) return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;

@@ -1772,6 +1772,7 @@ extern "C" int pmcgpu_set_condense_method(pmcgpu_ctx* ctx, int method) {
 extern "C" int pmcgpu_condense_particles(pmcgpu_ctx* ctx, const double* temp_final, const double* pressure_final,
                                          double del_t, double reltol, double* rel_humid_out, int* stats_out,
                                          double* water_rel_error_out) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_condense_particles");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !temp_final || !pressure_final || !(del_t > 0.0)) return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;
@@ -1847,6 +1848,7 @@ __global__ void k_condense_equilib(DevView v) {
   }
 }
 extern "C" int pmcgpu_condense_equilib_particles(pmcgpu_ctx* ctx) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_condense_equilib_particles");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx) return PMCGPU_ERR_ARG;
   if (ctx->v.i_water < 1) return PMCGPU_ERR_ARG;

@@ -125,6 +125,10 @@ extern "C" int pmcgpu_create(const pmcgpu_config* cfg, pmcgpu_ctx** out) {
   ctx->h_density.assign(cfg->density, cfg->density + v.S);
   v.dens_min = *std::min_element(ctx->h_density.begin(), ctx->h_density.end());
   v.dens_max = *std::max_element(ctx->h_density.begin(), ctx->h_density.end());
+  v.fr_df = 3.0;  // fractal_set_spherical (fractal.F90:73-82)
+  v.fr_r0 = 1e-8;
+  v.fr_fill = 1.0;
+  v.fr_on = 0;
   if (!cfg->periodic_x || !cfg->periodic_y) {
     // The reference treats every domain that is not doubly periodic as open in both directions
     // (get_array_extents, wrf_pmc_trans_aero.F90:1665-1705)

@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(DEP_WARPS * 32) k_dep_dry(DevView v, int nx, i
 }
 
 extern "C" int pmcgpu_wrf_pmc_dep_dry_driver(pmcgpu_ctx* ctx, const pmcgpu_dep_args* a) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_wrf_pmc_dep_dry_driver");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !a || !a->rmol || !a->znt || !a->ust || !a->ivgtyp || !a->height || !(a->dt > 0.0)) return PMCGPU_ERR_ARG;
   const pmcgpu_config& cfg = ctx->cfg;

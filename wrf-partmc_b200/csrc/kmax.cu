@@ -63,14 +63,31 @@ __global__ void __launch_bounds__(KMAX_THREADS) k_kernel_bounds(DevView v, int k
     for (int q = threadIdx.x; q < nb * nb; q += blockDim.x) {
       const int b1 = q % nb + 1, b2 = q / nb + 1;
       double kmax = 0.0;
-      if (ktype == PMCGPU_KERNEL_ADDITIVE || ktype == PMCGPU_KERNEL_SEDI) {
-        const double v1l = rad2vol(grid_edge(gmin, gmax, nb, b1)), v1h = rad2vol(grid_edge(gmin, gmax, nb, b1 + 1));
-        const double v2l = rad2vol(grid_edge(gmin, gmax, nb, b2)), v2h = rad2vol(grid_edge(gmin, gmax, nb, b2 + 1));
+      if (ktype == PMCGPU_KERNEL_ADDITIVE || ktype == PMCGPU_KERNEL_SEDI || ktype == PMCGPU_KERNEL_BROWN_FREE ||
+          ktype == PMCGPU_KERNEL_BROWN_CONT) {
+        // aero_data_rad2vol of the bin edges (coag_kernel.F90:316-321): fractal particles after pmcgpu_set_fractal
+        const double v1l = fr_rad2vol(v, grid_edge(gmin, gmax, nb, b1)), v1h = fr_rad2vol(v, grid_edge(gmin, gmax, nb, b1 + 1));
+        const double v2l = fr_rad2vol(v, grid_edge(gmin, gmax, nb, b2)), v2h = fr_rad2vol(v, grid_edge(gmin, gmax, nb, b2 + 1));
+        const double temp = v.temp[cell];
         for (int i = 1; i <= 3; i++)
           for (int j = 1; j <= 3; j++) {
             const double v1 = interp_linear_disc(v1l, v1h, 3, i);
             const double v2 = interp_linear_disc(v2l, v2h, 3, j);
-            const double k = (ktype == PMCGPU_KERNEL_SEDI) ? kernel_sedi(v1, v2) : BETA_1 * (v1 + v2);
+            double k;
+            if (ktype == PMCGPU_KERNEL_SEDI) {
+              k = kernel_sedi(v1, v2);
+            } else if (ktype == PMCGPU_KERNEL_ADDITIVE) {
+              k = BETA_1 * (v1 + v2);
+            } else if (ktype == PMCGPU_KERNEL_BROWN_CONT) {
+              k = kernel_brown_cont(v, v1, v2, temp);  // independent of the densities (coag_kernel_brown_cont.F90:62-107)
+            } else {
+              // kernel_brown_free_minmax (coag_kernel_brown_free.F90:62-108): 3 x 3 densities in [min rho, max rho]
+              k = 0.0;
+              for (int a = 1; a <= nd; a++)
+                for (int b = 1; b <= nd; b++)
+                  k = fmax(k, kernel_brown_free(v, v1, interp_linear_disc(v.dens_min, v.dens_max, 3, a), v2,
+                                                interp_linear_disc(v.dens_min, v.dens_max, 3, b), temp));
+            }
             kmax = (i == 1 && j == 1) ? k : fmax(kmax, k);
           }
       } else if (ktype == PMCGPU_KERNEL_CONSTANT) {
@@ -88,9 +105,15 @@ __global__ void __launch_bounds__(KMAX_THREADS) k_kernel_bounds(DevView v, int k
 int pmc_kernel_bounds_async(pmcgpu_ctx* ctx, int ktype) {
   DevView& v = ctx->v;
   if (ktype != PMCGPU_KERNEL_BROWN && ktype != PMCGPU_KERNEL_ADDITIVE && ktype != PMCGPU_KERNEL_CONSTANT &&
-      ktype != PMCGPU_KERNEL_ZERO && ktype != PMCGPU_KERNEL_SEDI) {
+      ktype != PMCGPU_KERNEL_ZERO && ktype != PMCGPU_KERNEL_SEDI && ktype != PMCGPU_KERNEL_BROWN_FREE &&
+      ktype != PMCGPU_KERNEL_BROWN_CONT) {
     ctx->err = "unknown kernel type";  // coag_kernel.F90:121 die_msg(200724934)
     return 200724934;
+  }
+  if (v.fr_on && (ktype == PMCGPU_KERNEL_BROWN || ktype == PMCGPU_KERNEL_SEDI)) {
+    ctx->err = "the Brownian and sedimentation kernels take the mobility radius of fractal particles "
+               "(fractal.F90:315-362), which is not built: use brown_free / brown_cont / additive / constant";
+    return PMCGPU_ERR_ARG;
   }
   const size_t smem = (size_t)v.nbcap * 9 * 4 * sizeof(double);
   if (smem > 48 * 1024 && smem > ctx->cfg_kmax_smem) {
@@ -116,5 +139,24 @@ extern "C" int pmcgpu_kernel_bounds(pmcgpu_ctx* ctx, int coag_kernel_type) {
   int rc = pmc_kernel_bounds_async(ctx, coag_kernel_type);
   if (rc) return rc;
   CUDA_OK(ctx, cudaStreamSynchronize(ctx->stream));
+  return PMCGPU_OK;
+}
+
+// aero_data%fractal (fractal.F90:55-66; spec file: do_fractal, frac_dim, prime_radius, vol_fill_factor).  The bin
+// grid and the majorant tables are functions of the geometric radius, so every cell gets a new grid at its next sort.
+extern "C" int pmcgpu_set_fractal(pmcgpu_ctx* ctx, double frac_dim, double prime_radius, double vol_fill_factor) {
+  if (!ctx) return PMCGPU_ERR_ARG;
+  if (cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;
+  if (!(frac_dim >= 1.0 && frac_dim <= 3.0) || !(prime_radius > 0.0) || !(vol_fill_factor >= 1.0)) {
+    ctx->err = "pmcgpu_set_fractal: 1 <= frac_dim <= 3, prime_radius > 0, vol_fill_factor >= 1";
+    return PMCGPU_ERR_ARG;
+  }
+  DevView& v = ctx->v;
+  v.fr_df = frac_dim;
+  v.fr_r0 = prime_radius;
+  v.fr_fill = vol_fill_factor;
+  v.fr_on = !(frac_dim == 3.0 && vol_fill_factor == 1.0);  // fractal_is_spherical (fractal.F90:296-307)
+  CUDA_OK(ctx, cudaMemsetAsync(v.grid_nb, 0, v.n_cells * sizeof(int), ctx->stream));
+  CUDA_OK(ctx, cudaMemsetAsync(v.bounds_valid, 0, v.n_cells * sizeof(int), ctx->stream));
   return PMCGPU_OK;
 }

@@ -32,6 +32,7 @@ struct PmcConst {  // partmc/src/constants.F90:30-65
   static constexpr double water_density = 1e3;
   static constexpr double air_molec_weight = 2.89644e-2;
   static constexpr double air_std_press = 101325.0;
+  static constexpr double air_dyn_visc = 1.78e-5;
 };
 
 // Cold part of the particle record (aero_particle.F90:53-61), carried only after pmcgpu_track_components:
@@ -116,6 +117,10 @@ struct DevView {
   // the aerosol step and the multinomial transport sampling cover interior cells only
   // (wrf_pmc_driver.F90:157-167, wrf_pmc_trans.F90:116-136, wrf_pmc_trans_aero.F90:497-506)
   const unsigned char* kind;
+  // aero_data%fractal (fractal.F90:55-66, pmcgpu_set_fractal): fr_on = 0 for spherical particles (the default and
+  // the WRF setting); read by the sort, the majorant tables and the fractal build of mc_coag only
+  double fr_df, fr_r0, fr_fill;
+  int fr_on;
 };
 
 // Transport work space of one patch (trans.cu).  "ext" arrays carry a one-cell ghost ring in x and y:
@@ -309,6 +314,16 @@ struct TmpDev {
 
 int pmc_first_status(pmcgpu_ctx* ctx);
 // brackets the launches of one scope with a pair of events on the context's stream
+// entry points whose formulas use the radius of a SPHERICAL particle (or the mobility radius, fractal.F90:239-440,
+// which is not built): refused while pmcgpu_set_fractal has a non-spherical setting
+#define PMC_SPHERICAL_ONLY(ctx, what)                                                                   \
+  do {                                                                                                  \
+    if ((ctx) && (ctx)->v.fr_on) {                                                                      \
+      (ctx)->err = what ": not built for fractal particles (pmcgpu_set_fractal has a non-spherical setting)"; \
+      return PMCGPU_ERR_ARG;                                                                            \
+    }                                                                                                   \
+  } while (0)
+
 struct ProfScope {
   pmcgpu_ctx* c;
   int idx;
@@ -450,6 +465,35 @@ static __device__ __noinline__ double vol2rad(double v) { return pow(3.0 * v / 4
 __device__ __forceinline__ double vol2rad(double v) { return pow(3.0 * v / 4.0 / PmcConst::pi, 1.0 / 3.0); }
 #endif
 __device__ __forceinline__ double rad2vol(double r) { return 4.0 * PmcConst::pi * (r * r * r) / 3.0; }
+// fractal.F90:90-100, 106-121, 142-158: number of monomers and geometric radius <-> mass-equivalent volume
+__device__ __forceinline__ double fr_monomers(const DevView& v, double vol) {
+  const double x = pow(3.0 * vol / 4.0 / PmcConst::pi, 1.0 / 3.0) / v.fr_r0;
+  return x * x * x;
+}
+__device__ __forceinline__ double fr_vol2rad(const DevView& v, double vol) {
+  if (!v.fr_on) return pow(3.0 * vol / 4.0 / PmcConst::pi, 1.0 / 3.0);
+  return v.fr_r0 * pow(fr_monomers(v, vol) * v.fr_fill, 1.0 / v.fr_df);
+}
+__device__ __forceinline__ double fr_rad2vol(const DevView& v, double r) {
+  if (!v.fr_on) return rad2vol(r);
+  return rad2vol(v.fr_r0) * pow(r / v.fr_r0, v.fr_df) / v.fr_fill;
+}
+// kernel_brown_free_helper (coag_kernel_brown_free.F90:118-147) and kernel_brown_cont_helper
+// (coag_kernel_brown_cont.F90:117-144): Eq. 4 and Eq. 6 of Vemury and Pratsinis [1995]
+__device__ __forceinline__ double kernel_brown_free(const DevView& v, double v1, double d1, double v2, double d2,
+                                                    double temp) {
+  const double rho = (v1 / (v1 + v2)) * d1 + (v2 / (v1 + v2)) * d2;
+  const double N_i = fr_monomers(v, v1), N_j = fr_monomers(v, v2);
+  const double N_i_inv_df = pow(N_i, 1.0 / v.fr_df), N_j_inv_df = pow(N_j, 1.0 / v.fr_df);
+  const double t = N_i_inv_df + N_j_inv_df;
+  return sqrt(6.0 * PmcConst::boltzmann * temp * v.fr_r0 / rho * (1.0 / N_i + 1.0 / N_j)) * (t * t);
+}
+__device__ __forceinline__ double kernel_brown_cont(const DevView& v, double v1, double v2, double temp) {
+  const double N_i = fr_monomers(v, v1), N_j = fr_monomers(v, v2);
+  const double N_i_inv_df = pow(N_i, 1.0 / v.fr_df), N_j_inv_df = pow(N_j, 1.0 / v.fr_df);
+  return 2.0 * PmcConst::boltzmann * temp / 3.0 / PmcConst::air_dyn_visc * (1.0 / N_i_inv_df + 1.0 / N_j_inv_df) *
+         (N_i_inv_df + N_j_inv_df);
+}
 // util.F90:663
 __device__ __forceinline__ double interp_linear_disc(double x_1, double x_n, int n, int i) {
   if (x_1 == x_n) return x_1;

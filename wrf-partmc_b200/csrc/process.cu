@@ -98,6 +98,7 @@ __global__ void __launch_bounds__(PROC_THREADS) k_partmc_process(DevView v, int 
 extern "C" int pmcgpu_partmc_process(pmcgpu_ctx* ctx, int n_bin, double d_min, double d_max, double* tot_num_conc,
                                      double* tot_wet_num_conc, double* tot_mass_conc, double* num_dist,
                                      double* mass_dist, double* num_conc_by_class, double* species_mass_conc) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_partmc_process");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || n_bin < 1 || n_bin > 2000 || !(d_min > 0.0) || !(d_max > d_min)) return PMCGPU_ERR_ARG;
   CUDA_OK(ctx, cudaSetDevice(ctx->cfg.device));
@@ -153,6 +154,7 @@ extern "C" int pmcgpu_partmc_process_static(pmcgpu_ctx* ctx, int n_bin, double d
                                             double* tot_num_conc, double* tot_wet_num_conc, double* tot_mass_conc,
                                             double* num_dist, double* mass_dist, double* num_conc_by_class,
                                             double* species_mass_conc) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_partmc_process_static");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || n_bin < 1 || n_bin > 2000 || !(d_min > 0.0) || !(d_max > d_min)) return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;

@@ -635,6 +635,7 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
 
 static int emit_run(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add);
 extern "C" int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_aero_state_add_aero_dist_sample");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   return emit_run(ctx, a, n_part_add);
 }
@@ -730,6 +731,7 @@ __global__ void k_seasalt_prop(int nx, int nz, int ny, const float* __restrict__
 }
 
 extern "C" int pmcgpu_seasalt_emissions(pmcgpu_ctx* ctx, const pmcgpu_seasalt_args* a, int* n_part_add) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_seasalt_emissions");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !a || !a->u10 || !a->v10 || !a->xland || !a->height || !a->weight_class || !(a->dt > 0.0)) return PMCGPU_ERR_ARG;
   DevView& v = ctx->v;

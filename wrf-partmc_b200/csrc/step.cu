@@ -118,6 +118,7 @@ extern "C" int pmcgpu_partmc_timestep(pmcgpu_ctx* ctx, const pmcgpu_timestep_arg
   // ---- wrf_to_partmc: keep the old (T, p) as env_state_initial, install the new env_state
   const bool chem = fmod(a->elapsed_time, a->chem_dt) == 0.0;  // wrf_pmc_driver.F90:189
   const bool cond = chem && a->do_condensation;
+  if (cond) PMC_SPHERICAL_ONLY(ctx, "pmcgpu_partmc_timestep with do_condensation");
   if (cond) {
     CUDA_OK(ctx, cudaMemcpyAsync(v.cond_T0, v.temp, nb, cudaMemcpyDeviceToDevice, st));
     CUDA_OK(ctx, cudaMemcpyAsync(v.cond_p0, v.pres, nb, cudaMemcpyDeviceToDevice, st));

@@ -999,6 +999,7 @@ static int tr_setup(pmcgpu_ctx* ctx) {
 }
 
 extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_args* a) {
+  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_wrf_pmc_trans_driver");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   if (!ctx || !a) return PMCGPU_ERR_ARG;
   int rc = tr_setup(ctx);

@@ -113,6 +113,10 @@ contains
     cfg%seed = seed
     cfg%device = local_rank
     call pmc_gpu_check(pmcgpu_create(cfg, pmc_gpu_handle), 'pmcgpu_create')
+    ! aero_data%fractal (fractal.F90:55-66): spherical in WRF-PartMC; a do_fractal run keeps coagulation with the
+    ! brown_free / brown_cont kernels and is refused by the calls that need the mobility radius (include/pmcgpu.h)
+    call pmc_gpu_check(pmcgpu_set_fractal(pmc_gpu_handle, aero_data%fractal%frac_dim, &
+         aero_data%fractal%prime_radius, aero_data%fractal%vol_fill_factor), 'pmcgpu_set_fractal')
   end subroutine pmc_gpu_init
 
   subroutine pmc_gpu_finalize()
@@ -835,6 +839,8 @@ contains
     cfg%seed = 1
     cfg%device = 0
     call pmc_gpu_check(pmcgpu_create(cfg, box), 'pmcgpu_create')
+    call pmc_gpu_check(pmcgpu_set_fractal(box, aero_data%fractal%frac_dim, aero_data%fractal%prime_radius, &
+         aero_data%fractal%vol_fill_factor), 'pmcgpu_set_fractal')
     allocate(counts(1), vol(max(n, 1), n_spec), wgroup(max(n, 1)), wclass(max(n, 1)), ids(max(n, 1)), &
          nprim(max(n, 1)), hyst(max(n, 1)), lct(max(n, 1)), gct(max(n, 1)))
     counts(1) = n

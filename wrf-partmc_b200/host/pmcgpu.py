@@ -17,6 +17,7 @@ import os
 import numpy as np
 
 KERNEL_SEDI, KERNEL_ADDITIVE, KERNEL_CONSTANT, KERNEL_BROWN, KERNEL_ZERO = 1, 2, 3, 4, 5
+KERNEL_BROWN_FREE, KERNEL_BROWN_CONT = 6, 7  # coag_kernel.F90:42-45
 WEIGHT_NONE, WEIGHT_POWER = 1, 2
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -534,6 +535,11 @@ class PartMCGPU:
         a = _f64(n_part_ideal)
         assert a.size == self.n_class * self.n_group
         self._chk(self.L.pmcgpu_set_n_part_ideal(self.h, _p(a)))
+
+    def set_fractal(self, frac_dim=3.0, prime_radius=1e-8, vol_fill_factor=1.0):
+        """aero_data%fractal (fractal.F90:55-82); no arguments = spherical.  Before the first sort of a run."""
+        self._chk(self.L.pmcgpu_set_fractal(self.h, C.c_double(frac_dim), C.c_double(prime_radius),
+                                            C.c_double(vol_fill_factor)))
 
     def check_status(self):
         self._chk(self.L.pmcgpu_check_status(self.h))
