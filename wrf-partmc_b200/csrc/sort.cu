@@ -56,8 +56,13 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
 // (rows read twice, scattered stores) takes the cells with n > n_split (n_split = -1: every cell).
 // s_st: how many of the S species rows the staged variant keeps in shared memory (the first s_st); the others are
 // streamed from HBM for the radius and gathered from the cell's own, just-read rows when the records leave.
-// geometric radius of fractal particles (pmcgpu_set_fractal); out of line: the spherical path keeps its code
-static __device__ __noinline__ double vol2rad_fractal(const DevView& v, double vol) { return fr_vol2rad(v, vol); }
+// geometric radius of fractal particles (pmcgpu_set_fractal, fractal.F90:106-121); out of line, so that the spherical
+// path keeps its code, and with scalar arguments: a reference to the by-value kernel parameter would put a copy of
+// the whole DevView on every thread's stack
+static __device__ __noinline__ double vol2rad_fractal(double vol, double r0, double fill, double df) {
+  const double x = pow(3.0 * vol / 4.0 / PmcConst::pi, 1.0 / 3.0) / r0;
+  return r0 * pow((x * x * x) * fill, 1.0 / df);
+}
 
 template <bool STAGED, int NT>
 __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, int n_split, int s_st, int n_lo) {
@@ -111,7 +116,7 @@ __global__ void __launch_bounds__(NT) k_sort_cells(DevView v, int edge_recheck, 
     } else {
       for (int s = 0; s < v.S; s++) vt += v.vol[(size_t)s * NS + base + p];  // aero_particle_volume
     }
-    const double r = v.fr_on ? vol2rad_fractal(v, vt) : vol2rad(vt);  // aero_particle_radius (aero_particle.F90:388-399)
+    const double r = v.fr_on ? vol2rad_fractal(vt, v.fr_r0, v.fr_fill, v.fr_df) : vol2rad(vt);  // aero_particle_radius (aero_particle.F90:388-399)
     if (STAGED)
       s_lnr[p] = log(r);
     else
