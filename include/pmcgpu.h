@@ -135,10 +135,12 @@ int pmcgpu_set_n_part_ideal(pmcgpu_ctx* ctx, const double* n_part_ideal);
  * spec_file_read_fractal fractal.F90:546-566).  Default: spherical particles (3, 1e-8, 1), which is what WRF-PartMC
  * runs with.  A non-spherical setting changes the geometric radius (fractal_vol2rad / fractal_rad2vol,
  * fractal.F90:106-158) that the sort, the majorant tables and mc_coag use, for the kernels brown_free, brown_cont,
- * additive, constant and zero.  NOT built for fractal particles: the mobility radius (fractal.F90:239-440), i.e. the
- * Brownian and sedimentation kernels (mc_coag returns PMCGPU_ERR_ARG) and condensation, dry deposition, emissions,
- * transport and the diagnostics, which return PMCGPU_ERR_ARG while a non-spherical setting is active.  Call before
- * the first sort of a run; every cell gets a new bin grid at its next sort. */
+ * additive, constant and zero, and the volume of the particles pmcgpu_aero_state_add_aero_dist_sample creates from
+ * their sampled geometric radius (aero_state.F90:817).  NOT built for fractal particles: the mobility radius
+ * (fractal.F90:239-440), i.e. the Brownian and sedimentation kernels (mc_coag returns PMCGPU_ERR_ARG) and
+ * condensation, dry deposition, sea salt, transport and the diagnostics, which return PMCGPU_ERR_ARG while a
+ * non-spherical setting is active.  Call before the first sort of a run; every cell gets a new bin grid at its
+ * next sort. */
 int pmcgpu_set_fractal(pmcgpu_ctx* ctx, double frac_dim, double prime_radius, double vol_fill_factor);
 
 /* ---- the path ---------------------------------------------------------- */

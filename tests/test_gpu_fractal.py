@@ -107,6 +107,33 @@ def test_fractal_coagulation_with_component_lists(mods):
     TC.assert_same_components(g, o, case, 0)
 
 
+def test_emission_samples_fractal_volumes(mods):
+    """aero_state_add_aero_dist_sample for fractal particles: the sampled GEOMETRIC radius becomes a volume through
+    fractal_rad2vol (aero_state.F90:817), the exponential mode through both conversions (aero_mode.F90:611); same
+    counts / ids / groups as the oracle, volumes to 1e-13 (two math libraries)"""
+    W, O = mods
+    fractal = (2.3, 6e-9, 1.2)
+    case = common.make_cells(4, 300, n_spec=3, n_class=2, seed=9, n_part_ideal=300.0)  # flat: exponential modes need it
+    g, o = both(W, O, case, fractal, cap=4000)
+    vf = np.array([[0.2, 0.8, 0.0], [0.0, 0.5, 0.5], [1.0, 0.0, 0.0]])
+    m = dict(mode_type=[1, 3, 2], weight_class=[1, 2, 2], char_radius=[3e-8, 2e-7, 5e-8], log10_std_dev=[0.25, 0.0, 0.0],
+             vol_frac=vf)
+    mag = case["wmag"][:, 0, 0]
+    for step in range(2):
+        num_conc = np.outer(np.array([50.0, 400.0, 0.0, 900.0]) * mag, [0.5, 0.2, 0.3])
+        n_dev = g.aero_state_add_aero_dist_sample(num_conc=num_conc, sample_prop=np.ones(4), characteristic_factor=60.0,
+                                                  create_time=10.0 * step, step=step, **m)
+        n_ora = [o.add_aero_dist_sample(c, num_conc=num_conc[c], sample_prop=1.0, characteristic_factor=60.0,
+                                        create_time=10.0 * step, step=step, **m) for c in range(4)]
+        assert np.array_equal(n_dev, n_ora) and sum(n_ora) > 300, (n_dev, n_ora)
+    common.assert_same_population(g, o, case, exact_fp=False, rtol=1e-13)
+    # a mono-disperse particle of geometric radius 2e-7 has the FRACTAL volume, well below the sphere's
+    P = g.get_particles()
+    vtot = P["vol"].sum(axis=0)
+    v_fr = 4.0 * np.pi * fractal[1] ** 3 / 3.0 * (2e-7 / fractal[1]) ** fractal[0] / fractal[2]
+    assert (np.abs(vtot / v_fr - 1.0) < 1e-12).sum() > 20 and v_fr < 0.2 * 4.0 * np.pi * 2e-7 ** 3 / 3.0
+
+
 def case_from_oracle(o, regime, seed):
     """the sampled initial state of the reference test as a case both sides are built from (same ids, same next id)"""
     q = o.get_cell(0)
@@ -179,6 +206,9 @@ def test_fractal_refusals(mods):
         g.condense_equilib_particles()
     with pytest.raises(W.PmcGpuError, match="fractal"):
         g.partmc_process(10, 1e-9, 1e-5)
+    with pytest.raises(W.PmcGpuError, match="fractal"):
+        g.seasalt_emissions(np.full((1, 2), 8.0), np.zeros((1, 2)), np.full((1, 2), 2.0), np.full((1, 2), 30.0), 1, 1, 2,
+                            1, 60.0, 600.0, step=3)
     with pytest.raises(W.PmcGpuError, match="fractal"):
         g.partmc_timestep(do_coagulation=True, do_condensation=True, chem_dt=60.0, step=1)
     g.mc_coag(W.KERNEL_BROWN_CONT, 1.0, step=1)  # built

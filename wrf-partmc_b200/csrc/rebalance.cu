@@ -473,7 +473,8 @@ __device__ __forceinline__ double aero_mode_number(int type, double num_conc, do
 __device__ double sample_mode_particle(int S, int type, double cr, double lsd, int wt, double we, double size_factor,
                                        const double* __restrict__ vf, const double* __restrict__ vs, RStream& s,
                                        double* vols, const SampTab& tab = SampTab{0, nullptr, nullptr},
-                                       double wm = 1.0) {
+                                       double wm = 1.0, double fr_df = 0.0, double fr_r0 = 0.0, double fr_fill = 0.0) {
+  // fr_df > 0: fractal particles, aero_data_rad2vol / aero_data_vol2rad (aero_mode.F90:611, aero_state.F90:817)
   // aero_mode_sample_radius
   double radius = cr;
   if (type == 4) {
@@ -514,9 +515,15 @@ __device__ double sample_mode_particle(int S, int type, double cr, double lsd, i
     }
     radius = pow(10.0, x);
   } else if (type == 2) {
-    radius = vol2rad(-rad2vol(cr) * log(s.next()));
+    if (fr_df > 0.0) {
+      const double v_exp = -(rad2vol(fr_r0) * pow(cr / fr_r0, fr_df) / fr_fill) * log(s.next());
+      const double x = pow(3.0 * v_exp / 4.0 / PmcConst::pi, 1.0 / 3.0) / fr_r0;
+      radius = fr_r0 * pow((x * x * x) * fr_fill, 1.0 / fr_df);
+    } else {
+      radius = vol2rad(-rad2vol(cr) * log(s.next()));
+    }
   }
-  const double total_vol = rad2vol(radius);
+  const double total_vol = (fr_df > 0.0) ? rad2vol(fr_r0) * pow(radius / fr_r0, fr_df) / fr_fill : rad2vol(radius);
   // aero_mode_sample_vols
     for (int it = 0; it < 1000000; it++) {
     double sum = 0.0;
@@ -595,7 +602,8 @@ __device__ int emit_cell(DevView& v, const EmitDev& e, int cell, int lane, doubl
       for (int i_samp = 1 + lane; i_samp <= n_samp; i_samp += 32) {
         RStream s{RKey{v.seed, gcell, e.step, PH_EMIT, a, (unsigned)i_samp}, 0u};
         double vols[PMC_MAX_SPEC];
-        const double radius = sample_mode_particle(v.S, type, cr, lsd, wt, we, size_factor, vf, vs, s, vols, tab, wm);
+        const double radius = sample_mode_particle(v.S, type, cr, lsd, wt, we, size_factor, vf, vs, s, vols, tab, wm,
+                                                   v.fr_on ? v.fr_df : 0.0, v.fr_r0, v.fr_fill);
         (void)radius;
         const int slot = n_cur + i_samp - 1;
         for (int k = 0; k < v.S; k++) v.vol[(size_t)k * NS + base + slot] = vols[k];
@@ -635,7 +643,6 @@ __global__ void __launch_bounds__(REB_WARPS * 32) k_emit(DevView v, EmitDev e) {
 
 static int emit_run(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add);
 extern "C" int pmcgpu_aero_state_add_aero_dist_sample(pmcgpu_ctx* ctx, const pmcgpu_emit_args* a, int* n_part_add) {
-  PMC_SPHERICAL_ONLY(ctx, "pmcgpu_aero_state_add_aero_dist_sample");
   if (ctx && cudaSetDevice(ctx->cfg.device) != cudaSuccess) return PMCGPU_ERR_CUDA;  // contexts may live on different devices
   return emit_run(ctx, a, n_part_add);
 }
