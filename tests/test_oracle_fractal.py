@@ -181,3 +181,23 @@ def test_mobility_radius_kernels_refuse_fractal_particles(fractal_setting):
     for kt in (O.KERNEL_BROWN, O.KERNEL_SEDI):
         with pytest.raises(Exception):
             o.mc_coag(0, kt, 1.0, step=1)
+
+
+def test_emitted_particles_have_fractal_volumes(fractal_setting):
+    """aero_state_add_aero_dist_sample: the sampled geometric radius goes through fractal_rad2vol
+    (aero_state.F90:817); the exponential mode draws a VOLUME with mean rad2vol(char_radius) (aero_mode.F90:611)"""
+    O = fractal_setting
+    df, R0, f = 2.3, 6e-9, 1.2
+    O.set_fractal(df, R0, f)
+    case = common.make_cells(1, 10, n_spec=1, seed=3, ragged=False, n_part_ideal=4000.0)
+    o = common.oracle_from_case(O, case)
+    mag = float(case["wmag"][0, 0, 0])
+    n = o.add_aero_dist_sample(0, [3, 2], [1, 1], [2e-7, 5e-8], [0.0, 0.0], [[1.0], [1.0]],
+                               [1500.0 * mag, 1500.0 * mag], 1.0, 60.0)
+    assert n > 2000
+    vol = o.get_cell(0)["vol"][0, 10:]
+    v_mono = 4.0 * np.pi * R0 ** 3 / 3.0 * (2e-7 / R0) ** df / f
+    mono = np.abs(vol / v_mono - 1.0) < 1e-12
+    assert 0.4 * n < mono.sum() < 0.6 * n and v_mono == pytest.approx(O.aero_rad2vol(2e-7), rel=1e-14)
+    v_exp_mean = 4.0 * np.pi * R0 ** 3 / 3.0 * (5e-8 / R0) ** df / f
+    assert vol[~mono].mean() == pytest.approx(v_exp_mean, rel=0.1)  # exponential in volume: sd of the mean ~ 3 %
