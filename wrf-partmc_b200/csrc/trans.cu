@@ -767,7 +767,13 @@ struct TrSeg {
   int off;        // offset in the list / slab
   int n;
 };
-__global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, TrSlab r0, TrSlab r1, TrSlab r2, TrSlab r3) {
+// The four receive slabs travel as ONE __grid_constant__ parameter: the side is chosen at run time, and a reference
+// picked among four by-value parameters made the compiler copy all of them (384 B) to every thread's stack at kernel
+// entry -- 1.6 GB of local-memory stores per launch on K4, more than the records the kernel moves.
+struct TrSlab4 {
+  TrSlab s[4];
+};
+__global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, const __grid_constant__ TrSlab4 rr) {
   const int cell = blockIdx.x;
   const int nx = t.nx, nz = t.nz, ny = t.ny, nd = TR_ND(t.nz);
   const int i = cell % nx, k = (cell / nx) % nz, j = cell / (nx * nz);
@@ -817,7 +823,7 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
         if (ok) {
           const int q = (side < 2) ? (k * nx + i) : (j * nz + k);
           kind = 2; src = side; off = t.roff[side][q]; cnt = t.roff[side][q + 1] - off;
-          const int pitch = (side == 0) ? r0.cap : (side == 1 ? r1.cap : (side == 2 ? r2.cap : r3.cap));
+          const int pitch = rr.s[side].cap;
           if (off + cnt > pitch) { cnt = 0; fail = 1; }  // the sender could not pack this cell (message pitch)
         }
       } else if (e < n_cand && v.kind) {
@@ -903,7 +909,7 @@ __global__ void __launch_bounds__(128, 8) k_tr_gather(DevView v, TransView t, Tr
     int r_wgc, r_nprim, r_hyst;
     double r_lct, r_gct;
     if (sg.kind == 2) {
-      const TrSlab& sl = (sg.src == 0) ? r0 : (sg.src == 1 ? r1 : (sg.src == 2 ? r2 : r3));
+      const TrSlab& sl = rr.s[sg.src];
       const size_t src = (size_t)sg.off + rel;
       r_id = sl.id[src]; r_wgc = sl.wgc[src]; r_nprim = sl.nprim[src]; r_hyst = sl.hyst[src];
       r_lct = sl.lct[src]; r_gct = sl.gct[src];
@@ -1161,7 +1167,9 @@ extern "C" int pmcgpu_wrf_pmc_trans_driver(pmcgpu_ctx* ctx, const pmcgpu_trans_a
       CUDA_OK(ctx, cudaFuncSetAttribute(k_tr_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seg_bytes));
       ctx->cfg_trans_smem = true;
     }
-    k_tr_gather<<<(unsigned)nc, 128, (size_t)tr_n_cand(t.nz, v.C) * sizeof(TrSeg), st>>>(v, t, rview[0], rview[1], rview[2], rview[3]);
+    TrSlab4 rr;
+    for (int q = 0; q < 4; q++) rr.s[q] = rview[q];
+    k_tr_gather<<<(unsigned)nc, 128, (size_t)tr_n_cand(t.nz, v.C) * sizeof(TrSeg), st>>>(v, t, rr);
     LAUNCH_CHECK(ctx);
   }
   if ((rc = pmc_rebalance_async(ctx, a->allow_doubling, a->allow_halving, a->step))) return rc;
